@@ -1,0 +1,170 @@
+"""skin_oracle.py -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+
+CPU (torch) restatement of the reference's skeleton skinning path, in the reference's own
+eager-op style so that, timed on the host cores, it is a fair stand-in for the reference's
+torch CPU skinning (the reference tree itself cannot travel to the GPU box).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module.
+
+Pinned against the real reference: tests/golden/make_skin_golden.py imports
+``skeleton_utils.skeleton_warp.SkeletonWarp`` and ``utils.dual_quaternion`` from
+/root/reference on the CPU and stores inputs + outputs (and autograd gradients) in
+tests/golden/skin_*.npz; tests/test_oracle_skin.py replays them through this file.
+
+Reference lines restated:
+  quaternion_to_matrix          utils/time_utils.py:115-132
+  matrix_to_quaternion          utils/time_utils.py:146-205
+  line_segment_distance         skeleton_utils/skeleton_warp.py:215-238
+  cal_nn_weight_skeleton (K=-1) skeleton_utils/skeleton_warp.py:41-76
+  chain_product_transform       skeleton_utils/skeleton_warp.py:242-273
+  deform_by_pose                skeleton_utils/skeleton_warp.py:130-172
+  QT2DQ / DQ2QT / DQBlending    utils/dual_quaternion.py:135-180
+  render() activations          gaussian_renderer/__init__.py:74-92, scene/gaussian_model.py:105-132
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+
+
+def quat_to_mat(q: torch.Tensor) -> torch.Tensor:
+    r, i, j, k = torch.unbind(q, -1)
+    two_s = 2.0 / (q * q).sum(-1)
+    o = torch.stack((1 - two_s * (j * j + k * k), two_s * (i * j - k * r), two_s * (i * k + j * r),
+                     two_s * (i * j + k * r), 1 - two_s * (i * i + k * k), two_s * (j * k - i * r),
+                     two_s * (i * k - j * r), two_s * (j * k + i * r), 1 - two_s * (i * i + j * j)), -1)
+    return o.reshape(q.shape[:-1] + (3, 3))
+
+
+def mat_to_quat(m: torch.Tensor) -> torch.Tensor:
+    """Four candidates, pick the one with the largest |component|; no sign standardisation."""
+    b = m.shape[:-2]
+    m00, m01, m02, m10, m11, m12, m20, m21, m22 = torch.unbind(m.reshape(b + (9,)), -1)
+    t = torch.stack([1.0 + m00 + m11 + m22, 1.0 + m00 - m11 - m22, 1.0 - m00 + m11 - m22,
+                     1.0 - m00 - m11 + m22], -1)
+    q_abs = torch.where(t > 0, torch.sqrt(t.clamp_min(0)), torch.zeros_like(t))
+    cand = torch.stack([
+        torch.stack([q_abs[..., 0] ** 2, m21 - m12, m02 - m20, m10 - m01], -1),
+        torch.stack([m21 - m12, q_abs[..., 1] ** 2, m10 + m01, m02 + m20], -1),
+        torch.stack([m02 - m20, m10 + m01, q_abs[..., 2] ** 2, m12 + m21], -1),
+        torch.stack([m10 - m01, m20 + m02, m21 + m12, q_abs[..., 3] ** 2], -1)], -2)
+    cand = cand / (2.0 * q_abs[..., None].clamp_min(0.1))
+    pick = q_abs.argmax(-1)
+    return torch.gather(cand, -2, pick[..., None, None].expand(b + (1, 4))).squeeze(-2)
+
+
+def bone_dist2(x: torch.Tensor, joints: torch.Tensor, parents: torch.Tensor) -> torch.Tensor:
+    """(N, J-1) squared distance from each point to bone segment parent(k) -> k, k = 1..J-1."""
+    b = joints[1:, :3]
+    a = joints[parents[1:].long(), :3]
+    p = x[:, None, :3]
+    ab = b - a
+    t = ((p - a) * ab).sum(-1, keepdim=True) / torch.clamp((ab * ab).sum(-1, keepdim=True), min=1e-6)
+    t = torch.clamp(t, 0.0, 1.0)
+    s = a + t * ab
+    return ((s - p) * (s - p)).sum(-1)
+
+
+def skin_weights(x, joints, parents, node_radius_raw, mlp_weight=None):
+    d2 = bone_dist2(x, joints, parents)
+    radius = torch.exp(node_radius_raw)[1:]
+    w = torch.exp(-d2 / (2 * radius ** 2))
+    if mlp_weight is not None:
+        w = w * mlp_weight
+    w = w + 1e-7
+    return w / w.sum(-1, keepdim=True), d2
+
+
+def forward_kinematics(local_rot_mats: torch.Tensor, joints: torch.Tensor, parents: torch.Tensor):
+    """Returns posed joints (J,3) and global transforms (J,4,4)."""
+    J = joints.shape[0]
+    vp = parents.clone().long()
+    vp[0] = 0
+    pj = joints[vp]
+    local_t = pj - torch.einsum("jab,jb->ja", local_rot_mats, pj)
+    T = torch.zeros(J, 4, 4, dtype=joints.dtype)
+    T[:, :3, :3] = local_rot_mats
+    T[:, :3, 3] = local_t
+    T[:, 3, 3] = 1.0
+    chain = [T[0]]
+    for i in range(1, J):
+        chain.append(chain[int(parents[i])] @ T[i])
+    G = torch.stack(chain, 0)
+    posed = torch.einsum("jab,jb->ja", G[:, :3, :3], joints) + G[:, :3, 3]
+    return posed, G
+
+
+def deform_by_pose(x, joints, parents, node_radius_raw, local_rotation, global_trans, motion_mask,
+                   mlp_weight=None, template_offsets=None):
+    """LBS core.  Returns the dict of the reference's third boundary."""
+    x = x.detach()
+    R_local = quat_to_mat(local_rotation)
+    w, _ = skin_weights(x, joints, parents, node_radius_raw, mlp_weight)
+    posed, G = forward_kinematics(R_local, joints[:, :3], parents)
+    G_R, G_t = G[:, :3, :3], G[:, :3, 3]
+    node_rot = mat_to_quat(G_R.detach())
+    Ax = torch.einsum("kab,nb->nka", G_R[1:], x) + G_t[1:][None]
+    Ax_avg = (Ax * w[..., None]).sum(1)
+    Ax_avg = Ax_avg + global_trans
+    if template_offsets is not None:
+        Ax_avg = Ax_avg + template_offsets
+    d_xyz = (Ax_avg - x) * motion_mask
+    d_rot = (node_rot[1:][None] * w[..., None]).sum(1) * motion_mask
+    return {"d_xyz": d_xyz, "d_rotation": d_rot, "d_scaling": torch.zeros(x.shape[0], 3, dtype=x.dtype),
+            "d_nodes": posed + global_trans, "nn_weight": w,
+            "nn_idx": torch.arange(1, joints.shape[0]).unsqueeze(0).expand(x.shape[0], -1),
+            "G": G, "node_rot": node_rot}
+
+
+# ---- dual-quaternion blending (utils/dual_quaternion.py) -------------------------------------
+
+def _qmul_raw(a, b):
+    aw, ax, ay, az = torch.unbind(a, -1)
+    bw, bx, by, bz = torch.unbind(b, -1)
+    return torch.stack((aw * bw - ax * bx - ay * by - az * bz, aw * bx + ax * bw + ay * bz - az * by,
+                        aw * by - ax * bz + ay * bw + az * bx, aw * bz + ax * by - ay * bx + az * bw), -1)
+
+
+def _qmul(a, b):
+    ab = _qmul_raw(a, b)
+    return torch.where(ab[..., 0:1] < 0, -ab, ab)
+
+
+def qt_to_dq(q, t):
+    q = F.normalize(q)  # note: dim=1, as the reference calls it (dual_quaternion.py:138)
+    tq = torch.cat([torch.zeros_like(t[..., :1]), t], -1)
+    return torch.cat([q, _qmul(tq, q) / 2], -1)
+
+
+def dq_to_rt(dq):
+    real, imag = dq[..., :4], dq[..., 4:]
+    n = real.norm(dim=-1, keepdim=True).clamp(min=1e-8)
+    real, imag = real / n, imag / n
+    w0, x0, y0, z0 = torch.unbind(real, -1)
+    w1, x1, y1, z1 = torch.unbind(imag, -1)
+    t = 2 * torch.stack([-w1 * x0 + x1 * w0 - y1 * z0 + z1 * y0, -w1 * y0 + x1 * z0 + y1 * w0 - z1 * x0,
+                         -w1 * z0 - x1 * y0 + y1 * x0 + z1 * w0], -1)
+    R = torch.stack([1 - 2 * y0 ** 2 - 2 * z0 ** 2, 2 * x0 * y0 - 2 * w0 * z0, 2 * x0 * z0 + 2 * w0 * y0,
+                     2 * x0 * y0 + 2 * w0 * z0, 1 - 2 * x0 ** 2 - 2 * z0 ** 2, 2 * y0 * z0 - 2 * w0 * x0,
+                     2 * x0 * z0 - 2 * w0 * y0, 2 * y0 * z0 + 2 * w0 * x0, 1 - 2 * x0 ** 2 - 2 * y0 ** 2],
+                    -1).reshape(*w0.shape, 3, 3)
+    return R, t
+
+
+def dq_blend(q, t, weights):
+    """q (K,4) already-normalised per-bone quats, t (K,3), weights (N,K) -> R (N,3,3), t (N,3)."""
+    dq = qt_to_dq(q, t)
+    avg = (dq[None] * weights[..., None]).sum(-2)
+    return dq_to_rt(avg)
+
+
+# ---- render() activations --------------------------------------------------------------------
+
+def activate(xyz, scaling_raw, rotation_raw, opacity_raw, d_xyz, d_rotation, d_scaling=0.0):
+    means3D = xyz + d_xyz
+    s = scaling_raw if scaling_raw.shape[-1] == 3 else scaling_raw[..., :1].repeat(1, 3)
+    scales = torch.exp(s) + d_scaling
+    rotations = F.normalize(rotation_raw + d_rotation)
+    opacity = torch.sigmoid(opacity_raw)
+    return means3D, scales, rotations, opacity
