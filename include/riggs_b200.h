@@ -1,0 +1,162 @@
+/*
+ * riggs_b200.h -- C ABI of libriggs_b200.so (sm_100a): the skin + splat-rasterize hot path of RigGS.
+ *
+ * Every entry point takes plain device pointers, sizes and a CUDA stream; no torch types cross this
+ * boundary.  All float data is fp32, all pointers are DEVICE pointers unless a comment says "host".
+ * Matrices `viewmatrix` / `projmatrix` are 16 floats in the reference's transposed storage
+ * (element [4*c + r] = M[r][c], scene/cameras.py:61-71).  A NULL optional pointer selects the other
+ * code path exactly like the reference's null tensors do (dgr/rasterize_points.cu:96-115).
+ *
+ * Return value: >= 0 on success (rg_rasterize_forward returns num_rendered), < 0 on error with the
+ * message available from rg_last_error().  With debug != 0 every launch is followed by a stream
+ * synchronise + error check, like the reference's CHECK_CUDA (dgr/cuda_rasterizer/auxiliary.h:166-173).
+ *
+ * Paths below are relative to the reference tree; dgr/ = submodules/diff-gaussian-rasterization/,
+ * knn/ = submodules/simple-knn/.
+ */
+#ifndef RIGGS_B200_H_INCLUDED
+#define RIGGS_B200_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* rg_stream_t; /* a cudaStream_t */
+
+/* Growable state buffers: the callee asks the caller for `bytes` of device memory and gets the base
+ * address back.  Replaces the three std::function<char*(size_t)> of
+ * dgr/cuda_rasterizer/rasterizer.h:33-35 (bound to torch resize_ lambdas at dgr/rasterize_points.cu:27-33). */
+typedef char* (*rg_alloc_fn)(void* ctx, size_t bytes);
+
+int rg_version(void);
+const char* rg_last_error(void);
+
+/* ---- rasterizer ------------------------------------------------------------------------------ */
+
+/* Sizes of the three opaque state buffers (replaces CudaRasterizer::required<T>,
+ * dgr/cuda_rasterizer/rasterizer_impl.h:64-71). */
+size_t rg_geom_bytes(int P);
+size_t rg_image_bytes(int width, int height);
+size_t rg_binning_bytes(int64_t num_rendered);
+
+/* Replaces CudaRasterizer::Rasterizer::forward (dgr/cuda_rasterizer/rasterizer.h:32-58,
+ * rasterizer_impl.cu:197-339; called from RasterizeGaussiansCUDA, dgr/rasterize_points.cu:91-116).
+ * Stages: preprocess -> scan -> [one 4-byte D2H read of num_rendered, as the reference does] ->
+ * key emission -> stable radix sort -> per-tile ranges -> alpha blend.
+ * out_color (3,H,W), out_depth (1,H,W), out_alpha (1,H,W), radii (P) int32 are fully written. */
+int rg_rasterize_forward(rg_alloc_fn geom_alloc, void* geom_ctx, rg_alloc_fn binning_alloc, void* binning_ctx,
+                         rg_alloc_fn image_alloc, void* image_ctx, int P, int D, int M,
+                         const float* background, int width, int height, const float* means3D,
+                         const float* shs, const float* colors_precomp, const float* opacities,
+                         const float* scales, float scale_modifier, const float* rotations,
+                         const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                         const float* cam_pos, float tan_fovx, float tan_fovy, int prefiltered,
+                         float* out_color, float* out_depth, float* out_alpha, int* radii, int debug,
+                         rg_stream_t stream);
+
+/* Replaces CudaRasterizer::Rasterizer::backward (dgr/cuda_rasterizer/rasterizer.h:60-89,
+ * rasterizer_impl.cu:343-447; called from RasterizeGaussiansBackwardCUDA, dgr/rasterize_points.cu:171-204).
+ * Every output is fully written by the kernels (no zero-initialisation needed by the caller):
+ * dL_dmean2D (P,3) [z = 0], dL_dconic (P,4) [.z = 0], dL_dopacity (P), dL_dcolor (P,3), dL_ddepth (P),
+ * dL_dmean3D (P,3), dL_dcov3D (P,6), dL_dsh (P,M,3) or NULL, dL_dscale (P,3) / dL_drot (P,4) or NULL. */
+int rg_rasterize_backward(int P, int D, int M, int R, const float* background, int width, int height,
+                          const float* means3D, const float* shs, const float* colors_precomp,
+                          const float* alphas, const float* scales, float scale_modifier,
+                          const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                          const float* projmatrix, const float* campos, float tan_fovx, float tan_fovy,
+                          const int* radii, char* geom_buffer, char* binning_buffer, char* image_buffer,
+                          const float* dL_dpix, const float* dL_dpix_depth, const float* dL_dalphas,
+                          float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+                          float* dL_ddepth, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
+                          float* dL_dscale, float* dL_drot, int debug, rg_stream_t stream);
+
+/* Replaces CudaRasterizer::Rasterizer::markVisible (dgr/cuda_rasterizer/rasterizer.h:25-30,
+ * rasterizer_impl.cu:141-153).  present: P bytes (bool). */
+int rg_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                    uint8_t* present, rg_stream_t stream);
+
+/* Addresses of the arrays inside the opaque buffers, for tests and debuggers (the reference keeps the
+ * same information in GeometryState / BinningState / ImageState, dgr/cuda_rasterizer/rasterizer_impl.h:30-61).
+ * out[0]=depths f32[P]            out[1]=clamped u8[P] (bit c = channel c clamped)
+ * out[2]=means2D f32x2[P]         out[3]=conic_opacity f32x4[P]      out[4]=rgb f32[3P]
+ * out[5]=tiles_touched u32[P]     out[6]=point_offsets u32[P] (inclusive scan)
+ * out[7]=cov3D f32[6P]
+ * out[8]=point_list u32[R]        out[9]=point_list_unsorted u32[R]
+ * out[10]=point_list_keys u64[R]  out[11]=point_list_keys_unsorted u64[R]
+ * out[12]=n_contrib u32[H*W]      out[13]=ranges u32x2[tiles] */
+int rg_state_ptrs(int P, int64_t R, int width, int height, char* geom_buffer, char* binning_buffer,
+                  char* image_buffer, void** out /* host, 14 entries */);
+
+/* ---- simple-knn -------------------------------------------------------------------------------- */
+
+/* Replaces SimpleKNN::knn (knn/simple_knn.h:18, knn/simple_knn.cu:186-221; bound by distCUDA2,
+ * knn/spatial.cu:15-26): mean squared distance of every point to its 3 nearest other points.
+ * scratch: device memory of rg_knn_scratch_bytes(P) bytes, caller-owned. */
+size_t rg_knn_scratch_bytes(int P);
+int rg_dist_cuda2(int P, const float* points, float* mean_dists, char* scratch, size_t scratch_bytes,
+                  rg_stream_t stream);
+
+/* ---- skeleton skinning -------------------------------------------------------------------------- */
+
+/* Per-frame bone table produced by forward kinematics and consumed by the skinning kernels:
+ *   G        (F,J,12)  global transform of every joint: row-major 3x3 rotation then translation
+ *   node_rot (F,J,4)   matrix_to_quaternion(G_R) (utils/time_utils.py:146-205), no sign standardisation
+ *   posed    (F,J,3)   posed joints + global_trans  (= d_nodes, skeleton_utils/skeleton_warp.py:146)
+ * Replaces quaternion_to_matrix (utils/time_utils.py:115-132), SkeletonWarp.chain_product_transform
+ * (skeleton_utils/skeleton_warp.py:242-273) and matrix_to_quaternion for F poses at once.
+ * local_rot (F,J,4) un-normalised quaternions, global_trans (F,3), joints (J,3) rest pose,
+ * parents (J) int32 with parents[0] = -1 and parents[i] < i. */
+int rg_fk_forward(int F, int J, const float* local_rot, const float* global_trans, const float* joints,
+                  const int* parents, float* G, float* node_rot, float* posed, rg_stream_t stream);
+
+/* Reverse of rg_fk_forward (the reference relies on torch autograd through the same ops):
+ * dG (F,J,12), dposed (F,J,3) or NULL  ->  dlocal_rot (F,J,4), dglobal_trans_from_posed (F,3) or NULL.
+ * dG_scratch: F*J*12 floats of caller-owned device scratch, overwritten (running per-joint gradient of
+ * the global transforms while the chain is walked back from the leaves). */
+int rg_fk_backward(int F, int J, const float* local_rot, const float* joints, const int* parents,
+                   const float* G, const float* dG, const float* dposed, float* dG_scratch,
+                   float* dlocal_rot, float* dglobal_trans, rg_stream_t stream);
+
+/* Linear-blend skinning of N points by the J-1 bones of one pose.  Replaces
+ * SkeletonWarp.cal_nn_weight_skeleton with K = -1 and the LBS part of SkeletonWarp.deform_by_pose
+ * (skeleton_utils/skeleton_warp.py:41-76, 130-172, 207-238):
+ *   d_xyz = mask * (sum_k w_k (R_k x + t_k) + global_trans + offsets - x),  d_rot = mask * sum_k w_k q_k.
+ * blend_mode 0 = linear blend (what the reference runs); 1 = dual-quaternion blend of the bone
+ * transforms (utils/dual_quaternion.py:135-180) for d_xyz, d_rot then holds the blended unit quaternion.
+ * Optional (NULL = absent): motion_mask (N), mlp_weight (N,J-1) = sigmoid(WeightMLP(x)),
+ * offsets (N,3) = detail_net output, nn_weight (N,J-1) output. */
+int rg_skin_forward(int N, int J, const float* xyz, const float* joints, const int* parents,
+                    const float* node_radius_raw, const float* G, const float* node_rot,
+                    const float* global_trans, const float* motion_mask, const float* mlp_weight,
+                    const float* offsets, int blend_mode, float* d_xyz, float* d_rot, float* nn_weight,
+                    rg_stream_t stream);
+
+/* Backward of rg_skin_forward (blend_mode 0).  Inputs: g_dxyz (N,3), g_drot (N,4).
+ * Outputs: dG (J,12) and dnode_radius_raw (J) and dglobal_trans (3) are ACCUMULATED with atomics and
+ * must be zeroed by the caller; dmask (N), dmlp_weight (N,J-1), doffsets (N,3) are written (NULL = skip).
+ * No gradient flows to xyz (x.detach(), skeleton_warp.py:131) nor through node_rot (:144). */
+int rg_skin_backward(int N, int J, const float* xyz, const float* joints, const int* parents,
+                     const float* node_radius_raw, const float* G, const float* node_rot,
+                     const float* global_trans, const float* motion_mask, const float* mlp_weight,
+                     const float* offsets, const float* g_dxyz, const float* g_drot, float* dG,
+                     float* dnode_radius_raw, float* dglobal_trans, float* dmask, float* dmlp_weight,
+                     float* doffsets, rg_stream_t stream);
+
+/* ---- measurement aids (no counterpart in the reference; used by bench.py) ------------------------ */
+
+/* Kernels of this library launched since it was loaded (library sort passes are not counted). */
+long long rg_launch_count(void);
+/* Per-kernel device timing: when enabled every launch is bracketed by CUDA events on its stream.
+ * rg_profile_get synchronises on the recorded events and returns the summed milliseconds per kernel name. */
+void rg_profile_enable(int on);
+void rg_profile_reset(void);
+int rg_profile_count(void);
+int rg_profile_get(int index, char* name_out, int name_cap, float* total_ms, int* launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RIGGS_B200_H_INCLUDED */

@@ -1,0 +1,131 @@
+"""ctypes binding of libriggs_b200.so (the C ABI declared in include/riggs_b200.h).
+
+There is no CPU fallback: if the shared library is missing this module raises at first use, and every
+wrapper raises when handed a non-CUDA tensor.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libriggs_b200.so")
+
+ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_size_t)
+_p = C.c_void_p
+_f = C.c_float
+_i = C.c_int
+
+_SIGNATURES = {
+    "rg_version": (C.c_int, []),
+    "rg_last_error": (C.c_char_p, []),
+    "rg_geom_bytes": (C.c_size_t, [_i]),
+    "rg_image_bytes": (C.c_size_t, [_i, _i]),
+    "rg_binning_bytes": (C.c_size_t, [C.c_int64]),
+    "rg_rasterize_forward": (C.c_int, [ALLOC_FN, _p, ALLOC_FN, _p, ALLOC_FN, _p, _i, _i, _i, _p, _i, _i, _p, _p, _p,
+                                       _p, _p, _f, _p, _p, _p, _p, _p, _f, _f, _i, _p, _p, _p, _p, _i, _p]),
+    "rg_rasterize_backward": (C.c_int, [_i, _i, _i, _i, _p, _i, _i, _p, _p, _p, _p, _p, _f, _p, _p, _p, _p, _p, _f,
+                                        _f, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i,
+                                        _p]),
+    "rg_mark_visible": (C.c_int, [_i, _p, _p, _p, _p, _p]),
+    "rg_state_ptrs": (C.c_int, [_i, C.c_int64, _i, _i, _p, _p, _p, C.POINTER(C.c_void_p)]),
+    "rg_knn_scratch_bytes": (C.c_size_t, [_i]),
+    "rg_dist_cuda2": (C.c_int, [_i, _p, _p, _p, C.c_size_t, _p]),
+    "rg_fk_forward": (C.c_int, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "rg_fk_backward": (C.c_int, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "rg_skin_forward": (C.c_int, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _p]),
+    "rg_skin_backward": (C.c_int, [_i, _i] + [_p] * 19),
+    "rg_launch_count": (C.c_longlong, []),
+    "rg_profile_enable": (None, [_i]),
+    "rg_profile_reset": (None, []),
+    "rg_profile_count": (C.c_int, []),
+    "rg_profile_get": (C.c_int, [_i, C.c_char_p, _i, C.POINTER(C.c_float), C.POINTER(C.c_int)]),
+}
+
+_lib: Optional[C.CDLL] = None
+
+
+def exported_symbols():
+    """Names of every entry point include/riggs_b200.h declares."""
+    return list(_SIGNATURES)
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -m riggs_b200.build` "
+                "(riggs_b200 has no CPU or PyTorch fallback)")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+class RiggsError(RuntimeError):
+    pass
+
+
+def check(rc: int, what: str) -> int:
+    if rc < 0:
+        raise RiggsError(f"{what}: {lib().rg_last_error().decode()}")
+    return rc
+
+
+def ptr(t: Optional[torch.Tensor]):
+    """Device address of a tensor, or NULL for None / empty tensors (the reference's null-pointer convention)."""
+    if t is None or t.numel() == 0:
+        return None
+    if not t.is_cuda:
+        raise RiggsError("riggs_b200 kernels need CUDA tensors; there is no CPU path")
+    return t.data_ptr()
+
+
+def stream_ptr() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def f32c(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    """contiguous fp32 view, 16-byte aligned (clones when a view is mis-aligned)."""
+    if t is None:
+        return None
+    if t.dtype != torch.float32:
+        t = t.float()
+    t = t.contiguous()
+    if t.numel() and t.data_ptr() % 16:
+        t = t.clone()
+    return t
+
+
+def profile_read():
+    """{kernel name: (total_ms, launches)} of everything recorded since the last reset."""
+    L = lib()
+    out = {}
+    for i in range(L.rg_profile_count()):
+        name = C.create_string_buffer(64)
+        ms, n = C.c_float(), C.c_int()
+        if L.rg_profile_get(i, name, 64, C.byref(ms), C.byref(n)) == 0:
+            out[name.value.decode()] = (ms.value, n.value)
+    return out
+
+
+class GrowBuffer:
+    """A growable uint8 CUDA tensor handed to the library as an rg_alloc_fn, the analogue of the reference's
+    resizeFunctional lambdas (dgr/rasterize_points.cu:27-33)."""
+
+    def __init__(self, device):
+        self.t = torch.empty(0, dtype=torch.uint8, device=device)
+
+        def _alloc(_ctx, nbytes):
+            if self.t.numel() < nbytes:
+                self.t = torch.empty(int(nbytes), dtype=torch.uint8, device=device)
+            return self.t.data_ptr()
+
+        self.fn = ALLOC_FN(_alloc)

@@ -1,0 +1,86 @@
+// Shared helpers for the sm_100a kernels of libriggs_b200.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+
+#define RG_TILE 16                 // tile edge in pixels (reference: BLOCK_X = BLOCK_Y = 16, dgr/cuda_rasterizer/config.h)
+#define RG_TILE_PIX (RG_TILE * RG_TILE)
+#define RG_NUM_SMS 148
+
+namespace rg {
+
+void set_error(const std::string& msg);
+// Returns 0 when the last launch (and, in debug mode, its execution) succeeded.
+int check_launch(const char* what, cudaStream_t stream, bool debug);
+
+// Counts kernel launches and, when profiling is enabled (rg_profile_enable), brackets them with CUDA events on
+// the launching stream.
+class LaunchScope {
+public:
+    LaunchScope(const char* name, cudaStream_t stream, int n_kernels = 1);
+    ~LaunchScope();
+private:
+    const char* name_;
+    cudaStream_t stream_;
+    cudaEvent_t start_;
+    bool on_;
+};
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// Carves typed arrays out of one opaque byte buffer, 256-byte aligned.
+struct Carver {
+    char* base;
+    size_t off = 0;
+    explicit Carver(char* b) : base(b) {}
+    template <typename T>
+    T* take(size_t count) {
+        off = align_up(off, 256);
+        T* p = reinterpret_cast<T*>(base + off);
+        off += count * sizeof(T);
+        return p;
+    }
+};
+
+// Per-Gaussian state kept between forward and backward ("geometry buffer").
+struct GeomState {
+    float* depths;            // P
+    uint8_t* clamped;         // P, bit c set when colour channel c was clamped at 0
+    float2* means2D;          // P
+    float4* conic_opacity;    // P
+    float* rgb;               // 3P
+    uint32_t* tiles_touched;  // P
+    uint32_t* point_offsets;  // P inclusive scan of tiles_touched
+    float* cov3D;             // 6P
+    uint32_t* block_sums;     // ceil(P / SCAN_ITEMS) partial sums + total at [nblocks]
+    uint32_t* grad_acc;       // 10P floats: per-Gaussian 2-D gradient accumulators of the backward blend
+    static GeomState carve(char* base, size_t P, size_t* bytes);
+};
+
+struct ImageState {
+    uint32_t* n_contrib;  // H*W
+    uint2* ranges;        // tiles
+    static ImageState carve(char* base, int W, int H, size_t* bytes);
+};
+
+struct BinningState {
+    uint32_t* point_list;
+    uint32_t* point_list_unsorted;
+    uint64_t* keys;
+    uint64_t* keys_unsorted;
+    char* sort_temp;
+    size_t sort_temp_bytes;
+    static BinningState carve(char* base, size_t R, size_t* bytes);
+};
+
+size_t sort_temp_bytes(size_t R);
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+}  // namespace rg

@@ -188,7 +188,7 @@ def slerp_pose_sequence(J: int, n_frames: int, g: torch.Generator, n_keys: int =
 def make_scene(N: int, J: int, width: int, height: int, n_views: int = 1, n_poses: Optional[int] = None,
                seed: int = 1234, isotropic: bool = False, soft_mask: bool = False,
                with_mlp_weight: bool = False, with_offsets: bool = False,
-               pose_sequence: bool = False, scale_mu: float = 0.012) -> Scene:
+               pose_sequence: bool = False, scale_mu: float = 0.012, cam_radius: float = 4.0) -> Scene:
     g = _gen(seed)
     joints, parents = make_skeleton(J, g)
     bone = torch.randint(1, J, (N,), generator=g)
@@ -210,7 +210,7 @@ def make_scene(N: int, J: int, width: int, height: int, n_views: int = 1, n_pose
     scene_range = xyz.max() - xyz.min()
     node_radius_raw = torch.log(0.1 * scene_range + 1e-7) * torch.ones(J)
     node_radius_raw = node_radius_raw + 0.2 * torch.randn(J, generator=g)
-    cams = make_cameras(n_views, width, height, g)
+    cams = make_cameras(n_views, width, height, g, radius=cam_radius)
     n_poses = n_views if n_poses is None else n_poses
     if pose_sequence:
         poses = slerp_pose_sequence(J, n_poses, g)
@@ -234,8 +234,9 @@ CONFIGS = {
     "C5": dict(N=2_000_000, J=60, width=800, height=800, n_views=1, n_poses=256, seed=1239,
                pose_sequence=True),
     # small parity cases
-    "tiny": dict(N=4096, J=6, width=128, height=128, n_views=2, seed=7),
-    "small": dict(N=20_000, J=24, width=256, height=192, n_views=2, seed=11),
+    "tiny": dict(N=4096, J=6, width=128, height=128, n_views=2, seed=7, cam_radius=1.2),
+    "small": dict(N=20_000, J=24, width=256, height=192, n_views=2, seed=11, cam_radius=3.0),
+    "ragged": dict(N=3001, J=7, width=97, height=61, n_views=1, seed=13, cam_radius=1.0, scale_mu=0.02),
 }
 
 
