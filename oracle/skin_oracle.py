@@ -83,7 +83,7 @@ def forward_kinematics(local_rot_mats: torch.Tensor, joints: torch.Tensor, paren
     vp[0] = 0
     pj = joints[vp]
     local_t = pj - torch.einsum("jab,jb->ja", local_rot_mats, pj)
-    T = torch.zeros(J, 4, 4, dtype=joints.dtype)
+    T = torch.zeros(J, 4, 4, dtype=joints.dtype, device=joints.device)
     T[:, :3, :3] = local_rot_mats
     T[:, :3, 3] = local_t
     T[:, 3, 3] = 1.0
@@ -111,9 +111,10 @@ def deform_by_pose(x, joints, parents, node_radius_raw, local_rotation, global_t
         Ax_avg = Ax_avg + template_offsets
     d_xyz = (Ax_avg - x) * motion_mask
     d_rot = (node_rot[1:][None] * w[..., None]).sum(1) * motion_mask
-    return {"d_xyz": d_xyz, "d_rotation": d_rot, "d_scaling": torch.zeros(x.shape[0], 3, dtype=x.dtype),
+    return {"d_xyz": d_xyz, "d_rotation": d_rot,
+            "d_scaling": torch.zeros(x.shape[0], 3, dtype=x.dtype, device=x.device),
             "d_nodes": posed + global_trans, "nn_weight": w,
-            "nn_idx": torch.arange(1, joints.shape[0]).unsqueeze(0).expand(x.shape[0], -1),
+            "nn_idx": torch.arange(1, joints.shape[0], device=x.device).unsqueeze(0).expand(x.shape[0], -1),
             "G": G, "node_rot": node_rot}
 
 

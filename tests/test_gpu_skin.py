@@ -105,7 +105,8 @@ def test_skin_vs_torch_oracle(cfg):
              ("g_template_offsets", None if o is None else o.grad)]
     for k, r in pairs:
         if r is not None:
-            assert helpers.rel_err(out[k].detach().cpu().numpy().reshape(-1), r.numpy().reshape(-1)) <= GRAD_RTOL, k
+            # floor: with a single bone the normalised weight is 1 and several gradients are exactly zero
+            assert helpers.rel_err(out[k].detach().cpu().numpy().reshape(-1), r.numpy().reshape(-1), floor=1e-6) <= GRAD_RTOL, k
 
 
 def test_fk_batched_sequence():
