@@ -1,13 +1,18 @@
-// Forward alpha blend: one CTA per 16x16 tile, one thread per pixel, front-to-back over the tile's depth-sorted
-// instance range.  Replaces renderCUDA (dgr/cuda_rasterizer/forward.cu:261-381).
+// Forward alpha blend: one CTA per 16x16 tile, front-to-back over the tile's depth-sorted instance range.
+// Replaces renderCUDA (dgr/cuda_rasterizer/forward.cu:261-381).
 //
-// Differences in HOW (results are the same):
-//  * colour and depth of each staged instance are gathered once per tile into shared memory together with
-//    xy / conic / opacity, instead of being fetched from global memory per contributing (pixel, instance) pair;
-//  * a per-instance log-threshold rejects pairs whose alpha would be < 1/255 before evaluating expf.  The test
-//    is conservative (margin far above the rounding error of expf/logf); every pair it lets through takes the
-//    reference's exact expression, so blended values and n_contrib are unchanged.
+// Differences in HOW (results are the same, see cull.cuh for the argument):
+//  * a warp owns an 8x4 pixel block of the tile.  Every batch of 256 staged instances is first filtered per
+//    warp (ellipse-vs-block test, 8 instances per lane, ballot-compacted into a per-warp list in shared
+//    memory); the per-pixel loop then runs over that list only.  On the C0 workload this removes ~3/4 of
+//    the (pixel, instance) evaluations and lets warps whose pixels are saturated or outside the silhouette
+//    skim through long lists at the cost of the filter alone;
+//  * colour and depth of each staged instance are gathered once per tile into shared memory instead of
+//    being fetched from global memory per contributing pair;
+//  * survivors take the reference's exact expression (same power / alpha / T tests), after a conservative
+//    log-threshold pre-test that avoids expf for pairs that are certainly below 1/255.
 #include "common.cuh"
+#include "cull.cuh"
 #include "kernels.cuh"
 
 namespace rg {
@@ -15,12 +20,17 @@ namespace rg {
 constexpr float kSkipMargin = 1e-4f;
 
 __global__ void __launch_bounds__(RG_TILE_PIX) blend_forward_kernel(BlendFwdArgs a) {
-    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-    const uint2 pix = {blockIdx.x * RG_TILE + tx, blockIdx.y * RG_TILE + ty};
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // warp -> 8x4 block: 2 blocks across, 4 down
+    const int bx0 = (warp & 1) * kBlkW, by0 = (warp >> 1) * kBlkH;
+    const uint2 pix = {blockIdx.x * RG_TILE + bx0 + (lane & 7), blockIdx.y * RG_TILE + by0 + (lane >> 3)};
     const uint32_t pix_id = a.W * pix.y + pix.x;
     const float2 pixf = {(float)pix.x, (float)pix.y};
     const bool inside = pix.x < (unsigned)a.W && pix.y < (unsigned)a.H;
     bool done = !inside;
+    const float tile_x0 = (float)(blockIdx.x * RG_TILE), tile_y0 = (float)(blockIdx.y * RG_TILE);
+    const float blk_x0 = tile_x0 + bx0, blk_y0 = tile_y0 + by0;
+    const float blk_x1 = blk_x0 + (kBlkW - 1), blk_y1 = blk_y0 + (kBlkH - 1);
 
     const uint2 range = a.ranges[blockIdx.y * a.grid_x + blockIdx.x];
     const int rounds = ((range.y - range.x + RG_TILE_PIX - 1) / RG_TILE_PIX);
@@ -30,28 +40,46 @@ __global__ void __launch_bounds__(RG_TILE_PIX) blend_forward_kernel(BlendFwdArgs
     __shared__ float4 s_co[RG_TILE_PIX];
     __shared__ float4 s_rgbd[RG_TILE_PIX];
     __shared__ float s_thr[RG_TILE_PIX];
+    __shared__ CullRec s_cull[RG_TILE_PIX];
+    __shared__ uint8_t s_list[8][RG_TILE_PIX];
 
     float T = 1.0f;
-    uint32_t contributor = 0, last_contributor = 0;
+    uint32_t last_contributor = 0;
     float C0 = 0.f, C1 = 0.f, C2 = 0.f, weight = 0.f, D = 0.f;
 
     for (int i = 0; i < rounds; i++, toDo -= RG_TILE_PIX) {
         int num_done = __syncthreads_count(done);
         if (num_done == RG_TILE_PIX) break;
-        int progress = i * RG_TILE_PIX + threadIdx.x;
+        const int progress = i * RG_TILE_PIX + tid;
         if (range.x + progress < range.y) {
             const uint32_t id = a.point_list[range.x + progress];
-            s_xy[threadIdx.x] = a.means2D[id];
+            const float2 xy = a.means2D[id];
             const float4 co = a.conic_opacity[id];
-            s_co[threadIdx.x] = co;
-            s_rgbd[threadIdx.x] = {a.colors[3 * id], a.colors[3 * id + 1], a.colors[3 * id + 2], a.depths[id]};
-            // alpha = o*exp(power) < 1/255  <=>  power < -log(255*o)
-            s_thr[threadIdx.x] = -logf(255.0f * co.w) - kSkipMargin;
+            s_xy[tid] = xy;
+            s_co[tid] = co;
+            s_rgbd[tid] = {a.colors[3 * id], a.colors[3 * id + 1], a.colors[3 * id + 2], a.depths[id]};
+            s_thr[tid] = -logf(255.0f * co.w) - kSkipMargin;  // alpha < 1/255  <=>  power < -log(255 o)
+            s_cull[tid] = make_cull(xy, co, tile_x0, tile_y0);
         }
         __syncthreads();
         const int n = min(RG_TILE_PIX, toDo);
-        for (int j = 0; !done && j < n; j++) {
-            contributor++;
+        if (__all_sync(0xffffffffu, done)) continue;  // this warp's block is finished; keep helping with loads
+        // ---- per-warp filter: which of the n staged instances can reach this 8x4 block?
+        int cnt = 0;
+#pragma unroll
+        for (int k = 0; k < RG_TILE_PIX / 32; k++) {
+            const int e = k * 32 + lane;
+            bool keep = false;
+            if (e < n) keep = cull_keep(s_cull[e], s_xy[e], s_co[e], blk_x0, blk_y0, blk_x1, blk_y1);
+            const unsigned m = __ballot_sync(0xffffffffu, keep);
+            if (keep) s_list[warp][cnt + __popc(m & ((1u << lane) - 1))] = (uint8_t)e;
+            cnt += __popc(m);
+        }
+        __syncwarp();
+        // ---- per-pixel blend over the surviving instances, in list (= depth) order
+        const uint32_t base = (uint32_t)i * RG_TILE_PIX;
+        for (int l = 0; !done && l < cnt; l++) {
+            const int j = s_list[warp][l];
             const float2 xy = s_xy[j];
             const float2 d = {xy.x - pixf.x, xy.y - pixf.y};
             const float4 con_o = s_co[j];
@@ -72,7 +100,7 @@ __global__ void __launch_bounds__(RG_TILE_PIX) blend_forward_kernel(BlendFwdArgs
             weight += alpha * T;
             D += c.w * alpha * T;
             T = test_T;
-            last_contributor = contributor;
+            last_contributor = base + j + 1;  // 1-based position in the tile's range, as the reference counts
         }
     }
     if (inside) {
