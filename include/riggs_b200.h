@@ -38,14 +38,16 @@ const char* rg_last_error(void);
 
 /* Sizes of the three opaque state buffers (replaces CudaRasterizer::required<T>,
  * dgr/cuda_rasterizer/rasterizer_impl.h:64-71). */
-size_t rg_geom_bytes(int P);
+size_t rg_geom_bytes(int P, int width, int height);
 size_t rg_image_bytes(int width, int height);
 size_t rg_binning_bytes(int64_t num_rendered);
 
 /* Replaces CudaRasterizer::Rasterizer::forward (dgr/cuda_rasterizer/rasterizer.h:32-58,
  * rasterizer_impl.cu:197-339; called from RasterizeGaussiansCUDA, dgr/rasterize_points.cu:91-116).
- * Stages: preprocess -> scan -> [one 4-byte D2H read of num_rendered, as the reference does] ->
- * key emission -> stable radix sort -> per-tile ranges -> alpha blend.
+ * Stages: preprocess -> depth sort of the Gaussians -> per-tile instance counts and ranges ->
+ * [one 4-byte D2H read of num_rendered, as the reference does, to size the binning buffer] ->
+ * in-order scatter of the instance ids into their tiles -> alpha blend.  The instance list equals the
+ * reference's sorted point_list (same tiles, same depth order, same tie order); no 64-bit keys are built.
  * out_color (3,H,W), out_depth (1,H,W), out_alpha (1,H,W), radii (P) int32 are fully written. */
 int rg_rasterize_forward(rg_alloc_fn geom_alloc, void* geom_ctx, rg_alloc_fn binning_alloc, void* binning_ctx,
                          rg_alloc_fn image_alloc, void* image_ctx, int P, int D, int M,
@@ -80,15 +82,19 @@ int rg_mark_visible(int P, const float* means3D, const float* viewmatrix, const 
 
 /* Addresses of the arrays inside the opaque buffers, for tests and debuggers (the reference keeps the
  * same information in GeometryState / BinningState / ImageState, dgr/cuda_rasterizer/rasterizer_impl.h:30-61).
- * out[0]=depths f32[P]            out[1]=clamped u8[P] (bit c = channel c clamped)
+ * out[0]=depths f32[P] (+inf where culled)  out[1]=clamped u8[P] (bit c = channel c clamped)
  * out[2]=means2D f32x2[P]         out[3]=conic_opacity f32x4[P]      out[4]=rgb f32[3P]
- * out[5]=tiles_touched u32[P]     out[6]=point_offsets u32[P] (inclusive scan)
- * out[7]=cov3D f32[6P]
- * out[8]=point_list u32[R]        out[9]=point_list_unsorted u32[R]
- * out[10]=point_list_keys u64[R]  out[11]=point_list_keys_unsorted u64[R]
- * out[12]=n_contrib u32[H*W]      out[13]=ranges u32x2[tiles] */
+ * out[5]=tiles_touched u32[P]     out[6]=ids in depth order u32[P]   out[7]=means3D f32[3P] (fused entry only)
+ * out[8]=point_list u32[R]        out[9]=n_contrib u32[H*W]          out[10]=ranges u32x2[tiles]
+ * out[11]=status u32[2]: num_rendered, overflow flag */
 int rg_state_ptrs(int P, int64_t R, int width, int height, char* geom_buffer, char* binning_buffer,
-                  char* image_buffer, void** out /* host, 14 entries */);
+                  char* image_buffer, void** out /* host, 12 entries */);
+
+/* Test aid: rebuilds the reference's SORTED 64-bit keys ((tile << 32) | depth bits,
+ * dgr/cuda_rasterizer/rasterizer_impl.cu:102-105) for the R instances of the last forward, from ranges,
+ * point_list and depths, so the bit-exact gate on keys can be applied although the kernels never build them. */
+int rg_debug_sorted_keys(int P, int64_t R, int width, int height, char* geom_buffer, char* binning_buffer,
+                         char* image_buffer, uint64_t* keys_out, rg_stream_t stream);
 
 /* ---- simple-knn -------------------------------------------------------------------------------- */
 

@@ -22,7 +22,7 @@ _i = C.c_int
 _SIGNATURES = {
     "rg_version": (C.c_int, []),
     "rg_last_error": (C.c_char_p, []),
-    "rg_geom_bytes": (C.c_size_t, [_i]),
+    "rg_geom_bytes": (C.c_size_t, [_i, _i, _i]),
     "rg_image_bytes": (C.c_size_t, [_i, _i]),
     "rg_binning_bytes": (C.c_size_t, [C.c_int64]),
     "rg_rasterize_forward": (C.c_int, [ALLOC_FN, _p, ALLOC_FN, _p, ALLOC_FN, _p, _i, _i, _i, _p, _i, _i, _p, _p, _p,
@@ -32,6 +32,7 @@ _SIGNATURES = {
                                         _p]),
     "rg_mark_visible": (C.c_int, [_i, _p, _p, _p, _p, _p]),
     "rg_state_ptrs": (C.c_int, [_i, C.c_int64, _i, _i, _p, _p, _p, C.POINTER(C.c_void_p)]),
+    "rg_debug_sorted_keys": (C.c_int, [_i, C.c_int64, _i, _i, _p, _p, _p, _p, _p]),
     "rg_knn_scratch_bytes": (C.c_size_t, [_i]),
     "rg_dist_cuda2": (C.c_int, [_i, _p, _p, _p, C.c_size_t, _p]),
     "rg_fk_forward": (C.c_int, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p]),

@@ -24,19 +24,29 @@ int check_launch(const char* what, cudaStream_t stream, bool debug) {
     return 0;
 }
 
-GeomState GeomState::carve(char* base, size_t P, size_t* bytes) {
+GeomState GeomState::carve(char* base, size_t P, int W, int H, size_t* bytes) {
     Carver c(base);
     GeomState g;
+    const int T = ((W + RG_TILE - 1) / RG_TILE) * ((H + RG_TILE - 1) / RG_TILE);
+    const BinPlan bp = make_bin_plan((int)P, T);
     g.depths = c.take<float>(P);
     g.clamped = c.take<uint8_t>(P);
     g.means2D = c.take<float2>(P);
     g.conic_opacity = c.take<float4>(P);
     g.rgb = c.take<float>(3 * P);
     g.tiles_touched = c.take<uint32_t>(P);
-    g.point_offsets = c.take<uint32_t>(P);
-    g.cov3D = c.take<float>(6 * P);
-    g.block_sums = c.take<uint32_t>((P + 255) / 256 + 2);
-    g.grad_acc = c.take<uint32_t>(10 * P);
+    g.means3D = c.take<float>(3 * P);
+    g.ids = c.take<uint32_t>(P);
+    g.sorted_keys = c.take<uint32_t>(P);
+    g.sorted_ids = c.take<uint32_t>(P);
+    g.sort_temp_bytes = depth_sort_temp_bytes(P);
+    g.sort_temp = c.take<char>(g.sort_temp_bytes);
+    g.M = c.take<uint16_t>((size_t)bp.NW * bp.Tpad);
+    g.E = c.take<uint32_t>((size_t)bp.NW * bp.T);
+    g.S = c.take<uint32_t>((size_t)bp.nseg * bp.T);
+    g.tile_base = c.take<uint32_t>(bp.T + 1);
+    g.status = c.take<uint32_t>(8);
+    g.grad_acc = c.take<float>(10 * P);
     if (bytes) *bytes = align_up(c.off, 256) + 256;
     return g;
 }
@@ -55,25 +65,8 @@ BinningState BinningState::carve(char* base, size_t R, size_t* bytes) {
     Carver c(base);
     BinningState b;
     b.point_list = c.take<uint32_t>(R);
-    b.point_list_unsorted = c.take<uint32_t>(R);
-    b.keys = c.take<uint64_t>(R);
-    b.keys_unsorted = c.take<uint64_t>(R);
-    b.sort_temp_bytes = radix_sort_temp_bytes(R);
-    b.sort_temp = c.take<char>(b.sort_temp_bytes);
     if (bytes) *bytes = align_up(c.off, 256) + 256;
     return b;
-}
-
-// Next-highest bit of the MSB, as the reference computes it on the host (rasterizer_impl.cu:35-50).
-static uint32_t higher_msb(uint32_t n) {
-    uint32_t msb = sizeof(n) * 4;
-    uint32_t step = msb;
-    while (step > 1) {
-        step /= 2;
-        if (n >> msb) msb += step; else msb -= step;
-    }
-    if (n >> msb) msb++;
-    return msb;
 }
 
 // The buffers handed over by torch are 512-byte aligned; be strict so carve() offsets stay valid.
@@ -99,7 +92,7 @@ extern "C" {
 int rg_version(void) { return 1; }
 const char* rg_last_error(void) { return g_error.c_str(); }
 
-size_t rg_geom_bytes(int P) { size_t b; GeomState::carve(nullptr, (size_t)P, &b); return b; }
+size_t rg_geom_bytes(int P, int width, int height) { size_t b; GeomState::carve(nullptr, (size_t)P, width, height, &b); return b; }
 size_t rg_image_bytes(int width, int height) { size_t b; ImageState::carve(nullptr, width, height, &b); return b; }
 size_t rg_binning_bytes(int64_t R) { size_t b; BinningState::carve(nullptr, (size_t)(R > 0 ? R : 0), &b); return b; }
 
@@ -121,11 +114,12 @@ int rg_rasterize_forward(rg_alloc_fn geom_alloc, void* geom_ctx, rg_alloc_fn bin
     const float focal_x = width / (2.0f * tan_fovx);
     const int grid_x = (width + RG_TILE - 1) / RG_TILE, grid_y = (height + RG_TILE - 1) / RG_TILE;
 
-    char* gptr = geom_alloc(geom_ctx, rg_geom_bytes(P));
+    char* gptr = geom_alloc(geom_ctx, rg_geom_bytes(P, width, height));
     char* iptr = image_alloc(image_ctx, rg_image_bytes(width, height));
     if (!gptr || !iptr) { set_error("rg_rasterize_forward: state buffer allocation failed"); return -1; }
-    GeomState geom = GeomState::carve(aligned_base(gptr), P, nullptr);
+    GeomState geom = GeomState::carve(aligned_base(gptr), P, width, height, nullptr);
     ImageState img = ImageState::carve(aligned_base(iptr), width, height, nullptr);
+    const BinPlan bp = make_bin_plan(P, grid_x * grid_y);
 
     PreprocessArgs pa;
     pa.P = P; pa.D = D; pa.M = M;
@@ -137,18 +131,24 @@ int rg_rasterize_forward(rg_alloc_fn geom_alloc, void* geom_ctx, rg_alloc_fn bin
     pa.sh_vec_ok = shs && M == 16 && is_aligned16(shs);
     pa.radii = radii; pa.means2D = geom.means2D; pa.depths = geom.depths; pa.cov3D_out = nullptr;
     pa.rgb = geom.rgb; pa.conic_opacity = geom.conic_opacity; pa.tiles_touched = geom.tiles_touched;
-    pa.clamped = geom.clamped; pa.block_sums = geom.block_sums;
+    pa.clamped = geom.clamped; pa.ids = geom.ids;
     launch_preprocess(pa, stream);
     if (check_launch("preprocess", stream, dbg)) return -1;
 
-    const int nblocks = (P + 255) / 256;
+    if (launch_depth_sort(geom.sort_temp, geom.sort_temp_bytes, geom.depths, geom.sorted_keys, geom.ids, geom.sorted_ids,
+                          P, stream))
+        return -1;
+    if (check_launch("depth_sort", stream, dbg)) return -1;
+    if (launch_tile_count(bp, P, grid_x, grid_y, geom.sorted_ids, geom.tiles_touched, geom.means2D, radii, geom.M, stream))
+        return -1;
+    launch_tile_offsets_a(bp, geom.M, geom.S, geom.tile_base, img.ranges, geom.status, 0xffffffffu, stream);
+    if (check_launch("tile_count/offsets", stream, dbg)) return -1;
+
+    // The one host round trip of the forward (the reference does the same, rasterizer_impl.cu:282): the
+    // binning buffer is sized by the caller's allocator from num_rendered.  rg_skinned_forward has no such trip.
     uint32_t* slot = pinned_slot();
     if (!slot) { set_error("rg_rasterize_forward: pinned host allocation failed"); return -1; }
-    launch_scan_block_sums(geom.block_sums, nblocks, nullptr, stream);
-    if (check_launch("scan", stream, dbg)) return -1;
-    // The one host round trip of the forward (the reference does the same, rasterizer_impl.cu:282): the
-    // binning buffer is sized by the caller's allocator from num_rendered.
-    cudaMemcpyAsync(slot, geom.block_sums + nblocks, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream);
+    cudaMemcpyAsync(slot, geom.status, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream);
     cudaError_t e = cudaStreamSynchronize(stream);
     if (e != cudaSuccess) { set_error(std::string("num_rendered read-back: ") + cudaGetErrorString(e)); return -1; }
     const int64_t R = *slot;
@@ -157,17 +157,11 @@ int rg_rasterize_forward(rg_alloc_fn geom_alloc, void* geom_ctx, rg_alloc_fn bin
     char* bptr = binning_alloc(binning_ctx, rg_binning_bytes(R));
     if (!bptr) { set_error("rg_rasterize_forward: binning buffer allocation failed"); return -1; }
     BinningState bin = BinningState::carve(aligned_base(bptr), (size_t)R, nullptr);
-
-    launch_emit_keys(P, grid_x, grid_y, geom.means2D, geom.depths, radii, geom.tiles_touched, geom.block_sums,
-                     geom.point_offsets, bin.keys_unsorted, bin.point_list_unsorted, stream);
-    if (check_launch("emit_keys", stream, dbg)) return -1;
-    const int bit = (int)higher_msb((uint32_t)(grid_x * grid_y));
-    if (launch_sort_pairs(bin.sort_temp, bin.sort_temp_bytes, bin.keys_unsorted, bin.keys, bin.point_list_unsorted,
-                          bin.point_list, R, 32 + bit, stream))
-        return -1;
-    if (check_launch("sort", stream, dbg)) return -1;
-    launch_tile_ranges(R, bin.keys, img.ranges, grid_x * grid_y, stream);
-    if (check_launch("tile_ranges", stream, dbg)) return -1;
+    if (R > 0) {
+        launch_tile_scatter(bp, P, grid_x, grid_y, geom.sorted_ids, geom.tiles_touched, geom.means2D, radii, geom.M,
+                            geom.S, geom.tile_base, geom.E, bin.point_list, (uint32_t)R, stream);
+        if (check_launch("tile_scatter", stream, dbg)) return -1;
+    }
 
     BlendFwdArgs fa;
     fa.W = width; fa.H = height; fa.grid_x = grid_x; fa.grid_y = grid_y;
@@ -202,11 +196,11 @@ int rg_rasterize_backward(int P, int D, int M, int R, const float* background, i
     const float focal_y = height / (2.0f * tan_fovy);
     const float focal_x = width / (2.0f * tan_fovx);
     const int grid_x = (width + RG_TILE - 1) / RG_TILE, grid_y = (height + RG_TILE - 1) / RG_TILE;
-    GeomState geom = GeomState::carve(aligned_base(geom_buffer), P, nullptr);
+    GeomState geom = GeomState::carve(aligned_base(geom_buffer), P, width, height, nullptr);
     ImageState img = ImageState::carve(aligned_base(image_buffer), width, height, nullptr);
     BinningState bin = BinningState::carve(aligned_base(binning_buffer), (size_t)(R > 0 ? R : 0), nullptr);
 
-    float* acc = reinterpret_cast<float*>(geom.grad_acc);
+    float* acc = geom.grad_acc;
     cudaMemsetAsync(acc, 0, sizeof(float) * 10 * (size_t)P, stream);
     BlendBwdArgs ba;
     ba.P = P; ba.W = width; ba.H = height; ba.grid_x = grid_x; ba.grid_y = grid_y;
@@ -243,18 +237,30 @@ int rg_mark_visible(int P, const float* means3D, const float* viewmatrix, const 
 
 int rg_state_ptrs(int P, int64_t R, int width, int height, char* geom_buffer, char* binning_buffer, char* image_buffer,
                   void** out) {
-    GeomState g = GeomState::carve(aligned_base(geom_buffer), P, nullptr);
+    GeomState g = GeomState::carve(aligned_base(geom_buffer), P, width, height, nullptr);
     out[0] = g.depths; out[1] = g.clamped; out[2] = g.means2D; out[3] = g.conic_opacity; out[4] = g.rgb;
-    out[5] = g.tiles_touched; out[6] = g.point_offsets; out[7] = g.cov3D;
+    out[5] = g.tiles_touched; out[6] = g.sorted_ids; out[7] = g.means3D;
     if (binning_buffer) {
         BinningState b = BinningState::carve(aligned_base(binning_buffer), (size_t)(R > 0 ? R : 0), nullptr);
-        out[8] = b.point_list; out[9] = b.point_list_unsorted; out[10] = b.keys; out[11] = b.keys_unsorted;
+        out[8] = b.point_list;
     } else {
-        out[8] = out[9] = out[10] = out[11] = nullptr;
+        out[8] = nullptr;
     }
     ImageState im = ImageState::carve(aligned_base(image_buffer), width, height, nullptr);
-    out[12] = im.n_contrib; out[13] = im.ranges;
+    out[9] = im.n_contrib; out[10] = im.ranges; out[11] = g.status;
     return 0;
+}
+
+int rg_debug_sorted_keys(int P, int64_t R, int width, int height, char* geom_buffer, char* binning_buffer,
+                         char* image_buffer, uint64_t* keys_out, rg_stream_t stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (R <= 0) return 0;
+    GeomState g = GeomState::carve(aligned_base(geom_buffer), P, width, height, nullptr);
+    BinningState b = BinningState::carve(aligned_base(binning_buffer), (size_t)R, nullptr);
+    ImageState im = ImageState::carve(aligned_base(image_buffer), width, height, nullptr);
+    const int T = ((width + RG_TILE - 1) / RG_TILE) * ((height + RG_TILE - 1) / RG_TILE);
+    launch_rebuild_keys(T, im.ranges, b.point_list, g.depths, keys_out, stream);
+    return check_launch("debug_sorted_keys", stream, false);
 }
 
 size_t rg_knn_scratch_bytes(int P) { return knn_scratch_bytes(P) + 256; }

@@ -1,7 +1,25 @@
-// Binning: offsets scan, (tile | depth) key emission, stable radix sort, per-tile ranges.
-// Replaces cub::DeviceScan::InclusiveSum + duplicateWithKeys + identifyTileRanges and the call to
-// cub::DeviceRadixSort::SortPairs of dgr/cuda_rasterizer/rasterizer_impl.cu:70-138, 278-319.
-// Pure integer work: results must be bit-identical to the reference's.
+// Binning: from per-Gaussian (depth, tile rectangle) to the per-tile, depth-ordered instance lists.
+//
+// The reference materialises one 64-bit key (tile << 32 | depth bits) + one 32-bit id per (Gaussian, tile)
+// instance and runs a 44..45-bit radix sort over all R instances (duplicateWithKeys + cub SortPairs +
+// identifyTileRanges, dgr/cuda_rasterizer/rasterizer_impl.cu:70-138, 278-319): ~12 B written and
+// 6 x 24 B moved per instance.  The result it defines -- instances grouped by tile, ordered by depth bits
+// inside a tile, ties in Gaussian-id order -- is produced here without ever building the keys:
+//
+//   1. stable radix sort of the P Gaussians by depth bits (32-bit keys, P items: small, L2 resident);
+//   2. tile_count:   the depth-ordered Gaussians are cut into NW contiguous chunks, one warp each; a warp
+//                    counts the instances of its chunk per tile in shared memory -> row of M[NW][T];
+//   3. column scans: per tile, prefix over the chunks (two levels) and prefix over the tiles ->
+//                    E[w][t] = first output slot of chunk w in tile t, ranges[t], num_rendered;
+//   4. tile_scatter: every warp walks its chunk again, in order, and drops each instance id straight into
+//                    its final slot (cursor per tile in shared memory, ranks inside a 32-instance step from
+//                    __match_any_sync in lane = depth order).
+//
+// The instance list is written exactly once (4 B per instance) and nothing instance-sized is ever read
+// back; num_rendered stays on the device (the sync-free entry points never look at it on the host).
+// Order proof: slots of tile t are handed out by (chunk index, position inside the chunk's walk), chunks
+// are contiguous ranges of the depth-sorted order, and the depth sort is stable over ascending ids -- the
+// same total order as the reference's stable sort on (tile, depth) over id-ordered emission.
 #include <cub/device/device_radix_sort.cuh>
 
 #include "common.cuh"
@@ -10,20 +28,138 @@
 
 namespace rg {
 
-// ---- level 2 of the offsets scan: exclusive scan of <= a few thousand block sums, one CTA ----------
-__global__ void __launch_bounds__(1024) scan_block_sums_kernel(uint32_t* sums, int n, uint32_t* total_out) {
+// ---- 1. depth sort -----------------------------------------------------------------------------------
+size_t depth_sort_temp_bytes(size_t P) {
+    size_t bytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, (const uint32_t*)nullptr,
+                                    (uint32_t*)nullptr, (int)P, 0, 32);
+    return bytes;
+}
+
+int launch_depth_sort(char* temp, size_t temp_bytes, const float* depths, uint32_t* keys_out, const uint32_t* ids_in,
+                      uint32_t* ids_out, int P, cudaStream_t stream) {
+    if (P <= 0) return 0;
+    LaunchScope ls("depth_sort", stream, 0);
+    cudaError_t e = cub::DeviceRadixSort::SortPairs(temp, temp_bytes, reinterpret_cast<const uint32_t*>(depths), keys_out,
+                                                    ids_in, ids_out, P, 0, 32, stream);
+    if (e != cudaSuccess) {
+        set_error(std::string("depth sort: ") + cudaGetErrorString(e));
+        return -1;
+    }
+    return 0;
+}
+
+// ---- shared walk: a warp visits the instances of its chunk in (Gaussian order, row-major tile) order ----
+// F is called by all 32 lanes for every step of 32 instances: F(valid, tile, gaussian_id).
+template <typename F>
+__device__ __forceinline__ void walk_chunk(int lo, int hi, int grid_x, int grid_y, const uint32_t* __restrict__ sorted_ids,
+                                           const uint32_t* __restrict__ tiles_touched, const float2* __restrict__ means2D,
+                                           const int* __restrict__ radii, F&& f) {
+    const int lane = threadIdx.x & 31;
+    const unsigned full = 0xffffffffu;
+    for (int base = lo; base < hi; base += 32) {
+        const int i = base + lane;
+        uint32_t id = 0, cnt = 0, x0 = 0, y0 = 0, w = 1;
+        if (i < hi) {
+            id = sorted_ids[i];
+            cnt = tiles_touched[id];
+            if (cnt > 0) {
+                uint2 rmin, rmax;
+                tile_rect(means2D[id], radii[id], rmin, rmax, grid_x, grid_y);
+                x0 = rmin.x; y0 = rmin.y; w = rmax.x - rmin.x;
+            }
+        }
+        uint32_t incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(full, incl, o);
+            if (lane >= o) incl += y;
+        }
+        const uint32_t excl = incl - cnt;
+        const uint32_t total = __shfl_sync(full, incl, 31);
+        for (uint32_t s0 = 0; s0 < total; s0 += 32) {
+            const uint32_t s = s0 + lane;
+            const bool valid = s < total;
+            // owner = largest lane o with excl[o] <= s (zero-count lanes share their successor's excl)
+            int o = 0;
+#pragma unroll
+            for (int step = 16; step > 0; step >>= 1) {
+                const int cand = o + step;
+                const uint32_t e = __shfl_sync(full, excl, cand & 31);
+                if (cand < 32 && e <= s) o = cand;
+            }
+            const uint32_t local = s - __shfl_sync(full, excl, o);
+            const uint32_t ox0 = __shfl_sync(full, x0, o), oy0 = __shfl_sync(full, y0, o), ow = __shfl_sync(full, w, o);
+            const uint32_t oid = __shfl_sync(full, id, o);
+            const uint32_t t = (oy0 + local / ow) * (uint32_t)grid_x + ox0 + local % ow;
+            f(valid, t, oid);
+        }
+    }
+}
+
+// ---- 2. per-chunk, per-tile counts ------------------------------------------------------------------
+__global__ void __launch_bounds__(256) tile_count_kernel(int P, int T, int NW, int L, int grid_x, int grid_y,
+                                                         const uint32_t* __restrict__ sorted_ids,
+                                                         const uint32_t* __restrict__ tiles_touched,
+                                                         const float2* __restrict__ means2D, const int* __restrict__ radii,
+                                                         uint16_t* __restrict__ M) {
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpc = blockDim.x >> 5;
+    const int gw = blockIdx.x * wpc + warp;
+    const int Tpad = (T + 1) & ~1;
+    uint16_t* hist = reinterpret_cast<uint16_t*>(s_raw) + (size_t)warp * Tpad;
+    if (gw >= NW) return;
+    uint32_t* h32 = reinterpret_cast<uint32_t*>(hist);
+    for (int k = lane; k < Tpad / 2; k += 32) h32[k] = 0;
+    __syncwarp();
+    const int lo = min(P, gw * L), hi = min(P, lo + L);
+    walk_chunk(lo, hi, grid_x, grid_y, sorted_ids, tiles_touched, means2D, radii,
+               [&](bool valid, uint32_t t, uint32_t) {
+                   const unsigned m = __match_any_sync(0xffffffffu, valid ? t : 0xffffff00u + lane);
+                   if (valid && (m & ((1u << lane) - 1)) == 0) hist[t] += (uint16_t)__popc(m);
+                   __syncwarp();
+               });
+    __syncwarp();
+    uint32_t* row = reinterpret_cast<uint32_t*>(M + (size_t)gw * Tpad);
+    for (int k = lane; k < Tpad / 2; k += 32) row[k] = h32[k];
+}
+
+// ---- 3a. sums over segments of 32 chunk rows -----------------------------------------------------------
+constexpr int kSegRows = 32;
+__global__ void __launch_bounds__(256) seg_sum_kernel(int T, int Tpad, int NW, const uint16_t* __restrict__ M,
+                                                      uint32_t* __restrict__ S) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int seg = blockIdx.y;
+    if (t >= T) return;
+    uint32_t s = 0;
+    const int w0 = seg * kSegRows, w1 = min(NW, w0 + kSegRows);
+    for (int w = w0; w < w1; w++) s += M[(size_t)w * Tpad + t];
+    S[(size_t)seg * T + t] = s;
+}
+
+// ---- 3b. per-tile totals, prefix over segments (in place), prefix over tiles, ranges, num_rendered -----
+__global__ void __launch_bounds__(1024) tile_base_kernel(int T, int nseg, uint32_t* __restrict__ S, uint32_t* __restrict__ tile_base,
+                                                         uint2* __restrict__ ranges, uint32_t* __restrict__ status,
+                                                         uint32_t capacity) {
     __shared__ uint32_t s_warp[32];
     __shared__ uint32_t s_carry;
     if (threadIdx.x == 0) s_carry = 0;
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int base = 0; base < n; base += 1024) {
-        int i = base + threadIdx.x;
-        uint32_t v = i < n ? sums[i] : 0;
-        uint32_t x = v;
+    for (int base = 0; base < T; base += 1024) {
+        const int t = base + threadIdx.x;
+        uint32_t tot = 0;
+        if (t < T) {
+            for (int s = 0; s < nseg; s++) {
+                const uint32_t v = S[(size_t)s * T + t];
+                S[(size_t)s * T + t] = tot;  // exclusive prefix over segments
+                tot += v;
+            }
+        }
+        uint32_t x = tot;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+            const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
             if (lane >= o) x += y;
         }
         if (lane == 31) s_warp[warp] = x;
@@ -32,147 +168,154 @@ __global__ void __launch_bounds__(1024) scan_block_sums_kernel(uint32_t* sums, i
             uint32_t w = s_warp[lane];
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
-                uint32_t y = __shfl_up_sync(0xffffffffu, w, o);
+                const uint32_t y = __shfl_up_sync(0xffffffffu, w, o);
                 if (lane >= o) w += y;
             }
             s_warp[lane] = w;
         }
         __syncthreads();
-        uint32_t warp_excl = warp == 0 ? 0 : s_warp[warp - 1];
-        uint32_t carry = s_carry;
-        if (i < n) sums[i] = carry + warp_excl + x - v;  // exclusive
+        const uint32_t carry = s_carry;
+        const uint32_t excl = carry + (warp ? s_warp[warp - 1] : 0) + x - tot;
+        if (t < T) {
+            tile_base[t] = excl;
+            ranges[t] = tot ? make_uint2(excl, excl + tot) : make_uint2(0, 0);
+        }
         __syncthreads();
         if (threadIdx.x == 1023) s_carry = carry + s_warp[31];
         __syncthreads();
     }
     if (threadIdx.x == 0) {
-        sums[n] = s_carry;
-        if (total_out) *total_out = s_carry;
+        status[0] = s_carry;                       // num_rendered
+        status[1] = s_carry > capacity ? 1u : 0u;  // instance list would overflow the caller's buffer
     }
 }
 
-int launch_scan_block_sums(uint32_t* block_sums, int nblocks, uint32_t* total_out, cudaStream_t stream) {
-    LaunchScope ls("scan_block_sums", stream);
-    scan_block_sums_kernel<<<1, 1024, 0, stream>>>(block_sums, nblocks, total_out);
-    return 0;
-}
-
-// ---- key emission ---------------------------------------------------------------------------------
-// One CTA per 256 Gaussians (the blocking of preprocess, whose per-block sums were scanned above).  The CTA
-// re-scans its 256 tile counts in shared memory, then its instances are emitted by all 256 threads in
-// flat order (instance s of the CTA -> owning Gaussian by binary search), so every store is coalesced and
-// a Gaussian covering 400 tiles costs its neighbours nothing.  Emission order (Gaussian id ascending,
-// tiles row-major inside the rectangle) equals the reference's, which fixes the order of equal keys.
-__global__ void __launch_bounds__(256) emit_keys_kernel(int P, int grid_x, int grid_y, const float2* __restrict__ means2D,
-                                                        const float* __restrict__ depths, const int* __restrict__ radii,
-                                                        const uint32_t* __restrict__ tiles_touched,
-                                                        const uint32_t* __restrict__ block_excl,
-                                                        uint32_t* __restrict__ point_offsets, uint64_t* __restrict__ keys,
-                                                        uint32_t* __restrict__ vals) {
-    __shared__ uint32_t s_off[257];   // exclusive offsets inside the CTA, s_off[256] = CTA total
-    __shared__ uint32_t s_warp[8];
-    __shared__ uint32_t s_depth[256];
-    __shared__ ushort4 s_rect[256];  // min.x, min.y, width, unused
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int idx = blockIdx.x * 256 + tid;
-    uint32_t cnt = 0;
-    if (idx < P) cnt = tiles_touched[idx];
-    uint32_t x = cnt;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
-        if (lane >= o) x += y;
-    }
-    if (lane == 31) s_warp[warp] = x;
-    __syncthreads();
-    uint32_t wbase = 0;
-#pragma unroll
-    for (int w = 0; w < 8; w++) wbase += (w < warp) ? s_warp[w] : 0;
-    const uint32_t incl = wbase + x;
-    const uint32_t base = block_excl[blockIdx.x];
-    s_off[tid] = incl - cnt;
-    if (tid == 255) s_off[256] = incl;
-    if (idx < P) point_offsets[idx] = base + incl;
-    if (cnt > 0) {
-        uint2 rmin, rmax;
-        tile_rect(means2D[idx], radii[idx], rmin, rmax, grid_x, grid_y);
-        s_rect[tid] = make_ushort4((unsigned short)rmin.x, (unsigned short)rmin.y, (unsigned short)(rmax.x - rmin.x), 0);
-        s_depth[tid] = __float_as_uint(depths[idx]);
-    }
-    __syncthreads();
-    const uint32_t total = s_off[256];
-    for (uint32_t s = tid; s < total; s += 256) {
-        // largest g with s_off[g] <= s  (counts may be zero, so take the last such g)
-        int lo = 0, hi = 255;
-#pragma unroll
-        for (int it = 0; it < 8; it++) {
-            int mid = (lo + hi + 1) >> 1;
-            if (s_off[mid] <= s) lo = mid; else hi = mid - 1;
-        }
-        const uint32_t local = s - s_off[lo];
-        const ushort4 r = s_rect[lo];
-        const uint32_t ty = r.y + local / r.z;
-        const uint32_t tx = r.x + local % r.z;
-        uint64_t key = (uint64_t)(ty * (uint32_t)grid_x + tx);
-        key <<= 32;
-        key |= s_depth[lo];
-        keys[base + s] = key;
-        vals[base + s] = (uint32_t)(blockIdx.x * 256 + lo);
+// ---- 3c. first slot of every (chunk, tile) -----------------------------------------------------------
+__global__ void __launch_bounds__(256) col_scan_kernel(int T, int Tpad, int NW, const uint16_t* __restrict__ M,
+                                                       const uint32_t* __restrict__ S, const uint32_t* __restrict__ tile_base,
+                                                       uint32_t* __restrict__ E) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int seg = blockIdx.y;
+    if (t >= T) return;
+    uint32_t run = tile_base[t] + S[(size_t)seg * T + t];
+    const int w0 = seg * kSegRows, w1 = min(NW, w0 + kSegRows);
+    for (int w = w0; w < w1; w++) {
+        E[(size_t)w * T + t] = run;
+        run += M[(size_t)w * Tpad + t];
     }
 }
 
-int launch_emit_keys(int P, int grid_x, int grid_y, const float2* means2D, const float* depths, const int* radii,
-                     const uint32_t* tiles_touched, const uint32_t* block_sums_excl, uint32_t* point_offsets,
-                     uint64_t* keys, uint32_t* vals, cudaStream_t stream) {
-    if (P == 0) return 0;
-    LaunchScope ls("emit_keys", stream);
-    emit_keys_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, grid_x, grid_y, means2D, depths, radii, tiles_touched,
-                                                          block_sums_excl, point_offsets, keys, vals);
-    return 0;
+// ---- 4. scatter ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int T, int NW, int L, int grid_x, int grid_y,
+                                                           const uint32_t* __restrict__ sorted_ids,
+                                                           const uint32_t* __restrict__ tiles_touched,
+                                                           const float2* __restrict__ means2D, const int* __restrict__ radii,
+                                                           const uint32_t* __restrict__ E, uint32_t* __restrict__ point_list,
+                                                           uint32_t capacity) {
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpc = blockDim.x >> 5;
+    const int gw = blockIdx.x * wpc + warp;
+    uint32_t* cur = reinterpret_cast<uint32_t*>(s_raw) + (size_t)warp * T;
+    if (gw >= NW) return;
+    const uint32_t* row = E + (size_t)gw * T;
+    for (int k = lane; k < T; k += 32) cur[k] = row[k];
+    __syncwarp();
+    const int lo = min(P, gw * L), hi = min(P, lo + L);
+    walk_chunk(lo, hi, grid_x, grid_y, sorted_ids, tiles_touched, means2D, radii,
+               [&](bool valid, uint32_t t, uint32_t id) {
+                   const unsigned m = __match_any_sync(0xffffffffu, valid ? t : 0xffffff00u + lane);
+                   const unsigned below = m & ((1u << lane) - 1);
+                   uint32_t c = 0;
+                   if (valid) c = cur[t];
+                   __syncwarp();
+                   if (valid) {
+                       const uint32_t pos = c + __popc(below);
+                       if (pos < capacity) point_list[pos] = id;
+                       if (below == 0) cur[t] = c + __popc(m);
+                   }
+                   __syncwarp();
+               });
 }
 
-// ---- sort -----------------------------------------------------------------------------------------
-size_t radix_sort_temp_bytes(size_t R) {
-    size_t bytes = 0;
-    cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint64_t*)nullptr, (uint64_t*)nullptr,
-                                    (const uint32_t*)nullptr, (uint32_t*)nullptr, (int64_t)R, 0, 64);
-    return bytes;
+// ---- launch plumbing ----------------------------------------------------------------------------------
+BinPlan make_bin_plan(int P, int T) {
+    BinPlan b;
+    b.T = T;
+    b.Tpad = (T + 1) & ~1;
+    int L = 256;
+    int NW = (P + L - 1) / L;
+    const int kMaxRows = 2048;
+    if (NW > kMaxRows) {
+        NW = kMaxRows;
+        L = (P + NW - 1) / NW;
+        NW = (P + L - 1) / L;
+    }
+    if (NW < 1) NW = 1;
+    b.L = L;
+    b.NW = NW;
+    b.nseg = (NW + kSegRows - 1) / kSegRows;
+    const size_t smem_budget = 200 * 1024;
+    int wpc_count = (int)(smem_budget / ((size_t)b.Tpad * 2));
+    int wpc_scatter = (int)(smem_budget / ((size_t)T * 4));
+    b.wpc_count = wpc_count > 8 ? 8 : wpc_count;
+    b.wpc_scatter = wpc_scatter > 8 ? 8 : wpc_scatter;
+    return b;
 }
 
-int launch_sort_pairs(char* temp, size_t temp_bytes, const uint64_t* keys_in, uint64_t* keys_out,
-                      const uint32_t* vals_in, uint32_t* vals_out, int64_t R, int end_bit, cudaStream_t stream) {
-    if (R <= 0) return 0;
-    LaunchScope ls("radix_sort", stream, 0);
-    cudaError_t e = cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, vals_in, vals_out, R, 0,
-                                                    end_bit, stream);
-    if (e != cudaSuccess) {
-        set_error(std::string("radix sort: ") + cudaGetErrorString(e));
+int launch_tile_count(const BinPlan& b, int P, int grid_x, int grid_y, const uint32_t* sorted_ids,
+                      const uint32_t* tiles_touched, const float2* means2D, const int* radii, uint16_t* M,
+                      cudaStream_t stream) {
+    if (b.wpc_count < 1 || b.wpc_scatter < 1 || b.L > 65535) {
+        set_error("binning: image has too many tiles (or chunk too long) for the shared-memory tile counters");
         return -1;
     }
+    const size_t smem = (size_t)b.wpc_count * b.Tpad * 2;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(tile_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        cudaFuncSetAttribute(tile_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        attr_set = true;
+    }
+    LaunchScope ls("tile_count", stream);
+    tile_count_kernel<<<(b.NW + b.wpc_count - 1) / b.wpc_count, b.wpc_count * 32, smem, stream>>>(
+        P, b.T, b.NW, b.L, grid_x, grid_y, sorted_ids, tiles_touched, means2D, radii, M);
     return 0;
 }
 
-// ---- per-tile ranges ------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) tile_ranges_kernel(int64_t L, const uint64_t* __restrict__ keys,
-                                                          uint2* __restrict__ ranges) {
-    int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= L) return;
-    uint32_t cur = (uint32_t)(keys[idx] >> 32);
-    if (idx == 0) ranges[cur].x = 0;
-    else {
-        uint32_t prev = (uint32_t)(keys[idx - 1] >> 32);
-        if (cur != prev) {
-            ranges[prev].y = (uint32_t)idx;
-            ranges[cur].x = (uint32_t)idx;
-        }
-    }
-    if (idx == L - 1) ranges[cur].y = (uint32_t)L;
+int launch_tile_offsets_a(const BinPlan& b, const uint16_t* M, uint32_t* S, uint32_t* tile_base, uint2* ranges,
+                          uint32_t* status, uint32_t capacity, cudaStream_t stream) {
+    LaunchScope ls("tile_offsets", stream, 2);
+    dim3 g((b.T + 255) / 256, b.nseg);
+    seg_sum_kernel<<<g, 256, 0, stream>>>(b.T, b.Tpad, b.NW, M, S);
+    tile_base_kernel<<<1, 1024, 0, stream>>>(b.T, b.nseg, S, tile_base, ranges, status, capacity);
+    return 0;
 }
 
-int launch_tile_ranges(int64_t R, const uint64_t* keys, uint2* ranges, int n_tiles, cudaStream_t stream) {
-    LaunchScope ls("tile_ranges", stream, R > 0 ? 1 : 0);
-    cudaMemsetAsync(ranges, 0, sizeof(uint2) * (size_t)n_tiles, stream);
-    if (R > 0) tile_ranges_kernel<<<(unsigned)((R + 255) / 256), 256, 0, stream>>>(R, keys, ranges);
+int launch_tile_scatter(const BinPlan& b, int P, int grid_x, int grid_y, const uint32_t* sorted_ids,
+                        const uint32_t* tiles_touched, const float2* means2D, const int* radii, const uint16_t* M,
+                        const uint32_t* S, const uint32_t* tile_base, uint32_t* E, uint32_t* point_list,
+                        uint32_t capacity, cudaStream_t stream) {
+    LaunchScope ls("tile_scatter", stream, 2);
+    dim3 g((b.T + 255) / 256, b.nseg);
+    col_scan_kernel<<<g, 256, 0, stream>>>(b.T, b.Tpad, b.NW, M, S, tile_base, E);
+    const size_t smem = (size_t)b.wpc_scatter * b.T * 4;
+    tile_scatter_kernel<<<(b.NW + b.wpc_scatter - 1) / b.wpc_scatter, b.wpc_scatter * 32, smem, stream>>>(
+        P, b.T, b.NW, b.L, grid_x, grid_y, sorted_ids, tiles_touched, means2D, radii, E, point_list, capacity);
+    return 0;
+}
+
+// ---- debug / test aid: rebuild the reference's sorted 64-bit keys from (ranges, point_list, depths) --------
+__global__ void rebuild_keys_kernel(int T, const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                                    const float* __restrict__ depths, uint64_t* __restrict__ keys) {
+    const int t = blockIdx.x;
+    const uint2 r = ranges[t];
+    for (uint32_t p = r.x + threadIdx.x; p < r.y; p += blockDim.x)
+        keys[p] = ((uint64_t)t << 32) | __float_as_uint(depths[point_list[p]]);
+}
+
+int launch_rebuild_keys(int T, const uint2* ranges, const uint32_t* point_list, const float* depths, uint64_t* keys,
+                        cudaStream_t stream) {
+    rebuild_keys_kernel<<<T, 256, 0, stream>>>(T, ranges, point_list, depths, keys);
     return 0;
 }
 

@@ -44,19 +44,27 @@ struct Carver {
     }
 };
 
-// Per-Gaussian state kept between forward and backward ("geometry buffer").
+// Per-Gaussian state kept between forward and backward ("geometry buffer"), plus the binning scratch.
 struct GeomState {
-    float* depths;            // P
+    float* depths;            // P (+inf for culled Gaussians: they sort last)
     uint8_t* clamped;         // P, bit c set when colour channel c was clamped at 0
     float2* means2D;          // P
     float4* conic_opacity;    // P
     float* rgb;               // 3P
     uint32_t* tiles_touched;  // P
-    uint32_t* point_offsets;  // P inclusive scan of tiles_touched
-    float* cov3D;             // 6P
-    uint32_t* block_sums;     // ceil(P / SCAN_ITEMS) partial sums + total at [nblocks]
-    uint32_t* grad_acc;       // 10P floats: per-Gaussian 2-D gradient accumulators of the backward blend
-    static GeomState carve(char* base, size_t P, size_t* bytes);
+    float* means3D;           // 3P, skinned positions kept by the fused entry point
+    uint32_t* ids;            // P iota
+    uint32_t* sorted_keys;    // P depth bits, ascending
+    uint32_t* sorted_ids;     // P Gaussian ids in depth order (stable)
+    char* sort_temp;
+    size_t sort_temp_bytes;
+    uint16_t* M;              // NW x Tpad instance counts per (chunk, tile)
+    uint32_t* E;              // NW x T first slot per (chunk, tile)
+    uint32_t* S;              // nseg x T
+    uint32_t* tile_base;      // T
+    uint32_t* status;         // [0] num_rendered, [1] overflow flag
+    float* grad_acc;          // 10P floats: per-Gaussian 2-D gradient accumulators of the backward blend
+    static GeomState carve(char* base, size_t P, int W, int H, size_t* bytes);
 };
 
 struct ImageState {
@@ -66,16 +74,9 @@ struct ImageState {
 };
 
 struct BinningState {
-    uint32_t* point_list;
-    uint32_t* point_list_unsorted;
-    uint64_t* keys;
-    uint64_t* keys_unsorted;
-    char* sort_temp;
-    size_t sort_temp_bytes;
+    uint32_t* point_list;  // R instance ids: grouped by tile, depth-ordered inside a tile
     static BinningState carve(char* base, size_t R, size_t* bytes);
 };
-
-size_t sort_temp_bytes(size_t R);
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

@@ -32,25 +32,35 @@ struct PreprocessArgs {
     float4* conic_opacity;
     uint32_t* tiles_touched;
     uint8_t* clamped;
-    uint32_t* block_sums;  // one partial sum per 256-Gaussian block
+    uint32_t* ids;  // iota, value array of the depth sort
 };
 
 int launch_preprocess(const PreprocessArgs& a, cudaStream_t stream);
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t stream);
 
-// Exclusive scan of the per-block sums in place; total written to block_sums[nblocks] and to *total_out.
-int launch_scan_block_sums(uint32_t* block_sums, int nblocks, uint32_t* total_out, cudaStream_t stream);
-
-// Balanced key emission + inclusive offsets (one block per 256 Gaussians, same blocking as preprocess).
-int launch_emit_keys(int P, int grid_x, int grid_y, const float2* means2D, const float* depths, const int* radii,
-                     const uint32_t* tiles_touched, const uint32_t* block_sums_excl, uint32_t* point_offsets,
-                     uint64_t* keys, uint32_t* vals, cudaStream_t stream);
-
-size_t radix_sort_temp_bytes(size_t R);
-int launch_sort_pairs(char* temp, size_t temp_bytes, const uint64_t* keys_in, uint64_t* keys_out,
-                      const uint32_t* vals_in, uint32_t* vals_out, int64_t R, int end_bit, cudaStream_t stream);
-
-int launch_tile_ranges(int64_t R, const uint64_t* keys, uint2* ranges, int n_tiles, cudaStream_t stream);
+// ---- binning (binning.cu) ----
+struct BinPlan {
+    int T, Tpad;      // tiles, tiles padded to even (u16 rows are copied as u32 words)
+    int NW, L;        // chunks (one warp each) of L depth-ordered Gaussians
+    int nseg;         // segments of 32 chunk rows
+    int wpc_count, wpc_scatter;  // warps per CTA of the two walking kernels (shared-memory bound)
+};
+BinPlan make_bin_plan(int P, int T);
+size_t depth_sort_temp_bytes(size_t P);
+int launch_depth_sort(char* temp, size_t temp_bytes, const float* depths, uint32_t* keys_out, const uint32_t* ids_in,
+                      uint32_t* ids_out, int P, cudaStream_t stream);
+int launch_tile_count(const BinPlan& b, int P, int grid_x, int grid_y, const uint32_t* sorted_ids,
+                      const uint32_t* tiles_touched, const float2* means2D, const int* radii, uint16_t* M,
+                      cudaStream_t stream);
+// segment sums + tile bases + ranges + status[0] = num_rendered, status[1] = overflow flag
+int launch_tile_offsets_a(const BinPlan& b, const uint16_t* M, uint32_t* S, uint32_t* tile_base, uint2* ranges,
+                          uint32_t* status, uint32_t capacity, cudaStream_t stream);
+int launch_tile_scatter(const BinPlan& b, int P, int grid_x, int grid_y, const uint32_t* sorted_ids,
+                        const uint32_t* tiles_touched, const float2* means2D, const int* radii, const uint16_t* M,
+                        const uint32_t* S, const uint32_t* tile_base, uint32_t* E, uint32_t* point_list,
+                        uint32_t capacity, cudaStream_t stream);
+int launch_rebuild_keys(int T, const uint2* ranges, const uint32_t* point_list, const float* depths, uint64_t* keys,
+                        cudaStream_t stream);
 
 struct BlendFwdArgs {
     int W, H, grid_x, grid_y;

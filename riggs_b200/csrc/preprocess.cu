@@ -138,20 +138,8 @@ __global__ void __launch_bounds__(256) preprocess_kernel(PreprocessArgs a) {
         } while (false);
         a.radii[idx] = radius_out;
         a.tiles_touched[idx] = my_tiles;
-    }
-    // Block partial sum of tiles_touched: first level of the offsets scan, fused here so the scan needs no
-    // separate read pass over tiles_touched.
-    uint32_t s = my_tiles;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    __shared__ uint32_t s_part[8];
-    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = s;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t t = 0;
-#pragma unroll
-        for (int w = 0; w < 8; w++) t += s_part[w];
-        a.block_sums[blockIdx.x] = t;
+        if (my_tiles == 0) a.depths[idx] = __int_as_float(0x7f800000);  // culled: +inf sorts behind everything
+        a.ids[idx] = idx;
     }
 }
 

@@ -111,6 +111,15 @@ def mark_visible(means3D, viewmatrix, projmatrix):
 def state_ptrs(P, R, W, H, geomBuffer, binningBuffer, imageBuffer):
     """Test/debug helper: device addresses of the arrays inside the three opaque state buffers."""
     import ctypes as C
-    out = (C.c_void_p * 14)()
+    out = (C.c_void_p * 12)()
     _lib.lib().rg_state_ptrs(P, int(R), W, H, ptr(geomBuffer), ptr(binningBuffer), ptr(imageBuffer), out)
     return [int(v) if v else 0 for v in out]
+
+
+def debug_sorted_keys(P, R, W, H, geomBuffer, binningBuffer, imageBuffer):
+    """Test helper: the reference's sorted (tile << 32 | depth bits) keys rebuilt from our state."""
+    keys = torch.empty(int(R), dtype=torch.int64, device=geomBuffer.device)
+    if R > 0:
+        check(_lib.lib().rg_debug_sorted_keys(P, int(R), W, H, ptr(geomBuffer), ptr(binningBuffer), ptr(imageBuffer),
+                                              ptr(keys), stream_ptr()), "debug_sorted_keys")
+    return keys

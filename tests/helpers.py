@@ -88,17 +88,15 @@ def ours_forward(cin):
     st["conic_opacity"] = _slice(geom, ptrs[3], 16 * P, torch.float32).cpu().numpy().reshape(P, 4)
     st["rgb"] = _slice(geom, ptrs[4], 12 * P, torch.float32).cpu().numpy().reshape(P, 3)
     st["tiles_touched"] = _slice(geom, ptrs[5], 4 * P, torch.int32).cpu().numpy().view(np.uint32)
-    st["point_offsets"] = _slice(geom, ptrs[6], 4 * P, torch.int32).cpu().numpy().view(np.uint32)
+    st["sorted_ids"] = _slice(geom, ptrs[6], 4 * P, torch.int32).cpu().numpy().view(np.uint32)
     if R > 0:
         st["point_list"] = _slice(binning, ptrs[8], 4 * R, torch.int32).cpu().numpy().view(np.uint32)
-        st["vals_unsorted"] = _slice(binning, ptrs[9], 4 * R, torch.int32).cpu().numpy().view(np.uint32)
-        st["keys"] = _slice(binning, ptrs[10], 8 * R, torch.int64).cpu().numpy().view(np.uint64)
-        st["keys_unsorted"] = _slice(binning, ptrs[11], 8 * R, torch.int64).cpu().numpy().view(np.uint64)
+        st["keys"] = _C.debug_sorted_keys(P, R, W, H, geom, binning, img).cpu().numpy().view(np.uint64)
     else:
-        st["point_list"] = st["vals_unsorted"] = np.zeros(0, np.uint32)
-        st["keys"] = st["keys_unsorted"] = np.zeros(0, np.uint64)
-    st["n_contrib"] = _slice(img, ptrs[12], 4 * W * H, torch.int32).cpu().numpy().view(np.uint32).reshape(H, W)
-    st["ranges"] = _slice(img, ptrs[13], 8 * T, torch.int32).cpu().numpy().view(np.uint32).reshape(T, 2)
+        st["point_list"] = np.zeros(0, np.uint32)
+        st["keys"] = np.zeros(0, np.uint64)
+    st["n_contrib"] = _slice(img, ptrs[9], 4 * W * H, torch.int32).cpu().numpy().view(np.uint32).reshape(H, W)
+    st["ranges"] = _slice(img, ptrs[10], 8 * T, torch.int32).cpu().numpy().view(np.uint32).reshape(T, 2)
     return st
 
 

@@ -30,7 +30,7 @@ def test_binding_covers_header():
 def test_size_queries_without_gpu():
     L = _lib.lib()
     assert L.rg_version() >= 1
-    g1, g2 = L.rg_geom_bytes(1000), L.rg_geom_bytes(2000)
+    g1, g2 = L.rg_geom_bytes(1000, 800, 800), L.rg_geom_bytes(2000, 800, 800)
     assert 0 < g1 < g2
     assert L.rg_image_bytes(800, 800) >= 800 * 800 * 4 + 2500 * 8
     assert L.rg_binning_bytes(10**6) >= 10**6 * 24
