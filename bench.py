@@ -40,6 +40,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true")
     ap.add_argument("--isotropic", action="store_true")
+    ap.add_argument("--unfused", action="store_true", help="reference call sequence (deform_by_pose + render) on our kernels")
     return ap.parse_args()
 
 
@@ -90,15 +91,21 @@ class ClockSampler:
 # algorithmic bytes (restated in DESIGN.md)
 def algorithmic_bytes(P, R, HW, in_P=236, out_P=248, passes=6):
     per = {
+        # fused path
+        "skin_preprocess": P * (in_P + 48 + 12),
+        "gauss_skin_backward": P * (in_P + 40 + 12 + out_P),
+        # unfused path
         "preprocess": P * (in_P + 48),
-        "emit_keys": P * 20 + R * 12,
-        "radix_sort": R * 24 * passes,
-        "tile_ranges": R * 8,
-        "blend_forward": R * 44 + HW * 24,
-        "blend_backward": HW * 28 + R * (44 + 40),
         "gauss_backward": P * (in_P + 40 + out_P),
         "skin_forward": P * (12 + 28),
         "skin_backward": P * (12 + 28),
+        # binning: depth sort of P (key,id) pairs, 4 digit passes; counts matrix; one 4-byte write per instance
+        "depth_sort": P * 16 * 4,
+        "tile_count": P * 20,
+        "tile_offsets": 0,
+        "tile_scatter": P * 20 + R * 4,
+        "blend_forward": R * 44 + HW * 24,
+        "blend_backward": HW * 28 + R * (44 + 40),
     }
     total = P * (2 * in_P + 336) + R * (148 + 24 * passes) + HW * 52
     return per, total
@@ -124,7 +131,7 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     scene = make_scene(args.workload, args.isotropic)
-    hp = HotPath(scene, device=dev)
+    hp = HotPath(scene, device=dev, fused=not args.unfused)
     cam = scene.cameras[rank % len(scene.cameras)].to(dev)
     H, W = cam.image_height, cam.image_width
     g = torch.Generator().manual_seed(1000 + rank)

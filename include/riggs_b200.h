@@ -119,12 +119,10 @@ int rg_fk_forward(int F, int J, const float* local_rot, const float* global_tran
                   const int* parents, float* G, float* node_rot, float* posed, rg_stream_t stream);
 
 /* Reverse of rg_fk_forward (the reference relies on torch autograd through the same ops):
- * dG (F,J,12), dposed (F,J,3) or NULL  ->  dlocal_rot (F,J,4), dglobal_trans_from_posed (F,3) or NULL.
- * dG_scratch: F*J*12 floats of caller-owned device scratch, overwritten (running per-joint gradient of
- * the global transforms while the chain is walked back from the leaves). */
+ * dG (F,J,12), dposed (F,J,3) or NULL  ->  dlocal_rot (F,J,4), dglobal_trans_from_posed (F,3) or NULL. */
 int rg_fk_backward(int F, int J, const float* local_rot, const float* joints, const int* parents,
-                   const float* G, const float* dG, const float* dposed, float* dG_scratch,
-                   float* dlocal_rot, float* dglobal_trans, rg_stream_t stream);
+                   const float* G, const float* dG, const float* dposed, float* dlocal_rot,
+                   float* dglobal_trans, rg_stream_t stream);
 
 /* Linear-blend skinning of N points by the J-1 bones of one pose.  Replaces
  * SkeletonWarp.cal_nn_weight_skeleton with K = -1 and the LBS part of SkeletonWarp.deform_by_pose
@@ -150,6 +148,68 @@ int rg_skin_backward(int N, int J, const float* xyz, const float* joints, const 
                      const float* offsets, const float* g_dxyz, const float* g_drot, float* dG,
                      float* dnode_radius_raw, float* dglobal_trans, float* dmask, float* dmlp_weight,
                      float* doffsets, rg_stream_t stream);
+
+/* ---- fused skin + rasterize (the hot path as ONE call per direction) ------------------------------ */
+
+/* What gaussian_renderer.render() + SkeletonWarp.deform_by_pose() are given, as raw device tensors: the model's
+ * un-activated parameters (scene/gaussian_model.py:105-132), the skeleton, one pose and one camera.  The
+ * fused entry points fold the whole chain  pose -> FK -> LBS -> means3D / exp / normalize / sigmoid / SH cat ->
+ * rasterize  (skeleton_utils/skeleton_warp.py:130-172, gaussian_renderer/__init__.py:37-151) into the kernels;
+ * they have no counterpart function in the reference (it runs ~70 eager torch kernels + the rasterizer). */
+typedef struct RgSkinnedScene {
+    int P, J;               /* Gaussians, joints */
+    int sh_degree, M_rest;  /* active SH degree; rows of features_rest (15 for degree 3) */
+    int isotropic;          /* scaling_raw is (P,1) and is repeated over the three axes */
+    int zero_d_rotation;    /* drop the blended bone rotation (trainer convention for isotropic Gaussians) */
+    int width, height;
+    float tan_fovx, tan_fovy, scale_modifier;
+    const float *xyz, *scaling_raw, *rotation_raw, *opacity_raw, *features_dc, *features_rest;
+    const float *motion_mask;   /* (P) or NULL = 1 */
+    const float *mlp_weight;    /* (P,J-1) sigmoid(WeightMLP(x)) or NULL */
+    const float *offsets;       /* (P,3) detail-net output or NULL */
+    const float *joints;        /* (J,3) rest pose */
+    const int *parents;         /* (J) */
+    const float *node_radius_raw; /* (J) */
+    const float *local_rot;     /* (J,4) un-normalised quaternions of the pose */
+    const float *global_trans;  /* (3) */
+    const float *viewmatrix, *projmatrix, *campos, *background;
+} RgSkinnedScene;
+
+/* Caller-owned device scratch, reused across frames; nothing is allocated and the host never waits.
+ * geom: rg_geom_bytes(P, width, height); image: rg_image_bytes(width, height); binning: any size -- it bounds
+ * the number of (Gaussian, tile) instances a frame may produce (rg_binning_capacity). */
+typedef struct RgWorkspace {
+    char* geom;    size_t geom_bytes;
+    char* image;   size_t image_bytes;
+    char* binning; size_t binning_bytes;
+} RgWorkspace;
+
+uint32_t rg_binning_capacity(size_t binning_bytes);
+
+/* Forward: out_color (3,H,W), out_depth (1,H,W), out_alpha (1,H,W), radii (P); optional d_nodes (J,3) = posed
+ * joints + global_trans; optional dbg_* (P,3)/(P,4)/(P) = the activated scales / rotations / opacities the
+ * kernel derived (test aid: these plus out[7] of rg_state_ptrs are what the reference rasterizer would be fed). */
+int rg_skinned_forward(const RgSkinnedScene* scene, const RgWorkspace* ws, float* out_color, float* out_depth,
+                       float* out_alpha, int* radii, float* d_nodes, float* dbg_scales, float* dbg_rotations,
+                       float* dbg_opacities, rg_stream_t stream);
+
+/* Queues an asynchronous copy of {num_rendered, overflow flag} of the last forward into host_out2 (pinned host
+ * memory, 2 x uint32).  overflow != 0 means the binning buffer was too small: the frame is invalid (but memory
+ * safe); grow the buffer and render again. */
+int rg_skinned_status(const RgSkinnedScene* scene, const RgWorkspace* ws, uint32_t* host_out2, rg_stream_t stream);
+
+/* Backward of rg_skinned_forward on the same scene/workspace.  Inputs: radii and alphas (= out_alpha) of the
+ * forward, dL/dcolor (3,H,W), dL/ddepth (1,H,W), dL/dalpha (1,H,W), optional dL/d(d_nodes) (J,3).
+ * Outputs (fully written): gradients of the raw tensors d_xyz (P,3), d_scaling_raw (P,3|1), d_rotation_raw (P,4),
+ * d_opacity_raw (P), d_features_dc (P,3), d_features_rest (P,M_rest,3), d_mean2D (P,3) [screen-space, z = 0],
+ * d_local_rot (J,4), d_global_trans (3), d_node_radius_raw (J); optional d_mask (P), d_mlp_weight (P,J-1),
+ * d_offsets (P,3). */
+int rg_skinned_backward(const RgSkinnedScene* scene, const RgWorkspace* ws, const int* radii, const float* alphas,
+                        const float* dL_dcolor, const float* dL_ddepth, const float* dL_dalpha,
+                        const float* dL_dnodes, float* d_xyz, float* d_scaling_raw, float* d_rotation_raw,
+                        float* d_opacity_raw, float* d_features_dc, float* d_features_rest, float* d_mean2D,
+                        float* d_local_rot, float* d_global_trans, float* d_node_radius_raw, float* d_mask,
+                        float* d_mlp_weight, float* d_offsets, rg_stream_t stream);
 
 /* ---- measurement aids (no counterpart in the reference; used by bench.py) ------------------------ */
 

@@ -19,6 +19,22 @@ _p = C.c_void_p
 _f = C.c_float
 _i = C.c_int
 
+
+
+class RgSkinnedScene(C.Structure):
+    _fields_ = ([(n, C.c_int) for n in ("P", "J", "sh_degree", "M_rest", "isotropic", "zero_d_rotation", "width", "height")] +
+                [(n, C.c_float) for n in ("tan_fovx", "tan_fovy", "scale_modifier")] +
+                [(n, C.c_void_p) for n in ("xyz", "scaling_raw", "rotation_raw", "opacity_raw", "features_dc",
+                                           "features_rest", "motion_mask", "mlp_weight", "offsets", "joints", "parents",
+                                           "node_radius_raw", "local_rot", "global_trans", "viewmatrix", "projmatrix",
+                                           "campos", "background")])
+
+
+class RgWorkspace(C.Structure):
+    _fields_ = [("geom", C.c_void_p), ("geom_bytes", C.c_size_t), ("image", C.c_void_p), ("image_bytes", C.c_size_t),
+                ("binning", C.c_void_p), ("binning_bytes", C.c_size_t)]
+
+
 _SIGNATURES = {
     "rg_version": (C.c_int, []),
     "rg_last_error": (C.c_char_p, []),
@@ -36,7 +52,11 @@ _SIGNATURES = {
     "rg_knn_scratch_bytes": (C.c_size_t, [_i]),
     "rg_dist_cuda2": (C.c_int, [_i, _p, _p, _p, C.c_size_t, _p]),
     "rg_fk_forward": (C.c_int, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
-    "rg_fk_backward": (C.c_int, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "rg_fk_backward": (C.c_int, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "rg_binning_capacity": (C.c_uint32, [C.c_size_t]),
+    "rg_skinned_forward": (C.c_int, [_p, _p] + [_p] * 9),
+    "rg_skinned_status": (C.c_int, [_p, _p, _p, _p]),
+    "rg_skinned_backward": (C.c_int, [_p, _p] + [_p] * 20),
     "rg_skin_forward": (C.c_int, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _p]),
     "rg_skin_backward": (C.c_int, [_i, _i] + [_p] * 19),
     "rg_launch_count": (C.c_longlong, []),

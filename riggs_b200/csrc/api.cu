@@ -47,6 +47,8 @@ GeomState GeomState::carve(char* base, size_t P, int W, int H, size_t* bytes) {
     g.tile_base = c.take<uint32_t>(bp.T + 1);
     g.status = c.take<uint32_t>(8);
     g.grad_acc = c.take<float>(10 * P);
+    g.d_rot = c.take<float>(4 * P);
+    g.fk = c.take<float>(128 * (12 + 4 + 3 + 12 + 1) + 4);
     if (bytes) *bytes = align_up(c.off, 256) + 256;
     return g;
 }
@@ -279,16 +281,15 @@ int rg_dist_cuda2(int P, const float* points, float* mean_dists, char* scratch, 
 int rg_fk_forward(int F, int J, const float* local_rot, const float* global_trans, const float* joints,
                   const int* parents, float* G, float* node_rot, float* posed, rg_stream_t stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-    launch_fk_forward(F, J, local_rot, global_trans, joints, parents, G, node_rot, posed, stream);
+    if (launch_fk_forward(F, J, local_rot, global_trans, joints, parents, G, node_rot, posed, stream)) return -1;
     return check_launch("fk_forward", stream, false);
 }
 
 int rg_fk_backward(int F, int J, const float* local_rot, const float* joints, const int* parents, const float* G,
-                   const float* dG, const float* dposed, float* dG_scratch, float* dlocal_rot, float* dglobal_trans,
-                   rg_stream_t stream_) {
+                   const float* dG, const float* dposed, float* dlocal_rot, float* dglobal_trans, rg_stream_t stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-    if (!dG_scratch) { set_error("rg_fk_backward: dG_scratch (F*J*12 floats) is required"); return -1; }
-    launch_fk_backward(F, J, local_rot, joints, parents, G, dG, dposed, dG_scratch, dlocal_rot, dglobal_trans, stream);
+    if (launch_fk_backward(F, J, local_rot, joints, parents, G, dG, dposed, dlocal_rot, dglobal_trans, nullptr, stream))
+        return -1;
     return check_launch("fk_backward", stream, false);
 }
 

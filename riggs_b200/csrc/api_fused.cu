@@ -1,0 +1,170 @@
+// extern "C" surface, part 2: the fused skin + rasterize entry points (no host round trip).
+#include "../../include/riggs_b200.h"
+
+#include <string>
+
+#include "common.cuh"
+#include "kernels.cuh"
+#include "skin.cuh"
+
+using namespace rg;
+
+namespace {
+char* abase(char* p) { return reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(p), 256)); }
+bool al16(const void* p) { return (reinterpret_cast<size_t>(p) & 15) == 0; }
+
+struct FkSlots {
+    float *G, *node_rot, *posed, *dG, *dradius, *dtrans;
+    explicit FkSlots(float* b) {
+        G = b; node_rot = G + 128 * 12; posed = node_rot + 128 * 4; dG = posed + 128 * 3; dradius = dG + 128 * 12;
+        dtrans = dradius + 128;
+    }
+};
+
+int check_scene(const RgSkinnedScene* s, const RgWorkspace* w, const char* who) {
+    if (!s || !w) { set_error(std::string(who) + ": null scene/workspace"); return -1; }
+    if (s->P <= 0 || s->width <= 0 || s->height <= 0) { set_error(std::string(who) + ": empty problem"); return -1; }
+    if (s->J < 2 || s->J > 128) { set_error(std::string(who) + ": J must be in [2, 128]"); return -1; }
+    if (s->M_rest < 0 || s->M_rest > 15) { set_error(std::string(who) + ": at most 15 rest SH coefficients"); return -1; }
+    if (!al16(s->rotation_raw)) { set_error(std::string(who) + ": rotation_raw must be 16-byte aligned"); return -1; }
+    if (!w->geom || !w->image || !w->binning) { set_error(std::string(who) + ": workspace buffers missing"); return -1; }
+    if (w->geom_bytes < rg_geom_bytes(s->P, s->width, s->height) || w->image_bytes < rg_image_bytes(s->width, s->height)) {
+        set_error(std::string(who) + ": workspace geom/image buffer too small");
+        return -1;
+    }
+    if (w->binning_bytes < 1024) { set_error(std::string(who) + ": workspace binning buffer too small"); return -1; }
+    return 0;
+}
+
+SkinFuseArgs fuse_args(const RgSkinnedScene* s, const GeomState& geom, const FkSlots& fk) {
+    SkinFuseArgs f = {};
+    f.J = s->J; f.M_rest = s->M_rest; f.isotropic = s->isotropic != 0; f.zero_d_rotation = s->zero_d_rotation != 0;
+    f.xyz = s->xyz; f.scaling_raw = s->scaling_raw; f.rotation_raw = s->rotation_raw; f.opacity_raw = s->opacity_raw;
+    f.features_dc = s->features_dc; f.features_rest = s->features_rest; f.motion_mask = s->motion_mask;
+    f.mlp_weight = s->mlp_weight; f.offsets = s->offsets; f.joints = s->joints; f.parents = s->parents;
+    f.node_radius_raw = s->node_radius_raw; f.G = fk.G; f.node_rot = fk.node_rot; f.global_trans = s->global_trans;
+    f.means3D_out = geom.means3D; f.d_rot_out = geom.d_rot;
+    return f;
+}
+}  // namespace
+
+extern "C" {
+
+uint32_t rg_binning_capacity(size_t binning_bytes) {
+    if (binning_bytes < 1024) return 0;
+    size_t n = (binning_bytes - 512) / 4;
+    return n > 0xfffffff0u ? 0xfffffff0u : (uint32_t)n;
+}
+
+int rg_skinned_forward(const RgSkinnedScene* s, const RgWorkspace* w, float* out_color, float* out_depth,
+                       float* out_alpha, int* radii, float* d_nodes, float* dbg_scales, float* dbg_rotations,
+                       float* dbg_opacities, rg_stream_t stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (check_scene(s, w, "rg_skinned_forward")) return -1;
+    const int P = s->P, W = s->width, H = s->height;
+    const int grid_x = (W + RG_TILE - 1) / RG_TILE, grid_y = (H + RG_TILE - 1) / RG_TILE;
+    GeomState geom = GeomState::carve(abase(w->geom), P, W, H, nullptr);
+    ImageState img = ImageState::carve(abase(w->image), W, H, nullptr);
+    const uint32_t cap = rg_binning_capacity(w->binning_bytes);
+    BinningState bin = BinningState::carve(abase(w->binning), cap, nullptr);
+    FkSlots fk(geom.fk);
+    const BinPlan bp = make_bin_plan(P, grid_x * grid_y);
+
+    if (launch_fk_forward(1, s->J, s->local_rot, s->global_trans, s->joints, s->parents, fk.G, fk.node_rot,
+                          d_nodes ? d_nodes : fk.posed, stream))
+        return -1;
+
+    PreprocessArgs pa = {};
+    pa.P = P; pa.D = s->sh_degree; pa.M = s->M_rest + 1;
+    pa.scale_modifier = s->scale_modifier;
+    pa.viewmatrix = s->viewmatrix; pa.projmatrix = s->projmatrix; pa.cam_pos = s->campos;
+    pa.W = W; pa.H = H; pa.tan_fovx = s->tan_fovx; pa.tan_fovy = s->tan_fovy;
+    pa.focal_y = H / (2.0f * s->tan_fovy); pa.focal_x = W / (2.0f * s->tan_fovx);
+    pa.grid_x = grid_x; pa.grid_y = grid_y; pa.prefiltered = false; pa.sh_vec_ok = false;
+    pa.radii = radii; pa.means2D = geom.means2D; pa.depths = geom.depths; pa.rgb = geom.rgb;
+    pa.conic_opacity = geom.conic_opacity; pa.tiles_touched = geom.tiles_touched; pa.clamped = geom.clamped;
+    pa.ids = geom.ids;
+    SkinFuseArgs f = fuse_args(s, geom, fk);
+    f.dbg_scales = dbg_scales; f.dbg_rotations = dbg_rotations; f.dbg_opacities = dbg_opacities;
+    if (dbg_rotations && !al16(dbg_rotations)) { set_error("rg_skinned_forward: dbg_rotations must be 16-byte aligned"); return -1; }
+    if (launch_skin_preprocess(pa, f, stream)) return -1;
+
+    if (launch_depth_sort(geom.sort_temp, geom.sort_temp_bytes, geom.depths, geom.sorted_keys, geom.ids, geom.sorted_ids, P, stream))
+        return -1;
+    if (launch_tile_count(bp, P, grid_x, grid_y, geom.sorted_ids, geom.tiles_touched, geom.means2D, radii, geom.M, stream))
+        return -1;
+    launch_tile_offsets_a(bp, geom.M, geom.S, geom.tile_base, img.ranges, geom.status, cap, stream);
+    launch_tile_scatter(bp, P, grid_x, grid_y, geom.sorted_ids, geom.tiles_touched, geom.means2D, radii, geom.M, geom.S,
+                        geom.tile_base, geom.E, bin.point_list, cap, stream);
+
+    BlendFwdArgs fa;
+    fa.W = W; fa.H = H; fa.grid_x = grid_x; fa.grid_y = grid_y;
+    fa.ranges = img.ranges; fa.point_list = bin.point_list; fa.means2D = geom.means2D; fa.colors = geom.rgb;
+    fa.depths = geom.depths; fa.conic_opacity = geom.conic_opacity; fa.bg = s->background;
+    fa.out_color = out_color; fa.out_depth = out_depth; fa.out_alpha = out_alpha; fa.n_contrib = img.n_contrib;
+    launch_blend_forward(fa, stream);
+    return check_launch("rg_skinned_forward", stream, false);
+}
+
+int rg_skinned_status(const RgSkinnedScene* s, const RgWorkspace* w, uint32_t* host_out2, rg_stream_t stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (!s || !w || !host_out2) { set_error("rg_skinned_status: null argument"); return -1; }
+    GeomState geom = GeomState::carve(abase(w->geom), s->P, s->width, s->height, nullptr);
+    cudaError_t e = cudaMemcpyAsync(host_out2, geom.status, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, stream);
+    if (e != cudaSuccess) { set_error(std::string("rg_skinned_status: ") + cudaGetErrorString(e)); return -1; }
+    return 0;
+}
+
+int rg_skinned_backward(const RgSkinnedScene* s, const RgWorkspace* w, const int* radii, const float* alphas,
+                        const float* dL_dcolor, const float* dL_ddepth, const float* dL_dalpha, const float* dL_dnodes,
+                        float* d_xyz, float* d_scaling_raw, float* d_rotation_raw, float* d_opacity_raw,
+                        float* d_features_dc, float* d_features_rest, float* d_mean2D, float* d_local_rot,
+                        float* d_global_trans, float* d_node_radius_raw, float* d_mask, float* d_mlp_weight,
+                        float* d_offsets, rg_stream_t stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (check_scene(s, w, "rg_skinned_backward")) return -1;
+    if (!al16(d_rotation_raw)) { set_error("rg_skinned_backward: d_rotation_raw must be 16-byte aligned"); return -1; }
+    const int P = s->P, W = s->width, H = s->height;
+    const int grid_x = (W + RG_TILE - 1) / RG_TILE, grid_y = (H + RG_TILE - 1) / RG_TILE;
+    GeomState geom = GeomState::carve(abase(w->geom), P, W, H, nullptr);
+    ImageState img = ImageState::carve(abase(w->image), W, H, nullptr);
+    const uint32_t cap = rg_binning_capacity(w->binning_bytes);
+    BinningState bin = BinningState::carve(abase(w->binning), cap, nullptr);
+    FkSlots fk(geom.fk);
+
+    cudaMemsetAsync(geom.grad_acc, 0, sizeof(float) * 10 * (size_t)P, stream);
+    cudaMemsetAsync(fk.dG, 0, sizeof(float) * (128 * 12 + 128 + 4), stream);
+
+    BlendBwdArgs ba;
+    ba.P = P; ba.W = W; ba.H = H; ba.grid_x = grid_x; ba.grid_y = grid_y;
+    ba.ranges = img.ranges; ba.point_list = bin.point_list; ba.bg = s->background; ba.means2D = geom.means2D;
+    ba.conic_opacity = geom.conic_opacity; ba.colors = geom.rgb; ba.depths = geom.depths; ba.alphas = alphas;
+    ba.n_contrib = img.n_contrib; ba.dL_dpix = dL_dcolor; ba.dL_dpix_depth = dL_ddepth; ba.dL_dalphas = dL_dalpha;
+    ba.grad_acc = geom.grad_acc;
+    launch_blend_backward(ba, stream);
+
+    GaussBwdArgs ga = {};
+    ga.P = P; ga.D = s->sh_degree; ga.M = s->M_rest + 1; ga.means3D = geom.means3D; ga.radii = radii;
+    ga.clamped = geom.clamped; ga.scale_modifier = s->scale_modifier;
+    ga.viewmatrix = s->viewmatrix; ga.projmatrix = s->projmatrix; ga.campos = s->campos; ga.W = W; ga.H = H;
+    ga.tan_fovx = s->tan_fovx; ga.tan_fovy = s->tan_fovy;
+    ga.focal_y = H / (2.0f * s->tan_fovy); ga.focal_x = W / (2.0f * s->tan_fovx);
+    ga.grad_acc = geom.grad_acc; ga.dL_dmean2D = d_mean2D;
+    SkinFuseBwdArgs sb = {};
+    sb.f = fuse_args(s, geom, fk);
+    sb.d_rot_saved = geom.d_rot;
+    sb.d_xyz = d_xyz; sb.d_scaling_raw = d_scaling_raw; sb.d_rotation_raw = d_rotation_raw; sb.d_opacity_raw = d_opacity_raw;
+    sb.d_features_dc = d_features_dc; sb.d_features_rest = d_features_rest;
+    sb.dG = fk.dG; sb.dnode_radius_raw = fk.dradius; sb.dglobal_trans = fk.dtrans;
+    sb.dmask = d_mask; sb.dmlp_weight = d_mlp_weight; sb.doffsets = d_offsets;
+    if (launch_gauss_skin_backward(ga, sb, stream)) return -1;
+
+    if (launch_fk_backward(1, s->J, s->local_rot, s->joints, s->parents, fk.G, fk.dG, dL_dnodes, d_local_rot, d_global_trans,
+                           fk.dtrans, stream))
+        return -1;
+    if (d_node_radius_raw)
+        cudaMemcpyAsync(d_node_radius_raw, fk.dradius, sizeof(float) * s->J, cudaMemcpyDeviceToDevice, stream);
+    return check_launch("rg_skinned_backward", stream, false);
+}
+
+}  // extern "C"

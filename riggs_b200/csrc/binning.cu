@@ -178,7 +178,8 @@ __global__ void __launch_bounds__(1024) tile_base_kernel(int T, int nseg, uint32
         const uint32_t excl = carry + (warp ? s_warp[warp - 1] : 0) + x - tot;
         if (t < T) {
             tile_base[t] = excl;
-            ranges[t] = tot ? make_uint2(excl, excl + tot) : make_uint2(0, 0);
+            // clamped to the caller's capacity so an overflowing frame (flagged in status[1]) stays memory-safe
+            ranges[t] = tot ? make_uint2(min(excl, capacity), min(excl + tot, capacity)) : make_uint2(0, 0);
         }
         __syncthreads();
         if (threadIdx.x == 1023) s_carry = carry + s_warp[31];

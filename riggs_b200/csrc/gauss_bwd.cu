@@ -1,121 +1,26 @@
-// Per-Gaussian backward: 2-D gradients (mean2D, conic, opacity, colour, depth) -> gradients of means3D,
-// cov3D, SH, scale, rotation.  One thread per Gaussian, ONE kernel: it replaces both computeCov2DCUDA
+// Per-Gaussian backward: 2-D gradients (mean2D, conic, opacity, colour, depth) -> gradients of the 3-D
+// parameters.  One thread per Gaussian, ONE kernel.
+//
+// gauss_backward_kernel<false> (reference-shaped entry) replaces both computeCov2DCUDA
 // (dgr/cuda_rasterizer/backward.cu:144-274) and the backward preprocessCUDA (:346-412) with their helpers
 // (SH backward :20-139, cov3D backward :278-341), which the reference runs as two passes over all P.
+// Every output row is written (zeros for culled Gaussians), so the caller hands in uninitialised memory; the
+// reference's binding zero-fills ~300 B per Gaussian per step instead (dgr/rasterize_points.cu:158-167).
 //
-// Every output row is written (zeros for culled Gaussians), so the caller hands in uninitialised memory;
-// the reference's binding zero-fills ~300 B per Gaussian per step instead (dgr/rasterize_points.cu:158-167).
-// HBM-bound: reads 44 + 12*M + 40 (+24 with a kept covariance) bytes, writes 88 + 12*M bytes per Gaussian.
+// gauss_backward_kernel<true> (fused entry) continues in registers through the activations
+// (exp / normalize / sigmoid, gaussian_renderer/__init__.py:74-92) and through the skinning
+// (SURVEY.md appendix A.2): it writes gradients of the RAW model tensors (_xyz, _scaling, _rotation, _opacity,
+// _features_dc, _features_rest) and reduces the per-bone gradients dL/dG (3x4), dL/d_node_radius and
+// dL/dglobal_trans -- warp transpose-reduce, shared-memory accumulators per CTA, one atomicAdd per value per CTA.
+//
+// HBM-bound: reads 44 + 12*M + 40 (+12 kept means3D) bytes, writes 88 + 12*M bytes per Gaussian.
+#include "bones.cuh"
 #include "common.cuh"
 #include "kernels.cuh"
 #include "math.cuh"
+#include "sh.cuh"
 
 namespace rg {
-
-__device__ __forceinline__ float3 dnormvdv(float3 v, float3 dv) {  // auxiliary.h:107-117
-    float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
-    float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
-    float3 r;
-    r.x = ((+sum2 - v.x * v.x) * dv.x - v.y * v.x * dv.y - v.z * v.x * dv.z) * invsum32;
-    r.y = (-v.x * v.y * dv.x + (sum2 - v.y * v.y) * dv.y - v.z * v.y * dv.z) * invsum32;
-    r.z = (-v.x * v.z * dv.x - v.y * v.z * dv.y + (sum2 - v.z * v.z) * dv.z) * invsum32;
-    return r;
-}
-
-// SH backward (backward.cu:20-139): writes dL_dsh rows 0..(deg+1)^2-1 and returns the mean gradient that
-// flows through the view direction.
-template <int MAXC>
-__device__ __forceinline__ float3 sh_backward(int deg, int M, const float3 pos, const float3 campos, const float* sh,
-                                              uint8_t clamp_bits, float3 dL_dcolor, float* __restrict__ dL_dsh_row,
-                                              bool vec_ok) {
-    const float3 dir_orig = {pos.x - campos.x, pos.y - campos.y, pos.z - campos.z};
-    const float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
-    const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
-    const float g[3] = {dL_dcolor.x * ((clamp_bits & 1) ? 0.f : 1.f), dL_dcolor.y * ((clamp_bits & 2) ? 0.f : 1.f),
-                        dL_dcolor.z * ((clamp_bits & 4) ? 0.f : 1.f)};
-    float dx[3] = {0, 0, 0}, dy[3] = {0, 0, 0}, dz[3] = {0, 0, 0};
-    float basis[MAXC];
-#pragma unroll
-    for (int k = 0; k < MAXC; k++) basis[k] = 0.f;
-    basis[0] = kSH_C0;
-#define SH(k, c) sh[(k) * 3 + (c)]
-    if (deg > 0) {
-        basis[1] = -kSH_C1 * y;
-        basis[2] = kSH_C1 * z;
-        basis[3] = -kSH_C1 * x;
-#pragma unroll
-        for (int c = 0; c < 3; c++) {
-            dx[c] = -kSH_C1 * SH(3, c);
-            dy[c] = -kSH_C1 * SH(1, c);
-            dz[c] = kSH_C1 * SH(2, c);
-        }
-        if (deg > 1) {
-            const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
-            basis[4] = kSH_C2[0] * xy;
-            basis[5] = kSH_C2[1] * yz;
-            basis[6] = kSH_C2[2] * (2.f * zz - xx - yy);
-            basis[7] = kSH_C2[3] * xz;
-            basis[8] = kSH_C2[4] * (xx - yy);
-#pragma unroll
-            for (int c = 0; c < 3; c++) {
-                dx[c] += kSH_C2[0] * y * SH(4, c) + kSH_C2[2] * 2.f * -x * SH(6, c) + kSH_C2[3] * z * SH(7, c) +
-                         kSH_C2[4] * 2.f * x * SH(8, c);
-                dy[c] += kSH_C2[0] * x * SH(4, c) + kSH_C2[1] * z * SH(5, c) + kSH_C2[2] * 2.f * -y * SH(6, c) +
-                         kSH_C2[4] * 2.f * -y * SH(8, c);
-                dz[c] += kSH_C2[1] * y * SH(5, c) + kSH_C2[2] * 2.f * 2.f * z * SH(6, c) + kSH_C2[3] * x * SH(7, c);
-            }
-            if (deg > 2) {
-                basis[9] = kSH_C3[0] * y * (3.f * xx - yy);
-                basis[10] = kSH_C3[1] * xy * z;
-                basis[11] = kSH_C3[2] * y * (4.f * zz - xx - yy);
-                basis[12] = kSH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy);
-                basis[13] = kSH_C3[4] * x * (4.f * zz - xx - yy);
-                basis[14] = kSH_C3[5] * z * (xx - yy);
-                basis[15] = kSH_C3[6] * x * (xx - 3.f * yy);
-#pragma unroll
-                for (int c = 0; c < 3; c++) {
-                    dx[c] += (kSH_C3[0] * SH(9, c) * 3.f * 2.f * xy + kSH_C3[1] * SH(10, c) * yz +
-                              kSH_C3[2] * SH(11, c) * -2.f * xy + kSH_C3[3] * SH(12, c) * -3.f * 2.f * xz +
-                              kSH_C3[4] * SH(13, c) * (-3.f * xx + 4.f * zz - yy) + kSH_C3[5] * SH(14, c) * 2.f * xz +
-                              kSH_C3[6] * SH(15, c) * 3.f * (xx - yy));
-                    dy[c] += (kSH_C3[0] * SH(9, c) * 3.f * (xx - yy) + kSH_C3[1] * SH(10, c) * xz +
-                              kSH_C3[2] * SH(11, c) * (-3.f * yy + 4.f * zz - xx) + kSH_C3[3] * SH(12, c) * -3.f * 2.f * yz +
-                              kSH_C3[4] * SH(13, c) * -2.f * xy + kSH_C3[5] * SH(14, c) * -2.f * yz +
-                              kSH_C3[6] * SH(15, c) * -3.f * 2.f * xy);
-                    dz[c] += (kSH_C3[1] * SH(10, c) * xy + kSH_C3[2] * SH(11, c) * 4.f * 2.f * yz +
-                              kSH_C3[3] * SH(12, c) * 3.f * (2.f * zz - xx - yy) + kSH_C3[4] * SH(13, c) * 4.f * 2.f * xz +
-                              kSH_C3[5] * SH(14, c) * (xx - yy));
-                }
-            }
-        }
-    }
-#undef SH
-    // dL_dsh[k] = basis_k * dL_dRGB; rows above the active degree stay zero.
-    if (vec_ok && M == MAXC) {
-        float out[MAXC * 3];
-#pragma unroll
-        for (int k = 0; k < MAXC; k++) {
-            out[3 * k] = basis[k] * g[0];
-            out[3 * k + 1] = basis[k] * g[1];
-            out[3 * k + 2] = basis[k] * g[2];
-        }
-        float4* o4 = reinterpret_cast<float4*>(dL_dsh_row);
-#pragma unroll
-        for (int i = 0; i < MAXC * 3 / 4; i++) o4[i] = {out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]};
-    } else {
-#pragma unroll
-        for (int k = 0; k < MAXC; k++) {
-            if (k < M) {
-                dL_dsh_row[3 * k] = basis[k] * g[0];
-                dL_dsh_row[3 * k + 1] = basis[k] * g[1];
-                dL_dsh_row[3 * k + 2] = basis[k] * g[2];
-            }
-        }
-    }
-    const float3 dL_ddir = {dx[0] * g[0] + dx[1] * g[1] + dx[2] * g[2], dy[0] * g[0] + dy[1] * g[1] + dy[2] * g[2],
-                            dz[0] * g[0] + dz[1] * g[1] + dz[2] * g[2]};
-    return dnormvdv(dir_orig, dL_ddir);
-}
 
 // cov3D backward (backward.cu:278-341): gradient w.r.t. scale and the UN-normalised quaternion.
 __device__ __forceinline__ void cov3d_backward(const float3 scale, float mod, const float4 rot, const float* dc,
@@ -155,181 +60,345 @@ __device__ __forceinline__ void cov3d_backward(const float3 scale, float mod, co
 #undef DM
 }
 
-__global__ void __launch_bounds__(256) gauss_backward_kernel(GaussBwdArgs a) {
+// Sum each of v[0..15] over the 32 lanes with 16 shuffles; the lane holds the total of v[(lane >> 1) & 15].
+__device__ __forceinline__ float transpose_reduce16(const float* v, int lane) {
+    const unsigned full = 0xffffffffu;
+    const bool u4 = lane & 16, u3 = lane & 8, u2 = lane & 4, u1 = lane & 2;
+    float w[8], x[4], y[2];
+#pragma unroll
+    for (int i = 0; i < 8; i++) w[i] = (u4 ? v[8 + i] : v[i]) + __shfl_xor_sync(full, u4 ? v[i] : v[8 + i], 16);
+#pragma unroll
+    for (int i = 0; i < 4; i++) x[i] = (u3 ? w[4 + i] : w[i]) + __shfl_xor_sync(full, u3 ? w[i] : w[4 + i], 8);
+#pragma unroll
+    for (int i = 0; i < 2; i++) y[i] = (u2 ? x[2 + i] : x[i]) + __shfl_xor_sync(full, u2 ? x[i] : x[2 + i], 4);
+    float s = (u1 ? y[1] : y[0]) + __shfl_xor_sync(full, u1 ? y[0] : y[1], 2);
+    s += __shfl_xor_sync(full, s, 1);
+    return s;  // value id = 8*u4 + 4*u3 + 2*u2 + u1
+}
+
+template <bool FUSED>
+__global__ void __launch_bounds__(256) gauss_backward_kernel(GaussBwdArgs a, SkinFuseBwdArgs s) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
     __shared__ float s_mat[35];
+    extern __shared__ __align__(16) unsigned char s_raw[];
     if (threadIdx.x < 16) s_mat[threadIdx.x] = a.viewmatrix[threadIdx.x];
     else if (threadIdx.x < 32) s_mat[threadIdx.x] = a.projmatrix[threadIdx.x - 16];
     else if (threadIdx.x < 35) s_mat[threadIdx.x] = a.campos[threadIdx.x - 32];
+    BoneSm* s_b = reinterpret_cast<BoneSm*>(s_raw);
+    const int K = FUSED ? s.f.J - 1 : 0;
+    float* s_acc = reinterpret_cast<float*>(s_raw + sizeof(BoneSm) * (size_t)(K > 1 ? K : 1));  // K*13 + 3
+    if (FUSED) {
+        stage_bones(s.f.J, s.f.joints, s.f.parents, s.f.node_radius_raw, s.f.G, s.f.node_rot, s_b);
+        for (int k = threadIdx.x; k < K * 13 + 3; k += blockDim.x) s_acc[k] = 0.f;
+    }
     __syncthreads();
-    if (idx >= a.P) return;
     const float* view = s_mat;
     const float* proj = s_mat + 16;
     const size_t i = (size_t)idx;
+    const bool in_range = idx < a.P;
+    const bool visible = in_range && a.radii[idx] > 0;
+    if (!FUSED && !in_range) return;
 
-    if (!(a.radii[idx] > 0)) {  // culled: all gradients are zero
-        a.dL_dmean2D[3 * i] = a.dL_dmean2D[3 * i + 1] = a.dL_dmean2D[3 * i + 2] = 0.f;
-        reinterpret_cast<float4*>(a.dL_dconic)[i] = {0.f, 0.f, 0.f, 0.f};
-        a.dL_dopacity[i] = 0.f;
-        a.dL_dcolor[3 * i] = a.dL_dcolor[3 * i + 1] = a.dL_dcolor[3 * i + 2] = 0.f;
-        a.dL_ddepth[i] = 0.f;
-        a.dL_dmean3D[3 * i] = a.dL_dmean3D[3 * i + 1] = a.dL_dmean3D[3 * i + 2] = 0.f;
+    float3 dL_dmean = {0, 0, 0};     // dL/dmeans3D
+    float3 ds = {0, 0, 0};           // dL/dscale (activated)
+    float4 dq = {0, 0, 0, 0};        // dL/drotation (as given to the rasterizer, i.e. normalised in the fused path)
+    float g_opacity = 0.f;
+    float2 g_mean2D = {0, 0};
+    float dcov[6] = {0, 0, 0, 0, 0, 0};
+    float3 g_color = {0, 0, 0};
+    float g_depth = 0.f;
+    float3 dL_dconic = {0, 0, 0};
+    float3 sc = {0, 0, 0};
+    float4 q = {0, 0, 0, 0};
+    float4 qraw = {0, 0, 0, 0};
+    float qnorm = 1.f, opacity_act = 0.f;
+    float basis[16], gsh[3] = {0, 0, 0};
 #pragma unroll
-        for (int k = 0; k < 6; k++) a.dL_dcov3D[6 * i + k] = 0.f;
+    for (int k = 0; k < 16; k++) basis[k] = 0.f;
+
+    if (visible) {
+        const float* acc = a.grad_acc + i * 10;
+        g_mean2D = {acc[0], acc[1]};
+        dL_dconic = {acc[2], acc[3], acc[4]};
+        g_opacity = acc[5];
+        g_color = {acc[6], acc[7], acc[8]};
+        g_depth = acc[9];
+        const float3 mean = {a.means3D[3 * i], a.means3D[3 * i + 1], a.means3D[3 * i + 2]};
+        float cov3D[6];
+        if (FUSED) {
+            // re-derive the activated scale / rotation exactly as the forward did
+            qraw = reinterpret_cast<const float4*>(s.f.rotation_raw)[i];
+            if (!s.f.zero_d_rotation) {
+                const float4 dr = reinterpret_cast<const float4*>(s.d_rot_saved)[i];
+                qraw.x += dr.x; qraw.y += dr.y; qraw.z += dr.z; qraw.w += dr.w;
+            }
+            qnorm = fmaxf(sqrtf(qraw.x * qraw.x + qraw.y * qraw.y + qraw.z * qraw.z + qraw.w * qraw.w), 1e-12f);
+            q = {qraw.x / qnorm, qraw.y / qnorm, qraw.z / qnorm, qraw.w / qnorm};
+            if (s.f.isotropic) { const float e = expf(s.f.scaling_raw[i]); sc = {e, e, e}; }
+            else sc = {expf(s.f.scaling_raw[3 * i]), expf(s.f.scaling_raw[3 * i + 1]), expf(s.f.scaling_raw[3 * i + 2])};
+            opacity_act = 1.0f / (1.0f + expf(-s.f.opacity_raw[i]));
+            cov3d_from_scale_rot(sc, a.scale_modifier, q, cov3D);
+        } else {
+            if (a.scales) {
+                sc = {a.scales[3 * i], a.scales[3 * i + 1], a.scales[3 * i + 2]};
+                q = reinterpret_cast<const float4*>(a.rotations)[i];
+            }
+            if (a.cov3D) {
+#pragma unroll
+                for (int k = 0; k < 6; k++) cov3D[k] = a.cov3D[6 * i + k];
+            } else {
+                cov3d_from_scale_rot(sc, a.scale_modifier, q, cov3D);
+            }
+        }
+
+        // ---- conic -> cov2D -> cov3D and the covariance path of the mean gradient (backward.cu:162-273)
+        Cov2D c2 = cov2d_project(mean, a.focal_x, a.focal_y, a.tan_fovx, a.tan_fovy, cov3D, view);
+        const Mat3& T = c2.T;
+        const float3 t = c2.t;
+        const float ca = c2.cov.x, cb = c2.cov.y, cc = c2.cov.z;
+        const float denom = ca * cc - cb * cb;
+        float dL_da = 0, dL_db = 0, dL_dc = 0;
+        const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+        if (denom2inv != 0) {
+            dL_da = denom2inv * (-cc * cc * dL_dconic.x + 2 * cb * cc * dL_dconic.y + (denom - ca * cc) * dL_dconic.z);
+            dL_dc = denom2inv * (-ca * ca * dL_dconic.z + 2 * ca * cb * dL_dconic.y + (denom - ca * cc) * dL_dconic.x);
+            dL_db = denom2inv * 2 * (cb * cc * dL_dconic.x - (denom + 2 * cb * cb) * dL_dconic.y + ca * cb * dL_dconic.z);
+            dcov[0] = (T.m[0][0] * T.m[0][0] * dL_da + T.m[0][0] * T.m[1][0] * dL_db + T.m[1][0] * T.m[1][0] * dL_dc);
+            dcov[3] = (T.m[0][1] * T.m[0][1] * dL_da + T.m[0][1] * T.m[1][1] * dL_db + T.m[1][1] * T.m[1][1] * dL_dc);
+            dcov[5] = (T.m[0][2] * T.m[0][2] * dL_da + T.m[0][2] * T.m[1][2] * dL_db + T.m[1][2] * T.m[1][2] * dL_dc);
+            dcov[1] = 2 * T.m[0][0] * T.m[0][1] * dL_da + (T.m[0][0] * T.m[1][1] + T.m[0][1] * T.m[1][0]) * dL_db +
+                      2 * T.m[1][0] * T.m[1][1] * dL_dc;
+            dcov[2] = 2 * T.m[0][0] * T.m[0][2] * dL_da + (T.m[0][0] * T.m[1][2] + T.m[0][2] * T.m[1][0]) * dL_db +
+                      2 * T.m[1][0] * T.m[1][2] * dL_dc;
+            dcov[4] = 2 * T.m[0][2] * T.m[0][1] * dL_da + (T.m[0][1] * T.m[1][2] + T.m[0][2] * T.m[1][1]) * dL_db +
+                      2 * T.m[1][1] * T.m[1][2] * dL_dc;
+        }
+        const float V[3][3] = {{cov3D[0], cov3D[1], cov3D[2]}, {cov3D[1], cov3D[3], cov3D[4]}, {cov3D[2], cov3D[4], cov3D[5]}};
+        float dT0[3], dT1[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            const float r0 = T.m[0][0] * V[k][0] + T.m[0][1] * V[k][1] + T.m[0][2] * V[k][2];
+            const float r1 = T.m[1][0] * V[k][0] + T.m[1][1] * V[k][1] + T.m[1][2] * V[k][2];
+            dT0[k] = 2 * r0 * dL_da + r1 * dL_db;
+            dT1[k] = 2 * r1 * dL_dc + r0 * dL_db;
+        }
+        // W[c][r] = view[4*r + c]
+        const float dL_dJ00 = view[0] * dT0[0] + view[4] * dT0[1] + view[8] * dT0[2];
+        const float dL_dJ02 = view[2] * dT0[0] + view[6] * dT0[1] + view[10] * dT0[2];
+        const float dL_dJ11 = view[1] * dT1[0] + view[5] * dT1[1] + view[9] * dT1[2];
+        const float dL_dJ12 = view[2] * dT1[0] + view[6] * dT1[1] + view[10] * dT1[2];
+        const float tz = 1.f / t.z;
+        const float tz2 = tz * tz;
+        const float tz3 = tz2 * tz;
+        const float h_x = a.focal_x, h_y = a.focal_y;
+        const float dL_dtx = c2.x_grad_mul * -h_x * tz2 * dL_dJ02;
+        const float dL_dty = c2.y_grad_mul * -h_y * tz2 * dL_dJ12;
+        const float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * t.x) * tz3 * dL_dJ02 +
+                             (2 * h_y * t.y) * tz3 * dL_dJ12;
+        dL_dmean = {view[0] * dL_dtx + view[1] * dL_dty + view[2] * dL_dtz,
+                    view[4] * dL_dtx + view[5] * dL_dty + view[6] * dL_dtz,
+                    view[8] * dL_dtx + view[9] * dL_dty + view[10] * dL_dtz};
+
+        // ---- projection and depth paths (backward.cu:372-403)
+        const float4 m_hom = xform_point_4x4(mean, proj);
+        const float m_w = 1.0f / (m_hom.w + 0.0000001f);
+        const float mul1 = (proj[0] * mean.x + proj[4] * mean.y + proj[8] * mean.z + proj[12]) * m_w * m_w;
+        const float mul2 = (proj[1] * mean.x + proj[5] * mean.y + proj[9] * mean.z + proj[13]) * m_w * m_w;
+        dL_dmean.x += (proj[0] * m_w - proj[3] * mul1) * g_mean2D.x + (proj[1] * m_w - proj[3] * mul2) * g_mean2D.y;
+        dL_dmean.y += (proj[4] * m_w - proj[7] * mul1) * g_mean2D.x + (proj[5] * m_w - proj[7] * mul2) * g_mean2D.y;
+        dL_dmean.z += (proj[8] * m_w - proj[11] * mul1) * g_mean2D.x + (proj[9] * m_w - proj[11] * mul2) * g_mean2D.y;
+        const float mul3 = view[2] * mean.x + view[6] * mean.y + view[10] * mean.z + view[14];
+        dL_dmean.x += (view[2] - view[3] * mul3) * g_depth;
+        dL_dmean.y += (view[6] - view[7] * mul3) * g_depth;
+        dL_dmean.z += (view[10] - view[11] * mul3) * g_depth;
+
+        // ---- SH path
+        if (FUSED || a.shs) {
+            float sh[48];
+            if (FUSED) load_sh_split(s.f.features_dc, s.f.features_rest, i, s.f.M_rest, sh);
+            else load_sh<16>(a.shs, i, a.M, a.sh_vec_ok, sh);
+            const float3 campos = {s_mat[32], s_mat[33], s_mat[34]};
+            const float3 dm = sh_backward_core(a.D, mean, campos, sh, a.clamped[idx], g_color, basis, gsh);
+            dL_dmean.x += dm.x;
+            dL_dmean.y += dm.y;
+            dL_dmean.z += dm.z;
+        }
+        // ---- scale / rotation path
+        if (FUSED || a.dL_dscale) cov3d_backward(sc, a.scale_modifier, q, dcov, ds, dq);
+    }
+
+    if (!FUSED) {
+        // ---- outputs of the reference-shaped entry: every row is written
+        a.dL_dmean2D[3 * i] = g_mean2D.x;
+        a.dL_dmean2D[3 * i + 1] = g_mean2D.y;
+        a.dL_dmean2D[3 * i + 2] = 0.f;
+        reinterpret_cast<float4*>(a.dL_dconic)[i] = {dL_dconic.x, dL_dconic.y, 0.f, dL_dconic.z};
+        a.dL_dopacity[i] = g_opacity;
+        a.dL_dcolor[3 * i] = g_color.x;
+        a.dL_dcolor[3 * i + 1] = g_color.y;
+        a.dL_dcolor[3 * i + 2] = g_color.z;
+        a.dL_ddepth[i] = g_depth;
+        a.dL_dmean3D[3 * i] = dL_dmean.x;
+        a.dL_dmean3D[3 * i + 1] = dL_dmean.y;
+        a.dL_dmean3D[3 * i + 2] = dL_dmean.z;
+#pragma unroll
+        for (int k = 0; k < 6; k++) a.dL_dcov3D[6 * i + k] = dcov[k];
         if (a.dL_dsh) {
             float* row = a.dL_dsh + i * a.M * 3;
             if (a.sh_vec_ok && a.M == 16) {
+                float out[48];
 #pragma unroll
-                for (int k = 0; k < 12; k++) reinterpret_cast<float4*>(row)[k] = {0.f, 0.f, 0.f, 0.f};
+                for (int k = 0; k < 16; k++) {
+                    out[3 * k] = basis[k] * gsh[0]; out[3 * k + 1] = basis[k] * gsh[1]; out[3 * k + 2] = basis[k] * gsh[2];
+                }
+#pragma unroll
+                for (int k = 0; k < 12; k++)
+                    reinterpret_cast<float4*>(row)[k] = {out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]};
             } else {
-                for (int k = 0; k < a.M * 3; k++) row[k] = 0.f;
+#pragma unroll
+                for (int k = 0; k < 16; k++) {
+                    if (k < a.M) {
+                        row[3 * k] = basis[k] * gsh[0]; row[3 * k + 1] = basis[k] * gsh[1]; row[3 * k + 2] = basis[k] * gsh[2];
+                    }
+                }
             }
         }
         if (a.dL_dscale) {
-            a.dL_dscale[3 * i] = a.dL_dscale[3 * i + 1] = a.dL_dscale[3 * i + 2] = 0.f;
-            reinterpret_cast<float4*>(a.dL_drot)[i] = {0.f, 0.f, 0.f, 0.f};
+            a.dL_dscale[3 * i] = ds.x;
+            a.dL_dscale[3 * i + 1] = ds.y;
+            a.dL_dscale[3 * i + 2] = ds.z;
+            reinterpret_cast<float4*>(a.dL_drot)[i] = dq;
         }
         return;
     }
 
-    // 2-D gradients accumulated by the backward blend
-    const float* acc = a.grad_acc + i * 10;
-    const float2 g_mean2D = {acc[0], acc[1]};
-    const float3 dL_dconic = {acc[2], acc[3], acc[4]};
-    const float g_opacity = acc[5];
-    const float3 g_color = {acc[6], acc[7], acc[8]};
-    const float g_depth = acc[9];
-    a.dL_dmean2D[3 * i] = g_mean2D.x;
-    a.dL_dmean2D[3 * i + 1] = g_mean2D.y;
-    a.dL_dmean2D[3 * i + 2] = 0.f;
-    reinterpret_cast<float4*>(a.dL_dconic)[i] = {dL_dconic.x, dL_dconic.y, 0.f, dL_dconic.z};
-    a.dL_dopacity[i] = g_opacity;
-    a.dL_dcolor[3 * i] = g_color.x;
-    a.dL_dcolor[3 * i + 1] = g_color.y;
-    a.dL_dcolor[3 * i + 2] = g_color.z;
-    a.dL_ddepth[i] = g_depth;
-
-    const float3 mean = {a.means3D[3 * i], a.means3D[3 * i + 1], a.means3D[3 * i + 2]};
-    float3 sc = {0, 0, 0};
-    float4 q = {0, 0, 0, 0};
-    float cov3D[6];
-    if (a.scales) {
-        sc = {a.scales[3 * i], a.scales[3 * i + 1], a.scales[3 * i + 2]};
-        q = reinterpret_cast<const float4*>(a.rotations)[i];
-    }
-    if (a.cov3D) {
+    // ================= fused entry: activations + skinning backward =================
+    // d(normalize): n = q / |q|  ->  dq_raw = (g - n (n.g)) / |q|
+    const float ndg = q.x * dq.x + q.y * dq.y + q.z * dq.z + q.w * dq.w;
+    const float4 drot_raw = {(dq.x - q.x * ndg) / qnorm, (dq.y - q.y * ndg) / qnorm, (dq.z - q.z * ndg) / qnorm,
+                             (dq.w - q.w * ndg) / qnorm};
+    if (in_range) {
+        s.d_xyz[3 * i] = dL_dmean.x; s.d_xyz[3 * i + 1] = dL_dmean.y; s.d_xyz[3 * i + 2] = dL_dmean.z;
+        a.dL_dmean2D[3 * i] = g_mean2D.x; a.dL_dmean2D[3 * i + 1] = g_mean2D.y; a.dL_dmean2D[3 * i + 2] = 0.f;
+        if (s.f.isotropic) s.d_scaling_raw[i] = (ds.x + ds.y + ds.z) * sc.x;
+        else { s.d_scaling_raw[3 * i] = ds.x * sc.x; s.d_scaling_raw[3 * i + 1] = ds.y * sc.y; s.d_scaling_raw[3 * i + 2] = ds.z * sc.z; }
+        reinterpret_cast<float4*>(s.d_rotation_raw)[i] = drot_raw;
+        s.d_opacity_raw[i] = g_opacity * opacity_act * (1.f - opacity_act);
+        s.d_features_dc[3 * i] = basis[0] * gsh[0]; s.d_features_dc[3 * i + 1] = basis[0] * gsh[1]; s.d_features_dc[3 * i + 2] = basis[0] * gsh[2];
+        float* rest = s.d_features_rest + i * s.f.M_rest * 3;
 #pragma unroll
-        for (int k = 0; k < 6; k++) cov3D[k] = a.cov3D[6 * i + k];
-    } else {
-        cov3d_from_scale_rot(sc, a.scale_modifier, q, cov3D);
-    }
-
-    // ---- conic -> cov2D -> cov3D and the covariance path of the mean gradient (backward.cu:162-273)
-    Cov2D c2 = cov2d_project(mean, a.focal_x, a.focal_y, a.tan_fovx, a.tan_fovy, cov3D, view);
-    const Mat3& T = c2.T;
-    const float3 t = c2.t;
-    const float ca = c2.cov.x, cb = c2.cov.y, cc = c2.cov.z;
-    const float denom = ca * cc - cb * cb;
-    float dL_da = 0, dL_db = 0, dL_dc = 0;
-    const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
-    float dcov[6] = {0, 0, 0, 0, 0, 0};
-    if (denom2inv != 0) {
-        dL_da = denom2inv * (-cc * cc * dL_dconic.x + 2 * cb * cc * dL_dconic.y + (denom - ca * cc) * dL_dconic.z);
-        dL_dc = denom2inv * (-ca * ca * dL_dconic.z + 2 * ca * cb * dL_dconic.y + (denom - ca * cc) * dL_dconic.x);
-        dL_db = denom2inv * 2 * (cb * cc * dL_dconic.x - (denom + 2 * cb * cb) * dL_dconic.y + ca * cb * dL_dconic.z);
-        dcov[0] = (T.m[0][0] * T.m[0][0] * dL_da + T.m[0][0] * T.m[1][0] * dL_db + T.m[1][0] * T.m[1][0] * dL_dc);
-        dcov[3] = (T.m[0][1] * T.m[0][1] * dL_da + T.m[0][1] * T.m[1][1] * dL_db + T.m[1][1] * T.m[1][1] * dL_dc);
-        dcov[5] = (T.m[0][2] * T.m[0][2] * dL_da + T.m[0][2] * T.m[1][2] * dL_db + T.m[1][2] * T.m[1][2] * dL_dc);
-        dcov[1] = 2 * T.m[0][0] * T.m[0][1] * dL_da + (T.m[0][0] * T.m[1][1] + T.m[0][1] * T.m[1][0]) * dL_db +
-                  2 * T.m[1][0] * T.m[1][1] * dL_dc;
-        dcov[2] = 2 * T.m[0][0] * T.m[0][2] * dL_da + (T.m[0][0] * T.m[1][2] + T.m[0][2] * T.m[1][0]) * dL_db +
-                  2 * T.m[1][0] * T.m[1][2] * dL_dc;
-        dcov[4] = 2 * T.m[0][2] * T.m[0][1] * dL_da + (T.m[0][1] * T.m[1][2] + T.m[0][2] * T.m[1][1]) * dL_db +
-                  2 * T.m[1][1] * T.m[1][2] * dL_dc;
-    }
-#pragma unroll
-    for (int k = 0; k < 6; k++) a.dL_dcov3D[6 * i + k] = dcov[k];
-
-    const float V[3][3] = {{cov3D[0], cov3D[1], cov3D[2]}, {cov3D[1], cov3D[3], cov3D[4]}, {cov3D[2], cov3D[4], cov3D[5]}};
-    float dT0[3], dT1[3];
-#pragma unroll
-    for (int k = 0; k < 3; k++) {
-        const float r0 = T.m[0][0] * V[k][0] + T.m[0][1] * V[k][1] + T.m[0][2] * V[k][2];
-        const float r1 = T.m[1][0] * V[k][0] + T.m[1][1] * V[k][1] + T.m[1][2] * V[k][2];
-        dT0[k] = 2 * r0 * dL_da + r1 * dL_db;
-        dT1[k] = 2 * r1 * dL_dc + r0 * dL_db;
-    }
-    // W[c][r] = view[4*r + c]
-    const float dL_dJ00 = view[0] * dT0[0] + view[4] * dT0[1] + view[8] * dT0[2];
-    const float dL_dJ02 = view[2] * dT0[0] + view[6] * dT0[1] + view[10] * dT0[2];
-    const float dL_dJ11 = view[1] * dT1[0] + view[5] * dT1[1] + view[9] * dT1[2];
-    const float dL_dJ12 = view[2] * dT1[0] + view[6] * dT1[1] + view[10] * dT1[2];
-    const float tz = 1.f / t.z;
-    const float tz2 = tz * tz;
-    const float tz3 = tz2 * tz;
-    const float h_x = a.focal_x, h_y = a.focal_y;
-    const float dL_dtx = c2.x_grad_mul * -h_x * tz2 * dL_dJ02;
-    const float dL_dty = c2.y_grad_mul * -h_y * tz2 * dL_dJ12;
-    const float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * t.x) * tz3 * dL_dJ02 +
-                         (2 * h_y * t.y) * tz3 * dL_dJ12;
-    float3 dL_dmean = {view[0] * dL_dtx + view[1] * dL_dty + view[2] * dL_dtz,
-                       view[4] * dL_dtx + view[5] * dL_dty + view[6] * dL_dtz,
-                       view[8] * dL_dtx + view[9] * dL_dty + view[10] * dL_dtz};
-
-    // ---- projection and depth paths (backward.cu:372-403)
-    const float4 m_hom = xform_point_4x4(mean, proj);
-    const float m_w = 1.0f / (m_hom.w + 0.0000001f);
-    const float mul1 = (proj[0] * mean.x + proj[4] * mean.y + proj[8] * mean.z + proj[12]) * m_w * m_w;
-    const float mul2 = (proj[1] * mean.x + proj[5] * mean.y + proj[9] * mean.z + proj[13]) * m_w * m_w;
-    dL_dmean.x += (proj[0] * m_w - proj[3] * mul1) * g_mean2D.x + (proj[1] * m_w - proj[3] * mul2) * g_mean2D.y;
-    dL_dmean.y += (proj[4] * m_w - proj[7] * mul1) * g_mean2D.x + (proj[5] * m_w - proj[7] * mul2) * g_mean2D.y;
-    dL_dmean.z += (proj[8] * m_w - proj[11] * mul1) * g_mean2D.x + (proj[9] * m_w - proj[11] * mul2) * g_mean2D.y;
-    const float mul3 = view[2] * mean.x + view[6] * mean.y + view[10] * mean.z + view[14];
-    dL_dmean.x += (view[2] - view[3] * mul3) * g_depth;
-    dL_dmean.y += (view[6] - view[7] * mul3) * g_depth;
-    dL_dmean.z += (view[10] - view[11] * mul3) * g_depth;
-
-    // ---- SH path
-    if (a.shs) {
-        float sh[48];
-        const float* src = a.shs + i * a.M * 3;
-        if (a.sh_vec_ok && a.M == 16) {
-#pragma unroll
-            for (int k = 0; k < 12; k++) {
-                float4 v = __ldg(reinterpret_cast<const float4*>(src) + k);
-                sh[4 * k] = v.x; sh[4 * k + 1] = v.y; sh[4 * k + 2] = v.z; sh[4 * k + 3] = v.w;
+        for (int k = 1; k < 16; k++) {
+            if (k <= s.f.M_rest) {
+                rest[3 * (k - 1)] = basis[k] * gsh[0]; rest[3 * (k - 1) + 1] = basis[k] * gsh[1]; rest[3 * (k - 1) + 2] = basis[k] * gsh[2];
             }
-        } else {
-#pragma unroll
-            for (int k = 0; k < 48; k++) sh[k] = k < a.M * 3 ? __ldg(src + k) : 0.f;
         }
-        const float3 campos = {s_mat[32], s_mat[33], s_mat[34]};
-        float3 dm = sh_backward<16>(a.D, a.M, mean, campos, sh, a.clamped[idx], g_color, a.dL_dsh + i * a.M * 3,
-                                    a.sh_vec_ok);
-        dL_dmean.x += dm.x;
-        dL_dmean.y += dm.y;
-        dL_dmean.z += dm.z;
     }
-    a.dL_dmean3D[3 * i] = dL_dmean.x;
-    a.dL_dmean3D[3 * i + 1] = dL_dmean.y;
-    a.dL_dmean3D[3 * i + 2] = dL_dmean.z;
 
-    // ---- scale / rotation path
-    if (a.dL_dscale) {
-        float3 ds;
-        float4 dq;
-        cov3d_backward(sc, a.scale_modifier, q, dcov, ds, dq);
-        a.dL_dscale[3 * i] = ds.x;
-        a.dL_dscale[3 * i + 1] = ds.y;
-        a.dL_dscale[3 * i + 2] = ds.z;
-        reinterpret_cast<float4*>(a.dL_drot)[i] = dq;
+    // ---- skinning backward (appendix A.2): a = dL/dmeans3D, h = dL/d(d_rotation)
+    float x = 0, y = 0, z = 0, m = 0;
+    if (in_range) {
+        x = s.f.xyz[3 * i]; y = s.f.xyz[3 * i + 1]; z = s.f.xyz[3 * i + 2];
+        m = s.f.motion_mask ? s.f.motion_mask[i] : 1.0f;
+    }
+    const float gx = dL_dmean.x, gy = dL_dmean.y, gz = dL_dmean.z;
+    const float h0 = s.f.zero_d_rotation ? 0.f : drot_raw.x, h1 = s.f.zero_d_rotation ? 0.f : drot_raw.y,
+                h2 = s.f.zero_d_rotation ? 0.f : drot_raw.z, h3 = s.f.zero_d_rotation ? 0.f : drot_raw.w;
+    const bool contributes = visible && (gx != 0.f || gy != 0.f || gz != 0.f || h0 != 0.f || h1 != 0.f || h2 != 0.f || h3 != 0.f);
+    const bool want_elem = s.dmask || s.doffsets || s.dmlp_weight;
+    if (!__any_sync(0xffffffffu, contributes)) {
+        if (in_range && want_elem) {
+            if (s.dmask) s.dmask[i] = 0.f;
+            if (s.doffsets) { s.doffsets[3 * i] = 0.f; s.doffsets[3 * i + 1] = 0.f; s.doffsets[3 * i + 2] = 0.f; }
+            if (s.dmlp_weight) for (int k = 0; k < K; k++) s.dmlp_weight[i * K + k] = 0.f;
+        }
+    } else {
+        // sweep 1: normaliser and sum_k w_k c_k
+        float wsum = 0.f, scw = 0.f, ax = 0.f, ay = 0.f, az = 0.f, q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
+        for (int k = 0; k < K; k++) {
+            const BoneSm& b = s_b[k];
+            const float d2 = seg_dist2(b, x, y, z);
+            float w = expf(-d2 * b.inv_2r2);
+            if (s.f.mlp_weight && in_range) w *= s.f.mlp_weight[i * K + k];
+            w += 1e-7f;
+            const float yx = b.G[0] * x + b.G[1] * y + b.G[2] * z + b.G[9];
+            const float yy = b.G[3] * x + b.G[4] * y + b.G[5] * z + b.G[10];
+            const float yz = b.G[6] * x + b.G[7] * y + b.G[8] * z + b.G[11];
+            const float c = gx * yx + gy * yy + gz * yz + h0 * b.q[0] + h1 * b.q[1] + h2 * b.q[2] + h3 * b.q[3];
+            wsum += w;
+            scw += w * c;
+            ax += w * yx; ay += w * yy; az += w * yz;
+            q0 += w * b.q[0]; q1 += w * b.q[1]; q2 += w * b.q[2]; q3 += w * b.q[3];
+        }
+        const float inv = 1.0f / wsum;
+        const float cbar = scw * inv;
+        if (in_range) {
+            float ox = 0.f, oy = 0.f, oz = 0.f;
+            if (s.f.offsets) { ox = s.f.offsets[3 * i]; oy = s.f.offsets[3 * i + 1]; oz = s.f.offsets[3 * i + 2]; }
+            if (s.dmask)
+                s.dmask[i] = gx * (ax * inv + s.f.global_trans[0] + ox - x) + gy * (ay * inv + s.f.global_trans[1] + oy - y) +
+                             gz * (az * inv + s.f.global_trans[2] + oz - z) + (h0 * q0 + h1 * q1 + h2 * q2 + h3 * q3) * inv;
+            if (s.doffsets) { s.doffsets[3 * i] = m * gx; s.doffsets[3 * i + 1] = m * gy; s.doffsets[3 * i + 2] = m * gz; }
+        }
+        const float mgx = m * gx, mgy = m * gy, mgz = m * gz;
+        {
+            const float s0 = warp_sum(mgx), s1 = warp_sum(mgy), s2 = warp_sum(mgz);
+            if (lane == 0) { atomicAdd(&s_acc[K * 13], s0); atomicAdd(&s_acc[K * 13 + 1], s1); atomicAdd(&s_acc[K * 13 + 2], s2); }
+        }
+        const int my_id = (lane >> 1) & 15;
+        const bool writer = !(lane & 1) && my_id < 13;
+        // sweep 2: per-bone terms, transpose-reduced over the warp
+        for (int k = 0; k < K; k++) {
+            const BoneSm& b = s_b[k];
+            const float d2 = seg_dist2(b, x, y, z);
+            const float e = expf(-d2 * b.inv_2r2);
+            const float sw = (s.f.mlp_weight && in_range) ? s.f.mlp_weight[i * K + k] : 1.0f;
+            const float w = (e * sw + 1e-7f) * inv;
+            const float yx = b.G[0] * x + b.G[1] * y + b.G[2] * z + b.G[9];
+            const float yy = b.G[3] * x + b.G[4] * y + b.G[5] * z + b.G[10];
+            const float yz = b.G[6] * x + b.G[7] * y + b.G[8] * z + b.G[11];
+            const float c = gx * yx + gy * yy + gz * yz + h0 * b.q[0] + h1 * b.q[1] + h2 * b.q[2] + h3 * b.q[3];
+            const float dwhat = m * (c - cbar) * inv;
+            if (s.dmlp_weight && in_range) s.dmlp_weight[i * K + k] = dwhat * e;
+            float v[16];
+            v[0] = mgx * w * x; v[1] = mgx * w * y; v[2] = mgx * w * z;
+            v[3] = mgy * w * x; v[4] = mgy * w * y; v[5] = mgy * w * z;
+            v[6] = mgz * w * x; v[7] = mgz * w * y; v[8] = mgz * w * z;
+            v[9] = mgx * w; v[10] = mgy * w; v[11] = mgz * w;
+            v[12] = dwhat * sw * e * d2 * (2.0f * b.inv_2r2);
+            v[13] = v[14] = v[15] = 0.f;
+            const float r = transpose_reduce16(v, lane);
+            if (writer && r != 0.f) atomicAdd(&s_acc[k * 13 + my_id], r);
+        }
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < K * 13; k += blockDim.x) {
+        const float val = s_acc[k];
+        if (val != 0.f) {
+            const int bone = k / 13, c = k % 13;
+            if (c < 12) atomicAdd(&s.dG[12 * (bone + 1) + c], val);
+            else atomicAdd(&s.dnode_radius_raw[bone + 1], val);
+        }
+    }
+    if (threadIdx.x < 3) {
+        const float val = s_acc[K * 13 + threadIdx.x];
+        if (val != 0.f) atomicAdd(&s.dglobal_trans[threadIdx.x], val);
     }
 }
 
 int launch_gauss_backward(const GaussBwdArgs& a, cudaStream_t stream) {
     if (a.P == 0) return 0;
     LaunchScope ls("gauss_backward", stream);
-    gauss_backward_kernel<<<(a.P + 255) / 256, 256, 0, stream>>>(a);
+    SkinFuseBwdArgs none = {};
+    gauss_backward_kernel<false><<<(a.P + 255) / 256, 256, 0, stream>>>(a, none);
+    return 0;
+}
+
+int launch_gauss_skin_backward(const GaussBwdArgs& a, const SkinFuseBwdArgs& s, cudaStream_t stream) {
+    if (a.P == 0) return 0;
+    if (s.f.J > kMaxJoints || s.f.J < 2) { set_error("skinned backward: J must be in [2, 128]"); return -1; }
+    LaunchScope ls("gauss_skin_backward", stream);
+    gauss_backward_kernel<true><<<(a.P + 255) / 256, 256, bone_smem_bytes(s.f.J, true), stream>>>(a, s);
     return 0;
 }
 

@@ -35,7 +35,55 @@ struct PreprocessArgs {
     uint32_t* ids;  // iota, value array of the depth sort
 };
 
+// Extra inputs of the fused skin + activation + preprocess kernel: raw model tensors and one pose's bone table.
+struct SkinFuseArgs {
+    int J, M_rest;
+    bool isotropic;        // _scaling has one column
+    bool zero_d_rotation;  // the trainer zeroes d_rotation for isotropic Gaussians (train_rig.py:422-423)
+    const float* xyz;
+    const float* scaling_raw;
+    const float* rotation_raw;
+    const float* opacity_raw;
+    const float* features_dc;
+    const float* features_rest;
+    const float* motion_mask;  // optional (N)
+    const float* mlp_weight;   // optional (N,J-1)
+    const float* offsets;      // optional (N,3)
+    const float* joints;
+    const int* parents;
+    const float* node_radius_raw;
+    const float* G;         // (J,12)
+    const float* node_rot;  // (J,4)
+    const float* global_trans;
+    float* means3D_out;  // (N,3) kept for the backward
+    float* d_rot_out;    // (N,4) blended bone quaternion * mask, kept for the backward
+    float* dbg_scales;   // optional test outputs: the activated tensors the reference rasterizer would be given
+    float* dbg_rotations;
+    float* dbg_opacities;
+};
+
+struct SkinFuseBwdArgs {
+    SkinFuseArgs f;
+    const float* d_rot_saved;  // (N,4) from the forward
+    // gradients of the raw model tensors (fully written)
+    float* d_xyz;
+    float* d_scaling_raw;
+    float* d_rotation_raw;
+    float* d_opacity_raw;
+    float* d_features_dc;
+    float* d_features_rest;
+    // skeleton gradients (accumulated with atomics; zeroed by the launcher's caller)
+    float* dG;                // (J,12)
+    float* dnode_radius_raw;  // (J)
+    float* dglobal_trans;     // (3)
+    // optional element-wise outputs
+    float* dmask;
+    float* dmlp_weight;
+    float* doffsets;
+};
+
 int launch_preprocess(const PreprocessArgs& a, cudaStream_t stream);
+int launch_skin_preprocess(const PreprocessArgs& a, const SkinFuseArgs& s, cudaStream_t stream);
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t stream);
 
 // ---- binning (binning.cu) ----
@@ -126,5 +174,6 @@ struct GaussBwdArgs {
     float* dL_drot;      // P*4 or null
 };
 int launch_gauss_backward(const GaussBwdArgs& a, cudaStream_t stream);
+int launch_gauss_skin_backward(const GaussBwdArgs& a, const SkinFuseBwdArgs& s, cudaStream_t stream);
 
 }  // namespace rg

@@ -1,146 +1,162 @@
-// Per-Gaussian forward stage: frustum cull, projection, 3D->2D covariance, conic, radius, tile rectangle,
-// SH->RGB.  One thread per Gaussian; replaces preprocessCUDA (dgr/cuda_rasterizer/forward.cu:155-256) and
-// checkFrustum (dgr/cuda_rasterizer/rasterizer_impl.cu:54-66).
+// Per-Gaussian forward stage: [skeleton skinning + parameter activations ->] frustum cull, projection, 3D->2D
+// covariance, conic, radius, tile rectangle, SH->RGB.  One thread per Gaussian.
+//
+// preprocess_kernel<false> replaces preprocessCUDA (dgr/cuda_rasterizer/forward.cu:155-256) behind the
+// reference-shaped entry point (activated means3D / scales / rotations / opacities / shs come from the caller).
+//
+// preprocess_kernel<true> is the fused entry: it starts from the RAW model parameters and folds in
+//   * linear-blend skinning over the bone table held in shared memory
+//     (SkeletonWarp.deform_by_pose, skeleton_utils/skeleton_warp.py:130-172),
+//   * means3D = xyz + d_xyz, scales = exp(_scaling), rotations = normalize(_rotation + d_rotation),
+//     opacity = sigmoid(_opacity), shs = cat(features_dc, features_rest)
+//     (render(), gaussian_renderer/__init__.py:74-114; scene/gaussian_model.py:105-132),
+// so the ~40 eager torch kernels of the skinning chain, the 6-8 activation kernels and the SH cat (192 B per
+// Gaussian read + written every frame) disappear; nothing of size N is materialised except means3D (kept for
+// the backward).
 //
 // HBM-bound streaming kernel: algorithmic bytes per Gaussian = 44 (xyz, rot, scale, opacity) + 12*M (SH)
-// read, 48 written (+1 clamp byte, +24 when cov3D is kept for a precomputed-covariance backward).
+// read, 48 written (+1 clamp byte, +12 means3D in the fused variant).
+#include "bones.cuh"
 #include "common.cuh"
-#include "math.cuh"
 #include "kernels.cuh"
+#include "math.cuh"
+#include "sh.cuh"
 
 namespace rg {
 
-// SH -> RGB for one Gaussian (forward.cu:20-71).  sh points at M*3 floats (coefficient-major, rgb inner).
-__device__ __forceinline__ float3 sh_to_rgb(int deg, const float3 pos, const float3 campos, const float* sh,
-                                            uint8_t& clamp_bits) {
-    float3 dir = {pos.x - campos.x, pos.y - campos.y, pos.z - campos.z};
-    float len = sqrtf(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
-    const float x = dir.x / len, y = dir.y / len, z = dir.z / len;
-    float res[3];
-#pragma unroll
-    for (int c = 0; c < 3; c++) {
-#define SH(k) sh[(k) * 3 + c]
-        float r = kSH_C0 * SH(0);
-        if (deg > 0) {
-            r = r - kSH_C1 * y * SH(1) + kSH_C1 * z * SH(2) - kSH_C1 * x * SH(3);
-            if (deg > 1) {
-                float xx = x * x, yy = y * y, zz = z * z;
-                float xy = x * y, yz = y * z, xz = x * z;
-                r = r + kSH_C2[0] * xy * SH(4) + kSH_C2[1] * yz * SH(5) + kSH_C2[2] * (2.0f * zz - xx - yy) * SH(6) +
-                    kSH_C2[3] * xz * SH(7) + kSH_C2[4] * (xx - yy) * SH(8);
-                if (deg > 2) {
-                    r = r + kSH_C3[0] * y * (3.0f * xx - yy) * SH(9) + kSH_C3[1] * xy * z * SH(10) +
-                        kSH_C3[2] * y * (4.0f * zz - xx - yy) * SH(11) +
-                        kSH_C3[3] * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * SH(12) +
-                        kSH_C3[4] * x * (4.0f * zz - xx - yy) * SH(13) + kSH_C3[5] * z * (xx - yy) * SH(14) +
-                        kSH_C3[6] * x * (xx - 3.0f * yy) * SH(15);
-                }
-            }
-        }
-#undef SH
-        r += 0.5f;
-        res[c] = r;
-    }
-    clamp_bits = (res[0] < 0 ? 1 : 0) | (res[1] < 0 ? 2 : 0) | (res[2] < 0 ? 4 : 0);
-    return {fmaxf(res[0], 0.0f), fmaxf(res[1], 0.0f), fmaxf(res[2], 0.0f)};
-}
-
-// Loads the M*3 SH floats of Gaussian idx into registers; 128-bit loads when the row is 16-byte aligned.
-template <int MAXC>
-__device__ __forceinline__ void load_sh(const float* __restrict__ shs, size_t idx, int M, bool vec_ok, float* sh) {
-    const float* src = shs + idx * (size_t)M * 3;
-    if (vec_ok && M == MAXC) {
-        const float4* s4 = reinterpret_cast<const float4*>(src);
-#pragma unroll
-        for (int i = 0; i < MAXC * 3 / 4; i++) {
-            float4 v = __ldg(s4 + i);
-            sh[4 * i] = v.x; sh[4 * i + 1] = v.y; sh[4 * i + 2] = v.z; sh[4 * i + 3] = v.w;
-        }
-    } else {
-#pragma unroll
-        for (int i = 0; i < MAXC * 3; i++) sh[i] = i < M * 3 ? __ldg(src + i) : 0.f;
-    }
-}
-
-__global__ void __launch_bounds__(256) preprocess_kernel(PreprocessArgs a) {
+template <bool FUSED>
+__global__ void __launch_bounds__(256) preprocess_kernel(PreprocessArgs a, SkinFuseArgs s) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     __shared__ float s_mat[35];  // view[16], proj[16], campos[3]
+    extern __shared__ __align__(16) unsigned char s_raw[];
     if (threadIdx.x < 16) s_mat[threadIdx.x] = a.viewmatrix[threadIdx.x];
     else if (threadIdx.x < 32) s_mat[threadIdx.x] = a.projmatrix[threadIdx.x - 16];
     else if (threadIdx.x < 35) s_mat[threadIdx.x] = a.cam_pos[threadIdx.x - 32];
+    BoneSm* s_b = reinterpret_cast<BoneSm*>(s_raw);
+    if (FUSED) stage_bones(s.J, s.joints, s.parents, s.node_radius_raw, s.G, s.node_rot, s_b);
     __syncthreads();
+    if (idx >= a.P) return;
     const float* view = s_mat;
     const float* proj = s_mat + 16;
-    uint32_t my_tiles = 0;
-    if (idx < a.P) {
-        int radius_out = 0;
-        float3 p_orig = {a.means3D[3 * idx], a.means3D[3 * idx + 1], a.means3D[3 * idx + 2]};
-        float3 p_view = xform_point_4x3(p_orig, view);
-        do {
-            if (p_view.z <= 0.2f) {  // near cull (auxiliary.h:154)
-                if (a.prefiltered) {
-                    printf("Point is filtered although prefiltered is set. This shouldn't happen!");
-                    __trap();
-                }
-                break;
-            }
-            float4 p_hom = xform_point_4x4(p_orig, proj);
-            float p_w = 1.0f / (p_hom.w + 0.0000001f);
-            float3 p_proj = {p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w};
+    const size_t i = (size_t)idx;
 
-            float cov3D[6];
-            if (a.cov3D_precomp != nullptr) {
-#pragma unroll
-                for (int k = 0; k < 6; k++) cov3D[k] = a.cov3D_precomp[6 * (size_t)idx + k];
-            } else {
-                float3 sc = {a.scales[3 * idx], a.scales[3 * idx + 1], a.scales[3 * idx + 2]};
-                float4 q = reinterpret_cast<const float4*>(a.rotations)[idx];
-                cov3d_from_scale_rot(sc, a.scale_modifier, q, cov3D);
-                if (a.cov3D_out) {
-#pragma unroll
-                    for (int k = 0; k < 6; k++) a.cov3D_out[6 * (size_t)idx + k] = cov3D[k];
-                }
-            }
-            Cov2D c2 = cov2d_project(p_orig, a.focal_x, a.focal_y, a.tan_fovx, a.tan_fovy, cov3D, view);
-            float3 cov = c2.cov;
-            float det = (cov.x * cov.z - cov.y * cov.y);
-            if (det == 0.0f) break;
-            float det_inv = 1.f / det;
-            float3 conic = {cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv};
-            float mid = 0.5f * (cov.x + cov.z);
-            float lambda1 = mid + sqrtf(fmaxf(0.1f, mid * mid - det));
-            float lambda2 = mid - sqrtf(fmaxf(0.1f, mid * mid - det));
-            float my_radius = ceilf(3.f * sqrtf(fmaxf(lambda1, lambda2)));
-            float2 point_image = {ndc_to_pix(p_proj.x, a.W), ndc_to_pix(p_proj.y, a.H)};
-            uint2 rect_min, rect_max;
-            tile_rect(point_image, (int)my_radius, rect_min, rect_max, a.grid_x, a.grid_y);
-            if ((rect_max.x - rect_min.x) * (rect_max.y - rect_min.y) == 0) break;
-
-            float3 color;
-            uint8_t clamp_bits = 0;
-            if (a.colors_precomp == nullptr) {
-                float sh[48];
-                load_sh<16>(a.shs, idx, a.M, a.sh_vec_ok, sh);
-                const float3 campos = {s_mat[32], s_mat[33], s_mat[34]};
-                color = sh_to_rgb(a.D, p_orig, campos, sh, clamp_bits);
-            } else {
-                color = {a.colors_precomp[3 * idx], a.colors_precomp[3 * idx + 1], a.colors_precomp[3 * idx + 2]};
-            }
-            a.clamped[idx] = clamp_bits;
-            a.rgb[3 * idx] = color.x;
-            a.rgb[3 * idx + 1] = color.y;
-            a.rgb[3 * idx + 2] = color.z;
-            a.depths[idx] = p_view.z;
-            radius_out = (int)my_radius;
-            a.means2D[idx] = point_image;
-            a.conic_opacity[idx] = {conic.x, conic.y, conic.z, a.opacities[idx]};
-            my_tiles = (rect_max.y - rect_min.y) * (rect_max.x - rect_min.x);
-        } while (false);
-        a.radii[idx] = radius_out;
-        a.tiles_touched[idx] = my_tiles;
-        if (my_tiles == 0) a.depths[idx] = __int_as_float(0x7f800000);  // culled: +inf sorts behind everything
-        a.ids[idx] = idx;
+    float3 p_orig, sc = {0, 0, 0};
+    float4 q = {0, 0, 0, 0};
+    float opacity;
+    if (FUSED) {
+        // ---- skinning (A.1 of SURVEY.md): weights recomputed in registers, bones from shared memory
+        const float x = s.xyz[3 * i], y = s.xyz[3 * i + 1], z = s.xyz[3 * i + 2];
+        const int K = s.J - 1;
+        float wsum = 0.f, ax = 0.f, ay = 0.f, az = 0.f, q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
+        for (int k = 0; k < K; k++) {
+            const BoneSm& b = s_b[k];
+            const float d2 = seg_dist2(b, x, y, z);
+            float w = expf(-d2 * b.inv_2r2);
+            if (s.mlp_weight) w *= s.mlp_weight[i * K + k];
+            w += 1e-7f;
+            wsum += w;
+            ax += w * (b.G[0] * x + b.G[1] * y + b.G[2] * z + b.G[9]);
+            ay += w * (b.G[3] * x + b.G[4] * y + b.G[5] * z + b.G[10]);
+            az += w * (b.G[6] * x + b.G[7] * y + b.G[8] * z + b.G[11]);
+            q0 += w * b.q[0]; q1 += w * b.q[1]; q2 += w * b.q[2]; q3 += w * b.q[3];
+        }
+        const float inv = 1.0f / wsum;
+        const float m = s.motion_mask ? s.motion_mask[i] : 1.0f;
+        float ox = 0.f, oy = 0.f, oz = 0.f;
+        if (s.offsets) { ox = s.offsets[3 * i]; oy = s.offsets[3 * i + 1]; oz = s.offsets[3 * i + 2]; }
+        const float dx = (ax * inv + s.global_trans[0] + ox - x) * m;
+        const float dy = (ay * inv + s.global_trans[1] + oy - y) * m;
+        const float dz = (az * inv + s.global_trans[2] + oz - z) * m;
+        p_orig = {x + dx, y + dy, z + dz};
+        s.means3D_out[3 * i] = p_orig.x; s.means3D_out[3 * i + 1] = p_orig.y; s.means3D_out[3 * i + 2] = p_orig.z;
+        // ---- activations
+        float4 r = reinterpret_cast<const float4*>(s.rotation_raw)[i];
+        if (!s.zero_d_rotation) {
+            const float4 dr = {q0 * inv * m, q1 * inv * m, q2 * inv * m, q3 * inv * m};
+            reinterpret_cast<float4*>(s.d_rot_out)[i] = dr;
+            r.x += dr.x; r.y += dr.y; r.z += dr.z; r.w += dr.w;
+        }
+        const float rn = fmaxf(sqrtf(r.x * r.x + r.y * r.y + r.z * r.z + r.w * r.w), 1e-12f);  // F.normalize eps
+        q = {r.x / rn, r.y / rn, r.z / rn, r.w / rn};
+        if (s.isotropic) { const float e = expf(s.scaling_raw[i]); sc = {e, e, e}; }
+        else sc = {expf(s.scaling_raw[3 * i]), expf(s.scaling_raw[3 * i + 1]), expf(s.scaling_raw[3 * i + 2])};
+        opacity = 1.0f / (1.0f + expf(-s.opacity_raw[i]));
+        if (s.dbg_scales) {  // test aid: the activated inputs the reference rasterizer would have been given
+            s.dbg_scales[3 * i] = sc.x; s.dbg_scales[3 * i + 1] = sc.y; s.dbg_scales[3 * i + 2] = sc.z;
+            reinterpret_cast<float4*>(s.dbg_rotations)[i] = q;
+            s.dbg_opacities[i] = opacity;
+        }
+    } else {
+        p_orig = {a.means3D[3 * i], a.means3D[3 * i + 1], a.means3D[3 * i + 2]};
+        opacity = a.opacities[i];
     }
+
+    uint32_t my_tiles = 0;
+    int radius_out = 0;
+    float3 p_view = xform_point_4x3(p_orig, view);
+    do {
+        if (p_view.z <= 0.2f) {  // near cull (auxiliary.h:154)
+            if (a.prefiltered) {
+                printf("Point is filtered although prefiltered is set. This shouldn't happen!");
+                __trap();
+            }
+            break;
+        }
+        float4 p_hom = xform_point_4x4(p_orig, proj);
+        float p_w = 1.0f / (p_hom.w + 0.0000001f);
+        float3 p_proj = {p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w};
+
+        float cov3D[6];
+        if (!FUSED && a.cov3D_precomp != nullptr) {
+#pragma unroll
+            for (int k = 0; k < 6; k++) cov3D[k] = a.cov3D_precomp[6 * i + k];
+        } else {
+            if (!FUSED) {
+                sc = {a.scales[3 * i], a.scales[3 * i + 1], a.scales[3 * i + 2]};
+                q = reinterpret_cast<const float4*>(a.rotations)[i];
+            }
+            cov3d_from_scale_rot(sc, a.scale_modifier, q, cov3D);
+        }
+        Cov2D c2 = cov2d_project(p_orig, a.focal_x, a.focal_y, a.tan_fovx, a.tan_fovy, cov3D, view);
+        float3 cov = c2.cov;
+        float det = (cov.x * cov.z - cov.y * cov.y);
+        if (det == 0.0f) break;
+        float det_inv = 1.f / det;
+        float3 conic = {cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv};
+        float mid = 0.5f * (cov.x + cov.z);
+        float lambda1 = mid + sqrtf(fmaxf(0.1f, mid * mid - det));
+        float lambda2 = mid - sqrtf(fmaxf(0.1f, mid * mid - det));
+        float my_radius = ceilf(3.f * sqrtf(fmaxf(lambda1, lambda2)));
+        float2 point_image = {ndc_to_pix(p_proj.x, a.W), ndc_to_pix(p_proj.y, a.H)};
+        uint2 rect_min, rect_max;
+        tile_rect(point_image, (int)my_radius, rect_min, rect_max, a.grid_x, a.grid_y);
+        if ((rect_max.x - rect_min.x) * (rect_max.y - rect_min.y) == 0) break;
+
+        float3 color;
+        uint8_t clamp_bits = 0;
+        if (FUSED || a.colors_precomp == nullptr) {
+            float sh[48];
+            if (FUSED) load_sh_split(s.features_dc, s.features_rest, i, s.M_rest, sh);
+            else load_sh<16>(a.shs, i, a.M, a.sh_vec_ok, sh);
+            const float3 campos = {s_mat[32], s_mat[33], s_mat[34]};
+            color = sh_to_rgb(a.D, p_orig, campos, sh, clamp_bits);
+        } else {
+            color = {a.colors_precomp[3 * i], a.colors_precomp[3 * i + 1], a.colors_precomp[3 * i + 2]};
+        }
+        a.clamped[idx] = clamp_bits;
+        a.rgb[3 * i] = color.x;
+        a.rgb[3 * i + 1] = color.y;
+        a.rgb[3 * i + 2] = color.z;
+        a.depths[idx] = p_view.z;
+        radius_out = (int)my_radius;
+        a.means2D[idx] = point_image;
+        a.conic_opacity[idx] = {conic.x, conic.y, conic.z, opacity};
+        my_tiles = (rect_max.y - rect_min.y) * (rect_max.x - rect_min.x);
+    } while (false);
+    a.radii[idx] = radius_out;
+    a.tiles_touched[idx] = my_tiles;
+    if (my_tiles == 0) a.depths[idx] = __int_as_float(0x7f800000);  // culled: +inf sorts behind everything
+    a.ids[idx] = idx;
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view,
@@ -155,7 +171,16 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, co
 int launch_preprocess(const PreprocessArgs& a, cudaStream_t stream) {
     if (a.P == 0) return 0;
     LaunchScope ls("preprocess", stream);
-    preprocess_kernel<<<(a.P + 255) / 256, 256, 0, stream>>>(a);
+    SkinFuseArgs none = {};
+    preprocess_kernel<false><<<(a.P + 255) / 256, 256, 0, stream>>>(a, none);
+    return 0;
+}
+
+int launch_skin_preprocess(const PreprocessArgs& a, const SkinFuseArgs& s, cudaStream_t stream) {
+    if (a.P == 0) return 0;
+    if (s.J > kMaxJoints || s.J < 2) { set_error("skinned preprocess: J must be in [2, 128]"); return -1; }
+    LaunchScope ls("skin_preprocess", stream);
+    preprocess_kernel<true><<<(a.P + 255) / 256, 256, bone_smem_bytes(s.J, false), stream>>>(a, s);
     return 0;
 }
 

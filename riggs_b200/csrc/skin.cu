@@ -10,6 +10,7 @@
 #include "common.cuh"
 #include "kernels.cuh"
 #include "skin.cuh"
+#include "bones.cuh"
 
 namespace rg {
 
@@ -54,38 +55,52 @@ __device__ __forceinline__ void mat_to_quat_rm(const float* m, float* q) {
     for (int c = 0; c < 4; c++) q[c] = cand[c] / den;
 }
 
-// One thread per pose walks the chain G_i = G_parent(i) * T_i (parents[i] < i).  J is a few dozen, so the
-// whole pose costs ~J*60 flops; poses of a sequence (novel-pose rendering) run side by side.
-__global__ void fk_forward_kernel(int F, int J, const float* __restrict__ local_rot, const float* __restrict__ gtrans,
-                                  const float* __restrict__ joints, const int* __restrict__ parents,
-                                  float* __restrict__ G, float* __restrict__ node_rot, float* __restrict__ posed) {
-    const int f = blockIdx.x * blockDim.x + threadIdx.x;
-    if (f >= F) return;
+// One warp per pose.  Lanes build the local transforms of all joints in shared memory in parallel, lane 0 walks
+// the chain G_i = G_parent(i) * T_i (parents[i] < i) on shared memory, then the lanes derive node_rot / posed
+// joints and write everything out coalesced.  A pose costs a few microseconds instead of ~2J eager launches;
+// the poses of a sequence (novel-pose rendering) run side by side, one CTA each.
+__global__ void __launch_bounds__(32) fk_forward_kernel(int F, int J, const float* __restrict__ local_rot,
+                                                        const float* __restrict__ gtrans, const float* __restrict__ joints,
+                                                        const int* __restrict__ parents, float* __restrict__ G,
+                                                        float* __restrict__ node_rot, float* __restrict__ posed) {
+    __shared__ float s_T[kMaxJoints * 12];   // local rotation (row-major) + local translation
+    __shared__ float s_G[kMaxJoints * 12];
+    __shared__ int s_par[kMaxJoints];
+    const int f = blockIdx.x, lane = threadIdx.x;
     const float* q = local_rot + (size_t)f * J * 4;
-    float* Gf = G + (size_t)f * J * 12;
-    for (int i = 0; i < J; i++) {
+    for (int i = lane; i < J; i += 32) {
         float R[9];
         quat_to_mat_rm(q + 4 * i, R);
         const int par = parents[i];
+        s_par[i] = par;
         const int vp = i == 0 ? 0 : par;  // the root pivots on itself (skeleton_warp.py:246-247)
-        const float px = joints[3 * vp], py = joints[3 * vp + 1], pz = joints[3 * vp + 2];
-        float tl[3];  // local translation p - R p
+        const float p[3] = {joints[3 * vp], joints[3 * vp + 1], joints[3 * vp + 2]};
 #pragma unroll
-        for (int a = 0; a < 3; a++) tl[a] = (a == 0 ? px : a == 1 ? py : pz) - (R[3 * a] * px + R[3 * a + 1] * py + R[3 * a + 2] * pz);
-        float* Gi = Gf + 12 * i;
-        if (i == 0) {
+        for (int a = 0; a < 9; a++) s_T[12 * i + a] = R[a];
 #pragma unroll
-            for (int a = 0; a < 9; a++) Gi[a] = R[a];
-            Gi[9] = tl[0]; Gi[10] = tl[1]; Gi[11] = tl[2];
-        } else {
-            const float* Gp = Gf + 12 * par;
+        for (int a = 0; a < 3; a++) s_T[12 * i + 9 + a] = p[a] - (R[3 * a] * p[0] + R[3 * a + 1] * p[1] + R[3 * a + 2] * p[2]);
+    }
+    __syncwarp();
+    if (lane == 0) {
+#pragma unroll
+        for (int a = 0; a < 12; a++) s_G[a] = s_T[a];
+        for (int i = 1; i < J; i++) {
+            const float* Gp = s_G + 12 * s_par[i];
+            const float* T = s_T + 12 * i;
+            float* Gi = s_G + 12 * i;
 #pragma unroll
             for (int a = 0; a < 3; a++) {
 #pragma unroll
-                for (int b = 0; b < 3; b++) Gi[3 * a + b] = Gp[3 * a] * R[b] + Gp[3 * a + 1] * R[3 + b] + Gp[3 * a + 2] * R[6 + b];
-                Gi[9 + a] = Gp[3 * a] * tl[0] + Gp[3 * a + 1] * tl[1] + Gp[3 * a + 2] * tl[2] + Gp[9 + a];
+                for (int b = 0; b < 3; b++) Gi[3 * a + b] = Gp[3 * a] * T[b] + Gp[3 * a + 1] * T[3 + b] + Gp[3 * a + 2] * T[6 + b];
+                Gi[9 + a] = Gp[3 * a] * T[9] + Gp[3 * a + 1] * T[10] + Gp[3 * a + 2] * T[11] + Gp[9 + a];
             }
         }
+    }
+    __syncwarp();
+    float* Gf = G + (size_t)f * J * 12;
+    for (int k = lane; k < J * 12; k += 32) Gf[k] = s_G[k];
+    for (int i = lane; i < J; i += 32) {
+        const float* Gi = s_G + 12 * i;
         if (node_rot) mat_to_quat_rm(Gi, node_rot + ((size_t)f * J + i) * 4);
         if (posed) {
             const float jx = joints[3 * i], jy = joints[3 * i + 1], jz = joints[3 * i + 2];
@@ -96,22 +111,24 @@ __global__ void fk_forward_kernel(int F, int J, const float* __restrict__ local_
     }
 }
 
-// Reverse sweep.  Scratch for the per-joint gradient of the global transforms lives in dG_work (F,J,12),
-// which the kernel overwrites (it is a private copy made by the launcher's caller: here we accumulate into
-// a local copy held in global scratch passed as dG_work).
-__global__ void fk_backward_kernel(int F, int J, const float* __restrict__ local_rot, const float* __restrict__ joints,
-                                   const int* __restrict__ parents, const float* __restrict__ G,
-                                   const float* __restrict__ dG_in, const float* __restrict__ dposed,
-                                   float* __restrict__ dG_work, float* __restrict__ dlocal_rot,
-                                   float* __restrict__ dgtrans) {
-    const int f = blockIdx.x * blockDim.x + threadIdx.x;
-    if (f >= F) return;
+// Reverse sweep, same layout: lanes seed the per-joint gradients of the global transforms in shared memory,
+// lane 0 walks the chain back from the leaves, lanes finish with the quaternion gradients.
+__global__ void __launch_bounds__(32) fk_backward_kernel(int F, int J, const float* __restrict__ local_rot,
+                                                         const float* __restrict__ joints, const int* __restrict__ parents,
+                                                         const float* __restrict__ G, const float* __restrict__ dG_in,
+                                                         const float* __restrict__ dposed, float* __restrict__ dlocal_rot,
+                                                         float* __restrict__ dgtrans, const float* __restrict__ dgtrans_add) {
+    __shared__ float s_W[kMaxJoints * 12];   // running dL/dG_i; afterwards dL/dT_i (local rotation + translation)
+    __shared__ float s_G[kMaxJoints * 12];
+    __shared__ float s_R[kMaxJoints * 9];
+    __shared__ float s_p[kMaxJoints * 3];    // pivot of joint i
+    __shared__ int s_par[kMaxJoints];
+    const int f = blockIdx.x, lane = threadIdx.x;
     const float* q = local_rot + (size_t)f * J * 4;
-    const float* Gf = G + (size_t)f * J * 12;
-    float* W = dG_work + (size_t)f * J * 12;
-    float gt_sum[3] = {0, 0, 0};
-    for (int i = 0; i < J; i++) {
-        float* Wi = W + 12 * i;
+    float gt[3] = {0, 0, 0};
+    for (int k = lane; k < J * 12; k += 32) s_G[k] = G[(size_t)f * J * 12 + k];
+    for (int i = lane; i < J; i += 32) {
+        float* Wi = s_W + 12 * i;
 #pragma unroll
         for (int a = 0; a < 12; a++) Wi[a] = dG_in ? dG_in[((size_t)f * J + i) * 12 + a] : 0.f;
         if (dposed) {  // posed_i = G_R p_i + G_t + g
@@ -121,49 +138,61 @@ __global__ void fk_backward_kernel(int F, int J, const float* __restrict__ local
             for (int a = 0; a < 3; a++) {
                 Wi[3 * a] += dp[a] * jx; Wi[3 * a + 1] += dp[a] * jy; Wi[3 * a + 2] += dp[a] * jz;
                 Wi[9 + a] += dp[a];
-                gt_sum[a] += dp[a];
+                gt[a] += dp[a];
             }
         }
-    }
-    if (dgtrans) { dgtrans[3 * f] = gt_sum[0]; dgtrans[3 * f + 1] = gt_sum[1]; dgtrans[3 * f + 2] = gt_sum[2]; }
-    for (int i = J - 1; i >= 0; i--) {
-        const float* Wi = W + 12 * i;
-        float R[9];
-        quat_to_mat_rm(q + 4 * i, R);
+        quat_to_mat_rm(q + 4 * i, s_R + 9 * i);
         const int par = parents[i];
+        s_par[i] = par;
         const int vp = i == 0 ? 0 : par;
-        const float p[3] = {joints[3 * vp], joints[3 * vp + 1], joints[3 * vp + 2]};
-        float tl[3];
 #pragma unroll
-        for (int a = 0; a < 3; a++) tl[a] = p[a] - (R[3 * a] * p[0] + R[3 * a + 1] * p[1] + R[3 * a + 2] * p[2]);
-        float gRl[9], gtl[3];
-        if (i == 0) {
+        for (int a = 0; a < 3; a++) s_p[3 * i + a] = joints[3 * vp + a];
+    }
+    if (dgtrans) {
 #pragma unroll
-            for (int a = 0; a < 9; a++) gRl[a] = Wi[a];
+        for (int a = 0; a < 3; a++) {
+            const float t = warp_sum(gt[a]);
+            if (lane == 0) dgtrans[3 * f + a] = t + (dgtrans_add ? dgtrans_add[a] : 0.f);
+        }
+    }
+    __syncwarp();
+    if (lane == 0) {
+        for (int i = J - 1; i >= 1; i--) {
+            float* Wi = s_W + 12 * i;
+            const float* R = s_R + 9 * i;
+            const float* p = s_p + 3 * i;
+            const float* Gp = s_G + 12 * s_par[i];
+            float* Wp = s_W + 12 * s_par[i];
+            float tl[3], gRl[9], gtl[3];
 #pragma unroll
-            for (int a = 0; a < 3; a++) gtl[a] = Wi[9 + a];
-        } else {
-            const float* Gp = Gf + 12 * par;
-            float* Wp = W + 12 * par;
+            for (int a = 0; a < 3; a++) tl[a] = p[a] - (R[3 * a] * p[0] + R[3 * a + 1] * p[1] + R[3 * a + 2] * p[2]);
             // G_R_i = Gp_R * R ; G_t_i = Gp_R * tl + Gp_t
 #pragma unroll
             for (int a = 0; a < 3; a++) {
 #pragma unroll
                 for (int b = 0; b < 3; b++) {
-                    // d/dGp_R[a][b] = sum_c gR_i[a][c] R[b][c] + gt_i[a] tl[b]
                     Wp[3 * a + b] += Wi[3 * a] * R[3 * b] + Wi[3 * a + 1] * R[3 * b + 1] + Wi[3 * a + 2] * R[3 * b + 2] + Wi[9 + a] * tl[b];
-                    // d/dR[a][b] = sum_c Gp_R[c][a] gR_i[c][b]
                     gRl[3 * a + b] = Gp[a] * Wi[b] + Gp[3 + a] * Wi[3 + b] + Gp[6 + a] * Wi[6 + b];
                 }
                 Wp[9 + a] += Wi[9 + a];
                 gtl[a] = Gp[a] * Wi[9] + Gp[3 + a] * Wi[10] + Gp[6 + a] * Wi[11];
             }
+#pragma unroll
+            for (int a = 0; a < 9; a++) Wi[a] = gRl[a];
+#pragma unroll
+            for (int a = 0; a < 3; a++) Wi[9 + a] = gtl[a];
         }
+    }
+    __syncwarp();
+    for (int i = lane; i < J; i += 32) {
+        const float* Wi = s_W + 12 * i;   // dL/dR_i (local), dL/dtl_i
+        const float* p = s_p + 3 * i;
+        float gRl[9];
         // tl = p - R p  ->  dR[a][b] -= gtl[a] p[b]
 #pragma unroll
         for (int a = 0; a < 3; a++)
 #pragma unroll
-            for (int b = 0; b < 3; b++) gRl[3 * a + b] -= gtl[a] * p[b];
+            for (int b = 0; b < 3; b++) gRl[3 * a + b] = Wi[3 * a + b] - Wi[9 + a] * p[b];
         // R = I + s*B(q), s = 2/|q|^2, ds/dq_m = -s^2 q_m
         const float r = q[4 * i], x = q[4 * i + 1], y = q[4 * i + 2], z = q[4 * i + 3];
         const float s = 2.0f / (r * r + x * x + y * y + z * z);
@@ -172,7 +201,6 @@ __global__ void fk_backward_kernel(int F, int J, const float* __restrict__ local
         float gB = 0.f;
 #pragma unroll
         for (int a = 0; a < 9; a++) gB += gRl[a] * B[a];
-        // dB/dr, dB/dx, dB/dy, dB/dz contracted with gRl
         const float dBr = -z * gRl[1] + y * gRl[2] + z * gRl[3] - x * gRl[5] - y * gRl[6] + x * gRl[7];
         const float dBx = y * gRl[1] + z * gRl[2] + y * gRl[3] - 2 * x * gRl[4] - r * gRl[5] + z * gRl[6] + r * gRl[7] - 2 * x * gRl[8];
         const float dBy = -2 * y * gRl[0] + x * gRl[1] + r * gRl[2] + x * gRl[3] + z * gRl[5] - r * gRl[6] + z * gRl[7] - 2 * y * gRl[8];
@@ -188,48 +216,6 @@ __global__ void fk_backward_kernel(int F, int J, const float* __restrict__ local
 
 // ---- skinning -------------------------------------------------------------------------------------------
 
-constexpr int kMaxJoints = 128;
-
-struct BoneSm {            // per bone k (child joint k = 1..J-1), staged once per CTA
-    float a[3];            // segment start = rest joint of the parent
-    float ab[3];           // segment vector
-    float inv_len2;        // 1 / max(|ab|^2, 1e-6)
-    float inv_2r2;         // 1 / (2 r_k^2), r_k = exp(node_radius_raw[k])
-    float G[12];           // global transform of joint k
-    float q[4];            // node_rot of joint k
-};
-
-__device__ __forceinline__ void stage_bones(int J, const float* joints, const int* parents, const float* radius_raw,
-                                            const float* G, const float* node_rot, BoneSm* s_b) {
-    for (int k = threadIdx.x + 1; k < J; k += blockDim.x) {
-        BoneSm b;
-        const int p = parents[k];
-        float l2 = 0.f;
-#pragma unroll
-        for (int c = 0; c < 3; c++) {
-            b.a[c] = joints[3 * p + c];
-            b.ab[c] = joints[3 * k + c] - b.a[c];
-            l2 += b.ab[c] * b.ab[c];
-        }
-        b.inv_len2 = 1.0f / fmaxf(l2, 1e-6f);
-        const float r = expf(radius_raw[k]);
-        b.inv_2r2 = 1.0f / (2 * r * r);
-#pragma unroll
-        for (int c = 0; c < 12; c++) b.G[c] = G[12 * k + c];
-#pragma unroll
-        for (int c = 0; c < 4; c++) b.q[c] = node_rot ? node_rot[4 * k + c] : 0.f;
-        s_b[k - 1] = b;
-    }
-}
-
-// squared distance of x to the bone segment (skeleton_warp.py:215-238)
-__device__ __forceinline__ float seg_dist2(const BoneSm& b, float x, float y, float z) {
-    const float px = x - b.a[0], py = y - b.a[1], pz = z - b.a[2];
-    float t = (px * b.ab[0] + py * b.ab[1] + pz * b.ab[2]) * b.inv_len2;
-    t = fminf(fmaxf(t, 0.0f), 1.0f);
-    const float sx = t * b.ab[0] - px, sy = t * b.ab[1] - py, sz = t * b.ab[2] - pz;
-    return sx * sx + sy * sy + sz * sz;
-}
 
 __global__ void __launch_bounds__(256) skin_forward_kernel(SkinArgs a) {
     extern __shared__ __align__(16) unsigned char s_raw[];
@@ -405,27 +391,23 @@ __global__ void __launch_bounds__(256) skin_backward_kernel(SkinBwdArgs a) {
     if (threadIdx.x < 3 && a.dglobal_trans) atomicAdd(&a.dglobal_trans[threadIdx.x], s_acc[K * 13 + threadIdx.x]);
 }
 
-static size_t skin_smem(int J, bool bwd) {
-    size_t b = sizeof(BoneSm) * (size_t)(J > 1 ? J - 1 : 1);
-    if (bwd) b += sizeof(float) * ((size_t)(J - 1) * 13 + 3);
-    return b;
-}
-
 int launch_fk_forward(int F, int J, const float* local_rot, const float* gtrans, const float* joints,
                       const int* parents, float* G, float* node_rot, float* posed, cudaStream_t stream) {
     if (F == 0 || J == 0) return 0;
+    if (J > kMaxJoints) { set_error("forward kinematics: at most 128 joints"); return -1; }
     LaunchScope ls("fk_forward", stream);
-    fk_forward_kernel<<<(F + 63) / 64, 64, 0, stream>>>(F, J, local_rot, gtrans, joints, parents, G, node_rot, posed);
+    fk_forward_kernel<<<F, 32, 0, stream>>>(F, J, local_rot, gtrans, joints, parents, G, node_rot, posed);
     return 0;
 }
 
 int launch_fk_backward(int F, int J, const float* local_rot, const float* joints, const int* parents, const float* G,
-                       const float* dG, const float* dposed, float* dG_work, float* dlocal_rot, float* dgtrans,
+                       const float* dG, const float* dposed, float* dlocal_rot, float* dgtrans, const float* dgtrans_add,
                        cudaStream_t stream) {
     if (F == 0 || J == 0) return 0;
+    if (J > kMaxJoints) { set_error("forward kinematics: at most 128 joints"); return -1; }
     LaunchScope ls("fk_backward", stream);
-    fk_backward_kernel<<<(F + 63) / 64, 64, 0, stream>>>(F, J, local_rot, joints, parents, G, dG, dposed, dG_work,
-                                                         dlocal_rot, dgtrans);
+    fk_backward_kernel<<<F, 32, 0, stream>>>(F, J, local_rot, joints, parents, G, dG, dposed, dlocal_rot, dgtrans,
+                                            dgtrans_add);
     return 0;
 }
 
@@ -435,7 +417,7 @@ int launch_skin_forward(const SkinArgs& a, cudaStream_t stream) {
     int blocks = (a.N + 255) / 256;
     if (blocks > RG_NUM_SMS * 8) blocks = RG_NUM_SMS * 8;
     LaunchScope ls("skin_forward", stream);
-    skin_forward_kernel<<<blocks, 256, skin_smem(a.J, false), stream>>>(a);
+    skin_forward_kernel<<<blocks, 256, bone_smem_bytes(a.J, false), stream>>>(a);
     return 0;
 }
 
@@ -445,7 +427,7 @@ int launch_skin_backward(const SkinBwdArgs& a, cudaStream_t stream) {
     int blocks = (a.N + 255) / 256;
     if (blocks > RG_NUM_SMS * 4) blocks = RG_NUM_SMS * 4;
     LaunchScope ls("skin_backward", stream);
-    skin_backward_kernel<<<blocks, 256, skin_smem(a.J, true), stream>>>(a);
+    skin_backward_kernel<<<blocks, 256, bone_smem_bytes(a.J, true), stream>>>(a);
     return 0;
 }
 

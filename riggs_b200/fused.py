@@ -1,0 +1,238 @@
+"""Fused hot path: pose -> forward kinematics -> skinning -> activations -> rasterize, forward and backward,
+as ONE C-ABI call per direction (rg_skinned_forward / rg_skinned_backward) with no host round trip.
+
+``render_skinned`` is the opt-in companion of ``gaussian_renderer.render()`` (same output dict): instead of taking
+``d_xyz / d_rotation / d_scaling`` that a separate ``SkeletonWarp.deform_by_pose`` call produced as N-sized
+tensors, it takes the skeleton module and the pose and lets the kernels skin the Gaussians in registers.
+The reference has no such function; what it replaces is the call sequence of train_rig.py:386-414 + :488
+(``deform_gaussians`` then ``render``).
+
+Workspaces (the reference's geomBuffer / binningBuffer / imgBuffer) are persistent and reused across frames.
+The instance list is bounded by the binning buffer's capacity; ``num_rendered`` never travels to the host on the
+critical path.  It is read back asynchronously and checked one call late; the first frame of a new
+(P, width, height) is checked synchronously to size the buffer.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Dict, Optional
+
+import torch
+
+from . import _lib
+from ._lib import check, f32c, ptr, stream_ptr
+
+
+class _Workspace:
+    def __init__(self, P, W, H, device, binning_bytes):
+        L = _lib.lib()
+        self.key = (P, W, H)
+        self.geom = torch.empty(int(L.rg_geom_bytes(P, W, H)), dtype=torch.uint8, device=device)
+        self.image = torch.empty(int(L.rg_image_bytes(W, H)), dtype=torch.uint8, device=device)
+        self.binning = torch.empty(int(binning_bytes), dtype=torch.uint8, device=device)
+        self.status = torch.zeros(2, dtype=torch.int32).pin_memory()
+        self.status_event: Optional[torch.cuda.Event] = None
+        self.c = _lib.RgWorkspace(self.geom.data_ptr(), self.geom.numel(), self.image.data_ptr(), self.image.numel(),
+                                  self.binning.data_ptr(), self.binning.numel())
+
+    def grow_binning(self, nbytes):
+        self.binning = torch.empty(int(nbytes), dtype=torch.uint8, device=self.geom.device)
+        self.c.binning = self.binning.data_ptr()
+        self.c.binning_bytes = self.binning.numel()
+
+
+class WorkspacePool:
+    """Free list of workspaces per (P, W, H); one is held from a forward until its backward (or its release)."""
+
+    def __init__(self, headroom: float = 1.5, initial_bytes: Optional[int] = None):
+        self.free: Dict[tuple, list] = {}
+        self.capacity_bytes: Dict[tuple, int] = {}
+        self.headroom = headroom
+        self.initial_bytes = initial_bytes  # binning bytes of a first-ever workspace (default: 8 tiles per Gaussian)
+
+    def acquire(self, P, W, H, device):
+        key = (P, W, H, str(device))
+        lst = self.free.setdefault(key, [])
+        if lst:
+            return lst.pop(), False
+        nbytes = self.capacity_bytes.get(key, 0)
+        fresh = nbytes == 0
+        if fresh:
+            nbytes = self.initial_bytes or (max(4 * 8 * P, 1 << 20) + 1024)
+        return _Workspace(P, W, H, device, nbytes), fresh
+
+    def release(self, ws, device):
+        P, W, H = ws.key
+        self.free.setdefault((P, W, H, str(device)), []).append(ws)
+
+    def note_capacity(self, ws, device):
+        P, W, H = ws.key
+        key = (P, W, H, str(device))
+        self.capacity_bytes[key] = max(self.capacity_bytes.get(key, 0), ws.binning.numel())
+
+
+_POOL = WorkspacePool()
+
+
+class _Lease:
+    """Returns the workspace to its pool after the backward -- or when autograd drops the graph without one."""
+
+    def __init__(self, pool, ws, dev):
+        self.pool, self.ws, self.dev = pool, ws, dev
+
+    def release(self):
+        if self.ws is not None:
+            self.pool.release(self.ws, self.dev)
+            self.ws = None
+
+    def __del__(self):
+        self.release()
+
+
+def _scene_struct(P, J, sh_degree, M_rest, isotropic, zero_d_rot, W, H, tfx, tfy, scale_mod, t):
+    s = _lib.RgSkinnedScene()
+    s.P, s.J, s.sh_degree, s.M_rest = P, J, sh_degree, M_rest
+    s.isotropic, s.zero_d_rotation, s.width, s.height = int(isotropic), int(zero_d_rot), W, H
+    s.tan_fovx, s.tan_fovy, s.scale_modifier = tfx, tfy, scale_mod
+    for name, ten in t.items():
+        setattr(s, name, ptr(ten))
+    return s
+
+
+class _SkinnedRender(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, xyz, scaling_raw, rotation_raw, opacity_raw, features_dc, features_rest, node_radius_raw,
+                local_rot, global_trans, motion_mask, mlp_weight, offsets, screenspace_points, cfg):
+        if not xyz.is_cuda:
+            raise _lib.RiggsError("render_skinned needs CUDA tensors; riggs_b200 has no CPU path")
+        dev = xyz.device
+        P, J = xyz.shape[0], cfg["joints"].shape[0]
+        W, H = cfg["width"], cfg["height"]
+        t = dict(xyz=f32c(xyz), scaling_raw=f32c(scaling_raw), rotation_raw=f32c(rotation_raw),
+                 opacity_raw=f32c(opacity_raw), features_dc=f32c(features_dc), features_rest=f32c(features_rest),
+                 motion_mask=f32c(motion_mask), mlp_weight=f32c(mlp_weight), offsets=f32c(offsets),
+                 joints=cfg["joints"], parents=cfg["parents_i32"], node_radius_raw=f32c(node_radius_raw),
+                 local_rot=f32c(local_rot), global_trans=f32c(global_trans), viewmatrix=cfg["viewmatrix"],
+                 projmatrix=cfg["projmatrix"], campos=cfg["campos"], background=cfg["bg"])
+        isotropic = scaling_raw.shape[-1] == 1
+        M_rest = features_rest.shape[1]
+        scene = _scene_struct(P, J, cfg["sh_degree"], M_rest, isotropic, cfg["zero_d_rotation"], W, H, cfg["tanfovx"],
+                              cfg["tanfovy"], cfg["scale_modifier"], t)
+        color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+        depth = torch.empty((1, H, W), dtype=torch.float32, device=dev)
+        alpha = torch.empty((1, H, W), dtype=torch.float32, device=dev)
+        radii = torch.empty((P,), dtype=torch.int32, device=dev)
+        d_nodes = torch.empty((J, 3), dtype=torch.float32, device=dev)
+        dbg = cfg.get("debug_outputs")
+        L = _lib.lib()
+        pool = cfg.get("pool") or _POOL
+        ws, fresh = pool.acquire(P, W, H, dev)
+        with torch.cuda.device(dev):
+            # late check of the previous frame that used this workspace
+            if ws.status_event is not None and ws.status_event.query() and int(ws.status[1]) != 0:
+                import warnings
+                warnings.warn("riggs_b200: the previous frame overflowed the instance buffer and was rendered "
+                              "incompletely; growing the buffer")
+                ws.status_event = None
+                fresh = True  # fall through to the synchronous sizing path
+            while True:
+                check(L.rg_skinned_forward(C.byref(scene), C.byref(ws.c), ptr(color), ptr(depth), ptr(alpha), ptr(radii),
+                                           ptr(d_nodes), ptr(dbg["scales"]) if dbg else None,
+                                           ptr(dbg["rotations"]) if dbg else None,
+                                           ptr(dbg["opacities"]) if dbg else None, stream_ptr()), "rg_skinned_forward")
+                check(L.rg_skinned_status(C.byref(scene), C.byref(ws.c), ws.status.data_ptr(), stream_ptr()),
+                      "rg_skinned_status")
+                if not fresh:
+                    ws.status_event = torch.cuda.Event()
+                    ws.status_event.record()
+                    break
+                torch.cuda.current_stream().synchronize()  # first frame of this shape only
+                R, overflow = int(ws.status[0]), int(ws.status[1])
+                want = int(4 * R * pool.headroom) + 1024
+                if overflow or ws.binning.numel() < want:
+                    # too small (or no headroom for the coming frames): grow and render this first frame again,
+                    # so the instance list the backward will read lives in the buffer the workspace keeps
+                    ws.grow_binning(want)
+                    pool.note_capacity(ws, dev)
+                    continue
+                pool.note_capacity(ws, dev)
+                break
+        ctx.scene_tensors = t  # keeps the contiguous copies alive
+        ctx.scene = scene
+        ctx.ws = ws
+        ctx.lease = _Lease(pool, ws, dev)
+        ctx.dev = dev
+        if not any(ctx.needs_input_grad):
+            ctx.lease.release()  # inference: the state is not needed any more
+        ctx.shapes = (P, J, W, H, M_rest, isotropic)
+        ctx.save_for_backward(radii, alpha)
+        ctx.mark_non_differentiable(radii)
+        ctx.num_rendered_host = ws.status  # valid after the next synchronisation
+        return color, depth, alpha, radii, d_nodes
+
+    @staticmethod
+    def backward(ctx, g_color, g_depth, g_alpha, _g_radii, g_nodes):
+        radii, alpha = ctx.saved_tensors
+        P, J, W, H, M_rest, isotropic = ctx.shapes
+        dev = ctx.dev
+        t = ctx.scene_tensors
+        opts = dict(dtype=torch.float32, device=dev)
+        z = lambda *s: torch.zeros(s, **opts)
+        g_color = f32c(g_color) if g_color is not None else z(3, H, W)
+        g_depth = f32c(g_depth) if g_depth is not None else z(1, H, W)
+        g_alpha = f32c(g_alpha) if g_alpha is not None else z(1, H, W)
+        g_nodes = f32c(g_nodes) if g_nodes is not None else None
+        d_xyz = torch.empty((P, 3), **opts)
+        d_scaling = torch.empty((P, 1 if isotropic else 3), **opts)
+        d_rotation = torch.empty((P, 4), **opts)
+        d_opacity = torch.empty((P, 1), **opts)
+        d_fdc = torch.empty((P, 1, 3), **opts)
+        d_frest = torch.empty((P, M_rest, 3), **opts)
+        d_mean2D = torch.empty((P, 3), **opts)
+        d_local_rot = torch.empty((J, 4), **opts)
+        d_trans = torch.empty((3,), **opts)
+        d_radius = torch.empty((J,), **opts)
+        need = ctx.needs_input_grad
+        d_mask = torch.empty((P,), **opts) if (t["motion_mask"] is not None and need[9]) else None
+        d_mlp = torch.empty((P, J - 1), **opts) if (t["mlp_weight"] is not None and need[10]) else None
+        d_off = torch.empty((P, 3), **opts) if (t["offsets"] is not None and need[11]) else None
+        with torch.cuda.device(dev):
+            check(_lib.lib().rg_skinned_backward(
+                C.byref(ctx.scene), C.byref(ctx.ws.c), ptr(radii), ptr(alpha), ptr(g_color), ptr(g_depth), ptr(g_alpha),
+                ptr(g_nodes), ptr(d_xyz), ptr(d_scaling), ptr(d_rotation), ptr(d_opacity), ptr(d_fdc), ptr(d_frest),
+                ptr(d_mean2D), ptr(d_local_rot), ptr(d_trans), ptr(d_radius), ptr(d_mask), ptr(d_mlp), ptr(d_off),
+                stream_ptr()), "rg_skinned_backward")
+        ctx.lease.release()
+        ctx.ws = None
+        if d_mask is not None:
+            d_mask = d_mask.view_as(t["motion_mask"])
+        return (d_xyz, d_scaling, d_rotation, d_opacity, d_fdc, d_frest, d_radius, d_local_rot, d_trans, d_mask, d_mlp,
+                d_off, d_mean2D, None)
+
+
+def render_skinned(viewpoint_camera, pc, skeleton, pose: Dict[str, torch.Tensor], pipe, bg_color: torch.Tensor,
+                   scaling_modifier=1.0, mlp_weight=None, offsets=None, zero_d_rotation: Optional[bool] = None,
+                   debug_outputs=None, pool: Optional[WorkspacePool] = None):
+    """Fused deform + render.  ``pc``: object with the GaussianModel raw tensors (_xyz, _scaling, _rotation, _opacity,
+    _features_dc, _features_rest, motion_mask, active_sh_degree); ``skeleton``: riggs_b200 SkeletonWarp (joints,
+    parents, _node_radius); ``pose``: {'local_rotation': (J,4), 'global_trans': (3,)}.
+    Returns the dict of ``render()`` plus ``d_nodes``."""
+    xyz = pc._xyz
+    screenspace_points = torch.zeros_like(xyz, requires_grad=True)
+    isotropic = pc._scaling.shape[-1] == 1
+    cfg = dict(joints=f32c(skeleton.nodes[:, :3].detach()), parents_i32=skeleton.parents_i32,
+               width=int(viewpoint_camera.image_width), height=int(viewpoint_camera.image_height),
+               tanfovx=math.tan(viewpoint_camera.FoVx * 0.5), tanfovy=math.tan(viewpoint_camera.FoVy * 0.5),
+               scale_modifier=float(scaling_modifier), sh_degree=int(pc.active_sh_degree),
+               viewmatrix=f32c(viewpoint_camera.world_view_transform), projmatrix=f32c(viewpoint_camera.full_proj_transform),
+               campos=f32c(viewpoint_camera.camera_center), bg=f32c(bg_color),
+               zero_d_rotation=isotropic if zero_d_rotation is None else zero_d_rotation, debug_outputs=debug_outputs,
+               pool=pool)
+    mm = getattr(pc, "_motion_mask", None)
+    mask = mm.reshape(-1) if mm is not None else None
+    color, depth, alpha, radii, d_nodes = _SkinnedRender.apply(
+        xyz, pc._scaling, pc._rotation, pc._opacity, pc._features_dc, pc._features_rest, skeleton._node_radius,
+        pose["local_rotation"], pose["global_trans"], mask, mlp_weight, offsets, screenspace_points, cfg)
+    return {"render": color, "viewspace_points": screenspace_points, "visibility_filter": radii > 0, "radii": radii,
+            "depth": depth, "alpha": alpha, "bg_color": bg_color, "d_nodes": d_nodes}

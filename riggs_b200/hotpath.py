@@ -19,7 +19,11 @@ class _Pipe:
 
 
 class HotPath:
-    def __init__(self, scene, device="cuda", use_mlp_weight: bool = False, use_offsets: bool = False):
+    def __init__(self, scene, device="cuda", use_mlp_weight: bool = False, use_offsets: bool = False,
+                 fused: bool = True):
+        """fused=True: one C-ABI call per direction (rg_skinned_forward/backward, no host sync);
+        fused=False: the reference's call sequence (deform_by_pose, then render()) on the same kernels."""
+        self.fused = fused
         self.device = torch.device(device)
         self.pc = GaussianParams.from_scene(scene, device=device)
         self.warp = sw.SkeletonWarp(scene.joints, scene.parents, scene.node_radius_raw,
@@ -41,6 +45,10 @@ class HotPath:
 
     def forward(self, cam, pose: Dict[str, torch.Tensor]):
         """pose: {'local_rotation': (J,4), 'global_trans': (3,)} on the device (may require grad)."""
+        if self.fused:
+            from .fused import render_skinned
+            return render_skinned(cam, self.pc, self.warp, pose, self.pipe, self.bg, mlp_weight=self.mlp_weight,
+                                  offsets=self.offsets)
         joints = self.warp.nodes[:, :3]
         G, node_rot, d_nodes = sw.fk(pose["local_rotation"], pose["global_trans"], joints, self.warp.parents_i32)
         mask = self.pc._motion_mask.reshape(-1) if self.pc._motion_mask is not None else None

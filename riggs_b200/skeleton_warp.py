@@ -52,12 +52,11 @@ class _FKFunction(torch.autograd.Function):
         dev = local_rot.device
         dG = f32c(dG) if dG is not None else None
         dposed = f32c(dposed) if dposed is not None else None
-        scratch = torch.empty((Fn, J, 12), dtype=torch.float32, device=dev)
         dq = torch.empty((Fn, J, 4), dtype=torch.float32, device=dev)
         dtr = torch.zeros((Fn, 3), dtype=torch.float32, device=dev)
         with torch.cuda.device(dev):
             check(_lib.lib().rg_fk_backward(Fn, J, ptr(local_rot), ptr(joints), ptr(parents_i32), ptr(G), ptr(dG),
-                                            ptr(dposed), ptr(scratch), ptr(dq), ptr(dtr), stream_ptr()), "fk_backward")
+                                            ptr(dposed), ptr(dq), ptr(dtr), stream_ptr()), "fk_backward")
         return dq, dtr, None, None
 
 
