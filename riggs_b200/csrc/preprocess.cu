@@ -64,10 +64,12 @@ __global__ void __launch_bounds__(256) preprocess_kernel(PreprocessArgs a, SkinF
         const float m = s.motion_mask ? s.motion_mask[i] : 1.0f;
         float ox = 0.f, oy = 0.f, oz = 0.f;
         if (s.offsets) { ox = s.offsets[3 * i]; oy = s.offsets[3 * i + 1]; oz = s.offsets[3 * i + 2]; }
-        const float dx = (ax * inv + s.global_trans[0] + ox - x) * m;
-        const float dy = (ay * inv + s.global_trans[1] + oy - y) * m;
-        const float dz = (az * inv + s.global_trans[2] + oz - z) * m;
-        p_orig = {x + dx, y + dy, z + dz};
+        // d_xyz is rounded before it is added to x (no FMA across the two): the unfused path stores d_xyz as a
+        // tensor and adds it in a separate op (gaussian_renderer/__init__.py:74), and the positions must be the same
+        const float dx = __fmul_rn(ax * inv + s.global_trans[0] + ox - x, m);
+        const float dy = __fmul_rn(ay * inv + s.global_trans[1] + oy - y, m);
+        const float dz = __fmul_rn(az * inv + s.global_trans[2] + oz - z, m);
+        p_orig = {__fadd_rn(x, dx), __fadd_rn(y, dy), __fadd_rn(z, dz)};
         s.means3D_out[3 * i] = p_orig.x; s.means3D_out[3 * i + 1] = p_orig.y; s.means3D_out[3 * i + 2] = p_orig.z;
         // ---- activations
         float4 r = reinterpret_cast<const float4*>(s.rotation_raw)[i];
