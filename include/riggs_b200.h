@@ -105,6 +105,21 @@ size_t rg_knn_scratch_bytes(int P);
 int rg_dist_cuda2(int P, const float* points, float* mean_dists, char* scratch, size_t scratch_bytes,
                   rg_stream_t stream);
 
+/* No counterpart in the reference.  Same result as rg_dist_cuda2, for callers that have no way to provide the
+ * scratch buffer: a viewer / inference plug-in living inside a fixed device-memory budget that must not touch the
+ * CUDA allocator once it is running (cudaMalloc stalls the whole device and may fail late), or a plain C host that
+ * carries no allocator of its own.  The scratch is a 2 MiB array built into the library, so
+ *   - every GPU that loads the library holds those 2 MiB until the process ends;
+ *   - P is limited to 65536 points per call; a larger P is refused with an error (rg_last_error);
+ *   - the function itself calls no cudaMalloc / cudaFree and no allocating library routine; points and mean_dists
+ *     are still the caller's buffers;
+ *   - all calls on one GPU share the array: calls whose kernels can overlap on the GPU (different streams, or
+ *     different host threads) race on it and must be serialised by the caller.  Nothing in it needs clearing
+ *     between calls;
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress) before launching;
+ *     make that first call outside any stream capture. */
+int rg_dist_cuda2_static(int P, const float* points, float* mean_dists, rg_stream_t stream);
+
 /* ---- skeleton skinning -------------------------------------------------------------------------- */
 
 /* Per-frame bone table produced by forward kinematics and consumed by the skinning kernels:

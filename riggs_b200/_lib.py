@@ -51,6 +51,7 @@ _SIGNATURES = {
     "rg_debug_sorted_keys": (C.c_int, [_i, C.c_int64, _i, _i, _p, _p, _p, _p, _p]),
     "rg_knn_scratch_bytes": (C.c_size_t, [_i]),
     "rg_dist_cuda2": (C.c_int, [_i, _p, _p, _p, C.c_size_t, _p]),
+    "rg_dist_cuda2_static": (C.c_int, [_i, _p, _p, _p]),
     "rg_fk_forward": (C.c_int, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
     "rg_fk_backward": (C.c_int, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "rg_binning_capacity": (C.c_uint32, [C.c_size_t]),

@@ -191,3 +191,71 @@ int launch_dist2_knn3(int P, const float* points, float* out, char* scratch, siz
 }
 
 }  // namespace rg
+
+// ---- rg_dist_cuda2_static: distCUDA2 for callers that cannot allocate device memory --------------------------
+//
+// Some hosts of this library have nowhere to get scratch memory from at the moment they need the 3-NN distances:
+// a viewer or inference plug-in that is handed a fixed device-memory budget at start-up and must not call the CUDA
+// allocator afterwards (cudaMalloc synchronises the whole device and can fail late, in the middle of a session), or a
+// plain C / C++ host that links neither torch nor any other caching allocator and therefore has no cheap way to
+// produce the rg_knn_scratch_bytes(P) bytes that rg_dist_cuda2 asks for.  For them the scratch lives in the array
+// below, inside the library image.  The price is stated up front: every GPU that loads the library holds
+// kStaticKnnBytes (2 MiB) until the process exits, and one call handles at most kStaticKnnMaxPoints points.
+#include <mutex>
+
+#include "../../include/riggs_b200.h"
+
+namespace {
+
+constexpr int kStaticKnnMaxPoints = 65536;
+constexpr size_t kStaticKnnBytes = 2097152;  // 2 MiB >= knn_scratch_bytes(65536) = 1,593,856 B on a B200 (the sort's share depends on the device)
+static __device__ __align__(256) unsigned char g_knn_static_scratch[kStaticKnnBytes];
+
+// In host code `g_knn_static_scratch` is only a handle for the symbol, not an address a kernel can use; the device
+// address has to be asked for, per device, with that device current.
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+char* g_static_ptr[kMaxDevices] = {nullptr};
+
+int static_scratch_for_current_device(char** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+        rg::set_error(std::string("rg_dist_cuda2_static: cudaGetDevice failed: ") + cudaGetErrorString(e));
+        return -1;
+    }
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_ptr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_knn_static_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            rg::set_error(std::string("rg_dist_cuda2_static: cudaGetSymbolAddress failed: ") + cudaGetErrorString(e));
+            return -1;
+        }
+        g_static_ptr[dev] = static_cast<char*>(p);
+    }
+    *out = g_static_ptr[dev];
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int rg_dist_cuda2_static(int P, const float* points, float* mean_dists, rg_stream_t stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (P <= 0) return 0;
+    if (P > kStaticKnnMaxPoints) {
+        rg::set_error("rg_dist_cuda2_static: at most 65536 points per call (built-in scratch is 2 MiB); "
+                      "use rg_dist_cuda2 with caller-provided scratch for larger clouds");
+        return -1;
+    }
+    if (rg::knn_scratch_bytes(P) > kStaticKnnBytes) {
+        rg::set_error("rg_dist_cuda2_static: built-in scratch too small for this point count");
+        return -1;
+    }
+    char* scratch = nullptr;
+    if (static_scratch_for_current_device(&scratch)) return -1;  // first call on a device looks the address up
+    // Nothing in the scratch has to start at zero: the bounding-box partials, Morton codes, index arrays and box AABBs
+    // are each fully written by one kernel before the next one reads them, and the radix sort clears its own counters.
+    if (rg::launch_dist2_knn3(P, points, mean_dists, scratch, kStaticKnnBytes, stream)) return -1;
+    return rg::check_launch("dist_cuda2_static", stream, false);
+}
