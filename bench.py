@@ -141,17 +141,13 @@ def run_ours(args):
     pose = {k: v.to(dev).requires_grad_(True) for k, v in pose_host.items()}
     params = hp.parameters()
     n_grad = sum(p.numel() for p in params)
-    flat = torch.zeros(n_grad, device=dev)
+    if world > 1:
+        # data parallel over views: the backward kernels write into one flat fp32 buffer, all-reduced in place by NCCL
+        hp.enable_flat_grads()
 
     def reduce_grads():
-        if world == 1:
-            return
-        off = 0
-        for p in params:
-            n = p.numel()
-            flat[off:off + n].copy_(p.grad.reshape(-1))
-            off += n
-        dist.all_reduce(flat)
+        if world > 1:
+            hp.reduce_grads()
 
     def one_step(tgt, ps):
         hp.zero_grad()

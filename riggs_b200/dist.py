@@ -1,0 +1,78 @@
+"""Multi-GPU plumbing of the hot path: one process per GPU (torchrun), torch.distributed for the collective.
+
+The path shards by view / frame: a view's skin + render forward/backward touches no other
+view's data.  Training steps are data-parallel over views -- every rank holds a full replica of the Gaussian and
+skeleton parameters, renders its views, and the parameter gradients are summed by ONE all-reduce over a flat fp32
+buffer that the backward kernels write into directly (no packing copy).  Novel-pose sequences are sharded by
+contiguous frame ranges with no collective at all.  The reference has no distributed code; this module is new.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+
+def shard_views(n_views: int, rank: int, world: int) -> List[int]:
+    """Views of a training batch handled by `rank`: r, r + world, r + 2*world, ..."""
+    return list(range(rank, n_views, world))
+
+
+def shard_frames(n_frames: int, rank: int, world: int) -> Tuple[int, int]:
+    """Contiguous [begin, end) frame range of `rank` for forward-only sequences; sizes differ by at most one."""
+    base, extra = divmod(n_frames, world)
+    begin = rank * base + min(rank, extra)
+    return begin, begin + base + (1 if rank < extra else 0)
+
+
+class FlatGrads:
+    """One flat fp32 gradient buffer with a named view per parameter.
+
+    Layout = the parameters in the order given (for the Gaussians: xyz 3 | f_dc 3 | f_rest 45 | opacity 1 | scaling 3 |
+    rotation 4 per Gaussian-major tensor, then the skeleton parameters).  The fused backward writes its outputs straight
+    into the views (``render_skinned(..., grad_out=flat.views)``), ``all_reduce`` sums the buffer over the ranks in
+    place, ``attach`` makes every ``param.grad`` a view of the reduced buffer."""
+
+    def __init__(self, named_params: Sequence[Tuple[str, torch.Tensor]], device=None):
+        self.names = [n for n, _ in named_params]
+        self.params = [p for _, p in named_params]
+        device = device if device is not None else self.params[0].device
+        total = sum(p.numel() for p in self.params)
+        self.flat = torch.zeros(total, dtype=torch.float32, device=device)
+        self.views: Dict[str, torch.Tensor] = {}
+        off = 0
+        for n, p in named_params:
+            k = p.numel()
+            self.views[n] = self.flat[off:off + k].view(p.shape)
+            off += k
+
+    def zero_(self):
+        self.flat.zero_()
+
+    def pack_from_grads(self):
+        """Fallback for paths whose backward does not write into the views: copy param.grad into the buffer."""
+        for n, p in zip(self.names, self.params):
+            if p.grad is None:
+                self.views[n].zero_()
+            elif p.grad.data_ptr() != self.views[n].data_ptr():
+                self.views[n].copy_(p.grad)
+
+    def all_reduce(self, average: bool = False, async_op: bool = False):
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+            return None
+        work = dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, async_op=async_op)
+        if average and not async_op:
+            self.flat.div_(dist.get_world_size())
+        return work
+
+    def attach(self):
+        for n, p in zip(self.names, self.params):
+            p.grad = self.views[n]
+
+
+def all_reduce_max_(t: torch.Tensor) -> torch.Tensor:
+    """Rank-wise maximum (e.g. max_radii2D of the densification statistics, scene/gaussian_model.py:516-518)."""
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return t

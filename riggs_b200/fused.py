@@ -163,6 +163,7 @@ class _SkinnedRender(torch.autograd.Function):
         ctx.ws = ws
         ctx.lease = _Lease(pool, ws, dev)
         ctx.dev = dev
+        ctx.grad_out = cfg.get("grad_out")
         if not any(ctx.needs_input_grad):
             ctx.lease.release()  # inference: the state is not needed any more
         ctx.shapes = (P, J, W, H, M_rest, isotropic)
@@ -183,16 +184,27 @@ class _SkinnedRender(torch.autograd.Function):
         g_depth = f32c(g_depth) if g_depth is not None else z(1, H, W)
         g_alpha = f32c(g_alpha) if g_alpha is not None else z(1, H, W)
         g_nodes = f32c(g_nodes) if g_nodes is not None else None
-        d_xyz = torch.empty((P, 3), **opts)
-        d_scaling = torch.empty((P, 1 if isotropic else 3), **opts)
-        d_rotation = torch.empty((P, 4), **opts)
-        d_opacity = torch.empty((P, 1), **opts)
-        d_fdc = torch.empty((P, 1, 3), **opts)
-        d_frest = torch.empty((P, M_rest, 3), **opts)
+        go = ctx.grad_out or {}
+
+        def out(name, shape):
+            """Gradient buffer: the caller's (e.g. a view of the flat all-reduce buffer) or a fresh one."""
+            b = go.get(name)
+            if b is not None:
+                if tuple(b.shape) != tuple(shape) or b.dtype != torch.float32 or not b.is_contiguous() or b.device != dev:
+                    raise _lib.RiggsError(f"grad_out[{name!r}] must be a contiguous fp32 tensor of shape {tuple(shape)}")
+                return b
+            return torch.empty(shape, **opts)
+
+        d_xyz = out("xyz", (P, 3))
+        d_scaling = out("scaling", (P, 1 if isotropic else 3))
+        d_rotation = out("rotation", (P, 4))
+        d_opacity = out("opacity", (P, 1))
+        d_fdc = out("features_dc", (P, 1, 3))
+        d_frest = out("features_rest", (P, M_rest, 3))
         d_mean2D = torch.empty((P, 3), **opts)
         d_local_rot = torch.empty((J, 4), **opts)
         d_trans = torch.empty((3,), **opts)
-        d_radius = torch.empty((J,), **opts)
+        d_radius = out("node_radius", (J,))
         need = ctx.needs_input_grad
         d_mask = torch.empty((P,), **opts) if (t["motion_mask"] is not None and need[9]) else None
         d_mlp = torch.empty((P, J - 1), **opts) if (t["mlp_weight"] is not None and need[10]) else None
@@ -207,16 +219,22 @@ class _SkinnedRender(torch.autograd.Function):
         ctx.ws = None
         if d_mask is not None:
             d_mask = d_mask.view_as(t["motion_mask"])
-        return (d_xyz, d_scaling, d_rotation, d_opacity, d_fdc, d_frest, d_radius, d_local_rot, d_trans, d_mask, d_mlp,
-                d_off, d_mean2D, None)
+        # A gradient that was written into a caller-provided buffer is delivered through that buffer only (autograd
+        # would otherwise clone it into param.grad: one more pass over ~240 B per Gaussian).
+        g = lambda name, ten: None if name in go else ten
+        return (g("xyz", d_xyz), g("scaling", d_scaling), g("rotation", d_rotation), g("opacity", d_opacity),
+                g("features_dc", d_fdc), g("features_rest", d_frest), g("node_radius", d_radius), d_local_rot, d_trans,
+                d_mask, d_mlp, d_off, d_mean2D, None)
 
 
 def render_skinned(viewpoint_camera, pc, skeleton, pose: Dict[str, torch.Tensor], pipe, bg_color: torch.Tensor,
                    scaling_modifier=1.0, mlp_weight=None, offsets=None, zero_d_rotation: Optional[bool] = None,
-                   debug_outputs=None, pool: Optional[WorkspacePool] = None):
+                   debug_outputs=None, pool: Optional[WorkspacePool] = None, grad_out=None):
     """Fused deform + render.  ``pc``: object with the GaussianModel raw tensors (_xyz, _scaling, _rotation, _opacity,
     _features_dc, _features_rest, motion_mask, active_sh_degree); ``skeleton``: riggs_b200 SkeletonWarp (joints,
     parents, _node_radius); ``pose``: {'local_rotation': (J,4), 'global_trans': (3,)}.
+    ``grad_out``: optional dict of preallocated gradient buffers (keys xyz, scaling, rotation, opacity, features_dc,
+    features_rest, node_radius) the backward kernels write into directly -- e.g. the views of ``dist.FlatGrads``.
     Returns the dict of ``render()`` plus ``d_nodes``."""
     xyz = pc._xyz
     screenspace_points = torch.zeros_like(xyz, requires_grad=True)
@@ -228,7 +246,7 @@ def render_skinned(viewpoint_camera, pc, skeleton, pose: Dict[str, torch.Tensor]
                viewmatrix=f32c(viewpoint_camera.world_view_transform), projmatrix=f32c(viewpoint_camera.full_proj_transform),
                campos=f32c(viewpoint_camera.camera_center), bg=f32c(bg_color),
                zero_d_rotation=isotropic if zero_d_rotation is None else zero_d_rotation, debug_outputs=debug_outputs,
-               pool=pool)
+               pool=pool, grad_out=grad_out)
     mm = getattr(pc, "_motion_mask", None)
     mask = mm.reshape(-1) if mm is not None else None
     color, depth, alpha, radii, d_nodes = _SkinnedRender.apply(

@@ -33,6 +33,28 @@ class HotPath:
         self.pipe = _Pipe()
         self.bg = torch.zeros(3, device=device)
         self.isotropic = self.pc.use_isotropic_gs
+        self.flat = None
+
+    def named_parameters(self):
+        pc = self.pc
+        return [("xyz", pc._xyz), ("features_dc", pc._features_dc), ("features_rest", pc._features_rest),
+                ("opacity", pc._opacity), ("scaling", pc._scaling), ("rotation", pc._rotation),
+                ("node_radius", self.warp._node_radius)]
+
+    def enable_flat_grads(self):
+        """Data-parallel mode: the fused backward writes the parameter gradients straight into one flat buffer
+        (dist.FlatGrads) that is all-reduced in place; ``reduce_grads()`` then exposes it through ``param.grad``."""
+        from .dist import FlatGrads
+        self.flat = FlatGrads(self.named_parameters(), device=self.device)
+        return self.flat
+
+    def reduce_grads(self):
+        if self.flat is None:
+            return
+        if not self.fused:
+            self.flat.pack_from_grads()
+        self.flat.all_reduce()
+        self.flat.attach()
 
     def parameters(self):
         pc = self.pc
@@ -48,7 +70,7 @@ class HotPath:
         if self.fused:
             from .fused import render_skinned
             return render_skinned(cam, self.pc, self.warp, pose, self.pipe, self.bg, mlp_weight=self.mlp_weight,
-                                  offsets=self.offsets)
+                                  offsets=self.offsets, grad_out=self.flat.views if self.flat is not None else None)
         joints = self.warp.nodes[:, :3]
         G, node_rot, d_nodes = sw.fk(pose["local_rotation"], pose["global_trans"], joints, self.warp.parents_i32)
         mask = self.pc._motion_mask.reshape(-1) if self.pc._motion_mask is not None else None
