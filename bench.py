@@ -129,7 +129,8 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=120))
     scene = make_scene(args.workload, args.isotropic)
     hp = HotPath(scene, device=dev, fused=not args.unfused)
     cam = scene.cameras[rank % len(scene.cameras)].to(dev)
@@ -167,9 +168,9 @@ def run_ours(args):
         t_wait = time.time()
         while not clocks.rows and time.time() - t_wait < 5.0:
             time.sleep(0.05)
-        for _ in range(3):
-            one_step(target, pose)
-        torch.cuda.synchronize()
+    for _ in range(3):  # every rank runs the same number of steps (each one contains a collective when N > 1)
+        one_step(target, pose)
+    torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
 
