@@ -29,6 +29,7 @@ private:
 };
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+__device__ __forceinline__ size_t align_up_dev(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // Carves typed arrays out of one opaque byte buffer, 256-byte aligned.
 struct Carver {

@@ -15,6 +15,7 @@
 //
 // HBM-bound: reads 44 + 12*M + 40 (+12 kept means3D) bytes, writes 88 + 12*M bytes per Gaussian.
 #include "bones.cuh"
+#include "bulk_copy.cuh"
 #include "common.cuh"
 #include "kernels.cuh"
 #include "math.cuh"
@@ -81,18 +82,45 @@ __global__ void __launch_bounds__(256) gauss_backward_kernel(GaussBwdArgs a, Ski
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
     __shared__ float s_mat[35];
+    __shared__ __align__(8) uint64_t s_bar;
     extern __shared__ __align__(16) unsigned char s_raw[];
     if (threadIdx.x < 16) s_mat[threadIdx.x] = a.viewmatrix[threadIdx.x];
     else if (threadIdx.x < 32) s_mat[threadIdx.x] = a.projmatrix[threadIdx.x - 16];
     else if (threadIdx.x < 35) s_mat[threadIdx.x] = a.campos[threadIdx.x - 32];
     BoneSm* s_b = reinterpret_cast<BoneSm*>(s_raw);
     const int K = FUSED ? s.f.J - 1 : 0;
-    float* s_acc = reinterpret_cast<float*>(s_raw + sizeof(BoneSm) * (size_t)(K > 1 ? K : 1));  // K*13 + 3
+    // per-warp accumulator rows (K*13 + 3 floats each): a warp owns its row, so no shared-memory atomics are needed
+    const int acc_stride = K * 13 + 3;
+    float* s_acc_all = reinterpret_cast<float*>(s_raw + sizeof(BoneSm) * (size_t)(K > 1 ? K : 1));
+    float* s_acc = s_acc_all + (threadIdx.x >> 5) * acc_stride;
     if (FUSED) {
         stage_bones(s.f.J, s.f.joints, s.f.parents, s.f.node_radius_raw, s.f.G, s.f.node_rot, s_b);
-        for (int k = threadIdx.x; k < K * 13 + 3; k += blockDim.x) s_acc[k] = 0.f;
+        for (int k = threadIdx.x; k < 8 * acc_stride; k += blockDim.x) s_acc_all[k] = 0.f;
+        if (threadIdx.x == 0) mbar_init(&s_bar, 1);
     }
     __syncthreads();
+    // Fused variant: the CTA's block of features_rest (256 rows, contiguous) comes in through one bulk (TMA) copy and
+    // the block of d_features_rest leaves the same way; per-thread accesses would have a 180-byte stride.
+    float* s_sh = nullptr;
+    size_t sh_row = 0, sh_first = 0;
+    uint32_t sh_bytes = 0;
+    bool sh_bulk = false;
+    if (FUSED) {
+        s_sh = reinterpret_cast<float*>(s_raw + align_up_dev(sizeof(BoneSm) * (size_t)(K > 1 ? K : 1) +
+                                                             sizeof(float) * 8 * (size_t)acc_stride, 128));
+        sh_row = (size_t)s.f.M_rest * 3;
+        sh_first = (size_t)blockIdx.x * blockDim.x;
+        const int n_valid = max(0, min((int)blockDim.x, a.P - (int)sh_first));
+        const float* src = s.f.features_rest + sh_first * sh_row;
+        sh_bytes = (uint32_t)(n_valid * sh_row * sizeof(float));
+        sh_bulk = (sh_bytes % 16 == 0) && ((reinterpret_cast<size_t>(src) & 15) == 0) && sh_bytes > 0;
+        if (sh_bulk) {
+            if (threadIdx.x == 0) bulk_load(s_sh, src, sh_bytes, &s_bar);
+        } else {
+            for (int k = threadIdx.x; k < (int)(sh_bytes / 4); k += blockDim.x) s_sh[k] = __ldg(src + k);
+            __syncthreads();
+        }
+    }
     const float* view = s_mat;
     const float* proj = s_mat + 16;
     const size_t i = (size_t)idx;
@@ -216,7 +244,10 @@ __global__ void __launch_bounds__(256) gauss_backward_kernel(GaussBwdArgs a, Ski
         // ---- SH path
         if (FUSED || a.shs) {
             float sh[48];
-            if (FUSED) load_sh_split(s.f.features_dc, s.f.features_rest, i, s.f.M_rest, sh);
+            if (FUSED) {
+                if (sh_bulk) mbar_wait(&s_bar, 0);
+                load_sh_staged(s.f.features_dc, s_sh + (size_t)threadIdx.x * sh_row, i, s.f.M_rest, sh);
+            }
             else load_sh<16>(a.shs, i, a.M, a.sh_vec_ok, sh);
             const float3 campos = {s_mat[32], s_mat[33], s_mat[34]};
             const float3 dm = sh_backward_core(a.D, mean, campos, sh, a.clamped[idx], g_color, basis, gsh);
@@ -286,12 +317,28 @@ __global__ void __launch_bounds__(256) gauss_backward_kernel(GaussBwdArgs a, Ski
         reinterpret_cast<float4*>(s.d_rotation_raw)[i] = drot_raw;
         s.d_opacity_raw[i] = g_opacity * opacity_act * (1.f - opacity_act);
         s.d_features_dc[3 * i] = basis[0] * gsh[0]; s.d_features_dc[3 * i + 1] = basis[0] * gsh[1]; s.d_features_dc[3 * i + 2] = basis[0] * gsh[2];
-        float* rest = s.d_features_rest + i * s.f.M_rest * 3;
+    }
+    // d_features_rest: every thread drops its row into the staging block (all SH rows have been read into registers
+    // by now), then the block leaves the SM as one bulk store (or a cooperative coalesced copy for a ragged tail).
+    if (sh_bulk) mbar_wait(&s_bar, 0);  // threads of culled Gaussians never waited: the load must have landed first
+    __syncthreads();
+    if (in_range) {
+        float* rest = s_sh + (size_t)threadIdx.x * sh_row;
 #pragma unroll
         for (int k = 1; k < 16; k++) {
             if (k <= s.f.M_rest) {
                 rest[3 * (k - 1)] = basis[k] * gsh[0]; rest[3 * (k - 1) + 1] = basis[k] * gsh[1]; rest[3 * (k - 1) + 2] = basis[k] * gsh[2];
             }
+        }
+    }
+    __syncthreads();
+    {
+        float* dst = s.d_features_rest + sh_first * sh_row;
+        const bool st_bulk = (sh_bytes % 16 == 0) && ((reinterpret_cast<size_t>(dst) & 15) == 0) && sh_bytes > 0;
+        if (st_bulk) {
+            if (threadIdx.x == 0) bulk_store(dst, s_sh, sh_bytes);
+        } else {
+            for (int k = threadIdx.x; k < (int)(sh_bytes / 4); k += blockDim.x) dst[k] = s_sh[k];
         }
     }
 
@@ -343,7 +390,7 @@ __global__ void __launch_bounds__(256) gauss_backward_kernel(GaussBwdArgs a, Ski
         const float mgx = m * gx, mgy = m * gy, mgz = m * gz;
         {
             const float s0 = warp_sum(mgx), s1 = warp_sum(mgy), s2 = warp_sum(mgz);
-            if (lane == 0) { atomicAdd(&s_acc[K * 13], s0); atomicAdd(&s_acc[K * 13 + 1], s1); atomicAdd(&s_acc[K * 13 + 2], s2); }
+            if (lane == 0) { s_acc[K * 13] += s0; s_acc[K * 13 + 1] += s1; s_acc[K * 13 + 2] += s2; }
         }
         const int my_id = (lane >> 1) & 15;
         const bool writer = !(lane & 1) && my_id < 13;
@@ -368,20 +415,25 @@ __global__ void __launch_bounds__(256) gauss_backward_kernel(GaussBwdArgs a, Ski
             v[12] = dwhat * sw * e * d2 * (2.0f * b.inv_2r2);
             v[13] = v[14] = v[15] = 0.f;
             const float r = transpose_reduce16(v, lane);
-            if (writer && r != 0.f) atomicAdd(&s_acc[k * 13 + my_id], r);
+            if (writer) s_acc[k * 13 + my_id] += r;
         }
     }
     __syncthreads();
     for (int k = threadIdx.x; k < K * 13; k += blockDim.x) {
-        const float val = s_acc[k];
+        float val = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; w++) val += s_acc_all[w * acc_stride + k];
         if (val != 0.f) {
             const int bone = k / 13, c = k % 13;
             if (c < 12) atomicAdd(&s.dG[12 * (bone + 1) + c], val);
             else atomicAdd(&s.dnode_radius_raw[bone + 1], val);
         }
     }
+    if (threadIdx.x == 0) bulk_store_wait_read();  // shared memory must outlive the bulk store's reads
     if (threadIdx.x < 3) {
-        const float val = s_acc[K * 13 + threadIdx.x];
+        float val = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; w++) val += s_acc_all[w * acc_stride + K * 13 + threadIdx.x];
         if (val != 0.f) atomicAdd(&s.dglobal_trans[threadIdx.x], val);
     }
 }
@@ -398,7 +450,14 @@ int launch_gauss_skin_backward(const GaussBwdArgs& a, const SkinFuseBwdArgs& s, 
     if (a.P == 0) return 0;
     if (s.f.J > kMaxJoints || s.f.J < 2) { set_error("skinned backward: J must be in [2, 128]"); return -1; }
     LaunchScope ls("gauss_skin_backward", stream);
-    gauss_backward_kernel<true><<<(a.P + 255) / 256, 256, bone_smem_bytes(s.f.J, true), stream>>>(a, s);
+    const size_t smem = align_up(bone_smem_bytes(s.f.J, false) + 8 * sizeof(float) * ((size_t)(s.f.J - 1) * 13 + 3), 128) +
+                        (size_t)256 * s.f.M_rest * 3 * sizeof(float) + 16;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(gauss_backward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+        attr_set = true;
+    }
+    gauss_backward_kernel<true><<<(a.P + 255) / 256, 256, smem, stream>>>(a, s);
     return 0;
 }
 

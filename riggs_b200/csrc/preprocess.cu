@@ -17,6 +17,7 @@
 // HBM-bound streaming kernel: algorithmic bytes per Gaussian = 44 (xyz, rot, scale, opacity) + 12*M (SH)
 // read, 48 written (+1 clamp byte, +12 means3D in the fused variant).
 #include "bones.cuh"
+#include "bulk_copy.cuh"
 #include "common.cuh"
 #include "kernels.cuh"
 #include "math.cuh"
@@ -33,8 +34,31 @@ __global__ void __launch_bounds__(256) preprocess_kernel(PreprocessArgs a, SkinF
     else if (threadIdx.x < 32) s_mat[threadIdx.x] = a.projmatrix[threadIdx.x - 16];
     else if (threadIdx.x < 35) s_mat[threadIdx.x] = a.cam_pos[threadIdx.x - 32];
     BoneSm* s_b = reinterpret_cast<BoneSm*>(s_raw);
-    if (FUSED) stage_bones(s.J, s.joints, s.parents, s.node_radius_raw, s.G, s.node_rot, s_b);
+    // Fused variant: this CTA's block of features_rest (256 rows of M_rest*12 B, contiguous in memory) is pulled into
+    // shared memory by one bulk (TMA) copy that runs while the threads do the skinning loop below.
+    __shared__ __align__(8) uint64_t s_bar;
+    float* s_sh = nullptr;
+    bool sh_bulk = false;
+    if (FUSED) {
+        stage_bones(s.J, s.joints, s.parents, s.node_radius_raw, s.G, s.node_rot, s_b);
+        s_sh = reinterpret_cast<float*>(s_raw + align_up_dev(sizeof(BoneSm) * (size_t)(s.J > 1 ? s.J - 1 : 1), 128));
+        if (threadIdx.x == 0) mbar_init(&s_bar, 1);
+    }
     __syncthreads();
+    if (FUSED) {
+        const size_t row = (size_t)s.M_rest * 3;
+        const size_t first = (size_t)blockIdx.x * blockDim.x;
+        const int n_valid = min((int)blockDim.x, a.P - (int)first);
+        const float* src = s.features_rest + first * row;
+        const uint32_t bytes = (uint32_t)(n_valid * row * sizeof(float));
+        sh_bulk = (bytes % 16 == 0) && ((reinterpret_cast<size_t>(src) & 15) == 0) && bytes > 0;
+        if (sh_bulk) {
+            if (threadIdx.x == 0) bulk_load(s_sh, src, bytes, &s_bar);
+        } else {  // ragged tail block: plain cooperative copy
+            for (int k = threadIdx.x; k < n_valid * (int)row; k += blockDim.x) s_sh[k] = __ldg(src + k);
+            __syncthreads();
+        }
+    }
     if (idx >= a.P) return;
     const float* view = s_mat;
     const float* proj = s_mat + 16;
@@ -138,7 +162,10 @@ __global__ void __launch_bounds__(256) preprocess_kernel(PreprocessArgs a, SkinF
         uint8_t clamp_bits = 0;
         if (FUSED || a.colors_precomp == nullptr) {
             float sh[48];
-            if (FUSED) load_sh_split(s.features_dc, s.features_rest, i, s.M_rest, sh);
+            if (FUSED) {
+                if (sh_bulk) mbar_wait(&s_bar, 0);
+                load_sh_staged(s.features_dc, s_sh + (size_t)threadIdx.x * s.M_rest * 3, i, s.M_rest, sh);
+            }
             else load_sh<16>(a.shs, i, a.M, a.sh_vec_ok, sh);
             const float3 campos = {s_mat[32], s_mat[33], s_mat[34]};
             color = sh_to_rgb(a.D, p_orig, campos, sh, clamp_bits);
@@ -182,7 +209,13 @@ int launch_skin_preprocess(const PreprocessArgs& a, const SkinFuseArgs& s, cudaS
     if (a.P == 0) return 0;
     if (s.J > kMaxJoints || s.J < 2) { set_error("skinned preprocess: J must be in [2, 128]"); return -1; }
     LaunchScope ls("skin_preprocess", stream);
-    preprocess_kernel<true><<<(a.P + 255) / 256, 256, bone_smem_bytes(s.J, false), stream>>>(a, s);
+    const size_t smem = align_up(bone_smem_bytes(s.J, false), 128) + (size_t)256 * s.M_rest * 3 * sizeof(float) + 16;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(preprocess_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        attr_set = true;
+    }
+    preprocess_kernel<true><<<(a.P + 255) / 256, 256, smem, stream>>>(a, s);
     return 0;
 }
 

@@ -70,6 +70,15 @@ __device__ __forceinline__ void load_sh_split(const float* __restrict__ dc, cons
     for (int i = 0; i < 45; i++) sh[3 + i] = i < M_rest * 3 ? __ldg(src + i) : 0.f;
 }
 
+// Same, with this Gaussian's features_rest row already staged in shared memory (row stride M_rest*3 floats; an
+// odd stride of 45 words makes the per-lane reads bank-conflict free).
+__device__ __forceinline__ void load_sh_staged(const float* __restrict__ dc, const float* s_row, size_t idx, int M_rest,
+                                               float* sh) {
+    sh[0] = __ldg(dc + 3 * idx); sh[1] = __ldg(dc + 3 * idx + 1); sh[2] = __ldg(dc + 3 * idx + 2);
+#pragma unroll
+    for (int i = 0; i < 45; i++) sh[3 + i] = i < M_rest * 3 ? s_row[i] : 0.f;
+}
+
 __device__ __forceinline__ float3 dnormvdv(float3 v, float3 dv) {  // auxiliary.h:107-117
     float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
     float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
