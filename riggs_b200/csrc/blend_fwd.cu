@@ -47,21 +47,34 @@ __global__ void __launch_bounds__(RG_TILE_PIX) blend_forward_kernel(BlendFwdArgs
     uint32_t last_contributor = 0;
     float C0 = 0.f, C1 = 0.f, C2 = 0.f, weight = 0.f, D = 0.f;
 
+    // Software pipeline: the gathers of batch i+1 (id -> xy, conic, colour, depth: two dependent trips to L2/HBM) are
+    // issued right after batch i has been published to shared memory and complete while the warps filter and blend
+    // batch i.  On tiles whose pixels never saturate the per-batch latency is the kernel's critical path.
+    float2 n_xy = {0.f, 0.f};
+    float4 n_co = {0.f, 0.f, 0.f, 0.f}, n_rgbd = {0.f, 0.f, 0.f, 0.f};
+    auto fetch = [&](int batch) {
+        const uint32_t pos = range.x + (uint32_t)batch * RG_TILE_PIX + tid;
+        if (pos < range.y) {
+            const uint32_t id = a.point_list[pos];
+            n_xy = a.means2D[id];
+            n_co = a.conic_opacity[id];
+            n_rgbd = {a.colors[3 * id], a.colors[3 * id + 1], a.colors[3 * id + 2], a.depths[id]};
+        }
+    };
+    if (rounds > 0) fetch(0);
     for (int i = 0; i < rounds; i++, toDo -= RG_TILE_PIX) {
         int num_done = __syncthreads_count(done);
         if (num_done == RG_TILE_PIX) break;
         const int progress = i * RG_TILE_PIX + tid;
         if (range.x + progress < range.y) {
-            const uint32_t id = a.point_list[range.x + progress];
-            const float2 xy = a.means2D[id];
-            const float4 co = a.conic_opacity[id];
-            s_xy[tid] = xy;
-            s_co[tid] = co;
-            s_rgbd[tid] = {a.colors[3 * id], a.colors[3 * id + 1], a.colors[3 * id + 2], a.depths[id]};
-            s_thr[tid] = -logf(255.0f * co.w) - kSkipMargin;  // alpha < 1/255  <=>  power < -log(255 o)
-            s_cull[tid] = make_cull(xy, co, tile_x0, tile_y0);
+            s_xy[tid] = n_xy;
+            s_co[tid] = n_co;
+            s_rgbd[tid] = n_rgbd;
+            s_thr[tid] = -logf(255.0f * n_co.w) - kSkipMargin;  // alpha < 1/255  <=>  power < -log(255 o)
+            s_cull[tid] = make_cull(n_xy, n_co, tile_x0, tile_y0);
         }
         __syncthreads();
+        if (i + 1 < rounds) fetch(i + 1);
         const int n = min(RG_TILE_PIX, toDo);
         if (__all_sync(0xffffffffu, done)) continue;  // this warp's block is finished; keep helping with loads
         // ---- per-warp filter: which of the n staged instances can reach this 8x4 block?
