@@ -83,7 +83,7 @@ int rg_mark_visible(int P, const float* means3D, const float* viewmatrix, const 
 /* Addresses of the arrays inside the opaque buffers, for tests and debuggers (the reference keeps the
  * same information in GeometryState / BinningState / ImageState, dgr/cuda_rasterizer/rasterizer_impl.h:30-61).
  * out[0]=depths f32[P] (+inf where culled)  out[1]=clamped u8[P] (bit c = channel c clamped)
- * out[2]=means2D f32x2[P]         out[3]=conic_opacity f32x4[P]      out[4]=rgb f32[3P]
+ * out[2]=means2D f32x2[P]         out[3]=conic_opacity f32x4[P]      out[4]=splat records f32x16[P] (rgb at 8..10)
  * out[5]=tiles_touched u32[P]     out[6]=ids in depth order u32[P]   out[7]=means3D f32[3P] (fused entry only)
  * out[8]=point_list u32[R]        out[9]=n_contrib u32[H*W]          out[10]=ranges u32x2[tiles]
  * out[11]=status u32[2]: num_rendered, overflow flag */
@@ -236,6 +236,10 @@ void rg_profile_enable(int on);
 void rg_profile_reset(void);
 int rg_profile_count(void);
 int rg_profile_get(int index, char* name_out, int name_cap, float* total_ms, int* launches);
+/* Per-(tile, warp) cycle counters of the two blend kernels: fwd / bwd point to tiles*8*8 uint32 of device memory
+ * (or NULL to switch the counters off): total cycles, prefetch-wait cycles, stage-1 cycles, stage-2 cycles, surviving
+ * list entries, groups walked, aux (fwd: list length, bwd: reductions issued), 0. */
+int rg_debug_tile_profile(uint32_t* fwd, uint32_t* bwd);
 
 #ifdef __cplusplus
 }

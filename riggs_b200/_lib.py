@@ -64,6 +64,7 @@ _SIGNATURES = {
     "rg_profile_enable": (None, [_i]),
     "rg_profile_reset": (None, []),
     "rg_profile_count": (C.c_int, []),
+    "rg_debug_tile_profile": (C.c_int, [_p, _p]),
     "rg_profile_get": (C.c_int, [_i, C.c_char_p, _i, C.POINTER(C.c_float), C.POINTER(C.c_int)]),
 }
 

@@ -33,7 +33,7 @@ GeomState GeomState::carve(char* base, size_t P, int W, int H, size_t* bytes) {
     g.clamped = c.take<uint8_t>(P);
     g.means2D = c.take<float2>(P);
     g.conic_opacity = c.take<float4>(P);
-    g.rgb = c.take<float>(3 * P);
+    g.rec = c.take<float4>(4 * P);
     g.tiles_touched = c.take<uint32_t>(P);
     g.means3D = c.take<float>(3 * P);
     g.ids = c.take<uint32_t>(P);
@@ -45,6 +45,7 @@ GeomState GeomState::carve(char* base, size_t P, int W, int H, size_t* bytes) {
     g.E = c.take<uint32_t>((size_t)bp.NW * bp.T);
     g.S = c.take<uint32_t>((size_t)bp.nseg * bp.T);
     g.tile_base = c.take<uint32_t>(bp.T + 1);
+    g.tile_order = c.take<uint32_t>(bp.T);
     g.status = c.take<uint32_t>(8);
     g.grad_acc = c.take<float>(10 * P);
     g.d_rot = c.take<float>(4 * P);
@@ -132,7 +133,7 @@ int rg_rasterize_forward(rg_alloc_fn geom_alloc, void* geom_ctx, rg_alloc_fn bin
     pa.grid_x = grid_x; pa.grid_y = grid_y; pa.prefiltered = prefiltered != 0;
     pa.sh_vec_ok = shs && M == 16 && is_aligned16(shs);
     pa.radii = radii; pa.means2D = geom.means2D; pa.depths = geom.depths; pa.cov3D_out = nullptr;
-    pa.rgb = geom.rgb; pa.conic_opacity = geom.conic_opacity; pa.tiles_touched = geom.tiles_touched;
+    pa.rec = geom.rec; pa.conic_opacity = geom.conic_opacity; pa.tiles_touched = geom.tiles_touched;
     pa.clamped = geom.clamped; pa.ids = geom.ids;
     launch_preprocess(pa, stream);
     if (check_launch("preprocess", stream, dbg)) return -1;
@@ -143,7 +144,7 @@ int rg_rasterize_forward(rg_alloc_fn geom_alloc, void* geom_ctx, rg_alloc_fn bin
     if (check_launch("depth_sort", stream, dbg)) return -1;
     if (launch_tile_count(bp, P, grid_x, grid_y, geom.sorted_ids, geom.tiles_touched, geom.means2D, radii, geom.M, stream))
         return -1;
-    launch_tile_offsets_a(bp, geom.M, geom.S, geom.tile_base, img.ranges, geom.status, 0xffffffffu, stream);
+    launch_tile_offsets_a(bp, geom.M, geom.S, geom.tile_base, img.ranges, geom.tile_order, geom.status, 0xffffffffu, stream);
     if (check_launch("tile_count/offsets", stream, dbg)) return -1;
 
     // The one host round trip of the forward (the reference does the same, rasterizer_impl.cu:282): the
@@ -167,9 +168,8 @@ int rg_rasterize_forward(rg_alloc_fn geom_alloc, void* geom_ctx, rg_alloc_fn bin
 
     BlendFwdArgs fa;
     fa.W = width; fa.H = height; fa.grid_x = grid_x; fa.grid_y = grid_y;
-    fa.ranges = img.ranges; fa.point_list = bin.point_list; fa.means2D = geom.means2D;
-    fa.colors = colors_precomp ? colors_precomp : geom.rgb;
-    fa.depths = geom.depths; fa.conic_opacity = geom.conic_opacity; fa.bg = background;
+    fa.ranges = img.ranges; fa.point_list = bin.point_list;
+    fa.rec = geom.rec; fa.bg = background; fa.tile_order = geom.tile_order;
     fa.out_color = out_color; fa.out_depth = out_depth; fa.out_alpha = out_alpha; fa.n_contrib = img.n_contrib;
     launch_blend_forward(fa, stream);
     if (check_launch("blend_forward", stream, dbg)) return -1;
@@ -206,9 +206,9 @@ int rg_rasterize_backward(int P, int D, int M, int R, const float* background, i
     cudaMemsetAsync(acc, 0, sizeof(float) * 10 * (size_t)P, stream);
     BlendBwdArgs ba;
     ba.P = P; ba.W = width; ba.H = height; ba.grid_x = grid_x; ba.grid_y = grid_y;
-    ba.ranges = img.ranges; ba.point_list = bin.point_list; ba.bg = background; ba.means2D = geom.means2D;
-    ba.conic_opacity = geom.conic_opacity; ba.colors = colors_precomp ? colors_precomp : geom.rgb;
-    ba.depths = geom.depths; ba.alphas = alphas; ba.n_contrib = img.n_contrib; ba.dL_dpix = dL_dpix;
+    ba.ranges = img.ranges; ba.point_list = bin.point_list; ba.bg = background;
+    ba.rec = geom.rec; ba.tile_order = geom.tile_order;
+    ba.alphas = alphas; ba.n_contrib = img.n_contrib; ba.dL_dpix = dL_dpix;
     ba.dL_dpix_depth = dL_dpix_depth; ba.dL_dalphas = dL_dalphas; ba.grad_acc = acc;
     if (R > 0) launch_blend_backward(ba, stream);
     if (check_launch("blend_backward", stream, dbg)) return -1;
@@ -240,7 +240,7 @@ int rg_mark_visible(int P, const float* means3D, const float* viewmatrix, const 
 int rg_state_ptrs(int P, int64_t R, int width, int height, char* geom_buffer, char* binning_buffer, char* image_buffer,
                   void** out) {
     GeomState g = GeomState::carve(aligned_base(geom_buffer), P, width, height, nullptr);
-    out[0] = g.depths; out[1] = g.clamped; out[2] = g.means2D; out[3] = g.conic_opacity; out[4] = g.rgb;
+    out[0] = g.depths; out[1] = g.clamped; out[2] = g.means2D; out[3] = g.conic_opacity; out[4] = g.rec;
     out[5] = g.tiles_touched; out[6] = g.sorted_ids; out[7] = g.means3D;
     if (binning_buffer) {
         BinningState b = BinningState::carve(aligned_base(binning_buffer), (size_t)(R > 0 ? R : 0), nullptr);

@@ -81,7 +81,7 @@ int rg_skinned_forward(const RgSkinnedScene* s, const RgWorkspace* w, float* out
     pa.W = W; pa.H = H; pa.tan_fovx = s->tan_fovx; pa.tan_fovy = s->tan_fovy;
     pa.focal_y = H / (2.0f * s->tan_fovy); pa.focal_x = W / (2.0f * s->tan_fovx);
     pa.grid_x = grid_x; pa.grid_y = grid_y; pa.prefiltered = false; pa.sh_vec_ok = false;
-    pa.radii = radii; pa.means2D = geom.means2D; pa.depths = geom.depths; pa.rgb = geom.rgb;
+    pa.radii = radii; pa.means2D = geom.means2D; pa.depths = geom.depths; pa.rec = geom.rec;
     pa.conic_opacity = geom.conic_opacity; pa.tiles_touched = geom.tiles_touched; pa.clamped = geom.clamped;
     pa.ids = geom.ids;
     SkinFuseArgs f = fuse_args(s, geom, fk);
@@ -93,14 +93,14 @@ int rg_skinned_forward(const RgSkinnedScene* s, const RgWorkspace* w, float* out
         return -1;
     if (launch_tile_count(bp, P, grid_x, grid_y, geom.sorted_ids, geom.tiles_touched, geom.means2D, radii, geom.M, stream))
         return -1;
-    launch_tile_offsets_a(bp, geom.M, geom.S, geom.tile_base, img.ranges, geom.status, cap, stream);
+    launch_tile_offsets_a(bp, geom.M, geom.S, geom.tile_base, img.ranges, geom.tile_order, geom.status, cap, stream);
     launch_tile_scatter(bp, P, grid_x, grid_y, geom.sorted_ids, geom.tiles_touched, geom.means2D, radii, geom.M, geom.S,
                         geom.tile_base, geom.E, bin.point_list, cap, stream);
 
     BlendFwdArgs fa;
     fa.W = W; fa.H = H; fa.grid_x = grid_x; fa.grid_y = grid_y;
-    fa.ranges = img.ranges; fa.point_list = bin.point_list; fa.means2D = geom.means2D; fa.colors = geom.rgb;
-    fa.depths = geom.depths; fa.conic_opacity = geom.conic_opacity; fa.bg = s->background;
+    fa.ranges = img.ranges; fa.point_list = bin.point_list; fa.rec = geom.rec; fa.tile_order = geom.tile_order;
+    fa.bg = s->background;
     fa.out_color = out_color; fa.out_depth = out_depth; fa.out_alpha = out_alpha; fa.n_contrib = img.n_contrib;
     launch_blend_forward(fa, stream);
     return check_launch("rg_skinned_forward", stream, false);
@@ -137,8 +137,8 @@ int rg_skinned_backward(const RgSkinnedScene* s, const RgWorkspace* w, const int
 
     BlendBwdArgs ba;
     ba.P = P; ba.W = W; ba.H = H; ba.grid_x = grid_x; ba.grid_y = grid_y;
-    ba.ranges = img.ranges; ba.point_list = bin.point_list; ba.bg = s->background; ba.means2D = geom.means2D;
-    ba.conic_opacity = geom.conic_opacity; ba.colors = geom.rgb; ba.depths = geom.depths; ba.alphas = alphas;
+    ba.ranges = img.ranges; ba.point_list = bin.point_list; ba.bg = s->background;
+    ba.rec = geom.rec; ba.tile_order = geom.tile_order; ba.alphas = alphas;
     ba.n_contrib = img.n_contrib; ba.dL_dpix = dL_dcolor; ba.dL_dpix_depth = dL_ddepth; ba.dL_dalphas = dL_dalpha;
     ba.grad_acc = geom.grad_acc;
     launch_blend_backward(ba, stream);

@@ -137,11 +137,19 @@ __global__ void __launch_bounds__(256) seg_sum_kernel(int T, int Tpad, int NW, c
     S[(size_t)seg * T + t] = s;
 }
 
+constexpr int kOrderBuckets = 128;
+__device__ __forceinline__ int order_bucket(uint32_t n) {
+    if (n < 4) return (int)n;
+    const int e = 31 - __clz(n);
+    return e * 4 + (int)((n >> (e - 2)) & 3u);
+}
+
 // ---- 3b. per-tile totals, prefix over segments (in place), prefix over tiles, ranges, num_rendered -----
 __global__ void __launch_bounds__(1024) tile_base_kernel(int T, int nseg, uint32_t* __restrict__ S, uint32_t* __restrict__ tile_base,
-                                                         uint2* __restrict__ ranges, uint32_t* __restrict__ status,
-                                                         uint32_t capacity) {
+                                                         uint2* __restrict__ ranges, uint32_t* __restrict__ tile_order,
+                                                         uint32_t* __restrict__ status, uint32_t capacity) {
     __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_bucket[kOrderBuckets];
     __shared__ uint32_t s_carry;
     if (threadIdx.x == 0) s_carry = 0;
     __syncthreads();
@@ -184,6 +192,29 @@ __global__ void __launch_bounds__(1024) tile_base_kernel(int T, int nseg, uint32
         __syncthreads();
         if (threadIdx.x == 1023) s_carry = carry + s_warp[31];
         __syncthreads();
+    }
+    // Launch order of the blend kernels: tiles with the longest lists first (counting sort on a 2-bit-mantissa log
+    // scale, descending), so that the frame's few heavy tiles start at once instead of wherever the raster order puts
+    // them, and the short ones fill in behind.
+    for (int b = threadIdx.x; b < kOrderBuckets; b += 1024) s_bucket[b] = 0;
+    __syncthreads();
+    for (int t = threadIdx.x; t < T; t += 1024) {
+        const uint2 r = ranges[t];
+        atomicAdd(&s_bucket[order_bucket(r.y - r.x)], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t run = 0;
+        for (int b = kOrderBuckets - 1; b >= 0; b--) {
+            const uint32_t c = s_bucket[b];
+            s_bucket[b] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < T; t += 1024) {
+        const uint2 r = ranges[t];
+        tile_order[atomicAdd(&s_bucket[order_bucket(r.y - r.x)], 1u)] = (uint32_t)t;
     }
     if (threadIdx.x == 0) {
         status[0] = s_carry;                       // num_rendered
@@ -284,11 +315,11 @@ int launch_tile_count(const BinPlan& b, int P, int grid_x, int grid_y, const uin
 }
 
 int launch_tile_offsets_a(const BinPlan& b, const uint16_t* M, uint32_t* S, uint32_t* tile_base, uint2* ranges,
-                          uint32_t* status, uint32_t capacity, cudaStream_t stream) {
+                          uint32_t* tile_order, uint32_t* status, uint32_t capacity, cudaStream_t stream) {
     LaunchScope ls("tile_offsets", stream, 2);
     dim3 g((b.T + 255) / 256, b.nseg);
     seg_sum_kernel<<<g, 256, 0, stream>>>(b.T, b.Tpad, b.NW, M, S);
-    tile_base_kernel<<<1, 1024, 0, stream>>>(b.T, b.nseg, S, tile_base, ranges, status, capacity);
+    tile_base_kernel<<<1, 1024, 0, stream>>>(b.T, b.nseg, S, tile_base, ranges, tile_order, status, capacity);
     return 0;
 }
 

@@ -1,24 +1,26 @@
-// Backward alpha blend: one CTA per tile, back-to-front replay.  Replaces renderCUDA of
-// dgr/cuda_rasterizer/backward.cu:415-601.
+// Backward alpha blend, back-to-front replay.  Replaces renderCUDA of dgr/cuda_rasterizer/backward.cu:415-601.
 //
-// The reference issues 10 global float atomicAdds per contributing (pixel, instance) pair.  Here
-//  * a warp owns an 8x4 pixel block and, per batch of 256 staged instances, first builds the list of
-//    instances whose alpha >= 1/255 ellipse can reach its block (cull.cuh) and that lie in front of the
-//    block's deepest last contributor; only those are replayed;
+// The reference issues 10 global float atomicAdds per contributing (pixel, instance) pair from a 256-thread CTA per
+// tile that walks the whole list in lock step.  Here (same decomposition as blend_fwd.cu)
+//  * one warp = one 8x4 pixel block, independent of the rest of its tile: it replays only the entries in front of
+//    ITS deepest last contributor (the reference skips the others one by one, backward.cu:517-519), and of those only
+//    the instances whose alpha >= 1/255 footprint can reach the block (ListWalker of blend_common.cuh);
+//  * two survivors are replayed per iteration: the Gaussian evaluations are independent, the T / accumulator
+//    recurrence between them is a handful of FMAs, and the two warp reductions interleave;
 //  * the ten per-pair terms of an instance are summed across the warp with a 12-shuffle transpose-reduce
 //    (10 values x 32 lanes -> one value per lane) and leave the SM as ONE 10-lane reduction per
-//    (warp block, instance): ~2 x 10 atomics per (tile, instance) instead of up to 2560;
-//  * the replay starts at the tile's largest n_contrib instead of the end of the range: entries behind
-//    every pixel's last contributor are skipped by the reference one by one (backward.cu:517-519).
+//    (warp block, instance) instead of up to 320 atomics.
 // Per-pair arithmetic is the reference's expression order; sums differ only in association (tolerance 1e-4).
-#include "common.cuh"
-#include "cull.cuh"
+#include "blend_common.cuh"
 #include "kernels.cuh"
 
 namespace rg {
 
-constexpr float kSkipMarginB = 1e-4f;
 constexpr int kAcc = 10;  // mean2D.x, mean2D.y, conic.x, conic.y, conic.w, opacity, r, g, b, depth
+
+// Optional per-(tile, warp) cycle counters for performance analysis (rg_debug_tile_profile); null in production.
+__device__ uint32_t* g_bwd_tile_prof = nullptr;
+void set_bwd_tile_profile(uint32_t* p) { cudaMemcpyToSymbol(g_bwd_tile_prof, &p, sizeof(p)); }
 
 // Sum each of v[0..9] over the 32 lanes.  Afterwards the lane with id_of_lane(lane) = k >= 0 holds the
 // total of v[k] in the return value.  12 shuffles (5+3+2+1+1) instead of 50.
@@ -63,41 +65,34 @@ __device__ __forceinline__ int id_of_lane(int lane) {
     return ((lane & 16) ? 5 : 0) + sub;
 }
 
-__global__ void __launch_bounds__(RG_TILE_PIX) blend_backward_kernel(BlendBwdArgs a) {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int bx0 = (warp & 1) * kBlkW, by0 = (warp >> 1) * kBlkH;
-    const uint2 pix = {blockIdx.x * RG_TILE + bx0 + (lane & 7), blockIdx.y * RG_TILE + by0 + (lane >> 3)};
+__global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendBwdArgs a) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tile = (int)a.tile_order[blockIdx.x >> 2], strip = blockIdx.x & 3;
+    const int tile_x = tile % a.grid_x, tile_y = tile / a.grid_x;
+    const int bx0 = warp * kBlkW, by0 = strip * kBlkH;
+    const uint2 pix = {(unsigned)(tile_x * RG_TILE + bx0 + (lane & 7)), (unsigned)(tile_y * RG_TILE + by0 + (lane >> 3))};
     const uint32_t pix_id = a.W * pix.y + pix.x;
     const float2 pixf = {(float)pix.x, (float)pix.y};
     const bool inside = pix.x < (unsigned)a.W && pix.y < (unsigned)a.H;
-    const uint2 range = a.ranges[blockIdx.y * a.grid_x + blockIdx.x];
-    const float tile_x0 = (float)(blockIdx.x * RG_TILE), tile_y0 = (float)(blockIdx.y * RG_TILE);
-    const float blk_x0 = tile_x0 + bx0, blk_y0 = tile_y0 + by0;
-    const float blk_x1 = blk_x0 + (kBlkW - 1), blk_y1 = blk_y0 + (kBlkH - 1);
 
-    __shared__ uint32_t s_id[RG_TILE_PIX];
-    __shared__ float2 s_xy[RG_TILE_PIX];
-    __shared__ float4 s_co[RG_TILE_PIX];
-    __shared__ float4 s_rgbd[RG_TILE_PIX];
-    __shared__ float s_thr[RG_TILE_PIX];
-    __shared__ CullRec s_cull[RG_TILE_PIX];
-    __shared__ uint8_t s_list[8][RG_TILE_PIX];
-    __shared__ int s_max;
+    const int last_contributor = inside ? a.n_contrib[pix_id] : 0;
+    int total = last_contributor;  // entries [range.x, range.x + total) can contribute to this block
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) total = max(total, __shfl_xor_sync(0xffffffffu, total, o));
+    if (total == 0) return;
+
+    __shared__ WarpStage s_stage[kBlendWarps];
+    WarpStage& st = s_stage[warp];
+    ListWalker<true> walk;
+    walk.pl = a.point_list; walk.rec = a.rec; walk.first = a.ranges[tile_y * a.grid_x + tile_x].x; walk.n = total;
+    walk.lane = lane;
+    walk.x0 = (float)(tile_x * RG_TILE + bx0); walk.y0 = (float)(tile_y * RG_TILE + by0);
+    walk.x1 = walk.x0 + (kBlkW - 1); walk.y1 = walk.y0 + (kBlkH - 1);
+    const int n_groups = (total + kGroup - 1) / kGroup;
+    walk.begin();
 
     const float T_final = inside ? (1 - a.alphas[pix_id]) : 0;
     float T = T_final;
-    const int last_contributor = inside ? a.n_contrib[pix_id] : 0;
-
-    if (tid == 0) s_max = 0;
-    __syncthreads();
-    int wmax = last_contributor;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
-    if (lane == 0) atomicMax(&s_max, wmax);
-    __syncthreads();
-    const int total = s_max;  // instances [range.x, range.x + total) can contribute to this tile
-    if (total == 0) return;
-
     float accum_rec[3] = {0, 0, 0}, dL_dpixel[3] = {0, 0, 0};
     float accum_depth_rec = 0, dL_dpixel_depth = 0, accum_alpha_rec = 0, dL_dalpha = 0;
     if (inside) {
@@ -112,102 +107,103 @@ __global__ void __launch_bounds__(RG_TILE_PIX) blend_backward_kernel(BlendBwdArg
     const float ddely_dy = 0.5 * a.H;
     const float bg_dot_dpixel = a.bg[0] * dL_dpixel[0] + a.bg[1] * dL_dpixel[1] + a.bg[2] * dL_dpixel[2];
     const int my_id = id_of_lane(lane);
+    uint32_t* const prof = g_bwd_tile_prof;
+    long long t_start = 0;
+    uint32_t n_list = 0, n_red = 0;
+    if (prof) { t_start = clock64(); walk.timing = true; }
 
-    const int rounds = (total + RG_TILE_PIX - 1) / RG_TILE_PIX;
-    for (int i = 0; i < rounds; i++) {
-        __syncthreads();
-        const int progress = i * RG_TILE_PIX + tid;  // 0 = deepest candidate
-        if (progress < total) {
-            const uint32_t id = a.point_list[range.x + total - progress - 1];
-            const float2 xy = a.means2D[id];
-            const float4 co = a.conic_opacity[id];
-            s_id[tid] = id;
-            s_xy[tid] = xy;
-            s_co[tid] = co;
-            s_rgbd[tid] = {a.colors[3 * id], a.colors[3 * id + 1], a.colors[3 * id + 2], a.depths[id]};
-            s_thr[tid] = -logf(255.0f * co.w) - kSkipMarginB;
-            s_cull[tid] = make_cull(xy, co, tile_x0, tile_y0);
-        }
-        __syncthreads();
-        const int n = min(RG_TILE_PIX, total - i * RG_TILE_PIX);
-        // position (0-based, in the tile's range) of staged entry e is  pos(e) = total - 1 - (i*256 + e)
-        const int pos0 = total - 1 - i * RG_TILE_PIX;
-        if (pos0 - (n - 1) >= wmax) continue;  // the whole batch lies behind this block's last contributors
-        int cnt = 0;
+    constexpr int U = 2;
+    for (int g = 0; g < n_groups; g++) {
+        const int cnt = walk.next(g, st);
+        if (prof) n_list += cnt;
+        for (int l = 0; l < cnt; l += U) {
+            float v[U][kAcc];
+            bool active[U];
+            float G[U], alpha[U];
+            float2 d[U];
+            float4 con_o[U];
+            int e[U];
+            // independent part: Gaussian falloff and alpha of each of the U survivors
 #pragma unroll
-        for (int k = 0; k < RG_TILE_PIX / 32; k++) {
-            const int e = k * 32 + lane;
-            bool keep = false;
-            if (e < n && pos0 - e < wmax) keep = cull_keep(s_cull[e], s_xy[e], s_co[e], blk_x0, blk_y0, blk_x1, blk_y1);
-            const unsigned m = __ballot_sync(0xffffffffu, keep);
-            if (keep) s_list[warp][cnt + __popc(m & ((1u << lane) - 1))] = (uint8_t)e;
-            cnt += __popc(m);
-        }
-        __syncwarp();
-        for (int l = 0; l < cnt; l++) {
-            const int j = s_list[warp][l];
-            const int contributor = pos0 - j;
-            float v[kAcc];
-#pragma unroll
-            for (int k = 0; k < kAcc; k++) v[k] = 0.f;
-            bool active = false;
-            if (contributor < last_contributor) {
-                const float2 xy = s_xy[j];
-                const float2 d = {xy.x - pixf.x, xy.y - pixf.y};
-                const float4 con_o = s_co[j];
-                const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
-                if (power <= 0.0f && !(power < s_thr[j])) {
-                    const float G = expf(power);
-                    const float alpha = fminf(0.99f, con_o.w * G);
-                    if (alpha >= 1.0f / 255.0f) {
-                        active = true;
-                        T = T / (1.f - alpha);
-                        const float dchannel_dcolor = alpha * T;
-                        const float4 c = s_rgbd[j];
-                        const float col[3] = {c.x, c.y, c.z};
-                        float dL_dopa = 0.0f;
-#pragma unroll
-                        for (int ch = 0; ch < 3; ch++) {
-                            accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
-                            last_color[ch] = col[ch];
-                            dL_dopa += (col[ch] - accum_rec[ch]) * dL_dpixel[ch];
-                            v[6 + ch] = dchannel_dcolor * dL_dpixel[ch];
-                        }
-                        accum_depth_rec = last_alpha * last_depth + (1.f - last_alpha) * accum_depth_rec;
-                        last_depth = c.w;
-                        dL_dopa += (c.w - accum_depth_rec) * dL_dpixel_depth;
-                        v[9] = dchannel_dcolor * dL_dpixel_depth;
-                        accum_alpha_rec = last_alpha + (1.f - last_alpha) * accum_alpha_rec;
-                        dL_dopa += (1 - accum_alpha_rec) * dL_dalpha;
-                        dL_dopa *= T;
-                        last_alpha = alpha;
-                        dL_dopa += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
-                        const float dL_dG = con_o.w * dL_dopa;
-                        const float gdx = G * d.x;
-                        const float gdy = G * d.y;
-                        const float dG_ddelx = -gdx * con_o.x - gdy * con_o.y;
-                        const float dG_ddely = -gdy * con_o.z - gdx * con_o.y;
-                        v[0] = dL_dG * dG_ddelx * ddelx_dx;
-                        v[1] = dL_dG * dG_ddely * ddely_dy;
-                        v[2] = -0.5f * gdx * d.x * dL_dG;
-                        v[3] = -0.5f * gdx * d.y * dL_dG;
-                        v[4] = -0.5f * gdy * d.y * dL_dG;
-                        v[5] = G * dL_dopa;
-                    }
+            for (int u = 0; u < U; u++) {
+                e[u] = min(l + u, kGroup - 1);
+                const float4 x = st.xyts[e[u]];
+                // walk position k is range entry total-1-k; the pixel saw entries [0, last_contributor)
+                const int contributor = total - 1 - __float_as_int(x.w);
+                con_o[u] = st.co[e[u]];
+                d[u] = {x.x - pixf.x, x.y - pixf.y};
+                const float power =
+                    -0.5f * (con_o[u].x * d[u].x * d[u].x + con_o[u].z * d[u].y * d[u].y) - con_o[u].y * d[u].x * d[u].y;
+                active[u] = l + u < cnt && contributor < last_contributor && !(power > 0.0f) && !(power < x.z);
+                G[u] = 0.f;
+                alpha[u] = 0.f;
+                if (active[u]) {
+                    G[u] = expf(power);
+                    alpha[u] = fminf(0.99f, con_o[u].w * G[u]);
+                    active[u] = !(alpha[u] < 1.0f / 255.0f);
                 }
             }
-            if (__any_sync(0xffffffffu, active)) {
-                const float s = transpose_reduce10(v, lane);
-                if (my_id >= 0 && s != 0.f) atomicAdd(a.grad_acc + (size_t)s_id[j] * kAcc + my_id, s);
+            // serial part: the back-to-front recurrence
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+#pragma unroll
+                for (int k = 0; k < kAcc; k++) v[u][k] = 0.f;
+                if (active[u]) {
+                    T = T / (1.f - alpha[u]);
+                    const float dchannel_dcolor = alpha[u] * T;
+                    const float4 c = st.rgbd[e[u]];
+                    const float col[3] = {c.x, c.y, c.z};
+                    float dL_dopa = 0.0f;
+#pragma unroll
+                    for (int ch = 0; ch < 3; ch++) {
+                        accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
+                        last_color[ch] = col[ch];
+                        dL_dopa += (col[ch] - accum_rec[ch]) * dL_dpixel[ch];
+                        v[u][6 + ch] = dchannel_dcolor * dL_dpixel[ch];
+                    }
+                    accum_depth_rec = last_alpha * last_depth + (1.f - last_alpha) * accum_depth_rec;
+                    last_depth = c.w;
+                    dL_dopa += (c.w - accum_depth_rec) * dL_dpixel_depth;
+                    v[u][9] = dchannel_dcolor * dL_dpixel_depth;
+                    accum_alpha_rec = last_alpha + (1.f - last_alpha) * accum_alpha_rec;
+                    dL_dopa += (1 - accum_alpha_rec) * dL_dalpha;
+                    dL_dopa *= T;
+                    last_alpha = alpha[u];
+                    dL_dopa += (-T_final / (1.f - alpha[u])) * bg_dot_dpixel;
+                    const float dL_dG = con_o[u].w * dL_dopa;
+                    const float gdx = G[u] * d[u].x;
+                    const float gdy = G[u] * d[u].y;
+                    const float dG_ddelx = -gdx * con_o[u].x - gdy * con_o[u].y;
+                    const float dG_ddely = -gdy * con_o[u].z - gdx * con_o[u].y;
+                    v[u][0] = dL_dG * dG_ddelx * ddelx_dx;
+                    v[u][1] = dL_dG * dG_ddely * ddely_dy;
+                    v[u][2] = -0.5f * gdx * d[u].x * dL_dG;
+                    v[u][3] = -0.5f * gdx * d[u].y * dL_dG;
+                    v[u][4] = -0.5f * gdy * d[u].y * dL_dG;
+                    v[u][5] = G[u] * dL_dopa;
+                }
+            }
+            // one 10-lane reduction per (block, instance)
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                if (__any_sync(0xffffffffu, active[u])) {
+                    if (prof) n_red++;
+                    const float s = transpose_reduce10(v[u], lane);
+                    if (my_id >= 0 && s != 0.f) atomicAdd(a.grad_acc + (size_t)st.id[e[u]] * kAcc + my_id, s);
+                }
             }
         }
+    }
+    if (prof && lane == 0) {
+        uint32_t* o = prof + ((size_t)(tile_y * a.grid_x + tile_x) * 8 + strip * 2 + warp) * 8;
+        o[0] = (uint32_t)(clock64() - t_start); o[1] = (uint32_t)walk.t_wait; o[2] = (uint32_t)walk.t_stage1; o[3] = (uint32_t)walk.t_stage2; o[4] = n_list; o[5] = n_groups; o[6] = n_red; o[7] = 0;
     }
 }
 
 int launch_blend_backward(const BlendBwdArgs& a, cudaStream_t stream) {
-    dim3 grid(a.grid_x, a.grid_y, 1);
+    const dim3 grid((unsigned)(a.grid_x * a.grid_y * 4), 1, 1);
     LaunchScope ls("blend_backward", stream);
-    blend_backward_kernel<<<grid, RG_TILE_PIX, 0, stream>>>(a);
+    blend_backward_kernel<<<grid, kBlendWarps * 32, 0, stream>>>(a);
     return 0;
 }
 

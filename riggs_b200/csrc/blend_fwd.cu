@@ -1,119 +1,100 @@
-// Forward alpha blend: one CTA per 16x16 tile, front-to-back over the tile's depth-sorted instance range.
-// Replaces renderCUDA (dgr/cuda_rasterizer/forward.cu:261-381).
+// Forward alpha blend.  Replaces renderCUDA (dgr/cuda_rasterizer/forward.cu:261-381).
 //
-// Differences in HOW (results are the same, see cull.cuh for the argument):
-//  * a warp owns an 8x4 pixel block of the tile.  Every batch of 256 staged instances is first filtered per
-//    warp (ellipse-vs-block test, 8 instances per lane, ballot-compacted into a per-warp list in shared
-//    memory); the per-pixel loop then runs over that list only.  On the C0 workload this removes ~3/4 of
-//    the (pixel, instance) evaluations and lets warps whose pixels are saturated or outside the silhouette
-//    skim through long lists at the cost of the filter alone;
-//  * colour and depth of each staged instance are gathered once per tile into shared memory instead of
-//    being fetched from global memory per contributing pair;
-//  * survivors take the reference's exact expression (same power / alpha / T tests), after a conservative
-//    log-threshold pre-test that avoids expf for pairs that are certainly below 1/255.
-#include "common.cuh"
-#include "cull.cuh"
+// The reference runs one 256-thread CTA per 16x16 tile: all threads walk the tile's whole depth-sorted list in
+// lock step (two __syncthreads per 256 instances) and every pixel evaluates every instance.  On B200 that shape is
+// latency-bound: the few heavy tiles of a frame decide the kernel's duration while most SMs idle.  Here the unit of
+// work is ONE WARP = one 8x4 pixel block, independent of the other seven blocks of its tile -- no block barrier, a
+// finished warp retires and frees its slot:
+//   * blend_common.cuh's ListWalker hands the warp, 64 list entries at a time, the instances whose alpha >= 1/255
+//     footprint can reach the block (exact-conservative test of cull.cuh), gathered with a two-deep prefetch;
+//   * the 32 pixels blend only those, in list order, with the reference's exact expressions (same power / alpha / T
+//     tests; a log-threshold pre-test avoids expf for pairs that are certainly below 1/255).  Four survivors are
+//     evaluated per iteration: their alphas are independent, only the short T / colour update is serial, so the
+//     expf latencies overlap instead of adding up;
+//   * the warp stops as soon as its 32 pixels are saturated (T < 1e-4) or the list ends.
+// Every warp re-reads the tile's list (8x the L2 reads of a cooperative staging; one frame's records fit in L2 several
+// times over) -- L2 bandwidth is plentiful here, latency and balance are not.
+#include "blend_common.cuh"
 #include "kernels.cuh"
 
 namespace rg {
 
-constexpr float kSkipMargin = 1e-4f;
+// Optional per-(tile, warp) cycle counters for performance analysis (rg_debug_tile_profile); null in production.
+__device__ uint32_t* g_fwd_tile_prof = nullptr;
+void set_fwd_tile_profile(uint32_t* p) { cudaMemcpyToSymbol(g_fwd_tile_prof, &p, sizeof(p)); }
 
-__global__ void __launch_bounds__(RG_TILE_PIX) blend_forward_kernel(BlendFwdArgs a) {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    // warp -> 8x4 block: 2 blocks across, 4 down
-    const int bx0 = (warp & 1) * kBlkW, by0 = (warp >> 1) * kBlkH;
-    const uint2 pix = {blockIdx.x * RG_TILE + bx0 + (lane & 7), blockIdx.y * RG_TILE + by0 + (lane >> 3)};
+__global__ void __launch_bounds__(kBlendWarps * 32) blend_forward_kernel(BlendFwdArgs a) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tile = (int)a.tile_order[blockIdx.x >> 2], strip = blockIdx.x & 3;
+    const int tile_x = tile % a.grid_x, tile_y = tile / a.grid_x;
+    const int bx0 = warp * kBlkW, by0 = strip * kBlkH;
+    const uint2 pix = {(unsigned)(tile_x * RG_TILE + bx0 + (lane & 7)), (unsigned)(tile_y * RG_TILE + by0 + (lane >> 3))};
     const uint32_t pix_id = a.W * pix.y + pix.x;
     const float2 pixf = {(float)pix.x, (float)pix.y};
     const bool inside = pix.x < (unsigned)a.W && pix.y < (unsigned)a.H;
     bool done = !inside;
-    const float tile_x0 = (float)(blockIdx.x * RG_TILE), tile_y0 = (float)(blockIdx.y * RG_TILE);
-    const float blk_x0 = tile_x0 + bx0, blk_y0 = tile_y0 + by0;
-    const float blk_x1 = blk_x0 + (kBlkW - 1), blk_y1 = blk_y0 + (kBlkH - 1);
+    const uint2 range = a.ranges[tile_y * a.grid_x + tile_x];
 
-    const uint2 range = a.ranges[blockIdx.y * a.grid_x + blockIdx.x];
-    const int rounds = ((range.y - range.x + RG_TILE_PIX - 1) / RG_TILE_PIX);
-    int toDo = range.y - range.x;
-
-    __shared__ float2 s_xy[RG_TILE_PIX];
-    __shared__ float4 s_co[RG_TILE_PIX];
-    __shared__ float4 s_rgbd[RG_TILE_PIX];
-    __shared__ float s_thr[RG_TILE_PIX];
-    __shared__ CullRec s_cull[RG_TILE_PIX];
-    __shared__ uint8_t s_list[8][RG_TILE_PIX];
+    __shared__ WarpStage s_stage[kBlendWarps];
+    WarpStage& st = s_stage[warp];
+    ListWalker<false> walk;
+    walk.pl = a.point_list; walk.rec = a.rec; walk.first = range.x; walk.n = (int)(range.y - range.x); walk.lane = lane;
+    walk.x0 = (float)(tile_x * RG_TILE + bx0); walk.y0 = (float)(tile_y * RG_TILE + by0);
+    walk.x1 = walk.x0 + (kBlkW - 1); walk.y1 = walk.y0 + (kBlkH - 1);
+    const int n_groups = (walk.n + kGroup - 1) / kGroup;
 
     float T = 1.0f;
     uint32_t last_contributor = 0;
     float C0 = 0.f, C1 = 0.f, C2 = 0.f, weight = 0.f, D = 0.f;
+    uint32_t* const prof = g_fwd_tile_prof;
+    long long t_start = 0;
+    uint32_t n_list = 0, n_seen = 0;
+    if (prof) { t_start = clock64(); walk.timing = true; }
 
-    // Software pipeline: the gathers of batch i+1 (id -> xy, conic, colour, depth: two dependent trips to L2/HBM) are
-    // issued right after batch i has been published to shared memory and complete while the warps filter and blend
-    // batch i.  On tiles whose pixels never saturate the per-batch latency is the kernel's critical path.
-    float2 n_xy = {0.f, 0.f};
-    float4 n_co = {0.f, 0.f, 0.f, 0.f}, n_rgbd = {0.f, 0.f, 0.f, 0.f};
-    auto fetch = [&](int batch) {
-        const uint32_t pos = range.x + (uint32_t)batch * RG_TILE_PIX + tid;
-        if (pos < range.y) {
-            const uint32_t id = a.point_list[pos];
-            n_xy = a.means2D[id];
-            n_co = a.conic_opacity[id];
-            n_rgbd = {a.colors[3 * id], a.colors[3 * id + 1], a.colors[3 * id + 2], a.depths[id]};
-        }
-    };
-    if (rounds > 0) fetch(0);
-    for (int i = 0; i < rounds; i++, toDo -= RG_TILE_PIX) {
-        int num_done = __syncthreads_count(done);
-        if (num_done == RG_TILE_PIX) break;
-        const int progress = i * RG_TILE_PIX + tid;
-        if (range.x + progress < range.y) {
-            s_xy[tid] = n_xy;
-            s_co[tid] = n_co;
-            s_rgbd[tid] = n_rgbd;
-            s_thr[tid] = -logf(255.0f * n_co.w) - kSkipMargin;  // alpha < 1/255  <=>  power < -log(255 o)
-            s_cull[tid] = make_cull(n_xy, n_co, tile_x0, tile_y0);
-        }
-        __syncthreads();
-        if (i + 1 < rounds) fetch(i + 1);
-        const int n = min(RG_TILE_PIX, toDo);
-        if (__all_sync(0xffffffffu, done)) continue;  // this warp's block is finished; keep helping with loads
-        // ---- per-warp filter: which of the n staged instances can reach this 8x4 block?
-        int cnt = 0;
+    if (n_groups > 0) walk.begin();
+    for (int g = 0; g < n_groups; g++) {
+        if (__all_sync(0xffffffffu, done)) break;
+        const int cnt = walk.next(g, st);
+        if (prof) { n_seen++; n_list += cnt; }
+        for (int l = 0; l < cnt; l += 4) {
+            if (done) break;
+            float alpha[4];
+            bool act[4];
 #pragma unroll
-        for (int k = 0; k < RG_TILE_PIX / 32; k++) {
-            const int e = k * 32 + lane;
-            bool keep = false;
-            if (e < n) keep = cull_keep(s_cull[e], s_xy[e], s_co[e], blk_x0, blk_y0, blk_x1, blk_y1);
-            const unsigned m = __ballot_sync(0xffffffffu, keep);
-            if (keep) s_list[warp][cnt + __popc(m & ((1u << lane) - 1))] = (uint8_t)e;
-            cnt += __popc(m);
-        }
-        __syncwarp();
-        // ---- per-pixel blend over the surviving instances, in list (= depth) order
-        const uint32_t base = (uint32_t)i * RG_TILE_PIX;
-        for (int l = 0; !done && l < cnt; l++) {
-            const int j = s_list[warp][l];
-            const float2 xy = s_xy[j];
-            const float2 d = {xy.x - pixf.x, xy.y - pixf.y};
-            const float4 con_o = s_co[j];
-            const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
-            if (power > 0.0f) continue;
-            if (power < s_thr[j]) continue;  // certainly alpha < 1/255
-            const float alpha = fminf(0.99f, con_o.w * expf(power));
-            if (alpha < 1.0f / 255.0f) continue;
-            const float test_T = T * (1 - alpha);
-            if (test_T < 0.0001f) {
-                done = true;
-                continue;
+            for (int u = 0; u < 4; u++) {
+                const int e = min(l + u, kGroup - 1);
+                const float4 x = st.xyts[e];
+                const float4 con_o = st.co[e];
+                const float2 d = {x.x - pixf.x, x.y - pixf.y};
+                const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
+                // the reference skips power > 0 and alpha < 1/255; power < thr is certainly alpha < 1/255
+                act[u] = l + u < cnt && !(power > 0.0f) && !(power < x.z);
+                alpha[u] = 0.f;
+                if (act[u]) {
+                    alpha[u] = fminf(0.99f, con_o.w * expf(power));
+                    act[u] = !(alpha[u] < 1.0f / 255.0f);
+                }
             }
-            const float4 c = s_rgbd[j];
-            C0 += c.x * alpha * T;
-            C1 += c.y * alpha * T;
-            C2 += c.z * alpha * T;
-            weight += alpha * T;
-            D += c.w * alpha * T;
-            T = test_T;
-            last_contributor = base + j + 1;  // 1-based position in the tile's range, as the reference counts
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                if (act[u] && !done) {
+                    const float test_T = T * (1 - alpha[u]);
+                    if (test_T < 0.0001f) {
+                        done = true;
+                    } else {
+                        const int e = min(l + u, kGroup - 1);
+                        const float4 c = st.rgbd[e];
+                        C0 += c.x * alpha[u] * T;
+                        C1 += c.y * alpha[u] * T;
+                        C2 += c.z * alpha[u] * T;
+                        weight += alpha[u] * T;
+                        D += c.w * alpha[u] * T;
+                        T = test_T;
+                        // 1-based position in the tile's range, as the reference counts
+                        last_contributor = (uint32_t)__float_as_int(st.xyts[e].w) + 1;
+                    }
+                }
+            }
         }
     }
     if (inside) {
@@ -125,12 +106,16 @@ __global__ void __launch_bounds__(RG_TILE_PIX) blend_forward_kernel(BlendFwdArgs
         a.out_alpha[pix_id] = weight;  // sum of alpha*T, as the reference (forward.cu:378)
         a.out_depth[pix_id] = D;
     }
+    if (prof && lane == 0) {
+        uint32_t* o = prof + ((size_t)(tile_y * a.grid_x + tile_x) * 8 + strip * 2 + warp) * 8;
+        o[0] = (uint32_t)(clock64() - t_start); o[1] = (uint32_t)walk.t_wait; o[2] = (uint32_t)walk.t_stage1; o[3] = (uint32_t)walk.t_stage2; o[4] = n_list; o[5] = n_seen; o[6] = walk.n; o[7] = 0;
+    }
 }
 
 int launch_blend_forward(const BlendFwdArgs& a, cudaStream_t stream) {
-    dim3 grid(a.grid_x, a.grid_y, 1);
+    const dim3 grid((unsigned)(a.grid_x * a.grid_y * 4), 1, 1);
     LaunchScope ls("blend_forward", stream);
-    blend_forward_kernel<<<grid, RG_TILE_PIX, 0, stream>>>(a);
+    blend_forward_kernel<<<grid, kBlendWarps * 32, 0, stream>>>(a);
     return 0;
 }
 

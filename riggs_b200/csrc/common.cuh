@@ -51,7 +51,7 @@ struct GeomState {
     uint8_t* clamped;         // P, bit c set when colour channel c was clamped at 0
     float2* means2D;          // P
     float4* conic_opacity;    // P
-    float* rgb;               // 3P
+    float4* rec;              // 4P: 64-byte splat record read by the blend kernels (cull.cuh: SplatRec layout)
     uint32_t* tiles_touched;  // P
     float* means3D;           // 3P, skinned positions kept by the fused entry point
     uint32_t* ids;            // P iota
@@ -63,6 +63,7 @@ struct GeomState {
     uint32_t* E;              // NW x T first slot per (chunk, tile)
     uint32_t* S;              // nseg x T
     uint32_t* tile_base;      // T
+    uint32_t* tile_order;     // T tile indices, longest instance lists first: launch order of the blend kernels
     uint32_t* status;         // [0] num_rendered, [1] overflow flag
     float* grad_acc;          // 10P floats: per-Gaussian 2-D gradient accumulators of the backward blend
     float* d_rot;             // 4P blended bone quaternion * mask (fused entry, kept for the backward)

@@ -2,17 +2,30 @@
 //
 // The reference evaluates every (pixel, instance) pair of a tile and discards the pair when
 // alpha = min(0.99, o * exp(power)) < 1/255 (forward.cu:339-349).  alpha >= 1/255 needs
-// q(d) = -power = 0.5 (A dx^2 + C dy^2) + B dx dy <= log(255 o), i.e. the pixel lies inside an ellipse
-// around the splat centre.  The blend kernels therefore split each 16x16 tile into eight 8x4 pixel blocks
-// (one warp each) and give a warp only the instances whose ellipse can reach its block:
+// q(d) = -power = 0.5 (A dx^2 + C dy^2) + B dx dy <= L = log(255 o), i.e. the pixel lies inside an ellipse around
+// the splat centre.  The blend kernels give each warp an 8x4 pixel block and let it skip every instance whose
+// ellipse cannot reach the block:
 //   stage 1  axis-aligned bounding box of the ellipse against the block rectangle (4 compares);
-//   stage 2  exact minimum of q over the block rectangle (q is convex: 0 if the centre is inside, else
-//            the smallest of the four edge minima).
-// Both stages test against log(255 o) + slack, where slack over-covers every rounding error that the
-// reference's float evaluation of `power`, expf and this file's own arithmetic can have on the tile
-// (4e-7 * sum of the magnitudes of the three products, bounded over the whole tile, + 1e-4).  A pair that
-// survives is then evaluated with the reference's exact expression, so the blended result, n_contrib and
-// every gradient are those of the reference; a pair that is dropped would have been discarded there too.
+//   stage 2  exact minimum of q over the block rectangle (q is convex: 0 if the centre is inside, else the
+//            smallest of the four edge minima).
+// Both stages test against an inflated level Lq >= L that over-covers every rounding error on the way:
+//   * the reference's float evaluation of `power` is off by at most ~4e-7 * S, S = sum of the magnitudes of its three
+//     products; with u = sqrt(A)|dx|, v = sqrt(C)|dy|, rho = B / sqrt(AC):
+//     q >= (1 - |rho|) (u^2 + v^2)/2 and S <= (1 + |rho|) (u^2 + v^2)/2, hence S <= kappa * q, kappa = (1+|rho|)/(1-|rho|);
+//   * a pixel is dropped only if q > Lq = (L + 1e-4) / (1 - 1e-6 kappa), which implies q - 4e-7 S > L + 1e-4: the
+//     reference's own float `power` is then below -L by a margin (1e-4) far above the error of expf / logf, so the
+//     reference discards that pair too;
+//   * kappa so large that 1e-6 kappa >= 0.5 (degenerate conics) switches the culling off for that Gaussian.
+// A pair that survives is evaluated with the reference's exact expression, so blended values, n_contrib and all
+// gradients are those of the reference; a dropped pair would have been discarded there as well.
+//
+// The per-Gaussian part is computed once in the preprocess kernel and stored with everything else the blend kernels
+// need about a splat in ONE 64-byte record (two 32-byte sectors, four 16-byte loads):
+//   rec[0] = {x, y, hx, hy}     pixel centre, half extents of the keep region    -> stage 1
+//   rec[1] = {A, B, C, o}       conic, opacity                                   -> stage 2 + blend
+//   rec[2] = {r, g, b, depth}                                                    -> blend
+//   rec[3] = {Lq, thr, 0, 0}    inflated level; thr = -L - 1e-4 is the per-pixel pre-test that avoids expf
+// hx = hy = -3e38 marks "cannot be seen at all" (o <= 1/255), hx = Lq = +3e38 "never cull".
 #pragma once
 #include <cuda_runtime.h>
 
@@ -20,61 +33,62 @@ namespace rg {
 
 constexpr int kBlkW = 8, kBlkH = 4;  // pixel block of one warp
 
-struct CullRec {     // per staged instance
-    float4 bb;       // xmin, xmax, ymin, ymax of the keep region (empty when xmin > xmax)
-    float4 q;        // Lq (level incl. slack), -B/C, -B/A, flag (1 = exact stage usable)
-};
-
-// Built once per (tile, instance) by the staging thread.  tile_x0/y0: first pixel of the tile.
-__device__ __forceinline__ CullRec make_cull(float2 xy, float4 co, float tile_x0, float tile_y0) {
-    CullRec r;
-    const float A = co.x, B = co.y, C = co.z, o = co.w;
-    const float det = A * C - B * B;
+__device__ __forceinline__ void write_splat_rec(float4* rec, float2 xy, float3 conic, float o, float3 color, float depth) {
+    const float A = conic.x, B = conic.y, C = conic.z;
     const float big = 3.0e38f;
-    if (!(o > 0.f)) {  // alpha <= 0 < 1/255 for every pixel (NaN opacity falls through to "keep")
-        if (o <= 0.f) { r.bb = {1.f, 0.f, 1.f, 0.f}; r.q = {0.f, 0.f, 0.f, 0.f}; return r; }
+    float hx, hy, Lq, thr;
+    const float L = logf(255.0f * o);
+    const float det = A * C - B * B;
+    thr = -L - 1e-4f;
+    if (o <= 0.f) {  // alpha <= 0 everywhere (a NaN opacity falls through to "never cull")
+        hx = hy = -big; Lq = 0.f; thr = big;
+    } else if (!(A > 0.f && C > 0.f && det > 0.f) || !(L == L)) {
+        hx = hy = Lq = big;
+    } else if (L < -1e-3f) {  // o < 1/255: no pixel reaches alpha >= 1/255
+        hx = hy = -big; Lq = 0.f;
+    } else {
+        const float rho = fminf(fabsf(B) * rsqrtf(A * C), 1.0f);
+        const float kappa = (1.f + rho) / fmaxf(1.f - rho, 1e-12f);
+        if (!(1e-6f * kappa < 0.5f)) {
+            hx = hy = Lq = big;
+        } else {
+            Lq = (fmaxf(L, 0.f) + 1e-4f) / (1.f - 1e-6f * kappa) * 1.00001f;
+            const float inv = 1.0f / det;
+            hx = sqrtf(2.f * Lq * C * inv) * 1.0001f + 1e-3f;
+            hy = sqrtf(2.f * Lq * A * inv) * 1.0001f + 1e-3f;
+        }
     }
-    const float L = logf(255.0f * o);  // alpha >= 1/255  <=>  q <= L
-    // bound of |0.5 A dx^2| + |0.5 C dy^2| + |B dx dy| over the tile
-    const float dxm = fmaxf(fabsf(xy.x - tile_x0), fabsf(xy.x - (tile_x0 + 15.f)));
-    const float dym = fmaxf(fabsf(xy.y - tile_y0), fabsf(xy.y - (tile_y0 + 15.f)));
-    const float S = 0.5f * (fabsf(A) * dxm * dxm + fabsf(C) * dym * dym) + fabsf(B) * dxm * dym;
-    const float Lq = L + 1e-4f + 1e-6f * S + 1e-6f * fabsf(L);
-    if (!(A > 0.f && C > 0.f && det > 0.f) || !(Lq == Lq) || Lq > 1e30f) {  // not a proper ellipse: never cull
-        r.bb = {-big, big, -big, big};
-        r.q = {big, 0.f, 0.f, 0.f};
-        return r;
-    }
-    if (Lq < 0.f) {  // o < 1/255: no pixel can reach alpha >= 1/255
-        r.bb = {1.f, 0.f, 1.f, 0.f}; r.q = {0.f, 0.f, 0.f, 0.f};
-        return r;
-    }
-    const float inv = 1.0f / det;
-    const float hx = sqrtf(2.f * Lq * C * inv) * 1.0001f + 1e-3f;
-    const float hy = sqrtf(2.f * Lq * A * inv) * 1.0001f + 1e-3f;
-    r.bb = {xy.x - hx, xy.x + hx, xy.y - hy, xy.y + hy};
-    r.q = {Lq, -B / C, -B / A, 1.f};
-    return r;
+    rec[0] = {xy.x, xy.y, hx, hy};
+    rec[1] = {A, B, C, o};
+    rec[2] = {color.x, color.y, color.z, depth};
+    rec[3] = {Lq, thr, 0.f, 0.f};
 }
 
-// True when the instance may contribute to some pixel of the block [x0, x0+w-1] x [y0, y0+h-1].
-__device__ __forceinline__ bool cull_keep(const CullRec& r, float2 xy, float4 co, float x0, float y0, float x1, float y1) {
-    if (r.bb.y < x0 || r.bb.x > x1 || r.bb.w < y0 || r.bb.z > y1) return false;
-    if (r.q.w == 0.f) return true;
-    const float dxlo = xy.x - x1, dxhi = xy.x - x0, dylo = xy.y - y1, dyhi = xy.y - y0;
+// Stage 1: can the keep region's bounding box touch the block [x0, x1] x [y0, y1] (pixel-centre coordinates)?
+__device__ __forceinline__ bool cull_aabb(float4 r0, float x0, float y0, float x1, float y1) {
+    return !(r0.x + r0.z < x0 || r0.x - r0.z > x1 || r0.y + r0.w < y0 || r0.y - r0.w > y1);
+}
+
+// Stage 2: true when the instance may contribute to some pixel of the block.
+__device__ __forceinline__ bool cull_exact(float4 r0, float4 co, float Lq, float x0, float y0, float x1, float y1) {
+    if (Lq > 1e37f) return true;
+    const float dxlo = r0.x - x1, dxhi = r0.x - x0, dylo = r0.y - y1, dyhi = r0.y - y0;
     if (dxlo <= 0.f && dxhi >= 0.f && dylo <= 0.f && dyhi >= 0.f) return true;  // centre inside the block
     const float A = co.x, B = co.y, C = co.z;
+    const float rBC = -B / C, rBA = -B / A;
     float qmin = 3.0e38f;
 #pragma unroll
     for (int e = 0; e < 2; e++) {
         const float dx = e ? dxhi : dxlo;
-        const float dy = fminf(fmaxf(r.q.y * dx, dylo), dyhi);
+        const float dy = fminf(fmaxf(rBC * dx, dylo), dyhi);
         qmin = fminf(qmin, 0.5f * (A * dx * dx + C * dy * dy) + B * dx * dy);
         const float ey = e ? dyhi : dylo;
-        const float ex = fminf(fmaxf(r.q.z * ey, dxlo), dxhi);
+        const float ex = fminf(fmaxf(rBA * ey, dxlo), dxhi);
         qmin = fminf(qmin, 0.5f * (A * ex * ex + C * ey * ey) + B * ex * ey);
     }
-    return qmin <= r.q.x;
+    // this file's own rounding in qmin is covered by the same kappa argument (relative 1e-6 kappa) plus the factor
+    // 1.00001 folded into Lq
+    return qmin <= Lq;
 }
 
 }  // namespace rg

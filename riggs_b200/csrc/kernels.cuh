@@ -28,7 +28,7 @@ struct PreprocessArgs {
     float2* means2D;
     float* depths;
     float* cov3D_out;  // may be null
-    float* rgb;
+    float4* rec;  // 4 x float4 per Gaussian: the packed splat record of cull.cuh, all the blend kernels read
     float4* conic_opacity;
     uint32_t* tiles_touched;
     uint8_t* clamped;
@@ -100,9 +100,9 @@ int launch_depth_sort(char* temp, size_t temp_bytes, const float* depths, uint32
 int launch_tile_count(const BinPlan& b, int P, int grid_x, int grid_y, const uint32_t* sorted_ids,
                       const uint32_t* tiles_touched, const float2* means2D, const int* radii, uint16_t* M,
                       cudaStream_t stream);
-// segment sums + tile bases + ranges + status[0] = num_rendered, status[1] = overflow flag
+// segment sums + tile bases + ranges + tile launch order (longest lists first) + status[0] = num_rendered, status[1] = overflow flag
 int launch_tile_offsets_a(const BinPlan& b, const uint16_t* M, uint32_t* S, uint32_t* tile_base, uint2* ranges,
-                          uint32_t* status, uint32_t capacity, cudaStream_t stream);
+                          uint32_t* tile_order, uint32_t* status, uint32_t capacity, cudaStream_t stream);
 int launch_tile_scatter(const BinPlan& b, int P, int grid_x, int grid_y, const uint32_t* sorted_ids,
                         const uint32_t* tiles_touched, const float2* means2D, const int* radii, const uint16_t* M,
                         const uint32_t* S, const uint32_t* tile_base, uint32_t* E, uint32_t* point_list,
@@ -114,10 +114,8 @@ struct BlendFwdArgs {
     int W, H, grid_x, grid_y;
     const uint2* ranges;
     const uint32_t* point_list;
-    const float2* means2D;
-    const float* colors;  // 3 per Gaussian
-    const float* depths;
-    const float4* conic_opacity;
+    const float4* rec;  // packed splat records (cull.cuh)
+    const uint32_t* tile_order;
     const float* bg;
     float* out_color;
     float* out_depth;
@@ -131,10 +129,8 @@ struct BlendBwdArgs {
     const uint2* ranges;
     const uint32_t* point_list;
     const float* bg;
-    const float2* means2D;
-    const float4* conic_opacity;
-    const float* colors;
-    const float* depths;
+    const float4* rec;
+    const uint32_t* tile_order;
     const float* alphas;
     const uint32_t* n_contrib;
     const float* dL_dpix;

@@ -19,6 +19,7 @@
 #include "bones.cuh"
 #include "bulk_copy.cuh"
 #include "common.cuh"
+#include "cull.cuh"
 #include "kernels.cuh"
 #include "math.cuh"
 #include "sh.cuh"
@@ -173,9 +174,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(PreprocessArgs a, SkinF
             color = {a.colors_precomp[3 * i], a.colors_precomp[3 * i + 1], a.colors_precomp[3 * i + 2]};
         }
         a.clamped[idx] = clamp_bits;
-        a.rgb[3 * i] = color.x;
-        a.rgb[3 * i + 1] = color.y;
-        a.rgb[3 * i + 2] = color.z;
+        write_splat_rec(a.rec + 4 * (size_t)idx, point_image, conic, opacity, color, p_view.z);
         a.depths[idx] = p_view.z;
         radius_out = (int)my_radius;
         a.means2D[idx] = point_image;

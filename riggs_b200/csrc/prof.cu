@@ -47,9 +47,20 @@ LaunchScope::~LaunchScope() {
 
 }  // namespace rg
 
+namespace rg {
+void set_fwd_tile_profile(uint32_t* p);
+void set_bwd_tile_profile(uint32_t* p);
+}
+
 using namespace rg;
 
 extern "C" {
+
+int rg_debug_tile_profile(uint32_t* fwd, uint32_t* bwd) {
+    set_fwd_tile_profile(fwd);
+    set_bwd_tile_profile(bwd);
+    return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
 
 long long rg_launch_count(void) { return g_launches.load(); }
 

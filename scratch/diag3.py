@@ -20,7 +20,7 @@ ptrs = _C.state_ptrs(P, R, W, H, ws.geom, ws.binning, ws.image)
 means_f = helpers._slice(ws.geom, ptrs[7], 12 * P, torch.float32).reshape(P, 3).clone()
 def geomarrays(geom, ptrs):
     return dict(depths=helpers._slice(geom, ptrs[0], 4*P, torch.float32).clone(), means2D=helpers._slice(geom, ptrs[2], 8*P, torch.float32).clone(),
-                conic=helpers._slice(geom, ptrs[3], 16*P, torch.float32).clone(), rgb=helpers._slice(geom, ptrs[4], 12*P, torch.float32).clone())
+                conic=helpers._slice(geom, ptrs[3], 16*P, torch.float32).clone(), rgb=None)
 A = geomarrays(ws.geom, ptrs)
 shs = torch.cat([pc._features_dc, pc._features_rest], 1).detach().contiguous()
 e = torch.empty(0)

@@ -86,7 +86,7 @@ def ours_forward(cin):
     st["clamped_bits"] = _slice(geom, ptrs[1], P, torch.uint8).cpu().numpy()
     st["means2D"] = _slice(geom, ptrs[2], 8 * P, torch.float32).cpu().numpy().reshape(P, 2)
     st["conic_opacity"] = _slice(geom, ptrs[3], 16 * P, torch.float32).cpu().numpy().reshape(P, 4)
-    st["rgb"] = _slice(geom, ptrs[4], 12 * P, torch.float32).cpu().numpy().reshape(P, 3)
+    st["rgb"] = _slice(geom, ptrs[4], 64 * P, torch.float32).cpu().numpy().reshape(P, 16)[:, 8:11].copy()
     st["tiles_touched"] = _slice(geom, ptrs[5], 4 * P, torch.int32).cpu().numpy().view(np.uint32)
     st["sorted_ids"] = _slice(geom, ptrs[6], 4 * P, torch.int32).cpu().numpy().view(np.uint32)
     if R > 0:
