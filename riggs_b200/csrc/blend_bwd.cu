@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendB
     walk.x0 = (float)(tile_x * RG_TILE + bx0); walk.y0 = (float)(tile_y * RG_TILE + by0);
     walk.x1 = walk.x0 + (kBlkW - 1); walk.y1 = walk.y0 + (kBlkH - 1);
     const int n_groups = (total + kGroup - 1) / kGroup;
-    walk.begin();
+    walk.begin(st);
 
     const float T_final = inside ? (1 - a.alphas[pix_id]) : 0;
     float T = T_final;

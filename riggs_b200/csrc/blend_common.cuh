@@ -4,12 +4,13 @@
 // The walk is software-pipelined so that the dependent chain  list entry -> record  (two trips to L2) never sits on
 // the warp's critical path -- the heavy tiles of a frame are walked by a handful of warps whose latency IS the
 // kernel's duration:
-//   iteration g   ids of group g+2 requested (coalesced)            ) in flight while group g is filtered and the
-//                 rec[0] of group g+1 requested (ids came in at g-1) ) caller blends group g's survivors
-//   stage 1       bounding-box test on rec[0] of group g (registers), ballot-compacted into a candidate buffer
-//   stage 2       candidates are spread over the lanes; each lane fetches the rest of its candidate's record, runs
-//                 the exact ellipse-vs-rectangle test (cull.cuh) and the survivors are ballot-compacted, in list
-//                 order, into the buffer the caller's per-pixel loop reads.
+//   stage 1   bounding-box test on rec[0] of a group of 64 entries (two per lane, registers), ballot-compacted into
+//             a candidate buffer;
+//   stage 2   candidates are spread over the lanes; each lane fetches the rest of its candidate's record, runs the
+//             exact ellipse-vs-rectangle test (cull.cuh) and the survivors are ballot-compacted, in list order,
+//             into the buffer the caller's per-pixel loop reads.
+// While the caller blends the survivors of group g, these requests are in flight: stage-2 records of group g+1
+// (its stage 1 already ran), rec[0] of group g+2, list entries of group g+3.
 #pragma once
 #include "common.cuh"
 #include "cull.cuh"
@@ -38,11 +39,15 @@ struct ListWalker {
     uint32_t first;
     int n, lane;
     float x0, y0, x1, y1;
-    uint32_t id_next[2], id_after[2];
-    float4 r0_next[2];
     static constexpr uint32_t kNone = 0xffffffffu;
     bool timing = false;  // performance analysis only (rg_debug_tile_profile)
     long long t_wait = 0, t_stage1 = 0, t_stage2 = 0;
+
+    // pipeline registers
+    uint32_t id_1[2], id_2[2];  // list entries of the next two groups (the second possibly in flight)
+    float4 r0_1[2];             // rec[0] of the next group (possibly in flight)
+    int ncand;                           // candidates of the group whose stage 2 is pending
+    float4 p_co, p_rgbd, p_tail;         // this lane's pending stage-2 record (in flight)
 
     __device__ __forceinline__ uint32_t load_id(int k) const {
         return k < n ? pl[REVERSE ? first + (uint32_t)(n - 1 - k) : first + (uint32_t)k] : kNone;
@@ -50,61 +55,55 @@ struct ListWalker {
     __device__ __forceinline__ float4 load_r0(uint32_t id) const {
         return id != kNone ? rec[4 * (size_t)id] : float4{0.f, 0.f, -3.0e38f, -3.0e38f};
     }
-    __device__ __forceinline__ void begin() {
-#pragma unroll
-        for (int j = 0; j < 2; j++) id_next[j] = load_id(j * 32 + lane);
-#pragma unroll
-        for (int j = 0; j < 2; j++) id_after[j] = load_id(kGroup + j * 32 + lane);
-#pragma unroll
-        for (int j = 0; j < 2; j++) r0_next[j] = load_r0(id_next[j]);
-    }
-    // Filters group g (walk positions [64 g, 64 g + 64)) into st; returns the number of survivors.  Position k of
-    // the walk is list entry first + k (or first + n - 1 - k when REVERSE).
-    __device__ __forceinline__ int next(int g, WarpStage& st) {
-        uint32_t id_cur[2];
-        float4 r0[2];
-        long long tt = 0;
-        if (timing) tt = clock64();
-#pragma unroll
-        for (int j = 0; j < 2; j++) {
-            id_cur[j] = id_next[j];
-            r0[j] = r0_next[j];
-            id_next[j] = id_after[j];
-        }
-#pragma unroll
-        for (int j = 0; j < 2; j++) id_after[j] = load_id((g + 2) * kGroup + j * 32 + lane);
-#pragma unroll
-        for (int j = 0; j < 2; j++) r0_next[j] = load_r0(id_next[j]);
+    // stage 1 of one group: registers -> candidate buffer; then request the first 32 candidates' records
+    __device__ __forceinline__ void stage1(const uint32_t (&id)[2], const float4 (&r0)[2], WarpStage& st) {
         const unsigned lt = (1u << lane) - 1;
-        if (timing) {
-            // force the prefetched values to land so that the wait is attributed here
-            asm volatile("" ::"r"(id_cur[0]), "r"(id_cur[1]), "f"(r0[0].x), "f"(r0[1].x), "r"(id_next[0]), "r"(id_next[1]));
-            const long long t = clock64();
-            t_wait += t - tt;
-            tt = t;
-        }
-        // ---- stage 1
-        int ncand = 0;
+        ncand = 0;
 #pragma unroll
         for (int j = 0; j < 2; j++) {
-            const bool pass = id_cur[j] != kNone && cull_aabb(r0[j], x0, y0, x1, y1);
+            const bool pass = id[j] != kNone && cull_aabb(r0[j], x0, y0, x1, y1);
             const unsigned m = __ballot_sync(0xffffffffu, pass);
             if (pass) {
                 const int slot = ncand + __popc(m & lt);
                 st.cand_r0[slot] = r0[j];
-                st.cand_id[slot] = id_cur[j];
+                st.cand_id[slot] = id[j];
                 st.cand_k[slot] = (uint8_t)(j * 32 + lane);
             }
             ncand += __popc(m);
         }
-        if (timing) {
-            const long long t = clock64();
-            t_stage1 += t - tt;
-            tt = t;
-        }
-        if (ncand == 0) return 0;
         __syncwarp();
-        // ---- stage 2
+        if (lane < ncand) {
+            const float4* r = rec + 4 * (size_t)st.cand_id[lane];
+            p_co = r[1];
+            p_rgbd = r[2];
+            p_tail = r[3];
+        }
+    }
+    __device__ __forceinline__ void begin(WarpStage& st) {
+        uint32_t id_0[2];
+        float4 r0_0[2];
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+            id_0[j] = load_id(j * 32 + lane);
+            id_1[j] = load_id(kGroup + j * 32 + lane);
+            id_2[j] = load_id(2 * kGroup + j * 32 + lane);
+        }
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+            r0_0[j] = load_r0(id_0[j]);
+            r0_1[j] = load_r0(id_1[j]);
+        }
+        stage1(id_0, r0_0, st);
+    }
+    // Hands out group g (walk positions [64 g, 64 g + 64)): finishes its stage 2 into st and returns the number of
+    // survivors; runs stage 1 of group g+1 and issues the loads further down the list before returning.  Position k
+    // of the walk is list entry first + k (or first + n - 1 - k when REVERSE).
+    __device__ __forceinline__ int next(int g, WarpStage& st) {
+        const unsigned lt = (1u << lane) - 1;
+        long long tt = 0;
+        if (timing) tt = clock64();
+        __syncwarp();  // every lane is done reading the previous group's survivors
+        // ---- finish stage 2 of group g
         int nsurv = 0;
         for (int c0 = 0; c0 < ncand; c0 += 32) {
             const int c = c0 + lane;
@@ -116,11 +115,13 @@ struct ListWalker {
                 id = st.cand_id[c];
                 a = st.cand_r0[c];
                 k = st.cand_k[c];
-                const float4* r = rec + 4 * (size_t)id;
-                co = r[1];
-                rgbd = r[2];
-                tail = r[3];
-                keep = cull_exact(a, co, tail.x, x0, y0, x1, y1);
+                if (c0 == 0) {
+                    co = p_co; rgbd = p_rgbd; tail = p_tail;
+                } else {  // more than 32 candidates in one group: not pipelined
+                    const float4* r = rec + 4 * (size_t)id;
+                    co = r[1]; rgbd = r[2]; tail = r[3];
+                }
+                keep = cull_exact(a, co, tail, x0, y0, x1, y1);
             }
             const unsigned m = __ballot_sync(0xffffffffu, keep);
             if (keep) {
@@ -133,7 +134,30 @@ struct ListWalker {
             nsurv += __popc(m);
         }
         __syncwarp();
-        if (timing) t_stage2 += clock64() - tt;
+        if (timing) {
+            const long long t = clock64();
+            t_stage2 += t - tt;
+            tt = t;
+        }
+        // ---- stage 1 of group g+1, then the requests for g+1 (stage 2), g+2 (rec[0]) and g+3 (list entries)
+        if ((g + 1) * kGroup < n) {
+            if (timing) {
+                asm volatile("" ::"r"(id_1[0]), "r"(id_1[1]), "f"(r0_1[0].x), "f"(r0_1[1].x));
+                const long long t = clock64();
+                t_wait += t - tt;
+                tt = t;
+            }
+            stage1(id_1, r0_1, st);
+#pragma unroll
+            for (int j = 0; j < 2; j++) {
+                id_1[j] = id_2[j];
+                r0_1[j] = load_r0(id_2[j]);
+                id_2[j] = load_id((g + 3) * kGroup + j * 32 + lane);
+            }
+            if (timing) t_stage1 += clock64() - tt;
+        } else {
+            ncand = 0;
+        }
         return nsurv;
     }
 };

@@ -51,48 +51,53 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_forward_kernel(BlendFw
     uint32_t n_list = 0, n_seen = 0;
     if (prof) { t_start = clock64(); walk.timing = true; }
 
-    if (n_groups > 0) walk.begin();
+    if (n_groups > 0) walk.begin(st);
     for (int g = 0; g < n_groups; g++) {
         if (__all_sync(0xffffffffu, done)) break;
         const int cnt = walk.next(g, st);
         if (prof) { n_seen++; n_list += cnt; }
         for (int l = 0; l < cnt; l += 4) {
             if (done) break;
-            float alpha[4];
+            float alpha[4], power[4], opac[4];
+            float4 c[4];
+            int pos[4];
             bool act[4];
 #pragma unroll
             for (int u = 0; u < 4; u++) {
                 const int e = min(l + u, kGroup - 1);
                 const float4 x = st.xyts[e];
                 const float4 con_o = st.co[e];
+                c[u] = st.rgbd[e];
                 const float2 d = {x.x - pixf.x, x.y - pixf.y};
-                const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
+                power[u] = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
                 // the reference skips power > 0 and alpha < 1/255; power < thr is certainly alpha < 1/255
-                act[u] = l + u < cnt && !(power > 0.0f) && !(power < x.z);
-                alpha[u] = 0.f;
-                if (act[u]) {
-                    alpha[u] = fminf(0.99f, con_o.w * expf(power));
-                    act[u] = !(alpha[u] < 1.0f / 255.0f);
-                }
+                act[u] = l + u < cnt && !(power[u] > 0.0f) && !(power[u] < x.z);
+                opac[u] = con_o.w;
+                pos[u] = __float_as_int(x.w);
             }
+            if (act[0] | act[1] | act[2] | act[3]) {
+                // the four falloffs are independent: evaluated together so that their latencies overlap
 #pragma unroll
-            for (int u = 0; u < 4; u++) {
-                if (act[u] && !done) {
+                for (int u = 0; u < 4; u++) {
+                    alpha[u] = fminf(0.99f, opac[u] * expf(power[u]));
+                    act[u] = act[u] && !(alpha[u] < 1.0f / 255.0f);
+                }
+                // the only serial part: transmittance and the accumulators
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
                     const float test_T = T * (1 - alpha[u]);
-                    if (test_T < 0.0001f) {
-                        done = true;
-                    } else {
-                        const int e = min(l + u, kGroup - 1);
-                        const float4 c = st.rgbd[e];
-                        C0 += c.x * alpha[u] * T;
-                        C1 += c.y * alpha[u] * T;
-                        C2 += c.z * alpha[u] * T;
-                        weight += alpha[u] * T;
-                        D += c.w * alpha[u] * T;
-                        T = test_T;
-                        // 1-based position in the tile's range, as the reference counts
-                        last_contributor = (uint32_t)__float_as_int(st.xyts[e].w) + 1;
-                    }
+                    const bool live = act[u] && !done;
+                    const bool stop = live && test_T < 0.0001f;
+                    const bool add = live && !stop;
+                    done = done || stop;
+                    C0 = add ? C0 + c[u].x * alpha[u] * T : C0;
+                    C1 = add ? C1 + c[u].y * alpha[u] * T : C1;
+                    C2 = add ? C2 + c[u].z * alpha[u] * T : C2;
+                    weight = add ? weight + alpha[u] * T : weight;
+                    D = add ? D + c[u].w * alpha[u] * T : D;
+                    // 1-based position in the tile's range, as the reference counts
+                    last_contributor = add ? (uint32_t)pos[u] + 1 : last_contributor;
+                    T = add ? test_T : T;
                 }
             }
         }

@@ -24,7 +24,8 @@
 //   rec[0] = {x, y, hx, hy}     pixel centre, half extents of the keep region    -> stage 1
 //   rec[1] = {A, B, C, o}       conic, opacity                                   -> stage 2 + blend
 //   rec[2] = {r, g, b, depth}                                                    -> blend
-//   rec[3] = {Lq, thr, 0, 0}    inflated level; thr = -L - 1e-4 is the per-pixel pre-test that avoids expf
+//   rec[3] = {Lq, thr, -B/C, -B/A}  inflated level; thr = -L - 1e-4 is the per-pixel pre-test that avoids expf; the two
+//                                   slopes locate the minimum of q along a vertical / horizontal edge (stage 2)
 // hx = hy = -3e38 marks "cannot be seen at all" (o <= 1/255), hx = Lq = +3e38 "never cull".
 #pragma once
 #include <cuda_runtime.h>
@@ -61,7 +62,7 @@ __device__ __forceinline__ void write_splat_rec(float4* rec, float2 xy, float3 c
     rec[0] = {xy.x, xy.y, hx, hy};
     rec[1] = {A, B, C, o};
     rec[2] = {color.x, color.y, color.z, depth};
-    rec[3] = {Lq, thr, 0.f, 0.f};
+    rec[3] = {Lq, thr, -B / C, -B / A};
 }
 
 // Stage 1: can the keep region's bounding box touch the block [x0, x1] x [y0, y1] (pixel-centre coordinates)?
@@ -70,12 +71,13 @@ __device__ __forceinline__ bool cull_aabb(float4 r0, float x0, float y0, float x
 }
 
 // Stage 2: true when the instance may contribute to some pixel of the block.
-__device__ __forceinline__ bool cull_exact(float4 r0, float4 co, float Lq, float x0, float y0, float x1, float y1) {
+__device__ __forceinline__ bool cull_exact(float4 r0, float4 co, float4 r3, float x0, float y0, float x1, float y1) {
+    const float Lq = r3.x;
     if (Lq > 1e37f) return true;
     const float dxlo = r0.x - x1, dxhi = r0.x - x0, dylo = r0.y - y1, dyhi = r0.y - y0;
     if (dxlo <= 0.f && dxhi >= 0.f && dylo <= 0.f && dyhi >= 0.f) return true;  // centre inside the block
     const float A = co.x, B = co.y, C = co.z;
-    const float rBC = -B / C, rBA = -B / A;
+    const float rBC = r3.z, rBA = r3.w;
     float qmin = 3.0e38f;
 #pragma unroll
     for (int e = 0; e < 2; e++) {
