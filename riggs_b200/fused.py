@@ -128,9 +128,13 @@ class _SkinnedRender(torch.autograd.Function):
         L = _lib.lib()
         pool = cfg.get("pool") or _POOL
         ws, fresh = pool.acquire(P, W, H, dev)
+        capturing = torch.cuda.is_current_stream_capturing()
+        if capturing and fresh:
+            raise _lib.RiggsError("render_skinned under CUDA-graph capture needs a workspace sized by an eager call "
+                                  "of the same shape first")
         with torch.cuda.device(dev):
             # late check of the previous frame that used this workspace
-            if ws.status_event is not None and ws.status_event.query() and int(ws.status[1]) != 0:
+            if not capturing and ws.status_event is not None and ws.status_event.query() and int(ws.status[1]) != 0:
                 import warnings
                 warnings.warn("riggs_b200: the previous frame overflowed the instance buffer and was rendered "
                               "incompletely; growing the buffer")
@@ -143,6 +147,9 @@ class _SkinnedRender(torch.autograd.Function):
                                            ptr(dbg["opacities"]) if dbg else None, stream_ptr()), "rg_skinned_forward")
                 check(L.rg_skinned_status(C.byref(scene), C.byref(ws.c), ws.status.data_ptr(), stream_ptr()),
                       "rg_skinned_status")
+                if capturing:  # the owner of the graph checks ws.status after its replays
+                    ws.status_event = None
+                    break
                 if not fresh:
                     ws.status_event = torch.cuda.Event()
                     ws.status_event.record()

@@ -34,6 +34,7 @@ class HotPath:
         self.bg = torch.zeros(3, device=device)
         self.isotropic = self.pc.use_isotropic_gs
         self.flat = None
+        self.pool = None  # fused.WorkspacePool override (GraphedStep keeps a private one)
 
     def named_parameters(self):
         pc = self.pc
@@ -70,7 +71,8 @@ class HotPath:
         if self.fused:
             from .fused import render_skinned
             return render_skinned(cam, self.pc, self.warp, pose, self.pipe, self.bg, mlp_weight=self.mlp_weight,
-                                  offsets=self.offsets, grad_out=self.flat.views if self.flat is not None else None)
+                                  offsets=self.offsets, grad_out=self.flat.views if self.flat is not None else None,
+                                  pool=self.pool)
         joints = self.warp.nodes[:, :3]
         G, node_rot, d_nodes = sw.fk(pose["local_rotation"], pose["global_trans"], joints, self.warp.parents_i32)
         mask = self.pc._motion_mask.reshape(-1) if self.pc._motion_mask is not None else None
@@ -86,3 +88,94 @@ class HotPath:
         loss = (out["render"] - target).abs().mean()
         loss.backward()
         return loss.detach()
+
+
+class GraphedStep:
+    """``HotPath.step`` for a fixed (P, J, width, height) captured once as a CUDA graph and replayed per view.
+
+    A step is ~30 short launches (kernels of this library, the CUB sort passes, the loss' element-wise kernels);
+    replayed from a graph they run back to back without the per-launch gaps of a Python-driven stream.
+    Inputs are copied into static device buffers (``cam`` matrices, pose, target image); gradients are OVERWRITTEN
+    by every replay (param.grad / ``pose_grads``), not accumulated.  The instance-list capacity check of the fused
+    path runs one replay late, exactly as in eager mode; an overflow re-captures with a larger buffer.
+    """
+
+    def __init__(self, hp: HotPath, cam, pose: Dict[str, torch.Tensor], target: torch.Tensor, warmup: int = 3):
+        if not hp.fused:
+            raise ValueError("GraphedStep needs HotPath(fused=True): the unfused path synchronises with the host")
+        from .fused import WorkspacePool
+        import copy
+        self.hp = hp
+        dev = hp.device
+        self.pool = WorkspacePool()
+        self.cam = copy.copy(cam)
+        self.cam.world_view_transform = cam.world_view_transform.to(dev).clone()
+        self.cam.full_proj_transform = cam.full_proj_transform.to(dev).clone()
+        self.cam.camera_center = cam.camera_center.to(dev).clone()
+        self.pose = {k: v.detach().to(dev).clone().requires_grad_(True) for k, v in pose.items()}
+        self.target = target.to(dev).clone()
+        self.loss: Optional[torch.Tensor] = None
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self._event: Optional[torch.cuda.Event] = None
+        self._warmup = max(int(warmup), 1)
+        self._capture()
+
+    def _one(self):
+        hp = self.hp
+        hp.zero_grad()
+        for v in self.pose.values():
+            v.grad = None
+        old, hp.pool = getattr(hp, "pool", None), self.pool
+        try:
+            return hp.step(self.cam, self.pose, self.target)
+        finally:
+            hp.pool = old
+
+    def _capture(self):
+        from . import _lib
+        s = torch.cuda.Stream(device=self.hp.device)
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):  # sizes the workspace (first frame is synchronous) and warms the allocator
+            for _ in range(self._warmup):
+                self._one()
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        n0 = _lib.lib().rg_launch_count()
+        with torch.cuda.graph(self.graph):
+            self.loss = self._one()
+        self.launches_per_replay = int(_lib.lib().rg_launch_count() - n0)
+        self.grads = {n: p.grad for n, p in self.hp.named_parameters()}  # static: rewritten by every replay
+        self._ws = self.pool.free and next(iter(self.pool.free.values()))[0]
+        self._event = None
+
+    @property
+    def pose_grads(self) -> Dict[str, torch.Tensor]:
+        return {k: v.grad for k, v in self.pose.items()}
+
+    def step(self, cam=None, pose=None, target=None) -> torch.Tensor:
+        """Copies whatever is given into the static inputs, replays the graph and returns the (device) loss."""
+        ws = self._ws
+        if ws is not None and self._event is not None and self._event.query() and int(ws.status[1]) != 0:
+            import warnings
+            warnings.warn("riggs_b200: the previous frame overflowed the instance buffer; re-capturing with a larger one")
+            ws.grow_binning(int(4 * int(ws.status[0]) * self.pool.headroom) + 1024)
+            self.pool.note_capacity(ws, self.hp.device)
+            self._capture()
+        if cam is not None:
+            self.cam.world_view_transform.copy_(cam.world_view_transform, non_blocking=True)
+            self.cam.full_proj_transform.copy_(cam.full_proj_transform, non_blocking=True)
+            self.cam.camera_center.copy_(cam.camera_center, non_blocking=True)
+        if pose is not None:
+            with torch.no_grad():
+                for k, v in pose.items():
+                    self.pose[k].copy_(v, non_blocking=True)
+        if target is not None:
+            self.target.copy_(target, non_blocking=True)
+        self.graph.replay()
+        for n, p in self.hp.named_parameters():
+            if self.grads[n] is not None and p.grad is not self.grads[n]:
+                p.grad = self.grads[n]
+        self._event = torch.cuda.Event()
+        self._event.record()
+        return self.loss

@@ -223,3 +223,36 @@ def test_fused_capacity_growth_and_reuse():
     ws = pool.free[key][0]
     assert int(ws.status[1]) == 0 and int(ws.status[0]) > 0
     assert ws.binning.numel() >= 4 * int(ws.status[0])
+
+
+def test_graphed_step_replays_the_eager_step():
+    """HotPath.step captured as a CUDA graph gives, replay after replay and for new inputs copied into its static
+    buffers, the loss and the gradients of the eager step."""
+    from riggs_b200.hotpath import GraphedStep, HotPath
+    scene = synth.make_config("small", n_views=2)
+    hp = HotPath(scene, device="cuda")
+    cams = [c.to("cuda") for c in scene.cameras[:2]]
+    H, W = cams[0].image_height, cams[0].image_width
+    g = torch.Generator().manual_seed(5)
+    targets = [torch.rand(3, H, W, generator=g).cuda() for _ in range(2)]
+    poses = [{k: v.cuda() for k, v in p.items()} for p in scene.poses[:2]]
+
+    def eager(i):
+        hp.zero_grad()
+        ps = {k: v.clone().requires_grad_(True) for k, v in poses[i].items()}
+        loss = hp.step(cams[i], ps, targets[i])
+        return float(loss), {n: p.grad.clone() for n, p in hp.named_parameters()}, {k: v.grad.clone() for k, v in ps.items()}
+
+    want = [eager(0), eager(1)]
+    gs = GraphedStep(hp, cams[0], poses[0], targets[0])
+    assert gs.launches_per_replay >= 8
+    for i in (0, 1, 0):
+        loss = gs.step(cam=cams[i], pose=poses[i], target=targets[i])
+        torch.cuda.synchronize()
+        wl, wg, wp = want[i]
+        assert abs(float(loss) - wl) <= 1e-6 * max(1.0, abs(wl))
+        for n, p in hp.named_parameters():
+            # float atomics in the blend backward make two runs of the same frame differ in the last bits
+            assert helpers.rel_err(p.grad.cpu().numpy(), wg[n].cpu().numpy(), floor=1e-7) <= 1e-4, n
+        for k, v in gs.pose_grads.items():
+            assert helpers.rel_err(v.cpu().numpy(), wp[k].cpu().numpy(), floor=1e-7) <= 1e-4, k
