@@ -230,6 +230,15 @@ int rg_skinned_backward(const RgSkinnedScene* scene, const RgWorkspace* ws, cons
 
 /* Kernels of this library launched since it was loaded (library sort passes are not counted). */
 long long rg_launch_count(void);
+/* L1 image loss and its gradient in one pass: *loss = mean |output - gt|, grad = sign(output - gt) / n.
+ * Replaces l1_loss of utils/loss_utils.py (torch.abs(network_output - gt).mean()) together with the element-wise
+ * kernels autograd runs for its backward.  output, gt, grad: n floats, 16-byte aligned.  scratch:
+ * rg_l1_loss_scratch_bytes() bytes of device memory, zero-filled before the first call and then reused (the kernel
+ * leaves it ready for the next call); one scratch per stream.  Deterministic for a given n. */
+size_t rg_l1_loss_scratch_bytes(void);
+int rg_l1_loss(size_t n, const float* output, const float* gt, float* loss, float* grad, void* scratch,
+               size_t scratch_bytes, rg_stream_t stream);
+
 /* Per-kernel device timing: when enabled every launch is bracketed by CUDA events on its stream.
  * rg_profile_get synchronises on the recorded events and returns the summed milliseconds per kernel name. */
 void rg_profile_enable(int on);

@@ -127,14 +127,16 @@ __global__ void __launch_bounds__(256) tile_count_kernel(int P, int T, int NW, i
 // ---- 3a. sums over segments of 32 chunk rows -----------------------------------------------------------
 constexpr int kSegRows = 32;
 __global__ void __launch_bounds__(256) seg_sum_kernel(int T, int Tpad, int NW, const uint16_t* __restrict__ M,
-                                                      uint32_t* __restrict__ S) {
+                                                      uint32_t* __restrict__ S, uint32_t* __restrict__ tile_total) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     const int seg = blockIdx.y;
     if (t >= T) return;
     uint32_t s = 0;
     const int w0 = seg * kSegRows, w1 = min(NW, w0 + kSegRows);
+#pragma unroll 8
     for (int w = w0; w < w1; w++) s += M[(size_t)w * Tpad + t];
     S[(size_t)seg * T + t] = s;
+    if (s) atomicAdd(tile_total + t, s);  // zeroed by the launcher; becomes tile_base in the next kernel
 }
 
 constexpr int kOrderBuckets = 128;
@@ -144,8 +146,8 @@ __device__ __forceinline__ int order_bucket(uint32_t n) {
     return e * 4 + (int)((n >> (e - 2)) & 3u);
 }
 
-// ---- 3b. per-tile totals, prefix over segments (in place), prefix over tiles, ranges, num_rendered -----
-__global__ void __launch_bounds__(1024) tile_base_kernel(int T, int nseg, uint32_t* __restrict__ S, uint32_t* __restrict__ tile_base,
+// ---- 3b. per-tile totals, prefix over tiles, ranges, launch order, num_rendered -----
+__global__ void __launch_bounds__(1024) tile_base_kernel(int T, uint32_t* __restrict__ tile_base,
                                                          uint2* __restrict__ ranges, uint32_t* __restrict__ tile_order,
                                                          uint32_t* __restrict__ status, uint32_t capacity) {
     __shared__ uint32_t s_warp[32];
@@ -156,14 +158,7 @@ __global__ void __launch_bounds__(1024) tile_base_kernel(int T, int nseg, uint32
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int base = 0; base < T; base += 1024) {
         const int t = base + threadIdx.x;
-        uint32_t tot = 0;
-        if (t < T) {
-            for (int s = 0; s < nseg; s++) {
-                const uint32_t v = S[(size_t)s * T + t];
-                S[(size_t)s * T + t] = tot;  // exclusive prefix over segments
-                tot += v;
-            }
-        }
+        const uint32_t tot = t < T ? tile_base[t] : 0u;  // per-tile totals accumulated by seg_sum_kernel
         uint32_t x = tot;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -229,7 +224,9 @@ __global__ void __launch_bounds__(256) col_scan_kernel(int T, int Tpad, int NW, 
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     const int seg = blockIdx.y;
     if (t >= T) return;
-    uint32_t run = tile_base[t] + S[(size_t)seg * T + t];
+    uint32_t run = tile_base[t];
+#pragma unroll 8
+    for (int s = 0; s < seg; s++) run += S[(size_t)s * T + t];  // prefix over the earlier segments
     const int w0 = seg * kSegRows, w1 = min(NW, w0 + kSegRows);
     for (int w = w0; w < w1; w++) {
         E[(size_t)w * T + t] = run;
@@ -274,9 +271,9 @@ BinPlan make_bin_plan(int P, int T) {
     BinPlan b;
     b.T = T;
     b.Tpad = (T + 1) & ~1;
-    int L = 256;
+    int L = 128;
     int NW = (P + L - 1) / L;
-    const int kMaxRows = 2048;
+    const int kMaxRows = 4096;
     if (NW > kMaxRows) {
         NW = kMaxRows;
         L = (P + NW - 1) / NW;
@@ -318,8 +315,9 @@ int launch_tile_offsets_a(const BinPlan& b, const uint16_t* M, uint32_t* S, uint
                           uint32_t* tile_order, uint32_t* status, uint32_t capacity, cudaStream_t stream) {
     LaunchScope ls("tile_offsets", stream, 2);
     dim3 g((b.T + 255) / 256, b.nseg);
-    seg_sum_kernel<<<g, 256, 0, stream>>>(b.T, b.Tpad, b.NW, M, S);
-    tile_base_kernel<<<1, 1024, 0, stream>>>(b.T, b.nseg, S, tile_base, ranges, tile_order, status, capacity);
+    cudaMemsetAsync(tile_base, 0, sizeof(uint32_t) * b.T, stream);
+    seg_sum_kernel<<<g, 256, 0, stream>>>(b.T, b.Tpad, b.NW, M, S, tile_base);
+    tile_base_kernel<<<1, 1024, 0, stream>>>(b.T, tile_base, ranges, tile_order, status, capacity);
     return 0;
 }
 

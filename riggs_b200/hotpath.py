@@ -10,6 +10,7 @@ import torch
 
 from . import skeleton_warp as sw
 from .gaussian_renderer import GaussianParams, render
+from .loss_utils import l1_loss
 
 
 class _Pipe:
@@ -85,7 +86,7 @@ class HotPath:
     def step(self, cam, pose, target: torch.Tensor) -> torch.Tensor:
         """Forward + backward of one view; returns the (device) loss.  Gradients accumulate in .grad."""
         out = self.forward(cam, pose)
-        loss = (out["render"] - target).abs().mean()
+        loss = l1_loss(out["render"], target)
         loss.backward()
         return loss.detach()
 

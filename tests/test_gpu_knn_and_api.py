@@ -128,3 +128,27 @@ def test_large_config_properties():
     for k in ("dmean3D", "dsh", "dscale", "drot", "dopacity"):
         lin = g1[k] + 2 * g2[k]
         assert helpers.rel_err(g12[k].cpu().numpy().reshape(-1), lin.cpu().numpy().reshape(-1)) <= 1e-4, k
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", [(3, 800, 800), (3, 37, 53), (1, 1, 1), (3, 1, 5)])
+def test_l1_loss_matches_torch(shape):
+    """loss_utils.l1_loss: value within fp32 rounding of torch's mean |a-b|, gradient = sign(a-b)/n exactly,
+    deterministic across calls, and usable twice in a row (the kernel re-arms its scratch)."""
+    from riggs_b200.loss_utils import l1_loss
+    g = torch.Generator().manual_seed(3)
+    a = torch.rand(*shape, generator=g).cuda().requires_grad_(True)
+    b = torch.rand(*shape, generator=g).cuda()
+    with torch.no_grad():
+        b.view(-1)[0] = a.view(-1)[0]  # a zero difference: gradient 0 there
+    ref = (a.detach().double() - b.double()).abs().mean()
+    losses = []
+    for _ in range(2):
+        a.grad = None
+        loss = l1_loss(a, b)
+        (loss * 2.0).backward()
+        losses.append(float(loss.detach()))
+        assert abs(float(loss.detach()) - float(ref)) <= 2e-6 * max(float(ref), 1e-6)
+        want = torch.sign(a.detach() - b) * (1.0 / a.numel()) * 2.0
+        assert torch.equal(a.grad, want.float())
+    assert losses[0] == losses[1]
