@@ -4,7 +4,7 @@
 // The walk is software-pipelined so that the dependent chain  list entry -> record  (two trips to L2) never sits on
 // the warp's critical path -- the heavy tiles of a frame are walked by a handful of warps whose latency IS the
 // kernel's duration:
-//   stage 1   bounding-box test on rec[0] of a group of 64 entries (two per lane, registers), ballot-compacted into
+//   stage 1   bounding-box test on rec[0] of a group of 128 entries (four per lane, registers), ballot-compacted into
 //             a candidate buffer;
 //   stage 2   candidates are spread over the lanes; each lane fetches the rest of its candidate's record, runs the
 //             exact ellipse-vs-rectangle test (cull.cuh) and the survivors are ballot-compacted, in list order,
@@ -17,7 +17,8 @@
 
 namespace rg {
 
-constexpr int kGroup = 64;      // list entries per iteration: two per lane
+constexpr int kPerLane = 4;
+constexpr int kGroup = 32 * kPerLane;  // list entries per iteration
 constexpr int kBlendWarps = 2;  // warps per CTA: a 16x4 pixel strip of one tile
 
 struct __align__(16) WarpStage {
@@ -44,8 +45,8 @@ struct ListWalker {
     long long t_wait = 0, t_stage1 = 0, t_stage2 = 0;
 
     // pipeline registers
-    uint32_t id_1[2], id_2[2];  // list entries of the next two groups (the second possibly in flight)
-    float4 r0_1[2];             // rec[0] of the next group (possibly in flight)
+    uint32_t id_1[kPerLane], id_2[kPerLane];  // list entries of the next two groups (the second possibly in flight)
+    float4 r0_1[kPerLane];             // rec[0] of the next group (possibly in flight)
     int ncand;                           // candidates of the group whose stage 2 is pending
     float4 p_co, p_rgbd, p_tail;         // this lane's pending stage-2 record (in flight)
 
@@ -56,11 +57,11 @@ struct ListWalker {
         return id != kNone ? rec[4 * (size_t)id] : float4{0.f, 0.f, -3.0e38f, -3.0e38f};
     }
     // stage 1 of one group: registers -> candidate buffer; then request the first 32 candidates' records
-    __device__ __forceinline__ void stage1(const uint32_t (&id)[2], const float4 (&r0)[2], WarpStage& st) {
+    __device__ __forceinline__ void stage1(const uint32_t (&id)[kPerLane], const float4 (&r0)[kPerLane], WarpStage& st) {
         const unsigned lt = (1u << lane) - 1;
         ncand = 0;
 #pragma unroll
-        for (int j = 0; j < 2; j++) {
+        for (int j = 0; j < kPerLane; j++) {
             const bool pass = id[j] != kNone && cull_aabb(r0[j], x0, y0, x1, y1);
             const unsigned m = __ballot_sync(0xffffffffu, pass);
             if (pass) {
@@ -80,22 +81,22 @@ struct ListWalker {
         }
     }
     __device__ __forceinline__ void begin(WarpStage& st) {
-        uint32_t id_0[2];
-        float4 r0_0[2];
+        uint32_t id_0[kPerLane];
+        float4 r0_0[kPerLane];
 #pragma unroll
-        for (int j = 0; j < 2; j++) {
+        for (int j = 0; j < kPerLane; j++) {
             id_0[j] = load_id(j * 32 + lane);
             id_1[j] = load_id(kGroup + j * 32 + lane);
             id_2[j] = load_id(2 * kGroup + j * 32 + lane);
         }
 #pragma unroll
-        for (int j = 0; j < 2; j++) {
+        for (int j = 0; j < kPerLane; j++) {
             r0_0[j] = load_r0(id_0[j]);
             r0_1[j] = load_r0(id_1[j]);
         }
         stage1(id_0, r0_0, st);
     }
-    // Hands out group g (walk positions [64 g, 64 g + 64)): finishes its stage 2 into st and returns the number of
+    // Hands out group g (walk positions [128 g, 128 g + 128)): finishes its stage 2 into st and returns the number of
     // survivors; runs stage 1 of group g+1 and issues the loads further down the list before returning.  Position k
     // of the walk is list entry first + k (or first + n - 1 - k when REVERSE).
     __device__ __forceinline__ int next(int g, WarpStage& st) {
@@ -149,7 +150,7 @@ struct ListWalker {
             }
             stage1(id_1, r0_1, st);
 #pragma unroll
-            for (int j = 0; j < 2; j++) {
+            for (int j = 0; j < kPerLane; j++) {
                 id_1[j] = id_2[j];
                 r0_1[j] = load_r0(id_2[j]);
                 id_2[j] = load_id((g + 3) * kGroup + j * 32 + lane);

@@ -5,7 +5,7 @@
 // latency-bound: the few heavy tiles of a frame decide the kernel's duration while most SMs idle.  Here the unit of
 // work is ONE WARP = one 8x4 pixel block, independent of the other seven blocks of its tile -- no block barrier, a
 // finished warp retires and frees its slot:
-//   * blend_common.cuh's ListWalker hands the warp, 64 list entries at a time, the instances whose alpha >= 1/255
+//   * blend_common.cuh's ListWalker hands the warp, 128 list entries at a time, the instances whose alpha >= 1/255
 //     footprint can reach the block (exact-conservative test of cull.cuh), gathered with a two-deep prefetch;
 //   * the 32 pixels blend only those, in list order, with the reference's exact expressions (same power / alpha / T
 //     tests; a log-threshold pre-test avoids expf for pairs that are certainly below 1/255).  Four survivors are
@@ -56,9 +56,13 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_forward_kernel(BlendFw
         if (__all_sync(0xffffffffu, done)) break;
         const int cnt = walk.next(g, st);
         if (prof) { n_seen++; n_list += cnt; }
-        for (int l = 0; l < cnt; l += 4) {
-            if (done) break;
-            float alpha[4], power[4], opac[4];
+        // Straight-line code, no per-lane branches: the warp that owns a heavy block is alone on the kernel's critical
+        // path, and what bounds it is the latency of its own dependent chain, not issue slots.  Entries that the
+        // reference would skip take alpha = 0 (T * (1 - 0) and C + 0 are exact), so only T -> test -> select is serial.
+        const int n_it = (cnt + 3) >> 2;
+        for (int it = 0; it < n_it; it++) {
+            const int l = it * 4;
+            float alpha[4];
             float4 c[4];
             int pos[4];
             bool act[4];
@@ -69,36 +73,30 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_forward_kernel(BlendFw
                 const float4 con_o = st.co[e];
                 c[u] = st.rgbd[e];
                 const float2 d = {x.x - pixf.x, x.y - pixf.y};
-                power[u] = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
+                const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
+                alpha[u] = fminf(0.99f, con_o.w * expf(power));
                 // the reference skips power > 0 and alpha < 1/255; power < thr is certainly alpha < 1/255
-                act[u] = l + u < cnt && !(power[u] > 0.0f) && !(power[u] < x.z);
-                opac[u] = con_o.w;
+                act[u] = l + u < cnt && !(power > 0.0f) && !(power < x.z) && !(alpha[u] < 1.0f / 255.0f);
                 pos[u] = __float_as_int(x.w);
             }
-            if (act[0] | act[1] | act[2] | act[3]) {
-                // the four falloffs are independent: evaluated together so that their latencies overlap
 #pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    alpha[u] = fminf(0.99f, opac[u] * expf(power[u]));
-                    act[u] = act[u] && !(alpha[u] < 1.0f / 255.0f);
-                }
-                // the only serial part: transmittance and the accumulators
-#pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    const float test_T = T * (1 - alpha[u]);
-                    const bool live = act[u] && !done;
-                    const bool stop = live && test_T < 0.0001f;
-                    const bool add = live && !stop;
-                    done = done || stop;
-                    C0 = add ? C0 + c[u].x * alpha[u] * T : C0;
-                    C1 = add ? C1 + c[u].y * alpha[u] * T : C1;
-                    C2 = add ? C2 + c[u].z * alpha[u] * T : C2;
-                    weight = add ? weight + alpha[u] * T : weight;
-                    D = add ? D + c[u].w * alpha[u] * T : D;
-                    // 1-based position in the tile's range, as the reference counts
-                    last_contributor = add ? (uint32_t)pos[u] + 1 : last_contributor;
-                    T = add ? test_T : T;
-                }
+            for (int u = 0; u < 4; u++) {
+                const float test_T = T * (1 - alpha[u]);
+                const bool live = act[u] && !done;
+                const bool stop = live && test_T < 0.0001f;
+                const bool add = live && !stop;
+                done = done || stop;
+                const float wa = add ? alpha[u] : 0.f;
+                const float cx = add ? c[u].x : 0.f, cy = add ? c[u].y : 0.f, cz = add ? c[u].z : 0.f;
+                const float cd = add ? c[u].w : 0.f;
+                C0 = C0 + cx * wa * T;
+                C1 = C1 + cy * wa * T;
+                C2 = C2 + cz * wa * T;
+                weight = weight + wa * T;
+                D = D + cd * wa * T;
+                // 1-based position in the tile's range, as the reference counts
+                last_contributor = add ? (uint32_t)pos[u] + 1 : last_contributor;
+                T = add ? test_T : T;
             }
         }
     }
