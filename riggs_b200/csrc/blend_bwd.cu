@@ -81,9 +81,10 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendB
     for (int o = 16; o > 0; o >>= 1) total = max(total, __shfl_xor_sync(0xffffffffu, total, o));
     if (total == 0) return;
 
-    __shared__ WarpStage s_stage[kBlendWarps];
-    WarpStage& st = s_stage[warp];
-    ListWalker<true> walk;
+    constexpr int kPerLane = 2, kGroup = 32 * kPerLane;
+    __shared__ WarpStage<kPerLane> s_stage[kBlendWarps];
+    WarpStage<kPerLane>& st = s_stage[warp];
+    ListWalker<true, kPerLane> walk;
     walk.pl = a.point_list; walk.rec = a.rec; walk.first = a.ranges[tile_y * a.grid_x + tile_x].x; walk.n = total;
     walk.lane = lane;
     walk.x0 = (float)(tile_x * RG_TILE + bx0); walk.y0 = (float)(tile_y * RG_TILE + by0);
@@ -149,7 +150,10 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendB
 #pragma unroll
                 for (int k = 0; k < kAcc; k++) v[u][k] = 0.f;
                 if (active[u]) {
-                    T = T / (1.f - alpha[u]);
+                    // one correctly rounded reciprocal serves both quotients of the reference (T / (1 - alpha) and
+                    // -T_final / (1 - alpha)): one rounding more than a division, far inside the 1e-4 gate
+                    const float inv_1ma = __frcp_rn(1.f - alpha[u]);
+                    T = T * inv_1ma;
                     const float dchannel_dcolor = alpha[u] * T;
                     const float4 c = st.rgbd[e[u]];
                     const float col[3] = {c.x, c.y, c.z};
@@ -169,7 +173,7 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendB
                     dL_dopa += (1 - accum_alpha_rec) * dL_dalpha;
                     dL_dopa *= T;
                     last_alpha = alpha[u];
-                    dL_dopa += (-T_final / (1.f - alpha[u])) * bg_dot_dpixel;
+                    dL_dopa += (-T_final * inv_1ma) * bg_dot_dpixel;
                     const float dL_dG = con_o[u].w * dL_dopa;
                     const float gdx = G[u] * d[u].x;
                     const float gdy = G[u] * d[u].y;

@@ -17,11 +17,13 @@
 
 namespace rg {
 
-constexpr int kPerLane = 4;
-constexpr int kGroup = 32 * kPerLane;  // list entries per iteration
 constexpr int kBlendWarps = 2;  // warps per CTA: a 16x4 pixel strip of one tile
 
+// kPerLane list entries per lane and walk step (kGroup = 32 kPerLane per step): the forward kernel, whose walk is a
+// third of its instructions, takes 4; the backward kernel, register-bound in its replay loop, takes 2.
+template <int kPerLane>
 struct __align__(16) WarpStage {
+    static constexpr int kGroup = 32 * kPerLane;
     float4 cand_r0[kGroup];  // stage-1 survivors
     float4 xyts[kGroup];     // stage-2 survivors: {x, y, thr, bits(position in the walk)}
     float4 co[kGroup];       //                    {A, B, C, opacity}
@@ -33,8 +35,10 @@ struct __align__(16) WarpStage {
 
 // REVERSE = false: entries first, first+1, ...   (forward blend: front to back)
 // REVERSE = true:  entries first+n-1, first+n-2, ...   (backward blend: back to front)
-template <bool REVERSE>
+template <bool REVERSE, int kPerLane>
 struct ListWalker {
+    static constexpr int kGroup = 32 * kPerLane;
+    using Stage = WarpStage<kPerLane>;
     const uint32_t* pl;
     const float4* rec;
     uint32_t first;
@@ -57,7 +61,7 @@ struct ListWalker {
         return id != kNone ? rec[4 * (size_t)id] : float4{0.f, 0.f, -3.0e38f, -3.0e38f};
     }
     // stage 1 of one group: registers -> candidate buffer; then request the first 32 candidates' records
-    __device__ __forceinline__ void stage1(const uint32_t (&id)[kPerLane], const float4 (&r0)[kPerLane], WarpStage& st) {
+    __device__ __forceinline__ void stage1(const uint32_t (&id)[kPerLane], const float4 (&r0)[kPerLane], Stage& st) {
         const unsigned lt = (1u << lane) - 1;
         ncand = 0;
 #pragma unroll
@@ -80,7 +84,7 @@ struct ListWalker {
             p_tail = r[3];
         }
     }
-    __device__ __forceinline__ void begin(WarpStage& st) {
+    __device__ __forceinline__ void begin(Stage& st) {
         uint32_t id_0[kPerLane];
         float4 r0_0[kPerLane];
 #pragma unroll
@@ -99,7 +103,7 @@ struct ListWalker {
     // Hands out group g (walk positions [128 g, 128 g + 128)): finishes its stage 2 into st and returns the number of
     // survivors; runs stage 1 of group g+1 and issues the loads further down the list before returning.  Position k
     // of the walk is list entry first + k (or first + n - 1 - k when REVERSE).
-    __device__ __forceinline__ int next(int g, WarpStage& st) {
+    __device__ __forceinline__ int next(int g, Stage& st) {
         const unsigned lt = (1u << lane) - 1;
         long long tt = 0;
         if (timing) tt = clock64();

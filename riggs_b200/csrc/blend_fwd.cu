@@ -35,9 +35,10 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_forward_kernel(BlendFw
     bool done = !inside;
     const uint2 range = a.ranges[tile_y * a.grid_x + tile_x];
 
-    __shared__ WarpStage s_stage[kBlendWarps];
-    WarpStage& st = s_stage[warp];
-    ListWalker<false> walk;
+    constexpr int kPerLane = 4, kGroup = 32 * kPerLane;
+    __shared__ WarpStage<kPerLane> s_stage[kBlendWarps];
+    WarpStage<kPerLane>& st = s_stage[warp];
+    ListWalker<false, kPerLane> walk;
     walk.pl = a.point_list; walk.rec = a.rec; walk.first = range.x; walk.n = (int)(range.y - range.x); walk.lane = lane;
     walk.x0 = (float)(tile_x * RG_TILE + bx0); walk.y0 = (float)(tile_y * RG_TILE + by0);
     walk.x1 = walk.x0 + (kBlkW - 1); walk.y1 = walk.y0 + (kBlkH - 1);
