@@ -81,22 +81,22 @@ __global__ void __launch_bounds__(32) fk_forward_kernel(int F, int J, const floa
         for (int a = 0; a < 3; a++) s_T[12 * i + 9 + a] = p[a] - (R[3 * a] * p[0] + R[3 * a + 1] * p[1] + R[3 * a + 2] * p[2]);
     }
     __syncwarp();
-    if (lane == 0) {
-#pragma unroll
-        for (int a = 0; a < 12; a++) s_G[a] = s_T[a];
-        for (int i = 1; i < J; i++) {
+    // The chain itself is serial in i, but the twelve elements of one G_i are independent: lanes 0..11 take one each
+    // (the single-lane walk was ~400 cycles per joint, all of it shared-memory round trips).
+    if (lane < 12) s_G[lane] = s_T[lane];
+    __syncwarp();
+    for (int i = 1; i < J; i++) {
+        if (lane < 12) {
             const float* Gp = s_G + 12 * s_par[i];
             const float* T = s_T + 12 * i;
-            float* Gi = s_G + 12 * i;
-#pragma unroll
-            for (int a = 0; a < 3; a++) {
-#pragma unroll
-                for (int b = 0; b < 3; b++) Gi[3 * a + b] = Gp[3 * a] * T[b] + Gp[3 * a + 1] * T[3 + b] + Gp[3 * a + 2] * T[6 + b];
-                Gi[9 + a] = Gp[3 * a] * T[9] + Gp[3 * a + 1] * T[10] + Gp[3 * a + 2] * T[11] + Gp[9 + a];
-            }
+            const int a = lane < 9 ? lane / 3 : lane - 9, b = lane < 9 ? lane % 3 : 0;
+            float v;
+            if (lane < 9) v = Gp[3 * a] * T[b] + Gp[3 * a + 1] * T[3 + b] + Gp[3 * a + 2] * T[6 + b];
+            else v = Gp[3 * a] * T[9] + Gp[3 * a + 1] * T[10] + Gp[3 * a + 2] * T[11] + Gp[9 + a];
+            s_G[12 * i + lane] = v;
         }
+        __syncwarp();
     }
-    __syncwarp();
     float* Gf = G + (size_t)f * J * 12;
     for (int k = lane; k < J * 12; k += 32) Gf[k] = s_G[k];
     for (int i = lane; i < J; i += 32) {
@@ -156,32 +156,42 @@ __global__ void __launch_bounds__(32) fk_backward_kernel(int F, int J, const flo
         }
     }
     __syncwarp();
-    if (lane == 0) {
-        for (int i = J - 1; i >= 1; i--) {
-            float* Wi = s_W + 12 * i;
+    // Serial part: children push their gradient into the parent, leaves first; the twelve elements of the parent's
+    // accumulator are independent (lanes 0..11).  G_R_i = Gp_R * R ; G_t_i = Gp_R * tl + Gp_t, tl = p - R p.
+    for (int i = J - 1; i >= 1; i--) {
+        if (lane < 12) {
+            const float* Wi = s_W + 12 * i;
             const float* R = s_R + 9 * i;
             const float* p = s_p + 3 * i;
-            const float* Gp = s_G + 12 * s_par[i];
             float* Wp = s_W + 12 * s_par[i];
-            float tl[3], gRl[9], gtl[3];
-#pragma unroll
-            for (int a = 0; a < 3; a++) tl[a] = p[a] - (R[3 * a] * p[0] + R[3 * a + 1] * p[1] + R[3 * a + 2] * p[2]);
-            // G_R_i = Gp_R * R ; G_t_i = Gp_R * tl + Gp_t
-#pragma unroll
-            for (int a = 0; a < 3; a++) {
-#pragma unroll
-                for (int b = 0; b < 3; b++) {
-                    Wp[3 * a + b] += Wi[3 * a] * R[3 * b] + Wi[3 * a + 1] * R[3 * b + 1] + Wi[3 * a + 2] * R[3 * b + 2] + Wi[9 + a] * tl[b];
-                    gRl[3 * a + b] = Gp[a] * Wi[b] + Gp[3 + a] * Wi[3 + b] + Gp[6 + a] * Wi[6 + b];
-                }
-                Wp[9 + a] += Wi[9 + a];
-                gtl[a] = Gp[a] * Wi[9] + Gp[3 + a] * Wi[10] + Gp[6 + a] * Wi[11];
+            const int a = lane < 9 ? lane / 3 : lane - 9, b = lane < 9 ? lane % 3 : 0;
+            float add;
+            if (lane < 9) {
+                const float tlb = p[b] - (R[3 * b] * p[0] + R[3 * b + 1] * p[1] + R[3 * b + 2] * p[2]);
+                add = Wi[3 * a] * R[3 * b] + Wi[3 * a + 1] * R[3 * b + 1] + Wi[3 * a + 2] * R[3 * b + 2] + Wi[9 + a] * tlb;
+            } else {
+                add = Wi[9 + a];
             }
-#pragma unroll
-            for (int a = 0; a < 9; a++) Wi[a] = gRl[a];
-#pragma unroll
-            for (int a = 0; a < 3; a++) Wi[9 + a] = gtl[a];
+            Wp[lane] += add;
         }
+        __syncwarp();
+    }
+    // Every accumulator is final now: turn dL/dG_i into the gradient of the local transform, one joint per lane
+    // (in place: a joint reads only its own row and its parent's G).
+    for (int i = 1 + lane; i < J; i += 32) {
+        float* Wi = s_W + 12 * i;
+        const float* Gp = s_G + 12 * s_par[i];
+        float gRl[9], gtl[3];
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+#pragma unroll
+            for (int b = 0; b < 3; b++) gRl[3 * a + b] = Gp[a] * Wi[b] + Gp[3 + a] * Wi[3 + b] + Gp[6 + a] * Wi[6 + b];
+            gtl[a] = Gp[a] * Wi[9] + Gp[3 + a] * Wi[10] + Gp[6 + a] * Wi[11];
+        }
+#pragma unroll
+        for (int a = 0; a < 9; a++) Wi[a] = gRl[a];
+#pragma unroll
+        for (int a = 0; a < 3; a++) Wi[9 + a] = gtl[a];
     }
     __syncwarp();
     for (int i = lane; i < J; i += 32) {
