@@ -233,9 +233,13 @@ def run_ours(args):
     class _HostCam:  # pinned host copies of the camera tensors
         world_view_transform, full_proj_transform, camera_center = cam_host
 
-    for _ in range(args.steps):
-        if gs is not None:  # host -> device copies go straight into the graph's static inputs
-            loss = gs.step(cam=_HostCam, pose=pose_host, target=target_host)
+    if gs is not None:  # input pipeline: step i+1's host -> device copies run while step i computes
+        gs.prefetch(cam=_HostCam, pose=pose_host, target=target_host)
+    for it in range(args.steps):
+        if gs is not None:
+            loss = gs.step()  # waits for this step's staged inputs, moves them into the graph's static buffers
+            if it + 1 < args.steps:
+                gs.prefetch(cam=_HostCam, pose=pose_host, target=target_host)
         else:
             tgt = target_host.to(dev, non_blocking=True)
             ps = {k: v.to(dev, non_blocking=True).requires_grad_(True) for k, v in pose_host.items()}

@@ -154,8 +154,57 @@ class GraphedStep:
     def pose_grads(self) -> Dict[str, torch.Tensor]:
         return {k: v.grad for k, v in self.pose.items()}
 
+    def prefetch(self, cam=None, pose=None, target=None) -> None:
+        """Starts copying the NEXT step's inputs (typically pinned host tensors) into staging buffers on a side
+        stream, so that the transfer overlaps the step that is running; the next ``step()`` without arguments picks
+        them up (a device-to-device copy of a few microseconds) before it replays."""
+        dev = self.hp.device
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(device=dev)
+            self._stage_cam = [torch.empty_like(t) for t in (self.cam.world_view_transform, self.cam.full_proj_transform,
+                                                             self.cam.camera_center)]
+            self._stage_pose = {k: torch.empty_like(v) for k, v in self.pose.items()}
+            self._stage_target = torch.empty_like(self.target)
+            self._consumed = None
+        cs = self._copy_stream
+        if self._consumed is not None:
+            cs.wait_event(self._consumed)  # the previous staged set has been moved into the static inputs
+        self._staged = (cam is not None, pose is not None, target is not None)
+        with torch.cuda.stream(cs), torch.no_grad():
+            if cam is not None:
+                for dst, src in zip(self._stage_cam, (cam.world_view_transform, cam.full_proj_transform, cam.camera_center)):
+                    dst.copy_(src, non_blocking=True)
+            if pose is not None:
+                for k, v in pose.items():
+                    self._stage_pose[k].copy_(v, non_blocking=True)
+            if target is not None:
+                self._stage_target.copy_(target, non_blocking=True)
+            self._ready = torch.cuda.Event()
+            self._ready.record(cs)
+
+    def _take_staged(self):
+        ready = getattr(self, "_ready", None)
+        if ready is None:
+            return
+        torch.cuda.current_stream().wait_event(ready)
+        has_cam, has_pose, has_target = self._staged
+        with torch.no_grad():
+            if has_cam:
+                for dst, src in zip((self.cam.world_view_transform, self.cam.full_proj_transform, self.cam.camera_center),
+                                    self._stage_cam):
+                    dst.copy_(src, non_blocking=True)
+            if has_pose:
+                for k, v in self._stage_pose.items():
+                    self.pose[k].copy_(v, non_blocking=True)
+            if has_target:
+                self.target.copy_(self._stage_target, non_blocking=True)
+        self._consumed = torch.cuda.Event()
+        self._consumed.record()
+        self._ready = None
+
     def step(self, cam=None, pose=None, target=None) -> torch.Tensor:
-        """Copies whatever is given into the static inputs, replays the graph and returns the (device) loss."""
+        """Copies whatever is given (or was staged by ``prefetch``) into the static inputs, replays the graph and
+        returns the (device) loss."""
         ws = self._ws
         if ws is not None and self._event is not None and self._event.query() and int(ws.status[1]) != 0:
             import warnings
@@ -163,6 +212,7 @@ class GraphedStep:
             ws.grow_binning(int(4 * int(ws.status[0]) * self.pool.headroom) + 1024)
             self.pool.note_capacity(ws, self.hp.device)
             self._capture()
+        self._take_staged()
         if cam is not None:
             self.cam.world_view_transform.copy_(cam.world_view_transform, non_blocking=True)
             self.cam.full_proj_transform.copy_(cam.full_proj_transform, non_blocking=True)

@@ -246,8 +246,13 @@ def test_graphed_step_replays_the_eager_step():
     want = [eager(0), eager(1)]
     gs = GraphedStep(hp, cams[0], poses[0], targets[0])
     assert gs.launches_per_replay >= 8
-    for i in (0, 1, 0):
-        loss = gs.step(cam=cams[i], pose=poses[i], target=targets[i])
+    for n, i in enumerate((0, 1, 0, 1)):
+        if n % 2 == 0:
+            loss = gs.step(cam=cams[i], pose=poses[i], target=targets[i])
+        else:  # inputs staged on the side stream (pinned host tensors), picked up by the next step()
+            gs.prefetch(cam=cams[i], pose={k: v.cpu().pin_memory() for k, v in poses[i].items()},
+                        target=targets[i].cpu().pin_memory())
+            loss = gs.step()
         torch.cuda.synchronize()
         wl, wg, wp = want[i]
         assert abs(float(loss) - wl) <= 1e-6 * max(1.0, abs(wl))
