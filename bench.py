@@ -291,12 +291,16 @@ def run_ours(args):
     kern = {k: {"ms_per_launch": v[0] / max(v[1], 1), "launches": v[1], "ms_per_step": v[0] / args.steps}
             for k, v in prof.items()}
     dom = max(kern, key=lambda k: kern[k]["ms_per_step"]) if kern else None
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch from the one `ncu --set full` capture of this workload
+    # (profiles/r1_p_full_raw.csv, C0 on one B200); other workloads have no capture -> null
+    ncu_traffic = {"blend_backward": 22842624, "blend_forward": 14176768, "gauss_skin_backward": 121907712,
+                   "skin_preprocess": 77956864} if args.workload == "C0" and not args.isotropic else {}
     roof = None
     if dom:
         b = per.get(dom, 0)
         achieved = b / (kern[dom]["ms_per_launch"] * 1e-3) / 1e9
         roof = {"kernel": dom, "bound": "hbm", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
-                "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                "frac": round(achieved / peak, 4), "traffic": ncu_traffic.get(dom), "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": b, "ms_per_launch": round(kern[dom]["ms_per_launch"], 4)}
     line = {
         "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
