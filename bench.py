@@ -321,7 +321,7 @@ def run_ours(args):
         "kernels": {k: {kk: round(vv, 4) if isinstance(vv, float) else vv for kk, vv in v.items()} for k, v in kern.items()},
     }
     if world == 1 and not args.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_baseline(scene, args, budget_s=20.0)
+        line["cpu_baseline"] = cpu_baseline(scene, args)
     if world == 1 and not args.no_ref_cuda:
         rc = ref_cuda_baseline(scene, cam, pose, target, steps=min(args.steps, 10))
         if rc:
@@ -387,7 +387,7 @@ def cpu_step(scene, view, target):
     return float(loss)
 
 
-def cpu_baseline(scene, args, budget_s=20.0):
+def cpu_baseline(scene, args, budget_s=12.0):
     import torch
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
@@ -399,7 +399,7 @@ def cpu_baseline(scene, args, budget_s=20.0):
     while True:
         cpu_step(scene, 0, target)
         n += 1
-        if time.time() - t0 > budget_s or n >= 5:
+        if time.time() - t0 > budget_s or n >= 40:  # a bounded sample: ~10-15 s of host work
             break
     dt = (time.time() - t0) / n
     return {"value": round(1.0 / dt, 4), "unit": UNIT, "cores": cores, "kind": "port",
