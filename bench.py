@@ -131,6 +131,7 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     if world > 1:
         import datetime
+        os.environ.setdefault("NCCL_DEBUG", "WARN")  # keep NCCL banner lines off stdout: rank 0 prints ONE JSON line
         dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=120))
     scene = make_scene(args.workload, args.isotropic)
     hp = HotPath(scene, device=dev, fused=not args.unfused)

@@ -150,9 +150,11 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendB
 #pragma unroll
                 for (int k = 0; k < kAcc; k++) v[u][k] = 0.f;
                 if (active[u]) {
-                    // one correctly rounded reciprocal serves both quotients of the reference (T / (1 - alpha) and
+                    // one reciprocal (accurate to the last bit or so) serves both quotients of the reference (T / (1 - alpha) and
                     // -T_final / (1 - alpha)): one rounding more than a division, far inside the 1e-4 gate
-                    const float inv_1ma = __frcp_rn(1.f - alpha[u]);
+                    const float one_ma = 1.f - alpha[u];  // in [0.01, 1]
+                    float inv_1ma = __fdividef(1.f, one_ma);        // MUFU.RCP, then one Newton step: < 1 ulp
+                    inv_1ma = fmaf(inv_1ma, fmaf(-one_ma, inv_1ma, 1.f), inv_1ma);
                     T = T * inv_1ma;
                     const float dchannel_dcolor = alpha[u] * T;
                     const float4 c = st.rgbd[e[u]];
@@ -191,7 +193,6 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendB
 #pragma unroll
             for (int u = 0; u < U; u++) {
                 if (__any_sync(0xffffffffu, active[u])) {
-                    if (prof) n_red++;
                     const float s = transpose_reduce10(v[u], lane);
                     if (my_id >= 0 && s != 0.f) atomicAdd(a.grad_acc + (size_t)st.id[e[u]] * kAcc + my_id, s);
                 }
