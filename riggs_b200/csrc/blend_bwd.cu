@@ -5,64 +5,97 @@
 //  * one warp = one 8x4 pixel block, independent of the rest of its tile: it replays only the entries in front of
 //    ITS deepest last contributor (the reference skips the others one by one, backward.cu:517-519), and of those only
 //    the instances whose alpha >= 1/255 footprint can reach the block (ListWalker of blend_common.cuh);
-//  * two survivors are replayed per iteration: the Gaussian evaluations are independent, the T / accumulator
-//    recurrence between them is a handful of FMAs, and the two warp reductions interleave;
-//  * the ten per-pair terms of an instance are summed across the warp with a 12-shuffle transpose-reduce
-//    (10 values x 32 lanes -> one value per lane) and leave the SM as ONE 10-lane reduction per
-//    (warp block, instance) instead of up to 320 atomics.
-// Per-pair arithmetic is the reference's expression order; sums differ only in association (tolerance 1e-4).
+//  * phase A, one pixel per lane: the reference's recurrence (T, the accumulated colour/depth/alpha behind the
+//    instance) in the reference's expression order.  Of the ten per-pair gradient terms only TWO scalars depend on
+//    that recurrence:  Q = G dL/d(alpha)  and  W = alpha T ; the rest is geometry of the pair and constants of the
+//    pixel.  Q and W go to a 32 x 32 (pixel x instance) tile in shared memory;
+//  * phase B, one INSTANCE per lane, every 32 instances: the ten sums over the block's pixels are linear in Q and W,
+//        sum Q {1, lx, ly, lx^2, lx ly, ly^2}   and   sum W {dL/dr, dL/dg, dL/db, dL/ddepth}
+//    (lx, ly = pixel position inside the block), so each lane runs 32 x 10 FMAs down its column, rebuilds the moments
+//    about its instance's centre and issues its ten reductions to global memory itself.
+// Against a cross-lane reduction per instance (12 shuffles + ~40 selects/adds + one RED instruction, per instance and
+// per block) this halves the kernel's instruction count: the sums cost 13 instructions per pixel per 32 instances.
+// Sums differ from the reference's in association only (tolerance 1e-4).
 #include "blend_common.cuh"
 #include "kernels.cuh"
 
 namespace rg {
 
 constexpr int kAcc = 10;  // mean2D.x, mean2D.y, conic.x, conic.y, conic.w, opacity, r, g, b, depth
+constexpr int kChunk = 32;          // instances per phase-B flush: one per lane
+constexpr int kPitch = kChunk + 1;  // row pitch of the Q / W tiles: conflict-free for both phases
 
 // Optional per-(tile, warp) cycle counters for performance analysis (rg_debug_tile_profile); null in production.
 __device__ uint32_t* g_bwd_tile_prof = nullptr;
 void set_bwd_tile_profile(uint32_t* p) { cudaMemcpyToSymbol(g_bwd_tile_prof, &p, sizeof(p)); }
 
-// Sum each of v[0..9] over the 32 lanes.  Afterwards the lane with id_of_lane(lane) = k >= 0 holds the
-// total of v[k] in the return value.  12 shuffles (5+3+2+1+1) instead of 50.
-__device__ __forceinline__ float transpose_reduce10(const float* v, int lane) {
-    const unsigned full = 0xffffffffu;
-    const bool u4 = lane & 16, u3 = lane & 8, u2 = lane & 4, u1 = lane & 2;
-    float w[5];
-#pragma unroll
-    for (int i = 0; i < 5; i++) {
-        const float keep = u4 ? v[5 + i] : v[i];
-        const float send = u4 ? v[i] : v[5 + i];
-        w[i] = keep + __shfl_xor_sync(full, send, 16);
-    }
-    float x[3];
-#pragma unroll
-    for (int i = 0; i < 3; i++) {
-        const float hi = i < 2 ? w[3 + i] : 0.f;
-        const float keep = u3 ? hi : w[i];
-        const float send = u3 ? w[i] : hi;
-        x[i] = keep + __shfl_xor_sync(full, send, 8);
-    }
-    float y[2];
-#pragma unroll
-    for (int i = 0; i < 2; i++) {
-        const float hi = i < 1 ? x[2] : 0.f;
-        const float keep = u2 ? hi : x[i];
-        const float send = u2 ? x[i] : hi;
-        y[i] = keep + __shfl_xor_sync(full, send, 4);
-    }
-    const float keep = u1 ? y[1] : y[0];
-    const float send = u1 ? y[0] : y[1];
-    float s = keep + __shfl_xor_sync(full, send, 2);
-    s += __shfl_xor_sync(full, s, 1);
-    return s;
-}
+struct __align__(16) BwdChunk {
+    float Q[32 * kPitch];   // [pixel][instance]
+    float W[32 * kPitch];
+    float4 xyts[kChunk];    // instance centre (x, y), unused, unused
+    float4 co[kChunk];      // conic + opacity
+    float4 cpix[32];        // per pixel: dL/d(r, g, b, depth)
+    uint32_t id[kChunk];
+    float out[kChunk * kAcc];  // phase-B results, instance-major, for the coalesced reductions
+};
 
-__device__ __forceinline__ int id_of_lane(int lane) {
-    // bits 3..1 select within a group of five: 000->0 001->1 010->2 100->3 101->4, others hold zeros
-    const int t = (lane >> 1) & 7;
-    const int sub = t == 0 ? 0 : t == 1 ? 1 : t == 2 ? 2 : t == 4 ? 3 : t == 5 ? 4 : -1;
-    if (sub < 0 || (lane & 1)) return -1;
-    return ((lane & 16) ? 5 : 0) + sub;
+// Phase B: lane e owns instance e of the chunk.
+__device__ __noinline__ void flush_chunk(BwdChunk& ch, int fill, int lane, float ox, float oy, float ddelx_dx,
+                                            float ddely_dy, float* __restrict__ grad_acc) {
+    __syncwarp();
+    if (lane < fill) {
+        float s0 = 0.f, sx = 0.f, sy = 0.f, sxx = 0.f, sxy = 0.f, syy = 0.f, wr = 0.f, wg = 0.f, wb = 0.f, wd = 0.f;
+#pragma unroll
+        for (int p = 0; p < 32; p++) {
+            const float lx = (float)(p & 7), ly = (float)(p >> 3);
+            const float q = ch.Q[p * kPitch + lane], w = ch.W[p * kPitch + lane];
+            const float4 c = ch.cpix[p];
+            s0 += q;
+            sx = fmaf(q, lx, sx);
+            sy = fmaf(q, ly, sy);
+            sxx = fmaf(q, lx * lx, sxx);
+            sxy = fmaf(q, lx * ly, sxy);
+            syy = fmaf(q, ly * ly, syy);
+            wr = fmaf(w, c.x, wr);
+            wg = fmaf(w, c.y, wg);
+            wb = fmaf(w, c.z, wb);
+            wd = fmaf(w, c.w, wd);
+        }
+        // moments about the instance centre: d = (X - lx, Y - ly), X = x - block origin
+        const float4 e = ch.xyts[lane];
+        const float4 co = ch.co[lane];
+        const float X = e.x - ox, Y = e.y - oy;
+        const float qdx = X * s0 - sx, qdy = Y * s0 - sy;
+        const float qdxx = X * (X * s0 - 2.f * sx) + sxx;
+        const float qdxy = X * (Y * s0 - sy) - Y * sx + sxy;
+        const float qdyy = Y * (Y * s0 - 2.f * sy) + syy;
+        // dL/dG = o dL/dalpha;  dG/ddelx = -G (A dx + B dy), dG/ddely = -G (C dy + B dx)
+        const float o = co.w;
+        float* out = ch.out + lane * kAcc;
+        out[0] = -o * ddelx_dx * (co.x * qdx + co.y * qdy);
+        out[1] = -o * ddely_dy * (co.z * qdy + co.y * qdx);
+        out[2] = -0.5f * o * qdxx;
+        out[3] = -0.5f * o * qdxy;
+        out[4] = -0.5f * o * qdyy;
+        out[5] = s0;
+        out[6] = wr;
+        out[7] = wg;
+        out[8] = wb;
+        out[9] = wd;
+    }
+    __syncwarp();
+    // The ten values of an instance are contiguous in grad_acc: lanes take consecutive (instance, value) pairs so that
+    // one instruction's reductions fall into a few 32-byte sectors instead of 32.
+#pragma unroll
+    for (int j = 0; j < kAcc; j++) {
+        const int idx = j * 32 + lane;
+        const int ent = idx / kAcc, k = idx - ent * kAcc;
+        if (ent < fill) {
+            const float v = ch.out[idx];
+            if (v != 0.f) atomicAdd(grad_acc + (size_t)ch.id[ent] * kAcc + k, v);
+        }
+    }
+    __syncwarp();
 }
 
 __global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendBwdArgs a) {
@@ -83,12 +116,15 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendB
 
     constexpr int kPerLane = 2, kGroup = 32 * kPerLane;
     __shared__ WarpStage<kPerLane> s_stage[kBlendWarps];
+    __shared__ BwdChunk s_chunk[kBlendWarps];
     WarpStage<kPerLane>& st = s_stage[warp];
+    BwdChunk& ch = s_chunk[warp];
     ListWalker<true, kPerLane> walk;
-    walk.pl = a.point_list; walk.rec = a.rec; walk.first = a.ranges[tile_y * a.grid_x + tile_x].x; walk.n = total;
+    walk.pl = a.point_list; walk.rec = a.rec; walk.first = a.ranges[tile].x; walk.n = total;
     walk.lane = lane;
-    walk.x0 = (float)(tile_x * RG_TILE + bx0); walk.y0 = (float)(tile_y * RG_TILE + by0);
-    walk.x1 = walk.x0 + (kBlkW - 1); walk.y1 = walk.y0 + (kBlkH - 1);
+    const float ox = (float)(tile_x * RG_TILE + bx0), oy = (float)(tile_y * RG_TILE + by0);  // block origin (pixel centres)
+    walk.x0 = ox; walk.y0 = oy;
+    walk.x1 = ox + (kBlkW - 1); walk.y1 = oy + (kBlkH - 1);
     const int n_groups = (total + kGroup - 1) / kGroup;
     walk.begin(st);
 
@@ -103,105 +139,111 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendB
         dL_dpixel_depth = a.dL_dpix_depth[pix_id];
         dL_dalpha = a.dL_dalphas[pix_id];
     }
+    ch.cpix[lane] = {dL_dpixel[0], dL_dpixel[1], dL_dpixel[2], dL_dpixel_depth};
     float last_alpha = 0, last_color[3] = {0, 0, 0}, last_depth = 0;
     const float ddelx_dx = 0.5 * a.W;
     const float ddely_dy = 0.5 * a.H;
     const float bg_dot_dpixel = a.bg[0] * dL_dpixel[0] + a.bg[1] * dL_dpixel[1] + a.bg[2] * dL_dpixel[2];
-    const int my_id = id_of_lane(lane);
     uint32_t* const prof = g_bwd_tile_prof;
     long long t_start = 0;
-    uint32_t n_list = 0, n_red = 0;
+    uint32_t n_list = 0, n_flush = 0;
     if (prof) { t_start = clock64(); walk.timing = true; }
 
+    // lanes 0-3 copy xyts, 4-7 conic+opacity, 8 the id (all 32-bit words; ids travel as bit patterns)
+    const uint32_t* meta_src = lane < 4 ? reinterpret_cast<const uint32_t*>(st.xyts) + lane
+                               : lane < 8 ? reinterpret_cast<const uint32_t*>(st.co) + (lane - 4) : st.id;
+    uint32_t* meta_dst = lane < 4 ? reinterpret_cast<uint32_t*>(ch.xyts) + lane
+                         : lane < 8 ? reinterpret_cast<uint32_t*>(ch.co) + (lane - 4) : ch.id;
+    const int meta_sstride = lane < 8 ? 4 : 1, meta_dstride = meta_sstride;
     constexpr int U = 2;
+    int fill = 0;  // instances waiting in the chunk
     for (int g = 0; g < n_groups; g++) {
         const int cnt = walk.next(g, st);
         if (prof) n_list += cnt;
-        for (int l = 0; l < cnt; l += U) {
-            float v[U][kAcc];
+        // Straight-line code without per-lane branches, U instances per iteration: the warps of the heavy blocks are
+        // the kernel's critical path and what bounds them is the latency of their own dependent chain.  A pair the
+        // reference skips takes alpha = 0 -- T / (1 - 0) is exact -- and leaves the recurrence state untouched.
+        const int n_it = (cnt + U - 1) / U;
+        for (int it = 0; it < n_it; it++) {
+            const int l = it * U;
             bool active[U];
-            float G[U], alpha[U];
-            float2 d[U];
-            float4 con_o[U];
+            float G[U], alpha[U], q[U], w[U];
+            float4 xy[U], con_o[U], col[U];
             int e[U];
             // independent part: Gaussian falloff and alpha of each of the U survivors
 #pragma unroll
             for (int u = 0; u < U; u++) {
                 e[u] = min(l + u, kGroup - 1);
-                const float4 x = st.xyts[e[u]];
-                // walk position k is range entry total-1-k; the pixel saw entries [0, last_contributor)
-                const int contributor = total - 1 - __float_as_int(x.w);
+                xy[u] = st.xyts[e[u]];
                 con_o[u] = st.co[e[u]];
-                d[u] = {x.x - pixf.x, x.y - pixf.y};
-                const float power =
-                    -0.5f * (con_o[u].x * d[u].x * d[u].x + con_o[u].z * d[u].y * d[u].y) - con_o[u].y * d[u].x * d[u].y;
-                active[u] = l + u < cnt && contributor < last_contributor && !(power > 0.0f) && !(power < x.z);
-                G[u] = 0.f;
-                alpha[u] = 0.f;
-                if (active[u]) {
-                    G[u] = expf(power);
-                    alpha[u] = fminf(0.99f, con_o[u].w * G[u]);
-                    active[u] = !(alpha[u] < 1.0f / 255.0f);
-                }
+                col[u] = st.rgbd[e[u]];
+                // walk position k is range entry total-1-k; the pixel saw entries [0, last_contributor)
+                const int contributor = total - 1 - __float_as_int(xy[u].w);
+                const float2 d = {xy[u].x - pixf.x, xy[u].y - pixf.y};
+                const float power = -0.5f * (con_o[u].x * d.x * d.x + con_o[u].z * d.y * d.y) - con_o[u].y * d.x * d.y;
+                G[u] = expf(power);
+                alpha[u] = fminf(0.99f, con_o[u].w * G[u]);
+                active[u] = l + u < cnt && contributor < last_contributor && !(power > 0.0f) && !(power < xy[u].z) &&
+                            !(alpha[u] < 1.0f / 255.0f);
             }
-            // serial part: the back-to-front recurrence
+            // serial part: the back-to-front recurrence of the reference, reduced to the two scalars phase B needs
 #pragma unroll
             for (int u = 0; u < U; u++) {
+                const bool on = active[u];
+                const float a_eff = on ? alpha[u] : 0.f;
+                // one reciprocal (accurate to the last bit or so) serves both quotients of the reference (T / (1 - alpha)
+                // and -T_final / (1 - alpha)): one rounding more than a division, far inside the 1e-4 gate
+                const float one_ma = 1.f - a_eff;  // in [0.01, 1]
+                float inv_1ma = __fdividef(1.f, one_ma);        // MUFU.RCP, then one Newton step: < 1 ulp
+                inv_1ma = fmaf(inv_1ma, fmaf(-one_ma, inv_1ma, 1.f), inv_1ma);
+                T = T * inv_1ma;
+                w[u] = a_eff * T;  // dchannel_dcolor
+                const float c3[3] = {col[u].x, col[u].y, col[u].z};
+                float dL_dopa = 0.0f;
 #pragma unroll
-                for (int k = 0; k < kAcc; k++) v[u][k] = 0.f;
-                if (active[u]) {
-                    // one reciprocal (accurate to the last bit or so) serves both quotients of the reference (T / (1 - alpha) and
-                    // -T_final / (1 - alpha)): one rounding more than a division, far inside the 1e-4 gate
-                    const float one_ma = 1.f - alpha[u];  // in [0.01, 1]
-                    float inv_1ma = __fdividef(1.f, one_ma);        // MUFU.RCP, then one Newton step: < 1 ulp
-                    inv_1ma = fmaf(inv_1ma, fmaf(-one_ma, inv_1ma, 1.f), inv_1ma);
-                    T = T * inv_1ma;
-                    const float dchannel_dcolor = alpha[u] * T;
-                    const float4 c = st.rgbd[e[u]];
-                    const float col[3] = {c.x, c.y, c.z};
-                    float dL_dopa = 0.0f;
-#pragma unroll
-                    for (int ch = 0; ch < 3; ch++) {
-                        accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
-                        last_color[ch] = col[ch];
-                        dL_dopa += (col[ch] - accum_rec[ch]) * dL_dpixel[ch];
-                        v[u][6 + ch] = dchannel_dcolor * dL_dpixel[ch];
-                    }
-                    accum_depth_rec = last_alpha * last_depth + (1.f - last_alpha) * accum_depth_rec;
-                    last_depth = c.w;
-                    dL_dopa += (c.w - accum_depth_rec) * dL_dpixel_depth;
-                    v[u][9] = dchannel_dcolor * dL_dpixel_depth;
-                    accum_alpha_rec = last_alpha + (1.f - last_alpha) * accum_alpha_rec;
-                    dL_dopa += (1 - accum_alpha_rec) * dL_dalpha;
-                    dL_dopa *= T;
-                    last_alpha = alpha[u];
-                    dL_dopa += (-T_final * inv_1ma) * bg_dot_dpixel;
-                    const float dL_dG = con_o[u].w * dL_dopa;
-                    const float gdx = G[u] * d[u].x;
-                    const float gdy = G[u] * d[u].y;
-                    const float dG_ddelx = -gdx * con_o[u].x - gdy * con_o[u].y;
-                    const float dG_ddely = -gdy * con_o[u].z - gdx * con_o[u].y;
-                    v[u][0] = dL_dG * dG_ddelx * ddelx_dx;
-                    v[u][1] = dL_dG * dG_ddely * ddely_dy;
-                    v[u][2] = -0.5f * gdx * d[u].x * dL_dG;
-                    v[u][3] = -0.5f * gdx * d[u].y * dL_dG;
-                    v[u][4] = -0.5f * gdy * d[u].y * dL_dG;
-                    v[u][5] = G[u] * dL_dopa;
+                for (int k = 0; k < 3; k++) {
+                    const float acc = last_alpha * last_color[k] + (1.f - last_alpha) * accum_rec[k];
+                    accum_rec[k] = on ? acc : accum_rec[k];
+                    last_color[k] = on ? c3[k] : last_color[k];
+                    dL_dopa += (c3[k] - acc) * dL_dpixel[k];
                 }
+                const float accd = last_alpha * last_depth + (1.f - last_alpha) * accum_depth_rec;
+                accum_depth_rec = on ? accd : accum_depth_rec;
+                last_depth = on ? col[u].w : last_depth;
+                dL_dopa += (col[u].w - accd) * dL_dpixel_depth;
+                const float acca = last_alpha + (1.f - last_alpha) * accum_alpha_rec;
+                accum_alpha_rec = on ? acca : accum_alpha_rec;
+                dL_dopa += (1 - acca) * dL_dalpha;
+                dL_dopa *= T;
+                last_alpha = on ? alpha[u] : last_alpha;
+                dL_dopa += (-T_final * inv_1ma) * bg_dot_dpixel;
+                q[u] = on ? G[u] * dL_dopa : 0.f;
             }
-            // one 10-lane reduction per (block, instance)
+            // park the pair scalars in the chunk; instances no pixel of the block sees are dropped
 #pragma unroll
             for (int u = 0; u < U; u++) {
                 if (__any_sync(0xffffffffu, active[u])) {
-                    const float s = transpose_reduce10(v[u], lane);
-                    if (my_id >= 0 && s != 0.f) atomicAdd(a.grad_acc + (size_t)st.id[e[u]] * kAcc + my_id, s);
+                    ch.Q[lane * kPitch + fill] = q[u];
+                    ch.W[lane * kPitch + fill] = w[u];
+                    // instance record -> chunk: nine words copied by nine lanes (no divergent single-lane stores)
+                    if (lane < 9) meta_dst[fill * meta_dstride] = meta_src[e[u] * meta_sstride];
+                    if (++fill == kChunk) {
+                        flush_chunk(ch, fill, lane, ox, oy, ddelx_dx, ddely_dy, a.grad_acc);
+                        fill = 0;
+                        if (prof) n_flush++;
+                    }
                 }
             }
         }
     }
+    if (fill > 0) {
+        flush_chunk(ch, fill, lane, ox, oy, ddelx_dx, ddely_dy, a.grad_acc);
+        if (prof) n_flush++;
+    }
     if (prof && lane == 0) {
-        uint32_t* o = prof + ((size_t)(tile_y * a.grid_x + tile_x) * 8 + strip * 2 + warp) * 8;
-        o[0] = (uint32_t)(clock64() - t_start); o[1] = (uint32_t)walk.t_wait; o[2] = (uint32_t)walk.t_stage1; o[3] = (uint32_t)walk.t_stage2; o[4] = n_list; o[5] = n_groups; o[6] = n_red; o[7] = 0;
+        uint32_t* o = prof + ((size_t)tile * 8 + strip * 2 + warp) * 8;
+        o[0] = (uint32_t)(clock64() - t_start); o[1] = (uint32_t)walk.t_wait; o[2] = (uint32_t)walk.t_stage1;
+        o[3] = (uint32_t)walk.t_stage2; o[4] = n_list; o[5] = n_groups; o[6] = n_flush; o[7] = 0;
     }
 }
 
