@@ -63,7 +63,8 @@ int rg_rasterize_forward(rg_alloc_fn geom_alloc, void* geom_ctx, rg_alloc_fn bin
  * rasterizer_impl.cu:343-447; called from RasterizeGaussiansBackwardCUDA, dgr/rasterize_points.cu:171-204).
  * Every output is fully written by the kernels (no zero-initialisation needed by the caller):
  * dL_dmean2D (P,3) [z = 0], dL_dconic (P,4) [.z = 0], dL_dopacity (P), dL_dcolor (P,3), dL_ddepth (P),
- * dL_dmean3D (P,3), dL_dcov3D (P,6), dL_dsh (P,M,3) or NULL, dL_dscale (P,3) / dL_drot (P,4) or NULL. */
+ * dL_dmean3D (P,3), dL_dcov3D (P,6), dL_dsh (P,M,3) or NULL, dL_dscale (P,3) / dL_drot (P,4) or NULL.
+ * dL_dpix_depth / dL_dalphas may be NULL (no cotangent for that output). */
 int rg_rasterize_backward(int P, int D, int M, int R, const float* background, int width, int height,
                           const float* means3D, const float* shs, const float* colors_precomp,
                           const float* alphas, const float* scales, float scale_modifier,
@@ -214,7 +215,8 @@ int rg_skinned_forward(const RgSkinnedScene* scene, const RgWorkspace* ws, float
 int rg_skinned_status(const RgSkinnedScene* scene, const RgWorkspace* ws, uint32_t* host_out2, rg_stream_t stream);
 
 /* Backward of rg_skinned_forward on the same scene/workspace.  Inputs: radii and alphas (= out_alpha) of the
- * forward, dL/dcolor (3,H,W), dL/ddepth (1,H,W), dL/dalpha (1,H,W), optional dL/d(d_nodes) (J,3).
+ * forward, dL/dcolor (3,H,W), dL/ddepth (1,H,W) and dL/dalpha (1,H,W) (either may be NULL: that output has no
+ * cotangent, which saves the caller a zero-filled image), optional dL/d(d_nodes) (J,3).
  * Outputs (fully written): gradients of the raw tensors d_xyz (P,3), d_scaling_raw (P,3|1), d_rotation_raw (P,4),
  * d_opacity_raw (P), d_features_dc (P,3), d_features_rest (P,M_rest,3), d_mean2D (P,3) [screen-space, z = 0],
  * d_local_rot (J,4), d_global_trans (3), d_node_radius_raw (J); optional d_mask (P), d_mlp_weight (P,J-1),

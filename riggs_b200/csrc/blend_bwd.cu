@@ -136,8 +136,8 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendB
         const size_t HW = (size_t)a.H * a.W;
 #pragma unroll
         for (int c = 0; c < 3; c++) dL_dpixel[c] = a.dL_dpix[c * HW + pix_id];
-        dL_dpixel_depth = a.dL_dpix_depth[pix_id];
-        dL_dalpha = a.dL_dalphas[pix_id];
+        if (a.dL_dpix_depth) dL_dpixel_depth = a.dL_dpix_depth[pix_id];  // null: that output has no cotangent
+        if (a.dL_dalphas) dL_dalpha = a.dL_dalphas[pix_id];
     }
     ch.cpix[lane] = {dL_dpixel[0], dL_dpixel[1], dL_dpixel[2], dL_dpixel_depth};
     float last_alpha = 0, last_color[3] = {0, 0, 0}, last_depth = 0;

@@ -188,8 +188,8 @@ class _SkinnedRender(torch.autograd.Function):
         opts = dict(dtype=torch.float32, device=dev)
         z = lambda *s: torch.zeros(s, **opts)
         g_color = f32c(g_color) if g_color is not None else z(3, H, W)
-        g_depth = f32c(g_depth) if g_depth is not None else z(1, H, W)
-        g_alpha = f32c(g_alpha) if g_alpha is not None else z(1, H, W)
+        g_depth = f32c(g_depth) if g_depth is not None else None  # NULL = no cotangent (rg_skinned_backward)
+        g_alpha = f32c(g_alpha) if g_alpha is not None else None
         g_nodes = f32c(g_nodes) if g_nodes is not None else None
         go = ctx.grad_out or {}
 
