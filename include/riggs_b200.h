@@ -228,6 +228,20 @@ int rg_skinned_backward(const RgSkinnedScene* scene, const RgWorkspace* ws, cons
                         float* d_local_rot, float* d_global_trans, float* d_node_radius_raw, float* d_mask,
                         float* d_mlp_weight, float* d_offsets, rg_stream_t stream);
 
+/* ---- multi-GPU (no counterpart in the reference, which is single-GPU) -------------------------------- */
+
+/* In-place sum over `world` ranks of a gradient buffer that every rank has mapped at the multicast (NVLS multimem)
+ * address `multicast_base` (the host maps it, e.g. torch.distributed._symmetric_memory).  Each rank calls this with
+ * its own rank on its own stream, between two cross-rank barriers: all ranks have finished writing the buffer /
+ * all ranks' kernels have finished.  n_floats must be a multiple of 4 and the base 16-byte aligned.  Rank r reduces
+ * the r-th slice through the switch (multimem.ld_reduce) and broadcasts it to every copy (multimem.st). */
+int rg_allreduce_multimem(float* multicast_base, size_t n_floats, int rank, int world, rg_stream_t stream);
+
+/* The same in-place sum over plain peer-to-peer mappings: peer_bufs[r] (host array of `world` device pointers, world
+ * in {2, 4, 8}) is rank r's copy of the buffer as mapped into THIS process.  Rank r loads its slice from every copy,
+ * adds in rank order (bit-identical results on all ranks) and stores the sum into every copy.  Same barrier contract. */
+int rg_allreduce_p2p(float* const* peer_bufs, size_t n_floats, int rank, int world, rg_stream_t stream);
+
 /* ---- measurement aids (no counterpart in the reference; used by bench.py) ------------------------ */
 
 /* Kernels of this library launched since it was loaded (library sort passes are not counted). */

@@ -62,6 +62,8 @@ _SIGNATURES = {
     "rg_skin_backward": (C.c_int, [_i, _i] + [_p] * 19),
     "rg_l1_loss_scratch_bytes": (C.c_size_t, []),
     "rg_l1_loss": (C.c_int, [C.c_size_t, _p, _p, _p, _p, _p, C.c_size_t, _p]),
+    "rg_allreduce_multimem": (C.c_int, [_p, C.c_size_t, _i, _i, _p]),
+    "rg_allreduce_p2p": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t, _i, _i, _p]),
     "rg_launch_count": (C.c_longlong, []),
     "rg_profile_enable": (None, [_i]),
     "rg_profile_reset": (None, []),

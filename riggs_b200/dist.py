@@ -34,18 +34,49 @@ class FlatGrads:
     into the views (``render_skinned(..., grad_out=flat.views)``), ``all_reduce`` sums the buffer over the ranks in
     place, ``attach`` makes every ``param.grad`` a view of the reduced buffer."""
 
-    def __init__(self, named_params: Sequence[Tuple[str, torch.Tensor]], device=None):
+    def __init__(self, named_params: Sequence[Tuple[str, torch.Tensor]], device=None, peer_memory: bool = True):
+        """peer_memory: with NCCL on 2, 4 or 8 GPUs of one node the buffer is allocated as symmetric memory (every
+        rank's copy mapped into every process over NVLink) and ``all_reduce`` runs this library's own kernel
+        (rg_allreduce_p2p) between two device-side barriers instead of ncclAllReduce; anything else uses NCCL / gloo."""
         self.names = [n for n, _ in named_params]
         self.params = [p for _, p in named_params]
-        device = device if device is not None else self.params[0].device
+        device = torch.device(device if device is not None else self.params[0].device)
         total = sum(p.numel() for p in self.params)
-        self.flat = torch.zeros(total, dtype=torch.float32, device=device)
+        self.total = total
+        self.hdl = None
+        self._peer_ptrs = None
+        padded = (total + 3) // 4 * 4  # the peer kernel moves 16-byte words
+        if peer_memory and device.type == "cuda":
+            self._try_symmetric(padded, device)
+        if self.hdl is None:
+            self._storage = torch.zeros(padded, dtype=torch.float32, device=device)
+        self.flat = self._storage[:total]
         self.views: Dict[str, torch.Tensor] = {}
         off = 0
         for n, p in named_params:
             k = p.numel()
             self.views[n] = self.flat[off:off + k].view(p.shape)
             off += k
+
+    def _try_symmetric(self, padded: int, device):
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_backend() != "nccl":
+            return
+        if dist.get_world_size() not in (2, 4, 8):
+            return
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            group = dist.group.WORLD.group_name
+            t = symm_mem.empty(padded, dtype=torch.float32, device=device)
+            hdl = symm_mem.rendezvous(t, group)
+            t.zero_()
+            import ctypes as C
+            off = t.data_ptr() - hdl.buffer_ptrs[hdl.rank]
+            self._peer_ptrs = (C.c_void_p * hdl.world_size)(*[int(hdl.buffer_ptrs[r]) + off for r in range(hdl.world_size)])
+            self._storage, self.hdl = t, hdl
+        except Exception as e:  # no peer access / no symmetric-memory support: NCCL does the job
+            import warnings
+            warnings.warn(f"riggs_b200: symmetric memory unavailable ({e}); gradients are all-reduced by NCCL")
+            self.hdl = None
 
     def zero_(self):
         self.flat.zero_()
@@ -60,6 +91,16 @@ class FlatGrads:
 
     def all_reduce(self, average: bool = False, async_op: bool = False):
         if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+            return None
+        if self.hdl is not None and not async_op:
+            from . import _lib
+            hdl = self.hdl
+            hdl.barrier(channel=0)  # every rank's backward has written its copy
+            _lib.check(_lib.lib().rg_allreduce_p2p(self._peer_ptrs, self._storage.numel(), hdl.rank, hdl.world_size,
+                                                   _lib.stream_ptr()), "rg_allreduce_p2p")
+            hdl.barrier(channel=1)  # every rank's slice has arrived in every copy
+            if average:
+                self.flat.div_(dist.get_world_size())
             return None
         work = dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, async_op=async_op)
         if average and not async_op:

@@ -1,0 +1,147 @@
+// Forward alpha blend.  Replaces renderCUDA (dgr/cuda_rasterizer/forward.cu:261-381).
+//
+// The reference runs one 256-thread CTA per 16x16 tile: all threads walk the tile's whole depth-sorted list in
+// lock step (two __syncthreads per 256 instances) and every pixel evaluates every instance.  On B200 that shape is
+// latency-bound: the few heavy tiles of a frame decide the kernel's duration while most SMs idle.  Here the unit of
+// work is ONE WARP = one 8x4 pixel block, independent of the other seven blocks of its tile -- no block barrier, a
+// finished warp retires and frees its slot:
+//   * blend_common.cuh's ListWalker hands the warp, 128 list entries at a time, the instances whose alpha >= 1/255
+//     footprint can reach the block (exact-conservative test of cull.cuh), gathered with a two-deep prefetch;
+//   * the 32 pixels blend only those, in list order, with the reference's exact expressions (same power / alpha / T
+//     tests; a log-threshold pre-test avoids expf for pairs that are certainly below 1/255).  Four survivors are
+//     evaluated per iteration: their alphas are independent, only the short T / colour update is serial, so the
+//     expf latencies overlap instead of adding up;
+//   * the warp stops as soon as its 32 pixels are saturated (T < 1e-4) or the list ends.
+// Every warp re-reads the tile's list (8x the L2 reads of a cooperative staging; one frame's records fit in L2 several
+// times over) -- L2 bandwidth is plentiful here, latency and balance are not.
+#include "blend_common.cuh"
+#include "kernels.cuh"
+
+namespace rg {
+
+// Optional per-(tile, warp) cycle counters for performance analysis (rg_debug_tile_profile); null in production.
+__device__ uint32_t* g_fwd_tile_prof = nullptr;
+void set_fwd_tile_profile(uint32_t* p) { cudaMemcpyToSymbol(g_fwd_tile_prof, &p, sizeof(p)); }
+
+__global__ void __launch_bounds__(kBlendThreads) blend_forward_kernel(BlendFwdArgs a) {
+    constexpr int kPerLane = 4, kGroup = 32 * kPerLane;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tile = (int)a.tile_order[blockIdx.x >> 3], blk = blockIdx.x & 7;
+    const int tile_x = tile % a.grid_x, tile_y = tile / a.grid_x;
+    const int bx0 = (blk & 1) * kBlkW, by0 = (blk >> 1) * kBlkH;  // 2 blocks across, 4 down
+    const uint2 range = a.ranges[tile];
+    const int n_total = (int)(range.y - range.x);
+
+    __shared__ BlockPipe<kPerLane> bp;
+    pipe_init(bp);
+    __syncthreads();
+
+    if (warp == 1) {  // ---- filter warp
+        if (n_total == 0) return;
+        const float x0 = (float)(tile_x * RG_TILE + bx0), y0 = (float)(tile_y * RG_TILE + by0);
+        run_filter_warp<false, kPerLane>(a.point_list, a.rec, range.x, n_total, lane, x0, y0, x0 + (kBlkW - 1),
+                                         y0 + (kBlkH - 1), bp,
+                                         g_fwd_tile_prof ? g_fwd_tile_prof + ((size_t)tile * 8 + blk) * 8 : nullptr);
+        return;
+    }
+
+    // ---- blend warp: one pixel per lane
+    const uint2 pix = {(unsigned)(tile_x * RG_TILE + bx0 + (lane & 7)), (unsigned)(tile_y * RG_TILE + by0 + (lane >> 3))};
+    const uint32_t pix_id = a.W * pix.y + pix.x;
+    const float2 pixf = {(float)pix.x, (float)pix.y};
+    const bool inside = pix.x < (unsigned)a.W && pix.y < (unsigned)a.H;
+    bool done = !inside;
+    float T = 1.0f;
+    uint32_t last_contributor = 0;
+    float C0 = 0.f, C1 = 0.f, C2 = 0.f, weight = 0.f, D = 0.f;
+    uint32_t* const prof = g_fwd_tile_prof;
+    long long t_start = 0, t_wait = 0;
+    uint32_t n_list = 0, n_slots = 0;
+    if (prof) t_start = clock64();
+
+    RingReader ring;
+    while (n_total > 0) {
+        long long tw = 0;
+        if (prof) tw = clock64();
+        const int cnt = ring.acquire(bp);
+        if (prof) { t_wait += clock64() - tw; n_slots++; n_list += max(cnt, 0); }
+        if (cnt < 0) break;
+        const SurvStage<kPerLane>& st = bp.stage[ring.slot];
+        // Straight-line code, no per-lane branches: the warp that owns a heavy block is alone on the kernel's critical
+        // path, and what bounds it is the latency of its own dependent chain, not issue slots.  Entries that the
+        // reference would skip take alpha = 0 (T * (1 - 0) and C + 0 are exact), so only T -> test -> select is serial.
+        const int n_it = (cnt + 3) >> 2;
+        for (int it = 0; it < n_it; it++) {
+            const int l = it * 4;
+            float alpha[4];
+            float4 c[4];
+            int pos[4];
+            bool act[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int e = min(l + u, kGroup - 1);
+                const float4 x = st.xyts[e];
+                const float4 con_o = st.co[e];
+                c[u] = st.rgbd[e];
+                const float2 d = {x.x - pixf.x, x.y - pixf.y};
+                const float power = -0.5f * (con_o.x * d.x * d.x + con_o.z * d.y * d.y) - con_o.y * d.x * d.y;
+                alpha[u] = fminf(0.99f, con_o.w * expf(power));
+                // the reference skips power > 0 and alpha < 1/255; power < thr is certainly alpha < 1/255
+                act[u] = l + u < cnt && !(power > 0.0f) && !(power < x.z) && !(alpha[u] < 1.0f / 255.0f);
+                pos[u] = __float_as_int(x.w);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const float test_T = T * (1 - alpha[u]);
+                const bool live = act[u] && !done;
+                const bool stop = live && test_T < 0.0001f;
+                const bool add = live && !stop;
+                done = done || stop;
+                const float wa = add ? alpha[u] : 0.f;
+                const float cx = add ? c[u].x : 0.f, cy = add ? c[u].y : 0.f, cz = add ? c[u].z : 0.f;
+                const float cd = add ? c[u].w : 0.f;
+                C0 = C0 + cx * wa * T;
+                C1 = C1 + cy * wa * T;
+                C2 = C2 + cz * wa * T;
+                weight = weight + wa * T;
+                D = D + cd * wa * T;
+                // 1-based position in the tile's range, as the reference counts
+                last_contributor = add ? (uint32_t)pos[u] + 1 : last_contributor;
+                T = add ? test_T : T;
+            }
+        }
+        ring.release(bp, lane);
+        if (__all_sync(0xffffffffu, done)) {
+            if (lane == 0) {  // tell the filter warp, and wake it if it is parked on a full ring
+                *reinterpret_cast<volatile int*>(&bp.stop) = 1;
+                __threadfence_block();
+#pragma unroll
+                for (int s = 0; s < kStages; s++) mbar_arrive(&bp.empty[s]);
+            }
+            break;
+        }
+    }
+    if (inside) {
+        const size_t HW = (size_t)a.H * a.W;
+        a.n_contrib[pix_id] = last_contributor;
+        a.out_color[pix_id] = C0 + T * a.bg[0];
+        a.out_color[HW + pix_id] = C1 + T * a.bg[1];
+        a.out_color[2 * HW + pix_id] = C2 + T * a.bg[2];
+        a.out_alpha[pix_id] = weight;  // sum of alpha*T, as the reference (forward.cu:378)
+        a.out_depth[pix_id] = D;
+    }
+    if (prof && lane == 0) {
+        uint32_t* o = prof + ((size_t)tile * 8 + blk) * 8;
+        o[0] = (uint32_t)(clock64() - t_start); o[1] = (uint32_t)t_wait;
+        o[4] = n_list; o[5] = n_slots; o[6] = (uint32_t)n_total;
+    }
+}
+
+int launch_blend_forward(const BlendFwdArgs& a, cudaStream_t stream) {
+    const dim3 grid((unsigned)(a.grid_x * a.grid_y * 8), 1, 1);
+    LaunchScope ls("blend_forward", stream);
+    blend_forward_kernel<<<grid, kBlendThreads, 0, stream>>>(a);
+    return 0;
+}
+
+}  // namespace rg
