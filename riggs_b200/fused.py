@@ -165,6 +165,7 @@ class _SkinnedRender(torch.autograd.Function):
                     continue
                 pool.note_capacity(ws, dev)
                 break
+        ctx.set_materialize_grads(False)  # outputs the loss does not use arrive as None, not as zero-filled images
         ctx.scene_tensors = t  # keeps the contiguous copies alive
         ctx.scene = scene
         ctx.ws = ws
