@@ -311,8 +311,9 @@ def run_ours(args):
                                f"fwd+bwd", "P": P, "visible": vis, "R": R, "HW": H * W,
                    "l2": "inputs+state per step (~%d MB) exceed no L2 flush; working set streams through HBM" % (total_bytes >> 20),
                    "launch": "cuda graph replay" if gs is not None else "eager",
-                   "parallelism": (f"dp{world} over views, " + ("own peer-memory all-reduce kernel (rg_allreduce_p2p over NVLink, "
-                                   "symmetric memory)" if getattr(hp.flat, "hdl", None) is not None else "NCCL all-reduce") +
+                   "parallelism": (f"dp{world} over views, " + (("own all-reduce kernel over symmetric memory (" + ("rg_allreduce_multimem, NVLS" if getattr(hp.flat, "_mc_ptr", 0)
+                                                                                       else "rg_allreduce_p2p, NVLink peer loads/stores") + ")")
+                                   if getattr(hp.flat, "hdl", None) is not None else "NCCL all-reduce") +
                                    f" of {n_grad} grad floats") if world > 1 else "single GPU"},
         "e2e": {"value": round(world * args.steps / (ms_e2e / 1e3), 3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 4, "last_loss": last},
