@@ -100,9 +100,11 @@ __device__ __noinline__ void flush_chunk(BwdChunk& ch, int fill, int lane, float
 
 __global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendBwdArgs a) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int tile = (int)a.tile_order[blockIdx.x >> 2], strip = blockIdx.x & 3;
+    constexpr int kCtasPerTile = 8 / kBlendWarps;
+    const int tile = (int)a.tile_order[blockIdx.x / kCtasPerTile];
+    const int blk = (blockIdx.x % kCtasPerTile) * kBlendWarps + warp;  // 8x4 block of the tile: 2 across, 4 down
     const int tile_x = tile % a.grid_x, tile_y = tile / a.grid_x;
-    const int bx0 = warp * kBlkW, by0 = strip * kBlkH;
+    const int bx0 = (blk & 1) * kBlkW, by0 = (blk >> 1) * kBlkH;
     const uint2 pix = {(unsigned)(tile_x * RG_TILE + bx0 + (lane & 7)), (unsigned)(tile_y * RG_TILE + by0 + (lane >> 3))};
     const uint32_t pix_id = a.W * pix.y + pix.x;
     const float2 pixf = {(float)pix.x, (float)pix.y};
@@ -241,14 +243,14 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendB
         if (prof) n_flush++;
     }
     if (prof && lane == 0) {
-        uint32_t* o = prof + ((size_t)tile * 8 + strip * 2 + warp) * 8;
+        uint32_t* o = prof + ((size_t)tile * 8 + blk) * 8;
         o[0] = (uint32_t)(clock64() - t_start); o[1] = (uint32_t)walk.t_wait; o[2] = (uint32_t)walk.t_stage1;
         o[3] = (uint32_t)walk.t_stage2; o[4] = n_list; o[5] = n_groups; o[6] = n_flush; o[7] = 0;
     }
 }
 
 int launch_blend_backward(const BlendBwdArgs& a, cudaStream_t stream) {
-    const dim3 grid((unsigned)(a.grid_x * a.grid_y * 4), 1, 1);
+    const dim3 grid((unsigned)(a.grid_x * a.grid_y * (8 / kBlendWarps)), 1, 1);
     LaunchScope ls("blend_backward", stream);
     blend_backward_kernel<<<grid, kBlendWarps * 32, 0, stream>>>(a);
     return 0;

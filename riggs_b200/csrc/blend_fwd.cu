@@ -25,9 +25,11 @@ void set_fwd_tile_profile(uint32_t* p) { cudaMemcpyToSymbol(g_fwd_tile_prof, &p,
 
 __global__ void __launch_bounds__(kBlendWarps * 32) blend_forward_kernel(BlendFwdArgs a) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int tile = (int)a.tile_order[blockIdx.x >> 2], strip = blockIdx.x & 3;
+    constexpr int kCtasPerTile = 8 / kBlendWarps;
+    const int tile = (int)a.tile_order[blockIdx.x / kCtasPerTile];
+    const int blk = (blockIdx.x % kCtasPerTile) * kBlendWarps + warp;  // 8x4 block of the tile: 2 across, 4 down
     const int tile_x = tile % a.grid_x, tile_y = tile / a.grid_x;
-    const int bx0 = warp * kBlkW, by0 = strip * kBlkH;
+    const int bx0 = (blk & 1) * kBlkW, by0 = (blk >> 1) * kBlkH;
     const uint2 pix = {(unsigned)(tile_x * RG_TILE + bx0 + (lane & 7)), (unsigned)(tile_y * RG_TILE + by0 + (lane >> 3))};
     const uint32_t pix_id = a.W * pix.y + pix.x;
     const float2 pixf = {(float)pix.x, (float)pix.y};
@@ -111,13 +113,13 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_forward_kernel(BlendFw
         a.out_depth[pix_id] = D;
     }
     if (prof && lane == 0) {
-        uint32_t* o = prof + ((size_t)(tile_y * a.grid_x + tile_x) * 8 + strip * 2 + warp) * 8;
+        uint32_t* o = prof + ((size_t)(tile_y * a.grid_x + tile_x) * 8 + blk) * 8;
         o[0] = (uint32_t)(clock64() - t_start); o[1] = (uint32_t)walk.t_wait; o[2] = (uint32_t)walk.t_stage1; o[3] = (uint32_t)walk.t_stage2; o[4] = n_list; o[5] = n_seen; o[6] = walk.n; o[7] = 0;
     }
 }
 
 int launch_blend_forward(const BlendFwdArgs& a, cudaStream_t stream) {
-    const dim3 grid((unsigned)(a.grid_x * a.grid_y * 4), 1, 1);
+    const dim3 grid((unsigned)(a.grid_x * a.grid_y * (8 / kBlendWarps)), 1, 1);
     LaunchScope ls("blend_forward", stream);
     blend_forward_kernel<<<grid, kBlendWarps * 32, 0, stream>>>(a);
     return 0;
