@@ -193,7 +193,9 @@ typedef struct RgSkinnedScene {
 
 /* Caller-owned device scratch, reused across frames; nothing is allocated and the host never waits.
  * geom: rg_geom_bytes(P, width, height); image: rg_image_bytes(width, height); binning: any size -- it bounds
- * the number of (Gaussian, tile) instances a frame may produce (rg_binning_capacity). */
+ * the number of (Gaussian, tile) instances a frame may produce (rg_binning_capacity; 5 bytes per instance: the list
+ * and the forward blend's survivor bitmaps, laid out for the CAPACITY -- pass rg_binning_capacity(bytes) as num_rendered
+ * to the reference-shaped calls that are to read a workspace's binning buffer). */
 typedef struct RgWorkspace {
     char* geom;    size_t geom_bytes;
     char* image;   size_t image_bytes;

@@ -68,6 +68,9 @@ BinningState BinningState::carve(char* base, size_t R, size_t* bytes) {
     Carver c(base);
     BinningState b;
     b.point_list = c.take<uint32_t>(R);
+    b.surv_stride = (R + 31) / 32 + 2;
+    b.surv_mask_bytes = 8 * b.surv_stride * sizeof(uint32_t);
+    b.surv_mask = c.take<uint32_t>(b.surv_mask_bytes / 4);
     if (bytes) *bytes = align_up(c.off, 256) + 256;
     return b;
 }
@@ -168,7 +171,8 @@ int rg_rasterize_forward(rg_alloc_fn geom_alloc, void* geom_ctx, rg_alloc_fn bin
 
     BlendFwdArgs fa;
     fa.W = width; fa.H = height; fa.grid_x = grid_x; fa.grid_y = grid_y;
-    fa.ranges = img.ranges; fa.point_list = bin.point_list;
+    cudaMemsetAsync(bin.surv_mask, 0, bin.surv_mask_bytes, stream);
+    fa.ranges = img.ranges; fa.point_list = bin.point_list; fa.surv_mask = bin.surv_mask; fa.surv_stride = bin.surv_stride;
     fa.rec = geom.rec; fa.bg = background; fa.tile_order = geom.tile_order;
     fa.out_color = out_color; fa.out_depth = out_depth; fa.out_alpha = out_alpha; fa.n_contrib = img.n_contrib;
     launch_blend_forward(fa, stream);
@@ -206,7 +210,7 @@ int rg_rasterize_backward(int P, int D, int M, int R, const float* background, i
     cudaMemsetAsync(acc, 0, sizeof(float) * 10 * (size_t)P, stream);
     BlendBwdArgs ba;
     ba.P = P; ba.W = width; ba.H = height; ba.grid_x = grid_x; ba.grid_y = grid_y;
-    ba.ranges = img.ranges; ba.point_list = bin.point_list; ba.bg = background;
+    ba.ranges = img.ranges; ba.point_list = bin.point_list; ba.surv_mask = bin.surv_mask; ba.surv_stride = bin.surv_stride; ba.bg = background;
     ba.rec = geom.rec; ba.tile_order = geom.tile_order;
     ba.alphas = alphas; ba.n_contrib = img.n_contrib; ba.dL_dpix = dL_dpix;
     ba.dL_dpix_depth = dL_dpix_depth; ba.dL_dalphas = dL_dalphas; ba.grad_acc = acc;

@@ -52,7 +52,7 @@ extern "C" {
 
 uint32_t rg_binning_capacity(size_t binning_bytes) {
     if (binning_bytes < 1024) return 0;
-    size_t n = (binning_bytes - 512) / 4;
+    size_t n = (binning_bytes - 1024) / 5;  // 4 bytes of list + 1 byte of survivor mask per instance
     return n > 0xfffffff0u ? 0xfffffff0u : (uint32_t)n;
 }
 
@@ -99,7 +99,8 @@ int rg_skinned_forward(const RgSkinnedScene* s, const RgWorkspace* w, float* out
 
     BlendFwdArgs fa;
     fa.W = W; fa.H = H; fa.grid_x = grid_x; fa.grid_y = grid_y;
-    fa.ranges = img.ranges; fa.point_list = bin.point_list; fa.rec = geom.rec; fa.tile_order = geom.tile_order;
+    cudaMemsetAsync(bin.surv_mask, 0, bin.surv_mask_bytes, stream);
+    fa.ranges = img.ranges; fa.point_list = bin.point_list; fa.surv_mask = bin.surv_mask; fa.surv_stride = bin.surv_stride; fa.rec = geom.rec; fa.tile_order = geom.tile_order;
     fa.bg = s->background;
     fa.out_color = out_color; fa.out_depth = out_depth; fa.out_alpha = out_alpha; fa.n_contrib = img.n_contrib;
     launch_blend_forward(fa, stream);
@@ -137,7 +138,7 @@ int rg_skinned_backward(const RgSkinnedScene* s, const RgWorkspace* w, const int
 
     BlendBwdArgs ba;
     ba.P = P; ba.W = W; ba.H = H; ba.grid_x = grid_x; ba.grid_y = grid_y;
-    ba.ranges = img.ranges; ba.point_list = bin.point_list; ba.bg = s->background;
+    ba.ranges = img.ranges; ba.point_list = bin.point_list; ba.surv_mask = bin.surv_mask; ba.surv_stride = bin.surv_stride; ba.bg = s->background;
     ba.rec = geom.rec; ba.tile_order = geom.tile_order; ba.alphas = alphas;
     ba.n_contrib = img.n_contrib; ba.dL_dpix = dL_dcolor; ba.dL_dpix_depth = dL_ddepth; ba.dL_dalphas = dL_dalpha;
     ba.grad_acc = geom.grad_acc;

@@ -121,12 +121,10 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendB
     __shared__ BwdChunk s_chunk[kBlendWarps];
     WarpStage<kPerLane>& st = s_stage[warp];
     BwdChunk& ch = s_chunk[warp];
-    ListWalker<true, kPerLane> walk;
-    walk.pl = a.point_list; walk.rec = a.rec; walk.first = a.ranges[tile].x; walk.n = total;
+    MaskWalker<kPerLane> walk;
+    walk.pl = a.point_list; walk.rec = a.rec; walk.surv_bits = a.surv_mask + (size_t)blk * a.surv_stride; walk.first = a.ranges[tile].x; walk.n = total;
     walk.lane = lane;
     const float ox = (float)(tile_x * RG_TILE + bx0), oy = (float)(tile_y * RG_TILE + by0);  // block origin (pixel centres)
-    walk.x0 = ox; walk.y0 = oy;
-    walk.x1 = ox + (kBlkW - 1); walk.y1 = oy + (kBlkH - 1);
     const int n_groups = (total + kGroup - 1) / kGroup;
     walk.begin(st);
 

@@ -31,6 +31,7 @@ struct __align__(16) WarpStage {
     uint32_t cand_id[kGroup];
     uint32_t id[kGroup];  // Gaussian id of each stage-2 survivor
     uint8_t cand_k[kGroup];  // position in the group of each candidate
+    uint32_t bits[kPerLane + 2];  // survivor bits of the group being filtered (forward)
 };
 
 // REVERSE = false: entries first, first+1, ...   (forward blend: front to back)
@@ -44,6 +45,8 @@ struct ListWalker {
     uint32_t first;
     int n, lane;
     float x0, y0, x1, y1;
+    uint32_t* surv_bits = nullptr;  // if set (forward): this block's bitmap over the instance list, one bit per entry,
+                                    // raised for every survivor; the backward blend walks by these bits
     static constexpr uint32_t kNone = 0xffffffffu;
     bool timing = false;  // performance analysis only (rg_debug_tile_profile)
     long long t_wait = 0, t_stage1 = 0, t_stage2 = 0;
@@ -107,6 +110,7 @@ struct ListWalker {
         const unsigned lt = (1u << lane) - 1;
         long long tt = 0;
         if (timing) tt = clock64();
+        if (surv_bits && lane < kPerLane + 2) st.bits[lane] = 0;
         __syncwarp();  // every lane is done reading the previous group's survivors
         // ---- finish stage 2 of group g
         int nsurv = 0;
@@ -135,10 +139,17 @@ struct ListWalker {
                 st.co[slot] = co;
                 st.rgbd[slot] = rgbd;
                 st.id[slot] = id;
+                if (surv_bits) atomicOr(&st.bits[((first & 31u) + (uint32_t)k) >> 5], 1u << ((first + (uint32_t)k) & 31u));
             }
             nsurv += __popc(m);
         }
         __syncwarp();
+        if (surv_bits && nsurv > 0 && lane < kPerLane + 2) {
+            // list index of walk position p is first + p (forward walks only); kGroup is a multiple of 32, so the group's
+            // bits start at bit (first & 31) of word (first >> 5) + g * kPerLane.  Neighbouring tiles share boundary words.
+            const uint32_t wbits = st.bits[lane];
+            if (wbits) atomicOr(surv_bits + (first >> 5) + (uint32_t)(g * kPerLane + lane), wbits);
+        }
         if (timing) {
             const long long t = clock64();
             t_stage2 += t - tt;
@@ -159,6 +170,106 @@ struct ListWalker {
                 r0_1[j] = load_r0(id_2[j]);
                 id_2[j] = load_id((g + 3) * kGroup + j * 32 + lane);
             }
+            if (timing) t_stage1 += clock64() - tt;
+        } else {
+            ncand = 0;
+        }
+        return nsurv;
+    }
+};
+
+// Backward-direction walker over the survivor bits the forward blend left behind: the entries of the tile's list
+// whose byte has bit `blk` set are exactly those the forward walker kept for this block, so neither the bounding-box
+// nor the ellipse test is repeated, and records are fetched for survivors only.  Walk position p is list entry
+// first + n - 1 - p.  Same interface and the same stage buffer as ListWalker.
+template <int kPerLane>
+struct MaskWalker {
+    static constexpr int kGroup = 32 * kPerLane;
+    using Stage = WarpStage<kPerLane>;
+    const uint32_t* pl;
+    const float4* rec;
+    const uint32_t* surv_bits;  // this block's bitmap (see ListWalker::surv_bits)
+    uint32_t first;
+    int n, lane;
+    static constexpr uint32_t kNone = 0xffffffffu;
+    bool timing = false;
+    long long t_wait = 0, t_stage1 = 0, t_stage2 = 0;
+
+    uint32_t id_1[kPerLane];   // list entries of the next group (in flight)
+    uint32_t bit_1[kPerLane];  // their survivor bits
+    int ncand;
+    float4 p_r0, p_co, p_rgbd, p_tail;  // this lane's pending record (in flight)
+
+    __device__ __forceinline__ void load_group(int g) {
+#pragma unroll
+        for (int j = 0; j < kPerLane; j++) {
+            const int p = g * kGroup + j * 32 + lane;
+            id_1[j] = kNone;
+            bit_1[j] = 0;
+            if (p < n) {
+                const uint32_t at = first + (uint32_t)(n - 1 - p);
+                id_1[j] = pl[at];
+                bit_1[j] = (surv_bits[at >> 5] >> (at & 31u)) & 1u;
+            }
+        }
+    }
+    __device__ __forceinline__ void stage1(Stage& st) {
+        const unsigned lt = (1u << lane) - 1;
+        ncand = 0;
+#pragma unroll
+        for (int j = 0; j < kPerLane; j++) {
+            const bool pass = bit_1[j] != 0;
+            const unsigned m = __ballot_sync(0xffffffffu, pass);
+            if (pass) {
+                const int slot = ncand + __popc(m & lt);
+                st.cand_id[slot] = id_1[j];
+                st.cand_k[slot] = (uint8_t)(j * 32 + lane);
+            }
+            ncand += __popc(m);
+        }
+        __syncwarp();
+        if (lane < ncand) {
+            const float4* r = rec + 4 * (size_t)st.cand_id[lane];
+            p_r0 = r[0]; p_co = r[1]; p_rgbd = r[2]; p_tail = r[3];
+        }
+    }
+    __device__ __forceinline__ void begin(Stage& st) {
+        load_group(0);
+        stage1(st);
+        load_group(1);
+    }
+    __device__ __forceinline__ int next(int g, Stage& st) {
+        long long tt = 0;
+        if (timing) tt = clock64();
+        __syncwarp();  // every lane is done reading the previous group's survivors
+        for (int c0 = 0; c0 < ncand; c0 += 32) {
+            const int c = c0 + lane;
+            if (c < ncand) {
+                const uint32_t id = st.cand_id[c];
+                const int k = st.cand_k[c];
+                float4 a, co, rgbd, tail;
+                if (c0 == 0) {
+                    a = p_r0; co = p_co; rgbd = p_rgbd; tail = p_tail;
+                } else {  // more than 32 survivors in one group: not pipelined
+                    const float4* r = rec + 4 * (size_t)id;
+                    a = r[0]; co = r[1]; rgbd = r[2]; tail = r[3];
+                }
+                st.xyts[c] = {a.x, a.y, tail.y, __int_as_float(g * kGroup + k)};
+                st.co[c] = co;
+                st.rgbd[c] = rgbd;
+                st.id[c] = id;
+            }
+        }
+        const int nsurv = ncand;
+        __syncwarp();
+        if (timing) {
+            const long long t = clock64();
+            t_stage2 += t - tt;
+            tt = t;
+        }
+        if ((g + 1) * kGroup < n) {
+            stage1(st);
+            load_group(g + 2);
             if (timing) t_stage1 += clock64() - tt;
         } else {
             ncand = 0;

@@ -44,6 +44,7 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_forward_kernel(BlendFw
     walk.pl = a.point_list; walk.rec = a.rec; walk.first = range.x; walk.n = (int)(range.y - range.x); walk.lane = lane;
     walk.x0 = (float)(tile_x * RG_TILE + bx0); walk.y0 = (float)(tile_y * RG_TILE + by0);
     walk.x1 = walk.x0 + (kBlkW - 1); walk.y1 = walk.y0 + (kBlkH - 1);
+    walk.surv_bits = a.surv_mask + (size_t)blk * a.surv_stride;
     const int n_groups = (walk.n + kGroup - 1) / kGroup;
 
     float T = 1.0f;

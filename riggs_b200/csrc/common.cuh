@@ -79,6 +79,10 @@ struct ImageState {
 
 struct BinningState {
     uint32_t* point_list;  // R instance ids: grouped by tile, depth-ordered inside a tile
+    uint32_t* surv_mask;   // eight bitmaps over the instance list, one per 8x4 block of a tile (surv_stride words each):
+                           // bit set when the forward blend found that the instance can reach that block of its
+                           // tile; the backward blend walks by these bits
+    size_t surv_mask_bytes, surv_stride;
     static BinningState carve(char* base, size_t R, size_t* bytes);
 };
 

@@ -116,6 +116,9 @@ struct BlendFwdArgs {
     const uint32_t* point_list;
     const float4* rec;  // packed splat records (cull.cuh)
     const uint32_t* tile_order;
+    uint32_t* surv_mask;  // written: eight bitmaps over the instance list (one per 8x4 block of a tile, surv_stride words
+                          // apart): bit set = the instance can reach that block (zeroed by the launcher's caller)
+    size_t surv_stride;
     const float* bg;
     float* out_color;
     float* out_depth;
@@ -131,6 +134,8 @@ struct BlendBwdArgs {
     const float* bg;
     const float4* rec;
     const uint32_t* tile_order;
+    const uint32_t* surv_mask;  // the forward blend's survivor bitmaps
+    size_t surv_stride;
     const float* alphas;
     const uint32_t* n_contrib;
     const float* dL_dpix;

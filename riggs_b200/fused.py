@@ -59,7 +59,7 @@ class WorkspacePool:
         nbytes = self.capacity_bytes.get(key, 0)
         fresh = nbytes == 0
         if fresh:
-            nbytes = self.initial_bytes or (max(4 * 8 * P, 1 << 20) + 1024)
+            nbytes = self.initial_bytes or int(_lib.lib().rg_binning_bytes(max(8 * P, 1 << 18)))
         return _Workspace(P, W, H, device, nbytes), fresh
 
     def release(self, ws, device):
@@ -156,7 +156,7 @@ class _SkinnedRender(torch.autograd.Function):
                     break
                 torch.cuda.current_stream().synchronize()  # first frame of this shape only
                 R, overflow = int(ws.status[0]), int(ws.status[1])
-                want = int(4 * R * pool.headroom) + 1024
+                want = int(_lib.lib().rg_binning_bytes(int(R * pool.headroom) + 256))
                 if overflow or ws.binning.numel() < want:
                     # too small (or no headroom for the coming frames): grow and render this first frame again,
                     # so the instance list the backward will read lives in the buffer the workspace keeps

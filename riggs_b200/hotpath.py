@@ -209,7 +209,8 @@ class GraphedStep:
         if ws is not None and self._event is not None and self._event.query() and int(ws.status[1]) != 0:
             import warnings
             warnings.warn("riggs_b200: the previous frame overflowed the instance buffer; re-capturing with a larger one")
-            ws.grow_binning(int(4 * int(ws.status[0]) * self.pool.headroom) + 1024)
+            from . import _lib
+            ws.grow_binning(int(_lib.lib().rg_binning_bytes(int(int(ws.status[0]) * self.pool.headroom) + 256)))
             self.pool.note_capacity(ws, self.hp.device)
             self._capture()
         self._take_staged()

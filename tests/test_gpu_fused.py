@@ -122,10 +122,14 @@ def test_fused_matches_unfused(name, over):
     # Gradients of this rasterizer are ill-conditioned in fp32: one ulp on a rotation moves the REFERENCE's own
     # gradients by 3e-4..5e-4 (measured, scratch/diag2.py).  So the backward kernels are compared on the SAME forward
     # state: the reference-shaped backward runs on the fused call's workspace (same buffer layout).
+    # the fused workspace lays its binning buffer out for its CAPACITY (the survivor mask sits behind the list), so the
+    # reference-shaped backward is told that number where it expects num_rendered
+    from riggs_b200 import _lib
+    cap = int(_lib.lib().rg_binning_capacity(ws.binning.numel()))
     gm2, _gc, gop, gm3, _gcov, gsh, gsc, grot = _C.rasterize_gaussians_backward(
         bg, means_f, out_f["radii"], e, dbg["scales"], dbg["rotations"], 1.0, e, cam.world_view_transform,
         cam.full_proj_transform, tfx, tfy, cots[0], cots[1], cots[2], shs.detach().contiguous(), 3, cam.camera_center,
-        ws.geom, R, ws.binning, ws.image, out_f["alpha"].detach(), False)
+        ws.geom, cap, ws.binning, ws.image, out_f["alpha"].detach(), False)
     torch.autograd.backward([means3D, scales, rots, opac, shs, d_nodes], [gm3, gsc, grot, gop, gsh, cot_nodes])
     g_u, g_u_opt = grads(pose, mlp, off, gm2)
 
