@@ -293,9 +293,9 @@ def run_ours(args):
             for k, v in prof.items()}
     dom = max(kern, key=lambda k: kern[k]["ms_per_step"]) if kern else None
     # dram__bytes_read.sum + dram__bytes_write.sum per launch from the one `ncu --set full` capture of this workload
-    # (profiles/r1_s_full_raw.csv, C0 on one B200); other workloads have no capture -> null
-    ncu_traffic = {"blend_backward": 22869760, "blend_forward": 14178304, "gauss_skin_backward": 121955072,
-                   "skin_preprocess": 79004416} if args.workload == "C0" and not args.isotropic else {}
+    # (profiles/r1_t_full_raw.csv, C0 on one B200); other workloads have no capture -> null
+    ncu_traffic = {"blend_backward": 17084416, "blend_forward": 14722304, "gauss_skin_backward": 122528256,
+                   "skin_preprocess": 78285056} if args.workload == "C0" and not args.isotropic else {}
     roof = None
     if dom:
         b = per.get(dom, 0)
