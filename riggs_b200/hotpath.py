@@ -10,7 +10,7 @@ import torch
 
 from . import skeleton_warp as sw
 from .gaussian_renderer import GaussianParams, render
-from .loss_utils import l1_loss
+from .loss_utils import l1_loss, l1_loss_and_grad  # noqa: F401
 
 
 class _Pipe:
@@ -86,9 +86,9 @@ class HotPath:
     def step(self, cam, pose, target: torch.Tensor) -> torch.Tensor:
         """Forward + backward of one view; returns the (device) loss.  Gradients accumulate in .grad."""
         out = self.forward(cam, pose)
-        loss = l1_loss(out["render"], target)
-        loss.backward()
-        return loss.detach()
+        loss, grad = l1_loss_and_grad(out["render"], target)  # one kernel: the loss and d loss / d image
+        out["render"].backward(grad)
+        return loss
 
 
 class GraphedStep:

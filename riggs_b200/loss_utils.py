@@ -49,6 +49,25 @@ class _L1Loss(torch.autograd.Function):
         return d, (-d if ctx.need_gt else None)
 
 
+def l1_loss_and_grad(network_output: torch.Tensor, gt: torch.Tensor):
+    """(mean |network_output - gt|, d loss / d network_output) from one kernel launch, outside autograd: a training
+    step whose only loss is L1 can feed the gradient straight to ``network_output.backward(grad)`` and skip the
+    image-sized multiply by the upstream 1.0 that autograd would run."""
+    if not network_output.is_cuda:
+        raise _lib.RiggsError("l1_loss needs CUDA tensors; riggs_b200 has no CPU path")
+    if network_output.shape != gt.shape:
+        raise ValueError(f"l1_loss: shapes differ: {tuple(network_output.shape)} vs {tuple(gt.shape)}")
+    with torch.no_grad():
+        a, b = f32c(network_output.detach()), f32c(gt.detach())
+        loss = torch.empty((), dtype=torch.float32, device=a.device)
+        grad = torch.empty_like(a)
+        sc = _scratch(a.device)
+        with torch.cuda.device(a.device):
+            check(_lib.lib().rg_l1_loss(a.numel(), ptr(a), ptr(b), ptr(loss), ptr(grad), ptr(sc), sc.numel(), stream_ptr()),
+                  "rg_l1_loss")
+    return loss, grad
+
+
 def l1_loss(network_output: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:
     """mean |network_output - gt| (utils/loss_utils.py l1_loss); the gradient is produced by the same kernel."""
     return _L1Loss.apply(network_output, gt)
