@@ -152,3 +152,37 @@ def test_l1_loss_matches_torch(shape):
         want = torch.sign(a.detach() - b) * (1.0 / a.numel()) * 2.0
         assert torch.equal(a.grad, want.float())
     assert losses[0] == losses[1]
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_allreduce_p2p_kernel_on_one_device(world):
+    """rg_allreduce_p2p with every 'rank' on this GPU (its peers' buffers are then ordinary local pointers): after each
+    rank has reduced its slice, every copy holds the sum in rank order -- bit-identical on all ranks."""
+    import ctypes as C
+    from riggs_b200 import _lib
+    n = 4 * 12345 + 4 * 3  # not a multiple of world * 4
+    g = torch.Generator().manual_seed(world)
+    bufs = [torch.randn(n, generator=g).cuda() for _ in range(world)]
+    want = bufs[0].clone()
+    for b in bufs[1:]:
+        want = want + b
+    arr = (C.c_void_p * world)(*[b.data_ptr() for b in bufs])
+    L = _lib.lib()
+    for r in range(world):
+        _lib.check(L.rg_allreduce_p2p(arr, n, r, world, _lib.stream_ptr()), "rg_allreduce_p2p")
+    torch.cuda.synchronize()
+    for b in bufs:
+        assert torch.equal(b, want)
+    assert L.rg_allreduce_p2p(arr, n + 1, 0, world, _lib.stream_ptr()) < 0  # length must be a multiple of 4 floats
+    assert L.rg_allreduce_p2p(arr, n, 0, 3, _lib.stream_ptr()) < 0
+
+
+def test_l1_loss_and_grad_outside_autograd():
+    from riggs_b200.loss_utils import l1_loss, l1_loss_and_grad
+    g = torch.Generator().manual_seed(9)
+    a = torch.rand(3, 64, 48, generator=g).cuda().requires_grad_(True)
+    b = torch.rand(3, 64, 48, generator=g).cuda()
+    loss, grad = l1_loss_and_grad(a, b)
+    ref = l1_loss(a, b)
+    ref.backward()
+    assert float(loss) == float(ref.detach()) and torch.equal(grad, a.grad) and not loss.requires_grad
