@@ -230,6 +230,17 @@ int rg_skinned_backward(const RgSkinnedScene* scene, const RgWorkspace* ws, cons
                         float* d_local_rot, float* d_global_trans, float* d_node_radius_raw, float* d_mask,
                         float* d_mlp_weight, float* d_offsets, rg_stream_t stream);
 
+/* rg_skinned_backward in parts, for callers that overlap the gradient all-reduce with the backward: `phases` is a bit
+ * set -- 1: zero the accumulators and run the blend backward, 2: per-Gaussian backward (parameter gradients) of rows
+ * [row_begin, row_end) only (row_begin a multiple of 256), 4: skeleton backward (d_local_rot, d_global_trans,
+ * d_node_radius_raw).  Running 1, then 2 over consecutive row chunks, then 4 equals rg_skinned_backward. */
+int rg_skinned_backward_part(const RgSkinnedScene* scene, const RgWorkspace* ws, int phases, int row_begin, int row_end,
+                             const int* radii, const float* alphas, const float* dL_dcolor, const float* dL_ddepth,
+                             const float* dL_dalpha, const float* dL_dnodes, float* d_xyz, float* d_scaling_raw,
+                             float* d_rotation_raw, float* d_opacity_raw, float* d_features_dc, float* d_features_rest,
+                             float* d_mean2D, float* d_local_rot, float* d_global_trans, float* d_node_radius_raw,
+                             float* d_mask, float* d_mlp_weight, float* d_offsets, rg_stream_t stream);
+
 /* ---- multi-GPU (no counterpart in the reference, which is single-GPU) -------------------------------- */
 
 /* In-place sum over `world` ranks of a gradient buffer that every rank has mapped at the multicast (NVLS multimem)
@@ -243,6 +254,12 @@ int rg_allreduce_multimem(float* multicast_base, size_t n_floats, int rank, int 
  * in {2, 4, 8}) is rank r's copy of the buffer as mapped into THIS process.  Rank r loads its slice from every copy,
  * adds in rank order (bit-identical results on all ranks) and stores the sum into every copy.  Same barrier contract. */
 int rg_allreduce_p2p(float* const* peer_bufs, size_t n_floats, int rank, int world, rg_stream_t stream);
+
+/* Both kernels over several ranges of the buffer in one launch (offsets / lengths in floats, multiples of 4, at most 8
+ * ranges): multicast_base != NULL selects the NVLS kernel, else peer_bufs.  `blocks` CTAs of 512 threads (0: one per
+ * SM) -- a small grid leaves room for a kernel running beside it.  Same barrier contract. */
+int rg_allreduce_ranges(float* const* peer_bufs, float* multicast_base, int n_ranges, const size_t* offsets,
+                        const size_t* lengths, int rank, int world, int blocks, rg_stream_t stream);
 
 /* ---- measurement aids (no counterpart in the reference; used by bench.py) ------------------------ */
 

@@ -58,12 +58,14 @@ _SIGNATURES = {
     "rg_skinned_forward": (C.c_int, [_p, _p] + [_p] * 9),
     "rg_skinned_status": (C.c_int, [_p, _p, _p, _p]),
     "rg_skinned_backward": (C.c_int, [_p, _p] + [_p] * 20),
+    "rg_skinned_backward_part": (C.c_int, [_p, _p, _i, _i, _i] + [_p] * 20),
     "rg_skin_forward": (C.c_int, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _p]),
     "rg_skin_backward": (C.c_int, [_i, _i] + [_p] * 19),
     "rg_l1_loss_scratch_bytes": (C.c_size_t, []),
     "rg_l1_loss": (C.c_int, [C.c_size_t, _p, _p, _p, _p, _p, C.c_size_t, _p]),
     "rg_allreduce_multimem": (C.c_int, [_p, C.c_size_t, _i, _i, _p]),
     "rg_allreduce_p2p": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t, _i, _i, _p]),
+    "rg_allreduce_ranges": (C.c_int, [C.POINTER(C.c_void_p), _p, _i, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t), _i, _i, _i, _p]),
     "rg_launch_count": (C.c_longlong, []),
     "rg_profile_enable": (None, [_i]),
     "rg_profile_reset": (None, []),

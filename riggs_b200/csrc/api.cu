@@ -218,6 +218,7 @@ int rg_rasterize_backward(int P, int D, int M, int R, const float* background, i
     if (check_launch("blend_backward", stream, dbg)) return -1;
 
     GaussBwdArgs ga;
+    ga.row_begin = 0; ga.row_end = 0;
     ga.P = P; ga.D = D; ga.M = M; ga.means3D = means3D; ga.radii = radii; ga.shs = shs; ga.clamped = geom.clamped;
     ga.scales = scales; ga.rotations = rotations; ga.scale_modifier = scale_modifier;
     ga.cov3D = cov3D_precomp;  // with scales/rotations the covariance is recomputed in registers

@@ -116,16 +116,23 @@ int rg_skinned_status(const RgSkinnedScene* s, const RgWorkspace* w, uint32_t* h
     return 0;
 }
 
-int rg_skinned_backward(const RgSkinnedScene* s, const RgWorkspace* w, const int* radii, const float* alphas,
-                        const float* dL_dcolor, const float* dL_ddepth, const float* dL_dalpha, const float* dL_dnodes,
-                        float* d_xyz, float* d_scaling_raw, float* d_rotation_raw, float* d_opacity_raw,
-                        float* d_features_dc, float* d_features_rest, float* d_mean2D, float* d_local_rot,
-                        float* d_global_trans, float* d_node_radius_raw, float* d_mask, float* d_mlp_weight,
-                        float* d_offsets, rg_stream_t stream_) {
+// phases: 1 = zero the accumulators + blend backward, 2 = per-Gaussian backward of rows [row_begin, row_end),
+// 4 = skeleton backward.  rg_skinned_backward runs 1|2|4 over all rows; a data-parallel caller runs 1, then 2 chunk by
+// chunk (all-reducing each chunk's finished gradient rows on another stream meanwhile), then 4.
+int rg_skinned_backward_part(const RgSkinnedScene* s, const RgWorkspace* w, int phases, int row_begin, int row_end,
+                             const int* radii, const float* alphas, const float* dL_dcolor, const float* dL_ddepth,
+                             const float* dL_dalpha, const float* dL_dnodes, float* d_xyz, float* d_scaling_raw,
+                             float* d_rotation_raw, float* d_opacity_raw, float* d_features_dc, float* d_features_rest,
+                             float* d_mean2D, float* d_local_rot, float* d_global_trans, float* d_node_radius_raw,
+                             float* d_mask, float* d_mlp_weight, float* d_offsets, rg_stream_t stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     if (check_scene(s, w, "rg_skinned_backward")) return -1;
     if (!al16(d_rotation_raw)) { set_error("rg_skinned_backward: d_rotation_raw must be 16-byte aligned"); return -1; }
     const int P = s->P, W = s->width, H = s->height;
+    if ((phases & 2) && (row_begin < 0 || row_end > P || row_begin > row_end || (row_begin & 255))) {
+        set_error("rg_skinned_backward_part: rows must lie in [0, P] and row_begin must be a multiple of 256");
+        return -1;
+    }
     const int grid_x = (W + RG_TILE - 1) / RG_TILE, grid_y = (H + RG_TILE - 1) / RG_TILE;
     GeomState geom = GeomState::carve(abase(w->geom), P, W, H, nullptr);
     ImageState img = ImageState::carve(abase(w->image), W, H, nullptr);
@@ -133,39 +140,56 @@ int rg_skinned_backward(const RgSkinnedScene* s, const RgWorkspace* w, const int
     BinningState bin = BinningState::carve(abase(w->binning), cap, nullptr);
     FkSlots fk(geom.fk);
 
-    cudaMemsetAsync(geom.grad_acc, 0, sizeof(float) * 10 * (size_t)P, stream);
-    cudaMemsetAsync(fk.dG, 0, sizeof(float) * (128 * 12 + 128 + 4), stream);
+    if (phases & 1) {
+        cudaMemsetAsync(geom.grad_acc, 0, sizeof(float) * 10 * (size_t)P, stream);
+        cudaMemsetAsync(fk.dG, 0, sizeof(float) * (128 * 12 + 128 + 4), stream);
 
-    BlendBwdArgs ba;
-    ba.P = P; ba.W = W; ba.H = H; ba.grid_x = grid_x; ba.grid_y = grid_y;
-    ba.ranges = img.ranges; ba.point_list = bin.point_list; ba.surv_mask = bin.surv_mask; ba.surv_stride = bin.surv_stride; ba.bg = s->background;
-    ba.rec = geom.rec; ba.tile_order = geom.tile_order; ba.alphas = alphas;
-    ba.n_contrib = img.n_contrib; ba.dL_dpix = dL_dcolor; ba.dL_dpix_depth = dL_ddepth; ba.dL_dalphas = dL_dalpha;
-    ba.grad_acc = geom.grad_acc;
-    launch_blend_backward(ba, stream);
-
-    GaussBwdArgs ga = {};
-    ga.P = P; ga.D = s->sh_degree; ga.M = s->M_rest + 1; ga.means3D = geom.means3D; ga.radii = radii;
-    ga.clamped = geom.clamped; ga.scale_modifier = s->scale_modifier;
-    ga.viewmatrix = s->viewmatrix; ga.projmatrix = s->projmatrix; ga.campos = s->campos; ga.W = W; ga.H = H;
-    ga.tan_fovx = s->tan_fovx; ga.tan_fovy = s->tan_fovy;
-    ga.focal_y = H / (2.0f * s->tan_fovy); ga.focal_x = W / (2.0f * s->tan_fovx);
-    ga.grad_acc = geom.grad_acc; ga.dL_dmean2D = d_mean2D;
-    SkinFuseBwdArgs sb = {};
-    sb.f = fuse_args(s, geom, fk);
-    sb.d_rot_saved = geom.d_rot;
-    sb.d_xyz = d_xyz; sb.d_scaling_raw = d_scaling_raw; sb.d_rotation_raw = d_rotation_raw; sb.d_opacity_raw = d_opacity_raw;
-    sb.d_features_dc = d_features_dc; sb.d_features_rest = d_features_rest;
-    sb.dG = fk.dG; sb.dnode_radius_raw = fk.dradius; sb.dglobal_trans = fk.dtrans;
-    sb.dmask = d_mask; sb.dmlp_weight = d_mlp_weight; sb.doffsets = d_offsets;
-    if (launch_gauss_skin_backward(ga, sb, stream)) return -1;
-
-    if (launch_fk_backward(1, s->J, s->local_rot, s->joints, s->parents, fk.G, fk.dG, dL_dnodes, d_local_rot, d_global_trans,
-                           fk.dtrans, stream))
-        return -1;
-    if (d_node_radius_raw)
-        cudaMemcpyAsync(d_node_radius_raw, fk.dradius, sizeof(float) * s->J, cudaMemcpyDeviceToDevice, stream);
+        BlendBwdArgs ba;
+        ba.P = P; ba.W = W; ba.H = H; ba.grid_x = grid_x; ba.grid_y = grid_y;
+        ba.ranges = img.ranges; ba.point_list = bin.point_list; ba.surv_mask = bin.surv_mask; ba.surv_stride = bin.surv_stride;
+        ba.bg = s->background;
+        ba.rec = geom.rec; ba.tile_order = geom.tile_order; ba.alphas = alphas;
+        ba.n_contrib = img.n_contrib; ba.dL_dpix = dL_dcolor; ba.dL_dpix_depth = dL_ddepth; ba.dL_dalphas = dL_dalpha;
+        ba.grad_acc = geom.grad_acc;
+        launch_blend_backward(ba, stream);
+    }
+    if ((phases & 2) && row_end > row_begin) {
+        GaussBwdArgs ga = {};
+        ga.P = P; ga.row_begin = row_begin; ga.row_end = row_end;
+        ga.D = s->sh_degree; ga.M = s->M_rest + 1; ga.means3D = geom.means3D; ga.radii = radii;
+        ga.clamped = geom.clamped; ga.scale_modifier = s->scale_modifier;
+        ga.viewmatrix = s->viewmatrix; ga.projmatrix = s->projmatrix; ga.campos = s->campos; ga.W = W; ga.H = H;
+        ga.tan_fovx = s->tan_fovx; ga.tan_fovy = s->tan_fovy;
+        ga.focal_y = H / (2.0f * s->tan_fovy); ga.focal_x = W / (2.0f * s->tan_fovx);
+        ga.grad_acc = geom.grad_acc; ga.dL_dmean2D = d_mean2D;
+        SkinFuseBwdArgs sb = {};
+        sb.f = fuse_args(s, geom, fk);
+        sb.d_rot_saved = geom.d_rot;
+        sb.d_xyz = d_xyz; sb.d_scaling_raw = d_scaling_raw; sb.d_rotation_raw = d_rotation_raw; sb.d_opacity_raw = d_opacity_raw;
+        sb.d_features_dc = d_features_dc; sb.d_features_rest = d_features_rest;
+        sb.dG = fk.dG; sb.dnode_radius_raw = fk.dradius; sb.dglobal_trans = fk.dtrans;
+        sb.dmask = d_mask; sb.dmlp_weight = d_mlp_weight; sb.doffsets = d_offsets;
+        if (launch_gauss_skin_backward(ga, sb, stream)) return -1;
+    }
+    if (phases & 4) {
+        if (launch_fk_backward(1, s->J, s->local_rot, s->joints, s->parents, fk.G, fk.dG, dL_dnodes, d_local_rot,
+                               d_global_trans, fk.dtrans, stream))
+            return -1;
+        if (d_node_radius_raw)
+            cudaMemcpyAsync(d_node_radius_raw, fk.dradius, sizeof(float) * s->J, cudaMemcpyDeviceToDevice, stream);
+    }
     return check_launch("rg_skinned_backward", stream, false);
+}
+
+int rg_skinned_backward(const RgSkinnedScene* s, const RgWorkspace* w, const int* radii, const float* alphas,
+                        const float* dL_dcolor, const float* dL_ddepth, const float* dL_dalpha, const float* dL_dnodes,
+                        float* d_xyz, float* d_scaling_raw, float* d_rotation_raw, float* d_opacity_raw,
+                        float* d_features_dc, float* d_features_rest, float* d_mean2D, float* d_local_rot,
+                        float* d_global_trans, float* d_node_radius_raw, float* d_mask, float* d_mlp_weight,
+                        float* d_offsets, rg_stream_t stream) {
+    return rg_skinned_backward_part(s, w, 7, 0, s ? s->P : 0, radii, alphas, dL_dcolor, dL_ddepth, dL_dalpha, dL_dnodes, d_xyz,
+                                    d_scaling_raw, d_rotation_raw, d_opacity_raw, d_features_dc, d_features_rest, d_mean2D,
+                                    d_local_rot, d_global_trans, d_node_radius_raw, d_mask, d_mlp_weight, d_offsets, stream);
 }
 
 }  // extern "C"

@@ -78,9 +78,88 @@ __global__ void __launch_bounds__(512) allreduce_p2p_kernel(PeerPtrs bufs, size_
     }
 }
 
+// ---- the same two kernels over several word ranges of the buffer (one launch): used when the all-reduce of a chunk of
+// gradient rows (one range per parameter tensor) runs beside the backward of the next chunk
+constexpr int kMaxRanges = 8;
+struct WordRanges {
+    int n;
+    size_t w0[kMaxRanges], w1[kMaxRanges];  // this rank's slice of each range, in 16-byte words
+};
+
+template <int WORLD>
+__global__ void __launch_bounds__(512) allreduce_p2p_ranges_kernel(PeerPtrs bufs, WordRanges rr) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (int q = 0; q < rr.n; q++) {
+        for (size_t i = rr.w0[q] + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < rr.w1[q]; i += stride) {
+            float4 v[WORLD];
+#pragma unroll
+            for (int r = 0; r < WORLD; r++) v[r] = __ldcv(reinterpret_cast<const float4*>(bufs.p[r]) + i);
+            float4 s = v[0];
+#pragma unroll
+            for (int r = 1; r < WORLD; r++) { s.x += v[r].x; s.y += v[r].y; s.z += v[r].z; s.w += v[r].w; }
+#pragma unroll
+            for (int r = 0; r < WORLD; r++) reinterpret_cast<float4*>(bufs.p[r])[i] = s;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(512) allreduce_multimem_ranges_kernel(float* __restrict__ mc, WordRanges rr) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (int q = 0; q < rr.n; q++)
+        for (size_t i = rr.w0[q] + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < rr.w1[q]; i += stride)
+            mm_st(mc + 4 * i, mm_ld_reduce_add(mc + 4 * i));
+}
+
+// false: bad ranges
+static bool slice_ranges(int n_ranges, const size_t* offsets, const size_t* lengths, int rank, int world, WordRanges& rr) {
+    if (n_ranges < 1 || n_ranges > kMaxRanges) return false;
+    rr.n = n_ranges;
+    for (int q = 0; q < n_ranges; q++) {
+        if ((offsets[q] & 3) || (lengths[q] & 3)) return false;
+        const size_t words = lengths[q] / 4, base = offsets[q] / 4;
+        const size_t per = (words + world - 1) / world;
+        const size_t a = per * (size_t)rank < words ? per * (size_t)rank : words;
+        const size_t b = a + per < words ? a + per : words;
+        rr.w0[q] = base + a;
+        rr.w1[q] = base + b;
+    }
+    return true;
+}
+
 }  // namespace rg
 
 using namespace rg;
+
+extern "C" int rg_allreduce_ranges(float* const* peer_bufs, float* multicast_base, int n_ranges, const size_t* offsets,
+                                   const size_t* lengths, int rank, int world, int blocks, rg_stream_t stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    WordRanges rr;
+    if (rank < 0 || rank >= world || !slice_ranges(n_ranges, offsets, lengths, rank, world, rr)) {
+        set_error("rg_allreduce_ranges: 1..8 ranges, offsets and lengths multiples of 4 floats, rank inside world");
+        return -1;
+    }
+    if (blocks <= 0) blocks = RG_NUM_SMS;
+    if (multicast_base) {
+        LaunchScope ls("allreduce_multimem", stream);
+        allreduce_multimem_ranges_kernel<<<blocks, 512, 0, stream>>>(multicast_base, rr);
+        return cudaGetLastError() == cudaSuccess ? 0 : -1;
+    }
+    if (!peer_bufs || !(world == 2 || world == 4 || world == 8)) {
+        set_error("rg_allreduce_ranges: peer buffers need a world of 2, 4 or 8");
+        return -1;
+    }
+    PeerPtrs pp;
+    for (int r = 0; r < world; r++) {
+        if (!peer_bufs[r] || (reinterpret_cast<uintptr_t>(peer_bufs[r]) & 15)) { set_error("rg_allreduce_ranges: null or misaligned peer buffer"); return -1; }
+        pp.p[r] = peer_bufs[r];
+    }
+    LaunchScope ls("allreduce_p2p", stream);
+    if (world == 2) allreduce_p2p_ranges_kernel<2><<<blocks, 512, 0, stream>>>(pp, rr);
+    else if (world == 4) allreduce_p2p_ranges_kernel<4><<<blocks, 512, 0, stream>>>(pp, rr);
+    else allreduce_p2p_ranges_kernel<8><<<blocks, 512, 0, stream>>>(pp, rr);
+    return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
 
 extern "C" int rg_allreduce_p2p(float* const* peer_bufs, size_t n_floats, int rank, int world, rg_stream_t stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);

@@ -79,7 +79,8 @@ __device__ __forceinline__ float transpose_reduce16(const float* v, int lane) {
 
 template <bool FUSED>
 __global__ void __launch_bounds__(256) gauss_backward_kernel(GaussBwdArgs a, SkinFuseBwdArgs s) {
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int idx = a.row_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    const int row_end = a.row_end > 0 ? a.row_end : a.P;
     const int lane = threadIdx.x & 31;
     __shared__ float s_mat[35];
     __shared__ __align__(8) uint64_t s_bar;
@@ -109,8 +110,8 @@ __global__ void __launch_bounds__(256) gauss_backward_kernel(GaussBwdArgs a, Ski
         s_sh = reinterpret_cast<float*>(s_raw + align_up_dev(sizeof(BoneSm) * (size_t)(K > 1 ? K : 1) +
                                                              sizeof(float) * 8 * (size_t)acc_stride, 128));
         sh_row = (size_t)s.f.M_rest * 3;
-        sh_first = (size_t)blockIdx.x * blockDim.x;
-        const int n_valid = max(0, min((int)blockDim.x, a.P - (int)sh_first));
+        sh_first = (size_t)a.row_begin + (size_t)blockIdx.x * blockDim.x;
+        const int n_valid = max(0, min((int)blockDim.x, row_end - (int)sh_first));
         const float* src = s.f.features_rest + sh_first * sh_row;
         sh_bytes = (uint32_t)(n_valid * sh_row * sizeof(float));
         sh_bulk = (sh_bytes % 16 == 0) && ((reinterpret_cast<size_t>(src) & 15) == 0) && sh_bytes > 0;
@@ -124,7 +125,7 @@ __global__ void __launch_bounds__(256) gauss_backward_kernel(GaussBwdArgs a, Ski
     const float* view = s_mat;
     const float* proj = s_mat + 16;
     const size_t i = (size_t)idx;
-    const bool in_range = idx < a.P;
+    const bool in_range = idx < row_end;
     const bool visible = in_range && a.radii[idx] > 0;
     if (!FUSED && !in_range) return;
 
@@ -457,7 +458,9 @@ int launch_gauss_skin_backward(const GaussBwdArgs& a, const SkinFuseBwdArgs& s, 
         cudaFuncSetAttribute(gauss_backward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
         attr_set = true;
     }
-    gauss_backward_kernel<true><<<(a.P + 255) / 256, 256, smem, stream>>>(a, s);
+    const int rows = (a.row_end > 0 ? a.row_end : a.P) - a.row_begin;
+    if (rows <= 0) return 0;
+    gauss_backward_kernel<true><<<(rows + 255) / 256, 256, smem, stream>>>(a, s);
     return 0;
 }
 

@@ -147,6 +147,7 @@ int launch_blend_backward(const BlendBwdArgs& a, cudaStream_t stream);
 
 struct GaussBwdArgs {
     int P, D, M;
+    int row_begin, row_end;  // rows handled by this launch (row_end = 0: all P rows); row_begin a multiple of 256
     const float* means3D;
     const int* radii;
     const float* shs;

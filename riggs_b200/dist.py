@@ -46,6 +46,12 @@ class FlatGrads:
         self.hdl = None
         self._peer_ptrs = None
         self._mc_ptr = 0
+        self.reduced_in_backward = False  # set by all_reduce_rows: the buffer already holds the sum
+        # Opt-in: sum the gradient chunk by chunk on a second stream while the backward computes later chunks
+        # (fused.render_skinned(reduce=...)).  Measured on 2 x B200 (C0): 0.725-0.731 ms/step against 0.72 ms with the
+        # single all-reduce after the backward -- the issue-bound per-Gaussian backward and the link-bound sum slow each
+        # other down by as much as the overlap hides, so it stays off.
+        self.overlap = False
         padded = (total + 3) // 4 * 4  # the peer kernel moves 16-byte words
         if peer_memory and device.type == "cuda":
             self._try_symmetric(padded, device)
@@ -98,6 +104,11 @@ class FlatGrads:
     def all_reduce(self, average: bool = False, async_op: bool = False):
         if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
             return None
+        if self.reduced_in_backward:  # summed chunk by chunk while the backward ran
+            self.reduced_in_backward = False
+            if average:
+                self.flat.div_(dist.get_world_size())
+            return None
         if self.hdl is not None and not async_op:
             from . import _lib
             hdl = self.hdl
@@ -116,6 +127,63 @@ class FlatGrads:
         if average and not async_op:
             self.flat.div_(dist.get_world_size())
         return work
+
+    # ---- all-reduce overlapped with the backward that fills the buffer ------------------------------------
+    def can_overlap(self, n_rows: int) -> bool:
+        """True when the buffer is peer-mapped and every per-row parameter (first dimension n_rows) and every other
+        parameter starts and ends on a 16-byte word, so that chunks of rows can be summed while later rows are still
+        being computed (``fused.render_skinned(..., reduce=flat)``)."""
+        if self.hdl is None or n_rows % 4:
+            return False
+        off = 0
+        n_ranges = 0
+        for p in self.params:
+            if off % 4 or p.numel() % 4:
+                return False
+            off += p.numel()
+            n_ranges += 1
+        return n_ranges <= 8
+
+    def row_chunks(self, n_rows: int, n_chunks: int = 4):
+        """Row ranges of about equal size whose starts are multiples of 256 (the backward's CTA granularity)."""
+        step = max(256, (n_rows + n_chunks - 1) // n_chunks // 256 * 256)
+        out, r = [], 0
+        while r < n_rows:
+            e = min(n_rows, r + step)
+            if n_rows - e < 256:
+                e = n_rows
+            out.append((r, e))
+            r = e
+        return out
+
+    def all_reduce_rows(self, n_rows: int, r0: int, r1: int, with_rest: bool, blocks: int = 64, barrier_after: bool = False):
+        """Device-side barrier, then the sum of rows [r0, r1) of every per-row parameter (plus, with_rest, of the other
+        parameters) on the current stream.  The caller orders this after the kernels that wrote those rows; successive
+        calls need no barrier in between (the next call's leading barrier also fences this call's kernel), the last one
+        passes barrier_after=True."""
+        import ctypes as C
+        from . import _lib
+        offs, lens, off = [], [], 0
+        for p in self.params:
+            k = p.numel()
+            if p.dim() > 0 and p.shape[0] == n_rows:
+                w = k // n_rows
+                offs.append(off + r0 * w)
+                lens.append((r1 - r0) * w)
+            elif with_rest:
+                offs.append(off)
+                lens.append(k)
+            off += k
+        hdl = self.hdl
+        hdl.barrier(channel=0)
+        if offs:
+            n = len(offs)
+            _lib.check(_lib.lib().rg_allreduce_ranges(self._peer_ptrs, self._mc_ptr or None, n, (C.c_size_t * n)(*offs),
+                                                      (C.c_size_t * n)(*lens), hdl.rank, hdl.world_size, blocks,
+                                                      _lib.stream_ptr()), "rg_allreduce_ranges")
+        if barrier_after:
+            hdl.barrier(channel=0)
+        self.reduced_in_backward = True
 
     def attach(self):
         for n, p in zip(self.names, self.params):

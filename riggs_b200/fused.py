@@ -73,6 +73,14 @@ class WorkspacePool:
 
 
 _POOL = WorkspacePool()
+_SIDE: Dict[str, torch.cuda.Stream] = {}
+
+
+def _side_stream(dev) -> torch.cuda.Stream:
+    s = _SIDE.get(str(dev))
+    if s is None:
+        s = _SIDE[str(dev)] = torch.cuda.Stream(device=dev)
+    return s
 
 
 class _Lease:
@@ -172,6 +180,7 @@ class _SkinnedRender(torch.autograd.Function):
         ctx.lease = _Lease(pool, ws, dev)
         ctx.dev = dev
         ctx.grad_out = cfg.get("grad_out")
+        ctx.reduce = cfg.get("reduce")
         if not any(ctx.needs_input_grad):
             ctx.lease.release()  # inference: the state is not needed any more
         ctx.shapes = (P, J, W, H, M_rest, isotropic)
@@ -217,12 +226,34 @@ class _SkinnedRender(torch.autograd.Function):
         d_mask = torch.empty((P,), **opts) if (t["motion_mask"] is not None and need[9]) else None
         d_mlp = torch.empty((P, J - 1), **opts) if (t["mlp_weight"] is not None and need[10]) else None
         d_off = torch.empty((P, 3), **opts) if (t["offsets"] is not None and need[11]) else None
-        with torch.cuda.device(dev):
-            check(_lib.lib().rg_skinned_backward(
-                C.byref(ctx.scene), C.byref(ctx.ws.c), ptr(radii), ptr(alpha), ptr(g_color), ptr(g_depth), ptr(g_alpha),
+        red = ctx.reduce
+        args = (ptr(radii), ptr(alpha), ptr(g_color), ptr(g_depth), ptr(g_alpha),
                 ptr(g_nodes), ptr(d_xyz), ptr(d_scaling), ptr(d_rotation), ptr(d_opacity), ptr(d_fdc), ptr(d_frest),
-                ptr(d_mean2D), ptr(d_local_rot), ptr(d_trans), ptr(d_radius), ptr(d_mask), ptr(d_mlp), ptr(d_off),
-                stream_ptr()), "rg_skinned_backward")
+                ptr(d_mean2D), ptr(d_local_rot), ptr(d_trans), ptr(d_radius), ptr(d_mask), ptr(d_mlp), ptr(d_off))
+        L = _lib.lib()
+        with torch.cuda.device(dev):
+            if red is not None and red.can_overlap(P) and all(n in go for n in red.names):
+                # Data parallel: the parameter gradients go straight into the ranks' peer-mapped flat buffer, and the
+                # rows of chunk c are summed over the ranks on a second stream while chunk c+1 is computed here.
+                part = lambda phases, r0, r1: check(L.rg_skinned_backward_part(
+                    C.byref(ctx.scene), C.byref(ctx.ws.c), phases, r0, r1, *args, stream_ptr()), "rg_skinned_backward_part")
+                main = torch.cuda.current_stream()
+                side = _side_stream(dev)
+                chunks = red.row_chunks(P)
+                part(1, 0, 0)
+                for c, (r0, r1) in enumerate(chunks):
+                    last = c == len(chunks) - 1
+                    part(2, r0, r1)
+                    if last:
+                        part(4, 0, 0)  # the skeleton gradients travel with the last chunk
+                    ev = torch.cuda.Event()
+                    ev.record(main)
+                    with torch.cuda.stream(side):
+                        side.wait_event(ev)
+                        red.all_reduce_rows(P, r0, r1, with_rest=last, barrier_after=last)
+                main.wait_stream(side)
+            else:
+                check(L.rg_skinned_backward(C.byref(ctx.scene), C.byref(ctx.ws.c), *args, stream_ptr()), "rg_skinned_backward")
         ctx.lease.release()
         ctx.ws = None
         if d_mask is not None:
@@ -237,12 +268,14 @@ class _SkinnedRender(torch.autograd.Function):
 
 def render_skinned(viewpoint_camera, pc, skeleton, pose: Dict[str, torch.Tensor], pipe, bg_color: torch.Tensor,
                    scaling_modifier=1.0, mlp_weight=None, offsets=None, zero_d_rotation: Optional[bool] = None,
-                   debug_outputs=None, pool: Optional[WorkspacePool] = None, grad_out=None):
+                   debug_outputs=None, pool: Optional[WorkspacePool] = None, grad_out=None, reduce=None):
     """Fused deform + render.  ``pc``: object with the GaussianModel raw tensors (_xyz, _scaling, _rotation, _opacity,
     _features_dc, _features_rest, motion_mask, active_sh_degree); ``skeleton``: riggs_b200 SkeletonWarp (joints,
     parents, _node_radius); ``pose``: {'local_rotation': (J,4), 'global_trans': (3,)}.
     ``grad_out``: optional dict of preallocated gradient buffers (keys xyz, scaling, rotation, opacity, features_dc,
     features_rest, node_radius) the backward kernels write into directly -- e.g. the views of ``dist.FlatGrads``.
+    ``reduce``: that ``dist.FlatGrads`` itself; when its buffer is peer-mapped the backward sums the gradient over the
+    ranks chunk by chunk while it is still computing later chunks (``FlatGrads.all_reduce`` then has nothing left to do).
     Returns the dict of ``render()`` plus ``d_nodes``."""
     xyz = pc._xyz
     screenspace_points = torch.zeros_like(xyz, requires_grad=True)
@@ -254,7 +287,7 @@ def render_skinned(viewpoint_camera, pc, skeleton, pose: Dict[str, torch.Tensor]
                viewmatrix=f32c(viewpoint_camera.world_view_transform), projmatrix=f32c(viewpoint_camera.full_proj_transform),
                campos=f32c(viewpoint_camera.camera_center), bg=f32c(bg_color),
                zero_d_rotation=isotropic if zero_d_rotation is None else zero_d_rotation, debug_outputs=debug_outputs,
-               pool=pool, grad_out=grad_out)
+               pool=pool, grad_out=grad_out, reduce=reduce)
     mm = getattr(pc, "_motion_mask", None)
     mask = mm.reshape(-1) if mm is not None else None
     color, depth, alpha, radii, d_nodes = _SkinnedRender.apply(

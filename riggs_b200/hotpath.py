@@ -73,7 +73,8 @@ class HotPath:
             from .fused import render_skinned
             return render_skinned(cam, self.pc, self.warp, pose, self.pipe, self.bg, mlp_weight=self.mlp_weight,
                                   offsets=self.offsets, grad_out=self.flat.views if self.flat is not None else None,
-                                  pool=self.pool)
+                                  pool=self.pool,
+                                  reduce=self.flat if getattr(self.flat, "overlap", False) else None)
         joints = self.warp.nodes[:, :3]
         G, node_rot, d_nodes = sw.fk(pose["local_rotation"], pose["global_trans"], joints, self.warp.parents_i32)
         mask = self.pc._motion_mask.reshape(-1) if self.pc._motion_mask is not None else None
@@ -147,6 +148,8 @@ class GraphedStep:
             self.loss = self._one()
         self.launches_per_replay = int(_lib.lib().rg_launch_count() - n0)
         self.grads = {n: p.grad for n, p in self.hp.named_parameters()}  # static: rewritten by every replay
+        # data parallel with a peer-mapped gradient buffer: the all-reduce was captured with the backward
+        self._reduces_in_graph = bool(self.hp.flat is not None and self.hp.flat.reduced_in_backward)
         self._ws = self.pool.free and next(iter(self.pool.free.values()))[0]
         self._event = None
 
@@ -225,6 +228,8 @@ class GraphedStep:
         if target is not None:
             self.target.copy_(target, non_blocking=True)
         self.graph.replay()
+        if self._reduces_in_graph:
+            self.hp.flat.reduced_in_backward = True
         for n, p in self.hp.named_parameters():
             if self.grads[n] is not None and p.grad is not self.grads[n]:
                 p.grad = self.grads[n]
