@@ -78,7 +78,7 @@ __device__ __forceinline__ float transpose_reduce16(const float* v, int lane) {
 }
 
 template <bool FUSED>
-__global__ void __launch_bounds__(256) gauss_backward_kernel(GaussBwdArgs a, SkinFuseBwdArgs s) {
+__global__ void __launch_bounds__(256, 3) gauss_backward_kernel(GaussBwdArgs a, SkinFuseBwdArgs s) {
     const int idx = a.row_begin + blockIdx.x * blockDim.x + threadIdx.x;
     const int row_end = a.row_end > 0 ? a.row_end : a.P;
     const int lane = threadIdx.x & 31;

@@ -27,7 +27,7 @@
 namespace rg {
 
 template <bool FUSED>
-__global__ void __launch_bounds__(256) preprocess_kernel(PreprocessArgs a, SkinFuseArgs s) {
+__global__ void __launch_bounds__(256, 4) preprocess_kernel(PreprocessArgs a, SkinFuseArgs s) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     __shared__ float s_mat[35];  // view[16], proj[16], campos[3]
     extern __shared__ __align__(16) unsigned char s_raw[];
