@@ -40,6 +40,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true")
     ap.add_argument("--isotropic", action="store_true")
+    ap.add_argument("--lambda-dssim", type=float, default=0.0,
+                    help="> 0: the step's loss is the trainer's (1-l)*L1 + l*(1-SSIM) (fused kernels) instead of L1")
     ap.add_argument("--no-graph", action="store_true", help="drive the fused step launch by launch instead of replaying a CUDA graph")
     ap.add_argument("--unfused", action="store_true", help="reference call sequence (deform_by_pose + render) on our kernels")
     return ap.parse_args()
@@ -134,7 +136,7 @@ def run_ours(args):
         os.environ.setdefault("NCCL_DEBUG", "WARN")  # keep NCCL banner lines off stdout: rank 0 prints ONE JSON line
         dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=120))
     scene = make_scene(args.workload, args.isotropic)
-    hp = HotPath(scene, device=dev, fused=not args.unfused)
+    hp = HotPath(scene, device=dev, fused=not args.unfused, lambda_dssim=args.lambda_dssim)
     cam = scene.cameras[rank % len(scene.cameras)].to(dev)
     H, W = cam.image_height, cam.image_width
     g = torch.Generator().manual_seed(1000 + rank)
@@ -311,6 +313,7 @@ def run_ours(args):
                                f"fwd+bwd", "P": P, "visible": vis, "R": R, "HW": H * W,
                    "l2": "inputs+state per step (~%d MB) exceed no L2 flush; working set streams through HBM" % (total_bytes >> 20),
                    "launch": "cuda graph replay" if gs is not None else "eager",
+                   "loss": "L1" if args.lambda_dssim <= 0 else f"(1-{args.lambda_dssim})*L1 + {args.lambda_dssim}*(1-SSIM)",
                    "parallelism": (f"dp{world} over views, " + (("own all-reduce kernel over symmetric memory (" + ("rg_allreduce_multimem, NVLS" if getattr(hp.flat, "_mc_ptr", 0)
                                                                                        else "rg_allreduce_p2p, NVLink peer loads/stores") + ")")
                                    if getattr(hp.flat, "hdl", None) is not None else "NCCL all-reduce") +

@@ -230,6 +230,17 @@ int rg_skinned_backward(const RgSkinnedScene* scene, const RgWorkspace* ws, cons
                         float* d_local_rot, float* d_global_trans, float* d_node_radius_raw, float* d_mask,
                         float* d_mlp_weight, float* d_offsets, rg_stream_t stream);
 
+/* The trainer's image loss and its gradient in two launches (train_rig.py:508-509):
+ *   loss = (1 - lambda_dssim) * mean|output - gt| + lambda_dssim * (1 - ssim(output, gt)),
+ * ssim = utils/loss_utils.py:36-77 (11x11 Gaussian window, sigma 1.5, zero padding, per channel, mean over all).
+ * output, gt, grad: (channels, height, width) fp32; loss3 receives {loss, l1, ssim}; scratch:
+ * rg_ssim_loss_scratch_bytes(channels, height, width) bytes, no initialisation needed.  lambda_dssim = 1 gives
+ * grad = -d ssim / d output.  Replaces l1_loss + ssim + their autograd (five grouped conv2d and ~20 element-wise
+ * launches forward, as many backward). */
+size_t rg_ssim_loss_scratch_bytes(int channels, int height, int width);
+int rg_ssim_l1_loss(int channels, int height, int width, const float* output, const float* gt, float lambda_dssim,
+                    float* loss3, float* grad, void* scratch, size_t scratch_bytes, rg_stream_t stream);
+
 /* rg_skinned_backward in parts, for callers that overlap the gradient all-reduce with the backward: `phases` is a bit
  * set -- 1: zero the accumulators and run the blend backward, 2: per-Gaussian backward (parameter gradients) of rows
  * [row_begin, row_end) only (row_begin a multiple of 256), 4: skeleton backward (d_local_rot, d_global_trans,

@@ -66,6 +66,8 @@ _SIGNATURES = {
     "rg_allreduce_multimem": (C.c_int, [_p, C.c_size_t, _i, _i, _p]),
     "rg_allreduce_p2p": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t, _i, _i, _p]),
     "rg_allreduce_ranges": (C.c_int, [C.POINTER(C.c_void_p), _p, _i, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t), _i, _i, _i, _p]),
+    "rg_ssim_loss_scratch_bytes": (C.c_size_t, [_i, _i, _i]),
+    "rg_ssim_l1_loss": (C.c_int, [_i, _i, _i, _p, _p, _f, _p, _p, _p, C.c_size_t, _p]),
     "rg_launch_count": (C.c_longlong, []),
     "rg_profile_enable": (None, [_i]),
     "rg_profile_reset": (None, []),

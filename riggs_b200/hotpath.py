@@ -10,7 +10,7 @@ import torch
 
 from . import skeleton_warp as sw
 from .gaussian_renderer import GaussianParams, render
-from .loss_utils import l1_loss, l1_loss_and_grad  # noqa: F401
+from .loss_utils import image_loss_and_grad, l1_loss, l1_loss_and_grad  # noqa: F401
 
 
 class _Pipe:
@@ -21,10 +21,11 @@ class _Pipe:
 
 class HotPath:
     def __init__(self, scene, device="cuda", use_mlp_weight: bool = False, use_offsets: bool = False,
-                 fused: bool = True):
+                 fused: bool = True, lambda_dssim: float = 0.0):
         """fused=True: one C-ABI call per direction (rg_skinned_forward/backward, no host sync);
         fused=False: the reference's call sequence (deform_by_pose, then render()) on the same kernels."""
         self.fused = fused
+        self.lambda_dssim = float(lambda_dssim)  # > 0: the trainer's L1 + SSIM image loss (train_rig.py:508-509)
         self.device = torch.device(device)
         self.pc = GaussianParams.from_scene(scene, device=device)
         self.warp = sw.SkeletonWarp(scene.joints, scene.parents, scene.node_radius_raw,
@@ -87,7 +88,10 @@ class HotPath:
     def step(self, cam, pose, target: torch.Tensor) -> torch.Tensor:
         """Forward + backward of one view; returns the (device) loss.  Gradients accumulate in .grad."""
         out = self.forward(cam, pose)
-        loss, grad = l1_loss_and_grad(out["render"], target)  # one kernel: the loss and d loss / d image
+        if self.lambda_dssim > 0.0:
+            loss, grad, _l1, _ssim = image_loss_and_grad(out["render"], target, self.lambda_dssim)
+        else:
+            loss, grad = l1_loss_and_grad(out["render"], target)  # one kernel: the loss and d loss / d image
         out["render"].backward(grad)
         return loss
 

@@ -186,3 +186,46 @@ def test_l1_loss_and_grad_outside_autograd():
     ref = l1_loss(a, b)
     ref.backward()
     assert float(loss) == float(ref.detach()) and torch.equal(grad, a.grad) and not loss.requires_grad
+
+
+@pytest.mark.parametrize("tag", ["a", "b", "c", "d"])
+def test_image_loss_vs_reference_golden(tag):
+    """csrc/ssim.cu against the reference's own l1_loss / ssim / autograd outputs (tests/golden/loss_ssim.npz):
+    loss, l1 and ssim within 1e-5, gradient within 1e-4 of its largest entry."""
+    import os
+    from riggs_b200.loss_utils import image_loss, image_loss_and_grad, ssim
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "loss_ssim.npz"))
+    img = torch.from_numpy(g[f"{tag}_img"]).float().cuda().requires_grad_(True)
+    gt = torch.from_numpy(g[f"{tag}_gt"]).float().cuda()
+    lam = float(g[f"{tag}_lambda"])
+    loss, grad, l1, s = image_loss_and_grad(img, gt, lam)
+    assert abs(float(loss) - float(g[f"{tag}_loss"])) <= 1e-5
+    assert abs(float(l1) - float(g[f"{tag}_l1"])) <= 1e-5
+    assert abs(float(s) - float(g[f"{tag}_ssim"])) <= 1e-5
+    assert helpers.rel_err(grad.cpu().numpy(), g[f"{tag}_grad"]) <= 1e-4
+    # the autograd wrappers
+    l2 = image_loss(img, gt, lam)
+    (l2 * 3.0).backward()
+    assert float(l2.detach()) == float(loss) and torch.equal(img.grad, grad * 3.0)
+    img.grad = None
+    s2 = ssim(img, gt)
+    s2.backward()
+    assert abs(float(s2.detach()) - float(g[f"{tag}_ssim"])) <= 1e-5
+
+
+@pytest.mark.parametrize("shape", [(3, 800, 800), (2, 3, 45, 31), (3, 1, 1), (3, 16, 17)])
+def test_image_loss_vs_torch_oracle(shape):
+    """Same kernels against oracle/loss_oracle.py (the reference's code restated) run in float64 on the same inputs,
+    at the bench image size, for a batch, and for images smaller than the window."""
+    from oracle import loss_oracle as lo
+    from riggs_b200.loss_utils import image_loss_and_grad
+    g = torch.Generator().manual_seed(11)
+    gt = torch.rand(*shape, generator=g)
+    img = (gt + 0.1 * torch.randn(*shape, generator=g)).clamp(0, 1)
+    a = img.double().requires_grad_(True)
+    want, wl1, ws = lo.image_loss(a, gt.double(), 0.2)
+    want.backward()
+    loss, grad, l1, s = image_loss_and_grad(img.cuda(), gt.cuda(), 0.2)
+    want, wl1, ws = want.detach(), wl1.detach(), ws.detach()
+    assert abs(float(loss) - float(want)) <= 1e-5 and abs(float(l1) - float(wl1)) <= 1e-5 and abs(float(s) - float(ws)) <= 1e-5
+    assert helpers.rel_err(grad.cpu().numpy(), a.grad.numpy()) <= 1e-4

@@ -134,3 +134,19 @@ def test_knn_oracle_small():
     assert np.isclose(out[0], (1 + 4 + 9) / 3)
     d = ((pts[4] - pts[:4]) ** 2).sum(1)
     assert np.isclose(out[4], np.sort(d)[:3].mean())
+
+
+@pytest.mark.parametrize("tag,tol", [("a", 1e-12), ("b", 2e-6), ("c", 1e-12), ("d", 1e-12)])
+def test_loss_oracle_vs_reference_golden(tag, tol):
+    """oracle/loss_oracle.py against outputs of the reference's utils/loss_utils.py (l1_loss, ssim, their autograd)."""
+    from oracle import loss_oracle as lo
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "loss_ssim.npz"))
+    img = torch.from_numpy(g[f"{tag}_img"]).requires_grad_(True)
+    gt = torch.from_numpy(g[f"{tag}_gt"])
+    loss, l1, s = lo.image_loss(img, gt, float(g[f"{tag}_lambda"]))
+    loss.backward()
+    loss, l1, s = loss.detach(), l1.detach(), s.detach()
+    assert abs(float(l1) - float(g[f"{tag}_l1"])) <= tol
+    assert abs(float(s) - float(g[f"{tag}_ssim"])) <= tol
+    assert abs(float(loss) - float(g[f"{tag}_loss"])) <= tol
+    assert helpers.rel_err(img.grad.numpy(), g[f"{tag}_grad"]) <= max(tol, 1e-12) * 10
