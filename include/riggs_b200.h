@@ -241,6 +241,31 @@ size_t rg_ssim_loss_scratch_bytes(int channels, int height, int width);
 int rg_ssim_l1_loss(int channels, int height, int width, const float* output, const float* gt, float lambda_dssim,
                     float* loss3, float* grad, void* scratch, size_t scratch_bytes, rg_stream_t stream);
 
+/* ---- what follows the backward in a training iteration --------------------------- */
+
+/* One parameter group of torch.optim.Adam as the reference sets it up (scene/gaussian_model.py:203-217). */
+typedef struct RgAdamGroup {
+    float* param;        /* updated in place */
+    const float* grad;
+    float* exp_avg;      /* Adam state, zero before the first step */
+    float* exp_avg_sq;
+    size_t n;            /* elements */
+    float lr;
+} RgAdamGroup;
+
+/* torch.optim.Adam.step() for up to 16 groups in one launch (no weight decay, no amsgrad); `step` = 1 for the first
+ * call.  The reference uses betas (0.9, 0.999) and eps 1e-15; they are doubles because torch forms 1 - beta in double
+ * before rounding to fp32. */
+int rg_adam_step(int n_groups, const RgAdamGroup* groups, int step, double beta1, double beta2, double eps,
+                 rg_stream_t stream);
+
+/* add_densification_stats (scene/gaussian_model.py:516-518) with update_filter = radii > 0, plus the max_radii2D update of
+ * train_rig.py:335 (max_radii2D may be NULL): for every visible Gaussian
+ * xyz_gradient_accum += |viewspace_grad.xy|, denom += 1, max_radii2D = max(max_radii2D, radii).
+ * viewspace_grad (P,3), radii (P) int32, the three statistics (P) fp32. */
+int rg_densification_stats(int P, const float* viewspace_grad, const int* radii, float* xyz_gradient_accum, float* denom,
+                           float* max_radii2D, rg_stream_t stream);
+
 /* rg_skinned_backward in parts, for callers that overlap the gradient all-reduce with the backward: `phases` is a bit
  * set -- 1: zero the accumulators and run the blend backward, 2: per-Gaussian backward (parameter gradients) of rows
  * [row_begin, row_end) only (row_begin a multiple of 256), 4: skeleton backward (d_local_rot, d_global_trans,

@@ -30,6 +30,11 @@ class RgSkinnedScene(C.Structure):
                                            "campos", "background")])
 
 
+class RgAdamGroup(C.Structure):
+    _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+                ("n", C.c_size_t), ("lr", C.c_float)]
+
+
 class RgWorkspace(C.Structure):
     _fields_ = [("geom", C.c_void_p), ("geom_bytes", C.c_size_t), ("image", C.c_void_p), ("image_bytes", C.c_size_t),
                 ("binning", C.c_void_p), ("binning_bytes", C.c_size_t)]
@@ -68,6 +73,8 @@ _SIGNATURES = {
     "rg_allreduce_ranges": (C.c_int, [C.POINTER(C.c_void_p), _p, _i, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t), _i, _i, _i, _p]),
     "rg_ssim_loss_scratch_bytes": (C.c_size_t, [_i, _i, _i]),
     "rg_ssim_l1_loss": (C.c_int, [_i, _i, _i, _p, _p, _f, _p, _p, _p, C.c_size_t, _p]),
+    "rg_adam_step": (C.c_int, [_i, _p, _i, C.c_double, C.c_double, C.c_double, _p]),
+    "rg_densification_stats": (C.c_int, [_i, _p, _p, _p, _p, _p, _p]),
     "rg_launch_count": (C.c_longlong, []),
     "rg_profile_enable": (None, [_i]),
     "rg_profile_reset": (None, []),

@@ -229,3 +229,60 @@ def test_image_loss_vs_torch_oracle(shape):
     want, wl1, ws = want.detach(), wl1.detach(), ws.detach()
     assert abs(float(loss) - float(want)) <= 1e-5 and abs(float(l1) - float(wl1)) <= 1e-5 and abs(float(s) - float(ws)) <= 1e-5
     assert helpers.rel_err(grad.cpu().numpy(), a.grad.numpy()) <= 1e-4
+
+
+@pytest.mark.parametrize("N", [5000, 5001])  # 16-byte-word path and the scalar path
+def test_fused_adam_matches_torch_adam(N):
+    """optim.FusedAdam against torch.optim.Adam on the reference's group layout (six groups, own learning rates, eps
+    1e-15, a learning-rate change between steps) over several steps."""
+    from riggs_b200.optim import FusedAdam
+    g = torch.Generator().manual_seed(21)
+    shapes = {"xyz": (N, 3), "f_dc": (N, 1, 3), "f_rest": (N, 15, 3), "opacity": (N, 1), "scaling": (N, 3),
+              "rotation": (N, 4)}
+    lrs = {"xyz": 1.6e-4 * 5, "f_dc": 2.5e-3, "f_rest": 2.5e-3 / 20, "opacity": 0.05, "scaling": 0.001 * 5, "rotation": 0.001}
+    init = {k: torch.randn(*s, generator=g) for k, s in shapes.items()}
+    a = {k: v.clone().cuda().requires_grad_(True) for k, v in init.items()}
+    b = {k: v.clone().cuda().requires_grad_(True) for k, v in init.items()}
+    mk = lambda d: [{"params": [d[k]], "lr": lrs[k], "name": k} for k in shapes]
+    ours, ref = FusedAdam(mk(a), lr=0.0, eps=1e-15), torch.optim.Adam(mk(b), lr=0.0, eps=1e-15)
+    for it in range(5):
+        for k in shapes:
+            gr = torch.randn(*shapes[k], generator=g).cuda() * (10.0 ** (it - 3))
+            if k == "opacity":
+                gr[::7] = 0.0  # zero gradients: the step is m / (sqrt(v) + 1e-15)
+            a[k].grad, b[k].grad = gr.clone(), gr.clone()
+        if it == 2:
+            for opt in (ours, ref):
+                for grp in opt.param_groups:
+                    if grp["name"] == "xyz":
+                        grp["lr"] = 3e-4
+        ours.step()
+        ref.step()
+    torch.cuda.synchronize()
+    for k in shapes:
+        assert helpers.rel_err(a[k].detach().cpu().numpy(), b[k].detach().cpu().numpy()) <= 2e-6, k
+        sa, sb = ours.state[a[k]], ref.state[b[k]]
+        assert helpers.rel_err(sa["exp_avg"].cpu().numpy(), sb["exp_avg"].cpu().numpy()) <= 2e-6
+        assert helpers.rel_err(sa["exp_avg_sq"].cpu().numpy(), sb["exp_avg_sq"].cpu().numpy()) <= 2e-6
+
+
+def test_densification_stats_match_reference_expressions():
+    from riggs_b200.optim import add_densification_stats
+    g = torch.Generator().manual_seed(22)
+    P = 10_001
+    vsp = torch.zeros(P, 3).cuda().requires_grad_(True)
+    vsp.grad = torch.randn(P, 3, generator=g).cuda()
+    radii = (torch.randint(-2, 40, (P,), generator=g)).to(torch.int32).cuda()
+    accum = torch.rand(P, 1, generator=g).cuda()
+    denom = torch.rand(P, 1, generator=g).cuda().round()
+    maxr = (torch.rand(P, generator=g) * 30).cuda()
+    w_accum, w_denom, w_maxr = accum.clone(), denom.clone(), maxr.clone()
+    vis = radii > 0
+    # scene/gaussian_model.py:516-518 and train_rig.py:335
+    w_accum[vis] += torch.norm(vsp.grad[vis, :2], dim=-1, keepdim=True)
+    w_denom[vis] += 1
+    w_maxr[vis] = torch.max(w_maxr[vis], radii[vis].float())
+    add_densification_stats(vsp, radii, accum, denom, maxr)
+    torch.cuda.synchronize()
+    assert helpers.rel_err(accum.cpu().numpy(), w_accum.cpu().numpy()) <= 1e-6
+    assert torch.equal(denom, w_denom) and torch.equal(maxr, w_maxr)
