@@ -333,9 +333,43 @@ def run_ours(args):
         rc = ref_cuda_baseline(scene, cam, pose, target, steps=min(args.steps, 10))
         if rc:
             line["reference_cuda_b200"] = rc
+    if world == 1:
+        line["next_rows"] = next_rows(hp, out["render"].detach(), target)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def next_rows(hp, render, target, iters=20):
+    """Device time of the SURVEY 8(f) rows built so far, outside the headline step: the trainer's L1 + SSIM image loss with
+    its gradient (N1) and the Adam step over every Gaussian parameter group (N2), CUDA events on the launching stream."""
+    import torch
+    from riggs_b200.loss_utils import image_loss_and_grad
+    from riggs_b200.optim import FusedAdam
+    names = ["xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation"]
+    ps = hp.parameters()[:6]
+    clones = [p.detach().clone().requires_grad_(True) for p in ps]
+    for c in clones:
+        c.grad = torch.randn_like(c) * 1e-3
+    opt = FusedAdam([{"params": [c], "lr": 1e-4, "name": n} for c, n in zip(clones, names)], lr=0.0, eps=1e-15)
+
+    def timed(fn):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / iters
+
+    n = sum(c.numel() for c in clones)
+    ms_adam = timed(opt.step)
+    ms_loss = timed(lambda: image_loss_and_grad(render, target, 0.2))
+    return {"image_loss_l1_ssim_ms": round(ms_loss, 4), "adam_step_ms": round(ms_adam, 4), "adam_params": n,
+            "adam_gbs": round(n * 28 / (ms_adam * 1e-3) / 1e9, 1)}
 
 
 def _count_rendered(hp, cam, pose):
