@@ -33,18 +33,21 @@ static SsimWindow make_window() {
 }
 
 constexpr int kPitch = 28;  // row pitch of the staged tiles: 26 used, rows start on 16-byte boundaries
+constexpr int kPitchH = 20;  // pitch of the filtered tiles (16 used): rows four apart fall into different banks
 
 // Separable 11-tap convolution of N_MAPS maps held as s_in[map][26][28] -> s_v[map][16][16].  Both passes are register
 // blocked: a thread produces four neighbouring outputs from fourteen inputs, so the shared-memory loads per FMA drop
 // from 1 to 1/11 (horizontal pass, 128-bit loads) and 1/3 (vertical pass); a one-load-per-FMA version of this function was
 // bound by the shared-memory pipe (72 us for the five maps of an 800x800x3 image; now ~45 us).
 template <int N_MAPS>
-__device__ __forceinline__ void separable(const float (*s_in)[kIn][kPitch], float (*s_h)[kIn][kTile],
-                                          float (*s_v)[kTile][kTile], const SsimWindow& g) {
+__device__ __forceinline__ void separable(const float (*s_in)[kIn][kPitch], float (*s_h)[kIn][kPitchH],
+                                          float (*s_v)[kTile][kPitchH], const SsimWindow& g) {
     const int tid = threadIdx.x;
     constexpr int kSeg = kTile / 4;  // four outputs per work item
     for (int it = tid; it < N_MAPS * kIn * kSeg; it += kTile * kTile) {
-        const int m = it / (kIn * kSeg), rem = it - m * (kIn * kSeg), r = rem / kSeg, c0 = (rem % kSeg) * 4;
+        // consecutive threads take consecutive ROWS of one column segment: with a pitch of 28 words the eight 128-bit
+        // loads of a quarter warp then fall into eight different groups of four banks
+        const int m = it / (kIn * kSeg), rem = it - m * (kIn * kSeg), r = rem % kIn, c0 = (rem / kIn) * 4;
         float in[16];
 #pragma unroll
         for (int q = 0; q < 4; q++) {
@@ -84,8 +87,8 @@ __global__ void __launch_bounds__(kTile* kTile) ssim_map_kernel(int C, int H, in
                                                                 float* __restrict__ dmap,  // [3][C][H][W]: Dm, Dxx, Dxy
                                                                 float* __restrict__ partial) {  // [blocks][2]: sum S, sum |x-y|
     __shared__ __align__(16) float s_in[5][kIn][kPitch];
-    __shared__ __align__(16) float s_h[5][kIn][kTile];
-    __shared__ float s_v[5][kTile][kTile];
+    __shared__ __align__(16) float s_h[5][kIn][kPitchH];
+    __shared__ float s_v[5][kTile][kPitchH];
     __shared__ float s_red[2][kTile * kTile / 32];
     const int ch = blockIdx.z, tx0 = blockIdx.x * kTile, ty0 = blockIdx.y * kTile;
     const size_t plane = (size_t)H * W;
@@ -140,8 +143,8 @@ __global__ void __launch_bounds__(kTile* kTile) ssim_grad_kernel(int C, int H, i
                                                                  float* __restrict__ grad, const float* __restrict__ partial,
                                                                  int n_partial, float* __restrict__ loss_out) {  // [3]: loss, l1, ssim
     __shared__ __align__(16) float s_in[3][kIn][kPitch];
-    __shared__ __align__(16) float s_h[3][kIn][kTile];
-    __shared__ float s_v[3][kTile][kTile];
+    __shared__ __align__(16) float s_h[3][kIn][kPitchH];
+    __shared__ float s_v[3][kTile][kPitchH];
     const int ch = blockIdx.z, tx0 = blockIdx.x * kTile, ty0 = blockIdx.y * kTile;
     const size_t plane = (size_t)H * W, maps = (size_t)C * plane;
     for (int r = threadIdx.x >> 5, c = threadIdx.x & 31; r < kIn; r += kTile * kTile / 32) {
