@@ -50,7 +50,7 @@ __device__ __forceinline__ float seg_dist2(const BoneSm& b, float x, float y, fl
 // bytes of dynamic shared memory for the bone table (+ the per-bone gradient accumulators of a backward kernel)
 inline size_t bone_smem_bytes(int J, bool with_grad_acc) {
     size_t b = sizeof(BoneSm) * (size_t)(J > 1 ? J - 1 : 1);
-    if (with_grad_acc) b += sizeof(float) * ((size_t)(J - 1) * 13 + 3);
+    if (with_grad_acc) b += 8 * sizeof(float) * ((size_t)(J - 1) * 13 + 3);  // one accumulator row per warp of a 256-thread CTA
     return b;
 }
 

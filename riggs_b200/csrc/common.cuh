@@ -92,4 +92,20 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
+// Sum each of v[0..15] over the 32 lanes with 16 shuffles; the lane holds the total of v[(lane >> 1) & 15].
+__device__ __forceinline__ float transpose_reduce16(const float* v, int lane) {
+    const unsigned full = 0xffffffffu;
+    const bool u4 = lane & 16, u3 = lane & 8, u2 = lane & 4, u1 = lane & 2;
+    float w[8], x[4], y[2];
+#pragma unroll
+    for (int i = 0; i < 8; i++) w[i] = (u4 ? v[8 + i] : v[i]) + __shfl_xor_sync(full, u4 ? v[i] : v[8 + i], 16);
+#pragma unroll
+    for (int i = 0; i < 4; i++) x[i] = (u3 ? w[4 + i] : w[i]) + __shfl_xor_sync(full, u3 ? w[i] : w[4 + i], 8);
+#pragma unroll
+    for (int i = 0; i < 2; i++) y[i] = (u2 ? x[2 + i] : x[i]) + __shfl_xor_sync(full, u2 ? x[i] : x[2 + i], 4);
+    float s = (u1 ? y[1] : y[0]) + __shfl_xor_sync(full, u1 ? y[0] : y[1], 2);
+    s += __shfl_xor_sync(full, s, 1);
+    return s;  // value id = 8*u4 + 4*u3 + 2*u2 + u1
+}
+
 }  // namespace rg

@@ -300,16 +300,18 @@ __global__ void __launch_bounds__(256) skin_forward_kernel(SkinArgs a) {
 
 // Backward of the linear-blend forward.  Per Gaussian two sweeps over the bone table (weights are recomputed,
 // nothing was stored): sweep 1 gets the normaliser and sum_k w_k dL/dw_k, sweep 2 emits the per-bone terms.
-// Per-bone sums (dG 12 floats, d radius 1 float) are reduced warp-wide with shuffles, met in shared memory
-// and flushed with one global atomicAdd per value per CTA; the grid is persistent (a few CTAs per SM), so
+// Per-bone sums (dG 12 floats, d radius 1 float) are reduced warp-wide with a 16-shuffle transpose-reduce into the
+// warp's own accumulator row in shared memory (no shared atomics) and flushed with one global atomicAdd per value per CTA; the grid is persistent (a few CTAs per SM), so
 // a frame costs ~600 x 13(J-1) atomics instead of N x 13(J-1).
 __global__ void __launch_bounds__(256) skin_backward_kernel(SkinBwdArgs a) {
     extern __shared__ __align__(16) unsigned char s_raw[];
     BoneSm* s_b = reinterpret_cast<BoneSm*>(s_raw);
     const int K = a.J - 1;
-    float* s_acc = reinterpret_cast<float*>(s_raw + sizeof(BoneSm) * (size_t)max(K, 1));  // K*13 + 3
+    const int acc_stride = K * 13 + 3;  // one row per warp
+    float* s_acc_all = reinterpret_cast<float*>(s_raw + sizeof(BoneSm) * (size_t)max(K, 1));
+    float* s_acc = s_acc_all + (threadIdx.x >> 5) * acc_stride;
     stage_bones(a.J, a.joints, a.parents, a.node_radius_raw, a.G, a.node_rot, s_b);
-    for (int i = threadIdx.x; i < K * 13 + 3; i += blockDim.x) s_acc[i] = 0.f;
+    for (int i = threadIdx.x; i < 8 * acc_stride; i += blockDim.x) s_acc_all[i] = 0.f;
     __syncthreads();
     const int lane = threadIdx.x & 31;
     const float g0 = a.global_trans[0], g1 = a.global_trans[1], g2 = a.global_trans[2];
@@ -360,7 +362,7 @@ __global__ void __launch_bounds__(256) skin_backward_kernel(SkinBwdArgs a) {
         // global_trans gradient: sum_n m a
         {
             const float s0 = warp_sum(mgx), s1 = warp_sum(mgy), s2 = warp_sum(mgz);
-            if (lane == 0) { atomicAdd(&s_acc[K * 13], s0); atomicAdd(&s_acc[K * 13 + 1], s1); atomicAdd(&s_acc[K * 13 + 2], s2); }
+            if (lane == 0) { s_acc[K * 13] += s0; s_acc[K * 13 + 1] += s1; s_acc[K * 13 + 2] += s2; }
         }
         // sweep 2
         for (int k = 0; k < K; k++) {
@@ -376,29 +378,35 @@ __global__ void __launch_bounds__(256) skin_backward_kernel(SkinBwdArgs a) {
             const float c = gx * yx + gy * yy + gz * yz + h0 * b.q[0] + h1 * b.q[1] + h2 * b.q[2] + h3 * b.q[3];
             const float dwhat = live ? m * (c - cbar) * inv : 0.f;  // dL/d what_k
             if (a.dmlp_weight && live) a.dmlp_weight[(size_t)n * K + k] = dwhat * e;
-            float v[13];
+            float v[16];
             v[0] = mgx * w * x; v[1] = mgx * w * y; v[2] = mgx * w * z;
             v[3] = mgy * w * x; v[4] = mgy * w * y; v[5] = mgy * w * z;
             v[6] = mgz * w * x; v[7] = mgz * w * y; v[8] = mgz * w * z;
             v[9] = mgx * w; v[10] = mgy * w; v[11] = mgz * w;
             v[12] = dwhat * s * e * d2 * (2.0f * b.inv_2r2);  // d/d(log r): e * d2 / r^2
-#pragma unroll
-            for (int c2 = 0; c2 < 13; c2++) {
-                const float r = warp_sum(v[c2]);
-                if (lane == c2) atomicAdd(&s_acc[k * 13 + c2], r);
-            }
+            v[13] = v[14] = v[15] = 0.f;
+            const float r = transpose_reduce16(v, lane);  // the lane holds the total of v[(lane >> 1) & 15]
+            const int my_id = (lane >> 1) & 15;
+            if (!(lane & 1) && my_id < 13) s_acc[k * 13 + my_id] += r;
         }
     }
     __syncthreads();
     for (int i = threadIdx.x; i < K * 13; i += blockDim.x) {
         const int k = i / 13, c = i % 13;
-        const float val = s_acc[i];
+        float val = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; w++) val += s_acc_all[w * acc_stride + i];
         if (val != 0.f) {
             if (c < 12) atomicAdd(&a.dG[12 * (k + 1) + c], val);
             else atomicAdd(&a.dnode_radius_raw[k + 1], val);
         }
     }
-    if (threadIdx.x < 3 && a.dglobal_trans) atomicAdd(&a.dglobal_trans[threadIdx.x], s_acc[K * 13 + threadIdx.x]);
+    if (threadIdx.x < 3 && a.dglobal_trans) {
+        float val = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; w++) val += s_acc_all[w * acc_stride + K * 13 + threadIdx.x];
+        atomicAdd(&a.dglobal_trans[threadIdx.x], val);
+    }
 }
 
 int launch_fk_forward(int F, int J, const float* local_rot, const float* gtrans, const float* joints,
@@ -437,6 +445,11 @@ int launch_skin_backward(const SkinBwdArgs& a, cudaStream_t stream) {
     int blocks = (a.N + 255) / 256;
     if (blocks > RG_NUM_SMS * 4) blocks = RG_NUM_SMS * 4;
     LaunchScope ls("skin_backward", stream);
+    static bool attr_set = false;
+    if (!attr_set) {  // J = 128: 13 KB of bones + 8 accumulator rows of 6.6 KB
+        cudaFuncSetAttribute(skin_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        attr_set = true;
+    }
     skin_backward_kernel<<<blocks, 256, bone_smem_bytes(a.J, true), stream>>>(a);
     return 0;
 }
