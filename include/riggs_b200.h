@@ -266,6 +266,20 @@ int rg_adam_step(int n_groups, const RgAdamGroup* groups, int step, double beta1
 int rg_densification_stats(int P, const float* viewspace_grad, const int* radii, float* xyz_gradient_accum, float* denom,
                            float* max_radii2D, rg_stream_t stream);
 
+/* Boolean-mask compaction of every per-Gaussian tensor in one go: GaussianModel.prune_points / _prune_optimizer
+ * (scene/gaussian_model.py:356-391) apply `tensor[valid_points_mask]` to the parameters, their Adam moments and the
+ * densification statistics one by one.  keep: P bytes (non-zero = the row survives); every tensor has P rows of
+ * row_bytes (a multiple of 4) and a destination with room for the surviving rows (P rows is always enough); survivors
+ * keep their order; *count_out (device int) receives their number.  scratch: rg_compact_scratch_bytes(P). */
+typedef struct RgRowTensor {
+    const void* src;
+    void* dst;
+    size_t row_bytes;
+} RgRowTensor;
+size_t rg_compact_scratch_bytes(int P);
+int rg_compact_rows(int P, const uint8_t* keep, int n_tensors, const RgRowTensor* tensors, void* scratch, size_t scratch_bytes,
+                    int* count_out, rg_stream_t stream);
+
 /* rg_skinned_backward in parts, for callers that overlap the gradient all-reduce with the backward: `phases` is a bit
  * set -- 1: zero the accumulators and run the blend backward, 2: per-Gaussian backward (parameter gradients) of rows
  * [row_begin, row_end) only (row_begin a multiple of 256), 4: skeleton backward (d_local_rot, d_global_trans,

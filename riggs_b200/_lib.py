@@ -35,6 +35,10 @@ class RgAdamGroup(C.Structure):
                 ("n", C.c_size_t), ("lr", C.c_float)]
 
 
+class RgRowTensor(C.Structure):
+    _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("row_bytes", C.c_size_t)]
+
+
 class RgWorkspace(C.Structure):
     _fields_ = [("geom", C.c_void_p), ("geom_bytes", C.c_size_t), ("image", C.c_void_p), ("image_bytes", C.c_size_t),
                 ("binning", C.c_void_p), ("binning_bytes", C.c_size_t)]
@@ -75,6 +79,8 @@ _SIGNATURES = {
     "rg_ssim_l1_loss": (C.c_int, [_i, _i, _i, _p, _p, _f, _p, _p, _p, C.c_size_t, _p]),
     "rg_adam_step": (C.c_int, [_i, _p, _i, C.c_double, C.c_double, C.c_double, _p]),
     "rg_densification_stats": (C.c_int, [_i, _p, _p, _p, _p, _p, _p]),
+    "rg_compact_scratch_bytes": (C.c_size_t, [_i]),
+    "rg_compact_rows": (C.c_int, [_i, _p, _i, _p, _p, C.c_size_t, _p, _p]),
     "rg_launch_count": (C.c_longlong, []),
     "rg_profile_enable": (None, [_i]),
     "rg_profile_reset": (None, []),

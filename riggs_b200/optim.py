@@ -86,3 +86,66 @@ def add_densification_stats(viewspace_point_tensor: torch.Tensor, radii: torch.T
     with torch.cuda.device(g.device):
         check(_lib.lib().rg_densification_stats(P, ptr(g), ptr(radii), ptr(xyz_gradient_accum), ptr(denom),
                                                 ptr(max_radii2D), stream_ptr()), "rg_densification_stats")
+
+
+_COMPACT_SCRATCH: Dict[tuple, torch.Tensor] = {}
+
+
+@torch.no_grad()
+def compact_rows(keep: torch.Tensor, tensors: List[torch.Tensor]) -> List[torch.Tensor]:
+    """``[t[keep] for t in tensors]`` for tensors that share their first dimension, with one scan of the mask and one
+    copy kernel for all of them (csrc/compact.cu).  keep: bool (P,); tensors: contiguous, 4-byte element types."""
+    if not keep.is_cuda:
+        raise _lib.RiggsError("compact_rows needs CUDA tensors; riggs_b200 has no CPU path")
+    P = keep.numel()
+    keep_u8 = keep.reshape(-1).to(torch.uint8).contiguous()
+    srcs = []
+    for t in tensors:
+        if t.shape[0] != P or t.element_size() != 4:
+            raise ValueError("compact_rows: every tensor needs P rows of 4-byte elements")
+        srcs.append(t if t.is_contiguous() else t.contiguous())
+    L = _lib.lib()
+    dev = keep.device
+    nbytes = int(L.rg_compact_scratch_bytes(P))
+    key = (str(dev), torch.cuda.current_stream(dev).cuda_stream, nbytes)
+    sc = _COMPACT_SCRATCH.get(key)
+    if sc is None:
+        sc = _COMPACT_SCRATCH[key] = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    count = torch.empty((), dtype=torch.int32, device=dev)
+    dsts = [torch.empty_like(t) for t in srcs]  # P rows of room; sliced to the survivors below
+    arr = (_lib.RgRowTensor * len(srcs))(*[_lib.RgRowTensor(ptr(s), ptr(d), (s.numel() // P) * 4) if P else _lib.RgRowTensor()
+                                          for s, d in zip(srcs, dsts)])
+    if P:
+        with torch.cuda.device(dev):
+            check(L.rg_compact_rows(P, ptr(keep_u8), len(srcs), C.cast(arr, C.c_void_p), ptr(sc), sc.numel(), ptr(count),
+                                    stream_ptr()), "rg_compact_rows")
+    n = int(count) if P else 0  # the one host round trip, as with boolean indexing
+    return [d[:n].clone() if n < P else d for d in dsts]
+
+
+def prune_points(optimizer: FusedAdam, mask: torch.Tensor, stats: Optional[Dict[str, torch.Tensor]] = None):
+    """GaussianModel.prune_points(mask) + _prune_optimizer (scene/gaussian_model.py:356-391) for a ``FusedAdam`` with
+    one parameter per group: drops the rows where ``mask`` is True from every parameter, its Adam moments and the
+    statistics in ``stats`` (xyz_gradient_accum, denom, max_radii2D ...).  Returns ({group name: new nn.Parameter},
+    {stat name: new tensor}); the optimizer's groups and state are updated in place like the reference does."""
+    keep = ~mask.reshape(-1).bool()
+    params = [g["params"][0] for g in optimizer.param_groups]
+    tensors: List[torch.Tensor] = [p.detach() for p in params]
+    has_state = [optimizer.state.get(p) for p in params]
+    for st in has_state:
+        if st is not None:
+            tensors += [st["exp_avg"], st["exp_avg_sq"]]
+    stat_names = list(stats or {})
+    tensors += [stats[k] for k in stat_names]
+    out = compact_rows(keep, tensors)
+    new_params: Dict[str, torch.nn.Parameter] = {}
+    k = len(params)
+    for i, (g, p, st) in enumerate(zip(optimizer.param_groups, params, has_state)):
+        newp = torch.nn.Parameter(out[i].requires_grad_(True))
+        if st is not None:
+            del optimizer.state[p]
+            optimizer.state[newp] = {"exp_avg": out[k], "exp_avg_sq": out[k + 1]}
+            k += 2
+        g["params"][0] = newp
+        new_params[g.get("name", str(i))] = newp
+    return new_params, {n: out[k + j] for j, n in enumerate(stat_names)}

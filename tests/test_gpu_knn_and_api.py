@@ -286,3 +286,40 @@ def test_densification_stats_match_reference_expressions():
     torch.cuda.synchronize()
     assert helpers.rel_err(accum.cpu().numpy(), w_accum.cpu().numpy()) <= 1e-6
     assert torch.equal(denom, w_denom) and torch.equal(maxr, w_maxr)
+
+
+def test_prune_points_matches_boolean_indexing():
+    """optim.prune_points against the reference's tensor[valid_points_mask] on parameters, Adam moments and statistics
+    (bit-exact: pure data movement), including the all-kept, none-kept and single-row cases."""
+    from riggs_b200.optim import FusedAdam, compact_rows, prune_points
+    g = torch.Generator().manual_seed(31)
+    P = 12_345
+    shapes = {"xyz": (P, 3), "f_dc": (P, 1, 3), "f_rest": (P, 15, 3), "opacity": (P, 1), "scaling": (P, 3), "rotation": (P, 4)}
+    params = {k: torch.randn(*s, generator=g).cuda().requires_grad_(True) for k, s in shapes.items()}
+    opt = FusedAdam([{"params": [params[k]], "lr": 1e-3, "name": k} for k in shapes], lr=0.0, eps=1e-15)
+    for p in params.values():
+        p.grad = torch.randn_like(p)
+    opt.step()
+    stats = {"xyz_gradient_accum": torch.rand(P, 1, generator=g).cuda(), "denom": torch.rand(P, 1, generator=g).cuda(),
+             "max_radii2D": torch.rand(P, generator=g).cuda()}
+    mask = (torch.rand(P, generator=g) < 0.3).cuda()
+    valid = ~mask
+    want_p = {k: v.detach()[valid].clone() for k, v in params.items()}
+    want_m = {k: opt.state[v]["exp_avg"][valid].clone() for k, v in params.items()}
+    want_v = {k: opt.state[v]["exp_avg_sq"][valid].clone() for k, v in params.items()}
+    want_s = {k: v[valid].clone() for k, v in stats.items()}
+    new_p, new_s = prune_points(opt, mask, stats)
+    for grp in opt.param_groups:
+        k = grp["name"]
+        assert grp["params"][0] is new_p[k] and new_p[k].requires_grad and torch.equal(new_p[k].detach(), want_p[k])
+        assert torch.equal(opt.state[new_p[k]]["exp_avg"], want_m[k]) and torch.equal(opt.state[new_p[k]]["exp_avg_sq"], want_v[k])
+    for k in stats:
+        assert torch.equal(new_s[k], want_s[k])
+    # the optimizer keeps stepping on the pruned tensors
+    for p in new_p.values():
+        p.grad = torch.randn_like(p)
+    opt.step()
+    x = torch.arange(7 * 5, dtype=torch.float32).reshape(7, 5).cuda()
+    for keep in (torch.ones(7, dtype=torch.bool), torch.zeros(7, dtype=torch.bool), torch.tensor([0, 0, 0, 1, 0, 0, 0]).bool()):
+        (y,) = compact_rows(keep.cuda(), [x])
+        assert torch.equal(y, x[keep.cuda()])
