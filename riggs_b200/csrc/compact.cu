@@ -32,21 +32,18 @@ __global__ void __launch_bounds__(256) survivors_kernel(int P, const uint8_t* __
     if (i == P - 1) *count_out = excl[i] + (keep[i] ? 1 : 0);
 }
 
-// one thread per (surviving row, word of the concatenated row)
+// blockIdx.y = tensor; threads run over (surviving row, word) of that tensor: coalesced writes, row-gathered reads
 __global__ void __launch_bounds__(256) gather_rows_kernel(RowTable t, const int* __restrict__ src_row,
                                                           const int* __restrict__ count) {
-    const size_t row_words = t.end[t.n - 1];
-    const size_t total = (size_t)(*count) * row_words;
+    const int q = blockIdx.y;
+    const uint32_t words = t.words[q];
+    const uint32_t* __restrict__ src = t.src[q];
+    uint32_t* __restrict__ dst = t.dst[q];
+    const size_t total = (size_t)(*count) * words;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-        // tensor-major inside a block of work would be friendlier to coalescing; rows are short, so go tensor by tensor:
-        // index = tensor segment first, then (row, word)
-        size_t rem = i;
-        int q = 0;
-        const size_t n = (size_t)(*count);
-        while (rem >= n * t.words[q]) { rem -= n * t.words[q]; q++; }
-        const size_t r = rem / t.words[q], w = rem - r * t.words[q];
-        t.dst[q][r * t.words[q] + w] = t.src[q][(size_t)src_row[r] * t.words[q] + w];
+        const size_t r = i / words, w = i - r * words;
+        dst[i] = src[(size_t)src_row[r] * words + w];
     }
 }
 
@@ -96,9 +93,9 @@ int rg_compact_rows(int P, const uint8_t* keep, int n_tensors, const RgRowTensor
     LaunchScope ls("compact_rows", stream, 0);
     if (cub::DeviceScan::ExclusiveSum(base, temp, it, excl, P, stream) != cudaSuccess) { set_error("rg_compact_rows: scan failed"); return -1; }
     survivors_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, keep, excl, src_row, count_out);
-    size_t blocks = ((size_t)P * acc + 255) / 256;
-    if (blocks > (size_t)RG_NUM_SMS * 16) blocks = (size_t)RG_NUM_SMS * 16;
-    gather_rows_kernel<<<(unsigned)blocks, 256, 0, stream>>>(t, src_row, count_out);
+    size_t blocks = ((size_t)P * 4 + 255) / 256;  // grid-stride: about four words per thread for a 1-word row
+    if (blocks > (size_t)RG_NUM_SMS * 8) blocks = (size_t)RG_NUM_SMS * 8;
+    gather_rows_kernel<<<dim3((unsigned)blocks, (unsigned)n_tensors), 256, 0, stream>>>(t, src_row, count_out);
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 

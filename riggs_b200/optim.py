@@ -111,16 +111,16 @@ def compact_rows(keep: torch.Tensor, tensors: List[torch.Tensor]) -> List[torch.
     sc = _COMPACT_SCRATCH.get(key)
     if sc is None:
         sc = _COMPACT_SCRATCH[key] = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    n = int(keep_u8.sum()) if P else 0  # the one host round trip, as with boolean indexing
     count = torch.empty((), dtype=torch.int32, device=dev)
-    dsts = [torch.empty_like(t) for t in srcs]  # P rows of room; sliced to the survivors below
-    arr = (_lib.RgRowTensor * len(srcs))(*[_lib.RgRowTensor(ptr(s), ptr(d), (s.numel() // P) * 4) if P else _lib.RgRowTensor()
-                                          for s, d in zip(srcs, dsts)])
-    if P:
+    dsts = [torch.empty((n,) + tuple(t.shape[1:]), dtype=t.dtype, device=dev) for t in srcs]
+    if n:
+        arr = (_lib.RgRowTensor * len(srcs))(*[_lib.RgRowTensor(ptr(s), ptr(d), (s.numel() // P) * 4)
+                                              for s, d in zip(srcs, dsts)])
         with torch.cuda.device(dev):
             check(L.rg_compact_rows(P, ptr(keep_u8), len(srcs), C.cast(arr, C.c_void_p), ptr(sc), sc.numel(), ptr(count),
                                     stream_ptr()), "rg_compact_rows")
-    n = int(count) if P else 0  # the one host round trip, as with boolean indexing
-    return [d[:n].clone() if n < P else d for d in dsts]
+    return dsts
 
 
 def prune_points(optimizer: FusedAdam, mask: torch.Tensor, stats: Optional[Dict[str, torch.Tensor]] = None):
