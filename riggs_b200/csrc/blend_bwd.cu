@@ -4,7 +4,8 @@
 // tile that walks the whole list in lock step.  Here (same decomposition as blend_fwd.cu)
 //  * one warp = one 8x4 pixel block, independent of the rest of its tile: it replays only the entries in front of
 //    ITS deepest last contributor (the reference skips the others one by one, backward.cu:517-519), and of those only
-//    the instances whose alpha >= 1/255 footprint can reach the block (ListWalker of blend_common.cuh);
+//    the instances the forward blend marked as able to reach the block (MaskWalker of blend_common.cuh reads the
+//    block's survivor bitmap: no culling test is repeated, records are fetched for survivors only);
 //  * phase A, one pixel per lane: the reference's recurrence (T, the accumulated colour/depth/alpha behind the
 //    instance) in the reference's expression order.  Of the ten per-pair gradient terms only TWO scalars depend on
 //    that recurrence:  Q = G dL/d(alpha)  and  W = alpha T ; the rest is geometry of the pair and constants of the
@@ -14,7 +15,8 @@
 //    (lx, ly = pixel position inside the block), so each lane runs 32 x 10 FMAs down its column, rebuilds the moments
 //    about its instance's centre and issues its ten reductions to global memory itself.
 // Against a cross-lane reduction per instance (12 shuffles + ~40 selects/adds + one RED instruction, per instance and
-// per block) this halves the kernel's instruction count: the sums cost 13 instructions per pixel per 32 instances.
+// per block) the sums cost 13 instructions per pixel per 32 instances and nothing sits in the per-instance dependent
+// chain any more (measured on the C0 frame: 114 M -> 80 M warp instructions, 205 -> 147 us with the bitmap walk).
 // Sums differ from the reference's in association only (tolerance 1e-4).
 #include "blend_common.cuh"
 #include "kernels.cuh"

@@ -11,6 +11,8 @@
 //             into the buffer the caller's per-pixel loop reads.
 // While the caller blends the survivors of group g, these requests are in flight: stage-2 records of group g+1
 // (its stage 1 already ran), rec[0] of group g+2, list entries of group g+3.
+// The forward walker also raises one bit per survivor in its block's bitmap over the instance list; the backward blend
+// walks by those bits (MaskWalker) instead of testing again.
 #pragma once
 #include "common.cuh"
 #include "cull.cuh"
