@@ -280,6 +280,13 @@ size_t rg_compact_scratch_bytes(int P);
 int rg_compact_rows(int P, const uint8_t* keep, int n_tensors, const RgRowTensor* tensors, void* scratch, size_t scratch_bytes,
                     int* count_out, rg_stream_t stream);
 
+/* K nearest of M nodes for each of N points, brute force: the search the reference's stage-1 control-node code gets from
+ * pytorch3d.ops.knn_points (utils/time_utils.py:950,980,1051,1061,1124).  points (N,D), nodes (M,D), 1 <= D <= 8,
+ * 1 <= K <= 16; dists (N,K) squared Euclidean distances in ascending order, idx (N,K) int64; ties go to the lower index;
+ * with M < K the tail is padded with distance 0 / index 0 as pytorch3d does. */
+int rg_knn_points(int N, int M, int D, int K, const float* points, const float* nodes, float* dists, long long* idx,
+                  rg_stream_t stream);
+
 /* rg_skinned_backward in parts, for callers that overlap the gradient all-reduce with the backward: `phases` is a bit
  * set -- 1: zero the accumulators and run the blend backward, 2: per-Gaussian backward (parameter gradients) of rows
  * [row_begin, row_end) only (row_begin a multiple of 256), 4: skeleton backward (d_local_rot, d_global_trans,

@@ -81,6 +81,7 @@ _SIGNATURES = {
     "rg_densification_stats": (C.c_int, [_i, _p, _p, _p, _p, _p, _p]),
     "rg_compact_scratch_bytes": (C.c_size_t, [_i]),
     "rg_compact_rows": (C.c_int, [_i, _p, _i, _p, _p, C.c_size_t, _p, _p]),
+    "rg_knn_points": (C.c_int, [_i, _i, _i, _i, _p, _p, _p, _p, _p]),
     "rg_launch_count": (C.c_longlong, []),
     "rg_profile_enable": (None, [_i]),
     "rg_profile_reset": (None, []),

@@ -323,3 +323,40 @@ def test_prune_points_matches_boolean_indexing():
     for keep in (torch.ones(7, dtype=torch.bool), torch.zeros(7, dtype=torch.bool), torch.tensor([0, 0, 0, 1, 0, 0, 0]).bool()):
         (y,) = compact_rows(keep.cuda(), [x])
         assert torch.equal(y, x[keep.cuda()])
+
+
+@pytest.mark.parametrize("N,M,D,K", [(5000, 512, 3, 3), (3001, 1024, 3, 1), (1000, 1000, 3, 9), (777, 1500, 5, 4),
+                                     (64, 5, 3, 8), (10, 2500, 8, 16)])
+def test_knn_points_vs_bruteforce(N, M, D, K):
+    """knn.knn_points against a float64 brute-force search: same neighbours in the same order, squared distances to
+    fp32 rounding; M < K pads with zeros as pytorch3d does; self-query (the reference's node graph, :1061) finds itself."""
+    from riggs_b200.knn import knn_points
+    g = torch.Generator().manual_seed(N + M)
+    p1 = torch.randn(1, N, D, generator=g).cuda()
+    p2 = p1[:, :M].clone() if (N == M) else torch.randn(1, M, D, generator=g).cuda()
+    out = knn_points(p1, p2, None, None, K=K, return_nn=True)
+    d = ((p1[0].double()[:, None] - p2[0].double()[None]) ** 2).sum(-1)
+    k = min(K, M)
+    wd, wi = torch.topk(d, k, dim=1, largest=False, sorted=True)
+    assert out.dists.shape == (1, N, K) and out.idx.dtype == torch.int64
+    assert torch.equal(out.idx[0, :, :k], wi)
+    assert helpers.rel_err(out.dists[0, :, :k].cpu().numpy(), wd.cpu().numpy()) <= 1e-6
+    assert torch.equal(out.knn[0, :, :k], p2[0][wi])
+    if K > M:
+        assert float(out.dists[0, :, M:].abs().max()) == 0.0 and int(out.idx[0, :, M:].max()) == 0
+    if N == M:
+        assert torch.equal(out.idx[0, :, 0], torch.arange(N, device="cuda"))
+
+
+def test_knn_points_gradient():
+    from riggs_b200.knn import knn_points
+    g = torch.Generator().manual_seed(5)
+    p1 = torch.randn(1, 300, 3, generator=g).cuda().requires_grad_(True)
+    p2 = torch.randn(1, 40, 3, generator=g).cuda().requires_grad_(True)
+    out = knn_points(p1, p2, K=3)
+    out.dists.sum().backward()
+    q1, q2 = p1.detach().clone().requires_grad_(True), p2.detach().clone().requires_grad_(True)
+    d = ((q1[0][:, None] - q2[0][None]) ** 2).sum(-1)
+    torch.topk(d, 3, dim=1, largest=False).values.sum().backward()
+    assert helpers.rel_err(p1.grad.cpu().numpy(), q1.grad.cpu().numpy()) <= 1e-5
+    assert helpers.rel_err(p2.grad.cpu().numpy(), q2.grad.cpu().numpy()) <= 1e-5
