@@ -240,3 +240,75 @@ class GraphedStep:
         self._event = torch.cuda.Event()
         self._event.record()
         return self.loss
+
+
+class PipelinedSteps:
+    """Input / output pipeline around ``GraphedStep`` for callers whose per-step inputs live in HOST memory
+    (a data loader's pinned target image, camera and pose) and who read every step's loss on the host.
+
+    Two captured graphs (slots) with their own static input buffers and workspaces alternate: while slot ``i % 2``
+    computes step i, ``feed`` copies step i+1's host inputs straight into the other slot's static buffers on a
+    copy stream (no staging copy on the compute stream), and step i's loss travels to a pinned host word that
+    ``result`` reads one step late.  The compute stream therefore always has the next replay queued; nothing
+    waits for the host.  Gradients are those of the slot replayed last (``param.grad``), as with ``GraphedStep``.
+    """
+
+    def __init__(self, hp: HotPath, cam, pose: Dict[str, torch.Tensor], target: torch.Tensor, warmup: int = 3,
+                 slots: int = 2):
+        self.hp = hp
+        self.slots = [GraphedStep(hp, cam, pose, target, warmup=warmup) for _ in range(slots)]
+        self.launches_per_replay = self.slots[0].launches_per_replay
+        self._copy_stream = torch.cuda.Stream(device=hp.device)
+        self._ready = [None] * slots   # inputs of the slot's next step have arrived
+        self._done = [None] * slots    # the slot's last replay (and its loss copy) has finished
+        self._loss_host = [torch.zeros(1).pin_memory() for _ in range(slots)]
+        self._fed = 0
+        self._run = 0
+
+    def feed(self, cam=None, pose=None, target=None) -> None:
+        """Queues the host -> device copies of the NEXT unfed step's inputs (pinned tensors make them asynchronous)."""
+        k = self._fed % len(self.slots)
+        g, cs = self.slots[k], self._copy_stream
+        if self._done[k] is not None:
+            cs.wait_event(self._done[k])  # the slot's previous step no longer reads these buffers
+        with torch.cuda.stream(cs), torch.no_grad():
+            if cam is not None:
+                g.cam.world_view_transform.copy_(cam.world_view_transform, non_blocking=True)
+                g.cam.full_proj_transform.copy_(cam.full_proj_transform, non_blocking=True)
+                g.cam.camera_center.copy_(cam.camera_center, non_blocking=True)
+            if pose is not None:
+                for name, v in pose.items():
+                    g.pose[name].copy_(v, non_blocking=True)
+            if target is not None:
+                g.target.copy_(target, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(cs)
+        self._ready[k] = ev
+        self._fed += 1
+
+    def launch(self) -> int:
+        """Replays the next step on the current stream (after its inputs have arrived) and queues the read-back of
+        its loss; returns the step's index for ``result``."""
+        i = self._run
+        k = i % len(self.slots)
+        g = self.slots[k]
+        if self._ready[k] is not None:
+            torch.cuda.current_stream().wait_event(self._ready[k])
+            self._ready[k] = None
+        loss = g.step()
+        self._loss_host[k].copy_(loss.detach().reshape(1), non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        self._done[k] = ev
+        self._run += 1
+        return i
+
+    def result(self, i: int) -> float:
+        """Host value of step i's loss; call it at most ``slots - 1`` launches late (the slot's word is reused)."""
+        k = i % len(self.slots)
+        self._done[k].synchronize()
+        return float(self._loss_host[k])
+
+    @property
+    def pose_grads(self) -> Dict[str, torch.Tensor]:
+        return self.slots[(self._run - 1) % len(self.slots)].pose_grads

@@ -265,3 +265,45 @@ def test_graphed_step_replays_the_eager_step():
             assert helpers.rel_err(p.grad.cpu().numpy(), wg[n].cpu().numpy(), floor=1e-7) <= 1e-4, n
         for k, v in gs.pose_grads.items():
             assert helpers.rel_err(v.cpu().numpy(), wp[k].cpu().numpy(), floor=1e-7) <= 1e-4, k
+
+
+def test_pipelined_steps_feed_from_host_and_read_losses_late():
+    """PipelinedSteps: host inputs fed one step ahead into the idle slot, losses read one step late -- every step
+    gives the loss and the gradients of the eager step on the same inputs."""
+    from riggs_b200.hotpath import HotPath, PipelinedSteps
+    scene = synth.make_config("small", n_views=2)
+    hp = HotPath(scene, device="cuda")
+    cams = [c.to("cuda") for c in scene.cameras[:2]]
+    H, W = cams[0].image_height, cams[0].image_width
+    g = torch.Generator().manual_seed(6)
+    targets = [torch.rand(3, H, W, generator=g).cuda() for _ in range(2)]
+    poses = [{k: v.cuda() for k, v in p.items()} for p in scene.poses[:2]]
+
+    def eager(i):
+        hp.zero_grad()
+        ps = {k: v.clone().requires_grad_(True) for k, v in poses[i].items()}
+        loss = hp.step(cams[i], ps, targets[i])
+        return float(loss), {n: p.grad.clone() for n, p in hp.named_parameters()}, {k: v.grad.clone() for k, v in ps.items()}
+
+    want = [eager(0), eager(1)]
+    host = [(cams[i], {k: v.cpu().pin_memory() for k, v in poses[i].items()}, targets[i].cpu().pin_memory())
+            for i in range(2)]
+    order = (0, 1, 1, 0, 1)
+    pipe = PipelinedSteps(hp, cams[0], poses[0], targets[0])
+    pipe.feed(*host[order[0]])
+    losses = {}
+    for n, i in enumerate(order):
+        assert pipe.launch() == n
+        if n + 1 < len(order):
+            pipe.feed(*host[order[n + 1]])
+        if n > 0:
+            losses[n - 1] = pipe.result(n - 1)
+        torch.cuda.synchronize()
+        wl, wg, wp = want[i]
+        for name, p in hp.named_parameters():
+            assert helpers.rel_err(p.grad.cpu().numpy(), wg[name].cpu().numpy(), floor=1e-7) <= 1e-4, name
+        for k, v in pipe.pose_grads.items():
+            assert helpers.rel_err(v.cpu().numpy(), wp[k].cpu().numpy(), floor=1e-7) <= 1e-4, k
+    losses[len(order) - 1] = pipe.result(len(order) - 1)
+    for n, i in enumerate(order):
+        assert abs(losses[n] - want[i][0]) <= 1e-6 * max(1.0, abs(want[i][0])), n
