@@ -169,3 +169,61 @@ def activate(xyz, scaling_raw, rotation_raw, opacity_raw, d_xyz, d_rotation, d_s
     rotations = F.normalize(rotation_raw + d_rotation)
     opacity = torch.sigmoid(opacity_raw)
     return means3D, scales, rotations, opacity
+
+
+# ---- stage-1 control-node warp ------------------------------------------------------
+# Reference lines restated: ControlNodeWarp.cal_nn_weight utils/time_utils.py:934-967 (non-skinning branch,
+# gs_kernel=True) and ControlNodeWarp.forward :1133-1236 without the animation branches (node_trans_bias,
+# animation_d_values) and the ARAP regulariser.  Pinned by tests/golden/node_warp_*.npz, which
+# tests/golden/make_node_warp_golden.py produced from the reference's own methods.
+
+def knn_brute(p, nodes, K):
+    """pytorch3d.ops.knn_points' contract for one cloud: K smallest squared distances, ascending, differentiable."""
+    d = ((p[:, None, :] - nodes[None, :, :]) ** 2).sum(-1)
+    idx = torch.topk(d.detach().double(), K, dim=-1, largest=False, sorted=True).indices
+    return torch.gather(d, 1, idx), idx
+
+
+def node_nn_weight(x, feature, nodes, node_radius_raw, node_weight_raw, K, hyper_dim):
+    """(nn_weight, nn_dist, nn_idx): utils/time_utils.py:943-963."""
+    p = x.detach()
+    if hyper_dim > 0 and feature is not None:
+        p = torch.cat([p, feature[..., :hyper_dim]], -1)
+        nd = torch.cat([nodes[..., :3].detach(), nodes[..., 3:]], -1)
+    else:
+        nd = nodes[..., :3].detach()
+    nn_dist, nn_idx = knn_brute(p, nd, K)
+    radius = torch.exp(node_radius_raw)[nn_idx]
+    w = torch.exp(-nn_dist / (2 * radius ** 2))
+    if node_weight_raw is not None:
+        w = w * torch.sigmoid(node_weight_raw.reshape(-1))[nn_idx]
+    w = w + 1e-7
+    return w / w.sum(-1, keepdim=True), nn_dist, nn_idx
+
+
+def node_warp(x, feature, nodes, node_radius_raw, node_weight_raw, node_attrs, motion_mask, K=3, hyper_dim=2,
+              local_frame=True, d_rot_as_res=True):
+    """ControlNodeWarp.forward (:1133-1198, 1213-1224): blends the per-node motion onto the points."""
+    x = x.detach()
+    w, dist, idx = node_nn_weight(x, feature, nodes, node_radius_raw, node_weight_raw, K, hyper_dim)
+    bias = torch.tensor([1.0, 0, 0, 0], dtype=x.dtype)
+    t, r, s = node_attrs["d_xyz"], node_attrs["d_rotation"], node_attrs["d_scaling"]
+    if local_frame:
+        R = quat_to_mat(node_attrs["local_rotation"] + bias)
+        c = nodes[idx][..., :3].detach()
+        Ax = torch.einsum("nkab,nkb->nka", R[idx], x[:, None] - c) + c + t[idx]
+        translate = (Ax * w[..., None]).sum(1) - x
+    else:
+        translate = (t[idx] * w[..., None]).sum(1)
+    translate = translate * motion_mask
+    if d_rot_as_res:
+        rotation = (r[idx] * w[..., None]).sum(1) * motion_mask
+    else:
+        rotation = (((r + bias)[idx] * w[..., None]).sum(1) - bias) * motion_mask + bias
+    out = {"d_xyz": translate, "d_rotation": rotation, "d_scaling": (s[idx] * w[..., None]).sum(1) * motion_mask,
+           "d_nodes": nodes[..., :3] + t, "nn_weight": w, "nn_dist": dist, "nn_idx": idx,
+           "d_opacity": None, "d_color": None}
+    for key in ("d_opacity", "d_color"):
+        if node_attrs.get(key) is not None:
+            out[key] = (node_attrs[key][idx] * w[..., None]).sum(1) * motion_mask
+    return out

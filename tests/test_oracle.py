@@ -150,3 +150,38 @@ def test_loss_oracle_vs_reference_golden(tag, tol):
     assert abs(float(s) - float(g[f"{tag}_ssim"])) <= tol
     assert abs(float(loss) - float(g[f"{tag}_loss"])) <= tol
     assert helpers.rel_err(img.grad.numpy(), g[f"{tag}_grad"]) <= max(tol, 1e-12) * 10
+
+
+@pytest.mark.parametrize("name", ["node_warp_local", "node_warp_plain", "node_warp_k4"])
+def test_node_warp_oracle_matches_reference_golden(name):
+    """oracle.skin_oracle.node_warp against outputs and autograd gradients of the reference's ControlNodeWarp
+    (tests/golden/make_node_warp_golden.py)."""
+    g = {k: v for k, v in np.load(os.path.join(os.path.dirname(__file__), "golden", name + ".npz")).items()}
+    T = lambda k, rg=False: torch.from_numpy(g[k]).clone().requires_grad_(rg)
+    K, hyper = int(g["K"]), int(g["hyper"])
+    nodes, radius = T("nodes", True), T("node_radius_raw", True)
+    nw = T("node_weight_raw", True) if int(g["with_node_weight"]) else None
+    feature = T("feature", True) if "feature" in g else None
+    attrs = {k[5:]: T(k, True) for k in g if k.startswith("node_d_") or k == "node_local_rotation"}
+    mask = T("mask", True)
+    out = so.node_warp(T("x"), feature, nodes, radius, nw, attrs, mask, K=K, hyper_dim=hyper,
+                       local_frame=bool(g["local_frame"]), d_rot_as_res=bool(g["d_rot_as_res"]))
+    assert np.array_equal(out["nn_idx"].numpy(), g["nn_idx"])
+    np.testing.assert_allclose(out["nn_weight"].detach().numpy(), g["nn_weight"], rtol=1e-5, atol=1e-7)
+    loss = 0
+    for k in ("d_xyz", "d_rotation", "d_scaling", "d_opacity", "d_color"):
+        if "out_" + k in g:
+            np.testing.assert_allclose(out[k].detach().numpy(), g["out_" + k], rtol=1e-5, atol=1e-6)
+            loss = loss + (out[k] * T("cot_" + k)).sum()
+    loss.backward()
+    close = lambda a, b: np.testing.assert_allclose(a, b, rtol=1e-4, atol=1e-5 * max(1.0, float(np.abs(b).max())))
+    close(mask.grad.numpy(), g["g_mask"])
+    close(radius.grad.numpy(), g["g_node_radius_raw"])
+    if nw is not None:
+        close(nw.grad.numpy(), g["g_node_weight_raw"])
+    if feature is not None:
+        close(feature.grad.numpy(), g["g_feature"])
+        close(nodes.grad.numpy(), g["g_nodes"])
+    for k, v in attrs.items():
+        if v.grad is not None:
+            close(v.grad.numpy(), g["g_node_" + k])
