@@ -234,7 +234,7 @@ def run_ours(args):
     pipe = None
     if gs is not None:  # two captured graphs alternate so that step i+1's inputs land while step i runs (set-up, untimed)
         from riggs_b200.hotpath import PipelinedSteps
-        pipe = PipelinedSteps(hp, cam, pose, target, warmup=3)
+        pipe = PipelinedSteps(hp, cam, pose, target, warmup=3, share_workspace=os.environ.get("RG_PIPE_SHARE", "1") != "0")
         for _ in range(2):
             pipe.feed(cam=_HostCam, pose=pose_host, target=target_host)
             pipe.result(pipe.launch())

@@ -165,6 +165,44 @@ int rg_skin_backward(int N, int J, const float* xyz, const float* joints, const 
                      float* dnode_radius_raw, float* dglobal_trans, float* dmask, float* dmlp_weight,
                      float* doffsets, rg_stream_t stream);
 
+/* ---- stage-1 control-node warp ------------------------------------------------------------------ */
+
+/* K nearest control nodes, their weights and the blend of the per-node motion onto N points.  Replaces
+ * ControlNodeWarp.cal_nn_weight (utils/time_utils.py:934-967, non-skinning branch with gs_kernel=True; the search
+ * itself is pytorch3d.ops.knn_points there) and the blending of ControlNodeWarp.forward (:1133-1198, 1213-1224;
+ * the animation branches with node_trans_bias are not covered):
+ *   search space: [x | feature[:, :hyper]] against nodes (M, 3+hyper), squared distances, K smallest ascending;
+ *   w_k = exp(-dist_k / (2 exp(radius_raw)^2)) [* sigmoid(weight_raw)] + 1e-7, normalised over the K neighbours;
+ *   d_xyz = mask * (sum_k w_k (R_k (x - c_k) + c_k + t_k) - x)   with R_k = quaternion_to_matrix(local_quat_k),
+ *           c_k = nodes[k, :3]  (local_quat != NULL: "local_frame"),   else   mask * sum_k w_k t_k;
+ *   d_rot / d_scale / d_opacity / d_color = mask * sum_k w_k (node value); add_rot_bias != 0 adds [1,0,0,0] to
+ *   d_rot after masking (d_rot_as_res = False).
+ * local_quat is the un-normalised quaternion local_rotation + [1,0,0,0] (M,4).  Optional (NULL = absent):
+ * feature (needed when hyper > 0), node_weight_raw, local_quat, node_opacity (M) with d_opacity (N),
+ * node_color (M,3) with d_color (N,3), motion_mask (N).  nn_idx (N,K) int64, nn_weight (N,K), nn_dist (N,K) are
+ * always written (they are what cal_nn_weight returns and what the backward reads).  1 <= K <= 8, hyper <= 5. */
+int rg_node_warp_forward(int N, int M, int K, int hyper, const float* x, const float* feature, const float* nodes,
+                         const float* node_radius_raw, const float* node_weight_raw, const float* local_quat,
+                         const float* node_trans, const float* node_rot, const float* node_scale,
+                         const float* node_opacity, const float* node_color, const float* motion_mask, int add_rot_bias,
+                         float* d_xyz, float* d_rot, float* d_scale, float* d_opacity, float* d_color,
+                         long long* nn_idx, float* nn_weight, float* nn_dist, rg_stream_t stream);
+
+/* Backward of rg_node_warp_forward (the reference relies on torch autograd through the same ops).  Cotangents
+ * g_* (NULL = none).  dnode (M, rg_node_warp_grad_channels()) is ACCUMULATED and must be zeroed by the caller; a
+ * row holds the gradients of [node_trans 0..2 | node_rot 3..6 | node_scale 7..9 | local_quat 10..13 |
+ * node_radius_raw 14 | node_weight_raw 15 | node_opacity 16 | node_color 17..19 | nodes[:, 3:3+hyper] 20..24].
+ * dmask (N) and dfeature (N,hyper) are written (NULL = skip).  No gradient flows to x or to nodes[:, :3]
+ * (both detached, utils/time_utils.py:946-949, 1136, 1153). */
+int rg_node_warp_grad_channels(void);
+int rg_node_warp_backward(int N, int M, int K, int hyper, const float* x, const float* feature, const float* nodes,
+                          const float* node_radius_raw, const float* node_weight_raw, const float* local_quat,
+                          const float* node_trans, const float* node_rot, const float* node_scale,
+                          const float* node_opacity, const float* node_color, const float* motion_mask,
+                          const long long* nn_idx, const float* nn_dist, const float* g_xyz, const float* g_rot,
+                          const float* g_scale, const float* g_opacity, const float* g_color, float* dnode,
+                          float* dmask, float* dfeature, rg_stream_t stream);
+
 /* ---- fused skin + rasterize (the hot path as ONE call per direction) ------------------------------ */
 
 /* What gaussian_renderer.render() + SkeletonWarp.deform_by_pose() are given, as raw device tensors: the model's

@@ -106,14 +106,15 @@ class GraphedStep:
     path runs one replay late, exactly as in eager mode; an overflow re-captures with a larger buffer.
     """
 
-    def __init__(self, hp: HotPath, cam, pose: Dict[str, torch.Tensor], target: torch.Tensor, warmup: int = 3):
+    def __init__(self, hp: HotPath, cam, pose: Dict[str, torch.Tensor], target: torch.Tensor, warmup: int = 3,
+                 pool=None):
         if not hp.fused:
             raise ValueError("GraphedStep needs HotPath(fused=True): the unfused path synchronises with the host")
         from .fused import WorkspacePool
         import copy
         self.hp = hp
         dev = hp.device
-        self.pool = WorkspacePool()
+        self.pool = pool if pool is not None else WorkspacePool()  # a shared pool = one workspace for several graphs
         self.cam = copy.copy(cam)
         self.cam.world_view_transform = cam.world_view_transform.to(dev).clone()
         self.cam.full_proj_transform = cam.full_proj_transform.to(dev).clone()
@@ -155,6 +156,7 @@ class GraphedStep:
         # data parallel with a peer-mapped gradient buffer: the all-reduce was captured with the backward
         self._reduces_in_graph = bool(self.hp.flat is not None and self.hp.flat.reduced_in_backward)
         self._ws = self.pool.free and next(iter(self.pool.free.values()))[0]
+        self._captured_binning = self._ws.binning.data_ptr() if self._ws else None
         self._event = None
 
     @property
@@ -220,6 +222,8 @@ class GraphedStep:
             ws.grow_binning(int(_lib.lib().rg_binning_bytes(int(int(ws.status[0]) * self.pool.headroom) + 256)))
             self.pool.note_capacity(ws, self.hp.device)
             self._capture()
+        elif ws is not None and ws.binning.data_ptr() != self._captured_binning:
+            self._capture()  # another graph on the same (shared) workspace grew the instance buffer
         self._take_staged()
         if cam is not None:
             self.cam.world_view_transform.copy_(cam.world_view_transform, non_blocking=True)
@@ -246,7 +250,7 @@ class PipelinedSteps:
     """Input / output pipeline around ``GraphedStep`` for callers whose per-step inputs live in HOST memory
     (a data loader's pinned target image, camera and pose) and who read every step's loss on the host.
 
-    Two captured graphs (slots) with their own static input buffers and workspaces alternate: while slot ``i % 2``
+    Two captured graphs (slots) with their own static input buffers alternate: while slot ``i % 2``
     computes step i, ``feed`` copies step i+1's host inputs straight into the other slot's static buffers on a
     copy stream (no staging copy on the compute stream), and step i's loss travels to a pinned host word that
     ``result`` reads one step late.  The compute stream therefore always has the next replay queued; nothing
@@ -254,11 +258,16 @@ class PipelinedSteps:
     """
 
     def __init__(self, hp: HotPath, cam, pose: Dict[str, torch.Tensor], target: torch.Tensor, warmup: int = 3,
-                 slots: int = 2):
+                 slots: int = 2, share_workspace: bool = True):
+        from .fused import WorkspacePool
         self.hp = hp
-        self.slots = [GraphedStep(hp, cam, pose, target, warmup=warmup) for _ in range(slots)]
+        # the slots run one after the other on one stream, so they can work in the same geometry / binning / image
+        # buffers (and keep that state in L2 from step to step); only the inputs are per slot
+        pool = WorkspacePool() if share_workspace else None
+        self.slots = [GraphedStep(hp, cam, pose, target, warmup=warmup, pool=pool) for _ in range(slots)]
         self.launches_per_replay = self.slots[0].launches_per_replay
         self._copy_stream = torch.cuda.Stream(device=hp.device)
+        self._out_stream = torch.cuda.Stream(device=hp.device)
         self._ready = [None] * slots   # inputs of the slot's next step have arrived
         self._done = [None] * slots    # the slot's last replay (and its loss copy) has finished
         self._loss_host = [torch.zeros(1).pin_memory() for _ in range(slots)]
@@ -296,9 +305,13 @@ class PipelinedSteps:
             torch.cuda.current_stream().wait_event(self._ready[k])
             self._ready[k] = None
         loss = g.step()
-        self._loss_host[k].copy_(loss.detach().reshape(1), non_blocking=True)
-        ev = torch.cuda.Event()
-        ev.record()
+        computed = torch.cuda.Event()
+        computed.record()
+        with torch.cuda.stream(self._out_stream):  # the read-back never sits between two replays on the compute stream
+            self._out_stream.wait_event(computed)
+            self._loss_host[k].copy_(loss.detach().reshape(1), non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self._out_stream)
         self._done[k] = ev
         self._run += 1
         return i
