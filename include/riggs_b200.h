@@ -97,6 +97,13 @@ int rg_state_ptrs(int P, int64_t R, int width, int height, char* geom_buffer, ch
 int rg_debug_sorted_keys(int P, int64_t R, int width, int height, char* geom_buffer, char* binning_buffer,
                          char* image_buffer, uint64_t* keys_out, rg_stream_t stream);
 
+/* Test aid: the stable depth sort of the forward pass (csrc/radix_sort.cu; replaces the depth half of the reference's
+ * cub::DeviceRadixSort::SortPairs, dgr/cuda_rasterizer/rasterizer_impl.cu:304-309) on caller-provided 32-bit keys:
+ * keys_out = keys ascending, ids_out = their original positions, equal keys in ascending position order.
+ * temp: rg_debug_depth_sort_bytes(P) bytes of device memory. */
+size_t rg_debug_depth_sort_bytes(int P);
+int rg_debug_depth_sort(int P, const uint32_t* keys, uint32_t* keys_out, uint32_t* ids_out, char* temp, rg_stream_t stream);
+
 /* ---- simple-knn -------------------------------------------------------------------------------- */
 
 /* Replaces SimpleKNN::knn (knn/simple_knn.h:18, knn/simple_knn.cu:186-221; bound by distCUDA2,

@@ -58,6 +58,8 @@ _SIGNATURES = {
     "rg_mark_visible": (C.c_int, [_i, _p, _p, _p, _p, _p]),
     "rg_state_ptrs": (C.c_int, [_i, C.c_int64, _i, _i, _p, _p, _p, C.POINTER(C.c_void_p)]),
     "rg_debug_sorted_keys": (C.c_int, [_i, C.c_int64, _i, _i, _p, _p, _p, _p, _p]),
+    "rg_debug_depth_sort_bytes": (C.c_size_t, [_i]),
+    "rg_debug_depth_sort": (C.c_int, [_i, _p, _p, _p, _p, _p]),
     "rg_knn_scratch_bytes": (C.c_size_t, [_i]),
     "rg_dist_cuda2": (C.c_int, [_i, _p, _p, _p, C.c_size_t, _p]),
     "rg_dist_cuda2_static": (C.c_int, [_i, _p, _p, _p]),

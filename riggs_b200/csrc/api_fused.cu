@@ -93,9 +93,10 @@ int rg_skinned_forward(const RgSkinnedScene* s, const RgWorkspace* w, float* out
         return -1;
     if (launch_tile_count(bp, P, grid_x, grid_y, geom.sorted_ids, geom.tiles_touched, geom.means2D, radii, geom.M, stream))
         return -1;
-    launch_tile_offsets_a(bp, geom.M, geom.S, geom.tile_base, img.ranges, geom.tile_order, geom.status, cap, stream);
+    // nobody reads num_rendered on the host here, so the prefix over the tiles rides along with the column scans
+    launch_tile_offsets_a(bp, geom.M, geom.S, geom.tile_base, img.ranges, geom.tile_order, geom.status, cap, stream, false);
     launch_tile_scatter(bp, P, grid_x, grid_y, geom.sorted_ids, geom.tiles_touched, geom.means2D, radii, geom.M, geom.S,
-                        geom.tile_base, geom.E, bin.point_list, cap, stream);
+                        geom.tile_base, geom.E, bin.point_list, cap, stream, true, img.ranges, geom.tile_order, geom.status);
 
     BlendFwdArgs fa;
     fa.W = W; fa.H = H; fa.grid_x = grid_x; fa.grid_y = grid_y;

@@ -28,16 +28,16 @@
 
 namespace rg {
 
-// ---- 1. depth sort -----------------------------------------------------------------------------------
-size_t depth_sort_temp_bytes(size_t P) {
+// ---- 1. depth sort: csrc/radix_sort.cu; the library sort below is kept as the A/B partner (RG_DEPTH_SORT=cub) ----
+size_t depth_sort_temp_bytes_cub(size_t P) {
     size_t bytes = 0;
     cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, (const uint32_t*)nullptr,
                                     (uint32_t*)nullptr, (int)P, 0, 32);
     return bytes;
 }
 
-int launch_depth_sort(char* temp, size_t temp_bytes, const float* depths, uint32_t* keys_out, const uint32_t* ids_in,
-                      uint32_t* ids_out, int P, cudaStream_t stream) {
+int launch_depth_sort_cub(char* temp, size_t temp_bytes, const float* depths, uint32_t* keys_out, const uint32_t* ids_in,
+                          uint32_t* ids_out, int P, cudaStream_t stream) {
     if (P <= 0) return 0;
     LaunchScope ls("depth_sort", stream, 0);
     cudaError_t e = cub::DeviceRadixSort::SortPairs(temp, temp_bytes, reinterpret_cast<const uint32_t*>(depths), keys_out,
@@ -98,6 +98,10 @@ __device__ __forceinline__ void walk_chunk(int lo, int hi, int grid_x, int grid_
 }
 
 // ---- 2. per-chunk, per-tile counts ------------------------------------------------------------------
+// Counting needs no order inside a chunk: every lane takes one Gaussian of the chunk and adds one to the counter of
+// each tile of its rectangle (two 16-bit counters per shared-memory word, a chunk holds at most 65535 Gaussians so a
+// half never carries into its neighbour).  Rectangles of more than kWideRect tiles are left to the whole warp.
+constexpr uint32_t kWideRect = 48;
 __global__ void __launch_bounds__(256) tile_count_kernel(int P, int T, int NW, int L, int grid_x, int grid_y,
                                                          const uint32_t* __restrict__ sorted_ids,
                                                          const uint32_t* __restrict__ tiles_touched,
@@ -113,12 +117,36 @@ __global__ void __launch_bounds__(256) tile_count_kernel(int P, int T, int NW, i
     for (int k = lane; k < Tpad / 2; k += 32) h32[k] = 0;
     __syncwarp();
     const int lo = min(P, gw * L), hi = min(P, lo + L);
-    walk_chunk(lo, hi, grid_x, grid_y, sorted_ids, tiles_touched, means2D, radii,
-               [&](bool valid, uint32_t t, uint32_t) {
-                   const unsigned m = __match_any_sync(0xffffffffu, valid ? t : 0xffffff00u + lane);
-                   if (valid && (m & ((1u << lane) - 1)) == 0) hist[t] += (uint16_t)__popc(m);
-                   __syncwarp();
-               });
+    for (int base = lo; base < hi; base += 32) {
+        const int i = base + lane;
+        uint32_t cnt = 0;
+        uint2 rmin = make_uint2(0, 0), rmax = make_uint2(0, 0);
+        if (i < hi) {
+            const uint32_t id = sorted_ids[i];
+            cnt = tiles_touched[id];
+            if (cnt > 0) tile_rect(means2D[id], radii[id], rmin, rmax, grid_x, grid_y);
+        }
+        if (cnt > 0 && cnt <= kWideRect) {
+            for (uint32_t y = rmin.y; y < rmax.y; y++) {
+                const uint32_t row = y * (uint32_t)grid_x;
+                for (uint32_t x = rmin.x; x < rmax.x; x++) {
+                    const uint32_t t = row + x;
+                    atomicAdd(&h32[t >> 1], 1u << ((t & 1u) * 16u));
+                }
+            }
+        }
+        unsigned wide = __ballot_sync(0xffffffffu, cnt > kWideRect);
+        while (wide) {
+            const int o = __ffs(wide) - 1;
+            wide &= wide - 1;
+            const uint32_t x0 = __shfl_sync(0xffffffffu, rmin.x, o), y0 = __shfl_sync(0xffffffffu, rmin.y, o);
+            const uint32_t w = __shfl_sync(0xffffffffu, rmax.x, o) - x0, n = __shfl_sync(0xffffffffu, cnt, o);
+            for (uint32_t s = lane; s < n; s += 32) {
+                const uint32_t t = (y0 + s / w) * (uint32_t)grid_x + x0 + s % w;
+                atomicAdd(&h32[t >> 1], 1u << ((t & 1u) * 16u));
+            }
+        }
+    }
     __syncwarp();
     uint32_t* row = reinterpret_cast<uint32_t*>(M + (size_t)gw * Tpad);
     for (int k = lane; k < Tpad / 2; k += 32) row[k] = h32[k];
@@ -147,16 +175,17 @@ __device__ __forceinline__ int order_bucket(uint32_t n) {
 }
 
 // ---- 3b. per-tile totals, prefix over tiles, ranges, launch order, num_rendered -----
-__global__ void __launch_bounds__(1024) tile_base_kernel(int T, uint32_t* __restrict__ tile_base,
-                                                         uint2* __restrict__ ranges, uint32_t* __restrict__ tile_order,
-                                                         uint32_t* __restrict__ status, uint32_t capacity) {
+template <int NT>
+__device__ __forceinline__ void tile_base_body(int T, uint32_t* __restrict__ tile_base, uint2* __restrict__ ranges,
+                                               uint32_t* __restrict__ tile_order, uint32_t* __restrict__ status,
+                                               uint32_t capacity) {
     __shared__ uint32_t s_warp[32];
     __shared__ uint32_t s_bucket[kOrderBuckets];
     __shared__ uint32_t s_carry;
     if (threadIdx.x == 0) s_carry = 0;
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int base = 0; base < T; base += 1024) {
+    for (int base = 0; base < T; base += NT) {
         const int t = base + threadIdx.x;
         const uint32_t tot = t < T ? tile_base[t] : 0u;  // per-tile totals accumulated by seg_sum_kernel
         uint32_t x = tot;
@@ -168,7 +197,7 @@ __global__ void __launch_bounds__(1024) tile_base_kernel(int T, uint32_t* __rest
         if (lane == 31) s_warp[warp] = x;
         __syncthreads();
         if (warp == 0) {
-            uint32_t w = s_warp[lane];
+            uint32_t w = lane < NT / 32 ? s_warp[lane] : 0u;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const uint32_t y = __shfl_up_sync(0xffffffffu, w, o);
@@ -185,15 +214,15 @@ __global__ void __launch_bounds__(1024) tile_base_kernel(int T, uint32_t* __rest
             ranges[t] = tot ? make_uint2(min(excl, capacity), min(excl + tot, capacity)) : make_uint2(0, 0);
         }
         __syncthreads();
-        if (threadIdx.x == 1023) s_carry = carry + s_warp[31];
+        if (threadIdx.x == NT - 1) s_carry = carry + s_warp[NT / 32 - 1];
         __syncthreads();
     }
     // Launch order of the blend kernels: tiles with the longest lists first (counting sort on a 2-bit-mantissa log
     // scale, descending), so that the frame's few heavy tiles start at once instead of wherever the raster order puts
     // them, and the short ones fill in behind.
-    for (int b = threadIdx.x; b < kOrderBuckets; b += 1024) s_bucket[b] = 0;
+    for (int b = threadIdx.x; b < kOrderBuckets; b += NT) s_bucket[b] = 0;
     __syncthreads();
-    for (int t = threadIdx.x; t < T; t += 1024) {
+    for (int t = threadIdx.x; t < T; t += NT) {
         const uint2 r = ranges[t];
         atomicAdd(&s_bucket[order_bucket(r.y - r.x)], 1u);
     }
@@ -207,7 +236,7 @@ __global__ void __launch_bounds__(1024) tile_base_kernel(int T, uint32_t* __rest
         }
     }
     __syncthreads();
-    for (int t = threadIdx.x; t < T; t += 1024) {
+    for (int t = threadIdx.x; t < T; t += NT) {
         const uint2 r = ranges[t];
         tile_order[atomicAdd(&s_bucket[order_bucket(r.y - r.x)], 1u)] = (uint32_t)t;
     }
@@ -217,14 +246,29 @@ __global__ void __launch_bounds__(1024) tile_base_kernel(int T, uint32_t* __rest
     }
 }
 
+__global__ void __launch_bounds__(1024) tile_base_kernel(int T, uint32_t* __restrict__ tile_base,
+                                                         uint2* __restrict__ ranges, uint32_t* __restrict__ tile_order,
+                                                         uint32_t* __restrict__ status, uint32_t capacity) {
+    tile_base_body<1024>(T, tile_base, ranges, tile_order, status, capacity);
+}
+
 // ---- 3c. first slot of every (chunk, tile) -----------------------------------------------------------
-__global__ void __launch_bounds__(256) col_scan_kernel(int T, int Tpad, int NW, const uint16_t* __restrict__ M,
-                                                       const uint32_t* __restrict__ S, const uint32_t* __restrict__ tile_base,
-                                                       uint32_t* __restrict__ E) {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+// E holds offsets RELATIVE to the tile's first slot, so this kernel does not wait for the prefix over the tiles:
+// with base_in_grid the block row y == nseg is one extra CTA that computes that prefix (tile_base, ranges, launch
+// order, num_rendered) next to the column scans instead of in a launch of its own before them.
+__global__ void __launch_bounds__(256) col_scan_kernel(int T, int Tpad, int NW, int nseg, const uint16_t* __restrict__ M,
+                                                       const uint32_t* __restrict__ S, uint32_t* __restrict__ E,
+                                                       uint32_t* __restrict__ tile_base, uint2* __restrict__ ranges,
+                                                       uint32_t* __restrict__ tile_order, uint32_t* __restrict__ status,
+                                                       uint32_t capacity) {
     const int seg = blockIdx.y;
+    if (seg == nseg) {  // only launched when the prefix over the tiles is still pending
+        if (blockIdx.x == 0) tile_base_body<256>(T, tile_base, ranges, tile_order, status, capacity);
+        return;
+    }
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= T) return;
-    uint32_t run = tile_base[t];
+    uint32_t run = 0;
 #pragma unroll 8
     for (int s = 0; s < seg; s++) run += S[(size_t)s * T + t];  // prefix over the earlier segments
     const int w0 = seg * kSegRows, w1 = min(NW, w0 + kSegRows);
@@ -239,15 +283,16 @@ __global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int T, int NW,
                                                            const uint32_t* __restrict__ sorted_ids,
                                                            const uint32_t* __restrict__ tiles_touched,
                                                            const float2* __restrict__ means2D, const int* __restrict__ radii,
-                                                           const uint32_t* __restrict__ E, uint32_t* __restrict__ point_list,
-                                                           uint32_t capacity) {
+                                                           const uint32_t* __restrict__ E,
+                                                           const uint32_t* __restrict__ tile_base,
+                                                           uint32_t* __restrict__ point_list, uint32_t capacity) {
     extern __shared__ __align__(16) unsigned char s_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpc = blockDim.x >> 5;
     const int gw = blockIdx.x * wpc + warp;
     uint32_t* cur = reinterpret_cast<uint32_t*>(s_raw) + (size_t)warp * T;
     if (gw >= NW) return;
     const uint32_t* row = E + (size_t)gw * T;
-    for (int k = lane; k < T; k += 32) cur[k] = row[k];
+    for (int k = lane; k < T; k += 32) cur[k] = row[k] + tile_base[k];
     __syncwarp();
     const int lo = min(P, gw * L), hi = min(P, lo + L);
     walk_chunk(lo, hi, grid_x, grid_y, sorted_ids, tiles_touched, means2D, radii,
@@ -312,25 +357,26 @@ int launch_tile_count(const BinPlan& b, int P, int grid_x, int grid_y, const uin
 }
 
 int launch_tile_offsets_a(const BinPlan& b, const uint16_t* M, uint32_t* S, uint32_t* tile_base, uint2* ranges,
-                          uint32_t* tile_order, uint32_t* status, uint32_t capacity, cudaStream_t stream) {
-    LaunchScope ls("tile_offsets", stream, 2);
+                          uint32_t* tile_order, uint32_t* status, uint32_t capacity, cudaStream_t stream, bool with_base) {
+    LaunchScope ls("tile_offsets", stream, with_base ? 2 : 1);
     dim3 g((b.T + 255) / 256, b.nseg);
     cudaMemsetAsync(tile_base, 0, sizeof(uint32_t) * b.T, stream);
     seg_sum_kernel<<<g, 256, 0, stream>>>(b.T, b.Tpad, b.NW, M, S, tile_base);
-    tile_base_kernel<<<1, 1024, 0, stream>>>(b.T, tile_base, ranges, tile_order, status, capacity);
+    if (with_base) tile_base_kernel<<<1, 1024, 0, stream>>>(b.T, tile_base, ranges, tile_order, status, capacity);
     return 0;
 }
 
 int launch_tile_scatter(const BinPlan& b, int P, int grid_x, int grid_y, const uint32_t* sorted_ids,
                         const uint32_t* tiles_touched, const float2* means2D, const int* radii, const uint16_t* M,
-                        const uint32_t* S, const uint32_t* tile_base, uint32_t* E, uint32_t* point_list,
-                        uint32_t capacity, cudaStream_t stream) {
+                        const uint32_t* S, uint32_t* tile_base, uint32_t* E, uint32_t* point_list,
+                        uint32_t capacity, cudaStream_t stream, bool base_pending, uint2* ranges, uint32_t* tile_order,
+                        uint32_t* status) {
     LaunchScope ls("tile_scatter", stream, 2);
-    dim3 g((b.T + 255) / 256, b.nseg);
-    col_scan_kernel<<<g, 256, 0, stream>>>(b.T, b.Tpad, b.NW, M, S, tile_base, E);
+    dim3 g((b.T + 255) / 256, b.nseg + (base_pending ? 1 : 0));
+    col_scan_kernel<<<g, 256, 0, stream>>>(b.T, b.Tpad, b.NW, b.nseg, M, S, E, tile_base, ranges, tile_order, status, capacity);
     const size_t smem = (size_t)b.wpc_scatter * b.T * 4;
     tile_scatter_kernel<<<(b.NW + b.wpc_scatter - 1) / b.wpc_scatter, b.wpc_scatter * 32, smem, stream>>>(
-        P, b.T, b.NW, b.L, grid_x, grid_y, sorted_ids, tiles_touched, means2D, radii, E, point_list, capacity);
+        P, b.T, b.NW, b.L, grid_x, grid_y, sorted_ids, tiles_touched, means2D, radii, E, tile_base, point_list, capacity);
     return 0;
 }
 

@@ -1,0 +1,228 @@
+// Stable LSD radix sort of the P Gaussians by depth bits (32-bit keys, value = Gaussian id), sized for the few
+// hundred thousand keys of one frame.  Same result as the stable cub::DeviceRadixSort::SortPairs it replaces
+// (which itself stands in for the depth half of the reference's 64-bit key sort, rasterizer_impl.cu:304-309):
+// ascending key bits, equal keys in ascending id order.
+//
+// Why not the library sort: its one-sweep kernel is tuned for huge arrays (384 threads x 23 keys per CTA), so 300 k
+// keys run on 34 of the 148 SMs and every one of the four digit passes is a 12-15 us latency chain (ncu,
+// profiles/r1_w_summary.md).  Here a CTA takes 2048 keys (147 CTAs for 300 k: one per SM):
+//   sort_hist_kernel   all four 8-bit digit histograms in one read of the keys;
+//   sort_pass_kernel   one sweep per digit: keys of a tile are ranked per warp with __match_any_sync (lane order =
+//                      key order, so the pass is stable), the digit counts of the tile are chained to the tiles
+//                      before it by decoupled look-back (one thread per digit, 48 predecessors fetched per
+//                      round), and every key goes straight to its final slot.  Tile numbers are handed out by an
+//                      atomic counter, so a tile never waits for one that has not started.
+// The first pass takes the ids from the key positions (no iota array is read).
+#include <cstdlib>
+
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace rg {
+
+constexpr int kSortBits = 8;
+constexpr int kSortBins = 1 << kSortBits;
+constexpr int kSortPasses = 32 / kSortBits;
+constexpr int kSortThreads = 256;
+constexpr int kSortItems = 8;
+constexpr int kSortTile = kSortThreads * kSortItems;  // 2048 keys per CTA
+constexpr int kSortWarps = kSortThreads / 32;
+constexpr uint32_t kFlagPartial = 1u << 30, kFlagInclusive = 2u << 30, kValueMask = (1u << 30) - 1;
+
+struct SortCtl {        // all zero before a sort starts (one memset)
+    uint32_t* hist;     // [passes][bins] digit totals
+    uint32_t* counter;  // [passes] next tile number of each pass
+    uint32_t* status;   // [passes][tiles][bins] look-back words: flag | count
+    size_t words;
+};
+
+static SortCtl sort_ctl(char* base, size_t tiles) {
+    SortCtl c;
+    c.hist = reinterpret_cast<uint32_t*>(base);
+    c.counter = c.hist + kSortPasses * kSortBins;
+    c.status = c.counter + 64;
+    c.words = (size_t)kSortPasses * kSortBins + 64 + (size_t)kSortPasses * tiles * kSortBins;
+    return c;
+}
+
+__global__ void __launch_bounds__(kSortThreads) sort_hist_kernel(const uint32_t* __restrict__ keys, int P,
+                                                                 uint32_t* __restrict__ hist) {
+    __shared__ uint32_t s_h[kSortPasses * kSortBins];
+    for (int i = threadIdx.x; i < kSortPasses * kSortBins; i += blockDim.x) s_h[i] = 0;
+    __syncthreads();
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < P; i += gridDim.x * blockDim.x) {
+        const uint32_t k = keys[i];
+#pragma unroll
+        for (int p = 0; p < kSortPasses; p++) atomicAdd(&s_h[p * kSortBins + ((k >> (p * kSortBits)) & (kSortBins - 1))], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < kSortPasses * kSortBins; i += blockDim.x)
+        if (s_h[i]) atomicAdd(&hist[i], s_h[i]);
+}
+
+__device__ __forceinline__ uint32_t ld_status(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_status(uint32_t* p, uint32_t v) {
+    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// vals_in == nullptr: the value of a key is its position (first pass).
+__global__ void __launch_bounds__(kSortThreads) sort_pass_kernel(const uint32_t* __restrict__ keys_in,
+                                                                 const uint32_t* __restrict__ vals_in,
+                                                                 uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
+                                                                 int P, int shift, const uint32_t* __restrict__ hist,
+                                                                 uint32_t* __restrict__ counter, uint32_t* __restrict__ status) {
+    __shared__ uint32_t s_cnt[kSortWarps][kSortBins];  // per warp: running digit counts, then exclusive offsets
+    __shared__ uint32_t s_base[kSortBins];             // first output slot of (this tile, digit)
+    __shared__ uint32_t s_scan[kSortWarps];
+    __shared__ uint32_t s_tile;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned full = 0xffffffffu;
+    if (tid == 0) s_tile = atomicAdd(counter, 1u);
+    for (int i = tid; i < kSortWarps * kSortBins; i += kSortThreads) (&s_cnt[0][0])[i] = 0;
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const int base = (int)tile * kSortTile + warp * (32 * kSortItems);
+
+    uint32_t key[kSortItems], rank[kSortItems];
+#pragma unroll
+    for (int j = 0; j < kSortItems; j++) {
+        const int i = base + j * 32 + lane;
+        key[j] = i < P ? keys_in[i] : 0xffffffffu;
+    }
+    // ---- rank inside the warp, key order = (item, lane) -------------------------------------------------
+#pragma unroll
+    for (int j = 0; j < kSortItems; j++) {
+        const bool valid = base + j * 32 + lane < P;
+        const uint32_t d = (key[j] >> shift) & (kSortBins - 1);
+        const unsigned peers = __match_any_sync(full, valid ? d : kSortBins + lane);
+        const int leader = __ffs(peers) - 1;
+        uint32_t old = 0;
+        if (valid && lane == leader) {
+            old = s_cnt[warp][d];
+            s_cnt[warp][d] = old + __popc(peers);
+        }
+        old = __shfl_sync(full, old, leader);
+        rank[j] = old + __popc(peers & ((1u << lane) - 1));
+        __syncwarp();
+    }
+    __syncthreads();
+    // ---- one thread per digit: offsets of the warps, look-back over the earlier tiles ----------------------
+    {
+        const int d = tid;  // kSortThreads == kSortBins
+        uint32_t total = 0;
+#pragma unroll
+        for (int w = 0; w < kSortWarps; w++) {
+            const uint32_t c = s_cnt[w][d];
+            s_cnt[w][d] = total;
+            total += c;
+        }
+        uint32_t* mine = status + (size_t)tile * kSortBins + d;
+        uint32_t prefix = 0;
+        if (tile == 0) {
+            st_status(mine, kFlagInclusive | total);
+        } else {
+            st_status(mine, kFlagPartial | total);
+            int t = (int)tile - 1;
+            while (t >= 0) {
+                constexpr int W = 48;
+                uint32_t v[W];
+#pragma unroll
+                for (int i = 0; i < W; i++) v[i] = t - i >= 0 ? ld_status(status + (size_t)(t - i) * kSortBins + d) : kFlagInclusive;
+                bool done = false;
+#pragma unroll
+                for (int i = 0; i < W; i++) {
+                    if (done) continue;
+                    if ((v[i] >> 30) == 0) { done = true; continue; }  // not published yet: fetch again from here
+                    prefix += v[i] & kValueMask;
+                    t--;
+                    if (v[i] & kFlagInclusive) { done = true; t = -1; }
+                }
+            }
+            st_status(mine, kFlagInclusive | (prefix + total));
+        }
+        // first slot of the digit in the whole array: exclusive scan of the digit totals over the 256 digits
+        const uint32_t h = hist[d];
+        uint32_t incl = h;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(full, incl, o);
+            if (lane >= o) incl += y;
+        }
+        if (lane == 31) s_scan[warp] = incl;
+        __syncthreads();
+        uint32_t before = 0;
+#pragma unroll
+        for (int w = 0; w < kSortWarps; w++)
+            if (w < warp) before += s_scan[w];
+        s_base[d] = before + incl - h + prefix;
+    }
+    __syncthreads();
+    // ---- scatter ------------------------------------------------------------------------------------------
+#pragma unroll
+    for (int j = 0; j < kSortItems; j++) {
+        const int i = base + j * 32 + lane;
+        if (i < P) {
+            const uint32_t d = (key[j] >> shift) & (kSortBins - 1);
+            const uint32_t pos = s_base[d] + s_cnt[warp][d] + rank[j];
+            keys_out[pos] = key[j];
+            vals_out[pos] = vals_in ? vals_in[i] : (uint32_t)i;
+        }
+    }
+}
+
+size_t depth_sort_temp_bytes(size_t P) {
+    const size_t tiles = (P + kSortTile - 1) / kSortTile;
+    SortCtl c = sort_ctl(nullptr, tiles);
+    const size_t own = align_up(c.words * 4, 256) + 2 * align_up(P * 4, 256);
+    return std::max(own, depth_sort_temp_bytes_cub(P));
+}
+
+static bool use_cub_sort() {
+    static const bool v = [] {
+        const char* e = std::getenv("RG_DEPTH_SORT");
+        return e && std::string(e) == "cub";
+    }();
+    return v;
+}
+
+int launch_depth_sort(char* temp, size_t temp_bytes, const float* depths, uint32_t* keys_out, const uint32_t* ids_in,
+                      uint32_t* ids_out, int P, cudaStream_t stream) {
+    if (P <= 0) return 0;
+    if (use_cub_sort() || P >= (1 << 30)) return launch_depth_sort_cub(temp, temp_bytes, depths, keys_out, ids_in, ids_out, P, stream);
+    LaunchScope ls("depth_sort", stream, 1 + kSortPasses);
+    const size_t tiles = ((size_t)P + kSortTile - 1) / kSortTile;
+    SortCtl c = sort_ctl(temp, tiles);
+    uint32_t* tmp_keys = reinterpret_cast<uint32_t*>(temp + align_up(c.words * 4, 256));
+    uint32_t* tmp_ids = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(tmp_keys) + align_up((size_t)P * 4, 256));
+    if (cudaMemsetAsync(temp, 0, c.words * 4, stream) != cudaSuccess) { set_error("depth sort: memset failed"); return -1; }
+    const uint32_t* keys = reinterpret_cast<const uint32_t*>(depths);
+    sort_hist_kernel<<<std::min<int>((int)((P + 2047) / 2048), RG_NUM_SMS * 2), kSortThreads, 0, stream>>>(keys, P, c.hist);
+    // depths -> tmp -> out -> tmp -> out
+    const uint32_t* kin = keys;
+    const uint32_t* vin = nullptr;
+    for (int p = 0; p < kSortPasses; p++) {
+        uint32_t* kout = (p & 1) ? keys_out : tmp_keys;
+        uint32_t* vout = (p & 1) ? ids_out : tmp_ids;
+        sort_pass_kernel<<<(unsigned)tiles, kSortThreads, 0, stream>>>(kin, vin, kout, vout, P, p * kSortBits, c.hist + p * kSortBins,
+                                                                       c.counter + p, c.status + (size_t)p * tiles * kSortBins);
+        kin = kout;
+        vin = vout;
+    }
+    if (cudaGetLastError() != cudaSuccess) { set_error("depth sort: launch failed"); return -1; }
+    return 0;
+}
+
+}  // namespace rg
+
+// Test aid: the depth sort on caller-provided keys (P x u32 -> sorted keys + original positions); temp must hold
+// rg_debug_depth_sort_bytes(P) bytes.
+extern "C" size_t rg_debug_depth_sort_bytes(int P) { return rg::depth_sort_temp_bytes((size_t)std::max(P, 1)); }
+extern "C" int rg_debug_depth_sort(int P, const uint32_t* keys, uint32_t* keys_out, uint32_t* ids_out, char* temp,
+                                   void* stream) {
+    return rg::launch_depth_sort(temp, rg::depth_sort_temp_bytes((size_t)std::max(P, 1)), reinterpret_cast<const float*>(keys),
+                                 keys_out, nullptr, ids_out, P, static_cast<cudaStream_t>(stream));
+}

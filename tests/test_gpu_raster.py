@@ -207,3 +207,36 @@ def test_mark_visible():
     ref = ref_cuda.mark_visible(pts, cam.world_view_transform.contiguous(), cam.full_proj_transform.contiguous())
     assert torch.equal(ours, ref)
     assert 0 < int(ours.sum()) <= pts.shape[0]
+
+
+@pytest.mark.parametrize("P,kind", [(1, "rand"), (31, "ties"), (2048, "rand"), (2049, "ties"), (300000, "depth"),
+                                    (300000, "ties"), (1000003, "rand"), (70000, "equal")])
+def test_depth_sort_is_the_stable_sort(P, kind):
+    """csrc/radix_sort.cu against torch's stable sort: ascending key bits, equal keys keep their order (the order
+    the reference's stable radix sort over id-ordered emission defines), for ragged sizes, heavy ties, one repeated
+    key, depth-like floats with culled (+inf) entries, and more tiles than SMs."""
+    from riggs_b200 import _lib
+    g = torch.Generator().manual_seed(P)
+    if kind == "rand":
+        keys = torch.randint(0, 2**31 - 1, (P,), generator=g, dtype=torch.int64) * 2 + torch.randint(0, 2, (P,), generator=g)
+    elif kind == "ties":
+        keys = torch.randint(0, 50, (P,), generator=g, dtype=torch.int64) * 65537
+    elif kind == "equal":
+        keys = torch.full((P,), 0x40A00000, dtype=torch.int64)
+    else:
+        d = 2.5 + 3.0 * torch.rand(P, generator=g)
+        d[torch.rand(P, generator=g) < 0.1] = float("inf")
+        keys = d.view(torch.int32).to(torch.int64)
+    dev_keys = torch.from_numpy(keys.numpy().astype(np.uint32).view(np.int32)).cuda()
+    out_k = torch.empty_like(dev_keys)
+    out_i = torch.empty_like(dev_keys)
+    L = _lib.lib()
+    temp = torch.empty(int(L.rg_debug_depth_sort_bytes(P)), dtype=torch.uint8, device="cuda")
+    for _ in range(2):  # the second call reuses the (dirty) temp buffer
+        _lib.check(L.rg_debug_depth_sort(P, dev_keys.data_ptr(), out_k.data_ptr(), out_i.data_ptr(), temp.data_ptr(),
+                                         _lib.stream_ptr()), "rg_debug_depth_sort")
+        torch.cuda.synchronize()
+        want_k, want_i = torch.sort(keys, stable=True)
+        got_k = torch.from_numpy(out_k.cpu().numpy().view(np.uint32).astype(np.int64))
+        assert torch.equal(got_k, want_k)
+        assert torch.equal(out_i.cpu().to(torch.int64), want_i)
