@@ -39,6 +39,7 @@ GeomState GeomState::carve(char* base, size_t P, int W, int H, size_t* bytes) {
     g.ids = c.take<uint32_t>(P);
     g.sorted_keys = c.take<uint32_t>(P);
     g.sorted_ids = c.take<uint32_t>(P);
+    g.rects = c.take<uint2>(P);
     g.sort_temp_bytes = depth_sort_temp_bytes(P);
     g.sort_temp = c.take<char>(g.sort_temp_bytes);
     g.M = c.take<uint16_t>((size_t)bp.NW * bp.Tpad);
@@ -145,7 +146,7 @@ int rg_rasterize_forward(rg_alloc_fn geom_alloc, void* geom_ctx, rg_alloc_fn bin
                           P, stream))
         return -1;
     if (check_launch("depth_sort", stream, dbg)) return -1;
-    if (launch_tile_count(bp, P, grid_x, grid_y, geom.sorted_ids, geom.tiles_touched, geom.means2D, radii, geom.M, stream))
+    if (launch_tile_count(bp, P, grid_x, grid_y, geom.sorted_ids, geom.tiles_touched, geom.means2D, radii, geom.rects, geom.M, stream))
         return -1;
     launch_tile_offsets_a(bp, geom.M, geom.S, geom.tile_base, img.ranges, geom.tile_order, geom.status, 0xffffffffu, stream);
     if (check_launch("tile_count/offsets", stream, dbg)) return -1;
@@ -164,7 +165,7 @@ int rg_rasterize_forward(rg_alloc_fn geom_alloc, void* geom_ctx, rg_alloc_fn bin
     if (!bptr) { set_error("rg_rasterize_forward: binning buffer allocation failed"); return -1; }
     BinningState bin = BinningState::carve(aligned_base(bptr), (size_t)R, nullptr);
     if (R > 0) {
-        launch_tile_scatter(bp, P, grid_x, grid_y, geom.sorted_ids, geom.tiles_touched, geom.means2D, radii, geom.M,
+        launch_tile_scatter(bp, P, grid_x, grid_y, geom.sorted_ids, geom.rects, geom.M,
                             geom.S, geom.tile_base, geom.E, bin.point_list, (uint32_t)R, stream);
         if (check_launch("tile_scatter", stream, dbg)) return -1;
     }

@@ -8,12 +8,13 @@
 //
 //   1. stable radix sort of the P Gaussians by depth bits (32-bit keys, P items: small, L2 resident);
 //   2. tile_count:   the depth-ordered Gaussians are cut into NW contiguous chunks, one warp each; a warp
-//                    counts the instances of its chunk per tile in shared memory -> row of M[NW][T];
+//                    counts the instances of its chunk per tile in shared memory (one lane per Gaussian, shared
+//                    atomics) -> row of M[NW][T], and keeps the tile rectangles in depth order;
 //   3. column scans: per tile, prefix over the chunks (two levels) and prefix over the tiles ->
 //                    E[w][t] = first output slot of chunk w in tile t, ranges[t], num_rendered;
-//   4. tile_scatter: every warp walks its chunk again, in order, and drops each instance id straight into
-//                    its final slot (cursor per tile in shared memory, ranks inside a 32-instance step from
-//                    __match_any_sync in lane = depth order).
+//   4. tile_scatter: every warp walks its chunk again, one Gaussian after the other, and drops each instance id
+//                    straight into its final slot (cursor per tile in shared memory; the tiles of one Gaussian are
+//                    distinct, so its lanes need no ranking among themselves).
 //
 // The instance list is written exactly once (4 B per instance) and nothing instance-sized is ever read
 // back; num_rendered stays on the device (the sync-free entry points never look at it on the host).
@@ -49,54 +50,6 @@ int launch_depth_sort_cub(char* temp, size_t temp_bytes, const float* depths, ui
     return 0;
 }
 
-// ---- shared walk: a warp visits the instances of its chunk in (Gaussian order, row-major tile) order ----
-// F is called by all 32 lanes for every step of 32 instances: F(valid, tile, gaussian_id).
-template <typename F>
-__device__ __forceinline__ void walk_chunk(int lo, int hi, int grid_x, int grid_y, const uint32_t* __restrict__ sorted_ids,
-                                           const uint32_t* __restrict__ tiles_touched, const float2* __restrict__ means2D,
-                                           const int* __restrict__ radii, F&& f) {
-    const int lane = threadIdx.x & 31;
-    const unsigned full = 0xffffffffu;
-    for (int base = lo; base < hi; base += 32) {
-        const int i = base + lane;
-        uint32_t id = 0, cnt = 0, x0 = 0, y0 = 0, w = 1;
-        if (i < hi) {
-            id = sorted_ids[i];
-            cnt = tiles_touched[id];
-            if (cnt > 0) {
-                uint2 rmin, rmax;
-                tile_rect(means2D[id], radii[id], rmin, rmax, grid_x, grid_y);
-                x0 = rmin.x; y0 = rmin.y; w = rmax.x - rmin.x;
-            }
-        }
-        uint32_t incl = cnt;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t y = __shfl_up_sync(full, incl, o);
-            if (lane >= o) incl += y;
-        }
-        const uint32_t excl = incl - cnt;
-        const uint32_t total = __shfl_sync(full, incl, 31);
-        for (uint32_t s0 = 0; s0 < total; s0 += 32) {
-            const uint32_t s = s0 + lane;
-            const bool valid = s < total;
-            // owner = largest lane o with excl[o] <= s (zero-count lanes share their successor's excl)
-            int o = 0;
-#pragma unroll
-            for (int step = 16; step > 0; step >>= 1) {
-                const int cand = o + step;
-                const uint32_t e = __shfl_sync(full, excl, cand & 31);
-                if (cand < 32 && e <= s) o = cand;
-            }
-            const uint32_t local = s - __shfl_sync(full, excl, o);
-            const uint32_t ox0 = __shfl_sync(full, x0, o), oy0 = __shfl_sync(full, y0, o), ow = __shfl_sync(full, w, o);
-            const uint32_t oid = __shfl_sync(full, id, o);
-            const uint32_t t = (oy0 + local / ow) * (uint32_t)grid_x + ox0 + local % ow;
-            f(valid, t, oid);
-        }
-    }
-}
-
 // ---- 2. per-chunk, per-tile counts ------------------------------------------------------------------
 // Counting needs no order inside a chunk: every lane takes one Gaussian of the chunk and adds one to the counter of
 // each tile of its rectangle (two 16-bit counters per shared-memory word, a chunk holds at most 65535 Gaussians so a
@@ -106,7 +59,7 @@ __global__ void __launch_bounds__(256) tile_count_kernel(int P, int T, int NW, i
                                                          const uint32_t* __restrict__ sorted_ids,
                                                          const uint32_t* __restrict__ tiles_touched,
                                                          const float2* __restrict__ means2D, const int* __restrict__ radii,
-                                                         uint16_t* __restrict__ M) {
+                                                         uint2* __restrict__ rects, uint16_t* __restrict__ M) {
     extern __shared__ __align__(16) unsigned char s_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpc = blockDim.x >> 5;
     const int gw = blockIdx.x * wpc + warp;
@@ -125,6 +78,8 @@ __global__ void __launch_bounds__(256) tile_count_kernel(int P, int T, int NW, i
             const uint32_t id = sorted_ids[i];
             cnt = tiles_touched[id];
             if (cnt > 0) tile_rect(means2D[id], radii[id], rmin, rmax, grid_x, grid_y);
+            // kept for the scatter pass, which then reads one packed word pair per Gaussian in depth order
+            rects[i] = make_uint2(rmin.y * (uint32_t)grid_x + rmin.x, (rmax.x - rmin.x) | ((rmax.y - rmin.y) << 16));
         }
         if (cnt > 0 && cnt <= kWideRect) {
             for (uint32_t y = rmin.y; y < rmax.y; y++) {
@@ -279,11 +234,13 @@ __global__ void __launch_bounds__(256) col_scan_kernel(int T, int Tpad, int NW, 
 }
 
 // ---- 4. scatter ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int T, int NW, int L, int grid_x, int grid_y,
+// A warp hands out the slots of its chunk one Gaussian at a time, in depth order: the tiles of ONE Gaussian are
+// distinct, so its lanes read, use and bump the per-tile cursors without any ranking among themselves, and the
+// order between Gaussians is the order of the loop.  (The earlier walk of 32 instances of mixed Gaussians per step
+// needed a MATCH.ANY per step to rank equal tiles: 36 % of that kernel's stall samples.)
+__global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int T, int NW, int L, int grid_x,
                                                            const uint32_t* __restrict__ sorted_ids,
-                                                           const uint32_t* __restrict__ tiles_touched,
-                                                           const float2* __restrict__ means2D, const int* __restrict__ radii,
-                                                           const uint32_t* __restrict__ E,
+                                                           const uint2* __restrict__ rects, const uint32_t* __restrict__ E,
                                                            const uint32_t* __restrict__ tile_base,
                                                            uint32_t* __restrict__ point_list, uint32_t capacity) {
     extern __shared__ __align__(16) unsigned char s_raw[];
@@ -295,20 +252,54 @@ __global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int T, int NW,
     for (int k = lane; k < T; k += 32) cur[k] = row[k] + tile_base[k];
     __syncwarp();
     const int lo = min(P, gw * L), hi = min(P, lo + L);
-    walk_chunk(lo, hi, grid_x, grid_y, sorted_ids, tiles_touched, means2D, radii,
-               [&](bool valid, uint32_t t, uint32_t id) {
-                   const unsigned m = __match_any_sync(0xffffffffu, valid ? t : 0xffffff00u + lane);
-                   const unsigned below = m & ((1u << lane) - 1);
-                   uint32_t c = 0;
-                   if (valid) c = cur[t];
-                   __syncwarp();
-                   if (valid) {
-                       const uint32_t pos = c + __popc(below);
-                       if (pos < capacity) point_list[pos] = id;
-                       if (below == 0) cur[t] = c + __popc(m);
-                   }
-                   __syncwarp();
-               });
+    if (lo >= hi) return;
+    const unsigned full = 0xffffffffu;
+    const uint32_t off_a = (uint32_t)(lane >> 3) * (uint32_t)grid_x + (uint32_t)(lane & 7);  // lane's tile in an 8 x 4 layout
+    const uint32_t off_b = (uint32_t)(lane >> 2) * (uint32_t)grid_x + (uint32_t)(lane & 3);  // ... in a 4 x 8 layout
+    // 32 Gaussians per block: one coalesced load of their rectangles and ids (the next block's is in flight while
+    // this one is handed out), then lane j's values are broadcast in turn
+    uint2 rc_next = lo + lane < hi ? rects[lo + lane] : make_uint2(0, 0);
+    uint32_t id_next = lo + lane < hi ? sorted_ids[lo + lane] : 0u;
+    for (int b0 = lo; b0 < hi; b0 += 32) {
+        const uint2 rc_mine = rc_next;
+        const uint32_t id_mine = id_next;
+        const int nx = b0 + 32 + lane;
+        rc_next = nx < hi ? rects[nx] : make_uint2(0, 0);
+        id_next = nx < hi ? sorted_ids[nx] : 0u;
+        unsigned live = __ballot_sync(full, rc_mine.y != 0);  // culled Gaussians have no tiles
+        while (live) {
+            const int j = __ffs(live) - 1;
+            live &= live - 1;
+            const uint32_t t0 = __shfl_sync(full, rc_mine.x, j), wh = __shfl_sync(full, rc_mine.y, j);
+            const uint32_t id = __shfl_sync(full, id_mine, j);
+            const uint32_t w = wh & 0xffffu, h = wh >> 16;
+            if (w <= 8 && h <= 4) {  // the usual case: the rectangle fits the warp laid out 8 x 4 ...
+                if ((uint32_t)(lane & 7) < w && (uint32_t)(lane >> 3) < h) {
+                    const uint32_t t = t0 + off_a;
+                    const uint32_t c = cur[t];
+                    if (c < capacity) point_list[c] = id;
+                    cur[t] = c + 1;
+                }
+            } else if (w <= 4 && h <= 8) {  // ... or 4 x 8
+                if ((uint32_t)(lane & 3) < w && (uint32_t)(lane >> 2) < h) {
+                    const uint32_t t = t0 + off_b;
+                    const uint32_t c = cur[t];
+                    if (c < capacity) point_list[c] = id;
+                    cur[t] = c + 1;
+                }
+            } else {
+                const uint32_t n = w * h;
+                for (uint32_t s = lane; s < n; s += 32) {
+                    const uint32_t q = s / w;
+                    const uint32_t t = t0 + q * (uint32_t)grid_x + (s - q * w);
+                    const uint32_t c = cur[t];
+                    if (c < capacity) point_list[c] = id;
+                    cur[t] = c + 1;
+                }
+            }
+            __syncwarp();  // the next Gaussian may touch the same tiles from other lanes
+        }
+    }
 }
 
 // ---- launch plumbing ----------------------------------------------------------------------------------
@@ -337,9 +328,9 @@ BinPlan make_bin_plan(int P, int T) {
 }
 
 int launch_tile_count(const BinPlan& b, int P, int grid_x, int grid_y, const uint32_t* sorted_ids,
-                      const uint32_t* tiles_touched, const float2* means2D, const int* radii, uint16_t* M,
+                      const uint32_t* tiles_touched, const float2* means2D, const int* radii, uint2* rects, uint16_t* M,
                       cudaStream_t stream) {
-    if (b.wpc_count < 1 || b.wpc_scatter < 1 || b.L > 65535) {
+    if (b.wpc_count < 1 || b.wpc_scatter < 1 || b.L > 65535 || b.T > 65535 || grid_x > 65535 || grid_y > 65535) {
         set_error("binning: image has too many tiles (or chunk too long) for the shared-memory tile counters");
         return -1;
     }
@@ -352,7 +343,7 @@ int launch_tile_count(const BinPlan& b, int P, int grid_x, int grid_y, const uin
     }
     LaunchScope ls("tile_count", stream);
     tile_count_kernel<<<(b.NW + b.wpc_count - 1) / b.wpc_count, b.wpc_count * 32, smem, stream>>>(
-        P, b.T, b.NW, b.L, grid_x, grid_y, sorted_ids, tiles_touched, means2D, radii, M);
+        P, b.T, b.NW, b.L, grid_x, grid_y, sorted_ids, tiles_touched, means2D, radii, rects, M);
     return 0;
 }
 
@@ -367,7 +358,7 @@ int launch_tile_offsets_a(const BinPlan& b, const uint16_t* M, uint32_t* S, uint
 }
 
 int launch_tile_scatter(const BinPlan& b, int P, int grid_x, int grid_y, const uint32_t* sorted_ids,
-                        const uint32_t* tiles_touched, const float2* means2D, const int* radii, const uint16_t* M,
+                        const uint2* rects, const uint16_t* M,
                         const uint32_t* S, uint32_t* tile_base, uint32_t* E, uint32_t* point_list,
                         uint32_t capacity, cudaStream_t stream, bool base_pending, uint2* ranges, uint32_t* tile_order,
                         uint32_t* status) {
@@ -376,7 +367,7 @@ int launch_tile_scatter(const BinPlan& b, int P, int grid_x, int grid_y, const u
     col_scan_kernel<<<g, 256, 0, stream>>>(b.T, b.Tpad, b.NW, b.nseg, M, S, E, tile_base, ranges, tile_order, status, capacity);
     const size_t smem = (size_t)b.wpc_scatter * b.T * 4;
     tile_scatter_kernel<<<(b.NW + b.wpc_scatter - 1) / b.wpc_scatter, b.wpc_scatter * 32, smem, stream>>>(
-        P, b.T, b.NW, b.L, grid_x, grid_y, sorted_ids, tiles_touched, means2D, radii, E, tile_base, point_list, capacity);
+        P, b.T, b.NW, b.L, grid_x, sorted_ids, rects, E, tile_base, point_list, capacity);
     return 0;
 }
 

@@ -57,6 +57,7 @@ struct GeomState {
     uint32_t* ids;            // P iota
     uint32_t* sorted_keys;    // P depth bits, ascending
     uint32_t* sorted_ids;     // P Gaussian ids in depth order (stable)
+    uint2* rects;             // P tile rectangles in depth order: {first tile, width | height << 16}, tile_count -> tile_scatter
     char* sort_temp;
     size_t sort_temp_bytes;
     uint16_t* M;              // NW x Tpad instance counts per (chunk, tile)

@@ -101,13 +101,13 @@ int launch_depth_sort_cub(char* temp, size_t temp_bytes, const float* depths, ui
 int launch_depth_sort(char* temp, size_t temp_bytes, const float* depths, uint32_t* keys_out, const uint32_t* ids_in,
                       uint32_t* ids_out, int P, cudaStream_t stream);
 int launch_tile_count(const BinPlan& b, int P, int grid_x, int grid_y, const uint32_t* sorted_ids,
-                      const uint32_t* tiles_touched, const float2* means2D, const int* radii, uint16_t* M,
+                      const uint32_t* tiles_touched, const float2* means2D, const int* radii, uint2* rects, uint16_t* M,
                       cudaStream_t stream);
 // segment sums + tile bases + ranges + tile launch order (longest lists first) + status[0] = num_rendered, status[1] = overflow flag
 int launch_tile_offsets_a(const BinPlan& b, const uint16_t* M, uint32_t* S, uint32_t* tile_base, uint2* ranges,
                           uint32_t* tile_order, uint32_t* status, uint32_t capacity, cudaStream_t stream, bool with_base = true);
 int launch_tile_scatter(const BinPlan& b, int P, int grid_x, int grid_y, const uint32_t* sorted_ids,
-                        const uint32_t* tiles_touched, const float2* means2D, const int* radii, const uint16_t* M,
+                        const uint2* rects, const uint16_t* M,
                         const uint32_t* S, uint32_t* tile_base, uint32_t* E, uint32_t* point_list,
                         uint32_t capacity, cudaStream_t stream, bool base_pending = false, uint2* ranges = nullptr,
                         uint32_t* tile_order = nullptr, uint32_t* status = nullptr);

@@ -23,8 +23,8 @@ namespace rg {
 constexpr int kSortBits = 8;
 constexpr int kSortBins = 1 << kSortBits;
 constexpr int kSortPasses = 32 / kSortBits;
-constexpr int kSortThreads = 256;
-constexpr int kSortItems = 8;
+constexpr int kSortThreads = 512;
+constexpr int kSortItems = 4;
 constexpr int kSortTile = kSortThreads * kSortItems;  // 2048 keys per CTA
 constexpr int kSortWarps = kSortThreads / 32;
 constexpr uint32_t kFlagPartial = 1u << 30, kFlagInclusive = 2u << 30, kValueMask = (1u << 30) - 1;
@@ -45,7 +45,7 @@ static SortCtl sort_ctl(char* base, size_t tiles) {
     return c;
 }
 
-__global__ void __launch_bounds__(kSortThreads) sort_hist_kernel(const uint32_t* __restrict__ keys, int P,
+__global__ void __launch_bounds__(256) sort_hist_kernel(const uint32_t* __restrict__ keys, int P,
                                                                  uint32_t* __restrict__ hist) {
     __shared__ uint32_t s_h[kSortPasses * kSortBins];
     for (int i = threadIdx.x; i < kSortPasses * kSortBins; i += blockDim.x) s_h[i] = 0;
@@ -76,8 +76,10 @@ __global__ void __launch_bounds__(kSortThreads) sort_pass_kernel(const uint32_t*
                                                                  int P, int shift, const uint32_t* __restrict__ hist,
                                                                  uint32_t* __restrict__ counter, uint32_t* __restrict__ status) {
     __shared__ uint32_t s_cnt[kSortWarps][kSortBins];  // per warp: running digit counts, then exclusive offsets
-    __shared__ uint32_t s_base[kSortBins];             // first output slot of (this tile, digit)
-    __shared__ uint32_t s_scan[kSortWarps];
+    __shared__ uint32_t s_local[kSortBins];            // first slot of the digit inside the sorted tile
+    __shared__ uint32_t s_delta[kSortBins];            // (first output slot of (this tile, digit)) - s_local
+    __shared__ uint32_t s_scan[2][kSortBins / 32];
+    __shared__ uint32_t s_keys[kSortTile], s_vals[kSortTile];  // the tile in sorted order (coalesced write-out)
     __shared__ uint32_t s_tile;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned full = 0xffffffffu;
@@ -85,13 +87,15 @@ __global__ void __launch_bounds__(kSortThreads) sort_pass_kernel(const uint32_t*
     for (int i = tid; i < kSortWarps * kSortBins; i += kSortThreads) (&s_cnt[0][0])[i] = 0;
     __syncthreads();
     const uint32_t tile = s_tile;
-    const int base = (int)tile * kSortTile + warp * (32 * kSortItems);
+    const int tile_base = (int)tile * kSortTile;
+    const int base = tile_base + warp * (32 * kSortItems);
 
-    uint32_t key[kSortItems], rank[kSortItems];
+    uint32_t key[kSortItems], val[kSortItems], rank[kSortItems];
 #pragma unroll
     for (int j = 0; j < kSortItems; j++) {
         const int i = base + j * 32 + lane;
         key[j] = i < P ? keys_in[i] : 0xffffffffu;
+        val[j] = (vals_in && i < P) ? vals_in[i] : (uint32_t)i;
     }
     // ---- rank inside the warp, key order = (item, lane) -------------------------------------------------
 #pragma unroll
@@ -110,10 +114,10 @@ __global__ void __launch_bounds__(kSortThreads) sort_pass_kernel(const uint32_t*
         __syncwarp();
     }
     __syncthreads();
-    // ---- one thread per digit: offsets of the warps, look-back over the earlier tiles ----------------------
-    {
-        const int d = tid;  // kSortThreads == kSortBins
-        uint32_t total = 0;
+    // ---- one thread per digit (warps 0..7): offsets of the warps, look-back over the earlier tiles -----------
+    uint32_t prefix = 0, total = 0, h = 0, incl_h = 0, incl_t = 0;
+    if (tid < kSortBins) {
+        const int d = tid;
 #pragma unroll
         for (int w = 0; w < kSortWarps; w++) {
             const uint32_t c = s_cnt[w][d];
@@ -121,14 +125,13 @@ __global__ void __launch_bounds__(kSortThreads) sort_pass_kernel(const uint32_t*
             total += c;
         }
         uint32_t* mine = status + (size_t)tile * kSortBins + d;
-        uint32_t prefix = 0;
         if (tile == 0) {
             st_status(mine, kFlagInclusive | total);
         } else {
             st_status(mine, kFlagPartial | total);
             int t = (int)tile - 1;
             while (t >= 0) {
-                constexpr int W = 48;
+                constexpr int W = 32;
                 uint32_t v[W];
 #pragma unroll
                 for (int i = 0; i < W; i++) v[i] = t - i >= 0 ? ld_status(status + (size_t)(t - i) * kSortBins + d) : kFlagInclusive;
@@ -144,32 +147,49 @@ __global__ void __launch_bounds__(kSortThreads) sort_pass_kernel(const uint32_t*
             }
             st_status(mine, kFlagInclusive | (prefix + total));
         }
-        // first slot of the digit in the whole array: exclusive scan of the digit totals over the 256 digits
-        const uint32_t h = hist[d];
-        uint32_t incl = h;
+        // exclusive scans over the 256 digits: of the array-wide digit totals (first slot of the digit in the
+        // output) and of this tile's totals (first slot of the digit in the sorted tile)
+        h = hist[d];
+        incl_h = h;
+        incl_t = total;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t y = __shfl_up_sync(full, incl, o);
-            if (lane >= o) incl += y;
+            const uint32_t y = __shfl_up_sync(full, incl_h, o), z = __shfl_up_sync(full, incl_t, o);
+            if (lane >= o) { incl_h += y; incl_t += z; }
         }
-        if (lane == 31) s_scan[warp] = incl;
-        __syncthreads();
-        uint32_t before = 0;
-#pragma unroll
-        for (int w = 0; w < kSortWarps; w++)
-            if (w < warp) before += s_scan[w];
-        s_base[d] = before + incl - h + prefix;
+        if (lane == 31) { s_scan[0][warp] = incl_h; s_scan[1][warp] = incl_t; }
     }
     __syncthreads();
-    // ---- scatter ------------------------------------------------------------------------------------------
+    if (tid < kSortBins) {
+        uint32_t before_h = 0, before_t = 0;
+#pragma unroll
+        for (int w = 0; w < kSortBins / 32; w++)
+            if (w < warp) { before_h += s_scan[0][w]; before_t += s_scan[1][w]; }
+        const uint32_t local = before_t + incl_t - total;
+        s_local[tid] = local;
+        s_delta[tid] = before_h + incl_h - h + prefix - local;
+    }
+    __syncthreads();
+    // ---- the tile in sorted order in shared memory, then out in runs of consecutive addresses -----------------
 #pragma unroll
     for (int j = 0; j < kSortItems; j++) {
-        const int i = base + j * 32 + lane;
-        if (i < P) {
+        if (base + j * 32 + lane < P) {
             const uint32_t d = (key[j] >> shift) & (kSortBins - 1);
-            const uint32_t pos = s_base[d] + s_cnt[warp][d] + rank[j];
-            keys_out[pos] = key[j];
-            vals_out[pos] = vals_in ? vals_in[i] : (uint32_t)i;
+            const uint32_t p = s_local[d] + s_cnt[warp][d] + rank[j];
+            s_keys[p] = key[j];
+            s_vals[p] = val[j];
+        }
+    }
+    __syncthreads();
+    const int n_valid = min(kSortTile, P - tile_base);
+#pragma unroll
+    for (int j = 0; j < kSortItems; j++) {
+        const int p = tid + j * kSortThreads;
+        if (p < n_valid) {
+            const uint32_t k = s_keys[p];
+            const uint32_t pos = s_delta[(k >> shift) & (kSortBins - 1)] + (uint32_t)p;
+            keys_out[pos] = k;
+            vals_out[pos] = s_vals[p];
         }
     }
 }
@@ -200,7 +220,7 @@ int launch_depth_sort(char* temp, size_t temp_bytes, const float* depths, uint32
     uint32_t* tmp_ids = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(tmp_keys) + align_up((size_t)P * 4, 256));
     if (cudaMemsetAsync(temp, 0, c.words * 4, stream) != cudaSuccess) { set_error("depth sort: memset failed"); return -1; }
     const uint32_t* keys = reinterpret_cast<const uint32_t*>(depths);
-    sort_hist_kernel<<<std::min<int>((int)((P + 2047) / 2048), RG_NUM_SMS * 2), kSortThreads, 0, stream>>>(keys, P, c.hist);
+    sort_hist_kernel<<<std::min<int>((int)((P + 2047) / 2048), RG_NUM_SMS * 2), 256, 0, stream>>>(keys, P, c.hist);
     // depths -> tmp -> out -> tmp -> out
     const uint32_t* kin = keys;
     const uint32_t* vin = nullptr;
