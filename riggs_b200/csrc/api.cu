@@ -43,7 +43,8 @@ GeomState GeomState::carve(char* base, size_t P, int W, int H, size_t* bytes) {
     g.sort_temp_bytes = depth_sort_temp_bytes(P);
     g.sort_temp = c.take<char>(g.sort_temp_bytes);
     g.M = c.take<uint16_t>((size_t)bp.NW * bp.Tpad);
-    g.E = c.take<uint32_t>((size_t)bp.NW * bp.T);
+    g.Mg = c.take<uint16_t>((size_t)bp.NG * bp.Tpad);
+    g.E = c.take<uint32_t>((size_t)bp.NG * bp.T);
     g.S = c.take<uint32_t>((size_t)bp.nseg * bp.T);
     g.tile_base = c.take<uint32_t>(bp.T + 1);
     g.tile_order = c.take<uint32_t>(bp.T);
@@ -146,9 +147,9 @@ int rg_rasterize_forward(rg_alloc_fn geom_alloc, void* geom_ctx, rg_alloc_fn bin
                           P, stream))
         return -1;
     if (check_launch("depth_sort", stream, dbg)) return -1;
-    if (launch_tile_count(bp, P, grid_x, grid_y, geom.sorted_ids, geom.tiles_touched, geom.means2D, radii, geom.rects, geom.M, stream))
+    if (launch_tile_count(bp, P, grid_x, grid_y, geom.sorted_ids, geom.tiles_touched, geom.means2D, radii, geom.rects, geom.M, geom.Mg, stream))
         return -1;
-    launch_tile_offsets_a(bp, geom.M, geom.S, geom.tile_base, img.ranges, geom.tile_order, geom.status, 0xffffffffu, stream);
+    launch_tile_offsets_a(bp, geom.Mg, geom.S, geom.tile_base, img.ranges, geom.tile_order, geom.status, 0xffffffffu, stream);
     if (check_launch("tile_count/offsets", stream, dbg)) return -1;
 
     // The one host round trip of the forward (the reference does the same, rasterizer_impl.cu:282): the
@@ -165,7 +166,7 @@ int rg_rasterize_forward(rg_alloc_fn geom_alloc, void* geom_ctx, rg_alloc_fn bin
     if (!bptr) { set_error("rg_rasterize_forward: binning buffer allocation failed"); return -1; }
     BinningState bin = BinningState::carve(aligned_base(bptr), (size_t)R, nullptr);
     if (R > 0) {
-        launch_tile_scatter(bp, P, grid_x, grid_y, geom.sorted_ids, geom.rects, geom.M,
+        launch_tile_scatter(bp, P, grid_x, grid_y, geom.sorted_ids, geom.rects, geom.M, geom.Mg,
                             geom.S, geom.tile_base, geom.E, bin.point_list, (uint32_t)R, stream);
         if (check_launch("tile_scatter", stream, dbg)) return -1;
     }

@@ -91,11 +91,11 @@ int rg_skinned_forward(const RgSkinnedScene* s, const RgWorkspace* w, float* out
 
     if (launch_depth_sort(geom.sort_temp, geom.sort_temp_bytes, geom.depths, geom.sorted_keys, geom.ids, geom.sorted_ids, P, stream))
         return -1;
-    if (launch_tile_count(bp, P, grid_x, grid_y, geom.sorted_ids, geom.tiles_touched, geom.means2D, radii, geom.rects, geom.M, stream))
+    if (launch_tile_count(bp, P, grid_x, grid_y, geom.sorted_ids, geom.tiles_touched, geom.means2D, radii, geom.rects, geom.M, geom.Mg, stream))
         return -1;
     // nobody reads num_rendered on the host here, so the prefix over the tiles rides along with the column scans
-    launch_tile_offsets_a(bp, geom.M, geom.S, geom.tile_base, img.ranges, geom.tile_order, geom.status, cap, stream, false);
-    launch_tile_scatter(bp, P, grid_x, grid_y, geom.sorted_ids, geom.rects, geom.M, geom.S,
+    launch_tile_offsets_a(bp, geom.Mg, geom.S, geom.tile_base, img.ranges, geom.tile_order, geom.status, cap, stream, false);
+    launch_tile_scatter(bp, P, grid_x, grid_y, geom.sorted_ids, geom.rects, geom.M, geom.Mg, geom.S,
                         geom.tile_base, geom.E, bin.point_list, cap, stream, true, img.ranges, geom.tile_order, geom.status);
 
     BlendFwdArgs fa;

@@ -59,17 +59,17 @@ __global__ void __launch_bounds__(256) tile_count_kernel(int P, int T, int NW, i
                                                          const uint32_t* __restrict__ sorted_ids,
                                                          const uint32_t* __restrict__ tiles_touched,
                                                          const float2* __restrict__ means2D, const int* __restrict__ radii,
-                                                         uint2* __restrict__ rects, uint16_t* __restrict__ M) {
+                                                         uint2* __restrict__ rects, uint16_t* __restrict__ M,
+                                                         uint16_t* __restrict__ Mg) {
     extern __shared__ __align__(16) unsigned char s_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpc = blockDim.x >> 5;
     const int gw = blockIdx.x * wpc + warp;
     const int Tpad = (T + 1) & ~1;
     uint16_t* hist = reinterpret_cast<uint16_t*>(s_raw) + (size_t)warp * Tpad;
-    if (gw >= NW) return;
     uint32_t* h32 = reinterpret_cast<uint32_t*>(hist);
     for (int k = lane; k < Tpad / 2; k += 32) h32[k] = 0;
     __syncwarp();
-    const int lo = min(P, gw * L), hi = min(P, lo + L);
+    const int lo = min(P, gw * L), hi = gw < NW ? min(P, lo + L) : lo;  // warps past the last chunk count nothing
     for (int base = lo; base < hi; base += 32) {
         const int i = base + lane;
         uint32_t cnt = 0;
@@ -102,14 +102,30 @@ __global__ void __launch_bounds__(256) tile_count_kernel(int P, int T, int NW, i
             }
         }
     }
-    __syncwarp();
+    // The warps of a CTA hold consecutive chunks (a group): per tile, turn their counts into offsets inside the
+    // group (what the scatter pass starts its cursors from) and keep one total per (group, tile) -- the column
+    // scans then run over the groups, eight times fewer rows than chunks.
+    __syncthreads();
+    const uint16_t* all = reinterpret_cast<const uint16_t*>(s_raw);
+    uint16_t* allw = reinterpret_cast<uint16_t*>(s_raw);
+    for (int t = threadIdx.x; t < Tpad; t += blockDim.x) {
+        uint32_t run = 0;
+        for (int w = 0; w < wpc; w++) {
+            const uint32_t c = all[(size_t)w * Tpad + t];
+            allw[(size_t)w * Tpad + t] = (uint16_t)run;
+            run += c;
+        }
+        Mg[(size_t)blockIdx.x * Tpad + t] = (uint16_t)run;
+    }
+    __syncthreads();
+    if (gw >= NW) return;
     uint32_t* row = reinterpret_cast<uint32_t*>(M + (size_t)gw * Tpad);
     for (int k = lane; k < Tpad / 2; k += 32) row[k] = h32[k];
 }
 
-// ---- 3a. sums over segments of 32 chunk rows -----------------------------------------------------------
+// ---- 3a. sums over segments of 32 group rows -----------------------------------------------------------
 constexpr int kSegRows = 32;
-__global__ void __launch_bounds__(256) seg_sum_kernel(int T, int Tpad, int NW, const uint16_t* __restrict__ M,
+__global__ void __launch_bounds__(256) seg_sum_kernel(int T, int Tpad, int NW, const uint16_t* __restrict__ M,  // rows = groups
                                                       uint32_t* __restrict__ S, uint32_t* __restrict__ tile_total) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     const int seg = blockIdx.y;
@@ -182,13 +198,20 @@ __device__ __forceinline__ void tile_base_body(int T, uint32_t* __restrict__ til
         atomicAdd(&s_bucket[order_bucket(r.y - r.x)], 1u);
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t run = 0;
-        for (int b = kOrderBuckets - 1; b >= 0; b--) {
-            const uint32_t c = s_bucket[b];
-            s_bucket[b] = run;
-            run += c;
+    if (threadIdx.x < 32) {  // exclusive prefix over the buckets in DESCENDING order, four buckets per lane
+        constexpr int kPer = kOrderBuckets / 32;
+        uint32_t c[kPer], tot = 0;
+#pragma unroll
+        for (int i = 0; i < kPer; i++) { c[i] = s_bucket[kOrderBuckets - 1 - (lane * kPer + i)]; tot += c[i]; }
+        uint32_t incl = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += y;
         }
+        uint32_t run = incl - tot;
+#pragma unroll
+        for (int i = 0; i < kPer; i++) { s_bucket[kOrderBuckets - 1 - (lane * kPer + i)] = run; run += c[i]; }
     }
     __syncthreads();
     for (int t = threadIdx.x; t < T; t += NT) {
@@ -207,18 +230,18 @@ __global__ void __launch_bounds__(1024) tile_base_kernel(int T, uint32_t* __rest
     tile_base_body<1024>(T, tile_base, ranges, tile_order, status, capacity);
 }
 
-// ---- 3c. first slot of every (chunk, tile) -----------------------------------------------------------
+// ---- 3c. first slot of every (group, tile) -----------------------------------------------------------
 // E holds offsets RELATIVE to the tile's first slot, so this kernel does not wait for the prefix over the tiles:
 // with base_in_grid the block row y == nseg is one extra CTA that computes that prefix (tile_base, ranges, launch
 // order, num_rendered) next to the column scans instead of in a launch of its own before them.
-__global__ void __launch_bounds__(256) col_scan_kernel(int T, int Tpad, int NW, int nseg, const uint16_t* __restrict__ M,
+__global__ void __launch_bounds__(1024) col_scan_kernel(int T, int Tpad, int NW, int nseg, const uint16_t* __restrict__ M,
                                                        const uint32_t* __restrict__ S, uint32_t* __restrict__ E,
                                                        uint32_t* __restrict__ tile_base, uint2* __restrict__ ranges,
                                                        uint32_t* __restrict__ tile_order, uint32_t* __restrict__ status,
                                                        uint32_t capacity) {
     const int seg = blockIdx.y;
     if (seg == nseg) {  // only launched when the prefix over the tiles is still pending
-        if (blockIdx.x == 0) tile_base_body<256>(T, tile_base, ranges, tile_order, status, capacity);
+        if (blockIdx.x == 0) tile_base_body<1024>(T, tile_base, ranges, tile_order, status, capacity);
         return;
     }
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -240,17 +263,27 @@ __global__ void __launch_bounds__(256) col_scan_kernel(int T, int Tpad, int NW, 
 // needed a MATCH.ANY per step to rank equal tiles: 36 % of that kernel's stall samples.)
 __global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int T, int NW, int L, int grid_x,
                                                            const uint32_t* __restrict__ sorted_ids,
-                                                           const uint2* __restrict__ rects, const uint32_t* __restrict__ E,
+                                                           const uint2* __restrict__ rects, const uint16_t* __restrict__ M,
+                                                           const uint32_t* __restrict__ E,
                                                            const uint32_t* __restrict__ tile_base,
                                                            uint32_t* __restrict__ point_list, uint32_t capacity) {
     extern __shared__ __align__(16) unsigned char s_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpc = blockDim.x >> 5;
     const int gw = blockIdx.x * wpc + warp;
-    uint32_t* cur = reinterpret_cast<uint32_t*>(s_raw) + (size_t)warp * T;
+    const int Tpad = (T + 1) & ~1;
+    // slot of an instance = first slot of (group, tile) [32-bit, shared by the CTA's warps] + the warp's running
+    // 16-bit cursor, which starts at the chunk's offset inside the group (tile_count's M rows)
+    uint32_t* base = reinterpret_cast<uint32_t*>(s_raw);
+    uint16_t* cur = reinterpret_cast<uint16_t*>(base + Tpad) + (size_t)warp * Tpad;
+    const uint32_t* grow = E + (size_t)blockIdx.x * T;
+    for (int k = threadIdx.x; k < T; k += blockDim.x) base[k] = grow[k] + tile_base[k];
+    if (gw < NW) {
+        const uint32_t* row = reinterpret_cast<const uint32_t*>(M + (size_t)gw * Tpad);
+        uint32_t* c32 = reinterpret_cast<uint32_t*>(cur);
+        for (int k = lane; k < Tpad / 2; k += 32) c32[k] = row[k];
+    }
+    __syncthreads();
     if (gw >= NW) return;
-    const uint32_t* row = E + (size_t)gw * T;
-    for (int k = lane; k < T; k += 32) cur[k] = row[k] + tile_base[k];
-    __syncwarp();
     const int lo = min(P, gw * L), hi = min(P, lo + L);
     if (lo >= hi) return;
     const unsigned full = 0xffffffffu;
@@ -276,25 +309,28 @@ __global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int T, int NW,
             if (w <= 8 && h <= 4) {  // the usual case: the rectangle fits the warp laid out 8 x 4 ...
                 if ((uint32_t)(lane & 7) < w && (uint32_t)(lane >> 3) < h) {
                     const uint32_t t = t0 + off_a;
-                    const uint32_t c = cur[t];
+                    const uint32_t k = cur[t];
+                    const uint32_t c = base[t] + k;
                     if (c < capacity) point_list[c] = id;
-                    cur[t] = c + 1;
+                    cur[t] = (uint16_t)(k + 1);
                 }
             } else if (w <= 4 && h <= 8) {  // ... or 4 x 8
                 if ((uint32_t)(lane & 3) < w && (uint32_t)(lane >> 2) < h) {
                     const uint32_t t = t0 + off_b;
-                    const uint32_t c = cur[t];
+                    const uint32_t k = cur[t];
+                    const uint32_t c = base[t] + k;
                     if (c < capacity) point_list[c] = id;
-                    cur[t] = c + 1;
+                    cur[t] = (uint16_t)(k + 1);
                 }
             } else {
                 const uint32_t n = w * h;
                 for (uint32_t s = lane; s < n; s += 32) {
                     const uint32_t q = s / w;
                     const uint32_t t = t0 + q * (uint32_t)grid_x + (s - q * w);
-                    const uint32_t c = cur[t];
+                    const uint32_t k = cur[t];
+                    const uint32_t c = base[t] + k;
                     if (c < capacity) point_list[c] = id;
-                    cur[t] = c + 1;
+                    cur[t] = (uint16_t)(k + 1);
                 }
             }
             __syncwarp();  // the next Gaussian may touch the same tiles from other lanes
@@ -318,23 +354,25 @@ BinPlan make_bin_plan(int P, int T) {
     if (NW < 1) NW = 1;
     b.L = L;
     b.NW = NW;
-    b.nseg = (NW + kSegRows - 1) / kSegRows;
+    // a group = the chunks of one CTA of the two walking kernels; its size is bounded by their shared memory
+    // (scatter: 4 bytes per tile for the group + 2 per tile and warp)
     const size_t smem_budget = 200 * 1024;
-    int wpc_count = (int)(smem_budget / ((size_t)b.Tpad * 2));
-    int wpc_scatter = (int)(smem_budget / ((size_t)T * 4));
-    b.wpc_count = wpc_count > 8 ? 8 : wpc_count;
-    b.wpc_scatter = wpc_scatter > 8 ? 8 : wpc_scatter;
+    int wpc = ((int)smem_budget - 4 * b.Tpad) / (2 * b.Tpad);
+    b.wpc = wpc > 8 ? 8 : wpc;
+    if (b.wpc < 1) b.wpc = 0;
+    b.NG = b.wpc ? (NW + b.wpc - 1) / b.wpc : 0;
+    b.nseg = (b.NG + kSegRows - 1) / kSegRows;
     return b;
 }
 
 int launch_tile_count(const BinPlan& b, int P, int grid_x, int grid_y, const uint32_t* sorted_ids,
                       const uint32_t* tiles_touched, const float2* means2D, const int* radii, uint2* rects, uint16_t* M,
-                      cudaStream_t stream) {
-    if (b.wpc_count < 1 || b.wpc_scatter < 1 || b.L > 65535 || b.T > 65535 || grid_x > 65535 || grid_y > 65535) {
+                      uint16_t* Mg, cudaStream_t stream) {
+    if (b.wpc < 1 || (size_t)b.L * b.wpc > 65535 || b.T > 65535 || grid_x > 65535 || grid_y > 65535) {
         set_error("binning: image has too many tiles (or chunk too long) for the shared-memory tile counters");
         return -1;
     }
-    const size_t smem = (size_t)b.wpc_count * b.Tpad * 2;
+    const size_t smem = (size_t)b.wpc * b.Tpad * 2;
     static bool attr_set = false;
     if (!attr_set) {
         cudaFuncSetAttribute(tile_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
@@ -342,32 +380,32 @@ int launch_tile_count(const BinPlan& b, int P, int grid_x, int grid_y, const uin
         attr_set = true;
     }
     LaunchScope ls("tile_count", stream);
-    tile_count_kernel<<<(b.NW + b.wpc_count - 1) / b.wpc_count, b.wpc_count * 32, smem, stream>>>(
-        P, b.T, b.NW, b.L, grid_x, grid_y, sorted_ids, tiles_touched, means2D, radii, rects, M);
+    tile_count_kernel<<<b.NG, b.wpc * 32, smem, stream>>>(P, b.T, b.NW, b.L, grid_x, grid_y, sorted_ids, tiles_touched, means2D,
+                                                        radii, rects, M, Mg);
     return 0;
 }
 
-int launch_tile_offsets_a(const BinPlan& b, const uint16_t* M, uint32_t* S, uint32_t* tile_base, uint2* ranges,
+int launch_tile_offsets_a(const BinPlan& b, const uint16_t* Mg, uint32_t* S, uint32_t* tile_base, uint2* ranges,
                           uint32_t* tile_order, uint32_t* status, uint32_t capacity, cudaStream_t stream, bool with_base) {
     LaunchScope ls("tile_offsets", stream, with_base ? 2 : 1);
     dim3 g((b.T + 255) / 256, b.nseg);
     cudaMemsetAsync(tile_base, 0, sizeof(uint32_t) * b.T, stream);
-    seg_sum_kernel<<<g, 256, 0, stream>>>(b.T, b.Tpad, b.NW, M, S, tile_base);
+    seg_sum_kernel<<<g, 256, 0, stream>>>(b.T, b.Tpad, b.NG, Mg, S, tile_base);
     if (with_base) tile_base_kernel<<<1, 1024, 0, stream>>>(b.T, tile_base, ranges, tile_order, status, capacity);
     return 0;
 }
 
 int launch_tile_scatter(const BinPlan& b, int P, int grid_x, int grid_y, const uint32_t* sorted_ids,
-                        const uint2* rects, const uint16_t* M,
+                        const uint2* rects, const uint16_t* M, const uint16_t* Mg,
                         const uint32_t* S, uint32_t* tile_base, uint32_t* E, uint32_t* point_list,
                         uint32_t capacity, cudaStream_t stream, bool base_pending, uint2* ranges, uint32_t* tile_order,
                         uint32_t* status) {
     LaunchScope ls("tile_scatter", stream, 2);
-    dim3 g((b.T + 255) / 256, b.nseg + (base_pending ? 1 : 0));
-    col_scan_kernel<<<g, 256, 0, stream>>>(b.T, b.Tpad, b.NW, b.nseg, M, S, E, tile_base, ranges, tile_order, status, capacity);
-    const size_t smem = (size_t)b.wpc_scatter * b.T * 4;
-    tile_scatter_kernel<<<(b.NW + b.wpc_scatter - 1) / b.wpc_scatter, b.wpc_scatter * 32, smem, stream>>>(
-        P, b.T, b.NW, b.L, grid_x, sorted_ids, rects, E, tile_base, point_list, capacity);
+    dim3 g((b.T + 1023) / 1024, b.nseg + (base_pending ? 1 : 0));
+    col_scan_kernel<<<g, 1024, 0, stream>>>(b.T, b.Tpad, b.NG, b.nseg, Mg, S, E, tile_base, ranges, tile_order, status, capacity);
+    const size_t smem = (size_t)b.Tpad * 4 + (size_t)b.wpc * b.Tpad * 2;
+    tile_scatter_kernel<<<b.NG, b.wpc * 32, smem, stream>>>(P, b.T, b.NW, b.L, grid_x, sorted_ids, rects, M, E, tile_base,
+                                                          point_list, capacity);
     return 0;
 }
 

@@ -60,8 +60,9 @@ struct GeomState {
     uint2* rects;             // P tile rectangles in depth order: {first tile, width | height << 16}, tile_count -> tile_scatter
     char* sort_temp;
     size_t sort_temp_bytes;
-    uint16_t* M;              // NW x Tpad instance counts per (chunk, tile)
-    uint32_t* E;              // NW x T first slot per (chunk, tile)
+    uint16_t* M;              // NW x Tpad per (chunk, tile): instances of the earlier chunks of the same group
+    uint16_t* Mg;             // NG x Tpad instance counts per (group, tile)
+    uint32_t* E;              // NG x T first slot of (group, tile) relative to the tile's first slot
     uint32_t* S;              // nseg x T
     uint32_t* tile_base;      // T
     uint32_t* tile_order;     // T tile indices, longest instance lists first: launch order of the blend kernels

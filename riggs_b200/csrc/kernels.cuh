@@ -90,8 +90,8 @@ int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t*
 struct BinPlan {
     int T, Tpad;      // tiles, tiles padded to even (u16 rows are copied as u32 words)
     int NW, L;        // chunks (one warp each) of L depth-ordered Gaussians
-    int nseg;         // segments of 32 chunk rows
-    int wpc_count, wpc_scatter;  // warps per CTA of the two walking kernels (shared-memory bound)
+    int wpc, NG;      // chunks per group (= warps per CTA of the two walking kernels, shared-memory bound), groups
+    int nseg;         // segments of 32 group rows
 };
 BinPlan make_bin_plan(int P, int T);
 size_t depth_sort_temp_bytes(size_t P);      // radix_sort.cu (covers the library sort's need as well)
@@ -102,12 +102,12 @@ int launch_depth_sort(char* temp, size_t temp_bytes, const float* depths, uint32
                       uint32_t* ids_out, int P, cudaStream_t stream);
 int launch_tile_count(const BinPlan& b, int P, int grid_x, int grid_y, const uint32_t* sorted_ids,
                       const uint32_t* tiles_touched, const float2* means2D, const int* radii, uint2* rects, uint16_t* M,
-                      cudaStream_t stream);
+                      uint16_t* Mg, cudaStream_t stream);
 // segment sums + tile bases + ranges + tile launch order (longest lists first) + status[0] = num_rendered, status[1] = overflow flag
-int launch_tile_offsets_a(const BinPlan& b, const uint16_t* M, uint32_t* S, uint32_t* tile_base, uint2* ranges,
+int launch_tile_offsets_a(const BinPlan& b, const uint16_t* Mg, uint32_t* S, uint32_t* tile_base, uint2* ranges,
                           uint32_t* tile_order, uint32_t* status, uint32_t capacity, cudaStream_t stream, bool with_base = true);
 int launch_tile_scatter(const BinPlan& b, int P, int grid_x, int grid_y, const uint32_t* sorted_ids,
-                        const uint2* rects, const uint16_t* M,
+                        const uint2* rects, const uint16_t* M, const uint16_t* Mg,
                         const uint32_t* S, uint32_t* tile_base, uint32_t* E, uint32_t* point_list,
                         uint32_t capacity, cudaStream_t stream, bool base_pending = false, uint2* ranges = nullptr,
                         uint32_t* tile_order = nullptr, uint32_t* status = nullptr);
