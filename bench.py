@@ -351,7 +351,7 @@ def run_ours(args):
             line["reference_cuda_b200"] = rc
     if world == 1:
         line["next_rows"] = next_rows(hp, out["render"].detach(), target)
-    print(json.dumps(line), flush=True)
+    _emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -494,7 +494,7 @@ def run_reference(args):
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": f"{steps} full iterations, oracle port (torch-CPU skinning + OpenMP C rasterizer)"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 def ref_cuda_baseline(scene, cam, pose, target, steps=10):
@@ -553,7 +553,19 @@ def ref_cuda_baseline(scene, cam, pose, target, steps=10):
         return {"unavailable": repr(ex)[:200]}
 
 
+def _emit(line: dict) -> None:
+    """The ONE JSON line goes to the process's original stdout; see __main__."""
+    os.write(_JSON_FD, (json.dumps(line) + "\n").encode())
+
+
+_JSON_FD = 1
+
 if __name__ == "__main__":
+    # Libraries write banners to file descriptor 1 behind Python's back (NCCL prints its version line there when the
+    # first communicator is made): keep a private copy of stdout for the JSON line and point fd 1 at stderr.
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     a = parse()
     if a.impl == "reference":
         run_reference(a)
