@@ -172,6 +172,26 @@ int rg_skin_backward(int N, int J, const float* xyz, const float* joints, const 
                      float* dnode_radius_raw, float* dglobal_trans, float* dmask, float* dmlp_weight,
                      float* doffsets, rg_stream_t stream);
 
+/* Linear-blend skinning by the K nearest bones of every point: SkeletonWarp.cal_nn_weight_skeleton with K > 0
+ * (skeleton_utils/skeleton_warp.py:46-49: torch.topk of the squared point-to-segment distances, smallest first,
+ * nn_idx = bone + 1) followed by the LBS of deform_by_pose (:130-172).  Same arguments as rg_skin_forward without
+ * mlp_weight (the reference's K > 0 branch indexes the MLP output out of range, :59) and with linear blending only.
+ * Outputs: d_xyz (N,3), d_rot (N,4), nn_weight (N,K), nn_idx (N,K) int64 joint numbers 1..J-1, nn_dist2 (N,K).
+ * 1 <= K <= min(8, J - 1). */
+int rg_skin_topk_forward(int N, int J, int K, const float* xyz, const float* joints, const int* parents,
+                         const float* node_radius_raw, const float* G, const float* node_rot, const float* global_trans,
+                         const float* motion_mask, const float* offsets, float* d_xyz, float* d_rot, float* nn_weight,
+                         long long* nn_idx, float* nn_dist2, rg_stream_t stream);
+
+/* Backward of rg_skin_topk_forward for the bones nn_idx selected (the selection itself has no gradient).  g_dxyz (N,3),
+ * g_drot (N,4) (NULL = none); dG (J,12), dnode_radius_raw (J), dglobal_trans (3) are ACCUMULATED (zero them first);
+ * dmask (N), doffsets (N,3) are written (NULL = skip). */
+int rg_skin_topk_backward(int N, int J, int K, const float* xyz, const float* joints, const int* parents,
+                          const float* node_radius_raw, const float* G, const float* node_rot, const float* global_trans,
+                          const float* motion_mask, const float* offsets, const long long* nn_idx, const float* g_dxyz,
+                          const float* g_drot, float* dG, float* dnode_radius_raw, float* dglobal_trans, float* dmask,
+                          float* doffsets, rg_stream_t stream);
+
 /* ---- stage-1 control-node warp ------------------------------------------------------------------ */
 
 /* K nearest control nodes, their weights and the blend of the per-node motion onto N points.  Replaces
@@ -324,6 +344,12 @@ typedef struct RgRowTensor {
 size_t rg_compact_scratch_bytes(int P);
 int rg_compact_rows(int P, const uint8_t* keep, int n_tensors, const RgRowTensor* tensors, void* scratch, size_t scratch_bytes,
                     int* count_out, rg_stream_t stream);
+
+/* Rows of up to 32 tensors regrouped by one explicit index list: dst tensor q gets n_out rows, row r = src row
+ * src_row[r] (any order, repeats allowed) or zeros where src_row[r] < 0.  Replaces the torch.cat + boolean-index pairs
+ * of densification_postfix / cat_tensors_to_optimizer / prune_points (scene/gaussian_model.py:356-440) when points are
+ * cloned or split: parameters are gathered from their parents, the Adam moments of new points start at zero. */
+int rg_gather_rows(long long n_out, const int* src_row, int n_tensors, const RgRowTensor* tensors, rg_stream_t stream);
 
 /* K nearest of M nodes for each of N points, brute force: the search the reference's stage-1 control-node code gets from
  * pytorch3d.ops.knn_points (utils/time_utils.py:950,980,1051,1061,1124).  points (N,D), nodes (M,D), 1 <= D <= 8,

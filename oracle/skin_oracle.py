@@ -66,14 +66,28 @@ def bone_dist2(x: torch.Tensor, joints: torch.Tensor, parents: torch.Tensor) -> 
     return ((s - p) * (s - p)).sum(-1)
 
 
-def skin_weights(x, joints, parents, node_radius_raw, mlp_weight=None):
+def skin_weights(x, joints, parents, node_radius_raw, mlp_weight=None, K=-1, nn_idx=None):
+    """cal_nn_weight_skeleton (skeleton_warp.py:41-76).  K <= 0: all bones, returns (w (N,J-1), d2 (N,J-1), None);
+    K > 0: the K nearest bones (torch.topk, ascending), returns (w (N,K), d2 (N,K), idx (N,K) = joint numbers 1..J-1)."""
     d2 = bone_dist2(x, joints, parents)
-    radius = torch.exp(node_radius_raw)[1:]
+    idx = None
+    if K > 0:
+        if nn_idx is not None:  # selection given (tests: equidistant bones make torch.topk's choice arbitrary)
+            idx = nn_idx.long() - 1
+            d2 = torch.gather(d2, 1, idx)
+        else:
+            d2, idx = torch.topk(d2, K, largest=False, dim=1)
+        idx = idx + 1
+        radius = torch.exp(node_radius_raw)[idx]
+        if mlp_weight is not None:
+            raise ValueError("K > 0 with the weight MLP is out of range in the reference (skeleton_warp.py:59)")
+    else:
+        radius = torch.exp(node_radius_raw)[1:]
     w = torch.exp(-d2 / (2 * radius ** 2))
     if mlp_weight is not None:
         w = w * mlp_weight
     w = w + 1e-7
-    return w / w.sum(-1, keepdim=True), d2
+    return w / w.sum(-1, keepdim=True), d2, idx
 
 
 def forward_kinematics(local_rot_mats: torch.Tensor, joints: torch.Tensor, parents: torch.Tensor):
@@ -96,25 +110,31 @@ def forward_kinematics(local_rot_mats: torch.Tensor, joints: torch.Tensor, paren
 
 
 def deform_by_pose(x, joints, parents, node_radius_raw, local_rotation, global_trans, motion_mask,
-                   mlp_weight=None, template_offsets=None):
+                   mlp_weight=None, template_offsets=None, K=-1, nn_idx=None):
     """LBS core.  Returns the dict of the reference's third boundary."""
     x = x.detach()
     R_local = quat_to_mat(local_rotation)
-    w, _ = skin_weights(x, joints, parents, node_radius_raw, mlp_weight)
+    w, d2, idx = skin_weights(x, joints, parents, node_radius_raw, mlp_weight, K, nn_idx)
     posed, G = forward_kinematics(R_local, joints[:, :3], parents)
     G_R, G_t = G[:, :3, :3], G[:, :3, 3]
     node_rot = mat_to_quat(G_R.detach())
-    Ax = torch.einsum("kab,nb->nka", G_R[1:], x) + G_t[1:][None]
+    if idx is None:
+        Ax = torch.einsum("kab,nb->nka", G_R[1:], x) + G_t[1:][None]
+        rot = node_rot[1:][None]
+        nn_idx = torch.arange(1, joints.shape[0], device=x.device).unsqueeze(0).expand(x.shape[0], -1)
+    else:
+        Ax = torch.einsum("nkab,nb->nka", G_R[idx], x) + G_t[idx]
+        rot = node_rot[idx]
+        nn_idx = idx
     Ax_avg = (Ax * w[..., None]).sum(1)
     Ax_avg = Ax_avg + global_trans
     if template_offsets is not None:
         Ax_avg = Ax_avg + template_offsets
     d_xyz = (Ax_avg - x) * motion_mask
-    d_rot = (node_rot[1:][None] * w[..., None]).sum(1) * motion_mask
+    d_rot = (rot * w[..., None]).sum(1) * motion_mask
     return {"d_xyz": d_xyz, "d_rotation": d_rot,
             "d_scaling": torch.zeros(x.shape[0], 3, dtype=x.dtype, device=x.device),
-            "d_nodes": posed + global_trans, "nn_weight": w,
-            "nn_idx": torch.arange(1, joints.shape[0], device=x.device).unsqueeze(0).expand(x.shape[0], -1),
+            "d_nodes": posed + global_trans, "nn_weight": w, "nn_idx": nn_idx, "nn_dist2": d2,
             "G": G, "node_rot": node_rot}
 
 

@@ -83,7 +83,10 @@ _SIGNATURES = {
     "rg_densification_stats": (C.c_int, [_i, _p, _p, _p, _p, _p, _p]),
     "rg_compact_scratch_bytes": (C.c_size_t, [_i]),
     "rg_compact_rows": (C.c_int, [_i, _p, _i, _p, _p, C.c_size_t, _p, _p]),
+    "rg_gather_rows": (C.c_int, [C.c_longlong, _p, _i, _p, _p]),
     "rg_knn_points": (C.c_int, [_i, _i, _i, _i, _p, _p, _p, _p, _p]),
+    "rg_skin_topk_forward": (C.c_int, [_i, _i, _i] + [_p] * 15),
+    "rg_skin_topk_backward": (C.c_int, [_i, _i, _i] + [_p] * 18),
     "rg_node_warp_forward": (C.c_int, [_i, _i, _i, _i] + [_p] * 12 + [_i] + [_p] * 9),
     "rg_node_warp_grad_channels": (C.c_int, []),
     "rg_node_warp_backward": (C.c_int, [_i, _i, _i, _i] + [_p] * 23),

@@ -47,6 +47,22 @@ __global__ void __launch_bounds__(256) gather_rows_kernel(RowTable t, const int*
     }
 }
 
+// dst row r = src row src_row[r], or zeros where src_row[r] < 0 (rows that start from nothing: the Adam moments of a
+// cloned or split Gaussian).  n_out is known on the host here.
+__global__ void __launch_bounds__(256) gather_rows_indexed_kernel(RowTable t, const int* __restrict__ src_row, size_t n_out) {
+    const int q = blockIdx.y;
+    const uint32_t words = t.words[q];
+    const uint32_t* __restrict__ src = t.src[q];
+    uint32_t* __restrict__ dst = t.dst[q];
+    const size_t total = n_out * words;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        const size_t r = i / words, w = i - r * words;
+        const int s = src_row[r];
+        dst[i] = s >= 0 ? src[(size_t)s * words + w] : 0u;
+    }
+}
+
 }  // namespace rg
 
 using namespace rg;
@@ -100,3 +116,38 @@ int rg_compact_rows(int P, const uint8_t* keep, int n_tensors, const RgRowTensor
 }
 
 }  // extern "C"
+
+// Rows of several tensors regrouped by ONE explicit index list: what densify_and_clone / densify_and_split /
+// cat_tensors_to_optimizer + prune_points do with a torch.cat and a boolean-mask index per tensor and per Adam moment
+// (scene/gaussian_model.py:356-518).  dst tensor q gets n_out rows; row r = src row src_row[r] (any order, repeats
+// allowed), or zeros where src_row[r] < 0.
+extern "C" int rg_gather_rows(long long n_out, const int* src_row, int n_tensors, const RgRowTensor* tensors, rg_stream_t stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (n_out < 0 || n_tensors < 1 || n_tensors > kMaxRowTensors || !tensors || (n_out > 0 && !src_row)) {
+        set_error("rg_gather_rows: bad argument (1..32 tensors)");
+        return -1;
+    }
+    if (n_out == 0) return 0;
+    RowTable t;
+    t.n = n_tensors;
+    size_t acc = 0, max_words = 1;
+    for (int q = 0; q < n_tensors; q++) {
+        if (!tensors[q].src || !tensors[q].dst || tensors[q].row_bytes == 0 || (tensors[q].row_bytes & 3) ||
+            (reinterpret_cast<uintptr_t>(tensors[q].src) & 3) || (reinterpret_cast<uintptr_t>(tensors[q].dst) & 3)) {
+            set_error("rg_gather_rows: rows must be non-empty multiples of 4 bytes, 4-byte aligned");
+            return -1;
+        }
+        t.src[q] = static_cast<const uint32_t*>(tensors[q].src);
+        t.dst[q] = static_cast<uint32_t*>(tensors[q].dst);
+        t.words[q] = (uint32_t)(tensors[q].row_bytes / 4);
+        acc += t.words[q];
+        t.end[q] = acc;
+        max_words = std::max<size_t>(max_words, t.words[q]);
+    }
+    LaunchScope ls("gather_rows", stream);
+    size_t blocks = ((size_t)n_out * std::min<size_t>(max_words, 8) + 255) / 256;
+    blocks = std::min<size_t>(std::max<size_t>(blocks, 1), (size_t)RG_NUM_SMS * 16);
+    gather_rows_indexed_kernel<<<dim3((unsigned)blocks, (unsigned)n_tensors), 256, 0, stream>>>(t, src_row, (size_t)n_out);
+    if (cudaGetLastError() != cudaSuccess) { set_error("rg_gather_rows: launch failed"); return -1; }
+    return 0;
+}

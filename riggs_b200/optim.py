@@ -149,3 +149,151 @@ def prune_points(optimizer: FusedAdam, mask: torch.Tensor, stats: Optional[Dict[
         g["params"][0] = newp
         new_params[g.get("name", str(i))] = newp
     return new_params, {n: out[k + j] for j, n in enumerate(stat_names)}
+
+
+# ---- densification: clone / split / prune (scene/gaussian_model.py:393-505) -------------------------------------
+# The reference appends the new points with a torch.cat per parameter and per Adam moment (cat_tensors_to_optimizer),
+# then -- for a split -- removes the parents with a boolean index per tensor again (prune_points).  Here every step is
+# ONE index list (kept rows, then the parents of the new rows) and two gather launches (csrc/compact.cu: the
+# parameters, and the Adam moments with zeros for the new rows); a split never materialises the parents + children set.
+
+def _groups(optimizer: FusedAdam):
+    return {g.get("name", str(i)): g for i, g in enumerate(optimizer.param_groups)}
+
+
+@torch.no_grad()
+def regroup_rows(optimizer: FusedAdam, src_row: torch.Tensor, n_old_rows: int) -> Dict[str, torch.nn.Parameter]:
+    """New parameters with ``len(src_row)`` rows: row r is a copy of old row ``src_row[r]``.  The Adam moments follow
+    for the first ``n_old_rows`` entries of ``src_row`` (rows that survive) and start at zero for the rest (new
+    points), as cat_tensors_to_optimizer does (:393-415).  Groups and optimizer state are replaced in place."""
+    dev = src_row.device
+    if not src_row.is_cuda:
+        raise _lib.RiggsError("regroup_rows needs CUDA tensors; riggs_b200 has no CPU path")
+    src_row = src_row.to(torch.int32).contiguous()
+    n_out = src_row.numel()
+    src_state = src_row.clone()
+    src_state[n_old_rows:] = -1
+    params = [g["params"][0] for g in optimizer.param_groups]
+    P = params[0].shape[0]
+    new = [torch.empty((n_out,) + tuple(p.shape[1:]), dtype=p.dtype, device=dev) for p in params]
+    states = [optimizer.state.get(p) for p in params]
+    m_src, m_dst = [], []
+    for p, st in zip(params, states):
+        if st is not None:
+            for k in ("exp_avg", "exp_avg_sq"):
+                m_src.append(st[k])
+                m_dst.append(torch.empty((n_out,) + tuple(p.shape[1:]), dtype=p.dtype, device=dev))
+    L = _lib.lib()
+
+    def gather(srcs, dsts, rows):
+        if not srcs or n_out == 0:
+            return
+        arr = (_lib.RgRowTensor * len(srcs))(*[_lib.RgRowTensor(ptr(s.detach().contiguous()), ptr(d), (s.numel() // P) * 4)
+                                              for s, d in zip(srcs, dsts)])
+        check(L.rg_gather_rows(n_out, ptr(rows), len(srcs), C.cast(arr, C.c_void_p), stream_ptr()), "rg_gather_rows")
+
+    with torch.cuda.device(dev):
+        gather(params, new, src_row)
+        gather(m_src, m_dst, src_state)
+    out: Dict[str, torch.nn.Parameter] = {}
+    k = 0
+    for i, (g, p, st) in enumerate(zip(optimizer.param_groups, params, states)):
+        newp = torch.nn.Parameter(new[i].requires_grad_(True))
+        if st is not None:
+            del optimizer.state[p]
+            optimizer.state[newp] = {"exp_avg": m_dst[k], "exp_avg_sq": m_dst[k + 1]}
+            k += 2
+        g["params"][0] = newp
+        out[g.get("name", str(i))] = newp
+    return out
+
+
+def _reset_stats(stats: Optional[Dict[str, torch.Tensor]], n: int, device) -> Dict[str, torch.Tensor]:
+    """densification_postfix (:437-439): the statistics start over at the new size."""
+    return {k: torch.zeros((n,) + tuple(v.shape[1:]), dtype=v.dtype, device=device) for k, v in (stats or {}).items()}
+
+
+def _scaling_activated(optimizer: FusedAdam) -> torch.Tensor:
+    s = _groups(optimizer)["scaling"]["params"][0].detach()
+    if s.shape[1] == 1:  # isotropic Gaussians keep one column (get_scaling, :105-110)
+        s = s.repeat(1, 3)
+    return torch.exp(s)
+
+
+def build_rotation(r: torch.Tensor) -> torch.Tensor:
+    """utils/general_utils.py:137-158."""
+    q = r / torch.sqrt((r * r).sum(1))[:, None]
+    w, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    return torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y),
+                        2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x),
+                        2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)], 1).reshape(-1, 3, 3)
+
+
+@torch.no_grad()
+def densify_and_clone(optimizer: FusedAdam, stats, grads=None, grad_threshold=None, scene_extent=None,
+                      percent_dense: float = 0.01, selected_pts_mask=None):
+    """GaussianModel.densify_and_clone (:479-499): small Gaussians with a large view-space gradient are duplicated.
+    Returns ({group name: new parameter}, fresh statistics)."""
+    params = _groups(optimizer)
+    P = params["xyz"]["params"][0].shape[0]
+    if selected_pts_mask is None:
+        selected_pts_mask = torch.norm(grads, dim=-1) >= grad_threshold
+        selected_pts_mask = torch.logical_and(selected_pts_mask,
+                                              _scaling_activated(optimizer).max(dim=1).values <= percent_dense * scene_extent)
+    dev = selected_pts_mask.device
+    sel = selected_pts_mask.reshape(-1).nonzero().reshape(-1).to(torch.int32)
+    src = torch.cat([torch.arange(P, dtype=torch.int32, device=dev), sel])
+    new = regroup_rows(optimizer, src, P)
+    return new, _reset_stats(stats, src.numel(), dev)
+
+
+@torch.no_grad()
+def densify_and_split(optimizer: FusedAdam, stats, grads=None, grad_threshold=None, scene_extent=None,
+                      percent_dense: float = 0.01, N: int = 2, selected_pts_mask=None, without_prune: bool = False,
+                      samples: Optional[torch.Tensor] = None, generator: Optional[torch.Generator] = None):
+    """GaussianModel.densify_and_split (:441-477): large Gaussians with a large gradient are replaced by N smaller
+    ones drawn from them.  ``samples``: optional (N * n_selected, 3) standard-normal draws (the reference calls
+    torch.normal(0, stds); here ``samples * stds``), so that a caller or a test controls the random numbers.
+    Returns ({group name: new parameter}, fresh statistics)."""
+    params = _groups(optimizer)
+    P = params["xyz"]["params"][0].shape[0]
+    dev = params["xyz"]["params"][0].device
+    if selected_pts_mask is None:
+        padded_grad = torch.zeros(P, device=dev)
+        padded_grad[:grads.shape[0]] = grads.squeeze()
+        selected_pts_mask = padded_grad >= grad_threshold
+        selected_pts_mask = torch.logical_and(selected_pts_mask,
+                                              _scaling_activated(optimizer).max(dim=1).values > percent_dense * scene_extent)
+    selected_pts_mask = selected_pts_mask.reshape(-1)
+    sel = selected_pts_mask.nonzero().reshape(-1).to(torch.int32)
+    kept = (torch.arange(P, dtype=torch.int32, device=dev) if without_prune
+            else (~selected_pts_mask).nonzero().reshape(-1).to(torch.int32))
+    n_keep, n_new = kept.numel(), sel.numel() * N
+    src = torch.cat([kept, sel.repeat(N)])
+    new = regroup_rows(optimizer, src, n_keep)
+    if n_new:
+        scaling = new["scaling"].data[n_keep:]
+        act = torch.exp(scaling.repeat(1, 3) if scaling.shape[1] == 1 else scaling)  # the parents' get_scaling
+        z = samples.to(dev).float() if samples is not None else torch.randn((n_new, 3), device=dev, generator=generator)
+        rots = build_rotation(new["rotation"].data[n_keep:])
+        new["xyz"].data[n_keep:] = torch.bmm(rots, (z * act).unsqueeze(-1)).squeeze(-1) + new["xyz"].data[n_keep:]
+        new_scaling = torch.log(act / (0.8 * N))
+        new["scaling"].data[n_keep:] = new_scaling[:, :scaling.shape[1]]
+    return new, _reset_stats(stats, src.numel(), dev)
+
+
+@torch.no_grad()
+def densify_and_prune(optimizer: FusedAdam, stats: Dict[str, torch.Tensor], max_grad, min_opacity, extent, max_screen_size,
+                      percent_dense: float = 0.01, generator: Optional[torch.Generator] = None):
+    """GaussianModel.densify_and_prune (:501-514) on ``stats`` = {xyz_gradient_accum (P,1), denom (P,1), max_radii2D (P)}."""
+    grads = stats["xyz_gradient_accum"] / stats["denom"]
+    grads[grads.isnan()] = 0.0
+    _, stats = densify_and_clone(optimizer, stats, grads, max_grad, extent, percent_dense)
+    _, stats = densify_and_split(optimizer, stats, grads, max_grad, extent, percent_dense, generator=generator)
+    opacity = torch.sigmoid(_groups(optimizer)["opacity"]["params"][0].detach())
+    prune_mask = (opacity < min_opacity).squeeze()
+    if max_screen_size:
+        big_points_vs = stats["max_radii2D"] > max_screen_size
+        big_points_ws = _scaling_activated(optimizer).max(dim=1).values > 0.1 * extent
+        prune_mask = torch.logical_or(torch.logical_or(prune_mask, big_points_vs), big_points_ws)
+    return prune_points(optimizer, prune_mask, stats)

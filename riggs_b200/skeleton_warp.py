@@ -114,6 +114,64 @@ class _SkinFunction(torch.autograd.Function):
                 None, None)
 
 
+class _SkinTopKFunction(torch.autograd.Function):
+    """LBS by the K nearest bones (cal_nn_weight_skeleton with K > 0, skeleton_warp.py:46-49) on csrc/skin_topk.cu."""
+
+    @staticmethod
+    def forward(ctx, xyz, joints, parents_i32, node_radius_raw, G, node_rot, global_trans, motion_mask, offsets, K):
+        if not xyz.is_cuda:
+            raise _lib.RiggsError("skinning needs CUDA tensors; riggs_b200 has no CPU path")
+        ctx.set_materialize_grads(False)
+        xyz, joints, node_radius_raw, G, node_rot, global_trans = (f32c(t) for t in (
+            xyz, joints, node_radius_raw, G, node_rot, global_trans))
+        motion_mask, offsets = f32c(motion_mask), f32c(offsets)
+        N, J = xyz.shape[0], joints.shape[0]
+        dev = xyz.device
+        d_xyz = torch.empty((N, 3), dtype=torch.float32, device=dev)
+        d_rot = torch.empty((N, 4), dtype=torch.float32, device=dev)
+        nn_w = torch.empty((N, K), dtype=torch.float32, device=dev)
+        nn_idx = torch.empty((N, K), dtype=torch.int64, device=dev)
+        nn_d2 = torch.empty((N, K), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            check(_lib.lib().rg_skin_topk_forward(N, J, int(K), ptr(xyz), ptr(joints), ptr(parents_i32),
+                                                  ptr(node_radius_raw), ptr(G), ptr(node_rot), ptr(global_trans),
+                                                  ptr(motion_mask), ptr(offsets), ptr(d_xyz), ptr(d_rot), ptr(nn_w),
+                                                  ptr(nn_idx), ptr(nn_d2), stream_ptr()), "rg_skin_topk_forward")
+        ctx.save_for_backward(xyz, joints, parents_i32, node_radius_raw, G, node_rot, global_trans, motion_mask, offsets,
+                              nn_idx)
+        ctx.K = int(K)
+        ctx.mark_non_differentiable(nn_w, nn_idx, nn_d2)
+        return d_xyz, d_rot, nn_w, nn_idx, nn_d2
+
+    @staticmethod
+    def backward(ctx, g_dxyz, g_drot, _gw, _gi, _gd):
+        (xyz, joints, parents_i32, node_radius_raw, G, node_rot, global_trans, motion_mask, offsets,
+         nn_idx) = ctx.saved_tensors
+        N, J = xyz.shape[0], joints.shape[0]
+        dev = xyz.device
+        g_dxyz = f32c(g_dxyz) if g_dxyz is not None else None
+        g_drot = f32c(g_drot) if g_drot is not None else None
+        dG = torch.zeros((J, 12), dtype=torch.float32, device=dev)
+        dradius = torch.zeros((J,), dtype=torch.float32, device=dev)
+        dtrans = torch.zeros((3,), dtype=torch.float32, device=dev)
+        need = ctx.needs_input_grad
+        dmask = torch.empty_like(motion_mask) if (motion_mask is not None and need[7]) else None
+        doff = torch.empty_like(offsets) if (offsets is not None and need[8]) else None
+        with torch.cuda.device(dev):
+            check(_lib.lib().rg_skin_topk_backward(N, J, ctx.K, ptr(xyz), ptr(joints), ptr(parents_i32),
+                                                   ptr(node_radius_raw), ptr(G), ptr(node_rot), ptr(global_trans),
+                                                   ptr(motion_mask), ptr(offsets), ptr(nn_idx), ptr(g_dxyz), ptr(g_drot),
+                                                   ptr(dG), ptr(dradius), ptr(dtrans), ptr(dmask), ptr(doff), stream_ptr()),
+                  "rg_skin_topk_backward")
+        return None, None, None, dradius, dG.view_as(G), None, dtrans.view_as(global_trans), dmask, doff, None
+
+
+def skin_topk(xyz, joints, parents_i32, node_radius_raw, G, node_rot, global_trans, motion_mask=None, offsets=None, K=3):
+    """(d_xyz, d_rotation, nn_weight (N,K), nn_idx (N,K) int64 joint numbers, nn_dist2 (N,K))."""
+    return _SkinTopKFunction.apply(xyz.detach(), joints, parents_i32, node_radius_raw, G, node_rot, global_trans,
+                                   motion_mask, offsets, int(K))
+
+
 def fk(local_rot: torch.Tensor, global_trans: torch.Tensor, joints: torch.Tensor, parents_i32: torch.Tensor):
     """Batched forward kinematics.  local_rot (F,J,4) or (J,4); returns G, node_rot, d_nodes with a leading F."""
     single = local_rot.dim() == 2
@@ -210,11 +268,11 @@ class DeformMLP(nn.Module):
 
 
 class SkeletonWarp(nn.Module):
-    """CUDA-backed counterpart of skeleton_utils/skeleton_warp.py:10-172 for K = -1 (all bones)."""
+    """CUDA-backed counterpart of skeleton_utils/skeleton_warp.py:10-172 (K = -1: all bones; K > 0: the K nearest)."""
 
     def __init__(self, joints: torch.Tensor, parent_indices: torch.Tensor, node_radius_raw: Optional[torch.Tensor] = None,
                  hyper_dim: int = 2, use_skinning_weight_mlp: bool = True, use_template_offsets: bool = True,
-                 blend_mode: str = "lbs", device="cuda"):
+                 blend_mode: str = "lbs", device="cuda", K: int = -1):
         super().__init__()
         J = joints.shape[0]
         nodes = torch.cat([joints.float(), 1e-2 * torch.ones(J, hyper_dim)], -1)
@@ -233,7 +291,7 @@ class SkeletonWarp(nn.Module):
         self.pose_net = PoseMLP(1, J * 4).to(device)
         self.skinning_weight_offsets = None
         self.template_offsets = None
-        self.K = -1
+        self.K = int(K)  # -1: all bones (what the reference's scripts run); > 0: the K nearest bones
 
     @property
     def node_radius(self):
@@ -263,10 +321,20 @@ class SkeletonWarp(nn.Module):
             offs = self.detail_net(x, pose)
         self.template_offsets = offs if offs is not None else torch.zeros_like(x)
         mask = motion_mask.reshape(-1) if torch.is_tensor(motion_mask) else None
-        d_xyz, d_rot, w = skin(x, joints, self.parents_i32, self._node_radius, G, node_rot, global_trans, mask, mlp_w,
-                               offs, self.blend_mode, want_weights)
         J = joints.shape[0]
-        nn_idx = torch.arange(1, J, dtype=torch.long, device=x.device).unsqueeze(0).expand(x.shape[0], -1)
+        if self.K > 0:
+            if mlp_w is not None:
+                # the reference gathers the MLP output by joint number (skeleton_warp.py:59), which is out of range for
+                # the last bone: there is no defined behaviour to mirror
+                raise _lib.RiggsError("SkeletonWarp with K > 0 needs use_skinning_weight_mlp = False")
+            if self.blend_mode != 0:
+                raise _lib.RiggsError("SkeletonWarp with K > 0 supports linear blending only")
+            d_xyz, d_rot, w, nn_idx, _ = skin_topk(x, joints, self.parents_i32, self._node_radius, G, node_rot,
+                                                   global_trans, mask, offs, self.K)
+        else:
+            d_xyz, d_rot, w = skin(x, joints, self.parents_i32, self._node_radius, G, node_rot, global_trans, mask, mlp_w,
+                                   offs, self.blend_mode, want_weights)
+            nn_idx = torch.arange(1, J, dtype=torch.long, device=x.device).unsqueeze(0).expand(x.shape[0], -1)
         return {"d_xyz": d_xyz, "d_rotation": d_rot, "d_scaling": torch.zeros(x.shape[0], 3, device=x.device),
                 "d_nodes": d_nodes, "nn_idx": nn_idx, "nn_weight": w, "local_rotation": local_rot,
                 "global_trans": global_trans, "d_opacity": None, "d_color": None}

@@ -325,6 +325,96 @@ def test_prune_points_matches_boolean_indexing():
         assert torch.equal(y, x[keep.cuda()])
 
 
+@pytest.mark.parametrize("isotropic", [False, True])
+def test_densify_clone_split_prune_match_the_reference_sequence(isotropic):
+    """optim.densify_and_clone / densify_and_split / densify_and_prune against the reference's own sequence restated with
+    torch.cat and boolean indexing (scene/gaussian_model.py:393-514): same rows in the same order for every parameter
+    (bit-exact for the copied ones, fp32 rounding for the children's sampled positions), zero Adam moments for new
+    points, moments of surviving points carried along, statistics reset."""
+    from riggs_b200.optim import FusedAdam, build_rotation, densify_and_clone, densify_and_prune, densify_and_split
+    g = torch.Generator().manual_seed(77)
+    P, extent, pd, thr, N = 8_001, 2.0, 0.01, 0.5, 2
+    sc_cols = 1 if isotropic else 3
+    shapes = {"xyz": (P, 3), "f_dc": (P, 1, 3), "f_rest": (P, 15, 3), "opacity": (P, 1), "scaling": (P, sc_cols),
+              "rotation": (P, 4)}
+    init = {k: torch.randn(*s, generator=g) for k, s in shapes.items()}
+    init["scaling"] = torch.log(0.02 * torch.exp(0.7 * torch.randn(P, sc_cols, generator=g)))  # around percent_dense * extent
+    params = {k: v.cuda().requires_grad_(True) for k, v in init.items()}
+    opt = FusedAdam([{"params": [params[k]], "lr": 1e-3, "name": k} for k in shapes], lr=0.0, eps=1e-15)
+    for p in params.values():
+        p.grad = torch.randn_like(p)
+    opt.step()
+    stats = {"xyz_gradient_accum": torch.rand(P, 1, generator=g).cuda(), "denom": torch.ones(P, 1).cuda(),
+             "max_radii2D": torch.rand(P, generator=g).cuda()}
+    grads = stats["xyz_gradient_accum"] / stats["denom"]
+
+    def act(s):
+        return torch.exp(s.repeat(1, 3) if s.shape[1] == 1 else s)
+
+    # ---- clone, the reference's way
+    cur = {k: v.detach().clone() for k, v in params.items()}
+    mom = {k: opt.state[v]["exp_avg"].clone() for k, v in params.items()}
+    sel = (torch.norm(grads, dim=-1) >= thr) & (act(cur["scaling"]).max(1).values <= pd * extent)
+    assert 0 < int(sel.sum()) < P
+    want = {k: torch.cat([v, v[sel]]) for k, v in cur.items()}
+    want_m = {k: torch.cat([v, torch.zeros_like(v[sel])]) for k, v in mom.items()}
+    new, st = densify_and_clone(opt, stats, grads, thr, extent, pd)
+    for k in shapes:
+        assert torch.equal(new[k].detach(), want[k]), k
+        assert torch.equal(opt.state[new[k]]["exp_avg"], want_m[k]), k
+        assert opt.param_groups[list(shapes).index(k)]["params"][0] is new[k]
+    n1 = want["xyz"].shape[0]
+    assert st["xyz_gradient_accum"].shape == (n1, 1) and st["max_radii2D"].shape == (n1,) and float(st["denom"].abs().sum()) == 0
+    # ---- split, the reference's way (grads padded with zeros for the clones)
+    cur, mom = want, want_m
+    padded = torch.zeros(n1, device="cuda")
+    padded[:P] = grads.squeeze()
+    sel = (padded >= thr) & (act(cur["scaling"]).max(1).values > pd * extent)
+    ns = int(sel.sum())
+    assert 0 < ns < n1
+    z = torch.randn(ns * N, 3, generator=g).cuda()
+    stds = act(cur["scaling"])[sel].repeat(N, 1)
+    rots = build_rotation(cur["rotation"][sel]).repeat(N, 1, 1)
+    child = {k: v[sel].repeat(N, *([1] * (v.dim() - 1))) for k, v in cur.items()}
+    child["xyz"] = torch.bmm(rots, (z * stds).unsqueeze(-1)).squeeze(-1) + cur["xyz"][sel].repeat(N, 1)
+    child["scaling"] = torch.log(stds / (0.8 * N))[:, :sc_cols]
+    keep = ~sel
+    want = {k: torch.cat([cur[k][keep], child[k]]) for k in cur}
+    want_m = {k: torch.cat([mom[k][keep], torch.zeros_like(child[k])]) for k in cur}
+    new, st = densify_and_split(opt, st, grads, thr, extent, pd, N=N, samples=z)
+    for k in shapes:
+        if k in ("xyz", "scaling"):
+            assert torch.allclose(new[k].detach(), want[k], rtol=1e-6, atol=1e-6), k
+            assert torch.equal(new[k].detach()[:int(keep.sum())], want[k][:int(keep.sum())]), k
+        else:
+            assert torch.equal(new[k].detach(), want[k]), k
+        assert torch.equal(opt.state[new[k]]["exp_avg"], want_m[k]), k
+    assert st["denom"].shape == (want["xyz"].shape[0], 1)
+    # the optimizer keeps stepping on the regrouped tensors
+    for p in new.values():
+        p.grad = torch.randn_like(p)
+    opt.step()
+    # ---- the whole densify_and_prune: sizes follow the reference's arithmetic
+    n2 = new["xyz"].shape[0]
+    stats2 = {"xyz_gradient_accum": torch.rand(n2, 1, generator=g).cuda(), "denom": torch.ones(n2, 1).cuda(),
+              "max_radii2D": torch.zeros(n2).cuda()}
+    stats2["denom"][::7] = 0  # 0 / 0 -> nan -> 0 as in the reference
+    stats2["xyz_gradient_accum"][::7] = 0
+    cur = {k: v.detach().clone() for k, v in new.items()}
+    gr = stats2["xyz_gradient_accum"] / stats2["denom"]
+    gr[gr.isnan()] = 0
+    big = act(cur["scaling"]).max(1).values > pd * extent
+    hot = torch.norm(gr, dim=-1) >= thr
+    n_clone, n_split = int((hot & ~big).sum()), int((hot & big).sum())
+    op = torch.sigmoid(cur["opacity"]).squeeze()
+    survivors = torch.cat([op[~(hot & big)], op[hot & ~big], op[hot & big].repeat(N)]) >= 0.3
+    gen = torch.Generator(device="cuda").manual_seed(5)
+    newp, news = densify_and_prune(opt, stats2, thr, 0.3, extent, None, pd, generator=gen)
+    assert newp["xyz"].shape[0] == int(survivors.sum()) and n_clone > 0 and n_split > 0
+    assert news["denom"].shape[0] == newp["xyz"].shape[0]
+    assert bool((torch.sigmoid(newp["opacity"].detach()) >= 0.3).all())
+
+
 @pytest.mark.parametrize("N,M,D,K", [(5000, 512, 3, 3), (3001, 1024, 3, 1), (1000, 1000, 3, 9), (777, 1500, 5, 4),
                                      (64, 5, 3, 8), (10, 2500, 8, 16)])
 def test_knn_points_vs_bruteforce(N, M, D, K):

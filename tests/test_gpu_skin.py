@@ -23,7 +23,7 @@ def _load(name):
     return {k: torch.from_numpy(v) for k, v in np.load(os.path.join(GOLD, name + ".npz")).items()}
 
 
-def _run_cuda(d, want_grad=True, blend_mode=0):
+def _run_cuda(d, want_grad=True, blend_mode=0, K=-1):
     from riggs_b200 import skeleton_warp as sw
     dev = "cuda"
     f = lambda k: d[k].float().to(dev) if k in d and d[k] is not None else None
@@ -40,8 +40,13 @@ def _run_cuda(d, want_grad=True, blend_mode=0):
     joints = f("joints")
     par = d["parents"].to(torch.int32).to(dev)
     G, node_rot, d_nodes = sw.fk(q, g, joints, par)
-    d_xyz, d_rot, w = sw.skin(f("xyz"), joints, par, nr, G, node_rot, g, mask, s, o, blend_mode, True)
-    out = dict(d_xyz=d_xyz, d_rotation=d_rot, d_nodes=d_nodes, nn_weight=w, G=G, node_rot=node_rot)
+    if K > 0:
+        d_xyz, d_rot, w, nn_idx, nn_d2 = sw.skin_topk(f("xyz"), joints, par, nr, G, node_rot, g, mask, o, K)
+    else:
+        d_xyz, d_rot, w = sw.skin(f("xyz"), joints, par, nr, G, node_rot, g, mask, s, o, blend_mode, True)
+        nn_idx = nn_d2 = None
+    out = dict(d_xyz=d_xyz, d_rotation=d_rot, d_nodes=d_nodes, nn_weight=w, G=G, node_rot=node_rot, nn_idx=nn_idx,
+               nn_dist2=nn_d2)
     if want_grad:
         loss = (d_xyz * f("cot_xyz")).sum() + (d_rot * f("cot_rot")).sum()
         if "cot_nodes" in d:
@@ -63,6 +68,90 @@ def test_skin_vs_reference_golden(name):
         if k in d:
             a = out[k].detach().cpu().numpy().reshape(-1)
             assert helpers.rel_err(a, d[k].numpy().reshape(-1)) <= GRAD_RTOL, k
+
+
+def _topk_oracle_grads(d, nn_idx, K):
+    """float64 oracle with the selection the kernel made, same cotangents."""
+    dd = lambda k: d[k].double() if k in d else None
+    q = dd("local_rotation").requires_grad_(True)
+    g = dd("global_trans").requires_grad_(True)
+    nr = dd("node_radius_raw").requires_grad_(True)
+    mask = dd("motion_mask").requires_grad_(True)
+    o = dd("template_offsets")
+    if o is not None:
+        o.requires_grad_(True)
+    ref = so.deform_by_pose(dd("xyz"), dd("joints"), d["parents"], nr, q, g, mask, None, o, K=K, nn_idx=nn_idx)
+    ((ref["d_xyz"] * dd("cot_xyz")).sum() + (ref["d_rotation"] * dd("cot_rot")).sum()).backward()
+    return ref, dict(g_local_rotation=q.grad, g_global_trans=g.grad, g_node_radius=nr.grad, g_motion_mask=mask.grad,
+                     g_template_offsets=None if o is None else o.grad)
+
+
+@pytest.mark.parametrize("name", ["skin_f64_j24_k3", "skin_f32_j20_k4"])
+def test_skin_topk_vs_reference_golden(name):
+    """K nearest bones only (cal_nn_weight_skeleton with K > 0).  A point whose nearest point on two bones is their
+    shared joint is exactly equidistant from both, and which of them torch.topk keeps is arbitrary: rows where the
+    kernel selected the same SET of bones as the reference must give the reference's outputs; the gradients are
+    checked over all rows against the float64 oracle (itself pinned to the reference in tests/test_oracle.py) run with
+    the kernel's selection."""
+    d = _load(name)
+    K = d["nn_idx"].shape[1]
+    out = _run_cuda(d, K=K)
+    got_idx = out["nn_idx"].cpu()
+    same = (torch.sort(got_idx, 1).values == torch.sort(d["nn_idx"], 1).values).all(1).numpy()
+    assert same.mean() >= 0.75  # J = 20 random tree: every eighth point sits in a joint-nearest region with a tie at the K-th place
+    for k in ("d_xyz", "d_rotation"):
+        assert helpers.rel_err(out[k].detach().cpu().numpy()[same], d[k].numpy()[same]) <= OUT_RTOL, k
+    assert helpers.rel_err(out["d_nodes"].detach().cpu().numpy(), d["d_nodes"].numpy()) <= OUT_RTOL
+    ref, grads = _topk_oracle_grads(d, got_idx, K)
+    for k in ("d_xyz", "d_rotation", "nn_weight", "nn_dist2"):
+        assert helpers.rel_err(out[k].detach().cpu().numpy(), ref[k].detach().numpy(), floor=1e-7) <= OUT_RTOL, k
+    for k, r in grads.items():
+        if r is not None:
+            a = out[k].detach().cpu().numpy().reshape(-1)
+            assert helpers.rel_err(a, r.numpy().reshape(-1), floor=1e-6) <= GRAD_RTOL, k
+
+
+def test_skin_topk_vs_oracle_and_module():
+    """A larger cloud against the float64 oracle, through SkeletonWarp(K=3).deform_by_pose; K = J - 1 equals all bones."""
+    from riggs_b200 import skeleton_warp as sw
+    sc = synth.make_scene(N=40_000, J=24, width=64, height=64, n_views=1, seed=41, soft_mask=True, with_offsets=True)
+    m = sw.SkeletonWarp(sc.joints, sc.parents, sc.node_radius_raw, use_skinning_weight_mlp=False,
+                        use_template_offsets=False, K=3)
+    pose = {k: v.cuda().requires_grad_(True) for k, v in sc.poses[0].items()}
+    mask = sc.motion_mask.cuda().requires_grad_(True)
+    out = m.deform_by_pose(sc.xyz.cuda(), pose, mask)
+    gen = torch.Generator().manual_seed(42)
+    ca, ch = torch.randn(sc.N, 3, generator=gen), torch.randn(sc.N, 4, generator=gen)
+    ((out["d_xyz"] * ca.cuda()).sum() + (out["d_rotation"] * ch.cuda()).sum()).backward()
+    dd = lambda t: t.double()
+    q = dd(sc.poses[0]["local_rotation"]).requires_grad_(True)
+    g = dd(sc.poses[0]["global_trans"]).requires_grad_(True)
+    nr = dd(sc.node_radius_raw).requires_grad_(True)
+    mk = dd(sc.motion_mask).requires_grad_(True)
+    free = so.deform_by_pose(dd(sc.xyz), dd(sc.joints), sc.parents, nr, q, g, mk, None, None, K=3)
+    # the kernel's distances are the K smallest (up to fp32 rounding), whatever it did with equidistant bones
+    assert helpers.rel_err(out["nn_weight"].sum(1).cpu().numpy(), np.ones(sc.N)) <= 1e-6
+    d2_sorted = torch.sort(free["nn_dist2"].detach(), 1).values.numpy()
+    got_d2 = so.bone_dist2(dd(sc.xyz), dd(sc.joints), sc.parents).gather(1, out["nn_idx"].cpu() - 1)
+    assert np.abs(torch.sort(got_d2, 1).values.numpy() - d2_sorted).max() <= 1e-6 * max(1.0, float(d2_sorted.max()))
+    ref = so.deform_by_pose(dd(sc.xyz), dd(sc.joints), sc.parents, nr, q, g, mk, None, None, K=3, nn_idx=out["nn_idx"].cpu())
+    ((ref["d_xyz"] * dd(ca)).sum() + (ref["d_rotation"] * dd(ch)).sum()).backward()
+    for k in ("d_xyz", "d_rotation", "nn_weight"):
+        assert helpers.rel_err(out[k].detach().cpu().numpy(), ref[k].detach().numpy()) <= OUT_RTOL, k
+    for a, r in ((pose["local_rotation"].grad, q.grad), (pose["global_trans"].grad, g.grad),
+                 (m._node_radius.grad, nr.grad), (mask.grad, mk.grad)):
+        assert helpers.rel_err(a.cpu().numpy().reshape(-1), r.numpy().reshape(-1), floor=1e-6) <= GRAD_RTOL
+    # all bones selected = the K = -1 kernel
+    sc2 = synth.make_scene(N=3000, J=6, width=64, height=64, n_views=1, seed=43)
+    f = lambda t: t.float().cuda()
+    par = sc2.parents.to(torch.int32).cuda()
+    G, node_rot, _ = sw.fk(f(sc2.poses[0]["local_rotation"]), f(sc2.poses[0]["global_trans"]), f(sc2.joints), par)
+    a = sw.skin(f(sc2.xyz), f(sc2.joints), par, f(sc2.node_radius_raw), G, node_rot, f(sc2.poses[0]["global_trans"]))
+    b = sw.skin_topk(f(sc2.xyz), f(sc2.joints), par, f(sc2.node_radius_raw), G, node_rot, f(sc2.poses[0]["global_trans"]), K=5)
+    assert helpers.rel_err(b[0].cpu().numpy(), a[0].cpu().numpy()) <= OUT_RTOL
+    assert helpers.rel_err(b[1].cpu().numpy(), a[1].cpu().numpy()) <= OUT_RTOL
+    with pytest.raises(Exception):
+        sw.skin_topk(f(sc2.xyz), f(sc2.joints), par, f(sc2.node_radius_raw), G, node_rot, f(sc2.poses[0]["global_trans"]), K=6)
 
 
 @pytest.mark.parametrize("cfg", [dict(N=50_000, J=24, seed=31), dict(N=30_011, J=60, seed=32, soft_mask=True,

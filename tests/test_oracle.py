@@ -23,7 +23,8 @@ def _load(name):
 
 
 @pytest.mark.parametrize("name,dt,tol", [("skin_f64_j7", torch.float64, 1e-12), ("skin_f64_j24_plain", torch.float64, 1e-12),
-                                         ("skin_f32_j24", torch.float32, 5e-6), ("skin_f32_j20_plain", torch.float32, 5e-6)])
+                                         ("skin_f32_j24", torch.float32, 5e-6), ("skin_f32_j20_plain", torch.float32, 5e-6),
+                                         ("skin_f64_j24_k3", torch.float64, 1e-12), ("skin_f32_j20_k4", torch.float32, 5e-6)])
 def test_skin_oracle_vs_reference(name, dt, tol):
     d = _load(name)
     f = lambda k: d[k].to(dt) if k in d else None
@@ -36,7 +37,8 @@ def test_skin_oracle_vs_reference(name, dt, tol):
         s = s.clone().requires_grad_(True)
     if o is not None:
         o = o.clone().requires_grad_(True)
-    out = so.deform_by_pose(f("xyz"), f("joints"), d["parents"], nr, q, g, mask, s, o)
+    K = d["nn_idx"].shape[1] if d["nn_idx"].shape[1] < d["joints"].shape[0] - 1 else -1  # K > 0: the nearest bones only
+    out = so.deform_by_pose(f("xyz"), f("joints"), d["parents"], nr, q, g, mask, s, o, K=K)
     ((out["d_xyz"] * f("cot_xyz")).sum() + (out["d_rotation"] * f("cot_rot")).sum()).backward()
     for k in ("d_xyz", "d_rotation", "d_nodes", "nn_weight"):
         assert helpers.rel_err(out[k].detach().numpy(), d[k].numpy()) <= tol, k
