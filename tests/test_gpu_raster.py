@@ -41,11 +41,21 @@ def _run_ref(cin, cots=None):
     return f, st, g
 
 
+# Forward-only cases that stress the binning: 8160 tiles (1080p; groups of eight chunks at the shared-memory limit),
+# rectangles far wider than a warp (large splats: the general and the warp-cooperative paths), more than 4096 chunks'
+# worth of Gaussians (chunks longer than 128), and almost everything culled.
+BINNING_CASES = [
+    ("C4", dict(N=60_000, n_views=1), (0.0, 0.0, 0.0)),
+    ("small", dict(N=30_000, scale_mu=0.12, n_views=1), (0.0, 0.0, 0.0)),
+    ("small", dict(N=600_000, n_views=1, scale_mu=0.004), (0.0, 0.0, 0.0)),
+    ("tiny", dict(cam_radius=0.05, n_views=1), (0.0, 0.0, 0.0)),
+]
+
 needs_ref = pytest.mark.skipif(not ref_cuda.available(), reason="oracle/_ref/libref_riggs.so not built")
 
 
 @needs_ref
-@pytest.mark.parametrize("name,over,bg", CASES)
+@pytest.mark.parametrize("name,over,bg", CASES + BINNING_CASES)
 def test_forward_vs_reference_cuda(name, over, bg):
     scene = synth.make_config(name, **over)
     for view in range(len(scene.cameras)):
