@@ -90,6 +90,20 @@ __global__ void __launch_bounds__(kSortThreads) sort_pass_kernel(const uint32_t*
     const int tile_base = (int)tile * kSortTile;
     const int base = tile_base + warp * (32 * kSortItems);
 
+    // All keys share this digit (typically the top byte: every depth of the frame inside one factor-of-four range and
+    // nothing culled): the pass is the identity permutation -- copy the tile and leave.
+    if (__syncthreads_or(tid < kSortBins && hist[tid] == (uint32_t)P)) {
+#pragma unroll
+        for (int j = 0; j < kSortItems; j++) {
+            const int i = tile_base + j * kSortThreads + tid;
+            if (i < P) {
+                keys_out[i] = keys_in[i];
+                vals_out[i] = vals_in ? vals_in[i] : (uint32_t)i;
+            }
+        }
+        return;
+    }
+
     uint32_t key[kSortItems], val[kSortItems], rank[kSortItems];
 #pragma unroll
     for (int j = 0; j < kSortItems; j++) {

@@ -220,7 +220,8 @@ def test_mark_visible():
 
 
 @pytest.mark.parametrize("P,kind", [(1, "rand"), (31, "ties"), (2048, "rand"), (2049, "ties"), (300000, "depth"),
-                                    (300000, "ties"), (1000003, "rand"), (70000, "equal")])
+                                    (300000, "ties"), (1000003, "rand"), (70000, "equal"), (50000, "onebyte"),
+                                    (300000, "depth_all_visible")])
 def test_depth_sort_is_the_stable_sort(P, kind):
     """csrc/radix_sort.cu against torch's stable sort: ascending key bits, equal keys keep their order (the order
     the reference's stable radix sort over id-ordered emission defines), for ragged sizes, heavy ties, one repeated
@@ -233,6 +234,10 @@ def test_depth_sort_is_the_stable_sort(P, kind):
         keys = torch.randint(0, 50, (P,), generator=g, dtype=torch.int64) * 65537
     elif kind == "equal":
         keys = torch.full((P,), 0x40A00000, dtype=torch.int64)
+    elif kind == "onebyte":  # three of the four digits are the same for every key: those passes are copies
+        keys = torch.randint(0, 256, (P,), generator=g, dtype=torch.int64) * 256 + 0x40A00011
+    elif kind == "depth_all_visible":  # depths inside [2, 8): the top byte is 0x40 for every key
+        keys = (2.5 + 3.0 * torch.rand(P, generator=g)).view(torch.int32).to(torch.int64)
     else:
         d = 2.5 + 3.0 * torch.rand(P, generator=g)
         d[torch.rand(P, generator=g) < 0.1] = float("inf")
