@@ -96,8 +96,10 @@ __global__ void __launch_bounds__(256) tile_count_kernel(int P, int T, int NW, i
             wide &= wide - 1;
             const uint32_t x0 = __shfl_sync(0xffffffffu, rmin.x, o), y0 = __shfl_sync(0xffffffffu, rmin.y, o);
             const uint32_t w = __shfl_sync(0xffffffffu, rmax.x, o) - x0, n = __shfl_sync(0xffffffffu, cnt, o);
+            const float rw = __frcp_rn((float)w);  // s / w through a reciprocal, exact here (see tile_scatter_kernel)
             for (uint32_t s = lane; s < n; s += 32) {
-                const uint32_t t = (y0 + s / w) * (uint32_t)grid_x + x0 + s % w;
+                const uint32_t q = __float2uint_rz(((float)s + 0.5f) * rw);
+                const uint32_t t = (y0 + q) * (uint32_t)grid_x + x0 + (s - q * w);
                 atomicAdd(&h32[t >> 1], 1u << ((t & 1u) * 16u));
             }
         }
@@ -323,9 +325,12 @@ __global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int T, int NW,
                     cur[t] = (uint16_t)(k + 1);
                 }
             } else {
+                // s / w through a reciprocal: (s + 0.5) / w stays 0.5 / w away from every integer, and three roundings of
+                // fp32 move it by less than that for s < 2^21 (a rectangle has at most 65535 tiles)
                 const uint32_t n = w * h;
+                const float rw = __frcp_rn((float)w);
                 for (uint32_t s = lane; s < n; s += 32) {
-                    const uint32_t q = s / w;
+                    const uint32_t q = __float2uint_rz(((float)s + 0.5f) * rw);
                     const uint32_t t = t0 + q * (uint32_t)grid_x + (s - q * w);
                     const uint32_t k = cur[t];
                     const uint32_t c = base[t] + k;
