@@ -5,13 +5,14 @@
 //
 // Why not the library sort: its one-sweep kernel is tuned for huge arrays (384 threads x 23 keys per CTA), so 300 k
 // keys run on 34 of the 148 SMs and every one of the four digit passes is a 12-15 us latency chain (ncu,
-// profiles/r1_w_summary.md).  Here a CTA takes 2048 keys (147 CTAs for 300 k: one per SM):
+// profiles/r1_z_summary.md).  Here a CTA takes 2048 keys (147 CTAs for 300 k: one per SM):
 //   sort_hist_kernel   all four 8-bit digit histograms in one read of the keys;
 //   sort_pass_kernel   one sweep per digit: keys of a tile are ranked per warp with __match_any_sync (lane order =
 //                      key order, so the pass is stable), the digit counts of the tile are chained to the tiles
-//                      before it by decoupled look-back (one thread per digit, 48 predecessors fetched per
-//                      round), and every key goes straight to its final slot.  Tile numbers are handed out by an
-//                      atomic counter, so a tile never waits for one that has not started.
+//                      before it by decoupled look-back (one thread per digit, 32 predecessors fetched per
+//                      round), the tile is laid out sorted in shared memory and written out in runs of consecutive
+//                      addresses.  Tile numbers are handed out by an atomic counter, so a tile never waits for one
+//                      that has not started.  A pass whose digit is the same for every key copies its tile.
 // The first pass takes the ids from the key positions (no iota array is read).
 #include <cstdlib>
 

@@ -73,6 +73,7 @@ class WorkspacePool:
 
 
 _POOL = WorkspacePool()
+_SCREENSPACE_ZEROS: Dict[tuple, torch.Tensor] = {}
 _SIDE: Dict[str, torch.cuda.Stream] = {}
 
 
@@ -278,7 +279,14 @@ def render_skinned(viewpoint_camera, pc, skeleton, pose: Dict[str, torch.Tensor]
     ranks chunk by chunk while it is still computing later chunks (``FlatGrads.all_reduce`` then has nothing left to do).
     Returns the dict of ``render()`` plus ``d_nodes``."""
     xyz = pc._xyz
-    screenspace_points = torch.zeros_like(xyz, requires_grad=True)
+    # the reference's dummy leaf whose .grad receives dL/dmean2D (gaussian_renderer/__init__.py:45-49); its values are
+    # never read, so every call wraps the same zero buffer in a new leaf instead of filling a fresh one
+    key = (xyz.shape[0], str(xyz.device))
+    zeros = _SCREENSPACE_ZEROS.get(key)
+    if zeros is None:
+        _SCREENSPACE_ZEROS.clear()
+        zeros = _SCREENSPACE_ZEROS[key] = torch.zeros_like(xyz, requires_grad=False)
+    screenspace_points = zeros.detach().requires_grad_(True)
     isotropic = pc._scaling.shape[-1] == 1
     cfg = dict(joints=f32c(skeleton.nodes[:, :3].detach()), parents_i32=skeleton.parents_i32,
                width=int(viewpoint_camera.image_width), height=int(viewpoint_camera.image_height),
