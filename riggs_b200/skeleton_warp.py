@@ -291,6 +291,8 @@ class SkeletonWarp(nn.Module):
         self.pose_net = PoseMLP(1, J * 4).to(device)
         self.skinning_weight_offsets = None
         self.template_offsets = None
+        self.cache_skinning_weights = False  # see _weight_mlp_output
+        self._weight_cache = None
         self.K = int(K)  # -1: all bones (what the reference's scripts run); > 0: the K nearest bones
 
     @property
@@ -313,7 +315,7 @@ class SkeletonWarp(nn.Module):
         G, node_rot, d_nodes = fk(local_rot, global_trans, joints, self.parents_i32)
         mlp_w = None
         if self.use_skinning_weight_mlp and self.skinning_weight_mlp is not None:
-            mlp_w = self.skinning_weight_mlp(x[..., :3])
+            mlp_w = self._weight_mlp_output(x)
             self.skinning_weight_offsets = mlp_w
         offs = None
         if self.use_template_offsets and self.detail_net is not None:
@@ -338,6 +340,23 @@ class SkeletonWarp(nn.Module):
         return {"d_xyz": d_xyz, "d_rotation": d_rot, "d_scaling": torch.zeros(x.shape[0], 3, device=x.device),
                 "d_nodes": d_nodes, "nn_idx": nn_idx, "nn_weight": w, "local_rotation": local_rot,
                 "global_trans": global_trans, "d_opacity": None, "d_color": None}
+
+    def _weight_mlp_output(self, x):
+        """sigmoid(WeightMLP(x)) (skeleton_warp.py:56-61).  It depends on the canonical positions only, not on the pose,
+        so with ``cache_skinning_weights = True`` (novel-pose rendering of a frozen model: the 8 x 256 MLP over every
+        Gaussian costs far more than skinning and rasterizing a frame) it is evaluated once per canonical cloud and
+        reused for every frame; the cache is keyed on the tensor's storage, shape and in-place version and is bypassed
+        whenever autograd is recording."""
+        if not self.cache_skinning_weights or torch.is_grad_enabled():
+            return self.skinning_weight_mlp(x[..., :3])
+        key = (x.data_ptr(), tuple(x.shape), x._version, str(x.device))
+        if self._weight_cache is None or self._weight_cache[0] != key:
+            self._weight_cache = (key, self.skinning_weight_mlp(x[..., :3]).detach())
+        return self._weight_cache[1]
+
+    def clear_weight_cache(self):
+        """Call after changing the weight MLP's parameters (e.g. loading a checkpoint) while caching is on."""
+        self._weight_cache = None
 
     def trainable_parameters(self):
         params = [{"params": [self._node_radius], "name": "nodes"},

@@ -92,3 +92,32 @@ def test_skeleton_state_dict_round_trip(tmp_path):
     assert torch.equal(b.nodes, a.nodes) and torch.equal(b._node_radius, a._node_radius)
     for (ka, va), (kb, vb) in zip(a.state_dict().items(), b.state_dict().items()):
         assert ka == kb and torch.equal(va, vb), ka
+
+
+def test_weight_mlp_cache_is_keyed_on_the_cloud():
+    """SkeletonWarp._weight_mlp_output: one evaluation per canonical cloud under no_grad, none cached under autograd."""
+    from riggs_b200.skeleton_warp import SkeletonWarp
+    m = SkeletonWarp(torch.randn(5, 3), torch.tensor([-1, 0, 1, 1, 0]), device="cpu")
+    calls = []
+    orig = m.skinning_weight_mlp.forward
+    m.skinning_weight_mlp.forward = lambda x: (calls.append(1), orig(x))[1]
+    x = torch.randn(40, 3)
+    m.cache_skinning_weights = True
+    with torch.no_grad():
+        a = m._weight_mlp_output(x)
+        b = m._weight_mlp_output(x)
+        assert len(calls) == 1 and a is b
+        x.add_(1.0)  # in-place change of the cloud: the cache must not be used
+        c = m._weight_mlp_output(x)
+        assert len(calls) == 2 and not torch.equal(a, c)
+        m.clear_weight_cache()
+        m._weight_mlp_output(x)
+        assert len(calls) == 3
+    m._weight_mlp_output(x)  # autograd on: evaluated, not cached
+    m._weight_mlp_output(x)
+    assert len(calls) == 5
+    m.cache_skinning_weights = False
+    with torch.no_grad():
+        m._weight_mlp_output(x)
+        m._weight_mlp_output(x)
+    assert len(calls) == 7
