@@ -132,8 +132,8 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendB
 
     const float T_final = inside ? (1 - a.alphas[pix_id]) : 0;
     float T = T_final;
-    float accum_rec[3] = {0, 0, 0}, dL_dpixel[3] = {0, 0, 0};
-    float accum_depth_rec = 0, dL_dpixel_depth = 0, accum_alpha_rec = 0, dL_dalpha = 0;
+    float S_rec[3] = {0, 0, 0}, dL_dpixel[3] = {0, 0, 0};  // S_*: un-normalised sums over the instances behind
+    float S_depth = 0, dL_dpixel_depth = 0, S_alpha = 0, dL_dalpha = 0;
     if (inside) {
         const size_t HW = (size_t)a.H * a.W;
 #pragma unroll
@@ -142,7 +142,6 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendB
         if (a.dL_dalphas) dL_dalpha = a.dL_dalphas[pix_id];
     }
     ch.cpix[lane] = {dL_dpixel[0], dL_dpixel[1], dL_dpixel[2], dL_dpixel_depth};
-    float last_alpha = 0, last_color[3] = {0, 0, 0}, last_depth = 0;
     const float ddelx_dx = 0.5 * a.W;
     const float ddely_dy = 0.5 * a.H;
     const float bg_dot_dpixel = a.bg[0] * dL_dpixel[0] + a.bg[1] * dL_dpixel[1] + a.bg[2] * dL_dpixel[2];
@@ -162,6 +161,16 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendB
     for (int g = 0; g < n_groups; g++) {
         const int cnt = walk.next(g, st);
         if (prof) n_list += cnt;
+        // The loop below evaluates U slots per iteration; the slots behind the last survivor hold whatever an earlier
+        // group left there (or nothing yet), and the suffix sums multiply colours by a zero weight instead of selecting:
+        // make those slots finite.
+        if (cnt % U) {
+            if (lane < U - cnt % U) {
+                const float4 z = {0.f, 0.f, 0.f, 0.f};
+                st.xyts[cnt + lane] = z; st.co[cnt + lane] = z; st.rgbd[cnt + lane] = z;
+            }
+            __syncwarp();
+        }
         // Straight-line code without per-lane branches, U instances per iteration: the warps of the heavy blocks are
         // the kernel's critical path and what bounds them is the latency of their own dependent chain.  A pair the
         // reference skips takes alpha = 0 -- T / (1 - 0) is exact -- and leaves the recurrence state untouched.
@@ -200,24 +209,22 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendB
                 inv_1ma = fmaf(inv_1ma, fmaf(-one_ma, inv_1ma, 1.f), inv_1ma);
                 T = T * inv_1ma;
                 w[u] = a_eff * T;  // dchannel_dcolor
-                const float c3[3] = {col[u].x, col[u].y, col[u].z};
+                // The reference carries "what lies behind the instance", normalised by the transmittance behind it, through
+                // acc = last_alpha last_c + (1 - last_alpha) acc (backward.cu:543-567).  Here the UN-normalised suffix sums
+                // S = sum over the instances behind of value * alpha * T are carried instead: T (c - acc) = c T - S / (1 - alpha),
+                // and S += c alpha T is a no-op for a skipped pair (alpha = 0) without any select.  Same value, one rounding
+                // order apart (tolerance 1e-4).
                 float dL_dopa = 0.0f;
 #pragma unroll
                 for (int k = 0; k < 3; k++) {
-                    const float acc = last_alpha * last_color[k] + (1.f - last_alpha) * accum_rec[k];
-                    accum_rec[k] = on ? acc : accum_rec[k];
-                    last_color[k] = on ? c3[k] : last_color[k];
-                    dL_dopa += (c3[k] - acc) * dL_dpixel[k];
+                    const float ck = k == 0 ? col[u].x : (k == 1 ? col[u].y : col[u].z);
+                    dL_dopa = fmaf(fmaf(-S_rec[k], inv_1ma, ck * T), dL_dpixel[k], dL_dopa);
+                    S_rec[k] = fmaf(ck, w[u], S_rec[k]);
                 }
-                const float accd = last_alpha * last_depth + (1.f - last_alpha) * accum_depth_rec;
-                accum_depth_rec = on ? accd : accum_depth_rec;
-                last_depth = on ? col[u].w : last_depth;
-                dL_dopa += (col[u].w - accd) * dL_dpixel_depth;
-                const float acca = last_alpha + (1.f - last_alpha) * accum_alpha_rec;
-                accum_alpha_rec = on ? acca : accum_alpha_rec;
-                dL_dopa += (1 - acca) * dL_dalpha;
-                dL_dopa *= T;
-                last_alpha = on ? alpha[u] : last_alpha;
+                dL_dopa = fmaf(fmaf(-S_depth, inv_1ma, col[u].w * T), dL_dpixel_depth, dL_dopa);
+                S_depth = fmaf(col[u].w, w[u], S_depth);
+                dL_dopa = fmaf(fmaf(-S_alpha, inv_1ma, T), dL_dalpha, dL_dopa);
+                S_alpha += w[u];
                 dL_dopa += (-T_final * inv_1ma) * bg_dot_dpixel;
                 q[u] = on ? G[u] * dL_dopa : 0.f;
             }
