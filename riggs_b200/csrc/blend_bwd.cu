@@ -6,8 +6,8 @@
 //    ITS deepest last contributor (the reference skips the others one by one, backward.cu:517-519), and of those only
 //    the instances the forward blend marked as able to reach the block (MaskWalker of blend_common.cuh reads the
 //    block's survivor bitmap: no culling test is repeated, records are fetched for survivors only);
-//  * phase A, one pixel per lane: the reference's recurrence (T, the accumulated colour/depth/alpha behind the
-//    instance) in the reference's expression order.  Of the ten per-pair gradient terms only TWO scalars depend on
+//  * phase A, one pixel per lane: the reference's recurrence for T; what lies behind the instance (accumulated
+//    colour / depth / alpha) is carried as un-normalised suffix sums (see the loop).  Of the ten per-pair gradient terms only TWO scalars depend on
 //    that recurrence:  Q = G dL/d(alpha)  and  W = alpha T ; the rest is geometry of the pair and constants of the
 //    pixel.  Q and W go to a 32 x 32 (pixel x instance) tile in shared memory;
 //  * phase B, one INSTANCE per lane, every 32 instances: the ten sums over the block's pixels are linear in Q and W,
