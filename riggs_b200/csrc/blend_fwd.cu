@@ -63,6 +63,14 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_forward_kernel(BlendFw
         // Straight-line code, no per-lane branches: the warp that owns a heavy block is alone on the kernel's critical
         // path, and what bounds it is the latency of its own dependent chain, not issue slots.  Entries that the
         // reference would skip take alpha = 0 (T * (1 - 0) and C + 0 are exact), so only T -> test -> select is serial.
+        // four slots are evaluated per iteration; make the ones behind the last survivor finite (zero weight, no select)
+        if (cnt & 3) {
+            if (lane < 4 - (cnt & 3)) {
+                const float4 z = {0.f, 0.f, 0.f, 0.f};
+                st.xyts[cnt + lane] = z; st.co[cnt + lane] = z; st.rgbd[cnt + lane] = z;
+            }
+            __syncwarp();
+        }
         const int n_it = (cnt + 3) >> 2;
         for (int it = 0; it < n_it; it++) {
             const int l = it * 4;
@@ -90,14 +98,13 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_forward_kernel(BlendFw
                 const bool stop = live && test_T < 0.0001f;
                 const bool add = live && !stop;
                 done = done || stop;
+                // a skipped entry has weight 0: its (finite) colour needs no select of its own
                 const float wa = add ? alpha[u] : 0.f;
-                const float cx = add ? c[u].x : 0.f, cy = add ? c[u].y : 0.f, cz = add ? c[u].z : 0.f;
-                const float cd = add ? c[u].w : 0.f;
-                C0 = C0 + cx * wa * T;
-                C1 = C1 + cy * wa * T;
-                C2 = C2 + cz * wa * T;
+                C0 = C0 + c[u].x * wa * T;
+                C1 = C1 + c[u].y * wa * T;
+                C2 = C2 + c[u].z * wa * T;
                 weight = weight + wa * T;
-                D = D + cd * wa * T;
+                D = D + c[u].w * wa * T;
                 // 1-based position in the tile's range, as the reference counts
                 last_contributor = add ? (uint32_t)pos[u] + 1 : last_contributor;
                 T = add ? test_T : T;
