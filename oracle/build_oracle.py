@@ -31,13 +31,16 @@ def _newer(target, sources):
     return any(os.path.getmtime(s) > t for s in sources)
 
 
-def build_cpu_oracle(verbose=False):
+def build_cpu_oracle(verbose=False, f64=False):
+    """f64=True: the same source with -DORC_DOUBLE (every expression in double) -> liboracle_f64.so."""
     src = os.path.join(HERE, "raster_oracle.c")
     out_dir = os.path.join(HERE, "_build")
     os.makedirs(out_dir, exist_ok=True)
-    out = os.path.join(out_dir, "liboracle.so")
+    out = os.path.join(out_dir, "liboracle_f64.so" if f64 else "liboracle.so")
     if _newer(out, [src]):
         cmd = ["gcc", "-O2", "-ffp-contract=off", "-fopenmp", "-shared", "-fPIC", "-o", out, src, "-lm"]
+        if f64:
+            cmd.insert(1, "-DORC_DOUBLE")
         if verbose:
             print(" ".join(cmd))
         subprocess.check_call(cmd)
@@ -81,4 +84,5 @@ def build_ref(verbose=False):
 
 if __name__ == "__main__":
     print(build_cpu_oracle(verbose=True))
+    print(build_cpu_oracle(verbose=True, f64=True))
     print(build_ref(verbose=True))

@@ -11,49 +11,59 @@ import numpy as np
 
 from . import build_oracle
 
-_lib = None
+_libs = {}
 
 
-def lib():
-    global _lib
-    if _lib is None:
-        _lib = C.CDLL(build_oracle.build_cpu_oracle())
-        _lib.orc_scan.restype = C.c_int64
-        _lib.orc_higher_msb.restype = C.c_uint32
-        _lib.orc_higher_msb.argtypes = [C.c_uint32]
-    return _lib
+def lib(f64: bool = False):
+    """f64=False: liboracle.so (fp32, the restatement proper); f64=True: the same source built with -DORC_DOUBLE,
+    every expression evaluated in double on double arrays (the arbiter for ill-conditioned gradients)."""
+    L = _libs.get(bool(f64))
+    if L is None:
+        L = C.CDLL(build_oracle.build_cpu_oracle(f64=f64))
+        L.orc_scan.restype = C.c_int64
+        L.orc_higher_msb.restype = C.c_uint32
+        L.orc_higher_msb.argtypes = [C.c_uint32]
+        assert L.orc_real_bytes() == (8 if f64 else 4)
+        _libs[bool(f64)] = L
+    return L
 
 
 def _p(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
 
-def _f(a):
-    return None if a is None else np.ascontiguousarray(a, dtype=np.float32)
+def _f(a, f64: bool = False):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.float64 if f64 else np.float32)
+
+
+def _real(f64):
+    return (np.float64, C.c_double) if f64 else (np.float32, C.c_float)
 
 
 def forward(means3D, opacities, view, proj, campos, W, H, tanfovx, tanfovy, bg, shs=None, colors_precomp=None,
-            scales=None, rotations=None, cov3D_precomp=None, scale_modifier=1.0, degree=3, geom_override=None):
+            scales=None, rotations=None, cov3D_precomp=None, scale_modifier=1.0, degree=3, geom_override=None, f64=False):
     """Whole forward pipeline on the CPU.  Returns a dict with every intermediate the gates compare.
 
     geom_override: dict with radii/means2D/depths/tiles_touched/(conic_opacity, rgb) taken from another
     implementation (e.g. the GPU) -- the integer binning stages then run on exactly those floats."""
-    L = lib()
+    L = lib(f64)
+    ft, cf = _real(f64)
+    _f = lambda a: globals()["_f"](a, f64)  # noqa: E731
     P = means3D.shape[0]
     means3D, opacities, view, proj, campos, bg = map(_f, (means3D, opacities, view, proj, campos, bg))
     shs, colors_precomp, scales, rotations, cov3D_precomp = map(_f, (shs, colors_precomp, scales, rotations, cov3D_precomp))
     M = shs.shape[1] if shs is not None else 0
     radii = np.zeros(P, np.int32)
-    means2D = np.zeros((P, 2), np.float32)
-    depths = np.zeros(P, np.float32)
-    cov3D = np.zeros((P, 6), np.float32)
-    rgb = np.zeros((P, 3), np.float32)
-    conic_opacity = np.zeros((P, 4), np.float32)
+    means2D = np.zeros((P, 2), ft)
+    depths = np.zeros(P, ft)
+    cov3D = np.zeros((P, 6), ft)
+    rgb = np.zeros((P, 3), ft)
+    conic_opacity = np.zeros((P, 4), ft)
     tiles = np.zeros(P, np.uint32)
     clamped = np.zeros((P, 3), np.uint8)
-    L.orc_preprocess(P, degree, M, _p(means3D), _p(scales), C.c_float(scale_modifier), _p(rotations), _p(opacities),
+    L.orc_preprocess(P, degree, M, _p(means3D), _p(scales), cf(scale_modifier), _p(rotations), _p(opacities),
                      _p(shs), _p(cov3D_precomp), _p(colors_precomp), _p(view), _p(proj), _p(campos), W, H,
-                     C.c_float(tanfovx), C.c_float(tanfovy), _p(radii), _p(means2D), _p(depths), _p(cov3D), _p(rgb),
+                     cf(tanfovx), cf(tanfovy), _p(radii), _p(means2D), _p(depths), _p(cov3D), _p(rgb),
                      _p(conic_opacity), _p(tiles), _p(clamped))
     if colors_precomp is not None:
         rgb = colors_precomp.copy()
@@ -62,16 +72,16 @@ def forward(means3D, opacities, view, proj, campos, W, H, tanfovx, tanfovy, bg, 
     if geom_override is not None:
         for k, v in geom_override.items():
             out[k] = np.ascontiguousarray(v)
-    out.update(binning(out["radii"], out["means2D"], out["depths"], out["tiles_touched"], W, H))
-    out.update(blend_forward(out, W, H, bg))
+    out.update(binning(out["radii"], out["means2D"], out["depths"], out["tiles_touched"], W, H, f64=f64))
+    out.update(blend_forward(out, W, H, bg, f64=f64))
     return out
 
 
-def binning(radii, means2D, depths, tiles, W, H):
-    L = lib()
+def binning(radii, means2D, depths, tiles, W, H, f64=False):
+    L = lib(f64)
     P = radii.shape[0]
     radii = np.ascontiguousarray(radii, np.int32)
-    means2D, depths = _f(means2D), _f(depths)
+    means2D, depths = _f(means2D, f64), _f(depths, f64)
     tiles = np.ascontiguousarray(tiles, np.uint32)
     offsets = np.zeros(P, np.uint32)
     R = int(L.orc_scan(P, _p(tiles), _p(offsets)))
@@ -89,11 +99,13 @@ def binning(radii, means2D, depths, tiles, W, H):
                 point_list=vals, ranges=ranges)
 
 
-def blend_forward(st, W, H, bg):
-    L = lib()
-    color = np.zeros((3, H, W), np.float32)
-    depth = np.zeros((1, H, W), np.float32)
-    alpha = np.zeros((1, H, W), np.float32)
+def blend_forward(st, W, H, bg, f64=False):
+    L = lib(f64)
+    ft, _ = _real(f64)
+    _f = lambda a: globals()["_f"](a, f64)  # noqa: E731
+    color = np.zeros((3, H, W), ft)
+    depth = np.zeros((1, H, W), ft)
+    alpha = np.zeros((1, H, W), ft)
     n_contrib = np.zeros((H, W), np.uint32)
     bg = _f(bg)
     L.orc_blend_forward(W, H, _p(st["ranges"]), _p(st["point_list"]), _p(_f(st["means2D"])), _p(_f(st["rgb"])),
@@ -103,9 +115,12 @@ def blend_forward(st, W, H, bg):
 
 
 def backward(st, means3D, view, proj, campos, W, H, tanfovx, tanfovy, bg, dL_dcolor, dL_ddepth, dL_dalpha, shs=None,
-             colors_precomp=None, scales=None, rotations=None, cov3D_precomp=None, scale_modifier=1.0, degree=3):
+             colors_precomp=None, scales=None, rotations=None, cov3D_precomp=None, scale_modifier=1.0, degree=3,
+             f64=False):
     """Backward pipeline on the CPU from the forward state dict `st`."""
-    L = lib()
+    L = lib(f64)
+    ft, cf = _real(f64)
+    _f = lambda a: globals()["_f"](a, f64)  # noqa: E731
     P = means3D.shape[0]
     means3D, view, proj, campos, bg = map(_f, (means3D, view, proj, campos, bg))
     shs, scales, rotations = map(_f, (shs, scales, rotations))
@@ -121,20 +136,20 @@ def backward(st, means3D, view, proj, campos, W, H, tanfovx, tanfovy, bg, dL_dco
                          _p(_f(st["conic_opacity"])), _p(colors), _p(_f(st["depths"])), _p(_f(st["alpha"])),
                          _p(np.ascontiguousarray(st["n_contrib"], np.uint32)), _p(gc), _p(gd), _p(ga), _p(dmean2D),
                          _p(dconic), _p(dopacity), _p(dcolor), _p(ddepth))
-    f_dmean2D, f_dconic, f_dcolor, f_ddepth = (x.astype(np.float32) for x in (dmean2D, dconic, dcolor, ddepth))
-    dmean3D = np.zeros((P, 3), np.float32)
-    dcov3D = np.zeros((P, 6), np.float32)
-    dsh = np.zeros((P, M, 3), np.float32) if shs is not None else None
-    dscale = np.zeros((P, 3), np.float32) if scales is not None else None
-    drot = np.zeros((P, 4), np.float32) if scales is not None else None
+    f_dmean2D, f_dconic, f_dcolor, f_ddepth = (x.astype(ft) for x in (dmean2D, dconic, dcolor, ddepth))
+    dmean3D = np.zeros((P, 3), ft)
+    dcov3D = np.zeros((P, 6), ft)
+    dsh = np.zeros((P, M, 3), ft) if shs is not None else None
+    dscale = np.zeros((P, 3), ft) if scales is not None else None
+    drot = np.zeros((P, 4), ft) if scales is not None else None
     cov3D = _f(st["cov3D"])
     clamped = np.ascontiguousarray(st["clamped"], np.uint8)
     L.orc_preprocess_backward(P, degree, M, _p(means3D), _p(np.ascontiguousarray(st["radii"], np.int32)), _p(shs),
-                              _p(clamped), _p(scales), _p(rotations), C.c_float(scale_modifier), _p(cov3D), _p(view),
-                              _p(proj), _p(campos), W, H, C.c_float(tanfovx), C.c_float(tanfovy), _p(f_dmean2D),
+                              _p(clamped), _p(scales), _p(rotations), cf(scale_modifier), _p(cov3D), _p(view),
+                              _p(proj), _p(campos), W, H, cf(tanfovx), cf(tanfovy), _p(f_dmean2D),
                               _p(f_dconic), _p(f_dcolor), _p(f_ddepth), _p(dmean3D), _p(dcov3D), _p(dsh), _p(dscale),
                               _p(drot))
-    return dict(dmean2D=f_dmean2D, dconic=f_dconic, dopacity=dopacity.astype(np.float32), dcolor=f_dcolor,
+    return dict(dmean2D=f_dmean2D, dconic=f_dconic, dopacity=dopacity.astype(ft), dcolor=f_dcolor,
                 ddepth=f_ddepth, dmean3D=dmean3D, dcov3D=dcov3D, dsh=dsh, dscale=dscale, drot=drot)
 
 

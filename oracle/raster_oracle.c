@@ -13,6 +13,9 @@
  * of that same compiled reference captured on a B200 by tests/golden/make_ref_cuda_golden.py.
  *
  * Build: gcc -O2 -ffp-contract=off -fopenmp -shared -fPIC (see oracle/build_oracle.py).
+ * A second build with -DORC_DOUBLE (liboracle_f64.so) evaluates the same expressions in double on
+ * double arrays: the arbiter when two fp32 implementations disagree about an ill-conditioned
+ * gradient.
  * -ffp-contract=off keeps every float expression exactly as written; the reference is
  * compiled by nvcc with FMA contraction, so float results agree to rounding, not bitwise.
  * Discrete outputs derived from floats (radius, tile rectangle) can therefore differ for
@@ -29,19 +32,36 @@
 #include <string.h>
 #include <float.h>
 
+#ifdef ORC_DOUBLE
+typedef double real;
+#define R_SQRT sqrt
+#define R_FMAX fmax
+#define R_FMIN fmin
+#define R_CEIL ceil
+#define R_EXP exp
+#else
+typedef float real;
+#define R_SQRT sqrtf
+#define R_FMAX fmaxf
+#define R_FMIN fminf
+#define R_CEIL ceilf
+#define R_EXP expf
+#endif
+int orc_real_bytes(void) { return (int)sizeof(real); }
+
 #define TILE 16 /* dgr/cuda_rasterizer/config.h:15-16 */
 
 /* SH basis constants, dgr/cuda_rasterizer/auxiliary.h:22-39 */
-static const float C0 = 0.28209479177387814f;
-static const float C1 = 0.4886025119029199f;
-static const float C2[5] = {1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f,
+static const real C0 = 0.28209479177387814f;
+static const real C1 = 0.4886025119029199f;
+static const real C2[5] = {1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f,
                             -1.0925484305920792f, 0.5462742152960396f};
-static const float C3[7] = {-0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f,
+static const real C3[7] = {-0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f,
                             0.3731763325901154f, -0.4570457994644658f, 1.445305721320277f,
                             -0.5900435899266435f};
 
 /* column-major 3x3, m[c][r], the layout GLM uses (type_mat3x3.inl:486-519) */
-typedef struct { float m[3][3]; } M3;
+typedef struct { real m[3][3]; } M3;
 
 static M3 m3_mul(const M3* a, const M3* b) {
     M3 r;
@@ -58,26 +78,26 @@ static M3 m3_t(const M3* a) {
 }
 
 /* auxiliary.h:58-77 */
-static void xform4x3(const float* p, const float* m, float* o) {
+static void xform4x3(const real* p, const real* m, real* o) {
     o[0] = m[0] * p[0] + m[4] * p[1] + m[8] * p[2] + m[12];
     o[1] = m[1] * p[0] + m[5] * p[1] + m[9] * p[2] + m[13];
     o[2] = m[2] * p[0] + m[6] * p[1] + m[10] * p[2] + m[14];
 }
-static void xform4x4(const float* p, const float* m, float* o) {
+static void xform4x4(const real* p, const real* m, real* o) {
     o[0] = m[0] * p[0] + m[4] * p[1] + m[8] * p[2] + m[12];
     o[1] = m[1] * p[0] + m[5] * p[1] + m[9] * p[2] + m[13];
     o[2] = m[2] * p[0] + m[6] * p[1] + m[10] * p[2] + m[14];
     o[3] = m[3] * p[0] + m[7] * p[1] + m[11] * p[2] + m[15];
 }
 
-/* auxiliary.h:41-44 -- evaluated in double, then rounded to float */
-static float ndc2pix(float v, int S) { return (float)(((v + 1.0) * S - 1.0) * 0.5); }
+/* auxiliary.h:41-44 -- evaluated in double, then rounded to real */
+static real ndc2pix(real v, int S) { return (real)(((v + 1.0) * S - 1.0) * 0.5); }
 
 static int imin(int a, int b) { return a < b ? a : b; }
 static int imax(int a, int b) { return a > b ? a : b; }
 
 /* auxiliary.h:46-56 */
-static void get_rect(float px, float py, int max_radius, int gx, int gy, uint32_t* mn, uint32_t* mx) {
+static void get_rect(real px, real py, int max_radius, int gx, int gy, uint32_t* mn, uint32_t* mx) {
     mn[0] = (uint32_t)imin(gx, imax(0, (int)((px - max_radius) / TILE)));
     mn[1] = (uint32_t)imin(gy, imax(0, (int)((py - max_radius) / TILE)));
     mx[0] = (uint32_t)imin(gx, imax(0, (int)((px + max_radius + TILE - 1) / TILE)));
@@ -85,13 +105,13 @@ static void get_rect(float px, float py, int max_radius, int gx, int gy, uint32_
 }
 
 /* dgr/cuda_rasterizer/forward.cu:118-152 (quaternion used as given, not normalised) */
-static void cov3d_from_scale_rot(const float* s, float mod, const float* q, float* cov) {
+static void cov3d_from_scale_rot(const real* s, real mod, const real* q, real* cov) {
     M3 S;
     memset(&S, 0, sizeof S);
     S.m[0][0] = mod * s[0];
     S.m[1][1] = mod * s[1];
     S.m[2][2] = mod * s[2];
-    float r = q[0], x = q[1], y = q[2], z = q[3];
+    real r = q[0], x = q[1], y = q[2], z = q[3];
     M3 R = {{{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
              {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
              {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}}};
@@ -103,14 +123,14 @@ static void cov3d_from_scale_rot(const float* s, float mod, const float* q, floa
 }
 
 /* forward.cu:74-113; also returns T (for the backward) when Tout != NULL */
-static void cov2d(const float* mean, float fx, float fy, float tfx, float tfy, const float* c3,
-                  const float* view, float* out3, M3* Tout, float* tout, float* gmul) {
-    float t[3];
+static void cov2d(const real* mean, real fx, real fy, real tfx, real tfy, const real* c3,
+                  const real* view, real* out3, M3* Tout, real* tout, real* gmul) {
+    real t[3];
     xform4x3(mean, view, t);
-    const float limx = 1.3f * tfx, limy = 1.3f * tfy;
-    const float txtz = t[0] / t[2], tytz = t[1] / t[2];
-    t[0] = fminf(limx, fmaxf(-limx, txtz)) * t[2];
-    t[1] = fminf(limy, fmaxf(-limy, tytz)) * t[2];
+    const real limx = 1.3f * tfx, limy = 1.3f * tfy;
+    const real txtz = t[0] / t[2], tytz = t[1] / t[2];
+    t[0] = R_FMIN(limx, R_FMAX(-limx, txtz)) * t[2];
+    t[1] = R_FMIN(limy, R_FMAX(-limy, tytz)) * t[2];
     if (gmul) {
         gmul[0] = (txtz < -limx || txtz > limx) ? 0.f : 1.f;
         gmul[1] = (tytz < -limy || tytz > limy) ? 0.f : 1.f;
@@ -132,19 +152,19 @@ static void cov2d(const float* mean, float fx, float fy, float tfx, float tfy, c
 }
 
 /* forward.cu:20-71 */
-static void sh_to_rgb(int deg, int M, const float* pos, const float* campos, const float* sh,
-                      float* rgb, uint8_t* clamped) {
-    float d[3] = {pos[0] - campos[0], pos[1] - campos[1], pos[2] - campos[2]};
-    float len = sqrtf(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
-    float x = d[0] / len, y = d[1] / len, z = d[2] / len;
+static void sh_to_rgb(int deg, int M, const real* pos, const real* campos, const real* sh,
+                      real* rgb, uint8_t* clamped) {
+    real d[3] = {pos[0] - campos[0], pos[1] - campos[1], pos[2] - campos[2]};
+    real len = R_SQRT(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+    real x = d[0] / len, y = d[1] / len, z = d[2] / len;
     (void)M;
     for (int c = 0; c < 3; c++) {
 #define SH(k) sh[(k) * 3 + c]
-        float r = C0 * SH(0);
+        real r = C0 * SH(0);
         if (deg > 0) {
             r = r - C1 * y * SH(1) + C1 * z * SH(2) - C1 * x * SH(3);
             if (deg > 1) {
-                float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+                real xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
                 r = r + C2[0] * xy * SH(4) + C2[1] * yz * SH(5) + C2[2] * (2.0f * zz - xx - yy) * SH(6) +
                     C2[3] * xz * SH(7) + C2[4] * (xx - yy) * SH(8);
                 if (deg > 2) {
@@ -165,13 +185,13 @@ static void sh_to_rgb(int deg, int M, const float* pos, const float* campos, con
 
 /* forward.cu:155-256.  Optional pointers (NULL selects the other path): shs | colors_precomp,
  * (scales, rots) | cov3D_precomp.  Outputs are fully written (zeros for culled Gaussians). */
-void orc_preprocess(int P, int D, int M, const float* means3D, const float* scales, float scale_mod,
-                    const float* rots, const float* opac, const float* shs, const float* cov3D_precomp,
-                    const float* colors_precomp, const float* view, const float* proj, const float* campos,
-                    int W, int H, float tfx, float tfy, int* radii, float* means2D, float* depths,
-                    float* cov3D, float* rgb, float* conic_opacity, uint32_t* tiles_touched,
+void orc_preprocess(int P, int D, int M, const real* means3D, const real* scales, real scale_mod,
+                    const real* rots, const real* opac, const real* shs, const real* cov3D_precomp,
+                    const real* colors_precomp, const real* view, const real* proj, const real* campos,
+                    int W, int H, real tfx, real tfy, int* radii, real* means2D, real* depths,
+                    real* cov3D, real* rgb, real* conic_opacity, uint32_t* tiles_touched,
                     uint8_t* clamped) {
-    const float fy = H / (2.0f * tfy), fx = W / (2.0f * tfx); /* rasterizer_impl.cu:223-224 */
+    const real fy = H / (2.0f * tfy), fx = W / (2.0f * tfx); /* rasterizer_impl.cu:223-224 */
     const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
 #pragma omp parallel for schedule(static)
     for (int i = 0; i < P; i++) {
@@ -182,27 +202,27 @@ void orc_preprocess(int P, int D, int M, const float* means3D, const float* scal
         for (int k = 0; k < 4; k++) conic_opacity[4 * i + k] = 0.f;
         for (int k = 0; k < 3; k++) { rgb[3 * i + k] = 0.f; clamped[3 * i + k] = 0; }
         for (int k = 0; k < 6; k++) cov3D[6 * i + k] = 0.f;
-        const float* p = means3D + 3 * i;
-        float pv[3], ph[4];
+        const real* p = means3D + 3 * i;
+        real pv[3], ph[4];
         xform4x3(p, view, pv);
         if (pv[2] <= 0.2f) continue; /* auxiliary.h:154 */
         xform4x4(p, proj, ph);
-        float pw = 1.0f / (ph[3] + 0.0000001f);
-        float pp[3] = {ph[0] * pw, ph[1] * pw, ph[2] * pw};
-        const float* c3;
+        real pw = 1.0f / (ph[3] + 0.0000001f);
+        real pp[3] = {ph[0] * pw, ph[1] * pw, ph[2] * pw};
+        const real* c3;
         if (cov3D_precomp) c3 = cov3D_precomp + 6 * i;
         else { cov3d_from_scale_rot(scales + 3 * i, scale_mod, rots + 4 * i, cov3D + 6 * i); c3 = cov3D + 6 * i; }
-        float cv[3];
+        real cv[3];
         cov2d(p, fx, fy, tfx, tfy, c3, view, cv, NULL, NULL, NULL);
-        float det = cv[0] * cv[2] - cv[1] * cv[1];
+        real det = cv[0] * cv[2] - cv[1] * cv[1];
         if (det == 0.0f) continue;
-        float det_inv = 1.f / det;
-        float conic[3] = {cv[2] * det_inv, -cv[1] * det_inv, cv[0] * det_inv};
-        float mid = 0.5f * (cv[0] + cv[2]);
-        float l1 = mid + sqrtf(fmaxf(0.1f, mid * mid - det));
-        float l2 = mid - sqrtf(fmaxf(0.1f, mid * mid - det));
-        float my_radius = ceilf(3.f * sqrtf(fmaxf(l1, l2)));
-        float px = ndc2pix(pp[0], W), py = ndc2pix(pp[1], H);
+        real det_inv = 1.f / det;
+        real conic[3] = {cv[2] * det_inv, -cv[1] * det_inv, cv[0] * det_inv};
+        real mid = 0.5f * (cv[0] + cv[2]);
+        real l1 = mid + R_SQRT(R_FMAX(0.1f, mid * mid - det));
+        real l2 = mid - R_SQRT(R_FMAX(0.1f, mid * mid - det));
+        real my_radius = R_CEIL(3.f * R_SQRT(R_FMAX(l1, l2)));
+        real px = ndc2pix(pp[0], W), py = ndc2pix(pp[1], H);
         uint32_t mn[2], mx[2];
         get_rect(px, py, (int)my_radius, gx, gy, mn, mx);
         if ((mx[0] - mn[0]) * (mx[1] - mn[1]) == 0) continue;
@@ -220,10 +240,10 @@ void orc_preprocess(int P, int D, int M, const float* means3D, const float* scal
 }
 
 /* rasterizer_impl.cu:54-66 */
-void orc_mark_visible(int P, const float* means3D, const float* view, const float* proj, uint8_t* present) {
+void orc_mark_visible(int P, const real* means3D, const real* view, const real* proj, uint8_t* present) {
     (void)proj;
     for (int i = 0; i < P; i++) {
-        float pv[3];
+        real pv[3];
         xform4x3(means3D + 3 * i, view, pv);
         present[i] = pv[2] > 0.2f;
     }
@@ -248,7 +268,7 @@ int64_t orc_scan(int P, const uint32_t* tiles_touched, uint32_t* offsets) {
 }
 
 /* rasterizer_impl.cu:70-111 */
-void orc_duplicate_with_keys(int P, int W, int H, const float* means2D, const float* depths,
+void orc_duplicate_with_keys(int P, int W, int H, const real* means2D, const real* depths,
                              const uint32_t* offsets, const int* radii, uint64_t* keys, uint32_t* vals) {
     const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
     for (int i = 0; i < P; i++) {
@@ -257,7 +277,8 @@ void orc_duplicate_with_keys(int P, int W, int H, const float* means2D, const fl
         uint32_t mn[2], mx[2];
         get_rect(means2D[2 * i], means2D[2 * i + 1], radii[i], gx, gy, mn, mx);
         uint32_t dbits;
-        memcpy(&dbits, depths + i, 4);
+        const float d32 = (float)depths[i]; /* the key holds the fp32 bits in both builds */
+        memcpy(&dbits, &d32, 4);
         for (uint32_t y = mn[1]; y < mx[1]; y++)
             for (uint32_t x = mn[0]; x < mx[0]; x++) {
                 uint64_t key = (uint64_t)(y * (uint32_t)gx + x);
@@ -317,28 +338,28 @@ void orc_tile_ranges(int64_t L, const uint64_t* keys, int n_tiles, uint32_t* ran
 
 /* forward.cu:261-381, one pixel at a time over the tile's sorted range. */
 void orc_blend_forward(int W, int H, const uint32_t* ranges, const uint32_t* point_list,
-                       const float* means2D, const float* colors, const float* depths,
-                       const float* conic_opacity, const float* bg, float* out_color, float* out_depth,
-                       float* out_alpha, uint32_t* n_contrib) {
+                       const real* means2D, const real* colors, const real* depths,
+                       const real* conic_opacity, const real* bg, real* out_color, real* out_depth,
+                       real* out_alpha, uint32_t* n_contrib) {
     const int gx = (W + TILE - 1) / TILE;
 #pragma omp parallel for schedule(dynamic, 8)
     for (int py = 0; py < H; py++)
         for (int px = 0; px < W; px++) {
             int tile = (py / TILE) * gx + px / TILE;
             uint32_t r0 = ranges[2 * tile], r1 = ranges[2 * tile + 1];
-            float T = 1.0f, C[3] = {0, 0, 0}, wsum = 0, Dp = 0;
+            real T = 1.0f, C[3] = {0, 0, 0}, wsum = 0, Dp = 0;
             uint32_t contributor = 0, last = 0;
-            const float pxf = (float)px, pyf = (float)py;
+            const real pxf = (real)px, pyf = (real)py;
             for (uint32_t k = r0; k < r1; k++) {
                 contributor++;
                 uint32_t id = point_list[k];
-                float dx = means2D[2 * id] - pxf, dy = means2D[2 * id + 1] - pyf;
-                const float* co = conic_opacity + 4 * id;
-                float power = -0.5f * (co[0] * dx * dx + co[2] * dy * dy) - co[1] * dx * dy;
+                real dx = means2D[2 * id] - pxf, dy = means2D[2 * id + 1] - pyf;
+                const real* co = conic_opacity + 4 * id;
+                real power = -0.5f * (co[0] * dx * dx + co[2] * dy * dy) - co[1] * dx * dy;
                 if (power > 0.0f) continue;
-                float alpha = fminf(0.99f, co[3] * expf(power));
+                real alpha = R_FMIN(0.99f, co[3] * R_EXP(power));
                 if (alpha < 1.0f / 255.0f) continue;
-                float test_T = T * (1 - alpha);
+                real test_T = T * (1 - alpha);
                 if (test_T < 0.0001f) break; /* done: entry not blended (forward.cu:351-355) */
                 for (int c = 0; c < 3; c++) C[c] += colors[3 * id + c] * alpha * T;
                 wsum += alpha * T;
@@ -354,58 +375,58 @@ void orc_blend_forward(int W, int H, const uint32_t* ranges, const uint32_t* poi
         }
 }
 
-/* backward.cu:415-601.  Per-pair terms are computed in float exactly as written there; the
+/* backward.cu:415-601.  Per-pair terms are computed in real exactly as written there; the
  * per-Gaussian sums (global atomicAdd in the reference, order-nondeterministic) are kept in
  * double here so the oracle is the better-rounded side of any disagreement.
  * Outputs (all double, zero-initialised by the caller): dmean2D[P*2], dconic[P*3] (x,y,w),
  * dopacity[P], dcolor[P*3], ddepth[P]. */
 void orc_blend_backward(int P, int W, int H, const uint32_t* ranges, const uint32_t* point_list,
-                        const float* bg, const float* means2D, const float* conic_opacity,
-                        const float* colors, const float* depths, const float* alphas,
-                        const uint32_t* n_contrib, const float* dL_dpix, const float* dL_dpix_depth,
-                        const float* dL_dpix_alpha, double* dmean2D, double* dconic, double* dopacity,
+                        const real* bg, const real* means2D, const real* conic_opacity,
+                        const real* colors, const real* depths, const real* alphas,
+                        const uint32_t* n_contrib, const real* dL_dpix, const real* dL_dpix_depth,
+                        const real* dL_dpix_alpha, double* dmean2D, double* dconic, double* dopacity,
                         double* dcolor, double* ddepth) {
     (void)P;
     const int gx = (W + TILE - 1) / TILE;
-    const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+    const real ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
 #pragma omp parallel for schedule(dynamic, 4)
     for (int py = 0; py < H; py++)
         for (int px = 0; px < W; px++) {
             int tile = (py / TILE) * gx + px / TILE;
             uint32_t r0 = ranges[2 * tile], r1 = ranges[2 * tile + 1];
             size_t pid = (size_t)py * W + px;
-            const float T_final = 1 - alphas[pid];
-            float T = T_final;
+            const real T_final = 1 - alphas[pid];
+            real T = T_final;
             const uint32_t last_contributor = n_contrib[pid];
-            float accum_rec[3] = {0, 0, 0}, dpix[3], accum_depth = 0, accum_alpha = 0;
+            real accum_rec[3] = {0, 0, 0}, dpix[3], accum_depth = 0, accum_alpha = 0;
             for (int c = 0; c < 3; c++) dpix[c] = dL_dpix[(size_t)c * H * W + pid];
-            const float dpd = dL_dpix_depth[pid], dpa = dL_dpix_alpha[pid];
-            float last_alpha = 0, last_color[3] = {0, 0, 0}, last_depth = 0;
-            const float pxf = (float)px, pyf = (float)py;
+            const real dpd = dL_dpix_depth[pid], dpa = dL_dpix_alpha[pid];
+            real last_alpha = 0, last_color[3] = {0, 0, 0}, last_depth = 0;
+            const real pxf = (real)px, pyf = (real)py;
             uint32_t contributor = r1 - r0;
             for (uint32_t k = r1; k-- > r0;) {
                 contributor--;
                 if (contributor >= last_contributor) continue;
                 uint32_t id = point_list[k];
-                float dx = means2D[2 * id] - pxf, dy = means2D[2 * id + 1] - pyf;
-                const float* co = conic_opacity + 4 * id;
-                float power = -0.5f * (co[0] * dx * dx + co[2] * dy * dy) - co[1] * dx * dy;
+                real dx = means2D[2 * id] - pxf, dy = means2D[2 * id + 1] - pyf;
+                const real* co = conic_opacity + 4 * id;
+                real power = -0.5f * (co[0] * dx * dx + co[2] * dy * dy) - co[1] * dx * dy;
                 if (power > 0.0f) continue;
-                const float G = expf(power);
-                const float alpha = fminf(0.99f, co[3] * G);
+                const real G = R_EXP(power);
+                const real alpha = R_FMIN(0.99f, co[3] * G);
                 if (alpha < 1.0f / 255.0f) continue;
                 T = T / (1.f - alpha);
-                const float w = alpha * T;
-                float dL_dopa = 0.0f;
+                const real w = alpha * T;
+                real dL_dopa = 0.0f;
                 for (int c = 0; c < 3; c++) {
-                    const float col = colors[3 * id + c];
+                    const real col = colors[3 * id + c];
                     accum_rec[c] = last_alpha * last_color[c] + (1.f - last_alpha) * accum_rec[c];
                     last_color[c] = col;
                     dL_dopa += (col - accum_rec[c]) * dpix[c];
                     _Pragma("omp atomic")
                     dcolor[3 * (size_t)id + c] += (double)(w * dpix[c]);
                 }
-                const float cd = depths[id];
+                const real cd = depths[id];
                 accum_depth = last_alpha * last_depth + (1.f - last_alpha) * accum_depth;
                 last_depth = cd;
                 dL_dopa += (cd - accum_depth) * dpd;
@@ -415,13 +436,13 @@ void orc_blend_backward(int P, int W, int H, const uint32_t* ranges, const uint3
                 dL_dopa += (1 - accum_alpha) * dpa;
                 dL_dopa *= T;
                 last_alpha = alpha;
-                float bgdot = 0;
+                real bgdot = 0;
                 for (int c = 0; c < 3; c++) bgdot += bg[c] * dpix[c];
                 dL_dopa += (-T_final / (1.f - alpha)) * bgdot;
-                const float dL_dG = co[3] * dL_dopa;
-                const float gdx = G * dx, gdy = G * dy;
-                const float dG_ddelx = -gdx * co[0] - gdy * co[1];
-                const float dG_ddely = -gdy * co[2] - gdx * co[1];
+                const real dL_dG = co[3] * dL_dopa;
+                const real gdx = G * dx, gdy = G * dy;
+                const real dG_ddelx = -gdx * co[0] - gdy * co[1];
+                const real dG_ddely = -gdy * co[2] - gdx * co[1];
                 _Pragma("omp atomic")
                 dmean2D[2 * (size_t)id] += (double)(dL_dG * dG_ddelx * ddelx_dx);
                 _Pragma("omp atomic")
@@ -439,23 +460,23 @@ void orc_blend_backward(int P, int W, int H, const uint32_t* ranges, const uint3
 }
 
 /* auxiliary.h:107-117 */
-static void dnormvdv3(const float* v, const float* dv, float* o) {
-    float sum2 = v[0] * v[0] + v[1] * v[1] + v[2] * v[2];
-    float inv = 1.0f / sqrtf(sum2 * sum2 * sum2);
+static void dnormvdv3(const real* v, const real* dv, real* o) {
+    real sum2 = v[0] * v[0] + v[1] * v[1] + v[2] * v[2];
+    real inv = 1.0f / R_SQRT(sum2 * sum2 * sum2);
     o[0] = ((+sum2 - v[0] * v[0]) * dv[0] - v[1] * v[0] * dv[1] - v[2] * v[0] * dv[2]) * inv;
     o[1] = (-v[0] * v[1] * dv[0] + (sum2 - v[1] * v[1]) * dv[1] - v[2] * v[1] * dv[2]) * inv;
     o[2] = (-v[0] * v[2] * dv[0] - v[1] * v[2] * dv[1] + (sum2 - v[2] * v[2]) * dv[2]) * inv;
 }
 
 /* backward.cu:20-139 */
-static void sh_backward(int deg, int M, const float* pos, const float* campos, const float* sh,
-                        const uint8_t* clamped, const float* dL_dcolor, float* dL_dmean_acc, float* dL_dsh) {
-    float dorig[3] = {pos[0] - campos[0], pos[1] - campos[1], pos[2] - campos[2]};
-    float len = sqrtf(dorig[0] * dorig[0] + dorig[1] * dorig[1] + dorig[2] * dorig[2]);
-    float x = dorig[0] / len, y = dorig[1] / len, z = dorig[2] / len;
-    float g[3] = {dL_dcolor[0] * (clamped[0] ? 0.f : 1.f), dL_dcolor[1] * (clamped[1] ? 0.f : 1.f),
+static void sh_backward(int deg, int M, const real* pos, const real* campos, const real* sh,
+                        const uint8_t* clamped, const real* dL_dcolor, real* dL_dmean_acc, real* dL_dsh) {
+    real dorig[3] = {pos[0] - campos[0], pos[1] - campos[1], pos[2] - campos[2]};
+    real len = R_SQRT(dorig[0] * dorig[0] + dorig[1] * dorig[1] + dorig[2] * dorig[2]);
+    real x = dorig[0] / len, y = dorig[1] / len, z = dorig[2] / len;
+    real g[3] = {dL_dcolor[0] * (clamped[0] ? 0.f : 1.f), dL_dcolor[1] * (clamped[1] ? 0.f : 1.f),
                   dL_dcolor[2] * (clamped[2] ? 0.f : 1.f)};
-    float dx[3] = {0, 0, 0}, dy[3] = {0, 0, 0}, dz[3] = {0, 0, 0};
+    real dx[3] = {0, 0, 0}, dy[3] = {0, 0, 0}, dz[3] = {0, 0, 0};
     (void)M;
 #define SH(k, c) sh[(k) * 3 + (c)]
 #define DSH(k, v) for (int c = 0; c < 3; c++) dL_dsh[(k) * 3 + c] = (v) * g[c]
@@ -464,7 +485,7 @@ static void sh_backward(int deg, int M, const float* pos, const float* campos, c
         DSH(1, -C1 * y); DSH(2, C1 * z); DSH(3, -C1 * x);
         for (int c = 0; c < 3; c++) { dx[c] = -C1 * SH(3, c); dy[c] = -C1 * SH(1, c); dz[c] = C1 * SH(2, c); }
         if (deg > 1) {
-            float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+            real xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
             DSH(4, C2[0] * xy); DSH(5, C2[1] * yz); DSH(6, C2[2] * (2.f * zz - xx - yy));
             DSH(7, C2[3] * xz); DSH(8, C2[4] * (xx - yy));
             for (int c = 0; c < 3; c++) {
@@ -495,20 +516,20 @@ static void sh_backward(int deg, int M, const float* pos, const float* campos, c
     }
 #undef SH
 #undef DSH
-    float ddir[3] = {dx[0] * g[0] + dx[1] * g[1] + dx[2] * g[2], dy[0] * g[0] + dy[1] * g[1] + dy[2] * g[2],
+    real ddir[3] = {dx[0] * g[0] + dx[1] * g[1] + dx[2] * g[2], dy[0] * g[0] + dy[1] * g[1] + dy[2] * g[2],
                      dz[0] * g[0] + dz[1] * g[1] + dz[2] * g[2]};
-    float dm[3];
+    real dm[3];
     dnormvdv3(dorig, ddir, dm);
     dL_dmean_acc[0] += dm[0]; dL_dmean_acc[1] += dm[1]; dL_dmean_acc[2] += dm[2];
 }
 
 /* backward.cu:278-341 */
-static void cov3d_backward(const float* scale, float mod, const float* q, const float* dc, float* dscale, float* drot) {
-    float r = q[0], x = q[1], y = q[2], z = q[3];
+static void cov3d_backward(const real* scale, real mod, const real* q, const real* dc, real* dscale, real* drot) {
+    real r = q[0], x = q[1], y = q[2], z = q[3];
     M3 R = {{{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
              {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
              {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}}};
-    float s[3] = {mod * scale[0], mod * scale[1], mod * scale[2]};
+    real s[3] = {mod * scale[0], mod * scale[1], mod * scale[2]};
     M3 S;
     memset(&S, 0, sizeof S);
     S.m[0][0] = s[0]; S.m[1][1] = s[1]; S.m[2][2] = s[2];
@@ -531,15 +552,15 @@ static void cov3d_backward(const float* scale, float mod, const float* q, const 
 
 /* backward.cu:144-274 (computeCov2DCUDA) followed by :346-412 (preprocessCUDA backward).
  * Inputs dmean2D[P*2], dconic[P*3] (x,y,w of the reference's float4), dcolor[P*3], ddepth[P]
- * are the (float) outputs of the blend backward.  Outputs are fully written; Gaussians with
+ * are the (real) outputs of the blend backward.  Outputs are fully written; Gaussians with
  * radii <= 0 get zeros (the reference leaves its zero-initialised tensors untouched there). */
-void orc_preprocess_backward(int P, int D, int M, const float* means3D, const int* radii, const float* shs,
-                             const uint8_t* clamped, const float* scales, const float* rots, float scale_mod,
-                             const float* cov3Ds, const float* view, const float* proj, const float* campos,
-                             int W, int H, float tfx, float tfy, const float* dmean2D, const float* dconic,
-                             const float* dcolor, const float* ddepth, float* dmean3D, float* dcov3D,
-                             float* dsh, float* dscale, float* drot) {
-    const float fy = H / (2.0f * tfy), fx = W / (2.0f * tfx);
+void orc_preprocess_backward(int P, int D, int M, const real* means3D, const int* radii, const real* shs,
+                             const uint8_t* clamped, const real* scales, const real* rots, real scale_mod,
+                             const real* cov3Ds, const real* view, const real* proj, const real* campos,
+                             int W, int H, real tfx, real tfy, const real* dmean2D, const real* dconic,
+                             const real* dcolor, const real* ddepth, real* dmean3D, real* dcov3D,
+                             real* dsh, real* dscale, real* drot) {
+    const real fy = H / (2.0f * tfy), fx = W / (2.0f * tfx);
 #pragma omp parallel for schedule(static)
     for (int i = 0; i < P; i++) {
         for (int k = 0; k < 3; k++) dmean3D[3 * i + k] = 0.f;
@@ -547,17 +568,17 @@ void orc_preprocess_backward(int P, int D, int M, const float* means3D, const in
         if (dsh) for (int k = 0; k < 3 * M; k++) dsh[(size_t)i * 3 * M + k] = 0.f;
         if (dscale) { for (int k = 0; k < 3; k++) dscale[3 * i + k] = 0.f; for (int k = 0; k < 4; k++) drot[4 * i + k] = 0.f; }
         if (!(radii[i] > 0)) continue;
-        const float* mean = means3D + 3 * i;
-        const float* c3 = cov3Ds + 6 * i;
-        float cv[3], t[3], gm[2];
+        const real* mean = means3D + 3 * i;
+        const real* c3 = cov3Ds + 6 * i;
+        real cv[3], t[3], gm[2];
         M3 T;
         cov2d(mean, fx, fy, tfx, tfy, c3, view, cv, &T, t, gm);
-        const float a = cv[0], b = cv[1], c = cv[2];
-        const float dcx = dconic[3 * i], dcy = dconic[3 * i + 1], dcz = dconic[3 * i + 2];
-        float denom = a * c - b * b;
-        float dL_da = 0, dL_db = 0, dL_dc = 0;
-        float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
-        float* dc = dcov3D + 6 * i;
+        const real a = cv[0], b = cv[1], c = cv[2];
+        const real dcx = dconic[3 * i], dcy = dconic[3 * i + 1], dcz = dconic[3 * i + 2];
+        real denom = a * c - b * b;
+        real dL_da = 0, dL_db = 0, dL_dc = 0;
+        real denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+        real* dc = dcov3D + 6 * i;
         if (denom2inv != 0) {
             dL_da = denom2inv * (-c * c * dcx + 2 * b * c * dcy + (denom - a * c) * dcz);
             dL_dc = denom2inv * (-a * a * dcz + 2 * a * b * dcy + (denom - a * c) * dcx);
@@ -570,8 +591,8 @@ void orc_preprocess_backward(int P, int D, int M, const float* means3D, const in
             dc[2] = 2 * TT(0, 0) * TT(0, 2) * dL_da + (TT(0, 0) * TT(1, 2) + TT(0, 2) * TT(1, 0)) * dL_db + 2 * TT(1, 0) * TT(1, 2) * dL_dc;
             dc[4] = 2 * TT(0, 2) * TT(0, 1) * dL_da + (TT(0, 1) * TT(1, 2) + TT(0, 2) * TT(1, 1)) * dL_db + 2 * TT(1, 1) * TT(1, 2) * dL_dc;
         }
-        float V[3][3] = {{c3[0], c3[1], c3[2]}, {c3[1], c3[3], c3[4]}, {c3[2], c3[4], c3[5]}};
-        float dT[2][3];
+        real V[3][3] = {{c3[0], c3[1], c3[2]}, {c3[1], c3[3], c3[4]}, {c3[2], c3[4], c3[5]}};
+        real dT[2][3];
         for (int k = 0; k < 3; k++) {
             dT[0][k] = 2 * (TT(0, 0) * V[k][0] + TT(0, 1) * V[k][1] + TT(0, 2) * V[k][2]) * dL_da +
                        (TT(1, 0) * V[k][0] + TT(1, 1) * V[k][1] + TT(1, 2) * V[k][2]) * dL_db;
@@ -581,31 +602,31 @@ void orc_preprocess_backward(int P, int D, int M, const float* means3D, const in
 #undef TT
         /* W (GLM, column-major): W[c][r] = view[4*r + c]  (backward.cu:182-185) */
 #define WW(c_, r_) view[4 * (r_) + (c_)]
-        float dJ00 = WW(0, 0) * dT[0][0] + WW(0, 1) * dT[0][1] + WW(0, 2) * dT[0][2];
-        float dJ02 = WW(2, 0) * dT[0][0] + WW(2, 1) * dT[0][1] + WW(2, 2) * dT[0][2];
-        float dJ11 = WW(1, 0) * dT[1][0] + WW(1, 1) * dT[1][1] + WW(1, 2) * dT[1][2];
-        float dJ12 = WW(2, 0) * dT[1][0] + WW(2, 1) * dT[1][1] + WW(2, 2) * dT[1][2];
+        real dJ00 = WW(0, 0) * dT[0][0] + WW(0, 1) * dT[0][1] + WW(0, 2) * dT[0][2];
+        real dJ02 = WW(2, 0) * dT[0][0] + WW(2, 1) * dT[0][1] + WW(2, 2) * dT[0][2];
+        real dJ11 = WW(1, 0) * dT[1][0] + WW(1, 1) * dT[1][1] + WW(1, 2) * dT[1][2];
+        real dJ12 = WW(2, 0) * dT[1][0] + WW(2, 1) * dT[1][1] + WW(2, 2) * dT[1][2];
 #undef WW
-        float tz = 1.f / t[2], tz2 = tz * tz, tz3 = tz2 * tz;
-        float dtx = gm[0] * -fx * tz2 * dJ02;
-        float dty = gm[1] * -fy * tz2 * dJ12;
-        float dtz = -fx * tz2 * dJ00 - fy * tz2 * dJ11 + (2 * fx * t[0]) * tz3 * dJ02 + (2 * fy * t[1]) * tz3 * dJ12;
-        float dm[3] = {view[0] * dtx + view[1] * dty + view[2] * dtz, view[4] * dtx + view[5] * dty + view[6] * dtz,
+        real tz = 1.f / t[2], tz2 = tz * tz, tz3 = tz2 * tz;
+        real dtx = gm[0] * -fx * tz2 * dJ02;
+        real dty = gm[1] * -fy * tz2 * dJ12;
+        real dtz = -fx * tz2 * dJ00 - fy * tz2 * dJ11 + (2 * fx * t[0]) * tz3 * dJ02 + (2 * fy * t[1]) * tz3 * dJ12;
+        real dm[3] = {view[0] * dtx + view[1] * dty + view[2] * dtz, view[4] * dtx + view[5] * dty + view[6] * dtz,
                        view[8] * dtx + view[9] * dty + view[10] * dtz}; /* auxiliary.h:89-97 */
         /* preprocess backward, backward.cu:372-403 */
-        float mh[4];
+        real mh[4];
         xform4x4(mean, proj, mh);
-        float mw = 1.0f / (mh[3] + 0.0000001f);
-        float mul1 = (proj[0] * mean[0] + proj[4] * mean[1] + proj[8] * mean[2] + proj[12]) * mw * mw;
-        float mul2 = (proj[1] * mean[0] + proj[5] * mean[1] + proj[9] * mean[2] + proj[13]) * mw * mw;
-        const float g2x = dmean2D[2 * i], g2y = dmean2D[2 * i + 1];
-        float d1[3];
+        real mw = 1.0f / (mh[3] + 0.0000001f);
+        real mul1 = (proj[0] * mean[0] + proj[4] * mean[1] + proj[8] * mean[2] + proj[12]) * mw * mw;
+        real mul2 = (proj[1] * mean[0] + proj[5] * mean[1] + proj[9] * mean[2] + proj[13]) * mw * mw;
+        const real g2x = dmean2D[2 * i], g2y = dmean2D[2 * i + 1];
+        real d1[3];
         d1[0] = (proj[0] * mw - proj[3] * mul1) * g2x + (proj[1] * mw - proj[3] * mul2) * g2y;
         d1[1] = (proj[4] * mw - proj[7] * mul1) * g2x + (proj[5] * mw - proj[7] * mul2) * g2y;
         d1[2] = (proj[8] * mw - proj[11] * mul1) * g2x + (proj[9] * mw - proj[11] * mul2) * g2y;
         for (int k = 0; k < 3; k++) dm[k] += d1[k];
-        float mul3 = view[2] * mean[0] + view[6] * mean[1] + view[10] * mean[2] + view[14];
-        float d2[3] = {(view[2] - view[3] * mul3) * ddepth[i], (view[6] - view[7] * mul3) * ddepth[i],
+        real mul3 = view[2] * mean[0] + view[6] * mean[1] + view[10] * mean[2] + view[14];
+        real d2[3] = {(view[2] - view[3] * mul3) * ddepth[i], (view[6] - view[7] * mul3) * ddepth[i],
                        (view[10] - view[11] * mul3) * ddepth[i]};
         for (int k = 0; k < 3; k++) dm[k] += d2[k];
         if (shs) sh_backward(D, M, mean, campos, shs + (size_t)i * 3 * M, clamped + 3 * i, dcolor + 3 * i, dm, dsh + (size_t)i * 3 * M);
@@ -617,17 +638,17 @@ void orc_preprocess_backward(int P, int D, int M, const float* means3D, const in
 /* simple-knn: the result of knn/simple_knn.cu:186-221 is the exact mean of the three smallest squared
  * distances to other points (the Morton boxes are only an acceleration structure), so a brute-force scan
  * is a valid restatement.  updateKBest (:120-134) keeps the three smallest, duplicates included. */
-void orc_dist2_knn3(int P, const float* pts, float* out) {
+void orc_dist2_knn3(int P, const real* pts, real* out) {
 #pragma omp parallel for schedule(static)
     for (int i = 0; i < P; i++) {
-        float best[3] = {FLT_MAX, FLT_MAX, FLT_MAX};
-        const float* r = pts + 3 * i;
+        real best[3] = {FLT_MAX, FLT_MAX, FLT_MAX};
+        const real* r = pts + 3 * i;
         for (int j = 0; j < P; j++) {
             if (j == i) continue;
-            float dx = pts[3 * j] - r[0], dy = pts[3 * j + 1] - r[1], dz = pts[3 * j + 2] - r[2];
-            float dist = dx * dx + dy * dy + dz * dz;
+            real dx = pts[3 * j] - r[0], dy = pts[3 * j + 1] - r[1], dz = pts[3 * j + 2] - r[2];
+            real dist = dx * dx + dy * dy + dz * dz;
             for (int k = 0; k < 3; k++)
-                if (best[k] > dist) { float t = best[k]; best[k] = dist; dist = t; }
+                if (best[k] > dist) { real t = best[k]; best[k] = dist; dist = t; }
         }
         out[i] = (best[0] + best[1] + best[2]) / 3.0f;
     }

@@ -378,12 +378,9 @@ int launch_tile_count(const BinPlan& b, int P, int grid_x, int grid_y, const uin
         return -1;
     }
     const size_t smem = (size_t)b.wpc * b.Tpad * 2;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(tile_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-        cudaFuncSetAttribute(tile_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-        attr_set = true;
-    }
+    if (ensure_dyn_smem(reinterpret_cast<const void*>(tile_count_kernel), 220 * 1024) ||
+        ensure_dyn_smem(reinterpret_cast<const void*>(tile_scatter_kernel), 220 * 1024))
+        return -1;
     LaunchScope ls("tile_count", stream);
     tile_count_kernel<<<b.NG, b.wpc * 32, smem, stream>>>(P, b.T, b.NW, b.L, grid_x, grid_y, sorted_ids, tiles_touched, means2D,
                                                         radii, rects, M, Mg);

@@ -25,21 +25,6 @@ __device__ __forceinline__ void bulk_load(void* smem_dst, const void* gmem_src, 
                  : "memory");
 }
 
-// All threads that read the staged block wait here (phase parity of the barrier's current use).
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "WAIT_LOOP:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra WAIT_DONE;\n"
-        "bra WAIT_LOOP;\n"
-        "WAIT_DONE:\n"
-        "}\n" ::"r"(smem_u32(bar)),
-        "r"(parity)
-        : "memory");
-}
-
 // Non-blocking probe and plain arrival, for warp-to-warp hand-offs inside a CTA (one lane arrives after a
 // __syncwarp; arrive has release, try_wait acquire semantics at CTA scope).
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
@@ -54,6 +39,11 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         : "r"(smem_u32(bar)), "r"(parity)
         : "memory");
     return ok != 0;
+}
+// All threads that read the staged block wait here (phase parity of the barrier's current use).  A plain loop over the
+// probe: no asm labels, so any number of inlined copies can live in one kernel.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    while (!mbar_try_wait(bar, parity)) {}
 }
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");

@@ -28,6 +28,10 @@ private:
     bool on_;
 };
 
+// Raises a kernel's dynamic shared-memory limit.  The attribute is per (function, device): remembered per pair, so a
+// process that drives several GPUs gets it on each of them.  Returns 0, or -1 with the error text set.
+int ensure_dyn_smem(const void* func, int bytes);
+
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 __device__ __forceinline__ size_t align_up_dev(size_t x, size_t a) { return (x + a - 1) / a * a; }
 

@@ -437,11 +437,7 @@ int launch_gauss_skin_backward(const GaussBwdArgs& a, const SkinFuseBwdArgs& s, 
     LaunchScope ls("gauss_skin_backward", stream);
     const size_t smem = align_up(bone_smem_bytes(s.f.J, false) + 8 * sizeof(float) * ((size_t)(s.f.J - 1) * 13 + 3), 128) +
                         (size_t)256 * s.f.M_rest * 3 * sizeof(float) + 16;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(gauss_backward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-        attr_set = true;
-    }
+    if (ensure_dyn_smem(reinterpret_cast<const void*>(gauss_backward_kernel<true>), 160 * 1024)) return -1;
     const int rows = (a.row_end > 0 ? a.row_end : a.P) - a.row_begin;
     if (rows <= 0) return 0;
     gauss_backward_kernel<true><<<(rows + 255) / 256, 256, smem, stream>>>(a, s);

@@ -4,7 +4,6 @@
 // equals the reference's up to floating-point ties.  Cold path (called once when a model is created,
 // scene/gaussian_model.py:170); all scratch comes from the caller, nothing is allocated per call.
 #include <cfloat>
-#include <cub/device/device_radix_sort.cuh>
 
 #include "common.cuh"
 #include "kernels.cuh"
@@ -27,12 +26,9 @@ struct KnnScratch {
     size_t total;
 };
 
-static size_t knn_sort_temp(int P) {
-    size_t b = 0;
-    cub::DeviceRadixSort::SortPairs(nullptr, b, (const uint32_t*)nullptr, (uint32_t*)nullptr, (const uint32_t*)nullptr,
-                                    (uint32_t*)nullptr, P, 0, 30);
-    return b;
-}
+// The Morton codes are ordered by the library's own stable radix sort (radix_sort.cu, the depth sort of the forward
+// pass: 32-bit keys, ids from the key positions); the 30-bit codes simply have an all-zero top digit.
+static size_t knn_sort_temp(int P) { return depth_sort_temp_bytes((size_t)P); }
 
 static KnnScratch carve_knn(char* base, int P) {
     KnnScratch s;
@@ -179,12 +175,12 @@ int launch_dist2_knn3(int P, const float* points, float* out, char* scratch, siz
     KnnScratch s = carve_knn(scratch, P);
     if (scratch_bytes < s.total) { set_error("rg_dist_cuda2: scratch buffer too small"); return -1; }
     const int nblk = (P + 1023) / 1024, nbox = (P + kBox - 1) / kBox;
-    LaunchScope ls("dist_cuda2", stream, 5);
+    LaunchScope ls("dist_cuda2", stream, 5);  // the sort counts its own launches
     bbox_partial_kernel<<<nblk, 1024, 0, stream>>>(P, points, s.minmax);
     bbox_final_kernel<<<1, 1024, 0, stream>>>(nblk, s.minmax, s.bbox);
     morton_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, points, s.bbox, s.codes, s.idx);
-    cudaError_t e = cub::DeviceRadixSort::SortPairs(s.sort_temp, s.sort_temp_bytes, s.codes, s.codes_s, s.idx, s.idx_s, P, 0, 30, stream);
-    if (e != cudaSuccess) { set_error(std::string("knn sort: ") + cudaGetErrorString(e)); return -1; }
+    if (launch_depth_sort(s.sort_temp, s.sort_temp_bytes, reinterpret_cast<const float*>(s.codes), s.codes_s, nullptr, s.idx_s, P, stream))
+        return -1;
     box_aabb_kernel<<<nbox, kBox, 0, stream>>>(P, points, s.idx_s, s.boxes);
     knn3_kernel<<<nbox, kBox, 0, stream>>>(P, points, s.idx_s, s.boxes, out);
     return 0;

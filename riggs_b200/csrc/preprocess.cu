@@ -60,6 +60,8 @@ __global__ void __launch_bounds__(256, 4) preprocess_kernel(PreprocessArgs a, Sk
             __syncthreads();
         }
     }
+    // The thread that started the bulk copy is thread 0 and it is always a valid row (first < P).  Threads past P own
+    // no row and never touch s_sh; the CTA stays alive until thread 0 has seen the copy land (end of the kernel).
     if (idx >= a.P) return;
     const float* view = s_mat;
     const float* proj = s_mat + 16;
@@ -185,6 +187,10 @@ __global__ void __launch_bounds__(256, 4) preprocess_kernel(PreprocessArgs a, Sk
     a.tiles_touched[idx] = my_tiles;
     if (my_tiles == 0) a.depths[idx] = __int_as_float(0x7f800000);  // culled: +inf sorts behind everything
     a.ids[idx] = idx;
+    // A culled Gaussian leaves the loop above without reading the staged SH block, so it never waited for the bulk
+    // copy.  The CTA must not retire while the copy engine may still write into its shared memory: the issuing thread
+    // waits for the barrier's phase here (immediate when it already waited above).
+    if (FUSED && sh_bulk && threadIdx.x == 0) mbar_wait(&s_bar, 0);
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view,
@@ -209,11 +215,7 @@ int launch_skin_preprocess(const PreprocessArgs& a, const SkinFuseArgs& s, cudaS
     if (s.J > kMaxJoints || s.J < 2) { set_error("skinned preprocess: J must be in [2, 128]"); return -1; }
     LaunchScope ls("skin_preprocess", stream);
     const size_t smem = align_up(bone_smem_bytes(s.J, false), 128) + (size_t)256 * s.M_rest * 3 * sizeof(float) + 16;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(preprocess_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-        attr_set = true;
-    }
+    if (ensure_dyn_smem(reinterpret_cast<const void*>(preprocess_kernel<true>), 96 * 1024)) return -1;
     preprocess_kernel<true><<<(a.P + 255) / 256, 256, smem, stream>>>(a, s);
     return 0;
 }

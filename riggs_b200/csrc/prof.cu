@@ -5,7 +5,9 @@
 #include <cstring>
 #include <map>
 #include <mutex>
+#include <set>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "common.cuh"
@@ -43,6 +45,22 @@ LaunchScope::~LaunchScope() {
         cudaEventRecord(stop, stream_);
         g_events[name_].push_back({start_, stop});
     }
+}
+
+int ensure_dyn_smem(const void* func, int bytes) {
+    static std::mutex mu;
+    static std::set<std::pair<const void*, int>> done;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { set_error("ensure_dyn_smem: no current device"); return -1; }
+    std::lock_guard<std::mutex> l(mu);
+    if (done.count({func, dev})) return 0;
+    cudaError_t e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) {
+        set_error(std::string("cudaFuncSetAttribute(MaxDynamicSharedMemorySize): ") + cudaGetErrorString(e));
+        return -1;
+    }
+    done.insert({func, dev});
+    return 0;
 }
 
 }  // namespace rg

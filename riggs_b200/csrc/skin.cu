@@ -445,11 +445,8 @@ int launch_skin_backward(const SkinBwdArgs& a, cudaStream_t stream) {
     int blocks = (a.N + 255) / 256;
     if (blocks > RG_NUM_SMS * 4) blocks = RG_NUM_SMS * 4;
     LaunchScope ls("skin_backward", stream);
-    static bool attr_set = false;
-    if (!attr_set) {  // J = 128: 13 KB of bones + 8 accumulator rows of 6.6 KB
-        cudaFuncSetAttribute(skin_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-        attr_set = true;
-    }
+    // J = 128: 13 KB of bones + 8 accumulator rows of 6.6 KB
+    if (ensure_dyn_smem(reinterpret_cast<const void*>(skin_backward_kernel), 96 * 1024)) return -1;
     skin_backward_kernel<<<blocks, 256, bone_smem_bytes(a.J, true), stream>>>(a);
     return 0;
 }

@@ -121,3 +121,27 @@ def rel_err(a, b, floor=0.0):
     if a.size == 0:
         return 0.0
     return float(np.abs(a - b).max() / max(np.abs(b).max(), floor, 1e-30))
+
+
+def rel_l2(a, b):
+    """|a - b|_2 / |b|_2: pins the bulk of the entries, which a max-norm ratio (rel_err) lets through."""
+    a = np.asarray(a, np.float64).reshape(-1)
+    b = np.asarray(b, np.float64).reshape(-1)
+    if a.size == 0:
+        return 0.0
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-30))
+
+
+def floored_rel(a, b, floor_frac=1e-3):
+    """max over the entries of |a - b| / max(|b|, floor_frac * max|b|): every entry down to floor_frac of the largest
+    one is compared on its OWN scale, smaller ones on the floor's."""
+    a = np.asarray(a, np.float64).reshape(-1)
+    b = np.asarray(b, np.float64).reshape(-1)
+    if a.size == 0:
+        return 0.0
+    floor = max(float(np.abs(b).max()) * floor_frac, 1e-30)
+    return float((np.abs(a - b) / np.maximum(np.abs(b), floor)).max())
+
+
+def grad_stats(a, b):
+    return dict(max=rel_err(a, b), l2=rel_l2(a, b), floored=floored_rel(a, b))

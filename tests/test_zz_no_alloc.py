@@ -61,6 +61,27 @@ def test_static_scratch_entry_matches_ordinary_entry_twice_in_a_row():
     assert np.allclose(out.cpu().numpy(), _ordinary(L, pts).cpu().numpy(), rtol=1e-5, atol=1e-12)
 
 
+def test_static_scratch_entry_allocates_no_device_memory():
+    """The property the entry point exists for: across its calls neither torch's allocator nor the driver hands out
+    any device memory (cudaMemGetInfo's free figure and torch's counters stay where they were)."""
+    from riggs_b200 import _lib
+    L = _lib.lib()
+    pts = torch.rand(30_000, 3, generator=torch.Generator().manual_seed(5)).cuda().contiguous()
+    out = torch.empty(pts.shape[0], device="cuda")
+    _static(L, pts, out)  # the first call on the device looks the array's address up; not part of the measurement
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    alloc0, reserved0 = torch.cuda.memory_allocated(), torch.cuda.memory_reserved()
+    n_alloc0 = torch.cuda.memory_stats().get("allocation.all.allocated", 0)
+    for _ in range(5):
+        _static(L, pts, out)
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert torch.cuda.memory_allocated() == alloc0 and torch.cuda.memory_reserved() == reserved0
+    assert torch.cuda.memory_stats().get("allocation.all.allocated", 0) == n_alloc0
+    assert free1 >= free0  # nothing was taken from the device behind torch's back either
+
+
 def test_static_scratch_entry_rejects_oversized_clouds():
     from riggs_b200 import _lib
     L = _lib.lib()
