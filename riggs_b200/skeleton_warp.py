@@ -207,64 +207,70 @@ class _Embedder(nn.Module):
         return torch.cat(out, -1)
 
 
-class _SkipMLP(nn.Module):
-    def __init__(self, in_ch, width=256, depth=8):
-        super().__init__()
-        self.skips = [depth // 2]
-        self.layers = nn.ModuleList([nn.Linear(in_ch, width)] + [
-            nn.Linear(width, width) if i not in self.skips else nn.Linear(width + in_ch, width)
-            for i in range(depth - 1)])
+def _skip_layers(in_ch, width=256, depth=8):
+    """The 8 x 256 ReLU stack with the embedded input re-fed after layer depth // 2 (network_utils.py:28-32, 85-89,
+    127-128).  A plain ModuleList, so that its parameters are named ``<attr>.{i}.weight`` like the reference's."""
+    skips = [depth // 2]
+    return nn.ModuleList([nn.Linear(in_ch, width)] + [
+        nn.Linear(width, width) if i not in skips else nn.Linear(width + in_ch, width) for i in range(depth - 1)])
 
-    def forward(self, e):
-        h = e
-        for i, l in enumerate(self.layers):
-            h = F.relu(l(h))
-            if i in self.skips:
-                h = torch.cat([e, h], -1)
-        return h
+
+def _skip_forward(layers, e, skip=4):
+    h = e
+    for i, l in enumerate(layers):
+        h = F.relu(l(h))
+        if i == skip:
+            h = torch.cat([e, h], -1)
+    return h
 
 
 class PoseMLP(nn.Module):
-    """t -> {'rotation': (4J,), 'translation': (3,)} (network_utils.py:115-150)."""
+    """t -> {'rotation': (4J,), 'translation': (3,)} (network_utils.py:115-150).  Parameter names are the reference's
+    (``net.{i}``, ``rotation_predictor``, ``translation_predictor``), so a ``skeleton.pth`` loads by key."""
 
     def __init__(self, input_ch, output_ch, multires=8):
         super().__init__()
         self.embed = _Embedder(multires, input_ch)
-        self.net = _SkipMLP(self.embed.out_dim)
+        self.net = _skip_layers(self.embed.out_dim)
         self.rotation_predictor = nn.Linear(256, output_ch)
         self.translation_predictor = nn.Linear(256, 3)
 
     def forward(self, t):
-        h = self.net(self.embed(t))
+        h = _skip_forward(self.net, self.embed(t))
         return {"rotation": self.rotation_predictor(h), "translation": self.translation_predictor(h)}
 
 
 class WeightMLP(nn.Module):
-    """x -> sigmoid (J-1) per-bone weight modulation (network_utils.py:73-107)."""
+    """x -> sigmoid (J-1) per-bone weight modulation (network_utils.py:73-107; parameters ``linear.{i}``,
+    ``weight_predict``)."""
 
     def __init__(self, input_ch, output_ch, multires=10):
         super().__init__()
         self.embed = _Embedder(multires, 3)
-        self.net = _SkipMLP(self.embed.out_dim)
+        self.linear = _skip_layers(self.embed.out_dim)
         self.weight_predict = nn.Linear(256, output_ch)
 
     def forward(self, x):
-        return torch.sigmoid(self.weight_predict(self.net(self.embed(x))))
+        return torch.sigmoid(self.weight_predict(_skip_forward(self.linear, self.embed(x))))
 
 
 class DeformMLP(nn.Module):
-    """(x, pose) -> 3-D template offset (network_utils.py:6-65)."""
+    """(x, pose) -> 3-D template offset (network_utils.py:6-65; parameters ``linear.{i}``, ``gaussian_warp``; the stack is
+    He-initialised with zero biases and the head starts at N(0, 1e-5) like the reference's, :35-40)."""
 
     def __init__(self, time_input_ch, multires=4):
         super().__init__()
         self.embed = _Embedder(multires, 3)
-        self.net = _SkipMLP(self.embed.out_dim + time_input_ch)
+        self.linear = _skip_layers(self.embed.out_dim + time_input_ch)
         self.gaussian_warp = nn.Linear(256, 3)
+        for layer in self.linear:
+            nn.init.kaiming_uniform_(layer.weight, mode="fan_in", nonlinearity="relu")
+            nn.init.zeros_(layer.bias)
         nn.init.normal_(self.gaussian_warp.weight, mean=0, std=1e-5)
         nn.init.zeros_(self.gaussian_warp.bias)
 
     def forward(self, x, t):
-        return self.gaussian_warp(self.net(torch.cat([self.embed(x), t], -1)))
+        return self.gaussian_warp(_skip_forward(self.linear, torch.cat([self.embed(x), t], -1)))
 
 
 class SkeletonWarp(nn.Module):
