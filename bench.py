@@ -4,11 +4,18 @@
     python bench.py --gpus N --steps K --warmup W            # our sm_100a path
     python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU path (oracle port), host cores
 
-A step = one pass of the hot path over one view: pose -> FK -> skin every Gaussian -> render 800x800 ->
-L1 loss -> backward to all Gaussian parameters and the skeleton inputs (train_rig.py:535-554 minus SSIM).
-Workload at every N: config C0 of SURVEY.md section 8(d) = the configuration the metric is quoted on
-(300k Gaussians, 24-joint SMPL-like skeleton, 800x800), one view per GPU per step (weak scaling); with N > 1
-the Gaussian-parameter gradients are summed across ranks by NCCL all-reduce inside the timed region.
+A step = one pass of the hot path over one view: pose -> FK -> skin every Gaussian -> render -> L1 loss -> backward to
+all Gaussian parameters and the skeleton inputs (train_rig.py:535-554 minus SSIM).  Default workload at every N: config
+C0 of SURVEY.md section 8(d) = the configuration the metric is quoted on (300k Gaussians, 24-joint SMPL-like skeleton,
+800x800), one view per GPU per step (weak scaling); camera, pose and target change every step (the scene's 8 views stay
+resident in HBM and are visited round-robin); with N > 1 the Gaussian-parameter gradients are summed across the ranks
+inside the timed region.
+
+Other shapes of BASELINE.json's configs:
+    --workload C3 --views-per-step 4      4-view batch per optimiser step (views sharded over the ranks, gradients
+    --workload C4 --views-per-step 8      accumulated per rank, ONE all-reduce per step); iterations = views; strong scaling
+    --workload C5 --mode sequence         256-frame novel-pose sequence, forward only, frames sharded over the ranks,
+                                          no collective; metric = frames/s
 Prints ONE JSON line on rank 0.
 """
 from __future__ import annotations
@@ -28,6 +35,7 @@ if ROOT not in sys.path:
 METRIC = "deform+raster fwd+bwd iters/s"
 UNIT = "iters/s"
 WORKLOAD = "C0"
+N_VIEWS = 8  # views of the synthetic scene that the steps rotate over
 
 
 def parse():
@@ -37,9 +45,19 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=WORKLOAD)
+    ap.add_argument("--mode", default="train", choices=["train", "sequence"],
+                    help="train: fwd+bwd steps (default); sequence: forward-only novel-pose frame sequence (C5)")
+    ap.add_argument("--views-per-step", type=int, default=0,
+                    help="global views per optimiser step, sharded over the ranks and accumulated per rank "
+                         "(0 = one view per GPU per step, weak scaling)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true")
+    ap.add_argument("--baselines", action="store_true",
+                    help="also time BASELINE.md's B1 (CPU skinning alone, C1) and B2 (reference CUDA rasterizer alone) rows")
     ap.add_argument("--isotropic", action="store_true")
+    ap.add_argument("--mlps", default="off", choices=["off", "on"],
+                    help="on: the reference's demo configuration (scripts/run_demo.py:32): per-Gaussian skinning-weight MLP "
+                         "and template-offset MLP evaluated (and differentiated) every step")
     ap.add_argument("--lambda-dssim", type=float, default=0.0,
                     help="> 0: the step's loss is the trainer's (1-l)*L1 + l*(1-SSIM) (fused kernels) instead of L1")
     ap.add_argument("--no-graph", action="store_true", help="drive the fused step launch by launch instead of replaying a CUDA graph")
@@ -92,7 +110,7 @@ class ClockSampler:
 
 # ---------------------------------------------------------------------------------------------------------
 # algorithmic bytes (restated in DESIGN.md)
-def algorithmic_bytes(P, R, HW, in_P=236, out_P=248, passes=6):
+def algorithmic_bytes(P, R, HW, in_P=236, out_P=248, passes=6, n_grad=0, world=1, multimem=False):
     per = {
         # fused path
         "skin_preprocess": P * (in_P + 48 + 12),
@@ -110,13 +128,62 @@ def algorithmic_bytes(P, R, HW, in_P=236, out_P=248, passes=6):
         "blend_forward": R * 44 + HW * 24,
         "blend_backward": HW * 28 + R * (44 + 40),
     }
+    if world > 1:
+        # bytes per NVLink direction and GPU: the switch-reduced kernel moves (N+1)/N of the buffer, the peer kernel 2(N-1)/N
+        per["allreduce_multimem"] = int(n_grad * 4 * (world + 1) / world)
+        per["allreduce_p2p"] = int(n_grad * 4 * 2 * (world - 1) / world)
     total = P * (2 * in_P + 336) + R * (148 + 24 * passes) + HW * 52
-    return per, total
+    own = sum(per[k] for k in ("skin_preprocess", "gauss_skin_backward", "depth_sort", "tile_count", "tile_scatter",
+                               "blend_forward", "blend_backward")) + HW * 3 * 12
+    return per, total, own
 
 
-def make_scene(workload, isotropic=False):
+def make_scene(workload, isotropic=False, mode="train"):
     from riggs_b200 import synth
-    return synth.make_config(workload, n_views=8, isotropic=isotropic)
+    if mode == "sequence":
+        return synth.make_config(workload, isotropic=isotropic)
+    return synth.make_config(workload, n_views=N_VIEWS, isotropic=isotropic)
+
+
+def views_of_rank(rank, world, vps, n_views=N_VIEWS):
+    """View indices this rank renders, step after step: step s covers global views s*world*vps .. (s+1)*world*vps - 1
+    (mod n_views), rank r takes r, r + world, ... of them.  Returned: the flat list over one rotation period."""
+    out, seen, s = [], set(), 0
+    while True:
+        grp = tuple((s * world * vps + rank + j * world) % n_views for j in range(vps))
+        if grp in seen:
+            break
+        seen.add(grp)
+        out.extend(grp)
+        s += 1
+    return out
+
+
+def workload_string(name, scene, W, H, args, world):
+    if args.mode == "sequence":
+        return (f"{name}: {scene.N} Gaussians, {scene.J}-joint skeleton, {W}x{H}, {len(scene.poses)}-frame novel-pose sequence, "
+                f"forward only, frames sharded over the GPUs")
+    if args.views_per_step > 0:
+        return (f"{name}: {scene.N} Gaussians, {scene.J}-joint skeleton, {W}x{H}, {args.views_per_step} views/step sharded over "
+                f"the GPUs, fwd+bwd, MLPs {args.mlps}")
+    return f"{name}: {scene.N} Gaussians, {scene.J}-joint skeleton, {W}x{H}, 1 view/GPU/step, fwd+bwd, MLPs {args.mlps}"
+
+
+def load_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        return {}
+
+
+def cpu_model():
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -134,46 +201,94 @@ def run_ours(args):
     if world > 1:
         import datetime
         os.environ.setdefault("NCCL_DEBUG", "WARN")  # keep NCCL banner lines off stdout: rank 0 prints ONE JSON line
-        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=120))
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
+    if args.mode == "sequence":
+        return run_sequence(args, rank, world, dev)
+
+    V = args.views_per_step
+    if V > 0 and V % world:
+        raise SystemExit(f"--views-per-step {V} must be a multiple of the number of GPUs ({world})")
+    vps = V // world if V > 0 else 1                      # views this rank renders per step
+    views_global = V if V > 0 else world                  # iterations (views) per step over the whole job
     scene = make_scene(args.workload, args.isotropic)
-    hp = HotPath(scene, device=dev, fused=not args.unfused, lambda_dssim=args.lambda_dssim)
-    cam = scene.cameras[rank % len(scene.cameras)].to(dev)
-    H, W = cam.image_height, cam.image_width
-    g = torch.Generator().manual_seed(1000 + rank)
-    target_host = torch.rand(3, H, W, generator=g).pin_memory()
-    target = target_host.to(dev)
-    pose_host = {k: v.clone().pin_memory() for k, v in scene.poses[rank % len(scene.poses)].items()}
-    pose = {k: v.to(dev).requires_grad_(True) for k, v in pose_host.items()}
+    hp = HotPath(scene, device=dev, fused=not args.unfused, lambda_dssim=args.lambda_dssim, mlps=args.mlps == "on")
+    order = views_of_rank(rank, world, vps)
+    H, W = scene.cameras[0].image_height, scene.cameras[0].image_width
+    g = torch.Generator().manual_seed(1000)
+    targets_host_all = [torch.rand(3, H, W, generator=g).pin_memory() for _ in range(N_VIEWS)]
+    cams = [scene.cameras[i].to(dev) for i in order]
+    targets_host = [targets_host_all[i] for i in order]
+    targets = [t.to(dev) for t in targets_host]
+    poses_host = [{k: v.clone().pin_memory() for k, v in scene.poses[i].items()} for i in order]
+    poses = [{k: v.to(dev) for k, v in p.items()} for p in poses_host]
+    n_groups = len(order) // vps
     params = hp.parameters()
     n_grad = sum(p.numel() for p in params)
-    if world > 1:
-        # data parallel over views: the backward kernels write into one flat fp32 buffer, all-reduced in place by NCCL
+    if world > 1 or vps > 1:
+        # the backward kernels write (first view) / add (later views) into one flat fp32 buffer, summed over the ranks in place
         hp.enable_flat_grads()
 
     def reduce_grads():
         if world > 1:
             hp.reduce_grads()
 
-    def eager_step(tgt, ps):
+    def group(i):
+        j = (i % n_groups) * vps
+        return cams[j:j + vps], poses[j:j + vps], targets[j:j + vps]
+
+    def eager_step(i):
         hp.zero_grad()
-        for v in ps.values():
-            v.grad = None
-        loss = hp.step(cam, ps, tgt)
+        cs, ps, ts = group(i)
+        ps = [{k: v.detach().clone().requires_grad_(True) for k, v in p.items()} for p in ps]
+        loss = hp.step_views(cs, ps, ts) if vps > 1 else hp.step(cs[0], ps[0], ts[0])
         reduce_grads()
         return loss
 
-    # The fused step is captured once as a CUDA graph (riggs_b200.hotpath.GraphedStep) and replayed; the gradient
-    # all-reduce of the data-parallel run stays an eager NCCL call after each replay.
-    use_graph = hp.fused and not args.no_graph
-    gs = None
-    if use_graph:
-        from riggs_b200.hotpath import GraphedStep
-        gs = GraphedStep(hp, cam, pose, target, warmup=3)
+    # ---- the all-reduce kernel's result against torch.distributed's, once, outside the timed regions -----------
+    allreduce_checked = None
+    if world > 1:
+        eager_step(0)  # leaves every rank's own gradients reduced; now redo it with a reference copy
+        hp.zero_grad()
+        cs, ps, ts = group(0)
+        ps = [{k: v.detach().clone().requires_grad_(True) for k, v in p.items()} for p in ps]
+        (hp.step_views(cs, ps, ts) if vps > 1 else hp.step(cs[0], ps[0], ts[0]))
+        ref = hp.flat.flat.clone()
+        dist.all_reduce(ref, op=dist.ReduceOp.SUM)
+        hp.reduce_grads()
+        torch.cuda.synchronize()
+        if getattr(hp.flat, "_mc_ptr", 0):  # switch-side sum: the order of the adds is the switch's
+            err = float((hp.flat.flat - ref).abs().max() / ref.abs().max().clamp_min(1e-30))
+            ok = err <= 1e-6
+        elif getattr(hp.flat, "hdl", None) is not None:  # rank-ordered adds on every rank: bit-identical to each other
+            err = float((hp.flat.flat - ref).abs().max() / ref.abs().max().clamp_min(1e-30))
+            ok = err <= 1e-6
+            chk = hp.flat.flat.clone()
+            dist.broadcast(chk, src=0)
+            ok = ok and bool(torch.equal(chk, hp.flat.flat))
+        else:
+            err, ok = 0.0, True
+        t_ok = torch.tensor([1 if ok else 0], device=dev)
+        dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
+        allreduce_checked = {"ok": bool(int(t_ok[0])), "max_rel_err_vs_nccl": err}
+        if not allreduce_checked["ok"]:
+            raise SystemExit(f"rank {rank}: own all-reduce disagrees with dist.all_reduce (rel err {err})")
 
-    def one_step(tgt, ps):
-        if gs is None:
-            return eager_step(tgt, ps)
-        loss = gs.step()  # target / pose / camera already sit in the graph's static device buffers
+    # The fused step is captured as CUDA graphs (riggs_b200.hotpath.RotatingSteps: one graph per group of views, the
+    # views' inputs resident in HBM) and replayed round-robin; the cross-rank sum stays an eager call after each replay.
+    use_graph = hp.fused and not args.no_graph
+    rot = None
+    if use_graph:
+        from riggs_b200.hotpath import RotatingSteps
+        rot = RotatingSteps(hp, cams, poses, targets, views_per_step=vps, warmup=2)
+
+    step_no = [0]
+
+    def one_step():
+        i = step_no[0]
+        step_no[0] += 1
+        if rot is None:
+            return eager_step(i)
+        loss = rot.step()  # the next group's graph: camera / pose / target change, nothing is copied
         reduce_grads()
         return loss
 
@@ -181,14 +296,14 @@ def run_ours(args):
     # nvidia-smi takes a driver lock while it starts: start it before the warm-up, not inside the timed region
     clocks = ClockSampler(local) if rank == 0 else None
     for _ in range(max(args.warmup, 3)):
-        one_step(target, pose)
+        one_step()
     torch.cuda.synchronize()
     if clocks is not None:
         t_wait = time.time()
         while not clocks.rows and time.time() - t_wait < 5.0:
             time.sleep(0.05)
     for _ in range(3):  # every rank runs the same number of steps (each one contains a collective when N > 1)
-        one_step(target, pose)
+        one_step()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -200,22 +315,25 @@ def run_ours(args):
     t0 = time.time()
     e0.record()
     for _ in range(args.steps):
-        one_step(target, pose)
+        one_step()
     e1.record()
     torch.cuda.synchronize()
     t1 = time.time()
     if world > 1:
         dist.barrier()
     ms = e0.elapsed_time(e1)
+    overflowed = bool(rot.overflowed) if rot is not None else False
     # kernels of this library inside the timed region (a replayed graph launches what its capture recorded)
-    launches = gs.launches_per_replay * args.steps if gs is not None else L.rg_launch_count() - launches0
+    launches = rot.launches_per_replay * args.steps if rot is not None else L.rg_launch_count() - launches0
+    if world > 1 and rot is not None:
+        launches += args.steps  # the all-reduce kernel, launched eagerly after each replay
     clk = clocks.stop(t0, t1) if clocks else None
 
     # ---- per-kernel durations: a separate eager pass with every launch bracketed by CUDA events on its stream ----
     L.rg_profile_reset()
     L.rg_profile_enable(1)
-    for _ in range(args.steps):
-        eager_step(target, pose)
+    for i in range(args.steps):
+        eager_step(i)
     torch.cuda.synchronize()
     L.rg_profile_enable(0)
     prof = _lib.profile_read()
@@ -224,49 +342,64 @@ def run_ours(args):
         dist.barrier()
 
     # ---- timed region 2: end to end through the public API, host buffers ------------------------------
-    cam_host = [cam.world_view_transform.cpu().pin_memory(), cam.full_proj_transform.cpu().pin_memory(),
-                cam.camera_center.cpu().pin_memory()]
-    import copy
-    cam2 = copy.copy(cam)
-    class _HostCam:  # pinned host copies of the camera tensors
-        world_view_transform, full_proj_transform, camera_center = cam_host
+    class _HostCam:  # pinned host copies of one view's camera tensors
+        def __init__(self, c):
+            self.world_view_transform = c.world_view_transform.cpu().pin_memory()
+            self.full_proj_transform = c.full_proj_transform.cpu().pin_memory()
+            self.camera_center = c.camera_center.cpu().pin_memory()
 
+    cams_host = [_HostCam(c) for c in cams]
+
+    def host_group(i):
+        j = (i % n_groups) * vps
+        c, p, t = cams_host[j:j + vps], poses_host[j:j + vps], targets_host[j:j + vps]
+        return (c, p, t) if vps > 1 else (c[0], p[0], t[0])
+
+    h2d = vps * (targets_host[0].numel() * 4 + sum(v.numel() * 4 for v in poses_host[0].values()) + (16 + 16 + 3) * 4)
     pipe = None
-    if gs is not None:  # two captured graphs alternate so that step i+1's inputs land while step i runs (set-up, untimed)
+    if use_graph:  # two captured graphs alternate so that step i+1's inputs land while step i runs (set-up, untimed)
         from riggs_b200.hotpath import PipelinedSteps
-        pipe = PipelinedSteps(hp, cam, pose, target, warmup=3, share_workspace=os.environ.get("RG_PIPE_SHARE", "1") != "0")
-        for _ in range(2):
-            pipe.feed(cam=_HostCam, pose=pose_host, target=target_host)
+        c0, p0, t0_ = group(0)
+        first = (c0, p0, t0_) if vps > 1 else (c0[0], p0[0], t0_[0])
+        pipe = PipelinedSteps(hp, *first, warmup=2, pool=rot.pool)
+        for i in range(2):
+            pipe.feed(*host_group(i))
             pipe.result(pipe.launch())
             reduce_grads()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    h2d = target_host.numel() * 4 + sum(v.numel() * 4 for v in pose_host.values()) + sum(c.numel() * 4 for c in cam_host)
     torch.cuda.synchronize()
     f0.record()
     last = 0.0
     if pipe is not None:  # input pipeline: step i+1's host -> device copies run while step i computes
-        pipe.feed(cam=_HostCam, pose=pose_host, target=target_host)
+        pipe.feed(*host_group(0))
     for it in range(args.steps):
         if pipe is not None:
             pipe.launch()  # waits for this step's inputs, replays, queues the read-back of the step's loss
             if it + 1 < args.steps:
-                pipe.feed(cam=_HostCam, pose=pose_host, target=target_host)
+                pipe.feed(*host_group(it + 1))
             reduce_grads()
             if it > 0:
                 last = pipe.result(it - 1)  # host read of the previous step's loss while this step runs
             continue
-        tgt = target_host.to(dev, non_blocking=True)
-        ps = {k: v.to(dev, non_blocking=True).requires_grad_(True) for k, v in pose_host.items()}
-        cam2.world_view_transform = cam_host[0].to(dev, non_blocking=True)
-        cam2.full_proj_transform = cam_host[1].to(dev, non_blocking=True)
-        cam2.camera_center = cam_host[2].to(dev, non_blocking=True)
+        c, p, t = host_group(it)
+        c, p, t = (c, p, t) if vps > 1 else ([c], [p], [t])
+        import copy
+        dc = []
+        for hc, src in zip(c, group(it)[0]):
+            cc = copy.copy(src)
+            cc.world_view_transform = hc.world_view_transform.to(dev, non_blocking=True)
+            cc.full_proj_transform = hc.full_proj_transform.to(dev, non_blocking=True)
+            cc.camera_center = hc.camera_center.to(dev, non_blocking=True)
+            dc.append(cc)
+        dp = [{k: v.to(dev, non_blocking=True).requires_grad_(True) for k, v in pp.items()} for pp in p]
+        dt = [tt.to(dev, non_blocking=True) for tt in t]
         hp.zero_grad()
-        loss = hp.step(cam2, ps, tgt)
+        loss = hp.step_views(dc, dp, dt) if vps > 1 else hp.step(dc[0], dp[0], dt[0])
         reduce_grads()
-        last = float(loss.cpu())  # device -> host read of the step's result
+        last = loss.detach().cpu()  # device -> host read of the step's result
     if pipe is not None:
         last = pipe.result(args.steps - 1)
     f1.record()
@@ -274,6 +407,11 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
     ms_e2e = f0.elapsed_time(f1)
+    last = float(last) if not hasattr(last, "numel") else float(last.reshape(-1)[-1])
+    overflowed = overflowed or bool(pipe is not None and pipe.overflowed_steps)
+
+    # NVLink: a peer copy of the gradient buffer's size on the same box, for the all-reduce's achieved-vs-link figure
+    nvlink = peer_copy_bandwidth(hp, dev) if world > 1 else None
 
     # max over ranks
     if world > 1:
@@ -286,34 +424,28 @@ def run_ours(args):
             dist.destroy_process_group()
         return
 
-    # workload facts for the roofline
+    # workload facts for the roofline (first view of this rank)
     with torch.no_grad():
-        out = hp.forward(cam, pose)
+        out = hp.forward(cams[0], poses[0])
+    torch.cuda.synchronize()
     P = scene.N
     vis = int((out["radii"] > 0).sum())
-    from riggs_b200.diff_gaussian_rasterization import _C  # noqa: F401
-    R = int(getattr(hp, "_last_R", 0))
-    # num_rendered is returned by the C ABI; fetch it once more through the binding
-    from riggs_b200 import gaussian_renderer as gr  # noqa: F401
-    R = _count_rendered(hp, cam, pose)
+    R = int(out["status"][0]) if out.get("status") is not None else _count_rendered(hp, cams[0], poses[0])
     in_P = 236 - (8 if args.isotropic else 0)
-    per, total_bytes = algorithmic_bytes(P, R, H * W, in_P=in_P)
+    multimem = bool(getattr(hp.flat, "_mc_ptr", 0)) if hp.flat is not None else False
+    per, total_bytes, own_bytes = algorithmic_bytes(P, R, H * W, in_P=in_P, n_grad=n_grad, world=world, multimem=multimem)
     step_ms = ms / args.steps
-    value = world * args.steps / (ms / 1e3)
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
+    view_ms = step_ms / vps
+    value = views_global * args.steps / (ms / 1e3)
+    peaks = load_peaks()
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured" if "hbm_gbs" in peaks else "fallback"
     kern = {k: {"ms_per_launch": v[0] / max(v[1], 1), "launches": v[1], "ms_per_step": v[0] / args.steps}
             for k, v in prof.items()}
     dom = max(kern, key=lambda k: kern[k]["ms_per_step"]) if kern else None
-    # dram__bytes_read.sum + dram__bytes_write.sum per launch from the one `ncu --set full` capture of this workload
-    # (profiles/r1_t_full_raw.csv, C0 on one B200); other workloads have no capture -> null
-    ncu_traffic = {"blend_backward": 17084416, "blend_forward": 14722304, "gauss_skin_backward": 122528256,
-                   "skin_preprocess": 78285056} if args.workload == "C0" and not args.isotropic else {}
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` capture of this workload
+    # (profiles/r2_*_full_raw.csv, C0 on one B200); other workloads have no capture -> null
+    ncu_traffic = NCU_TRAFFIC if args.workload == "C0" and not args.isotropic and args.mlps == "off" else {}
     roof = None
     if dom:
         b = per.get(dom, 0)
@@ -321,36 +453,245 @@ def run_ours(args):
         roof = {"kernel": dom, "bound": "hbm", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
                 "frac": round(achieved / peak, 4), "traffic": ncu_traffic.get(dom), "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": b, "ms_per_launch": round(kern[dom]["ms_per_launch"], 4)}
+        if dom.startswith("allreduce") and nvlink:
+            roof.update(bound="nvlink", peak=nvlink["peer_read_gbs"], frac=round(achieved / max(nvlink["peer_read_gbs"], 1e-9), 4),
+                        peak_source="peer copy of the same size measured in this run")
+    footprint = P * (in_P + 248) + own_bytes - per["skin_preprocess"] - per["gauss_skin_backward"] + P * 150
+    par = "single GPU"
+    if world > 1:
+        kind = ("own all-reduce kernel over symmetric memory (" + ("rg_allreduce_multimem, NVLS" if multimem else
+                "rg_allreduce_p2p, NVLink peer loads/stores") + ")") if getattr(hp.flat, "hdl", None) is not None else "NCCL all-reduce"
+        par = f"dp{world} over views, {kind} of {n_grad} grad floats"
     line = {
         "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": round(step_ms, 4), "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.workload}: {P} Gaussians, {scene.J}-joint skeleton, {W}x{H}, 1 view/GPU/step, "
-                               f"fwd+bwd", "P": P, "visible": vis, "R": R, "HW": H * W,
-                   "l2": "inputs+state per step (~%d MB) exceed no L2 flush; working set streams through HBM" % (total_bytes >> 20),
-                   "launch": "cuda graph replay" if gs is not None else "eager",
+        "warmup": max(args.warmup, 3), "ms_per_step": round(step_ms, 4), "higher_is_better": True,
+        "scaling": "strong" if V > 0 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_string(args.workload, scene, W, H, args, world), "P": P, "visible": vis, "R": R,
+                   "HW": H * W, "views_per_step_per_gpu": vps,
+                   "views": f"{len(order)} resident views visited round-robin (camera, pose and target change every step)",
+                   "l2": (f"no explicit flush: a step reads the parameters and writes their gradients once "
+                          f"(~{footprint >> 20} MB touched per view incl. the per-frame state) against a 126 MB L2, and the "
+                          f"view changes every step; the per-frame state itself (~{(R * 5 + P * 150 + H * W * 28) >> 20} MB) "
+                          f"stays L2-resident between the kernels of one step (ncu: dram bytes << algorithmic bytes for the blend kernels)"),
+                   "launch": "cuda graph replay" if rot is not None else "eager",
                    "loss": "L1" if args.lambda_dssim <= 0 else f"(1-{args.lambda_dssim})*L1 + {args.lambda_dssim}*(1-SSIM)",
-                   "parallelism": (f"dp{world} over views, " + (("own all-reduce kernel over symmetric memory (" + ("rg_allreduce_multimem, NVLS" if getattr(hp.flat, "_mc_ptr", 0)
-                                                                                       else "rg_allreduce_p2p, NVLink peer loads/stores") + ")")
-                                   if getattr(hp.flat, "hdl", None) is not None else "NCCL all-reduce") +
-                                   f" of {n_grad} grad floats") if world > 1 else "single GPU"},
-        "e2e": {"value": round(world * args.steps / (ms_e2e / 1e3), 3), "unit": UNIT, "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": 4, "last_loss": last},
+                   "mlps": args.mlps, "parallelism": par},
+        "e2e": {"value": round(views_global * args.steps / (ms_e2e / 1e3), 3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": 4 * vps, "last_loss": last},
         "gpu_launches": int(launches),
         "clocks": clk,
         "roofline": roof,
-        "step_hbm": {"algorithmic_bytes_per_step": total_bytes, "achieved_gbs": round(total_bytes / (step_ms * 1e-3) / 1e9, 2),
-                     "frac_of_peak": round(total_bytes / (step_ms * 1e-3) / 1e9 / peak, 4), "peak": peak},
+        "step_hbm": {"algorithmic_bytes_per_view": total_bytes, "achieved_gbs": round(total_bytes / (view_ms * 1e-3) / 1e9, 2),
+                     "frac_of_peak": round(total_bytes / (view_ms * 1e-3) / 1e9 / peak, 4), "peak": peak,
+                     "own_bytes_per_view": own_bytes,
+                     "own_frac_of_peak": round(own_bytes / (view_ms * 1e-3) / 1e9 / peak, 4),
+                     "note": "algorithmic = SURVEY 8(d) contract formula (charges a 6-pass 64-bit key sort this design does not run); "
+                             "own = the bytes this design's kernels are asked to move"},
         "kernels": {k: {kk: round(vv, 4) if isinstance(vv, float) else vv for kk, vv in v.items()} for k, v in kern.items()},
+        "instance_buffer_overflowed": overflowed,
     }
+    if allreduce_checked is not None:
+        line["allreduce_checked"] = allreduce_checked
+    if nvlink:
+        ar = [k for k in kern if k.startswith("allreduce")]
+        if ar:
+            k = ar[0]
+            nvlink["allreduce_kernel"] = k
+            nvlink["allreduce_ms"] = round(kern[k]["ms_per_launch"], 4)
+            nvlink["allreduce_gbs_per_direction"] = round(per.get(k, 0) / (kern[k]["ms_per_launch"] * 1e-3) / 1e9, 1)
+        line["nvlink"] = nvlink
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(scene, args)
     if world == 1 and not args.no_ref_cuda:
-        rc = ref_cuda_baseline(scene, cam, pose, target, steps=min(args.steps, 10))
+        rc = ref_cuda_baseline(scene, cams[0], poses[0], targets[0], steps=min(args.steps, 10), mlps=hp if args.mlps == "on" else None)
         if rc:
             line["reference_cuda_b200"] = rc
+    if world == 1 and args.baselines:
+        line["reference_cpu_skinning"] = reference_cpu_skinning()
+        line["reference_cuda_rasterizer"] = reference_cuda_rasterizer(["C2", "C3", "C4", "C5"])
     if world == 1:
-        line["next_rows"] = next_rows(hp, out["render"].detach(), target)
+        line["next_rows"] = next_rows(hp, out["render"].detach(), targets[0])
+    _emit(line)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full, C0 on one B200 (profiles/)
+NCU_TRAFFIC = {"blend_backward": 17084416, "blend_forward": 14722304, "gauss_skin_backward": 122528256,
+               "skin_preprocess": 78285056}
+
+
+def peer_copy_bandwidth(hp, dev, iters=10):
+    """GB/s of a plain device copy that READS a peer's copy of the gradient buffer over NVLink (what one direction of
+    one link pair delivers to a copy of this size on this box)."""
+    import torch
+    flat = hp.flat
+    hdl = getattr(flat, "hdl", None)
+    if hdl is None:
+        return None
+    try:
+        n = flat._storage.numel()
+        peer = (hdl.rank + 1) % hdl.world_size
+        src = hdl.get_buffer(peer, (n,), torch.float32)
+        dst = torch.empty(n, dtype=torch.float32, device=dev)
+        hdl.barrier(channel=0)
+        for _ in range(2):
+            dst.copy_(src)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            dst.copy_(src)
+        e1.record()
+        torch.cuda.synchronize()
+        hdl.barrier(channel=0)
+        msc = e0.elapsed_time(e1) / iters
+        return {"peer_read_gbs": round(n * 4 / (msc * 1e-3) / 1e9, 1), "bytes": n * 4,
+                "how": "torch copy_ from the next rank's symmetric-memory buffer, CUDA events, all ranks at once"}
+    except Exception as ex:
+        return {"unavailable": repr(ex)[:160]}
+
+
+# ---------------------------------------------------------------------------------------------------------
+def run_sequence(args, rank, world, dev):
+    """C5 as BASELINE.json states it: a 256-frame novel-pose sequence, forward only, frames sharded contiguously over
+    the ranks, no collective in the timed region (model: render_rig.py:250-334)."""
+    import torch
+    import torch.distributed as dist
+    from riggs_b200 import _lib
+    from riggs_b200.dist import shard_frames
+    from riggs_b200.hotpath import HotPath, PoseSequenceRenderer
+
+    scene = make_scene(args.workload, args.isotropic, mode="sequence")
+    hp = HotPath(scene, device=dev, fused=True, mlps=args.mlps == "on", inference=True)
+    cam = scene.cameras[0].to(dev)
+    H, W = cam.image_height, cam.image_width
+    F_total = len(scene.poses)
+    b, e = shard_frames(F_total, rank, world)
+    F = e - b
+    rot_host = torch.stack([p["local_rotation"] for p in scene.poses[b:e]]).pin_memory()
+    trans_host = torch.stack([p["global_trans"] for p in scene.poses[b:e]]).pin_memory()
+    seq = PoseSequenceRenderer(hp, cam, scene.J, max_frames=max(F, 1))
+    seq.load(rot_host, trans_host)
+    torch.cuda.synchronize()
+    L = _lib.lib()
+
+    def one_pass():
+        seq.rewind()
+        for _ in range(F):
+            seq.render_next()
+
+    clocks = ClockSampler(dev.index or 0) if rank == 0 else None
+    for _ in range(max(min(args.warmup, 3), 1)):
+        one_pass()
+    torch.cuda.synchronize()
+    if clocks is not None:
+        t_wait = time.time()
+        while not clocks.rows and time.time() - t_wait < 5.0:
+            time.sleep(0.05)
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    t0 = time.time()
+    e0.record()
+    for _ in range(args.steps):
+        one_pass()
+    e1.record()
+    torch.cuda.synchronize()
+    t1 = time.time()
+    if world > 1:
+        dist.barrier()
+    ms = e0.elapsed_time(e1)
+    clk = clocks.stop(t0, t1) if clocks else None
+    overflowed = seq.overflowed
+
+    # per-kernel durations of one eager frame loop
+    L.rg_profile_reset()
+    L.rg_profile_enable(1)
+    n_prof = min(F, 16)
+    with torch.no_grad():
+        for f in range(n_prof):
+            hp.forward(cam, {"local_rotation": seq.rot[f], "global_trans": seq.trans[f]})
+    torch.cuda.synchronize()
+    L.rg_profile_enable(0)
+    prof = _lib.profile_read()
+    L.rg_profile_reset()
+
+    # end to end: the pose sequence comes from pinned host memory every pass, every frame's image goes to pinned host memory
+    ring = [torch.empty(3, H, W).pin_memory() for _ in range(2)]
+    out_stream = torch.cuda.Stream(device=dev)
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    f0.record()
+    for _ in range(args.steps):
+        seq.load(rot_host, trans_host)
+        for _ in range(F):
+            slot, img = seq.render_next()
+            done = torch.cuda.Event()
+            done.record()
+            with torch.cuda.stream(out_stream):
+                out_stream.wait_event(done)
+                ring[slot].copy_(img, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(out_stream)
+            seq.release(slot, ev)
+    torch.cuda.current_stream().wait_stream(out_stream)
+    f1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms_e2e = f0.elapsed_time(f1)
+    if world > 1:
+        t = torch.tensor([ms, ms_e2e], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, ms_e2e = float(t[0]), float(t[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    with torch.no_grad():
+        out = hp.forward(cam, {"local_rotation": seq.rot[0], "global_trans": seq.trans[0]})
+    torch.cuda.synchronize()
+    P, R = scene.N, int(out["status"][0])
+    vis = int((out["radii"] > 0).sum())
+    in_P = 236 - (8 if args.isotropic else 0)
+    fwd_bytes = P * (in_P + 48) + R * 208 + H * W * 24       # SURVEY 8(d): B_fwd
+    own_fwd = P * (in_P + 60) + P * 64 + P * 40 + R * 4 + R * 44 + H * W * 24
+    frames = F_total * args.steps
+    frame_ms = ms / (args.steps * max(F, 1))
+    peaks = load_peaks()
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    kern = {k: {"ms_per_launch": v[0] / max(v[1], 1), "launches": v[1], "ms_per_frame": v[0] / n_prof} for k, v in prof.items()}
+    dom = max(kern, key=lambda k: kern[k]["ms_per_frame"]) if kern else None
+    per = {"skin_preprocess": P * (in_P + 60), "blend_forward": R * 44 + H * W * 24, "depth_sort": P * 64,
+           "tile_count": P * 20, "tile_scatter": P * 20 + R * 4, "tile_offsets": 0}
+    roof = None
+    if dom:
+        bts = per.get(dom, 0)
+        ach = bts / (kern[dom]["ms_per_launch"] * 1e-3) / 1e9
+        roof = {"kernel": dom, "bound": "hbm", "achieved": round(ach, 2), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
+                "traffic": None, "algorithmic_bytes_per_launch": bts, "ms_per_launch": round(kern[dom]["ms_per_launch"], 4),
+                "peak_source": "measured" if "hbm_gbs" in peaks else "fallback"}
+    line = {
+        "metric": "novel-pose frames/s (skin + rasterize, forward only)", "value": round(frames / (ms / 1e3), 3), "unit": "frames/s",
+        "n_gpus": world, "steps": args.steps, "warmup": max(min(args.warmup, 3), 1), "ms_per_step": round(ms / args.steps, 4),
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_string(args.workload, scene, W, H, args, world), "P": P, "visible": vis, "R_frame0": R,
+                   "HW": H * W, "frames_total": F_total, "frames_per_gpu": F, "ms_per_frame_per_gpu": round(frame_ms, 4),
+                   "step": "one pass over the whole sequence", "mlps": args.mlps,
+                   "l2": f"no explicit flush: one frame reads {P * in_P >> 20} MB of parameters (> 126 MB L2) and the pose changes every frame",
+                   "launch": "cuda graph replay, the graph advances its own frame index", "parallelism":
+                       (f"frames sharded contiguously over {world} GPUs, no collective" if world > 1 else "single GPU")},
+        "e2e": {"value": round(frames / (ms_e2e / 1e3), 3), "unit": "frames/s",
+                "h2d_bytes_per_step": int(rot_host.numel() * 4 + trans_host.numel() * 4), "d2h_bytes_per_step": int(F * 3 * H * W * 4)},
+        "gpu_launches": int(seq.launches_per_replay * F * args.steps),
+        "clocks": clk, "roofline": roof,
+        "step_hbm": {"algorithmic_bytes_per_frame": fwd_bytes, "frac_of_peak": round(fwd_bytes / (frame_ms * 1e-3) / 1e9 / peak, 4),
+                     "own_bytes_per_frame": own_fwd, "own_frac_of_peak": round(own_fwd / (frame_ms * 1e-3) / 1e9 / peak, 4), "peak": peak},
+        "kernels": {k: {kk: round(vv, 4) if isinstance(vv, float) else vv for kk, vv in v.items()} for k, v in kern.items()},
+        "instance_buffer_overflowed": bool(overflowed),
+    }
     _emit(line)
     if world > 1:
         dist.destroy_process_group()
@@ -411,20 +752,47 @@ def _count_rendered(hp, cam, pose):
 
 # ---------------------------------------------------------------------------------------------------------
 # CPU path: the oracle port (skin_oracle.py in torch on all host threads + raster_oracle.c with OpenMP)
-def cpu_step(scene, view, target):
+_CPU_MLPS = {}
+
+
+def _cpu_mlps(scene):
+    """The two per-Gaussian MLPs on the host (modules pinned to the reference's own, tests/test_mlp_front_end.py),
+    with the seeded weights the GPU arm uses (HotPath(mlps=True))."""
+    import torch
+    from riggs_b200 import skeleton_warp as sw
+    key = (scene.N, scene.J)
+    if key not in _CPU_MLPS:
+        torch.manual_seed(4321)
+        wm = sw.WeightMLP(3, scene.J - 1)
+        dn = sw.DeformMLP(4 * scene.J)
+        with torch.no_grad():
+            dn.gaussian_warp.weight.normal_(0, 1e-3)
+        _CPU_MLPS[key] = (wm, dn)
+    return _CPU_MLPS[key]
+
+
+def cpu_step(scene, view, target, mlps=False):
     """One full iteration on the host cores; returns the loss."""
     import numpy as np
     import torch
     from oracle import oracle_py as orc
     from oracle import skin_oracle as so
     import math
-    cam = scene.cameras[view]
-    p = scene.poses[view]
+    cam = scene.cameras[view % len(scene.cameras)]
+    p = scene.poses[view % len(scene.poses)]
     leaf = lambda t: t.clone().requires_grad_(True)
     xyz, sc_raw, rot_raw, op_raw = leaf(scene.xyz), leaf(scene.scaling_raw), leaf(scene.rotation_raw), leaf(scene.opacity_raw)
     fdc, frest = leaf(scene.features_dc), leaf(scene.features_rest)
     q, g, nr = leaf(p["local_rotation"]), leaf(p["global_trans"]), leaf(scene.node_radius_raw)
-    d = so.deform_by_pose(xyz, scene.joints, scene.parents, nr, q, g, scene.motion_mask)
+    mlp_w = offs = None
+    if mlps:
+        wm, dn = _cpu_mlps(scene)
+        for m in (wm, dn):
+            for prm in m.parameters():
+                prm.grad = None
+        mlp_w = wm(xyz.detach())
+        offs = dn(xyz.detach(), q.detach().reshape(-1)[None].expand(scene.N, -1))
+    d = so.deform_by_pose(xyz, scene.joints, scene.parents, nr, q, g, scene.motion_mask, mlp_w, offs)
     means3D, scales, rots, opac = so.activate(xyz, sc_raw, rot_raw, op_raw, d["d_xyz"], d["d_rotation"])
     shs = torch.cat([fdc, frest], 1)
     W, H = cam.image_width, cam.image_height
@@ -444,23 +812,31 @@ def cpu_step(scene, view, target):
     return float(loss)
 
 
+def _cpu_targets(scene):
+    import torch
+    cam = scene.cameras[0]
+    g = torch.Generator().manual_seed(1000)
+    return [torch.rand(3, cam.image_height, cam.image_width, generator=g) for _ in range(N_VIEWS)]
+
+
 def cpu_baseline(scene, args, budget_s=12.0):
     import torch
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     os.environ.setdefault("OMP_NUM_THREADS", str(cores))
-    cam = scene.cameras[0]
-    target = torch.rand(3, cam.image_height, cam.image_width, generator=torch.Generator().manual_seed(1000))
-    cpu_step(scene, 0, target)  # warm-up (also builds the oracle library)
+    targets = _cpu_targets(scene)
+    mlps = args.mlps == "on"
+    cpu_step(scene, 0, targets[0], mlps)  # warm-up (also builds the oracle library)
     n, t0 = 0, time.time()
     while True:
-        cpu_step(scene, 0, target)
+        cpu_step(scene, n, targets[n % N_VIEWS], mlps)
         n += 1
         if time.time() - t0 > budget_s or n >= 40:  # a bounded sample: ~10-15 s of host work
             break
     dt = (time.time() - t0) / n
-    return {"value": round(1.0 / dt, 4), "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{n} full {args.workload} iterations (skin_oracle.py torch-CPU + raster_oracle.c OpenMP), {dt:.2f} s each"}
+    return {"value": round(1.0 / dt, 4), "unit": UNIT, "cores": cores, "kind": "port", "cpu": cpu_model(),
+            "sample": f"{n} full {args.workload} iterations (skin_oracle.py torch-CPU + raster_oracle.c OpenMP"
+                      f"{', both MLPs in torch-CPU' if mlps else ''}), {dt:.2f} s each"}
 
 
 def run_reference(args):
@@ -472,34 +848,184 @@ def run_reference(args):
     import torch
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    scene = make_scene(args.workload, args.isotropic)
+    scene = make_scene(args.workload, args.isotropic, mode=args.mode)
     cam = scene.cameras[0]
-    target = torch.rand(3, cam.image_height, cam.image_width, generator=torch.Generator().manual_seed(1000))
-    for _ in range(min(args.warmup, 1)):
-        cpu_step(scene, 0, target)
+    W, H = cam.image_width, cam.image_height
+    if args.mode == "sequence":
+        return run_reference_sequence(args, scene, world, cores)
+    targets = _cpu_targets(scene)
+    mlps = args.mlps == "on"
+    warm = max(args.warmup, 3)
+    t_w = time.time()
+    for i in range(warm):
+        cpu_step(scene, i, targets[i % N_VIEWS], mlps)
+        if time.time() - t_w > 60:  # the warm-up is part of the contract, but a slow host must not eat the run
+            warm = i + 1
+            break
     t0 = time.time()
     steps = 0
-    for _ in range(args.steps):
-        cpu_step(scene, 0, target)
+    for i in range(args.steps):
+        cpu_step(scene, i, targets[i % N_VIEWS], mlps)
         steps += 1
         if time.time() - t0 > 150:  # keep the whole run within a few minutes
             break
     dt = (time.time() - t0) / steps
     v = round(1.0 / dt, 4)
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world, "steps": steps,
-            "warmup": min(args.warmup, 1), "ms_per_step": round(dt * 1e3, 2), "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"{args.workload}: {scene.N} Gaussians, {scene.J}-joint skeleton, "
-                                   f"{cam.image_width}x{cam.image_height}, 1 view/step, fwd+bwd on host cores"},
-            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+            "warmup": warm, "ms_per_step": round(dt * 1e3, 2), "higher_is_better": True,
+            "scaling": "strong" if args.views_per_step > 0 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_string(args.workload, scene, W, H, args, world),
+                       "where": "host cores; each step = one view fwd+bwd (a bounded sample of the workload)"},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "cpu": cpu_model(),
                              "sample": f"{steps} full iterations, oracle port (torch-CPU skinning + OpenMP C rasterizer)"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     _emit(line)
 
 
-def ref_cuda_baseline(scene, cam, pose, target, steps=10):
+def run_reference_sequence(args, scene, world, cores):
+    """Forward-only frames of the novel-pose sequence on the host cores (a bounded sample of frames)."""
+    import math
+    import numpy as np
+    import torch
+    from oracle import oracle_py as orc
+    from oracle import skin_oracle as so
+    cam = scene.cameras[0]
+    W, H = cam.image_width, cam.image_height
+    tfx, tfy = math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5)
+    view_m, proj_m, campos = cam.world_view_transform.numpy(), cam.full_proj_transform.numpy(), cam.camera_center.numpy()
+    shs = torch.cat([scene.features_dc, scene.features_rest], 1).numpy()
+    bg = np.zeros(3, np.float32)
+
+    def frame(f):
+        p = scene.poses[f % len(scene.poses)]
+        with torch.no_grad():
+            d = so.deform_by_pose(scene.xyz, scene.joints, scene.parents, scene.node_radius_raw, p["local_rotation"],
+                                  p["global_trans"], scene.motion_mask)
+            m, s, r, o = so.activate(scene.xyz, scene.scaling_raw, scene.rotation_raw, scene.opacity_raw, d["d_xyz"], d["d_rotation"])
+        orc.forward(m.numpy(), o.numpy(), view_m, proj_m, campos, W, H, tfx, tfy, bg, shs=shs, scales=s.numpy(), rotations=r.numpy())
+
+    frame(0)
+    n, t0 = 0, time.time()
+    while n < max(args.steps, 1) * 4 and time.time() - t0 < 120:
+        frame(n)
+        n += 1
+    dt = (time.time() - t0) / n
+    v = round(1.0 / dt, 4)
+    line = {"impl": "reference", "metric": "novel-pose frames/s (skin + rasterize, forward only)", "value": v, "unit": "frames/s",
+            "n_gpus": world, "steps": n, "warmup": 1, "ms_per_step": round(dt * 1e3, 2), "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_string(args.workload, scene, W, H, args, world), "where": "host cores; each step = one frame"},
+            "cpu_baseline": {"value": v, "unit": "frames/s", "cores": cores, "kind": "port", "cpu": cpu_model(),
+                             "sample": f"{n} frames of the sequence, oracle port"},
+            "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    _emit(line)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# BASELINE.md rows B1 / B2
+def reference_cpu_skinning():
+    """B1: the reference's torch CPU skinning path ALONE (skin_oracle.deform_by_pose, the restatement pinned to
+    SkeletonWarp.deform_by_pose) on C1 = 100 k Gaussians, J = 24, one frame, forward: all cores and one thread,
+    MLPs off and on.  The reference's own class is timed in the build container by profiles/tools/time_reference_skinning.py
+    (/root/reference does not travel to the GPU box)."""
+    import torch
+    from oracle import skin_oracle as so
+    from riggs_b200 import synth
+    scene = synth.make_config("C1")
+    wm, dn = _cpu_mlps(scene)
+    p = scene.poses[0]
+    cores = os.cpu_count() or 1
+
+    def run(mlps):
+        with torch.no_grad():
+            mw = off = None
+            if mlps:
+                mw = wm(scene.xyz)
+                off = dn(scene.xyz, p["local_rotation"].reshape(-1)[None].expand(scene.N, -1))
+            so.deform_by_pose(scene.xyz, scene.joints, scene.parents, scene.node_radius_raw, p["local_rotation"],
+                              p["global_trans"], scene.motion_mask, mw, off)
+
+    def timed(mlps, threads, reps):
+        torch.set_num_threads(threads)
+        run(mlps)
+        ts = []
+        for _ in range(reps):
+            t0 = time.time()
+            run(mlps)
+            ts.append(time.time() - t0)
+        ts.sort()
+        return round(ts[len(ts) // 2] * 1e3, 2)
+
+    out = {"workload": "C1: 100000 Gaussians, 24-joint skeleton, 1 frame, deform_by_pose forward", "cpu": cpu_model(),
+           "os_cpu_count": cores, "kind": "port (oracle/skin_oracle.py, pinned to the reference's SkeletonWarp.deform_by_pose)",
+           "mlps_off_all_cores_ms": timed(False, cores, 10), "mlps_off_1_thread_ms": timed(False, 1, 3),
+           "mlps_on_all_cores_ms": timed(True, cores, 5), "mlps_on_1_thread_ms": timed(True, 1, 1)}
+    torch.set_num_threads(cores)
+    out["torch_num_threads"] = torch.get_num_threads()
+    return out
+
+
+def reference_cuda_rasterizer(workloads):
+    """B2: the reference's CUDA rasterizer ALONE (oracle/_ref, unmodified sources), forward and backward of one view, CUDA
+    events on the legacy default stream it launches on, beside this library's reference-shaped entry on the same inputs."""
+    try:
+        import torch
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import helpers
+        from oracle import ref_cuda
+        from riggs_b200 import synth
+        if not ref_cuda.available():
+            return {"unavailable": "oracle/_ref/libref_riggs.so not built"}
+        rows = {}
+        for name in workloads:
+            scene = synth.make_config(name, n_views=1, n_poses=1) if name != "C5" else synth.make_config(name, n_poses=2)
+            cin = helpers.to_cuda(helpers.raster_inputs(scene, view=0))
+            cots = [t.cuda() for t in synth.seeded_cotangents(cin["H"], cin["W"])]
+            ref = ref_cuda.RefRasterizer()
+
+            def fwd():
+                return ref.forward(cin["bg"], cin["means3D"], cin["opacities"], cin["view"], cin["proj"], cin["campos"], cin["W"],
+                                   cin["H"], cin["tanfovx"], cin["tanfovy"], shs=cin["shs"], scales=cin["scales"], rotations=cin["rotations"])
+
+            def bwd(f):
+                return ref.backward(cin["bg"], cin["means3D"], f["radii"], f["alpha"], cin["view"], cin["proj"], cin["campos"],
+                                    cin["tanfovx"], cin["tanfovy"], cots[0], cots[1], cots[2], shs=cin["shs"], scales=cin["scales"],
+                                    rotations=cin["rotations"])
+
+            def ev_time(fn, reps=5):
+                fn()
+                ts = []
+                for _ in range(reps):
+                    torch.cuda.synchronize()
+                    t0 = time.perf_counter()
+                    r = fn()
+                    torch.cuda.synchronize()
+                    ts.append((time.perf_counter() - t0) * 1e3)
+                ts.sort()
+                return ts[len(ts) // 2], r
+
+            t_f, f = ev_time(fwd)
+            t_b, _ = ev_time(lambda: bwd(f))
+            # ours, reference-shaped entry, same inputs
+            st = helpers.ours_forward(cin)
+            t_of, _ = ev_time(lambda: helpers.ours_forward(cin) and None)
+            t_ob, _ = ev_time(lambda: helpers.ours_backward(cin, st, cots) and None)
+            rows[name] = {"P": scene.N, "R": int(f["num_rendered"]), "W": cin["W"], "H": cin["H"],
+                          "reference_forward_ms": round(t_f, 3), "reference_backward_ms": round(t_b, 3),
+                          "ours_reference_shaped_forward_ms_incl_state_decode": round(t_of, 3),
+                          "ours_reference_shaped_backward_ms": round(t_ob, 3)}
+            del cin, cots, ref, st, f
+            torch.cuda.empty_cache()
+        rows["how"] = ("median of 5, host timer between device synchronisations (the reference binding allocates its outputs and "
+                       "launches on the legacy default stream; its forward includes one blocking 4-byte read-back)")
+        return rows
+    except Exception as ex:
+        return {"unavailable": repr(ex)[:200]}
+
+
+def ref_cuda_baseline(scene, cam, pose, target, steps=10, mlps=None):
     """Context number asked by the north star: the reference's own CUDA rasterizer (compiled unmodified,
-    oracle/_ref) behind an eager-torch skinning chain on the same B200.  Not the reference arm."""
+    oracle/_ref) behind an eager-torch skinning chain on the same B200, with the share of each stage.  Not the reference arm."""
     try:
         import math
         import torch
@@ -521,34 +1047,57 @@ def ref_cuda_baseline(scene, cam, pose, target, steps=10):
         tfx, tfy = math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5)
         bg = torch.zeros(3, device=dev)
         view_m, proj_m, campos = cam.world_view_transform.contiguous(), cam.full_proj_transform.contiguous(), cam.camera_center.contiguous()
+        stage = {"skinning_forward": 0.0, "rasterizer_forward": 0.0, "rasterizer_backward": 0.0, "skinning_backward": 0.0}
 
-        def step():
+        def lap(key, t0):
+            torch.cuda.synchronize()
+            stage[key] += time.perf_counter() - t0
+            return time.perf_counter()
+
+        def step(record):
+            t0 = time.perf_counter()
             q = pose["local_rotation"].detach().clone().requires_grad_(True)
             g = pose["global_trans"].detach().clone().requires_grad_(True)
-            d = so.deform_by_pose(xyz, joints, parents, nr, q, g, mask)
+            mw = off = None
+            if mlps is not None:  # the same torch modules the GPU arm's reference would run eagerly (cuBLAS)
+                mw = mlps.weight_mlp(xyz.detach())
+                off = mlps.detail_net(xyz.detach(), q.detach().reshape(-1)[None].expand(xyz.shape[0], -1))
+            d = so.deform_by_pose(xyz, joints, parents, nr, q, g, mask, mw, off)
             means3D, scales, rots, opac = so.activate(xyz, sc_raw, rot_raw, op_raw, d["d_xyz"], d["d_rotation"])
             shs = torch.cat([fdc, frest], 1)
             a = [t.detach().contiguous() for t in (means3D, opac, shs, scales, rots)]
+            if record:
+                t0 = lap("skinning_forward", t0)
             f = ref.forward(bg, a[0], a[1], view_m, proj_m, campos, W, H, tfx, tfy, shs=a[2], scales=a[3], rotations=a[4])
+            if record:
+                t0 = lap("rasterizer_forward", t0)
             gimg = (torch.sign(f["color"] - target) / target.numel()).contiguous()
             z = torch.zeros(1, H, W, device=dev)
             gr = ref.backward(bg, a[0], f["radii"], f["alpha"], view_m, proj_m, campos, tfx, tfy, gimg, z, z, shs=a[2],
                               scales=a[3], rotations=a[4])
+            if record:
+                t0 = lap("rasterizer_backward", t0)
             torch.autograd.backward([means3D, scales, rots, opac, shs],
                                     [gr["dmean3D"], gr["dscale"], gr["drot"], gr["dopacity"], gr["dsh"]])
             for t in (xyz, sc_raw, rot_raw, op_raw, fdc, frest, nr):
                 t.grad = None
+            if record:
+                lap("skinning_backward", t0)
 
         for _ in range(3):
-            step()
+            step(False)
         torch.cuda.synchronize()
         t0 = time.time()
         for _ in range(steps):
-            step()
+            step(False)
         torch.cuda.synchronize()
         dt = (time.time() - t0) / steps
+        for _ in range(3):
+            step(True)
         return {"value": round(1.0 / dt, 3), "unit": UNIT, "ms_per_step": round(dt * 1e3, 3),
-                "what": "eager-torch skinning on CUDA + the reference's CUDA rasterizer (oracle/_ref, unmodified sources) fwd+bwd"}
+                "stages_ms": {k: round(v / 3 * 1e3, 3) for k, v in stage.items()},
+                "what": "eager-torch skinning on CUDA + the reference's CUDA rasterizer (oracle/_ref, unmodified sources) fwd+bwd"
+                        + (", both MLPs eager torch/cuBLAS" if mlps is not None else "")}
     except Exception as ex:  # context number only: never fail the bench for it
         return {"unavailable": repr(ex)[:200]}
 

@@ -361,7 +361,12 @@ int rg_knn_points(int N, int M, int D, int K, const float* points, const float* 
 /* rg_skinned_backward in parts, for callers that overlap the gradient all-reduce with the backward: `phases` is a bit
  * set -- 1: zero the accumulators and run the blend backward, 2: per-Gaussian backward (parameter gradients) of rows
  * [row_begin, row_end) only (row_begin a multiple of 256), 4: skeleton backward (d_local_rot, d_global_trans,
- * d_node_radius_raw).  Running 1, then 2 over consecutive row chunks, then 4 equals rg_skinned_backward. */
+ * d_node_radius_raw).  Running 1, then 2 over consecutive row chunks, then 4 equals rg_skinned_backward.
+ * Bit 8 (with 2 and/or 4): the gradients of the PARAMETERS -- d_xyz, d_scaling_raw, d_rotation_raw, d_opacity_raw,
+ * d_features_dc, d_features_rest, d_node_radius_raw -- are ADDED to what the buffers hold instead of overwriting it
+ * (the second and later views of a multi-view batch: configs of several views per optimiser step; the reference
+ * gets the same sum from autograd accumulating into .grad).  Per-view outputs (d_mean2D, d_local_rot, d_global_trans,
+ * d_mask, d_mlp_weight, d_offsets) are always overwritten. */
 int rg_skinned_backward_part(const RgSkinnedScene* scene, const RgWorkspace* ws, int phases, int row_begin, int row_end,
                              const int* radii, const float* alphas, const float* dL_dcolor, const float* dL_ddepth,
                              const float* dL_dalpha, const float* dL_dnodes, float* d_xyz, float* d_scaling_raw,

@@ -10,6 +10,12 @@
 using namespace rg;
 
 namespace {
+// d_node_radius_raw leaves the workspace's accumulator either as a copy or, for the later views of a batch, as a sum
+__global__ void small_copy_or_add_kernel(float* __restrict__ dst, const float* __restrict__ src, int n, int add) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = add ? dst[i] + src[i] : src[i];
+}
+
 char* abase(char* p) { return reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(p), 256)); }
 bool al16(const void* p) { return (reinterpret_cast<size_t>(p) & 15) == 0; }
 
@@ -118,7 +124,8 @@ int rg_skinned_status(const RgSkinnedScene* s, const RgWorkspace* w, uint32_t* h
 }
 
 // phases: 1 = zero the accumulators + blend backward, 2 = per-Gaussian backward of rows [row_begin, row_end),
-// 4 = skeleton backward.  rg_skinned_backward runs 1|2|4 over all rows; a data-parallel caller runs 1, then 2 chunk by
+// 4 = skeleton backward, 8 = ADD into the parameter gradients (d_xyz .. d_features_rest, d_node_radius_raw) instead of
+// overwriting them: the second and later views of a multi-view batch.  rg_skinned_backward runs 1|2|4 over all rows; a data-parallel caller runs 1, then 2 chunk by
 // chunk (all-reducing each chunk's finished gradient rows on another stream meanwhile), then 4.
 int rg_skinned_backward_part(const RgSkinnedScene* s, const RgWorkspace* w, int phases, int row_begin, int row_end,
                              const int* radii, const float* alphas, const float* dL_dcolor, const float* dL_ddepth,
@@ -170,6 +177,7 @@ int rg_skinned_backward_part(const RgSkinnedScene* s, const RgWorkspace* w, int 
         sb.d_features_dc = d_features_dc; sb.d_features_rest = d_features_rest;
         sb.dG = fk.dG; sb.dnode_radius_raw = fk.dradius; sb.dglobal_trans = fk.dtrans;
         sb.dmask = d_mask; sb.dmlp_weight = d_mlp_weight; sb.doffsets = d_offsets;
+        sb.accumulate = (phases & 8) != 0;
         if (launch_gauss_skin_backward(ga, sb, stream)) return -1;
     }
     if (phases & 4) {
@@ -177,7 +185,7 @@ int rg_skinned_backward_part(const RgSkinnedScene* s, const RgWorkspace* w, int 
                                d_global_trans, fk.dtrans, stream))
             return -1;
         if (d_node_radius_raw)
-            cudaMemcpyAsync(d_node_radius_raw, fk.dradius, sizeof(float) * s->J, cudaMemcpyDeviceToDevice, stream);
+            small_copy_or_add_kernel<<<1, 128, 0, stream>>>(d_node_radius_raw, fk.dradius, s->J, (phases & 8) != 0);
     }
     return check_launch("rg_skinned_backward", stream, false);
 }

@@ -58,6 +58,16 @@ __device__ __forceinline__ void bulk_store(void* gmem_dst, const void* smem_src,
     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }
 
+// Shared -> global bulk REDUCTION: global[i] += shared[i] for `bytes / 4` floats, performed by the copy engine at the
+// L2 (no read-back into the SM).  Same calling convention as bulk_store.
+__device__ __forceinline__ void bulk_reduce_add_f32(void* gmem_dst, const void* smem_src, uint32_t bytes) {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(gmem_dst),
+                 "r"(smem_u32(smem_src)), "r"(bytes)
+                 : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+
 // The issuing thread must not let shared memory go away (CTA exit) before the engine has read it.
 __device__ __forceinline__ void bulk_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 

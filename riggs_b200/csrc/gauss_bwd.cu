@@ -295,13 +295,26 @@ __global__ void __launch_bounds__(256, 3) gauss_backward_kernel(GaussBwdArgs a, 
     const float4 drot_raw = {(dq.x - q.x * ndg) / qnorm, (dq.y - q.y * ndg) / qnorm, (dq.z - q.z * ndg) / qnorm,
                              (dq.w - q.w * ndg) / qnorm};
     if (in_range) {
-        s.d_xyz[3 * i] = dL_dmean.x; s.d_xyz[3 * i + 1] = dL_dmean.y; s.d_xyz[3 * i + 2] = dL_dmean.z;
-        a.dL_dmean2D[3 * i] = g_mean2D.x; a.dL_dmean2D[3 * i + 1] = g_mean2D.y; a.dL_dmean2D[3 * i + 2] = 0.f;
-        if (s.f.isotropic) s.d_scaling_raw[i] = (ds.x + ds.y + ds.z) * sc.x;
-        else { s.d_scaling_raw[3 * i] = ds.x * sc.x; s.d_scaling_raw[3 * i + 1] = ds.y * sc.y; s.d_scaling_raw[3 * i + 2] = ds.z * sc.z; }
-        reinterpret_cast<float4*>(s.d_rotation_raw)[i] = drot_raw;
-        s.d_opacity_raw[i] = g_opacity * opacity_act * (1.f - opacity_act);
-        s.d_features_dc[3 * i] = basis[0] * gsh[0]; s.d_features_dc[3 * i + 1] = basis[0] * gsh[1]; s.d_features_dc[3 * i + 2] = basis[0] * gsh[2];
+        a.dL_dmean2D[3 * i] = g_mean2D.x; a.dL_dmean2D[3 * i + 1] = g_mean2D.y; a.dL_dmean2D[3 * i + 2] = 0.f;  // per view
+        const float dsc0 = ds.x * sc.x, dsc1 = ds.y * sc.y, dsc2 = ds.z * sc.z;
+        const float dop = g_opacity * opacity_act * (1.f - opacity_act);
+        if (!s.accumulate) {
+            s.d_xyz[3 * i] = dL_dmean.x; s.d_xyz[3 * i + 1] = dL_dmean.y; s.d_xyz[3 * i + 2] = dL_dmean.z;
+            if (s.f.isotropic) s.d_scaling_raw[i] = dsc0 + dsc1 + dsc2;
+            else { s.d_scaling_raw[3 * i] = dsc0; s.d_scaling_raw[3 * i + 1] = dsc1; s.d_scaling_raw[3 * i + 2] = dsc2; }
+            reinterpret_cast<float4*>(s.d_rotation_raw)[i] = drot_raw;
+            s.d_opacity_raw[i] = dop;
+            s.d_features_dc[3 * i] = basis[0] * gsh[0]; s.d_features_dc[3 * i + 1] = basis[0] * gsh[1]; s.d_features_dc[3 * i + 2] = basis[0] * gsh[2];
+        } else if (visible) {  // a row belongs to one thread: plain read-modify-write
+            s.d_xyz[3 * i] += dL_dmean.x; s.d_xyz[3 * i + 1] += dL_dmean.y; s.d_xyz[3 * i + 2] += dL_dmean.z;
+            if (s.f.isotropic) s.d_scaling_raw[i] += dsc0 + dsc1 + dsc2;
+            else { s.d_scaling_raw[3 * i] += dsc0; s.d_scaling_raw[3 * i + 1] += dsc1; s.d_scaling_raw[3 * i + 2] += dsc2; }
+            float4 r = reinterpret_cast<float4*>(s.d_rotation_raw)[i];
+            r.x += drot_raw.x; r.y += drot_raw.y; r.z += drot_raw.z; r.w += drot_raw.w;
+            reinterpret_cast<float4*>(s.d_rotation_raw)[i] = r;
+            s.d_opacity_raw[i] += dop;
+            s.d_features_dc[3 * i] += basis[0] * gsh[0]; s.d_features_dc[3 * i + 1] += basis[0] * gsh[1]; s.d_features_dc[3 * i + 2] += basis[0] * gsh[2];
+        }
     }
     // d_features_rest: every thread drops its row into the staging block (all SH rows have been read into registers
     // by now), then the block leaves the SM as one bulk store (or a cooperative coalesced copy for a ragged tail).
@@ -321,7 +334,12 @@ __global__ void __launch_bounds__(256, 3) gauss_backward_kernel(GaussBwdArgs a, 
         float* dst = s.d_features_rest + sh_first * sh_row;
         const bool st_bulk = (sh_bytes % 16 == 0) && ((reinterpret_cast<size_t>(dst) & 15) == 0) && sh_bytes > 0;
         if (st_bulk) {
-            if (threadIdx.x == 0) bulk_store(dst, s_sh, sh_bytes);
+            if (threadIdx.x == 0) {
+                if (s.accumulate) bulk_reduce_add_f32(dst, s_sh, sh_bytes);
+                else bulk_store(dst, s_sh, sh_bytes);
+            }
+        } else if (s.accumulate) {
+            for (int k = threadIdx.x; k < (int)(sh_bytes / 4); k += blockDim.x) dst[k] += s_sh[k];
         } else {
             for (int k = threadIdx.x; k < (int)(sh_bytes / 4); k += blockDim.x) dst[k] = s_sh[k];
         }

@@ -80,6 +80,9 @@ struct SkinFuseBwdArgs {
     float* dmask;
     float* dmlp_weight;
     float* doffsets;
+    // multi-view batches: ADD into the six parameter-gradient tensors instead of overwriting them (a culled Gaussian
+    // then adds nothing); d_features_rest goes through the copy engine's bulk reduction
+    bool accumulate;
 };
 
 int launch_preprocess(const PreprocessArgs& a, cudaStream_t stream);

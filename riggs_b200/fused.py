@@ -66,6 +66,18 @@ class WorkspacePool:
         P, W, H = ws.key
         self.free.setdefault((P, W, H, str(device)), []).append(ws)
 
+    def reserve(self, P, W, H, device, num_rendered: int):
+        """Sizes the binning buffers of this shape for `num_rendered` instances (times the headroom): call it with
+        the largest count seen over a pass of the training views (``measure_instances``) so that no later view
+        overflows a buffer that was sized from the first frame alone."""
+        key = (P, W, H, str(device))
+        want = int(_lib.lib().rg_binning_bytes(int(num_rendered * self.headroom) + 256))
+        if want > self.capacity_bytes.get(key, 0):
+            self.capacity_bytes[key] = want
+            for ws in self.free.get(key, []):
+                if ws.binning.numel() < want:
+                    ws.grow_binning(want)
+
     def note_capacity(self, ws, device):
         P, W, H = ws.key
         key = (P, W, H, str(device))
@@ -182,16 +194,24 @@ class _SkinnedRender(torch.autograd.Function):
         ctx.dev = dev
         ctx.grad_out = cfg.get("grad_out")
         ctx.reduce = cfg.get("reduce")
+        ctx.accumulate = bool(cfg.get("accumulate"))
+        if ctx.accumulate and not ctx.grad_out:
+            raise _lib.RiggsError("render_skinned(accumulate=True) adds into caller-owned buffers: pass grad_out")
         if not any(ctx.needs_input_grad):
             ctx.lease.release()  # inference: the state is not needed any more
         ctx.shapes = (P, J, W, H, M_rest, isotropic)
         ctx.save_for_backward(radii, alpha)
         ctx.mark_non_differentiable(radii)
         ctx.num_rendered_host = ws.status  # valid after the next synchronisation
+        cfg["_status"] = ws.status
         return color, depth, alpha, radii, d_nodes
 
     @staticmethod
     def backward(ctx, g_color, g_depth, g_alpha, _g_radii, g_nodes):
+        if ctx.ws is None:
+            # the forward state lives in a pooled workspace that went back to the pool after the first backward
+            raise _lib.RiggsError("render_skinned: backward was already run for this frame (the workspace holding its "
+                                  "forward state has been released); render the frame again for a second backward")
         radii, alpha = ctx.saved_tensors
         P, J, W, H, M_rest, isotropic = ctx.shapes
         dev = ctx.dev
@@ -236,8 +256,10 @@ class _SkinnedRender(torch.autograd.Function):
             if red is not None and red.can_overlap(P) and all(n in go for n in red.names):
                 # Data parallel: the parameter gradients go straight into the ranks' peer-mapped flat buffer, and the
                 # rows of chunk c are summed over the ranks on a second stream while chunk c+1 is computed here.
+                acc = 8 if ctx.accumulate else 0
                 part = lambda phases, r0, r1: check(L.rg_skinned_backward_part(
-                    C.byref(ctx.scene), C.byref(ctx.ws.c), phases, r0, r1, *args, stream_ptr()), "rg_skinned_backward_part")
+                    C.byref(ctx.scene), C.byref(ctx.ws.c), phases | (acc if phases & 6 else 0), r0, r1, *args, stream_ptr()),
+                    "rg_skinned_backward_part")
                 main = torch.cuda.current_stream()
                 side = _side_stream(dev)
                 chunks = red.row_chunks(P)
@@ -253,6 +275,9 @@ class _SkinnedRender(torch.autograd.Function):
                         side.wait_event(ev)
                         red.all_reduce_rows(P, r0, r1, with_rest=last, barrier_after=last)
                 main.wait_stream(side)
+            elif ctx.accumulate:  # a later view of a multi-view batch: add into the parameter-gradient buffers
+                check(L.rg_skinned_backward_part(C.byref(ctx.scene), C.byref(ctx.ws.c), 7 | 8, 0, P, *args, stream_ptr()),
+                      "rg_skinned_backward_part")
             else:
                 check(L.rg_skinned_backward(C.byref(ctx.scene), C.byref(ctx.ws.c), *args, stream_ptr()), "rg_skinned_backward")
         ctx.lease.release()
@@ -269,7 +294,8 @@ class _SkinnedRender(torch.autograd.Function):
 
 def render_skinned(viewpoint_camera, pc, skeleton, pose: Dict[str, torch.Tensor], pipe, bg_color: torch.Tensor,
                    scaling_modifier=1.0, mlp_weight=None, offsets=None, zero_d_rotation: Optional[bool] = None,
-                   debug_outputs=None, pool: Optional[WorkspacePool] = None, grad_out=None, reduce=None):
+                   debug_outputs=None, pool: Optional[WorkspacePool] = None, grad_out=None, reduce=None,
+                   accumulate: bool = False):
     """Fused deform + render.  ``pc``: object with the GaussianModel raw tensors (_xyz, _scaling, _rotation, _opacity,
     _features_dc, _features_rest, motion_mask, active_sh_degree); ``skeleton``: riggs_b200 SkeletonWarp (joints,
     parents, _node_radius); ``pose``: {'local_rotation': (J,4), 'global_trans': (3,)}.
@@ -277,7 +303,10 @@ def render_skinned(viewpoint_camera, pc, skeleton, pose: Dict[str, torch.Tensor]
     features_rest, node_radius) the backward kernels write into directly -- e.g. the views of ``dist.FlatGrads``.
     ``reduce``: that ``dist.FlatGrads`` itself; when its buffer is peer-mapped the backward sums the gradient over the
     ranks chunk by chunk while it is still computing later chunks (``FlatGrads.all_reduce`` then has nothing left to do).
-    Returns the dict of ``render()`` plus ``d_nodes``."""
+    ``accumulate``: the backward ADDS the parameter gradients into ``grad_out`` instead of overwriting them -- the second
+    and later views of a multi-view batch (rg_skinned_backward_part, phase bit 8).
+    Returns the dict of ``render()`` plus ``d_nodes`` and ``status``: a pinned host tensor {num_rendered, overflow}
+    that is valid once the stream has been synchronised (``frame_overflowed``)."""
     xyz = pc._xyz
     # the reference's dummy leaf whose .grad receives dL/dmean2D (gaussian_renderer/__init__.py:45-49); its values are
     # never read, so every call wraps the same zero buffer in a new leaf instead of filling a fresh one
@@ -295,11 +324,43 @@ def render_skinned(viewpoint_camera, pc, skeleton, pose: Dict[str, torch.Tensor]
                viewmatrix=f32c(viewpoint_camera.world_view_transform), projmatrix=f32c(viewpoint_camera.full_proj_transform),
                campos=f32c(viewpoint_camera.camera_center), bg=f32c(bg_color),
                zero_d_rotation=isotropic if zero_d_rotation is None else zero_d_rotation, debug_outputs=debug_outputs,
-               pool=pool, grad_out=grad_out, reduce=reduce)
+               pool=pool, grad_out=grad_out, reduce=reduce, accumulate=accumulate)
     mm = getattr(pc, "_motion_mask", None)
     mask = mm.reshape(-1) if mm is not None else None
     color, depth, alpha, radii, d_nodes = _SkinnedRender.apply(
         xyz, pc._scaling, pc._rotation, pc._opacity, pc._features_dc, pc._features_rest, skeleton._node_radius,
         pose["local_rotation"], pose["global_trans"], mask, mlp_weight, offsets, screenspace_points, cfg)
     return {"render": color, "viewspace_points": screenspace_points, "visibility_filter": radii > 0, "radii": radii,
-            "depth": depth, "alpha": alpha, "bg_color": bg_color, "d_nodes": d_nodes}
+            "depth": depth, "alpha": alpha, "bg_color": bg_color, "d_nodes": d_nodes, "status": cfg.get("_status")}
+
+
+def frame_overflowed(out) -> bool:
+    """True when the frame `out` (a ``render_skinned`` result) produced more (Gaussian, tile) instances than the
+    workspace's instance buffer holds: the image and the gradients of that frame are incomplete and must not reach the
+    optimiser.  Synchronises the current stream (call it where the loss is read on the host anyway).  The next
+    ``render_skinned`` of the same shape grows the buffer; render the frame again."""
+    torch.cuda.current_stream().synchronize()
+    st = out.get("status")
+    return st is not None and int(st[1]) != 0
+
+
+def measure_instances(viewpoint_cameras, pc, skeleton, poses, pipe, bg_color, pool: Optional[WorkspacePool] = None,
+                      **kw) -> int:
+    """Renders every (camera, pose) pair once without gradients, reads each frame's instance count on the host and sizes
+    the pool's instance buffers for the LARGEST one (``WorkspacePool.reserve``).  Returns that count.  Run it once over
+    the training views before the first step (and after densification): later frames then cannot overflow a buffer that
+    the first frame alone would have sized."""
+    pool = pool or _POOL
+    r_max = 0
+    xyz = pc._xyz
+    with torch.no_grad():
+        for cam, pose in zip(viewpoint_cameras, poses):
+            out = render_skinned(cam, pc, skeleton, pose, pipe, bg_color, pool=pool, **kw)
+            torch.cuda.current_stream().synchronize()
+            if int(out["status"][1]) != 0:  # grown by the next call; the count is valid even for an overflowed frame
+                pool.reserve(xyz.shape[0], int(cam.image_width), int(cam.image_height), xyz.device, int(out["status"][0]))
+            r_max = max(r_max, int(out["status"][0]))
+    if viewpoint_cameras:
+        cam = viewpoint_cameras[0]
+        pool.reserve(xyz.shape[0], int(cam.image_width), int(cam.image_height), xyz.device, r_max)
+    return r_max

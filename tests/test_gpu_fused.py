@@ -447,3 +447,113 @@ def test_fused_gradients_against_float64_arbiter(name):
 
 
 F64_CEIL = 2e-3
+
+
+def _view_inputs(scene, n):
+    cams = [c.to("cuda") for c in scene.cameras[:n]]
+    H, W = cams[0].image_height, cams[0].image_width
+    g = torch.Generator().manual_seed(8)
+    targets = [torch.rand(3, H, W, generator=g).cuda() for _ in range(n)]
+    poses = [{k: v.cuda() for k, v in p.items()} for p in scene.poses[:n]]
+    return cams, poses, targets
+
+
+def test_multi_view_batch_accumulates_parameter_gradients():
+    """Several views per optimiser step on one GPU (BASELINE configs C3 / C4): the first view's backward overwrites
+    the flat gradient buffer, later views ADD to it (rg_skinned_backward_part, phase bit 8; d_features_rest through the
+    copy engine's bulk reduction).  The result must be the sum of the single-view gradients -- eagerly and replayed from
+    one captured graph -- and the per-view pose gradients must stay those of their own view."""
+    from riggs_b200.hotpath import GraphedStep, HotPath
+    scene = synth.make_config("small", n_views=3)
+    hp = HotPath(scene, device="cuda")
+    cams, poses, targets = _view_inputs(scene, 3)
+
+    def single(i):
+        hp.zero_grad()
+        ps = {k: v.clone().requires_grad_(True) for k, v in poses[i].items()}
+        loss = hp.step(cams[i], ps, targets[i])
+        return float(loss), {n: p.grad.clone() for n, p in hp.named_parameters()}, {k: v.grad.clone() for k, v in ps.items()}
+
+    singles = [single(i) for i in range(3)]
+    want = {n: sum(s[1][n] for s in singles) for n, _ in hp.named_parameters()}
+
+    ps = [{k: v.clone().requires_grad_(True) for k, v in p.items()} for p in poses]
+    hp.zero_grad()
+    losses = hp.step_views(cams, ps, targets)
+    hp.reduce_grads()  # single process: only exposes the flat buffer through param.grad
+    torch.cuda.synchronize()
+    for i in range(3):
+        assert abs(float(losses[i]) - singles[i][0]) <= 1e-6
+        for k in ps[i]:
+            assert helpers.rel_err(ps[i][k].grad.cpu().numpy(), singles[i][2][k].cpu().numpy(), floor=1e-7) <= 1e-4, (i, k)
+    for n, p in hp.named_parameters():
+        assert helpers.rel_err(p.grad.cpu().numpy(), want[n].cpu().numpy(), floor=1e-7) <= 1e-4, n
+        assert helpers.rel_l2(p.grad.cpu().numpy(), want[n].cpu().numpy()) <= 1e-4, n
+
+    gs = GraphedStep(hp, cams, poses, targets)
+    for _ in range(2):  # a second replay must not add to the first one's sums
+        losses = gs.step()
+        torch.cuda.synchronize()
+        assert not gs.overflowed
+        assert losses.shape == (3,)
+        for n, p in hp.named_parameters():
+            assert helpers.rel_err(p.grad.cpu().numpy(), want[n].cpu().numpy(), floor=1e-7) <= 1e-4, n
+
+
+def test_rotating_steps_visit_resident_views_without_copies():
+    from riggs_b200.hotpath import HotPath, RotatingSteps
+    scene = synth.make_config("small", n_views=4)
+    hp = HotPath(scene, device="cuda")
+    cams, poses, targets = _view_inputs(scene, 4)
+    want = []
+    for i in range(4):
+        hp.zero_grad()
+        ps = {k: v.clone().requires_grad_(True) for k, v in poses[i].items()}
+        want.append((float(hp.step(cams[i], ps, targets[i])), hp.pc._xyz.grad.clone()))
+    rot = RotatingSteps(hp, cams, poses, targets, views_per_step=1)
+    assert rot.max_instances > 0 and len(rot.slots) == 4
+    for n in range(6):
+        loss = rot.step()
+        torch.cuda.synchronize()
+        assert not rot.overflowed
+        wl, wg = want[n % 4]
+        assert abs(float(loss) - wl) <= 1e-6
+        assert helpers.rel_err(hp.pc._xyz.grad.cpu().numpy(), wg.cpu().numpy(), floor=1e-7) <= 1e-4
+
+
+def test_pose_sequence_renderer_renders_every_frame_of_the_sequence():
+    """Forward-only novel-pose sequence (render_rig.py:250-334): the graph that picks its own frame out of the resident
+    pose sequence gives, frame by frame, the image of an eager render_skinned call with that pose."""
+    from riggs_b200.fused import WorkspacePool, render_skinned
+    from riggs_b200.hotpath import HotPath, PoseSequenceRenderer
+    scene = synth.make_config("small", n_views=1, n_poses=12, pose_sequence=True)
+    hp = HotPath(scene, device="cuda")
+    cam = scene.cameras[0].to("cuda")
+    rot = torch.stack([p["local_rotation"] for p in scene.poses]).pin_memory()
+    trans = torch.stack([p["global_trans"] for p in scene.poses]).pin_memory()
+    seq = PoseSequenceRenderer(hp, cam, scene.J, max_frames=16)
+    seq.load(rot, trans)
+    pool = WorkspacePool()
+    for rep in range(2):
+        seq.rewind()
+        for f in range(12):
+            slot, img = seq.render_next()
+            got = img.clone()
+            with torch.no_grad():
+                want = render_skinned(cam, hp.pc, hp.warp, {k: v.cuda() for k, v in scene.poses[f].items()}, _Pipe(),
+                                      hp.bg, pool=pool)["render"]
+            assert torch.equal(got, want), (rep, f)
+    assert not seq.overflowed
+    assert seq.launches_per_replay >= 8
+
+
+def test_second_backward_raises_a_clear_error():
+    from riggs_b200 import _lib
+    from riggs_b200.fused import WorkspacePool, render_skinned
+    scene, pc, warp, cam = _setup("tiny", dict(n_views=1))
+    pose, _, _ = _leafs(scene)
+    out = render_skinned(cam, pc, warp, pose, _Pipe(), torch.zeros(3, device="cuda"), pool=WorkspacePool())
+    loss = out["render"].sum()
+    loss.backward(retain_graph=True)
+    with pytest.raises(_lib.RiggsError, match="already run"):
+        loss.backward()
