@@ -159,7 +159,9 @@ class HotPath:
     def step(self, cam, pose, target: torch.Tensor, accumulate: bool = False, last_view: bool = True) -> torch.Tensor:
         """Forward + backward of one view; returns the (device) loss.  Gradients accumulate in .grad."""
         out = self.forward(cam, pose, accumulate=accumulate, last_view=last_view)
-        self.last_out = out  # radii / viewspace_points / status of the last view (densification statistics, overflow check)
+        # radii / viewspace_points / status of the last view (densification statistics, overflow check); nothing that
+        # carries a grad_fn is kept: a graph held across steps keeps its AccumulateGrad nodes (and their stream) alive
+        self.last_out = {k: out[k] for k in ("radii", "viewspace_points", "status")}
         if self.lambda_dssim > 0.0:
             loss, grad, _l1, _ssim = image_loss_and_grad(out["render"], target, self.lambda_dssim)
         else:
