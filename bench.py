@@ -325,8 +325,8 @@ def run_ours(args):
     overflowed = bool(rot.overflowed) if rot is not None else False
     # kernels of this library inside the timed region (a replayed graph launches what its capture recorded)
     launches = rot.launches_per_replay * args.steps if rot is not None else L.rg_launch_count() - launches0
-    if world > 1 and rot is not None:
-        launches += args.steps  # the all-reduce kernel, launched eagerly after each replay
+    if world > 1 and rot is not None and not rot.slots[0]._reduces_in_graph:
+        launches += args.steps  # the all-reduce kernel, launched eagerly after each replay (NCCL fallback: not ours, not counted)
     clk = clocks.stop(t0, t1) if clocks else None
 
     # ---- per-kernel durations: a separate eager pass with every launch bracketed by CUDA events on its stream ----

@@ -8,6 +8,7 @@ contiguous frame ranges with no collective at all.  The reference has no distrib
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, List, Sequence, Tuple
 
 import torch
@@ -51,8 +52,12 @@ class FlatGrads:
         # (fused.render_skinned(reduce=...)).  Measured on 2 x B200 (C0): 0.725-0.731 ms/step against 0.72 ms with the
         # single all-reduce after the backward -- the issue-bound per-Gaussian backward and the link-bound sum slow each
         # other down by as much as the overlap hides, so it stays off.
-        self.overlap = False
+        self.overlap = os.environ.get("RG_DP_OVERLAP", "0") == "1"
+        self.overlap_blocks = int(os.environ.get("RG_DP_BLOCKS", "32"))   # CTAs of the reduce kernel running beside the backward
+        self.overlap_chunks = int(os.environ.get("RG_DP_CHUNKS", "4"))
         padded = (total + 3) // 4 * 4  # the peer kernel moves 16-byte words
+        if os.environ.get("RG_ALLREDUCE", "") == "nccl":
+            peer_memory = False
         if peer_memory and device.type == "cuda":
             self._try_symmetric(padded, device)
         if self.hdl is None:
@@ -82,7 +87,8 @@ class FlatGrads:
             # NVLS multicast address of the same buffer: the switch reduces (multimem.ld_reduce) and replicates
             # (multimem.st), which moves (N+1)/N of the buffer per link direction instead of 2(N-1)/N -- measured on
             # B200: slower than the peer kernel at N=2 (0.19 vs 0.11 ms), faster at N=8 (0.15 vs 0.22 ms)
-            mc = int(hdl.multicast_ptr) if hdl.world_size >= 8 else 0
+            want_mc = {"multimem": True, "p2p": False}.get(os.environ.get("RG_ALLREDUCE", ""), hdl.world_size >= 8)
+            mc = int(hdl.multicast_ptr) if want_mc else 0
             self._mc_ptr = mc + off if mc else 0
             self._storage, self.hdl = t, hdl
         except Exception as e:  # no peer access / no symmetric-memory support: NCCL does the job
@@ -144,8 +150,9 @@ class FlatGrads:
             n_ranges += 1
         return n_ranges <= 8
 
-    def row_chunks(self, n_rows: int, n_chunks: int = 4):
+    def row_chunks(self, n_rows: int, n_chunks: int = 0):
         """Row ranges of about equal size whose starts are multiples of 256 (the backward's CTA granularity)."""
+        n_chunks = n_chunks or self.overlap_chunks
         step = max(256, (n_rows + n_chunks - 1) // n_chunks // 256 * 256)
         out, r = [], 0
         while r < n_rows:
@@ -156,13 +163,14 @@ class FlatGrads:
             r = e
         return out
 
-    def all_reduce_rows(self, n_rows: int, r0: int, r1: int, with_rest: bool, blocks: int = 64, barrier_after: bool = False):
+    def all_reduce_rows(self, n_rows: int, r0: int, r1: int, with_rest: bool, blocks: int = 0, barrier_after: bool = False):
         """Device-side barrier, then the sum of rows [r0, r1) of every per-row parameter (plus, with_rest, of the other
         parameters) on the current stream.  The caller orders this after the kernels that wrote those rows; successive
         calls need no barrier in between (the next call's leading barrier also fences this call's kernel), the last one
         passes barrier_after=True."""
         import ctypes as C
         from . import _lib
+        blocks = blocks or self.overlap_blocks
         offs, lens, off = [], [], 0
         for p in self.params:
             k = p.numel()

@@ -220,10 +220,20 @@ class GraphedStep:
         old, hp.pool = getattr(hp, "pool", None), self.pool
         try:
             if self.n_views == 1:
-                return hp.step(self.cam, self.pose, self.target)
-            return hp.step_views(self.cams, self.poses, self.targets)
+                loss = hp.step(self.cam, self.pose, self.target)
+            else:
+                loss = hp.step_views(self.cams, self.poses, self.targets)
+            if self._reduce_in_graph():
+                # data parallel over a peer-mapped gradient buffer: the cross-rank sum (two device-side barriers and this
+                # library's all-reduce kernel) is part of the captured step, not an eager call after each replay
+                hp.flat.all_reduce()
+            return loss
         finally:
             hp.pool = old
+
+    def _reduce_in_graph(self) -> bool:
+        flat = self.hp.flat
+        return flat is not None and getattr(flat, "hdl", None) is not None
 
     def _capture(self):
         from . import _lib
@@ -241,7 +251,7 @@ class GraphedStep:
         self.launches_per_replay = int(_lib.lib().rg_launch_count() - n0)
         self.grads = {n: p.grad for n, p in self.hp.named_parameters()}  # static: rewritten by every replay
         # data parallel with a peer-mapped gradient buffer: the all-reduce was captured with the backward
-        self._reduces_in_graph = bool(self.hp.flat is not None and self.hp.flat.reduced_in_backward)
+        self._reduces_in_graph = bool(self.hp.flat is not None and (self.hp.flat.reduced_in_backward or self._reduce_in_graph()))
         self._ws = self.pool.free and next(iter(self.pool.free.values()))[0]
         self._captured_binning = self._ws.binning.data_ptr() if self._ws else None
         self._event = None

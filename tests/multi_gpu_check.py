@@ -1,0 +1,97 @@
+"""Multi-process checker of the library's own all-reduce kernels (run under torchrun by tests/test_gpu_multi.py, or by
+hand:  python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 tests/multi_gpu_check.py).
+
+Every rank fills a symmetric-memory gradient buffer (dist.FlatGrads) with rank-dependent values and sums it over the
+ranks three ways: ncclAllReduce on a clone (the comparator), rg_allreduce_p2p (peer loads, rank-ordered adds: must be
+bit-identical on every rank and equal to a rank-ordered sum computed with torch) and rg_allreduce_multimem (NVLS: the
+switch adds, order unspecified: 1e-6 relative).  rg_allreduce_ranges is checked on both paths with row chunks.
+Prints one JSON line per check on rank 0 and exits non-zero on any mismatch."""
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    from riggs_b200.dist import FlatGrads
+    ok_all = True
+    P = 30_000
+    shapes = [("xyz", (P, 3)), ("f_dc", (P, 1, 3)), ("f_rest", (P, 15, 3)), ("opacity", (P, 1)), ("scaling", (P, 3)),
+              ("rotation", (P, 4)), ("node_radius", (24,))]
+    for mode in ("p2p", "multimem"):
+        os.environ["RG_ALLREDUCE"] = mode
+        params = [(n, torch.zeros(s, device=dev)) for n, s in shapes]
+        flat = FlatGrads(params, device=dev)
+        if flat.hdl is None:
+            if rank == 0:
+                print(json.dumps({"mode": mode, "skipped": "no symmetric memory on this box"}))
+            continue
+        if mode == "multimem" and not flat._mc_ptr:
+            if rank == 0:
+                print(json.dumps({"mode": mode, "skipped": "no multicast (NVLS) address on this box"}))
+            continue
+        g = torch.Generator(device="cpu").manual_seed(100 + rank)
+        mine = (torch.randn(flat.total, generator=g) * (1.0 + rank)).to(dev)
+        # rank-ordered reference: gather every rank's values, add in rank order
+        allv = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allv, mine)
+        want = allv[0].clone()
+        for r in range(1, world):
+            want += allv[r]
+        nccl = mine.clone()
+        dist.all_reduce(nccl)
+        for trial in range(3):  # the kernel runs on a buffer that holds the previous trial's result on every rank
+            flat.flat.copy_(mine)
+            torch.cuda.synchronize()
+            dist.barrier()
+            flat.all_reduce()
+            torch.cuda.synchronize()
+            got = flat.flat.clone()
+            if mode == "p2p":
+                ok = bool(torch.equal(got, want))
+            else:
+                ok = float((got - want).abs().max() / want.abs().max()) <= 1e-6
+            chk = got.clone()
+            dist.broadcast(chk, src=0)
+            same = bool(torch.equal(chk, got))  # every rank ends with the same bits (one rank computed each slice)
+            err = float((got - nccl).abs().max() / nccl.abs().max())
+            t = torch.tensor([int(ok and same and err <= 1e-6)], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+            ok_all = ok_all and bool(int(t[0]))
+            if rank == 0:
+                print(json.dumps({"mode": mode, "kernel": "rg_allreduce_" + mode, "world": world, "trial": trial,
+                                  "matches_rank_ordered_sum": ok, "identical_on_all_ranks": same,
+                                  "max_rel_err_vs_nccl": err, "floats": flat.total}))
+        # row-chunked ranges (the overlap path): chunks of rows + the rest with the last chunk
+        flat.flat.copy_(mine)
+        torch.cuda.synchronize()
+        dist.barrier()
+        chunks = flat.row_chunks(P, 3)
+        for c, (r0, r1) in enumerate(chunks):
+            flat.all_reduce_rows(P, r0, r1, with_rest=c == len(chunks) - 1, blocks=16, barrier_after=c == len(chunks) - 1)
+        flat.reduced_in_backward = False
+        torch.cuda.synchronize()
+        got = flat.flat.clone()
+        ok = bool(torch.equal(got, want)) if mode == "p2p" else float((got - want).abs().max() / want.abs().max()) <= 1e-6
+        t = torch.tensor([int(ok)], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        ok_all = ok_all and bool(int(t[0]))
+        if rank == 0:
+            print(json.dumps({"mode": mode, "kernel": "rg_allreduce_ranges", "world": world, "chunks": len(chunks), "ok": bool(int(t[0]))}))
+        del flat
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(0 if ok_all else 1)
+
+
+if __name__ == "__main__":
+    main()
