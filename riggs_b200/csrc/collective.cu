@@ -7,6 +7,8 @@
 // The caller brackets the kernel with two cross-rank barriers on the stream (all ranks have finished writing their
 // gradients / all slices have been written back).  The reference has no distributed code; this replaces the
 // ncclAllReduce a data-parallel trainer would issue after the backward.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "../../include/riggs_b200.h"
 
@@ -130,6 +132,16 @@ static bool slice_ranges(int n_ranges, const size_t* offsets, const size_t* leng
 
 using namespace rg;
 
+// CTAs of the whole-buffer kernels: two per SM unless RG_AR_BLOCKS says otherwise (tuning aid)
+static int allreduce_blocks() {
+    static const int v = [] {
+        const char* e = std::getenv("RG_AR_BLOCKS");
+        const int n = e ? std::atoi(e) : 0;
+        return n > 0 ? n : RG_NUM_SMS * 2;
+    }();
+    return v;
+}
+
 extern "C" int rg_allreduce_ranges(float* const* peer_bufs, float* multicast_base, int n_ranges, const size_t* offsets,
                                    const size_t* lengths, int rank, int world, int blocks, rg_stream_t stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
@@ -180,7 +192,7 @@ extern "C" int rg_allreduce_p2p(float* const* peer_bufs, size_t n_floats, int ra
     const size_t w1 = w0 + per < words ? w0 + per : words;
     if (w1 == w0) return 0;
     LaunchScope ls("allreduce_p2p", stream);
-    const int nb = RG_NUM_SMS * 2;
+    const int nb = allreduce_blocks();
     if (world == 2) allreduce_p2p_kernel<2><<<nb, 512, 0, stream>>>(pp, w0, w1);
     else if (world == 4) allreduce_p2p_kernel<4><<<nb, 512, 0, stream>>>(pp, w0, w1);
     else allreduce_p2p_kernel<8><<<nb, 512, 0, stream>>>(pp, w0, w1);
@@ -201,6 +213,6 @@ extern "C" int rg_allreduce_multimem(float* multicast_base, size_t n_floats, int
     const size_t w1 = w0 + per < words ? w0 + per : words;
     if (w1 == w0) return 0;
     LaunchScope ls("allreduce_multimem", stream);
-    allreduce_multimem_kernel<<<RG_NUM_SMS * 2, 512, 0, stream>>>(multicast_base, w0, w1);
+    allreduce_multimem_kernel<<<allreduce_blocks(), 512, 0, stream>>>(multicast_base, w0, w1);
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
