@@ -251,11 +251,13 @@ def run_ours(args):
         hp.zero_grad()
         cs, ps, ts = group(0)
         ps = [{k: v.detach().clone().requires_grad_(True) for k, v in p.items()} for p in ps]
+        overlap_mode, hp.flat.overlap = hp.flat.overlap, False  # this step must leave the rank's OWN gradients in the buffer
         (hp.step_views(cs, ps, ts) if vps > 1 else hp.step(cs[0], ps[0], ts[0]))
         ref = hp.flat.flat.clone()
         dist.all_reduce(ref, op=dist.ReduceOp.SUM)
         hp.reduce_grads()
         torch.cuda.synchronize()
+        hp.flat.overlap = overlap_mode
         if getattr(hp.flat, "_mc_ptr", 0):  # switch-side sum: the order of the adds is the switch's
             err = float((hp.flat.flat - ref).abs().max() / ref.abs().max().clamp_min(1e-30))
             ok = err <= 1e-6
@@ -267,9 +269,17 @@ def run_ours(args):
             ok = ok and bool(torch.equal(chk, hp.flat.flat))
         else:
             err, ok = 0.0, True
+        err_overlap = None
+        if overlap_mode:  # the sum taken chunk by chunk while the backward runs, on the same inputs (float atomics: not bit-equal)
+            eager_step(0)
+            torch.cuda.synchronize()
+            err_overlap = float((hp.flat.flat - ref).abs().max() / ref.abs().max().clamp_min(1e-30))
+            ok = ok and err_overlap <= 1e-4
         t_ok = torch.tensor([1 if ok else 0], device=dev)
         dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
         allreduce_checked = {"ok": bool(int(t_ok[0])), "max_rel_err_vs_nccl": err}
+        if err_overlap is not None:
+            allreduce_checked["overlapped_with_backward_max_rel_err"] = err_overlap
         if not allreduce_checked["ok"]:
             raise SystemExit(f"rank {rank}: own all-reduce disagrees with dist.all_reduce (rel err {err})")
 
@@ -414,7 +424,12 @@ def run_ours(args):
     nvlink = peer_copy_bandwidth(hp, dev) if world > 1 else None
 
     # max over ranks
+    per_rank_ms = None
     if world > 1:
+        mine = torch.tensor([ms / args.steps], device=dev)
+        allms = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allms, mine)
+        per_rank_ms = [round(float(x), 4) for x in allms]
         t = torch.tensor([ms, ms_e2e], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms, ms_e2e = float(t[0]), float(t[1])
@@ -492,6 +507,8 @@ def run_ours(args):
     }
     if allreduce_checked is not None:
         line["allreduce_checked"] = allreduce_checked
+    if per_rank_ms is not None:
+        line["per_rank_ms_per_step"] = per_rank_ms
     if nvlink:
         ar = [k for k in kern if k.startswith("allreduce")]
         if ar:
@@ -642,7 +659,12 @@ def run_sequence(args, rank, world, dev):
     if world > 1:
         dist.barrier()
     ms_e2e = f0.elapsed_time(f1)
+    per_rank_ms = None
     if world > 1:
+        mine = torch.tensor([ms / (args.steps * max(F, 1))], device=dev)
+        allms = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allms, mine)
+        per_rank_ms = [round(float(x), 4) for x in allms]
         t = torch.tensor([ms, ms_e2e], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms, ms_e2e = float(t[0]), float(t[1])
@@ -692,6 +714,8 @@ def run_sequence(args, rank, world, dev):
         "kernels": {k: {kk: round(vv, 4) if isinstance(vv, float) else vv for kk, vv in v.items()} for k, v in kern.items()},
         "instance_buffer_overflowed": bool(overflowed),
     }
+    if per_rank_ms is not None:
+        line["per_rank_ms_per_frame"] = per_rank_ms
     _emit(line)
     if world > 1:
         dist.destroy_process_group()
