@@ -50,6 +50,8 @@ def parse():
     ap.add_argument("--views-per-step", type=int, default=0,
                     help="global views per optimiser step, sharded over the ranks and accumulated per rank "
                          "(0 = one view per GPU per step, weak scaling)")
+    ap.add_argument("--frame-sharding", default="interleaved", choices=["interleaved", "contiguous"],
+                    help="sequence mode: frames r, r+N, ... per rank (balanced) or one contiguous range per rank")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true")
     ap.add_argument("--baselines", action="store_true",
@@ -576,7 +578,7 @@ def run_sequence(args, rank, world, dev):
     import torch
     import torch.distributed as dist
     from riggs_b200 import _lib
-    from riggs_b200.dist import shard_frames
+    from riggs_b200.dist import shard_frames, shard_frames_interleaved
     from riggs_b200.hotpath import HotPath, PoseSequenceRenderer
 
     scene = make_scene(args.workload, args.isotropic, mode="sequence")
@@ -584,10 +586,14 @@ def run_sequence(args, rank, world, dev):
     cam = scene.cameras[0].to(dev)
     H, W = cam.image_height, cam.image_width
     F_total = len(scene.poses)
-    b, e = shard_frames(F_total, rank, world)
-    F = e - b
-    rot_host = torch.stack([p["local_rotation"] for p in scene.poses[b:e]]).pin_memory()
-    trans_host = torch.stack([p["global_trans"] for p in scene.poses[b:e]]).pin_memory()
+    if args.frame_sharding == "contiguous":
+        b, e = shard_frames(F_total, rank, world)
+        mine = list(range(b, e))
+    else:
+        mine = shard_frames_interleaved(F_total, rank, world)
+    F = len(mine)
+    rot_host = torch.stack([scene.poses[f]["local_rotation"] for f in mine]).pin_memory()
+    trans_host = torch.stack([scene.poses[f]["global_trans"] for f in mine]).pin_memory()
     seq = PoseSequenceRenderer(hp, cam, scene.J, max_frames=max(F, 1))
     seq.load(rot_host, trans_host)
     torch.cuda.synchronize()
@@ -704,7 +710,7 @@ def run_sequence(args, rank, world, dev):
                    "step": "one pass over the whole sequence", "mlps": args.mlps,
                    "l2": f"no explicit flush: one frame reads {P * in_P >> 20} MB of parameters (> 126 MB L2) and the pose changes every frame",
                    "launch": "cuda graph replay, the graph advances its own frame index", "parallelism":
-                       (f"frames sharded contiguously over {world} GPUs, no collective" if world > 1 else "single GPU")},
+                       (f"frames sharded over {world} GPUs ({args.frame_sharding}), no collective" if world > 1 else "single GPU")},
         "e2e": {"value": round(frames / (ms_e2e / 1e3), 3), "unit": "frames/s",
                 "h2d_bytes_per_step": int(rot_host.numel() * 4 + trans_host.numel() * 4), "d2h_bytes_per_step": int(F * 3 * H * W * 4)},
         "gpu_launches": int(seq.launches_per_replay * F * args.steps),

@@ -27,6 +27,14 @@ def shard_frames(n_frames: int, rank: int, world: int) -> Tuple[int, int]:
     return begin, begin + base + (1 if rank < extra else 0)
 
 
+def shard_frames_interleaved(n_frames: int, rank: int, world: int) -> List[int]:
+    """Frames rank, rank + world, rank + 2*world, ...: the cost of a frame (its instance count) drifts slowly along a
+    pose sequence, so contiguous ranges leave the ranks unevenly loaded (measured on C5, 2 GPUs: 1.08 vs 1.63 ms per
+    frame) while interleaved frames give every rank the same mix.  Frames keep their index, so the output order is
+    unaffected."""
+    return list(range(rank, n_frames, world))
+
+
 class FlatGrads:
     """One flat fp32 gradient buffer with a named view per parameter.
 

@@ -9,7 +9,7 @@ import torch.distributed as dist
 import torch.multiprocessing as mp
 
 import helpers  # noqa: F401
-from riggs_b200.dist import FlatGrads, all_reduce_max_, shard_frames, shard_views
+from riggs_b200.dist import FlatGrads, all_reduce_max_, shard_frames, shard_frames_interleaved, shard_views
 
 
 def test_sharding_covers_every_unit_once():
@@ -22,6 +22,9 @@ def test_sharding_covers_every_unit_once():
             assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
             sizes = [e - b for b, e in spans]
             assert max(sizes) - min(sizes) <= 1
+            inter = [shard_frames_interleaved(n, r, world) for r in range(world)]
+            assert sorted(f for fr in inter for f in fr) == list(range(n))
+            assert max(map(len, inter)) - min(map(len, inter)) <= 1
 
 
 def _free_port():
