@@ -12,7 +12,7 @@ from typing import Optional
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libriggs_b200.so")
+LIB_PATH = os.environ.get("RG_LIB") or os.path.join(_HERE, "lib", "libriggs_b200.so")  # RG_LIB: a tuning build (build.py --variant)
 
 ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_size_t)
 _p = C.c_void_p

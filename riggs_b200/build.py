@@ -37,21 +37,26 @@ def _stale(target, deps):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(verbose: bool = False, force: bool = False) -> str:
-    os.makedirs(OBJDIR, exist_ok=True)
+def build(verbose: bool = False, force: bool = False, variant: str = "", defines=()) -> str:
+    """variant / defines: a tuning build -- the same sources with extra -D flags, linked to lib/libriggs_b200_<variant>.so
+    (selected at run time with RG_LIB=<path>); the product library is the plain build."""
+    objdir = OBJDIR + ("_" + variant if variant else "")
+    lib = LIB if not variant else os.path.join(LIBDIR, f"libriggs_b200_{variant}.so")
+    flags = FLAGS + [f"-D{d}" for d in defines]
+    os.makedirs(objdir, exist_ok=True)
     hdrs = _headers()
     jobs = []
     objs = []
     for src in _sources():
         s = os.path.join(CSRC, src)
-        o = os.path.join(OBJDIR, src[:-3] + ".o")
+        o = os.path.join(objdir, src[:-3] + ".o")
         objs.append(o)
         if force or _stale(o, [s] + hdrs):
             jobs.append((s, o))
 
     def run(job):
         s, o = job
-        cmd = [NVCC, *FLAGS, "-c", s, "-o", o]
+        cmd = [NVCC, *flags, "-c", s, "-o", o]
         r = subprocess.run(cmd, capture_output=True, text=True)
         log = o[:-2] + ".ptxas.log"
         with open(log, "w") as f:
@@ -65,13 +70,17 @@ def build(verbose: bool = False, force: bool = False) -> str:
     if jobs:
         with ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:
             list(ex.map(run, jobs))
-    if force or jobs or _stale(LIB, objs):
-        cmd = [NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB, *objs]
+    if force or jobs or _stale(lib, objs):
+        cmd = [NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", lib, *objs]
         subprocess.check_call(cmd)
         if verbose:
-            print("linked", LIB)
-    return LIB
+            print("linked", lib)
+    return lib
 
 
 if __name__ == "__main__":
-    print(build(verbose=True, force="--force" in sys.argv))
+    # python build.py [--force] [--variant NAME -DX=1 -DY=2 ...]
+    args = sys.argv[1:]
+    variant = args[args.index("--variant") + 1] if "--variant" in args else ""
+    defines = [a[2:] for a in args if a.startswith("-D")]
+    print(build(verbose=True, force="--force" in args, variant=variant, defines=defines))

@@ -31,20 +31,25 @@ constexpr int kPitch = kChunk + 1;  // row pitch of the Q / W tiles: conflict-fr
 __device__ uint32_t* g_bwd_tile_prof = nullptr;
 void set_bwd_tile_profile(uint32_t* p) { cudaMemcpyToSymbol(g_bwd_tile_prof, &p, sizeof(p)); }
 
+// Shared memory per warp decides how many warps an SM holds here (the kernel is issue-bound and wants all it can get):
+// the phase-B results reuse the W tile once every lane has read its column.
 struct __align__(16) BwdChunk {
     float Q[32 * kPitch];   // [pixel][instance]
-    float W[32 * kPitch];
-    float4 xyts[kChunk];    // instance centre (x, y), unused, unused
+    float W[32 * kPitch];   // ... and, from the middle of a flush on, out[kChunk * kAcc]: phase-B results, instance-major
+    float2 xy[kChunk];      // instance centre
     float4 co[kChunk];      // conic + opacity
     float4 cpix[32];        // per pixel: dL/d(r, g, b, depth)
     uint32_t id[kChunk];
-    float out[kChunk * kAcc];  // phase-B results, instance-major, for the coalesced reductions
 };
+static_assert(kChunk * kAcc <= 32 * kPitch, "phase-B results must fit into the W tile");
 
 // Phase B: lane e owns instance e of the chunk.
 __device__ __noinline__ void flush_chunk(BwdChunk& ch, int fill, int lane, float ox, float oy, float ddelx_dx,
                                             float ddely_dy, float* __restrict__ grad_acc) {
     __syncwarp();
+    float r[kAcc];
+#pragma unroll
+    for (int k = 0; k < kAcc; k++) r[k] = 0.f;
     if (lane < fill) {
         float s0 = 0.f, sx = 0.f, sy = 0.f, sxx = 0.f, sxy = 0.f, syy = 0.f, wr = 0.f, wg = 0.f, wb = 0.f, wd = 0.f;
 #pragma unroll
@@ -64,7 +69,7 @@ __device__ __noinline__ void flush_chunk(BwdChunk& ch, int fill, int lane, float
             wd = fmaf(w, c.w, wd);
         }
         // moments about the instance centre: d = (X - lx, Y - ly), X = x - block origin
-        const float4 e = ch.xyts[lane];
+        const float2 e = ch.xy[lane];
         const float4 co = ch.co[lane];
         const float X = e.x - ox, Y = e.y - oy;
         const float qdx = X * s0 - sx, qdy = Y * s0 - sy;
@@ -73,17 +78,23 @@ __device__ __noinline__ void flush_chunk(BwdChunk& ch, int fill, int lane, float
         const float qdyy = Y * (Y * s0 - 2.f * sy) + syy;
         // dL/dG = o dL/dalpha;  dG/ddelx = -G (A dx + B dy), dG/ddely = -G (C dy + B dx)
         const float o = co.w;
-        float* out = ch.out + lane * kAcc;
-        out[0] = -o * ddelx_dx * (co.x * qdx + co.y * qdy);
-        out[1] = -o * ddely_dy * (co.z * qdy + co.y * qdx);
-        out[2] = -0.5f * o * qdxx;
-        out[3] = -0.5f * o * qdxy;
-        out[4] = -0.5f * o * qdyy;
-        out[5] = s0;
-        out[6] = wr;
-        out[7] = wg;
-        out[8] = wb;
-        out[9] = wd;
+        r[0] = -o * ddelx_dx * (co.x * qdx + co.y * qdy);
+        r[1] = -o * ddely_dy * (co.z * qdy + co.y * qdx);
+        r[2] = -0.5f * o * qdxx;
+        r[3] = -0.5f * o * qdxy;
+        r[4] = -0.5f * o * qdyy;
+        r[5] = s0;
+        r[6] = wr;
+        r[7] = wg;
+        r[8] = wb;
+        r[9] = wd;
+    }
+    __syncwarp();  // every lane has read its W column: the tile's memory now carries the results
+    float* const out_all = ch.W;
+    if (lane < fill) {
+        float* out = out_all + lane * kAcc;
+#pragma unroll
+        for (int k = 0; k < kAcc; k++) out[k] = r[k];
     }
     __syncwarp();
     // The ten values of an instance are contiguous in grad_acc: lanes take consecutive (instance, value) pairs so that
@@ -93,14 +104,20 @@ __device__ __noinline__ void flush_chunk(BwdChunk& ch, int fill, int lane, float
         const int idx = j * 32 + lane;
         const int ent = idx / kAcc, k = idx - ent * kAcc;
         if (ent < fill) {
-            const float v = ch.out[idx];
+            const float v = out_all[idx];
             if (v != 0.f) atomicAdd(grad_acc + (size_t)ch.id[ent] * kAcc + k, v);
         }
     }
     __syncwarp();
 }
 
-__global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendBwdArgs a) {
+#ifndef RG_BWD_MINBLK
+#define RG_BWD_MINBLK 8  // 8 CTAs (16 warps) per SM: at most 128 registers; measured 0.1351 -> 0.1316 ms at C0 against no bound (133 registers, 6 CTAs)
+#endif
+#ifndef RG_BWD_PERLANE
+#define RG_BWD_PERLANE 2
+#endif
+__global__ void __launch_bounds__(kBlendWarps * 32, RG_BWD_MINBLK) blend_backward_kernel(BlendBwdArgs a) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     constexpr int kCtasPerTile = 8 / kBlendWarps;
     const int tile = (int)a.tile_order[blockIdx.x / kCtasPerTile];
@@ -118,10 +135,10 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendB
     for (int o = 16; o > 0; o >>= 1) total = max(total, __shfl_xor_sync(0xffffffffu, total, o));
     if (total == 0) return;
 
-    constexpr int kPerLane = 2, kGroup = 32 * kPerLane;
-    __shared__ WarpStage<kPerLane> s_stage[kBlendWarps];
+    constexpr int kPerLane = RG_BWD_PERLANE, kGroup = 32 * kPerLane;
+    __shared__ WarpStage<kPerLane, false> s_stage[kBlendWarps];
     __shared__ BwdChunk s_chunk[kBlendWarps];
-    WarpStage<kPerLane>& st = s_stage[warp];
+    WarpStage<kPerLane, false>& st = s_stage[warp];
     BwdChunk& ch = s_chunk[warp];
     MaskWalker<kPerLane> walk;
     walk.pl = a.point_list; walk.rec = a.rec; walk.surv_bits = a.surv_mask + (size_t)blk * a.surv_stride; walk.first = a.ranges[tile].x; walk.n = total;
@@ -150,12 +167,12 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendB
     uint32_t n_list = 0, n_flush = 0;
     if (prof) { t_start = clock64(); walk.timing = true; }
 
-    // lanes 0-3 copy xyts, 4-7 conic+opacity, 8 the id (all 32-bit words; ids travel as bit patterns)
-    const uint32_t* meta_src = lane < 4 ? reinterpret_cast<const uint32_t*>(st.xyts) + lane
-                               : lane < 8 ? reinterpret_cast<const uint32_t*>(st.co) + (lane - 4) : st.id;
-    uint32_t* meta_dst = lane < 4 ? reinterpret_cast<uint32_t*>(ch.xyts) + lane
-                         : lane < 8 ? reinterpret_cast<uint32_t*>(ch.co) + (lane - 4) : ch.id;
-    const int meta_sstride = lane < 8 ? 4 : 1, meta_dstride = meta_sstride;
+    // lanes 0-1 copy the centre, 2-5 conic+opacity, 6 the id (all 32-bit words; ids travel as bit patterns)
+    const uint32_t* meta_src = lane < 2 ? reinterpret_cast<const uint32_t*>(st.xyts) + lane
+                               : lane < 6 ? reinterpret_cast<const uint32_t*>(st.co) + (lane - 2) : st.id;
+    uint32_t* meta_dst = lane < 2 ? reinterpret_cast<uint32_t*>(ch.xy) + lane
+                         : lane < 6 ? reinterpret_cast<uint32_t*>(ch.co) + (lane - 2) : ch.id;
+    const int meta_sstride = lane < 6 ? 4 : 1, meta_dstride = lane < 2 ? 2 : (lane < 6 ? 4 : 1);
     constexpr int U = 2;
     int fill = 0;  // instances waiting in the chunk
     for (int g = 0; g < n_groups; g++) {
@@ -235,7 +252,7 @@ __global__ void __launch_bounds__(kBlendWarps * 32) blend_backward_kernel(BlendB
                     ch.Q[lane * kPitch + fill] = q[u];
                     ch.W[lane * kPitch + fill] = w[u];
                     // instance record -> chunk: nine words copied by nine lanes (no divergent single-lane stores)
-                    if (lane < 9) meta_dst[fill * meta_dstride] = meta_src[e[u] * meta_sstride];
+                    if (lane < 7) meta_dst[fill * meta_dstride] = meta_src[e[u] * meta_sstride];
                     if (++fill == kChunk) {
                         flush_chunk(ch, fill, lane, ox, oy, ddelx_dx, ddely_dy, a.grad_acc);
                         fill = 0;

@@ -23,17 +23,18 @@ constexpr int kBlendWarps = 2;  // warps per CTA: a 16x4 pixel strip of one tile
 
 // kPerLane list entries per lane and walk step (kGroup = 32 kPerLane per step): the forward kernel, whose walk is a
 // third of its instructions, takes 4; the backward kernel, register-bound in its replay loop, takes 2.
-template <int kPerLane>
+// kCull = false (the backward's bitmap walk): no candidate records and no survivor bits are staged.
+template <int kPerLane, bool kCull = true>
 struct __align__(16) WarpStage {
     static constexpr int kGroup = 32 * kPerLane;
-    float4 cand_r0[kGroup];  // stage-1 survivors
+    float4 cand_r0[kCull ? kGroup : 1];  // stage-1 survivors
     float4 xyts[kGroup];     // stage-2 survivors: {x, y, thr, bits(position in the walk)}
     float4 co[kGroup];       //                    {A, B, C, opacity}
     float4 rgbd[kGroup];     //                    {r, g, b, depth}
     uint32_t cand_id[kGroup];
     uint32_t id[kGroup];  // Gaussian id of each stage-2 survivor
     uint8_t cand_k[kGroup];  // position in the group of each candidate
-    uint32_t bits[kPerLane + 2];  // survivor bits of the group being filtered (forward)
+    uint32_t bits[kCull ? kPerLane + 2 : 1];  // survivor bits of the group being filtered (forward)
 };
 
 // REVERSE = false: entries first, first+1, ...   (forward blend: front to back)
@@ -187,7 +188,7 @@ struct ListWalker {
 template <int kPerLane>
 struct MaskWalker {
     static constexpr int kGroup = 32 * kPerLane;
-    using Stage = WarpStage<kPerLane>;
+    using Stage = WarpStage<kPerLane, false>;
     const uint32_t* pl;
     const float4* rec;
     const uint32_t* surv_bits;  // this block's bitmap (see ListWalker::surv_bits)

@@ -23,7 +23,10 @@ namespace rg {
 __device__ uint32_t* g_fwd_tile_prof = nullptr;
 void set_fwd_tile_profile(uint32_t* p) { cudaMemcpyToSymbol(g_fwd_tile_prof, &p, sizeof(p)); }
 
-__global__ void __launch_bounds__(kBlendWarps * 32) blend_forward_kernel(BlendFwdArgs a) {
+#ifndef RG_FWD_MINBLK
+#define RG_FWD_MINBLK 1
+#endif
+__global__ void __launch_bounds__(kBlendWarps * 32, RG_FWD_MINBLK) blend_forward_kernel(BlendFwdArgs a) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     constexpr int kCtasPerTile = 8 / kBlendWarps;
     const int tile = (int)a.tile_order[blockIdx.x / kCtasPerTile];
