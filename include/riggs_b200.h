@@ -374,6 +374,34 @@ int rg_skinned_backward_part(const RgSkinnedScene* scene, const RgWorkspace* ws,
                              float* d_mean2D, float* d_local_rot, float* d_global_trans, float* d_node_radius_raw,
                              float* d_mask, float* d_mlp_weight, float* d_offsets, rg_stream_t stream);
 
+/* ---- the per-Gaussian MLP front end of the skinning path, on the tensor cores ---------- */
+
+/* The reference's two per-Gaussian MLPs -- WeightMLP (skeleton_utils/network_utils.py:73-107; called at
+ * skeleton_utils/skeleton_warp.py:56-61) and DeformMLP = detail_net (network_utils.py:6-65; skeleton_warp.py:98-104,
+ * 152-153) -- share one shape: positional encoding of x (3 + 6 * multires <= 63 values), eight 256-wide ReLU layers, the
+ * encoding concatenated in FRONT of the input of layer 5, a linear head (sigmoid for WeightMLP).  The reference runs each
+ * as ~20 eager torch kernels per direction with fp32 cuBLAS GEMMs over all N points; here a tile of 128 points goes
+ * through all nine layers inside one kernel (tcgen05.mma with the activations in tensor memory, csrc/mlp.cu).  bf16
+ * operands, fp32 accumulation.
+ *
+ * rg_mlp_pack: torch.nn.Linear weights (fp32, (n_out, ld) row-major; weights[0..7] the hidden layers, weights[8] the
+ * head) -> the bf16 chunk images the kernels stream.  For layer l, emb_col0[l] is the first column that multiplies the
+ * encoding (layers 0 and 5; ignored elsewhere) and act_col0[l] the first of the 256 columns that multiply the previous
+ * layer's activations (layers 1..8).  Columns in between (detail_net's pose input, the same for every point) are NOT
+ * packed: the caller folds W[:, pose columns] @ pose into that layer's bias.  packed: rg_mlp_packed_bytes(out_ch) bytes.
+ * Call it again whenever the weights change. */
+size_t rg_mlp_packed_bytes(int out_ch);
+int rg_mlp_pack(int emb_cols, int out_ch, const float* const* weights /* host array of 9 device pointers */,
+                const int* lds /* host, 9 */, const int* emb_col0 /* host, 9 */, const int* act_col0 /* host, 9 */,
+                void* packed, rg_stream_t stream);
+
+/* Forward: x (N,3) -> out (N,out_ch); out_act 0 = linear head (detail_net), 1 = sigmoid (WeightMLP).  bias: (9,256)
+ * fp32, the hidden layers' biases then the head's, zero padded.  Training (acts != NULL): also stores the post-ReLU
+ * activations of the eight hidden layers as bf16, feature-major (8, 256, n_pad), and the encoding (64, n_pad) into emb;
+ * n_pad >= N, a multiple of 64.  These are what rg_mlp_backward reads. */
+int rg_mlp_forward(int N, int multires, int out_ch, int out_act, const float* x, const void* packed, const float* bias,
+                   float* out, void* acts, void* emb, long long n_pad, rg_stream_t stream);
+
 /* ---- multi-GPU (no counterpart in the reference, which is single-GPU) -------------------------------- */
 
 /* In-place sum over `world` ranks of a gradient buffer that every rank has mapped at the multicast (NVLS multimem)

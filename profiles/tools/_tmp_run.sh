@@ -1,6 +1,2 @@
-CMD="python bench.py --steps 2 --warmup 3 --no-graph --no-cpu-baseline --no-ref-cuda"
-$CMD > gpurun_out/r2h_plain.log 2>&1 && \
-ncu --metrics gpu__time_duration.sum --clock-control none -s 100 -c 300 --csv --log-file gpurun_out/r2h_launches.csv $CMD > gpurun_out/r2h_ncu1.log 2>&1
-echo "launch list rc=$?"
-ncu --set full --clock-control none --import-source on -k regex:"blend_backward|blend_forward|gauss_backward|preprocess_kernel" -s 8 -c 4 -o gpurun_out/r2h_full $CMD > gpurun_out/r2h_ncu2.log 2>&1
-echo "full rc=$?"; ls -la gpurun_out/r2h_*
+timeout 120 python -m pytest tests/test_gpu_mlp.py -m gpu -x -q 2>&1 | tail -25
+cat gpurun_out/mlp_fwd_*.json 2>/dev/null

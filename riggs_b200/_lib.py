@@ -90,6 +90,9 @@ _SIGNATURES = {
     "rg_node_warp_forward": (C.c_int, [_i, _i, _i, _i] + [_p] * 12 + [_i] + [_p] * 9),
     "rg_node_warp_grad_channels": (C.c_int, []),
     "rg_node_warp_backward": (C.c_int, [_i, _i, _i, _i] + [_p] * 23),
+    "rg_mlp_packed_bytes": (C.c_size_t, [_i]),
+    "rg_mlp_pack": (C.c_int, [_i, _i, C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), _p, _p]),
+    "rg_mlp_forward": (C.c_int, [_i, _i, _i, _i, _p, _p, _p, _p, _p, _p, C.c_longlong, _p]),
     "rg_launch_count": (C.c_longlong, []),
     "rg_profile_enable": (None, [_i]),
     "rg_profile_reset": (None, []),

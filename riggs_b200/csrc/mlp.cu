@@ -1,0 +1,473 @@
+// The per-Gaussian MLP front end of the skinning path as tensor-core kernels for sm_100a (tcgen05 + TMEM):
+//   WeightMLP  (skeleton_utils/network_utils.py:73-107):  x -> PE(10) 63 -> 8 x 256 ReLU (skip after layer 4) -> J-1, sigmoid
+//   DeformMLP  (network_utils.py:6-65, "detail_net"):     (x PE(4) 27, pose 4J) -> 8 x 256 ReLU (skip) -> 3
+// The reference runs them as ~20 eager torch kernels each way with fp32 cuBLAS GEMMs over all N points and keeps every
+// (N, 256) fp32 activation in HBM.  Here ONE kernel carries a tile of 128 points through all nine layers:
+//   * activations never leave the SM: the bf16 activation matrix of a tile lives in TENSOR MEMORY and is the A operand
+//     of the next layer's tcgen05.mma (A from TMEM, B = weights from shared memory, fp32 accumulators in TMEM);
+//   * a layer's 256 outputs are produced in four quarters of 64 columns with two accumulator buffers, so the four
+//     epilogue warps (TMEM -> registers, bias, ReLU, bf16, -> TMEM) work on quarter q while the tensor core computes
+//     quarter q+1, and layer l+1 starts on the k-slabs whose quarters are already written;
+//   * weights stream through a ring of 8 KB chunks (64 outputs x 64 inputs, bf16, pre-swizzled by mlp_pack_kernel) filled
+//     by 1-D bulk (TMA) copies from a producer warp, freed by tcgen05.commit;
+//   * the positional encoding is computed in registers, and a pose that is the same for every point (detail_net's second
+//     input) is folded into the biases of the two layers that see it by the caller.
+// Arithmetic: bf16 operands, fp32 accumulation (the reference: fp32 cuBLAS).  Tolerances are stated in DESIGN.md and
+// tests/test_gpu_mlp.py.
+//
+// Training: the forward also stores every layer's post-ReLU activations, bf16, FEATURE-major ([layer][feature][point]),
+// which is the K-major operand layout the weight-gradient GEMMs want; mlp_chain_kernel<true> runs the same pipeline
+// backwards (dH = dZ W, masked by the stored activations) and stores dZ the same way; mlp_wgrad_kernel contracts the two
+// over the points.
+#include "../../include/riggs_b200.h"
+
+#include <cuda_bf16.h>
+
+#include <algorithm>
+#include <string>
+
+#include "bulk_copy.cuh"
+#include "common.cuh"
+
+namespace rg {
+
+constexpr int kHid = 256;        // hidden width of the reference's MLPs (W = 256)
+constexpr int kLayers = 8;       // D = 8 hidden layers, then the head
+constexpr int kSkipInto = 5;     // the embedded input is concatenated in front of layer 5's input (skips = [D // 2])
+constexpr int kTileM = 128;      // points per tile = TMEM lanes
+constexpr int kQuarter = 64;     // output columns per accumulator buffer = input columns per k-slab
+constexpr int kChunkBytes = kQuarter * kQuarter * 2;  // one weight chunk: 64 outputs x 64 inputs, bf16 = 8 KB
+constexpr int kStages = 20;      // ring depth: 160 KB of weights in flight / resident
+constexpr int kEpiWarps = 4;
+constexpr int kMlpThreads = (kEpiWarps + 2) * 32;  // + MMA warp + producer warp
+
+// TMEM columns (32-bit each, 128 lanes): two fp32 accumulator quarters, two bf16 activation buffers (256 values = 128
+// columns each), the embedded input (64 values = 32 columns)
+constexpr uint32_t kColAcc = 0, kColAct = 128, kColEmb = 384, kTmemCols = 512;
+
+struct MlpLayerPlan {
+    int n_quarters;  // output quarters (4 for hidden layers; 1 or 2 for the head)
+    int n_slabs;     // input k-slabs of 64: [embedding?] + [4 activation slabs?]
+    int has_emb;     // slab 0 is the embedded input
+    int has_act;     // the other slabs are the previous layer's activations
+    int n_last;      // columns of the last quarter (multiple of 16)
+};
+
+struct MlpArgs {
+    int N;                 // points
+    int n_tiles;
+    int multires;          // positional-encoding octaves (10: WeightMLP, 4: DeformMLP); embedding = 3 + 6 * multires <= 63
+    int out_ch;            // head outputs
+    int out_act;           // 0: none, 1: sigmoid
+    int total_chunks;      // weight chunks per tile
+    const float* x;        // (N, 3)
+    const unsigned char* w_packed;  // chunk images in consumption order
+    const float* bias;     // (9, 256): hidden layers' biases, then the head's (zero padded)
+    float* out;            // (N, out_ch)
+    __nv_bfloat16* acts;   // training: (8, 256, n_pad) post-ReLU activations, feature-major; null: not stored
+    __nv_bfloat16* emb;    // training: (64, n_pad) embedded input, feature-major; null: not stored
+    long long n_pad;       // row pitch of acts / emb (points, multiple of 64)
+    MlpLayerPlan plan[kLayers + 1];
+};
+
+// ---------------------------------------------------------------------------------------------------------------------
+// PTX wrappers (tcgen05 / TMEM)
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+// arrives on the mbarrier once every tcgen05 operation issued so far by this thread has completed
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem]^T, bf16 x bf16 -> fp32, M = 128
+__device__ __forceinline__ void mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t"
+        "}\n" ::"r"(d_tmem),
+        "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, "
+        "%18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+          "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+          "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, "
+        "%18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]),
+        "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]),
+        "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]),
+        "r"(r[31])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);  // .x (low half) = lo
+    return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// Shared-memory matrix descriptor of one weight chunk's k-step: K-major rows of 128 bytes (64 bf16), 128-byte swizzle,
+// eight-row groups 1024 bytes apart; the k-step of 16 columns starts 32 bytes further into the (un-swizzled) row.
+__device__ __forceinline__ uint64_t b_desc(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3ffff) >> 4);  // start address, bits [0,14)
+    d |= (uint64_t)1 << 16;                       // leading byte offset (unused for swizzled K-major), bits [16,30)
+    d |= (uint64_t)(1024 >> 4) << 32;             // stride byte offset: 8 rows x 128 B, bits [32,46)
+    d |= (uint64_t)1 << 46;                       // descriptor version (sm_100)
+    d |= (uint64_t)2 << 61;                       // SWIZZLE_128B
+    return d;
+}
+// instruction descriptor: D fp32, A/B bf16, both K-major, M = 128, N = n
+__device__ __forceinline__ uint32_t instr_desc(int n) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
+}
+
+struct MlpSmem {
+    uint64_t full[kStages], empty[kStages];
+    uint64_t acc_full[2], acc_free[2];
+    uint64_t act_ready[2][4];
+    uint64_t emb_ready;
+    uint32_t tmem_base;
+    float bias[(kLayers + 1) * kHid];
+};
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Forward chain.  Persistent: CTA b handles tiles b, b + gridDim.x, ...
+__global__ void __launch_bounds__(kMlpThreads, 1) mlp_forward_kernel(MlpArgs a) {
+    extern __shared__ __align__(1024) unsigned char s_dyn[];
+    unsigned char* ring = reinterpret_cast<unsigned char*>(align_up_dev(reinterpret_cast<size_t>(s_dyn), 1024));
+    MlpSmem& sm = *reinterpret_cast<MlpSmem*>(ring + (size_t)kStages * kChunkBytes);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kStages; i++) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], 1); }
+        for (int i = 0; i < 2; i++) { mbar_init(&sm.acc_full[i], 1); mbar_init(&sm.acc_free[i], kEpiWarps * 32); }
+        for (int i = 0; i < 8; i++) mbar_init(&sm.act_ready[i >> 2][i & 3], kEpiWarps * 32);
+        mbar_init(&sm.emb_ready, kEpiWarps * 32);
+    }
+    for (int i = threadIdx.x; i < (kLayers + 1) * kHid; i += blockDim.x) sm.bias[i] = a.bias[i];
+    if (warp == kEpiWarps) tmem_alloc(&sm.tmem_base, kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = sm.tmem_base;
+    const int my_tiles = a.n_tiles > (int)blockIdx.x ? (a.n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+
+    if (warp == kEpiWarps + 1) {
+        // ===================== producer: weight chunks, the same sequence for every tile =====================
+        if (lane == 0) {
+            uint32_t c = 0;
+            for (int t = 0; t < my_tiles; t++) {
+                for (int j = 0; j < a.total_chunks; j++, c++) {
+                    const uint32_t st = c % kStages;
+                    mbar_wait(&sm.empty[st], ((c / kStages) & 1) ^ 1);  // passes at once the first time round
+                    bulk_load(ring + (size_t)st * kChunkBytes, a.w_packed + (size_t)j * kChunkBytes, kChunkBytes, &sm.full[st]);
+                }
+            }
+        }
+    } else if (warp == kEpiWarps) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            uint32_t c = 0, g = 0;
+            for (int t = 0; t < my_tiles; t++) {
+                mbar_wait(&sm.emb_ready, t & 1);
+                tc_fence_after();
+#pragma unroll 1
+                for (int l = 0; l <= kLayers; l++) {
+                    const MlpLayerPlan p = a.plan[l];
+                    const uint32_t in_col = kColAct + (uint32_t)(l & 1) * 128;  // layer l reads buffer l & 1 (l >= 1)
+                    const int n_use = (l - 1) >> 1;  // how often this tile has written that buffer before (parity of the wait)
+#pragma unroll 1
+                    for (int q = 0; q < p.n_quarters; q++, g++) {
+                        const uint32_t ab = g & 1;
+                        mbar_wait(&sm.acc_free[ab], ((g >> 1) & 1) ^ 1);
+                        tc_fence_after();
+                        const int n = (q == p.n_quarters - 1) ? p.n_last : kQuarter;
+                        const uint32_t idesc = instr_desc(n);
+                        const uint32_t d_col = tmem + kColAcc + ab * kQuarter;
+                        for (int s = 0; s < p.n_slabs; s++, c++) {
+                            uint32_t a_col;
+                            if (p.has_emb && s == 0) {
+                                a_col = tmem + kColEmb;
+                            } else {
+                                const int sa = s - p.has_emb;  // activation slab = output quarter of the previous layer
+                                mbar_wait(&sm.act_ready[l & 1][sa], n_use & 1);
+                                tc_fence_after();
+                                a_col = tmem + in_col + (uint32_t)sa * 32;
+                            }
+                            const uint32_t st = c % kStages;
+                            mbar_wait(&sm.full[st], (c / kStages) & 1);
+                            tc_fence_after();
+                            const uint32_t b_addr = smem_u32(ring + (size_t)st * kChunkBytes);
+#pragma unroll
+                            for (int k = 0; k < 4; k++)
+                                mma_ts(d_col, a_col + (uint32_t)k * 8, b_desc(b_addr + (uint32_t)k * 32), idesc, (s | k) != 0);
+                            tc_commit(&sm.empty[st]);  // the chunk's slot is free once these MMAs have read it
+                        }
+                        tc_commit(&sm.acc_full[ab]);
+                    }
+                }
+            }
+        }
+    } else {
+        // ===================== epilogue warps: thread = point = TMEM lane =====================
+        const uint32_t lane_base = (uint32_t)(warp * 32) << 16;
+        const int row = warp * 32 + lane;
+        uint32_t g = 0;
+        const int n_emb = 3 + 6 * a.multires;
+        for (int t = 0; t < my_tiles; t++) {
+            const long long pt = ((long long)blockIdx.x + (long long)t * gridDim.x) * kTileM + row;
+            const bool valid = pt < a.N;
+            // ---- positional encoding (utils/time_utils.py:208-256: x, then sin / cos per octave), bf16, into TMEM
+            {
+                float e[64];
+                float xv[3] = {0.f, 0.f, 0.f};
+                if (valid) { xv[0] = a.x[3 * pt]; xv[1] = a.x[3 * pt + 1]; xv[2] = a.x[3 * pt + 2]; }
+#pragma unroll
+                for (int i = 0; i < 64; i++) e[i] = 0.f;
+                e[0] = xv[0]; e[1] = xv[1]; e[2] = xv[2];
+                float f = 1.0f;
+#pragma unroll
+                for (int o = 0; o < 10; o++) {
+                    if (o < a.multires) {
+#pragma unroll
+                        for (int d = 0; d < 3; d++) {
+                            float sv, cv;
+                            sincosf(xv[d] * f, &sv, &cv);
+                            e[3 + 6 * o + d] = sv;
+                            e[6 + 6 * o + d] = cv;
+                        }
+                    }
+                    f *= 2.0f;
+                }
+                uint32_t pk[32];
+#pragma unroll
+                for (int i = 0; i < 32; i++) pk[i] = pack_bf16(e[2 * i], e[2 * i + 1]);
+                tmem_st32(tmem + lane_base + kColEmb, pk);
+                if (a.emb && valid) {
+#pragma unroll
+                    for (int i = 0; i < 64; i++)
+                        if (i < n_emb) a.emb[(size_t)i * a.n_pad + pt] = __float2bfloat16_rn(e[i]);
+                }
+                tmem_st_wait();
+                tc_fence_before();
+                mbar_arrive(&sm.emb_ready);
+            }
+#pragma unroll 1
+            for (int l = 0; l <= kLayers; l++) {
+                const MlpLayerPlan p = a.plan[l];
+                const uint32_t out_col = kColAct + (uint32_t)((l + 1) & 1) * 128;  // layer l writes buffer (l + 1) & 1
+                const float* bias = sm.bias + l * kHid;
+#pragma unroll 1
+                for (int q = 0; q < p.n_quarters; q++, g++) {
+                    const uint32_t ab = g & 1;
+                    mbar_wait(&sm.acc_full[ab], (g >> 1) & 1);
+                    tc_fence_after();
+                    uint32_t v0[32], v1[32];
+                    tmem_ld32(tmem + lane_base + kColAcc + ab * kQuarter, v0);
+                    tmem_ld32(tmem + lane_base + kColAcc + ab * kQuarter + 32, v1);
+                    tmem_ld_wait();
+                    if (l < kLayers) {
+                        uint32_t pk[32];
+#pragma unroll
+                        for (int i = 0; i < 32; i++) {
+                            const int c0 = 2 * i;
+                            const float x0 = c0 < 32 ? __uint_as_float(v0[c0]) : __uint_as_float(v1[c0 - 32]);
+                            const float x1 = c0 + 1 < 32 ? __uint_as_float(v0[c0 + 1]) : __uint_as_float(v1[c0 + 1 - 32]);
+                            const float h0 = fmaxf(x0 + bias[q * kQuarter + c0], 0.f);
+                            const float h1 = fmaxf(x1 + bias[q * kQuarter + c0 + 1], 0.f);
+                            pk[i] = pack_bf16(h0, h1);
+                        }
+                        tmem_st32(tmem + lane_base + out_col + (uint32_t)q * 32, pk);
+                        if (a.acts && valid) {  // training: post-ReLU activations, feature-major (coalesced over the warp's points)
+                            __nv_bfloat16* dst = a.acts + ((size_t)l * kHid + (size_t)q * kQuarter) * a.n_pad + pt;
+#pragma unroll
+                            for (int i = 0; i < 32; i++) {
+                                const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&pk[i]);
+                                dst[(size_t)(2 * i) * a.n_pad] = h.x;
+                                dst[(size_t)(2 * i + 1) * a.n_pad] = h.y;
+                            }
+                        }
+                        tmem_st_wait();
+                        tc_fence_before();
+                        mbar_arrive(&sm.act_ready[(l + 1) & 1][q]);
+                        mbar_arrive(&sm.acc_free[ab]);
+                    } else {
+                        tc_fence_before();
+                        mbar_arrive(&sm.acc_free[ab]);  // the values are in registers
+                        if (valid) {
+#pragma unroll
+                            for (int i = 0; i < 64; i++) {
+                                const int col = q * kQuarter + i;
+                                if (col < a.out_ch) {
+                                    float z = (i < 32 ? __uint_as_float(v0[i]) : __uint_as_float(v1[i - 32])) + bias[col];
+                                    if (a.out_act == 1) z = 1.0f / (1.0f + expf(-z));
+                                    a.out[(size_t)pt * a.out_ch + col] = z;
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kEpiWarps) tmem_dealloc(tmem, kTmemCols);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Weight packing: fp32 (out, in) matrices of torch.nn.Linear -> bf16 chunk images in the order the kernel consumes them.
+struct PackLayer {
+    const float* w;   // (n_out, ld) row-major
+    int n_out, ld;
+    int emb_col0, emb_cols;  // columns of the embedded-input part (-1: none)
+    int act_col0;            // first column of the 256 activation inputs (-1: none)
+    int chunk0;              // index of the layer's first chunk
+    int n_quarters, n_slabs;
+};
+struct PackArgs {
+    PackLayer layer[kLayers + 1];
+    unsigned char* out;
+    int total_chunks;
+};
+
+__global__ void mlp_pack_kernel(PackArgs a) {
+    // one thread per 16-byte piece: 8 input columns of one output row of one chunk
+    const long long piece = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long n_pieces = (long long)a.total_chunks * (kChunkBytes / 16);
+    if (piece >= n_pieces) return;
+    const int chunk = (int)(piece / (kChunkBytes / 16));
+    const int in_chunk = (int)(piece % (kChunkBytes / 16));
+    const int r = in_chunk >> 3, cchunk = in_chunk & 7;  // row of the chunk, logical 16-byte column group
+    int l = 0;
+    while (l < kLayers && chunk >= a.layer[l + 1].chunk0) l++;
+    const PackLayer L = a.layer[l];
+    const int rel = chunk - L.chunk0;
+    const int q = rel / L.n_slabs, s = rel % L.n_slabs;
+    const int n = q * kQuarter + r;
+    __nv_bfloat16 v[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const int kk = cchunk * 8 + j;  // column inside the slab
+        float w = 0.f;
+        if (n < L.n_out) {
+            if (L.emb_col0 >= 0 && s == 0) {
+                if (kk < L.emb_cols) w = L.w[(size_t)n * L.ld + L.emb_col0 + kk];
+            } else {
+                const int sa = s - (L.emb_col0 >= 0 ? 1 : 0);
+                w = L.w[(size_t)n * L.ld + L.act_col0 + sa * kQuarter + kk];
+            }
+        }
+        v[j] = __float2bfloat16_rn(w);
+    }
+    // 128-byte swizzle: the 16-byte piece c of row r sits at piece position c ^ (r & 7)
+    unsigned char* dst = a.out + (size_t)chunk * kChunkBytes + (size_t)r * 128 + (size_t)((cchunk ^ (r & 7)) * 16);
+    *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(v);
+}
+
+static int plan_layers(int out_ch, MlpLayerPlan* plan, int* chunk0, int* total) {
+    int c = 0;
+    for (int l = 0; l <= kLayers; l++) {
+        MlpLayerPlan p;
+        p.has_emb = (l == 0 || l == kSkipInto) ? 1 : 0;
+        p.has_act = l > 0 ? 1 : 0;
+        p.n_slabs = p.has_emb + 4 * p.has_act;
+        if (l < kLayers) { p.n_quarters = 4; p.n_last = kQuarter; }
+        else {
+            const int out_pad = (out_ch + 15) / 16 * 16;
+            p.n_quarters = (out_pad + kQuarter - 1) / kQuarter;
+            p.n_last = out_pad - (p.n_quarters - 1) * kQuarter;
+        }
+        plan[l] = p;
+        chunk0[l] = c;
+        c += p.n_quarters * p.n_slabs;
+    }
+    *total = c;
+    return 0;
+}
+
+}  // namespace rg
+
+using namespace rg;
+
+extern "C" {
+
+size_t rg_mlp_packed_bytes(int out_ch) {
+    MlpLayerPlan plan[kLayers + 1];
+    int chunk0[kLayers + 1], total = 0;
+    if (out_ch < 1 || out_ch > 128) return 0;
+    plan_layers(out_ch, plan, chunk0, &total);
+    return (size_t)total * kChunkBytes;
+}
+
+int rg_mlp_pack(int emb_cols, int out_ch, const float* const* weights, const int* lds, const int* emb_col0, const int* act_col0,
+                void* packed, rg_stream_t stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (emb_cols < 1 || emb_cols > 63 || out_ch < 1 || out_ch > 128 || !weights || !lds || !emb_col0 || !act_col0 || !packed) {
+        set_error("rg_mlp_pack: bad argument (embedding of at most 63 columns, at most 128 outputs)");
+        return -1;
+    }
+    MlpLayerPlan plan[kLayers + 1];
+    int chunk0[kLayers + 1], total = 0;
+    plan_layers(out_ch, plan, chunk0, &total);
+    PackArgs a;
+    for (int l = 0; l <= kLayers; l++) {
+        PackLayer& L = a.layer[l];
+        L.w = weights[l]; L.ld = lds[l]; L.n_out = l < kLayers ? kHid : out_ch;
+        L.emb_col0 = plan[l].has_emb ? emb_col0[l] : -1; L.emb_cols = emb_cols;
+        L.act_col0 = plan[l].has_act ? act_col0[l] : -1;
+        L.chunk0 = chunk0[l]; L.n_quarters = plan[l].n_quarters; L.n_slabs = plan[l].n_slabs;
+        if (!L.w) { set_error("rg_mlp_pack: null weight matrix"); return -1; }
+    }
+    a.out = static_cast<unsigned char*>(packed);
+    a.total_chunks = total;
+    const long long pieces = (long long)total * (kChunkBytes / 16);
+    LaunchScope ls("mlp_pack", stream);
+    mlp_pack_kernel<<<(unsigned)((pieces + 255) / 256), 256, 0, stream>>>(a);
+    return check_launch("rg_mlp_pack", stream, false);
+}
+
+int rg_mlp_forward(int N, int multires, int out_ch, int out_act, const float* x, const void* packed, const float* bias,
+                   float* out, void* acts, void* emb, long long n_pad, rg_stream_t stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (N < 0 || multires < 0 || multires > 10 || out_ch < 1 || out_ch > 128 || !x || !packed || !bias || !out) {
+        set_error("rg_mlp_forward: bad argument");
+        return -1;
+    }
+    if ((acts || emb) && (n_pad < N || (n_pad & 63))) { set_error("rg_mlp_forward: n_pad must be a multiple of 64 and >= N"); return -1; }
+    if (N == 0) return 0;
+    MlpArgs a = {};
+    int chunk0[kLayers + 1];
+    plan_layers(out_ch, a.plan, chunk0, &a.total_chunks);
+    a.N = N; a.n_tiles = (N + kTileM - 1) / kTileM; a.multires = multires; a.out_ch = out_ch; a.out_act = out_act;
+    a.x = x; a.w_packed = static_cast<const unsigned char*>(packed); a.bias = bias; a.out = out;
+    a.acts = static_cast<__nv_bfloat16*>(acts); a.emb = static_cast<__nv_bfloat16*>(emb); a.n_pad = n_pad;
+    const size_t smem = (size_t)kStages * kChunkBytes + sizeof(MlpSmem) + 1024;
+    if (ensure_dyn_smem(reinterpret_cast<const void*>(mlp_forward_kernel), (int)smem)) return -1;
+    const int grid = std::min(a.n_tiles, RG_NUM_SMS);
+    LaunchScope ls("mlp_forward", stream);
+    mlp_forward_kernel<<<grid, kMlpThreads, smem, stream>>>(a);
+    return check_launch("rg_mlp_forward", stream, false);
+}
+
+}  // extern "C"
