@@ -57,9 +57,10 @@ def parse():
     ap.add_argument("--baselines", action="store_true",
                     help="also time BASELINE.md's B1 (CPU skinning alone, C1) and B2 (reference CUDA rasterizer alone) rows")
     ap.add_argument("--isotropic", action="store_true")
-    ap.add_argument("--mlps", default="off", choices=["off", "on"],
+    ap.add_argument("--mlps", default="off", choices=["off", "on", "torch"],
                     help="on: the reference's demo configuration (scripts/run_demo.py:32): per-Gaussian skinning-weight MLP "
-                         "and template-offset MLP evaluated (and differentiated) every step")
+                         "and template-offset MLP evaluated (and differentiated) every step, on the tensor-core kernels; "
+                         "torch: the same with the eager fp32 torch modules (what the reference runs)")
     ap.add_argument("--lambda-dssim", type=float, default=0.0,
                     help="> 0: the step's loss is the trainer's (1-l)*L1 + l*(1-SSIM) (fused kernels) instead of L1")
     ap.add_argument("--no-graph", action="store_true", help="drive the fused step launch by launch instead of replaying a CUDA graph")
@@ -213,7 +214,8 @@ def run_ours(args):
     vps = V // world if V > 0 else 1                      # views this rank renders per step
     views_global = V if V > 0 else world                  # iterations (views) per step over the whole job
     scene = make_scene(args.workload, args.isotropic)
-    hp = HotPath(scene, device=dev, fused=not args.unfused, lambda_dssim=args.lambda_dssim, mlps=args.mlps == "on")
+    hp = HotPath(scene, device=dev, fused=not args.unfused, lambda_dssim=args.lambda_dssim,
+                 mlps={"off": False, "on": True, "torch": "torch"}[args.mlps])
     order = views_of_rank(rank, world, vps)
     H, W = scene.cameras[0].image_height, scene.cameras[0].image_width
     g = torch.Generator().manual_seed(1000)
@@ -463,8 +465,23 @@ def run_ours(args):
     # dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` capture of this workload
     # (profiles/r2_*_full_raw.csv, C0 on one B200); other workloads have no capture -> null
     ncu_traffic = NCU_TRAFFIC if args.workload == "C0" and not args.isotropic and args.mlps == "off" else {}
+    if args.mlps != "off":  # the MLP kernels are tensor-core work: FLOPs, not bytes
+        J = scene.J
+        macs = lambda e, o: e * 256 + 4 * 256 * 256 + (e + 256) * 256 + 2 * 256 * 256 + 256 * o
+        fl_w, fl_d = 2 * P * macs(63, J - 1), 2 * P * macs(27, 3)
+        per["mlp_forward"] = (fl_w + fl_d) // 2  # per launch: one of the two MLPs (their mean)
+        per["mlp_backward_chain"] = (fl_w + fl_d) // 2
+        per["mlp_wgrad"] = (fl_w + fl_d) // 2
     roof = None
-    if dom:
+    if dom and dom.startswith("mlp_"):
+        fl = per.get(dom, 0)
+        tf = fl / (kern[dom]["ms_per_launch"] * 1e-3) / 1e12
+        peak_tf = float(peaks.get("bf16_tflops_sustained", 1400.0))
+        roof = {"kernel": dom, "bound": "tensor", "achieved": round(tf, 2), "peak": peak_tf, "unit": "TFLOP/s",
+                "frac": round(tf / peak_tf, 4), "traffic": None,
+                "peak_source": "measured (sustained bf16 GEMM)" if "bf16_tflops_sustained" in peaks else "fallback",
+                "algorithmic_flops_per_launch": fl, "ms_per_launch": round(kern[dom]["ms_per_launch"], 4)}
+    elif dom:
         b = per.get(dom, 0)
         achieved = b / (kern[dom]["ms_per_launch"] * 1e-3) / 1e9
         roof = {"kernel": dom, "bound": "hbm", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
@@ -522,7 +539,7 @@ def run_ours(args):
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(scene, args)
     if world == 1 and not args.no_ref_cuda:
-        rc = ref_cuda_baseline(scene, cams[0], poses[0], targets[0], steps=min(args.steps, 10), mlps=hp if args.mlps == "on" else None)
+        rc = ref_cuda_baseline(scene, cams[0], poses[0], targets[0], steps=min(args.steps, 10), mlps=hp if args.mlps != "off" else None)
         if rc:
             line["reference_cuda_b200"] = rc
     if world == 1 and args.baselines:
@@ -582,7 +599,7 @@ def run_sequence(args, rank, world, dev):
     from riggs_b200.hotpath import HotPath, PoseSequenceRenderer
 
     scene = make_scene(args.workload, args.isotropic, mode="sequence")
-    hp = HotPath(scene, device=dev, fused=True, mlps=args.mlps == "on", inference=True)
+    hp = HotPath(scene, device=dev, fused=True, mlps={"off": False, "on": True, "torch": "torch"}[args.mlps], inference=True)
     cam = scene.cameras[0].to(dev)
     H, W = cam.image_height, cam.image_width
     F_total = len(scene.poses)
@@ -855,7 +872,7 @@ def cpu_baseline(scene, args, budget_s=12.0):
     torch.set_num_threads(cores)
     os.environ.setdefault("OMP_NUM_THREADS", str(cores))
     targets = _cpu_targets(scene)
-    mlps = args.mlps == "on"
+    mlps = args.mlps != "off"
     cpu_step(scene, 0, targets[0], mlps)  # warm-up (also builds the oracle library)
     n, t0 = 0, time.time()
     while True:
@@ -884,7 +901,7 @@ def run_reference(args):
     if args.mode == "sequence":
         return run_reference_sequence(args, scene, world, cores)
     targets = _cpu_targets(scene)
-    mlps = args.mlps == "on"
+    mlps = args.mlps != "off"
     warm = max(args.warmup, 3)
     t_w = time.time()
     for i in range(warm):

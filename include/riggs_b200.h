@@ -398,9 +398,24 @@ int rg_mlp_pack(int emb_cols, int out_ch, const float* const* weights /* host ar
 /* Forward: x (N,3) -> out (N,out_ch); out_act 0 = linear head (detail_net), 1 = sigmoid (WeightMLP).  bias: (9,256)
  * fp32, the hidden layers' biases then the head's, zero padded.  Training (acts != NULL): also stores the post-ReLU
  * activations of the eight hidden layers as bf16, feature-major (8, 256, n_pad), and the encoding (64, n_pad) into emb;
- * n_pad >= N, a multiple of 64.  These are what rg_mlp_backward reads. */
+ * n_pad >= N, a multiple of 128 (columns of points past N are written as zeros).  These are what rg_mlp_backward reads. */
 int rg_mlp_forward(int N, int multires, int out_ch, int out_act, const float* x, const void* packed, const float* bias,
                    float* out, void* acts, void* emb, long long n_pad, rg_stream_t stream);
+
+/* Backward of rg_mlp_forward (the reference: torch autograd through the same ~20 ops).  g_out (N,out_ch) is dL/d out;
+ * out_fwd the forward's output (needed for the sigmoid head, else NULL); acts / emb the state the forward stored; dz
+ * scratch of 9 * 256 * n_pad bf16 (dL/d pre-activation of every layer, written here).  No gradient flows to x (it is
+ * detached, skeleton_utils/skeleton_warp.py:131).  d_weights[l] (host array of 9 device pointers, fp32, the shapes and
+ * column conventions of rg_mlp_pack) and d_bias (9,256) are ACCUMULATED into with atomics: zero them first.  Columns of
+ * a weight that rg_mlp_pack skips (the pose columns of detail_net's layers 0 and 5) get no gradient here: theirs is the
+ * outer product d_bias[l] x pose, which the caller forms.
+ * Two kernels: the chain run backwards on the tensor cores (dH = dZ W with the transposed weight image, ReLU' from the
+ * stored activations), then one tcgen05 GEMM per (layer, half of its outputs, slice of the points) that contracts dZ
+ * with the layer's inputs over the points, operands arriving as 2-D TMA tiles. */
+int rg_mlp_backward(int N, int out_ch, int out_act, int emb_cols, const float* g_out, const float* out_fwd, const void* packed,
+                    const void* acts, const void* emb, void* dz, long long n_pad, float* const* d_weights /* host, 9 */,
+                    const int* lds /* host, 9 */, const int* emb_col0 /* host, 9 */, const int* act_col0 /* host, 9 */,
+                    float* d_bias, rg_stream_t stream);
 
 /* ---- multi-GPU (no counterpart in the reference, which is single-GPU) -------------------------------- */
 

@@ -21,6 +21,7 @@
 // over the points.
 #include "../../include/riggs_b200.h"
 
+#include <cuda.h>
 #include <cuda_bf16.h>
 
 #include <algorithm>
@@ -47,15 +48,16 @@ constexpr uint32_t kColAcc = 0, kColAct = 128, kColEmb = 384, kTmemCols = 512;
 
 struct MlpLayerPlan {
     int n_quarters;  // output quarters (4 for hidden layers; 1 or 2 for the head)
-    int n_slabs;     // input k-slabs of 64: [embedding?] + [4 activation slabs?]
-    int has_emb;     // slab 0 is the embedded input
-    int has_act;     // the other slabs are the previous layer's activations
+    int n_slabs;     // input k-slabs of 64: [input-region slabs] + [4 activation slabs?]
+    int n_emb;       // leading slabs that come from the tile's input region (forward: the encoding; backward: dL/d head)
+    int has_act;     // the other slabs are the previous step's activations
     int n_last;      // columns of the last quarter (multiple of 16)
 };
 
 struct MlpArgs {
     int N;                 // points
     int n_tiles;
+    int n_steps;           // forward: 9 (eight hidden layers + head); backward: 8
     int multires;          // positional-encoding octaves (10: WeightMLP, 4: DeformMLP); embedding = 3 + 6 * multires <= 63
     int out_ch;            // head outputs
     int out_act;           // 0: none, 1: sigmoid
@@ -66,7 +68,11 @@ struct MlpArgs {
     float* out;            // (N, out_ch)
     __nv_bfloat16* acts;   // training: (8, 256, n_pad) post-ReLU activations, feature-major; null: not stored
     __nv_bfloat16* emb;    // training: (64, n_pad) embedded input, feature-major; null: not stored
-    long long n_pad;       // row pitch of acts / emb (points, multiple of 64)
+    long long n_pad;       // row pitch of acts / emb / dz (points, multiple of 128)
+    // backward chain (mlp_chain_kernel<true>): dL/d out -> dL/d(pre-activation) of every layer
+    const float* g_out;    // (N, out_ch) upstream gradient
+    const float* out_fwd;  // (N, out_ch) forward output (for the sigmoid's derivative), or null
+    __nv_bfloat16* dz;     // (9, 256, n_pad): slot l = dL/dZ_l of hidden layer l, slot 8 = dL/dZ of the head; feature-major
     MlpLayerPlan plan[kLayers + 1];
 };
 
@@ -151,8 +157,14 @@ struct MlpSmem {
 };
 
 // ---------------------------------------------------------------------------------------------------------------------
-// Forward chain.  Persistent: CTA b handles tiles b, b + gridDim.x, ...
-__global__ void __launch_bounds__(kMlpThreads, 1) mlp_forward_kernel(MlpArgs a) {
+// The chain kernel.  Persistent: CTA b handles tiles b, b + gridDim.x, ...
+// BWD = false: forward (encoding -> 8 hidden layers -> head).
+// BWD = true:  the same pipeline run backwards: step 0 multiplies dL/d(head pre-activation) by the head's weights, step j by
+//              layer 8-j's; the epilogue masks with the stored activations (ReLU') instead of adding a bias, and stores
+//              dL/dZ of every layer for the weight-gradient kernel.  No gradient is wanted for x (it is detached,
+//              skeleton_warp.py:131), so the chain stops at dZ_0.
+template <bool BWD>
+__global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
     extern __shared__ __align__(1024) unsigned char s_dyn[];
     unsigned char* ring = reinterpret_cast<unsigned char*>(align_up_dev(reinterpret_cast<size_t>(s_dyn), 1024));
     MlpSmem& sm = *reinterpret_cast<MlpSmem*>(ring + (size_t)kStages * kChunkBytes);
@@ -164,7 +176,8 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_forward_kernel(MlpArgs a) 
         for (int i = 0; i < 8; i++) mbar_init(&sm.act_ready[i >> 2][i & 3], kEpiWarps * 32);
         mbar_init(&sm.emb_ready, kEpiWarps * 32);
     }
-    for (int i = threadIdx.x; i < (kLayers + 1) * kHid; i += blockDim.x) sm.bias[i] = a.bias[i];
+    if (!BWD)
+        for (int i = threadIdx.x; i < (kLayers + 1) * kHid; i += blockDim.x) sm.bias[i] = a.bias[i];
     if (warp == kEpiWarps) tmem_alloc(&sm.tmem_base, kTmemCols);
     tc_fence_before();
     __syncthreads();
@@ -192,7 +205,7 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_forward_kernel(MlpArgs a) 
                 mbar_wait(&sm.emb_ready, t & 1);
                 tc_fence_after();
 #pragma unroll 1
-                for (int l = 0; l <= kLayers; l++) {
+                for (int l = 0; l < a.n_steps; l++) {
                     const MlpLayerPlan p = a.plan[l];
                     const uint32_t in_col = kColAct + (uint32_t)(l & 1) * 128;  // layer l reads buffer l & 1 (l >= 1)
                     const int n_use = (l - 1) >> 1;  // how often this tile has written that buffer before (parity of the wait)
@@ -206,10 +219,10 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_forward_kernel(MlpArgs a) 
                         const uint32_t d_col = tmem + kColAcc + ab * kQuarter;
                         for (int s = 0; s < p.n_slabs; s++, c++) {
                             uint32_t a_col;
-                            if (p.has_emb && s == 0) {
-                                a_col = tmem + kColEmb;
+                            if (s < p.n_emb) {
+                                a_col = tmem + kColEmb + (uint32_t)s * 32;
                             } else {
-                                const int sa = s - p.has_emb;  // activation slab = output quarter of the previous layer
+                                const int sa = s - p.n_emb;  // activation slab = output quarter of the previous layer
                                 mbar_wait(&sm.act_ready[l & 1][sa], n_use & 1);
                                 tc_fence_after();
                                 a_col = tmem + in_col + (uint32_t)sa * 32;
@@ -237,8 +250,8 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_forward_kernel(MlpArgs a) 
         for (int t = 0; t < my_tiles; t++) {
             const long long pt = ((long long)blockIdx.x + (long long)t * gridDim.x) * kTileM + row;
             const bool valid = pt < a.N;
-            // ---- positional encoding (utils/time_utils.py:208-256: x, then sin / cos per octave), bf16, into TMEM
-            {
+            if (!BWD) {
+                // ---- positional encoding (utils/time_utils.py:208-256: x, then sin / cos per octave), bf16, into TMEM
                 float e[64];
                 float xv[3] = {0.f, 0.f, 0.f};
                 if (valid) { xv[0] = a.x[3 * pt]; xv[1] = a.x[3 * pt + 1]; xv[2] = a.x[3 * pt + 2]; }
@@ -263,19 +276,54 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_forward_kernel(MlpArgs a) 
 #pragma unroll
                 for (int i = 0; i < 32; i++) pk[i] = pack_bf16(e[2 * i], e[2 * i + 1]);
                 tmem_st32(tmem + lane_base + kColEmb, pk);
-                if (a.emb && valid) {
+                if (a.emb && pt < a.n_pad) {  // rows of points past N are written as zeros: the weight-gradient GEMM sums over them
 #pragma unroll
                     for (int i = 0; i < 64; i++)
-                        if (i < n_emb) a.emb[(size_t)i * a.n_pad + pt] = __float2bfloat16_rn(e[i]);
+                        if (i < n_emb) a.emb[(size_t)i * a.n_pad + pt] = __float2bfloat16_rn(valid ? e[i] : 0.f);
                 }
-                tmem_st_wait();
-                tc_fence_before();
-                mbar_arrive(&sm.emb_ready);
-            }
+            } else {
+                // ---- dL/d(head pre-activation) of this point: the upstream gradient (times the sigmoid's derivative)
+                const int n_in = a.plan[0].n_emb;  // slabs of 64 head outputs
 #pragma unroll 1
-            for (int l = 0; l <= kLayers; l++) {
+                for (int sl = 0; sl < n_in; sl++) {
+                    uint32_t pk[32];
+#pragma unroll
+                    for (int i = 0; i < 32; i++) {
+                        float g2[2];
+#pragma unroll
+                        for (int h = 0; h < 2; h++) {
+                            const int col = sl * 64 + 2 * i + h;
+                            float gv = 0.f;
+                            if (valid && col < a.out_ch) {
+                                gv = a.g_out[(size_t)pt * a.out_ch + col];
+                                if (a.out_act == 1) {
+                                    const float sg = a.out_fwd[(size_t)pt * a.out_ch + col];
+                                    gv *= sg * (1.f - sg);
+                                }
+                            }
+                            g2[h] = gv;
+                        }
+                        pk[i] = pack_bf16(g2[0], g2[1]);
+                    }
+                    tmem_st32(tmem + lane_base + kColEmb + (uint32_t)sl * 32, pk);
+                    if (pt < a.n_pad) {
+                        __nv_bfloat16* dst = a.dz + ((size_t)kLayers * kHid + (size_t)sl * 64) * a.n_pad + pt;
+#pragma unroll
+                        for (int i = 0; i < 32; i++) {
+                            const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&pk[i]);
+                            dst[(size_t)(2 * i) * a.n_pad] = h.x;
+                            dst[(size_t)(2 * i + 1) * a.n_pad] = h.y;
+                        }
+                    }
+                }
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            mbar_arrive(&sm.emb_ready);
+#pragma unroll 1
+            for (int l = 0; l < a.n_steps; l++) {
                 const MlpLayerPlan p = a.plan[l];
-                const uint32_t out_col = kColAct + (uint32_t)((l + 1) & 1) * 128;  // layer l writes buffer (l + 1) & 1
+                const uint32_t out_col = kColAct + (uint32_t)((l + 1) & 1) * 128;  // step l writes buffer (l + 1) & 1
                 const float* bias = sm.bias + l * kHid;
 #pragma unroll 1
                 for (int q = 0; q < p.n_quarters; q++, g++) {
@@ -286,20 +334,34 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_forward_kernel(MlpArgs a) 
                     tmem_ld32(tmem + lane_base + kColAcc + ab * kQuarter, v0);
                     tmem_ld32(tmem + lane_base + kColAcc + ab * kQuarter + 32, v1);
                     tmem_ld_wait();
-                    if (l < kLayers) {
+                    if (BWD || l < kLayers) {
                         uint32_t pk[32];
+                        // forward: this layer's slot; backward step l produces dZ of hidden layer 7 - l
+                        const int slot = BWD ? (kLayers - 1 - l) : l;
+                        const size_t goff = ((size_t)slot * kHid + (size_t)q * kQuarter) * a.n_pad + (size_t)pt;
+                        const bool in_buf = pt < a.n_pad;
 #pragma unroll
                         for (int i = 0; i < 32; i++) {
                             const int c0 = 2 * i;
                             const float x0 = c0 < 32 ? __uint_as_float(v0[c0]) : __uint_as_float(v1[c0 - 32]);
                             const float x1 = c0 + 1 < 32 ? __uint_as_float(v0[c0 + 1]) : __uint_as_float(v1[c0 + 1 - 32]);
-                            const float h0 = fmaxf(x0 + bias[q * kQuarter + c0], 0.f);
-                            const float h1 = fmaxf(x1 + bias[q * kQuarter + c0 + 1], 0.f);
+                            float h0, h1;
+                            if (!BWD) {
+                                h0 = fmaxf(x0 + bias[q * kQuarter + c0], 0.f);
+                                h1 = fmaxf(x1 + bias[q * kQuarter + c0 + 1], 0.f);
+                                if (!valid) { h0 = 0.f; h1 = 0.f; }
+                            } else {  // ReLU': pass the gradient where the stored activation is positive
+                                const bool m0 = valid && __bfloat162float(a.acts[goff + (size_t)c0 * a.n_pad]) > 0.f;
+                                const bool m1 = valid && __bfloat162float(a.acts[goff + (size_t)(c0 + 1) * a.n_pad]) > 0.f;
+                                h0 = m0 ? x0 : 0.f;
+                                h1 = m1 ? x1 : 0.f;
+                            }
                             pk[i] = pack_bf16(h0, h1);
                         }
                         tmem_st32(tmem + lane_base + out_col + (uint32_t)q * 32, pk);
-                        if (a.acts && valid) {  // training: post-ReLU activations, feature-major (coalesced over the warp's points)
-                            __nv_bfloat16* dst = a.acts + ((size_t)l * kHid + (size_t)q * kQuarter) * a.n_pad + pt;
+                        __nv_bfloat16* store = BWD ? a.dz : a.acts;  // training state, feature-major (coalesced over the warp's points)
+                        if (store && in_buf) {
+                            __nv_bfloat16* dst = store + goff;
 #pragma unroll
                             for (int i = 0; i < 32; i++) {
                                 const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&pk[i]);
@@ -336,23 +398,26 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_forward_kernel(MlpArgs a) 
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// Weight packing: fp32 (out, in) matrices of torch.nn.Linear -> bf16 chunk images in the order the kernel consumes them.
+// Weight packing: fp32 (out, in) matrices of torch.nn.Linear -> bf16 chunk images in the order the chain kernel consumes
+// them.  Forward image: chunk (layer, quarter q, slab s) holds rows n = 64 q + r of W_l and 64 of its input columns.
+// Backward image (transposed): step j multiplies by W^T -- chunk (step, q, s) holds rows k = 64 q + r (an INPUT feature of
+// the forward layer) and columns n = 64 s + kk (its outputs): B[k][n] = W[n][act_col0 + k].
 struct PackLayer {
     const float* w;   // (n_out, ld) row-major
     int n_out, ld;
-    int emb_col0, emb_cols;  // columns of the embedded-input part (-1: none)
+    int emb_col0, emb_cols;  // forward: columns of the embedded-input part (-1: none)
     int act_col0;            // first column of the 256 activation inputs (-1: none)
-    int chunk0;              // index of the layer's first chunk
+    int chunk0;              // index of the step's first chunk
     int n_quarters, n_slabs;
 };
 struct PackArgs {
     PackLayer layer[kLayers + 1];
     unsigned char* out;
-    int total_chunks;
+    int total_chunks, n_steps, transposed;
 };
 
 __global__ void mlp_pack_kernel(PackArgs a) {
-    // one thread per 16-byte piece: 8 input columns of one output row of one chunk
+    // one thread per 16-byte piece: 8 columns of one row of one chunk
     const long long piece = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const long long n_pieces = (long long)a.total_chunks * (kChunkBytes / 16);
     if (piece >= n_pieces) return;
@@ -360,23 +425,28 @@ __global__ void mlp_pack_kernel(PackArgs a) {
     const int in_chunk = (int)(piece % (kChunkBytes / 16));
     const int r = in_chunk >> 3, cchunk = in_chunk & 7;  // row of the chunk, logical 16-byte column group
     int l = 0;
-    while (l < kLayers && chunk >= a.layer[l + 1].chunk0) l++;
+    while (l + 1 < a.n_steps && chunk >= a.layer[l + 1].chunk0) l++;
     const PackLayer L = a.layer[l];
     const int rel = chunk - L.chunk0;
     const int q = rel / L.n_slabs, s = rel % L.n_slabs;
-    const int n = q * kQuarter + r;
+    const int row = q * kQuarter + r;
     __nv_bfloat16 v[8];
 #pragma unroll
     for (int j = 0; j < 8; j++) {
         const int kk = cchunk * 8 + j;  // column inside the slab
         float w = 0.f;
-        if (n < L.n_out) {
-            if (L.emb_col0 >= 0 && s == 0) {
-                if (kk < L.emb_cols) w = L.w[(size_t)n * L.ld + L.emb_col0 + kk];
-            } else {
-                const int sa = s - (L.emb_col0 >= 0 ? 1 : 0);
-                w = L.w[(size_t)n * L.ld + L.act_col0 + sa * kQuarter + kk];
+        if (!a.transposed) {
+            if (row < L.n_out) {
+                if (L.emb_col0 >= 0 && s == 0) {
+                    if (kk < L.emb_cols) w = L.w[(size_t)row * L.ld + L.emb_col0 + kk];
+                } else {
+                    const int sa = s - (L.emb_col0 >= 0 ? 1 : 0);
+                    w = L.w[(size_t)row * L.ld + L.act_col0 + sa * kQuarter + kk];
+                }
             }
+        } else {
+            const int n = s * kQuarter + kk;  // forward output = contraction index of the backward step
+            if (n < L.n_out) w = L.w[(size_t)n * L.ld + L.act_col0 + row];
         }
         v[j] = __float2bfloat16_rn(w);
     }
@@ -385,13 +455,14 @@ __global__ void mlp_pack_kernel(PackArgs a) {
     *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(v);
 }
 
-static int plan_layers(int out_ch, MlpLayerPlan* plan, int* chunk0, int* total) {
+// forward plan: 8 hidden layers + head
+static void plan_forward(int out_ch, MlpLayerPlan* plan, int* chunk0, int* total) {
     int c = 0;
     for (int l = 0; l <= kLayers; l++) {
         MlpLayerPlan p;
-        p.has_emb = (l == 0 || l == kSkipInto) ? 1 : 0;
+        p.n_emb = (l == 0 || l == kSkipInto) ? 1 : 0;
         p.has_act = l > 0 ? 1 : 0;
-        p.n_slabs = p.has_emb + 4 * p.has_act;
+        p.n_slabs = p.n_emb + 4 * p.has_act;
         if (l < kLayers) { p.n_quarters = 4; p.n_last = kQuarter; }
         else {
             const int out_pad = (out_ch + 15) / 16 * 16;
@@ -403,6 +474,211 @@ static int plan_layers(int out_ch, MlpLayerPlan* plan, int* chunk0, int* total) 
         c += p.n_quarters * p.n_slabs;
     }
     *total = c;
+}
+// backward plan: step 0 = through the head (its input region holds dL/d head, 1 or 2 slabs), steps 1..7 = through layers 7..1
+static void plan_backward(int out_ch, MlpLayerPlan* plan, int* chunk0, int* total) {
+    int c = 0;
+    for (int j = 0; j < kLayers; j++) {
+        MlpLayerPlan p;
+        p.n_emb = j == 0 ? (out_ch + kQuarter - 1) / kQuarter : 0;
+        p.has_act = j > 0 ? 1 : 0;
+        p.n_slabs = p.n_emb + 4 * p.has_act;
+        p.n_quarters = 4;
+        p.n_last = kQuarter;
+        plan[j] = p;
+        chunk0[j] = c;
+        c += p.n_quarters * p.n_slabs;
+    }
+    *total = c;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Weight gradients: dW_l[n][k] = sum over the points of dZ_l[pt][n] * H_{l-1}[pt][k]  (H_{-1} = the encoding; layer 5 sees
+// both), db_l[n] = sum dZ_l[pt][n].  Both operands were stored feature-major, i.e. K-major for this contraction, so they come
+// in as plain 2-D TMA tiles (128-byte swizzle) and go straight into tcgen05.mma from shared memory.  One CTA owns one
+// (layer, half of the outputs) pair and one slice of the points; its 128 x (256 + 64 + 16) fp32 result lives in TMEM and is
+// added to the fp32 gradient tensors (torch layout) with atomics at the end.  The bias gradient is the product with a
+// tile of ones.
+constexpr int kWgStages = 3;
+constexpr int kWgATile = 128 * 128;   // dZ^T tile: 128 outputs x 64 points, bf16
+constexpr int kWgBTile = 256 * 128;   // H^T tile: 256 inputs x 64 points
+constexpr int kWgETile = 64 * 128;    // encoding^T tile: 64 x 64 points
+constexpr int kWgStageBytes = kWgATile + kWgBTile + kWgETile;
+constexpr int kWgThreads = 6 * 32;    // producer, MMA issuer, four epilogue warps
+constexpr uint32_t kWgColAct = 0, kWgColEmb = 256, kWgColBias = 320;
+
+struct WgItem {
+    int layer;      // 0..8 (8 = head)
+    int m0;         // first output row of this CTA's half
+    int rows;       // valid output rows from m0 on (<= 128)
+    int has_act, has_emb;
+    float* dw;      // (n_out, ld) fp32
+    int ld, emb_col0, emb_cols, act_col0;
+    float* db;      // (n_out)
+};
+struct WgArgs {
+    WgItem item[2 * (kLayers + 1)];
+    int n_items, n_splits;
+    long long n_slabs;  // n_pad / 64
+};
+
+struct WgSmem {
+    uint64_t full[kWgStages], empty[kWgStages], done;
+    uint32_t tmem_base;
+};
+
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const void* tmap, int x, int y, uint64_t* bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(tmap), "r"(x), "r"(y), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T
+__device__ __forceinline__ void mma_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc_, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}\n" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc_), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+__global__ void __launch_bounds__(kWgThreads, 1)
+mlp_wgrad_kernel(WgArgs a, const __grid_constant__ CUtensorMap tm_dz, const __grid_constant__ CUtensorMap tm_act,
+                 const __grid_constant__ CUtensorMap tm_emb) {
+    extern __shared__ __align__(1024) unsigned char s_dyn[];
+    unsigned char* ring = reinterpret_cast<unsigned char*>(align_up_dev(reinterpret_cast<size_t>(s_dyn), 1024));
+    unsigned char* ones = ring + (size_t)kWgStages * kWgStageBytes;  // 16 rows x 128 bytes of bf16 1.0
+    WgSmem& sm = *reinterpret_cast<WgSmem*>(ones + 16 * 128);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const WgItem it = a.item[blockIdx.x / a.n_splits];
+    const int split = blockIdx.x % a.n_splits;
+    const long long per = (a.n_slabs + a.n_splits - 1) / a.n_splits;
+    const long long s0 = per * split, s1 = s0 + per < a.n_slabs ? s0 + per : a.n_slabs;
+    const int n_my = s1 > s0 ? (int)(s1 - s0) : 0;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kWgStages; i++) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], 1); }
+        mbar_init(&sm.done, 1);
+    }
+    for (int i = threadIdx.x; i < 16 * 64; i += blockDim.x) reinterpret_cast<__nv_bfloat16*>(ones)[i] = __float2bfloat16_rn(1.0f);
+    if (warp == 1) tmem_alloc(&sm.tmem_base, 512);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the ones tile is read by the tensor core (async proxy)
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = sm.tmem_base;
+    const uint32_t stage_bytes = kWgATile + (it.has_act ? kWgBTile : 0) + (it.has_emb ? kWgETile : 0);
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int i = 0; i < n_my; i++) {
+                const int st = i % kWgStages;
+                mbar_wait(&sm.empty[st], ((i / kWgStages) & 1) ^ 1);
+                unsigned char* base = ring + (size_t)st * kWgStageBytes;
+                const int x = (int)((s0 + i) * 64);
+                mbar_expect_tx(&sm.full[st], stage_bytes);
+                tma_load_2d(base, &tm_dz, x, it.layer * kHid + it.m0, &sm.full[st]);
+                if (it.has_act) tma_load_2d(base + kWgATile, &tm_act, x, (it.layer - 1) * kHid, &sm.full[st]);
+                if (it.has_emb) tma_load_2d(base + kWgATile + kWgBTile, &tm_emb, x, 0, &sm.full[st]);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t id_act = instr_desc(256), id_emb = instr_desc(64), id_one = instr_desc(16);
+            const uint32_t ones_addr = smem_u32(ones);
+            for (int i = 0; i < n_my; i++) {
+                const int st = i % kWgStages;
+                mbar_wait(&sm.full[st], (i / kWgStages) & 1);
+                tc_fence_after();
+                const uint32_t base = smem_u32(ring + (size_t)st * kWgStageBytes);
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const uint64_t ad = b_desc(base + (uint32_t)k * 32);
+                    const uint32_t acc = (i | k) != 0;
+                    if (it.has_act) mma_ss(tmem + kWgColAct, ad, b_desc(base + kWgATile + (uint32_t)k * 32), id_act, acc);
+                    if (it.has_emb) mma_ss(tmem + kWgColEmb, ad, b_desc(base + kWgATile + kWgBTile + (uint32_t)k * 32), id_emb, acc);
+                    mma_ss(tmem + kWgColBias, ad, b_desc(ones_addr), id_one, acc);  // every point weighs 1: the k-step does not matter
+                }
+                tc_commit(&sm.empty[st]);
+            }
+            tc_commit(&sm.done);
+        }
+    } else if (n_my > 0) {
+        // ---- epilogue: thread = output row; add the tile to the fp32 gradient tensors
+        const int ew = warp & 3;  // a warp reaches the TMEM lanes 32 (warp % 4) .. +31 only: warps 2, 3, 4, 5 -> quarters 2, 3, 0, 1
+        const uint32_t lane_base = (uint32_t)(ew * 32) << 16;
+        const int r = ew * 32 + lane;
+        mbar_wait(&sm.done, 0);
+        tc_fence_after();
+        const bool row_ok = r < it.rows;
+        float* dwrow = it.dw + (size_t)(it.m0 + r) * it.ld;
+        if (it.has_act) {
+#pragma unroll 1
+            for (int c0 = 0; c0 < 256; c0 += 32) {
+                uint32_t v[32];
+                tmem_ld32(tmem + lane_base + kWgColAct + (uint32_t)c0, v);
+                tmem_ld_wait();
+                if (row_ok) {
+#pragma unroll
+                    for (int i = 0; i < 32; i++) atomicAdd(dwrow + it.act_col0 + c0 + i, __uint_as_float(v[i]));
+                }
+            }
+        }
+        if (it.has_emb) {
+#pragma unroll 1
+            for (int c0 = 0; c0 < 64; c0 += 32) {
+                uint32_t v[32];
+                tmem_ld32(tmem + lane_base + kWgColEmb + (uint32_t)c0, v);
+                tmem_ld_wait();
+                if (row_ok) {
+#pragma unroll
+                    for (int i = 0; i < 32; i++)
+                        if (c0 + i < it.emb_cols) atomicAdd(dwrow + it.emb_col0 + c0 + i, __uint_as_float(v[i]));
+                }
+            }
+        }
+        {
+            uint32_t v[32];
+            tmem_ld32(tmem + lane_base + kWgColBias, v);  // 16 columns are meaningful, all equal
+            tmem_ld_wait();
+            if (row_ok) atomicAdd(it.db + it.m0 + r, __uint_as_float(v[0]));
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
+// 2-D bf16 tensor map over a feature-major (rows, n_pad) array: box = 64 points x box_rows features, 128-byte swizzle
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
+static int make_tmap(CUtensorMap* tm, void* base, long long rows, long long n_pad, int box_rows) {
+    EncodeTiledFn fn = encode_tiled_fn();
+    if (!fn) { set_error("rg_mlp_backward: cuTensorMapEncodeTiled is not available from this driver"); return -1; }
+    cuuint64_t dims[2] = {(cuuint64_t)n_pad, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)n_pad * 2};
+    cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("rg_mlp_backward: cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")"); return -1; }
     return 0;
 }
 
@@ -414,10 +690,11 @@ extern "C" {
 
 size_t rg_mlp_packed_bytes(int out_ch) {
     MlpLayerPlan plan[kLayers + 1];
-    int chunk0[kLayers + 1], total = 0;
+    int chunk0[kLayers + 1], tf = 0, tb = 0;
     if (out_ch < 1 || out_ch > 128) return 0;
-    plan_layers(out_ch, plan, chunk0, &total);
-    return (size_t)total * kChunkBytes;
+    plan_forward(out_ch, plan, chunk0, &tf);
+    plan_backward(out_ch, plan, chunk0, &tb);
+    return (size_t)(tf + tb) * kChunkBytes;  // forward image, then the transposed image of the backward chain
 }
 
 int rg_mlp_pack(int emb_cols, int out_ch, const float* const* weights, const int* lds, const int* emb_col0, const int* act_col0,
@@ -427,24 +704,50 @@ int rg_mlp_pack(int emb_cols, int out_ch, const float* const* weights, const int
         set_error("rg_mlp_pack: bad argument (embedding of at most 63 columns, at most 128 outputs)");
         return -1;
     }
+    for (int l = 0; l <= kLayers; l++)
+        if (!weights[l]) { set_error("rg_mlp_pack: null weight matrix"); return -1; }
     MlpLayerPlan plan[kLayers + 1];
     int chunk0[kLayers + 1], total = 0;
-    plan_layers(out_ch, plan, chunk0, &total);
+    LaunchScope ls("mlp_pack", stream, 2);
+    // ---- forward image
+    plan_forward(out_ch, plan, chunk0, &total);
     PackArgs a;
     for (int l = 0; l <= kLayers; l++) {
         PackLayer& L = a.layer[l];
         L.w = weights[l]; L.ld = lds[l]; L.n_out = l < kLayers ? kHid : out_ch;
-        L.emb_col0 = plan[l].has_emb ? emb_col0[l] : -1; L.emb_cols = emb_cols;
+        L.emb_col0 = plan[l].n_emb ? emb_col0[l] : -1; L.emb_cols = emb_cols;
         L.act_col0 = plan[l].has_act ? act_col0[l] : -1;
         L.chunk0 = chunk0[l]; L.n_quarters = plan[l].n_quarters; L.n_slabs = plan[l].n_slabs;
-        if (!L.w) { set_error("rg_mlp_pack: null weight matrix"); return -1; }
     }
     a.out = static_cast<unsigned char*>(packed);
-    a.total_chunks = total;
-    const long long pieces = (long long)total * (kChunkBytes / 16);
-    LaunchScope ls("mlp_pack", stream);
+    a.total_chunks = total; a.n_steps = kLayers + 1; a.transposed = 0;
+    long long pieces = (long long)total * (kChunkBytes / 16);
+    mlp_pack_kernel<<<(unsigned)((pieces + 255) / 256), 256, 0, stream>>>(a);
+    // ---- backward image: step 0 uses the head's weights, step j layer 8 - j's (activation columns only)
+    const size_t fwd_bytes = (size_t)total * kChunkBytes;
+    plan_backward(out_ch, plan, chunk0, &total);
+    for (int j = 0; j < kLayers; j++) {
+        const int l = kLayers - j;  // 8 = head, 7, ..., 1
+        PackLayer& L = a.layer[j];
+        L.w = weights[l]; L.ld = lds[l]; L.n_out = l < kLayers ? kHid : out_ch;
+        L.emb_col0 = -1; L.emb_cols = 0; L.act_col0 = act_col0[l];
+        L.chunk0 = chunk0[j]; L.n_quarters = plan[j].n_quarters; L.n_slabs = plan[j].n_slabs;
+    }
+    a.out = static_cast<unsigned char*>(packed) + fwd_bytes;
+    a.total_chunks = total; a.n_steps = kLayers; a.transposed = 1;
+    pieces = (long long)total * (kChunkBytes / 16);
     mlp_pack_kernel<<<(unsigned)((pieces + 255) / 256), 256, 0, stream>>>(a);
     return check_launch("rg_mlp_pack", stream, false);
+}
+
+static int launch_chain(bool bwd, MlpArgs& a, cudaStream_t stream) {
+    const size_t smem = (size_t)kStages * kChunkBytes + sizeof(MlpSmem) + 1024;
+    const void* fn = bwd ? reinterpret_cast<const void*>(mlp_chain_kernel<true>) : reinterpret_cast<const void*>(mlp_chain_kernel<false>);
+    if (ensure_dyn_smem(fn, (int)smem)) return -1;
+    const int grid = std::min(a.n_tiles, RG_NUM_SMS);
+    if (bwd) mlp_chain_kernel<true><<<grid, kMlpThreads, smem, stream>>>(a);
+    else mlp_chain_kernel<false><<<grid, kMlpThreads, smem, stream>>>(a);
+    return 0;
 }
 
 int rg_mlp_forward(int N, int multires, int out_ch, int out_act, const float* x, const void* packed, const float* bias,
@@ -454,20 +757,76 @@ int rg_mlp_forward(int N, int multires, int out_ch, int out_act, const float* x,
         set_error("rg_mlp_forward: bad argument");
         return -1;
     }
-    if ((acts || emb) && (n_pad < N || (n_pad & 63))) { set_error("rg_mlp_forward: n_pad must be a multiple of 64 and >= N"); return -1; }
+    if ((acts || emb) && (n_pad < N || (n_pad & 127) || !acts || !emb)) {
+        set_error("rg_mlp_forward: training state needs both acts and emb, n_pad a multiple of 128 and >= N");
+        return -1;
+    }
     if (N == 0) return 0;
     MlpArgs a = {};
     int chunk0[kLayers + 1];
-    plan_layers(out_ch, a.plan, chunk0, &a.total_chunks);
+    plan_forward(out_ch, a.plan, chunk0, &a.total_chunks);
+    a.n_steps = kLayers + 1;
     a.N = N; a.n_tiles = (N + kTileM - 1) / kTileM; a.multires = multires; a.out_ch = out_ch; a.out_act = out_act;
     a.x = x; a.w_packed = static_cast<const unsigned char*>(packed); a.bias = bias; a.out = out;
     a.acts = static_cast<__nv_bfloat16*>(acts); a.emb = static_cast<__nv_bfloat16*>(emb); a.n_pad = n_pad;
-    const size_t smem = (size_t)kStages * kChunkBytes + sizeof(MlpSmem) + 1024;
-    if (ensure_dyn_smem(reinterpret_cast<const void*>(mlp_forward_kernel), (int)smem)) return -1;
-    const int grid = std::min(a.n_tiles, RG_NUM_SMS);
     LaunchScope ls("mlp_forward", stream);
-    mlp_forward_kernel<<<grid, kMlpThreads, smem, stream>>>(a);
+    if (launch_chain(false, a, stream)) return -1;
     return check_launch("rg_mlp_forward", stream, false);
+}
+
+int rg_mlp_backward(int N, int out_ch, int out_act, int emb_cols, const float* g_out, const float* out_fwd, const void* packed,
+                    const void* acts, const void* emb, void* dz, long long n_pad, float* const* d_weights, const int* lds,
+                    const int* emb_col0, const int* act_col0, float* d_bias, rg_stream_t stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (N < 0 || out_ch < 1 || out_ch > 128 || !g_out || !packed || !acts || !emb || !dz || !d_weights || !lds || !emb_col0 ||
+        !act_col0 || !d_bias || (out_act == 1 && !out_fwd) || n_pad < N || (n_pad & 127)) {
+        set_error("rg_mlp_backward: bad argument");
+        return -1;
+    }
+    if (N == 0) return 0;
+    // ---- 1. the chain, backwards: dL/dZ of every layer
+    MlpArgs a = {};
+    MlpLayerPlan fplan[kLayers + 1];
+    int chunk0[kLayers + 1], fwd_chunks = 0;
+    plan_forward(out_ch, fplan, chunk0, &fwd_chunks);
+    plan_backward(out_ch, a.plan, chunk0, &a.total_chunks);
+    a.n_steps = kLayers;
+    a.N = N; a.n_tiles = (N + kTileM - 1) / kTileM; a.out_ch = out_ch; a.out_act = out_act;
+    a.w_packed = static_cast<const unsigned char*>(packed) + (size_t)fwd_chunks * kChunkBytes;
+    a.acts = static_cast<__nv_bfloat16*>(const_cast<void*>(acts));
+    a.n_pad = n_pad; a.g_out = g_out; a.out_fwd = out_fwd; a.dz = static_cast<__nv_bfloat16*>(dz);
+    {
+        LaunchScope ls("mlp_backward_chain", stream);
+        if (launch_chain(true, a, stream)) return -1;
+    }
+    // ---- 2. weight and bias gradients
+    CUtensorMap tm_dz, tm_act, tm_emb;
+    if (make_tmap(&tm_dz, dz, (long long)(kLayers + 1) * kHid, n_pad, 128)) return -1;
+    if (make_tmap(&tm_act, const_cast<void*>(acts), (long long)kLayers * kHid, n_pad, 256)) return -1;
+    if (make_tmap(&tm_emb, const_cast<void*>(emb), 64, n_pad, 64)) return -1;
+    WgArgs w = {};
+    int n = 0;
+    for (int l = 0; l <= kLayers; l++) {
+        const int n_out = l < kLayers ? kHid : out_ch;
+        for (int m0 = 0; m0 < n_out; m0 += 128) {
+            WgItem& it = w.item[n++];
+            it.layer = l; it.m0 = m0; it.rows = std::min(128, n_out - m0);
+            it.has_act = l > 0; it.has_emb = (l == 0 || l == kSkipInto);
+            it.dw = d_weights[l]; it.ld = lds[l]; it.emb_col0 = emb_col0[l]; it.emb_cols = emb_cols; it.act_col0 = act_col0[l];
+            it.db = d_bias + (size_t)l * kHid;
+            if (!it.dw) { set_error("rg_mlp_backward: null gradient tensor"); return -1; }
+        }
+    }
+    w.n_items = n;
+    w.n_slabs = n_pad / 64;
+    w.n_splits = (int)std::max<long long>(1, std::min<long long>(w.n_slabs, (2 * RG_NUM_SMS) / n));
+    const size_t smem = (size_t)kWgStages * kWgStageBytes + 16 * 128 + sizeof(WgSmem) + 1024;
+    if (ensure_dyn_smem(reinterpret_cast<const void*>(mlp_wgrad_kernel), (int)smem)) return -1;
+    {
+        LaunchScope ls("mlp_wgrad", stream);
+        mlp_wgrad_kernel<<<n * w.n_splits, kWgThreads, smem, stream>>>(w, tm_dz, tm_act, tm_emb);
+    }
+    return check_launch("rg_mlp_backward", stream, false);
 }
 
 }  // extern "C"

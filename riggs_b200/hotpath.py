@@ -40,6 +40,7 @@ class HotPath:
         self.mlps = bool(mlps)
         self.inference = bool(inference)
         self.weight_mlp = self.detail_net = None
+        self.fused_weight_mlp = self.fused_detail_net = None
         self._weight_cache = None
         if self.mlps:
             torch.manual_seed(4321)  # the CPU arm of bench.py draws the same weights
@@ -48,6 +49,9 @@ class HotPath:
             with torch.no_grad():
                 dn.gaussian_warp.weight.normal_(0, 1e-3)  # the reference's 1e-5 start would leave the offsets at ~0
             self.weight_mlp, self.detail_net = wm.to(device), dn.to(device)
+            if mlps != "torch":  # the tensor-core kernels (csrc/mlp.cu); "torch": the eager fp32 modules, for comparison
+                from .mlp import FusedSkipMLP
+                self.fused_weight_mlp, self.fused_detail_net = FusedSkipMLP(self.weight_mlp), FusedSkipMLP(self.detail_net)
         self.pipe = _Pipe()
         self.bg = torch.zeros(3, device=device)
         self.isotropic = self.pc.use_isotropic_gs
@@ -85,13 +89,18 @@ class HotPath:
         if not self.mlps:
             return self.mlp_weight, self.offsets
         x = self.pc._xyz.detach()
-        q = pose["local_rotation"].detach().reshape(-1)[None].expand(x.shape[0], -1)
+        if self.fused_weight_mlp is not None:
+            q = pose["local_rotation"].detach().reshape(-1)
+            wmlp, dnet = self.fused_weight_mlp, (lambda xx, qq: self.fused_detail_net(xx, qq))
+        else:
+            q = pose["local_rotation"].detach().reshape(-1)[None].expand(x.shape[0], -1)
+            wmlp, dnet = self.weight_mlp, self.detail_net
         if self.inference:
             with torch.no_grad():
                 if self._weight_cache is None:
-                    self._weight_cache = self.weight_mlp(x)
-                return self._weight_cache, self.detail_net(x, q)
-        return self.weight_mlp(x), self.detail_net(x, q)
+                    self._weight_cache = wmlp(x)
+                return self._weight_cache, dnet(x, q)
+        return wmlp(x), dnet(x, q)
 
     def named_parameters(self):
         pc = self.pc

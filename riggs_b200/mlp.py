@@ -55,10 +55,7 @@ class FusedSkipMLP:
         n = len(wc)
         ptrs = (C.c_void_p * n)(*[w.data_ptr() for w in wc])
         lds = (C.c_int * n)(*[w.shape[1] for w in wc])
-        emb0 = (C.c_int * n)(*[0] * n)
-        act0 = [0] * n
-        act0[5] = self.emb_cols + self.extra  # layer 5 sees [encoding, pose, activations]
-        act0 = (C.c_int * n)(*act0)
+        emb0, act0 = self._col_args()
         with torch.cuda.device(self.packed.device):
             check(_lib.lib().rg_mlp_pack(self.emb_cols, self.out_ch, ptrs, lds, emb0, act0, self.packed.data_ptr(), stream_ptr()),
                   "rg_mlp_pack")
@@ -82,11 +79,18 @@ class FusedSkipMLP:
         return b
 
     # ---- evaluation ------------------------------------------------------------------------------------------
+    def _col_args(self):
+        n = 9
+        act0 = [0] * n
+        act0[5] = self.emb_cols + self.extra  # layer 5 sees [encoding, pose, activations]
+        return (C.c_int * n)(*[0] * n), (C.c_int * n)(*act0)
+
     def forward(self, x: torch.Tensor, pose: Optional[torch.Tensor] = None, save: bool = False):
-        """x (N,3) -> (N,out_ch).  save=True also returns the state the backward needs."""
+        """x (N,3) -> (N,out_ch), no autograd.  save=True also returns the state ``backward`` needs."""
         if not x.is_cuda:
             raise _lib.RiggsError("FusedSkipMLP needs CUDA tensors; riggs_b200 has no CPU path")
-        self.repack()
+        # under CUDA-graph capture the packing is recorded too: a replay then packs whatever the weights hold by then
+        self.repack(force=torch.cuda.is_current_stream_capturing())
         x = f32c(x.detach())
         N = x.shape[0]
         out = torch.empty(N, self.out_ch, device=x.device)
@@ -94,14 +98,70 @@ class FusedSkipMLP:
         acts = emb = None
         n_pad = 0
         if save:
-            n_pad = (N + 63) // 64 * 64
+            n_pad = (N + 127) // 128 * 128
             acts = torch.empty(8, 256, n_pad, dtype=torch.bfloat16, device=x.device)
-            emb = torch.zeros(64, n_pad, dtype=torch.bfloat16, device=x.device)
+            emb = torch.empty(64, n_pad, dtype=torch.bfloat16, device=x.device)
+            emb[self.emb_cols:].zero_()  # the kernel writes the rows of the encoding only
         with torch.cuda.device(x.device):
             check(_lib.lib().rg_mlp_forward(N, self.multires, self.out_ch, self.out_act, ptr(x), self.packed.data_ptr(),
                                             bias.data_ptr(), ptr(out), ptr(acts), ptr(emb), n_pad, stream_ptr()), "rg_mlp_forward")
         if save:
-            return out, (x, acts, emb, n_pad, bias)
+            return out, (N, acts, emb, n_pad, pose.detach().reshape(-1).float() if pose is not None else None)
         return out
 
-    __call__ = forward
+    def backward(self, g_out: torch.Tensor, out: torch.Tensor, state):
+        """dL/d out (N,out_ch) -> gradients of the module's parameters, in the order of ``parameters()``:
+        [linear.0.weight, linear.0.bias, ..., head.weight, head.bias]."""
+        N, acts, emb, n_pad, pose = state
+        dev = g_out.device
+        ws = self._weights()
+        dws = [torch.zeros_like(w, dtype=torch.float32) for w in ws]
+        db = torch.zeros(9, 256, device=dev)
+        dz = torch.empty(9, 256, n_pad, dtype=torch.bfloat16, device=dev)
+        n = len(ws)
+        ptrs = (C.c_void_p * n)(*[d.data_ptr() for d in dws])
+        lds = (C.c_int * n)(*[w.shape[1] for w in ws])
+        emb0, act0 = self._col_args()
+        g = f32c(g_out)
+        with torch.cuda.device(dev):
+            check(_lib.lib().rg_mlp_backward(N, self.out_ch, self.out_act, self.emb_cols, ptr(g), ptr(f32c(out)) if self.out_act else None,
+                                             self.packed.data_ptr(), ptr(acts), ptr(emb), ptr(dz), n_pad, ptrs, lds, emb0, act0,
+                                             db.data_ptr(), stream_ptr()), "rg_mlp_backward")
+        if self.extra:  # the pose columns saw the same input for every point: their gradient is d_bias (x) pose
+            lo, hi = self.emb_cols, self.emb_cols + self.extra
+            dws[0][:, lo:hi] = torch.outer(db[0], pose)
+            dws[5][:, lo:hi] = torch.outer(db[5], pose)
+        grads = []
+        for i in range(8):
+            grads += [dws[i], db[i].clone()]
+        grads += [dws[8], db[8, :self.out_ch].clone()]
+        return grads
+
+    def parameters(self):
+        ps = []
+        for l in self.layers:
+            ps += [l.weight, l.bias]
+        return ps + [self.head.weight, self.head.bias]
+
+    def __call__(self, x: torch.Tensor, pose: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Differentiable w.r.t. the module's parameters when autograd is recording (x and the pose are inputs the
+        reference detaches, skeleton_warp.py:131, 152); plain inference otherwise."""
+        if not torch.is_grad_enabled() or not any(p.requires_grad for p in self.parameters()):
+            return self.forward(x, pose)
+        return _FusedMLPFunction.apply(self, x, pose, *self.parameters())
+
+
+class _FusedMLPFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, mlp: FusedSkipMLP, x, pose, *params):
+        out, state = mlp.forward(x, pose, save=True)
+        ctx.mlp, ctx.state = mlp, state
+        ctx.save_for_backward(out)
+        return out
+
+    @staticmethod
+    def backward(ctx, g_out):
+        (out,) = ctx.saved_tensors
+        grads = ctx.mlp.backward(g_out, out, ctx.state)
+        ctx.state = None
+        return (None, None, None, *grads)

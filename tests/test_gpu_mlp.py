@@ -39,8 +39,9 @@ def test_fused_mlp_forward_matches_torch(N, J):
     with torch.no_grad():
         want_w = wm(x)
         want_d = dn(x, pose[None].expand(N, -1))
-    got_w = fw(x)
-    got_d = fd(x, pose)
+    with torch.no_grad():
+        got_w = fw(x)
+        got_d = fd(x, pose)
     torch.cuda.synchronize()
     ew = helpers.rel_err(got_w.cpu().numpy(), want_w.cpu().numpy())
     ed = helpers.rel_err(got_d.cpu().numpy(), want_d.cpu().numpy())
@@ -56,4 +57,99 @@ def test_fused_mlp_forward_matches_torch(N, J):
     assert ew <= FWD_TOL, ew
     assert ed <= FWD_TOL, ed
     # a second call (weights unchanged: no repack) gives the same bits
-    assert torch.equal(fw(x), got_w)
+    with torch.no_grad():
+        assert torch.equal(fw(x), got_w)
+
+
+# Gradients.  Against fp32 autograd the comparison is dominated by ReLU units whose pre-activation is so close to zero that
+# the bf16 forward and the fp32 forward put them on different sides (a fraction f of the units gives a relative L2 error of
+# about sqrt(f) per mask crossed: measured 3e-2 at the last hidden layer .. 1.4e-1 at the first).  The kernels are
+# therefore pinned against autograd through a torch model of THEIR arithmetic -- operands rounded to bf16, fp32
+# accumulation, activations kept in bf16 (straight-through rounding) -- and the fp32 comparison is kept as a loose bound.
+BWD_L2_EMULATED = 3e-2
+BWD_MAX_EMULATED = 5e-2
+BWD_L2_FP32 = 0.3
+
+
+def _bf(t):
+    """round to bf16, straight-through gradient"""
+    return t + (t.to(torch.bfloat16).float() - t).detach()
+
+
+def _emulated_forward(mod, x, pose=None):
+    """The arithmetic of csrc/mlp.cu in torch: bf16 operands, fp32 accumulate, bf16 activations; the pose's contribution
+    folded into the biases of layers 0 and 5 in fp32."""
+    e = _bf(mod.embed(x))
+    n_e = e.shape[1]
+    layers = list(mod.linear)
+    head = mod.weight_predict if hasattr(mod, "weight_predict") else mod.gaussian_warp
+    extra = layers[0].in_features - n_e
+    h = None
+    for i, l in enumerate(layers):
+        b = l.bias
+        W = l.weight
+        if i in (0, 5) and extra:
+            b = b + W[:, n_e:n_e + extra] @ pose
+        if i == 0:
+            z = e @ _bf(W[:, :n_e]).T + b
+        elif i == 5:
+            z = e @ _bf(W[:, :n_e]).T + h @ _bf(W[:, n_e + extra:]).T + b
+        else:
+            z = h @ _bf(W).T + b
+        h = _bf(torch.relu(z))
+    out = h @ _bf(head.weight).T + head.bias
+    return torch.sigmoid(out) if hasattr(mod, "weight_predict") else out
+
+
+@pytest.mark.parametrize("N,J", [(1000, 24), (20_000, 24), (257, 7)])
+def test_fused_mlp_backward_matches_torch_autograd(N, J):
+    """dL/d(parameters) of both MLPs through the tensor-core backward (chain + weight-gradient GEMMs) against torch
+    autograd, for a seeded upstream gradient."""
+    from riggs_b200.mlp import FusedSkipMLP
+    wm, dn = _modules(J, seed=5)
+    g = torch.Generator().manual_seed(N + 1)
+    x = (torch.randn(N, 3, generator=g) * 0.6).cuda()
+    pose = (torch.randn(4 * J, generator=g) * 0.3).cuda()
+    stats = {}
+    for name, mod, args, fargs in (("weight_mlp", wm, (x,), (x,)), ("detail_net", dn, (x, pose[None].expand(N, -1)), (x, pose))):
+        fused = FusedSkipMLP(mod)
+        cot = torch.randn(N, fused.out_ch, generator=g).cuda() / N
+
+        def grads_of(fn):
+            for p in mod.parameters():
+                p.grad = None
+            (fn() * cot).sum().backward()
+            return [p.grad.clone() for p in fused.parameters()]
+
+        want32 = grads_of(lambda: mod(*args))
+        want_em = grads_of(lambda: _emulated_forward(mod, *fargs))
+        out = fused(*fargs)
+        assert out.requires_grad
+        for p in mod.parameters():
+            p.grad = None
+        (out * cot).sum().backward()
+        torch.cuda.synchronize()
+        got = [p.grad.clone() for p in fused.parameters()]
+        # the emulation is the same function: its forward must agree with the kernel's far inside the bf16 error
+        with torch.no_grad():
+            em_out = _emulated_forward(mod, *fargs)
+        stats[f"{name}.forward_vs_emulated"] = dict(max=helpers.rel_err(out.detach().cpu().numpy(), em_out.cpu().numpy()))
+        for i, (a, b, c) in enumerate(zip(got, want_em, want32)):
+            assert a.shape == b.shape
+            assert torch.isfinite(a).all(), (name, i)
+            an = a.cpu().numpy()
+            stats[f"{name}.{i}"] = dict(max=helpers.rel_err(an, b.cpu().numpy()), l2=helpers.rel_l2(an, b.cpu().numpy()),
+                                        l2_vs_fp32=helpers.rel_l2(an, c.cpu().numpy()),
+                                        emulated_vs_fp32_l2=helpers.rel_l2(b.cpu().numpy(), c.cpu().numpy()))
+    try:
+        with open(os.path.join(helpers.ROOT, "gpurun_out", f"mlp_bwd_N{N}_J{J}.json"), "w") as f:
+            json.dump(stats, f, indent=1)
+    except OSError:
+        pass
+    for k, s in stats.items():
+        if k.endswith("forward_vs_emulated"):
+            assert s["max"] <= 5e-3, (k, s)
+            continue
+        assert s["max"] <= BWD_MAX_EMULATED, (k, s)
+        assert s["l2"] <= BWD_L2_EMULATED, (k, s)
+        assert s["l2_vs_fp32"] <= BWD_L2_FP32, (k, s)
