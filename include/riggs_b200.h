@@ -397,10 +397,11 @@ int rg_mlp_pack(int emb_cols, int out_ch, const float* const* weights /* host ar
 
 /* Forward: x (N,3) -> out (N,out_ch); out_act 0 = linear head (detail_net), 1 = sigmoid (WeightMLP).  bias: (9,256)
  * fp32, the hidden layers' biases then the head's, zero padded.  Training (acts != NULL): also stores the post-ReLU
- * activations of the eight hidden layers as bf16, feature-major (8, 256, n_pad), and the encoding (64, n_pad) into emb;
+ * activations of the eight hidden layers as bf16, feature-major (8, 256, n_pad), the encoding (64, n_pad) into emb and one
+ * bit per hidden unit ("was it positive") into relu_mask (8 * 8 * n_pad 32-bit words);
  * n_pad >= N, a multiple of 128 (columns of points past N are written as zeros).  These are what rg_mlp_backward reads. */
 int rg_mlp_forward(int N, int multires, int out_ch, int out_act, const float* x, const void* packed, const float* bias,
-                   float* out, void* acts, void* emb, long long n_pad, rg_stream_t stream);
+                   float* out, void* acts, void* emb, void* relu_mask, long long n_pad, rg_stream_t stream);
 
 /* Backward of rg_mlp_forward (the reference: torch autograd through the same ~20 ops).  g_out (N,out_ch) is dL/d out;
  * out_fwd the forward's output (needed for the sigmoid head, else NULL); acts / emb the state the forward stored; dz
@@ -413,7 +414,8 @@ int rg_mlp_forward(int N, int multires, int out_ch, int out_act, const float* x,
  * stored activations), then one tcgen05 GEMM per (layer, half of its outputs, slice of the points) that contracts dZ
  * with the layer's inputs over the points, operands arriving as 2-D TMA tiles. */
 int rg_mlp_backward(int N, int out_ch, int out_act, int emb_cols, const float* g_out, const float* out_fwd, const void* packed,
-                    const void* acts, const void* emb, void* dz, long long n_pad, float* const* d_weights /* host, 9 */,
+                    const void* acts, const void* emb, const void* relu_mask, void* dz, long long n_pad,
+                    float* const* d_weights /* host, 9 */,
                     const int* lds /* host, 9 */, const int* emb_col0 /* host, 9 */, const int* act_col0 /* host, 9 */,
                     float* d_bias, rg_stream_t stream);
 

@@ -92,8 +92,8 @@ _SIGNATURES = {
     "rg_node_warp_backward": (C.c_int, [_i, _i, _i, _i] + [_p] * 23),
     "rg_mlp_packed_bytes": (C.c_size_t, [_i]),
     "rg_mlp_pack": (C.c_int, [_i, _i, C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), _p, _p]),
-    "rg_mlp_forward": (C.c_int, [_i, _i, _i, _i, _p, _p, _p, _p, _p, _p, C.c_longlong, _p]),
-    "rg_mlp_backward": (C.c_int, [_i, _i, _i, _i, _p, _p, _p, _p, _p, _p, C.c_longlong, C.POINTER(C.c_void_p), C.POINTER(C.c_int),
+    "rg_mlp_forward": (C.c_int, [_i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, C.c_longlong, _p]),
+    "rg_mlp_backward": (C.c_int, [_i, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p, C.c_longlong, C.POINTER(C.c_void_p), C.POINTER(C.c_int),
                                   C.POINTER(C.c_int), C.POINTER(C.c_int), _p, _p]),
     "rg_launch_count": (C.c_longlong, []),
     "rg_profile_enable": (None, [_i]),

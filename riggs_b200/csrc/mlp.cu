@@ -39,7 +39,7 @@ constexpr int kTileM = 128;      // points per tile = TMEM lanes
 constexpr int kQuarter = 64;     // output columns per accumulator buffer = input columns per k-slab
 constexpr int kChunkBytes = kQuarter * kQuarter * 2;  // one weight chunk: 64 outputs x 64 inputs, bf16 = 8 KB
 constexpr int kStages = 20;      // ring depth: 160 KB of weights in flight / resident
-constexpr int kEpiWarps = 4;
+constexpr int kEpiWarps = 8;   // two per TMEM lane quarter, each takes half of a quarter's 64 columns
 constexpr int kMlpThreads = (kEpiWarps + 2) * 32;  // + MMA warp + producer warp
 
 // TMEM columns (32-bit each, 128 lanes): two fp32 accumulator quarters, two bf16 activation buffers (256 values = 128
@@ -68,6 +68,7 @@ struct MlpArgs {
     float* out;            // (N, out_ch)
     __nv_bfloat16* acts;   // training: (8, 256, n_pad) post-ReLU activations, feature-major; null: not stored
     __nv_bfloat16* emb;    // training: (64, n_pad) embedded input, feature-major; null: not stored
+    uint32_t* relu_mask;   // training: (8, 8, n_pad) words: bit i of word [layer][2 q + half][point] = unit 64 q + 32 half + i is on
     long long n_pad;       // row pitch of acts / emb / dz (points, multiple of 128)
     // backward chain (mlp_chain_kernel<true>): dL/d out -> dL/d(pre-activation) of every layer
     const float* g_out;    // (N, out_ch) upstream gradient
@@ -153,28 +154,51 @@ struct MlpSmem {
     uint64_t act_ready[2][4];
     uint64_t emb_ready;
     uint32_t tmem_base;
-    float bias[(kLayers + 1) * kHid];
+    alignas(16) float bias[(kLayers + 1) * kHid];  // read as float4
 };
+
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(
+            taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]),
+        "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+        : "memory");
+}
+
+// 16 packed bf16 pairs = 32 consecutive features of one point -> feature-major global memory (coalesced over the warp's points)
+__device__ __forceinline__ void store_features(__nv_bfloat16* dst, long long pitch, const uint32_t (&pk)[16]) {
+    unsigned short* p = reinterpret_cast<unsigned short*>(dst);
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        p[0] = (unsigned short)(pk[i] & 0xffffu);
+        p[pitch] = (unsigned short)(pk[i] >> 16);
+        p += 2 * pitch;
+    }
+}
 
 // ---------------------------------------------------------------------------------------------------------------------
 // The chain kernel.  Persistent: CTA b handles tiles b, b + gridDim.x, ...
 // BWD = false: forward (encoding -> 8 hidden layers -> head).
 // BWD = true:  the same pipeline run backwards: step 0 multiplies dL/d(head pre-activation) by the head's weights, step j by
-//              layer 8-j's; the epilogue masks with the stored activations (ReLU') instead of adding a bias, and stores
-//              dL/dZ of every layer for the weight-gradient kernel.  No gradient is wanted for x (it is detached,
-//              skeleton_warp.py:131), so the chain stops at dZ_0.
+//              layer 8-j's; the epilogue applies ReLU' (one bit per unit, left behind by the forward) instead of adding a
+//              bias, and stores dL/dZ of every layer for the weight-gradient kernel.  No gradient is wanted for x (it is
+//              detached, skeleton_warp.py:131), so the chain stops at dZ_0.
+// Warps 0..7: epilogue -- warp e owns TMEM lanes 32 (e & 3) .. +31 (a warp reaches only the lane quarter warp % 4) and
+// the column half e >> 2 of every 64-column quarter; warp 8: MMA issuer; warp 9: weight producer.
 template <bool BWD>
 __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
     extern __shared__ __align__(1024) unsigned char s_dyn[];
     unsigned char* ring = reinterpret_cast<unsigned char*>(align_up_dev(reinterpret_cast<size_t>(s_dyn), 1024));
     MlpSmem& sm = *reinterpret_cast<MlpSmem*>(ring + (size_t)kStages * kChunkBytes);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    constexpr int kEpiThreads = kEpiWarps * 32;
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < kStages; i++) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], 1); }
-        for (int i = 0; i < 2; i++) { mbar_init(&sm.acc_full[i], 1); mbar_init(&sm.acc_free[i], kEpiWarps * 32); }
-        for (int i = 0; i < 8; i++) mbar_init(&sm.act_ready[i >> 2][i & 3], kEpiWarps * 32);
-        mbar_init(&sm.emb_ready, kEpiWarps * 32);
+        for (int i = 0; i < 2; i++) { mbar_init(&sm.acc_full[i], 1); mbar_init(&sm.acc_free[i], kEpiThreads); }
+        for (int i = 0; i < 8; i++) mbar_init(&sm.act_ready[i >> 2][i & 3], kEpiThreads);
+        mbar_init(&sm.emb_ready, kEpiThreads);
     }
     if (!BWD)
         for (int i = threadIdx.x; i < (kLayers + 1) * kHid; i += blockDim.x) sm.bias[i] = a.bias[i];
@@ -207,7 +231,7 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
 #pragma unroll 1
                 for (int l = 0; l < a.n_steps; l++) {
                     const MlpLayerPlan p = a.plan[l];
-                    const uint32_t in_col = kColAct + (uint32_t)(l & 1) * 128;  // layer l reads buffer l & 1 (l >= 1)
+                    const uint32_t in_col = kColAct + (uint32_t)(l & 1) * 128;  // step l reads buffer l & 1 (l >= 1)
                     const int n_use = (l - 1) >> 1;  // how often this tile has written that buffer before (parity of the wait)
 #pragma unroll 1
                     for (int q = 0; q < p.n_quarters; q++, g++) {
@@ -222,18 +246,20 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
                             if (s < p.n_emb) {
                                 a_col = tmem + kColEmb + (uint32_t)s * 32;
                             } else {
-                                const int sa = s - p.n_emb;  // activation slab = output quarter of the previous layer
-                                mbar_wait(&sm.act_ready[l & 1][sa], n_use & 1);
-                                tc_fence_after();
+                                const int sa = s - p.n_emb;  // activation slab = output quarter of the previous step
+                                if (q == 0) {  // later quarters of this step read slabs that quarter 0 has already waited for
+                                    mbar_wait(&sm.act_ready[l & 1][sa], n_use & 1);
+                                    tc_fence_after();
+                                }
                                 a_col = tmem + in_col + (uint32_t)sa * 32;
                             }
                             const uint32_t st = c % kStages;
                             mbar_wait(&sm.full[st], (c / kStages) & 1);
                             tc_fence_after();
-                            const uint32_t b_addr = smem_u32(ring + (size_t)st * kChunkBytes);
+                            const uint64_t bd = b_desc(smem_u32(ring + (size_t)st * kChunkBytes));
 #pragma unroll
-                            for (int k = 0; k < 4; k++)
-                                mma_ts(d_col, a_col + (uint32_t)k * 8, b_desc(b_addr + (uint32_t)k * 32), idesc, (s | k) != 0);
+                            for (int k = 0; k < 4; k++)  // the k-step of 16 columns starts 32 bytes (2 address units) further on
+                                mma_ts(d_col, a_col + (uint32_t)k * 8, bd + (uint64_t)(k * 2), idesc, (s | k) != 0);
                             tc_commit(&sm.empty[st]);  // the chunk's slot is free once these MMAs have read it
                         }
                         tc_commit(&sm.acc_full[ab]);
@@ -242,16 +268,19 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
             }
         }
     } else {
-        // ===================== epilogue warps: thread = point = TMEM lane =====================
-        const uint32_t lane_base = (uint32_t)(warp * 32) << 16;
-        const int row = warp * 32 + lane;
+        // ===================== epilogue warps: thread = point (TMEM lane) x half of a quarter's columns =====================
+        const int lq = warp & 3, ch = warp >> 2;
+        const uint32_t lane_base = (uint32_t)(lq * 32) << 16;
+        const int row = lq * 32 + lane;
         uint32_t g = 0;
         const int n_emb = 3 + 6 * a.multires;
         for (int t = 0; t < my_tiles; t++) {
             const long long pt = ((long long)blockIdx.x + (long long)t * gridDim.x) * kTileM + row;
             const bool valid = pt < a.N;
+            const bool in_buf = pt < a.n_pad;
             if (!BWD) {
-                // ---- positional encoding (utils/time_utils.py:208-256: x, then sin / cos per octave), bf16, into TMEM
+                // ---- positional encoding (utils/time_utils.py:208-256: x, then sin / cos per octave), bf16, into TMEM:
+                //      this thread packs features 32 ch .. 32 ch + 31
                 float e[64];
                 float xv[3] = {0.f, 0.f, 0.f};
                 if (valid) { xv[0] = a.x[3 * pt]; xv[1] = a.x[3 * pt + 1]; xv[2] = a.x[3 * pt + 2]; }
@@ -272,27 +301,29 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
                     }
                     f *= 2.0f;
                 }
-                uint32_t pk[32];
+                uint32_t pk[16];
 #pragma unroll
-                for (int i = 0; i < 32; i++) pk[i] = pack_bf16(e[2 * i], e[2 * i + 1]);
-                tmem_st32(tmem + lane_base + kColEmb, pk);
-                if (a.emb && pt < a.n_pad) {  // rows of points past N are written as zeros: the weight-gradient GEMM sums over them
+                for (int i = 0; i < 16; i++) pk[i] = ch ? pack_bf16(e[32 + 2 * i], e[33 + 2 * i]) : pack_bf16(e[2 * i], e[2 * i + 1]);
+                tmem_st16(tmem + lane_base + kColEmb + (uint32_t)ch * 16, pk);
+                if (a.emb && in_buf) {  // rows of points past N are written as zeros: the weight-gradient GEMM sums over them
 #pragma unroll
-                    for (int i = 0; i < 64; i++)
-                        if (i < n_emb) a.emb[(size_t)i * a.n_pad + pt] = __float2bfloat16_rn(valid ? e[i] : 0.f);
+                    for (int i = 0; i < 32; i++) {
+                        const int fi = ch * 32 + i;
+                        if (fi < n_emb) a.emb[(size_t)fi * a.n_pad + pt] = __float2bfloat16_rn(valid ? (ch ? e[32 + i] : e[i]) : 0.f);
+                    }
                 }
             } else {
                 // ---- dL/d(head pre-activation) of this point: the upstream gradient (times the sigmoid's derivative)
                 const int n_in = a.plan[0].n_emb;  // slabs of 64 head outputs
 #pragma unroll 1
                 for (int sl = 0; sl < n_in; sl++) {
-                    uint32_t pk[32];
+                    uint32_t pk[16];
 #pragma unroll
-                    for (int i = 0; i < 32; i++) {
+                    for (int i = 0; i < 16; i++) {
                         float g2[2];
 #pragma unroll
                         for (int h = 0; h < 2; h++) {
-                            const int col = sl * 64 + 2 * i + h;
+                            const int col = sl * 64 + ch * 32 + 2 * i + h;
                             float gv = 0.f;
                             if (valid && col < a.out_ch) {
                                 gv = a.g_out[(size_t)pt * a.out_ch + col];
@@ -305,16 +336,8 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
                         }
                         pk[i] = pack_bf16(g2[0], g2[1]);
                     }
-                    tmem_st32(tmem + lane_base + kColEmb + (uint32_t)sl * 32, pk);
-                    if (pt < a.n_pad) {
-                        __nv_bfloat16* dst = a.dz + ((size_t)kLayers * kHid + (size_t)sl * 64) * a.n_pad + pt;
-#pragma unroll
-                        for (int i = 0; i < 32; i++) {
-                            const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&pk[i]);
-                            dst[(size_t)(2 * i) * a.n_pad] = h.x;
-                            dst[(size_t)(2 * i + 1) * a.n_pad] = h.y;
-                        }
-                    }
+                    tmem_st16(tmem + lane_base + kColEmb + (uint32_t)sl * 32 + (uint32_t)ch * 16, pk);
+                    if (in_buf) store_features(a.dz + ((size_t)kLayers * kHid + (size_t)sl * 64 + (size_t)ch * 32) * a.n_pad + pt, a.n_pad, pk);
                 }
             }
             tmem_st_wait();
@@ -330,58 +353,63 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
                     const uint32_t ab = g & 1;
                     mbar_wait(&sm.acc_full[ab], (g >> 1) & 1);
                     tc_fence_after();
-                    uint32_t v0[32], v1[32];
-                    tmem_ld32(tmem + lane_base + kColAcc + ab * kQuarter, v0);
-                    tmem_ld32(tmem + lane_base + kColAcc + ab * kQuarter + 32, v1);
+                    uint32_t v[32];
+                    tmem_ld32(tmem + lane_base + kColAcc + ab * kQuarter + (uint32_t)ch * 32, v);
                     tmem_ld_wait();
+                    // the accumulator is in registers: hand the buffer back before doing anything else (the tensor core is
+                    // waiting for it two quarters ahead)
+                    tc_fence_before();
+                    mbar_arrive(&sm.acc_free[ab]);
+                    const int col0 = q * kQuarter + ch * 32;  // first of this thread's 32 columns
                     if (BWD || l < kLayers) {
-                        uint32_t pk[32];
+                        uint32_t pk[16];
                         // forward: this layer's slot; backward step l produces dZ of hidden layer 7 - l
                         const int slot = BWD ? (kLayers - 1 - l) : l;
-                        const size_t goff = ((size_t)slot * kHid + (size_t)q * kQuarter) * a.n_pad + (size_t)pt;
-                        const bool in_buf = pt < a.n_pad;
+                        uint32_t* mword = a.relu_mask + (((size_t)slot * 8 + (size_t)(q * 2 + ch)) * a.n_pad + (size_t)pt);
+                        uint32_t bits = 0;
+                        if (BWD) bits = valid ? *mword : 0u;  // one bit per unit: was its activation positive?
+                        if (!BWD) {
+                            const float4* b4 = reinterpret_cast<const float4*>(bias + col0);
 #pragma unroll
-                        for (int i = 0; i < 32; i++) {
-                            const int c0 = 2 * i;
-                            const float x0 = c0 < 32 ? __uint_as_float(v0[c0]) : __uint_as_float(v1[c0 - 32]);
-                            const float x1 = c0 + 1 < 32 ? __uint_as_float(v0[c0 + 1]) : __uint_as_float(v1[c0 + 1 - 32]);
-                            float h0, h1;
-                            if (!BWD) {
-                                h0 = fmaxf(x0 + bias[q * kQuarter + c0], 0.f);
-                                h1 = fmaxf(x1 + bias[q * kQuarter + c0 + 1], 0.f);
-                                if (!valid) { h0 = 0.f; h1 = 0.f; }
-                            } else {  // ReLU': pass the gradient where the stored activation is positive
-                                const bool m0 = valid && __bfloat162float(a.acts[goff + (size_t)c0 * a.n_pad]) > 0.f;
-                                const bool m1 = valid && __bfloat162float(a.acts[goff + (size_t)(c0 + 1) * a.n_pad]) > 0.f;
-                                h0 = m0 ? x0 : 0.f;
-                                h1 = m1 ? x1 : 0.f;
+                            for (int i = 0; i < 8; i++) {
+                                const float4 bb = b4[i];
+                                const float z0 = __uint_as_float(v[4 * i]) + bb.x, z1 = __uint_as_float(v[4 * i + 1]) + bb.y;
+                                const float z2 = __uint_as_float(v[4 * i + 2]) + bb.z, z3 = __uint_as_float(v[4 * i + 3]) + bb.w;
+                                // one bit per unit (a positive fp32 value never rounds to a bf16 zero: same exponent range)
+                                bits |= (z0 > 0.f ? 1u : 0u) << (4 * i) | (z1 > 0.f ? 1u : 0u) << (4 * i + 1) |
+                                        (z2 > 0.f ? 1u : 0u) << (4 * i + 2) | (z3 > 0.f ? 1u : 0u) << (4 * i + 3);
+                                pk[2 * i] = pack_bf16(fmaxf(z0, 0.f), fmaxf(z1, 0.f));
+                                pk[2 * i + 1] = pack_bf16(fmaxf(z2, 0.f), fmaxf(z3, 0.f));
                             }
-                            pk[i] = pack_bf16(h0, h1);
-                        }
-                        tmem_st32(tmem + lane_base + out_col + (uint32_t)q * 32, pk);
-                        __nv_bfloat16* store = BWD ? a.dz : a.acts;  // training state, feature-major (coalesced over the warp's points)
-                        if (store && in_buf) {
-                            __nv_bfloat16* dst = store + goff;
+                            if (!valid) {  // rows past N (last tile only): zeros, so that the weight gradients sum nothing
+                                bits = 0;
 #pragma unroll
-                            for (int i = 0; i < 32; i++) {
-                                const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&pk[i]);
-                                dst[(size_t)(2 * i) * a.n_pad] = h.x;
-                                dst[(size_t)(2 * i + 1) * a.n_pad] = h.y;
+                                for (int i = 0; i < 16; i++) pk[i] = 0u;
+                            }
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 16; i++) {
+                                const float h0 = (bits >> (2 * i)) & 1u ? __uint_as_float(v[2 * i]) : 0.f;
+                                const float h1 = (bits >> (2 * i + 1)) & 1u ? __uint_as_float(v[2 * i + 1]) : 0.f;
+                                pk[i] = pack_bf16(h0, h1);
                             }
                         }
+                        tmem_st16(tmem + lane_base + out_col + (uint32_t)q * 32 + (uint32_t)ch * 16, pk);
                         tmem_st_wait();
                         tc_fence_before();
-                        mbar_arrive(&sm.act_ready[(l + 1) & 1][q]);
-                        mbar_arrive(&sm.acc_free[ab]);
+                        mbar_arrive(&sm.act_ready[(l + 1) & 1][q]);  // the next step may start on this k-slab
+                        __nv_bfloat16* store = BWD ? a.dz : a.acts;  // training state, feature-major
+                        if (store && in_buf) {
+                            store_features(store + ((size_t)slot * kHid + (size_t)col0) * a.n_pad + (size_t)pt, a.n_pad, pk);
+                            if (!BWD) *mword = bits;
+                        }
                     } else {
-                        tc_fence_before();
-                        mbar_arrive(&sm.acc_free[ab]);  // the values are in registers
                         if (valid) {
 #pragma unroll
-                            for (int i = 0; i < 64; i++) {
-                                const int col = q * kQuarter + i;
+                            for (int i = 0; i < 32; i++) {
+                                const int col = col0 + i;
                                 if (col < a.out_ch) {
-                                    float z = (i < 32 ? __uint_as_float(v0[i]) : __uint_as_float(v1[i - 32])) + bias[col];
+                                    float z = __uint_as_float(v[i]) + bias[col];
                                     if (a.out_act == 1) z = 1.0f / (1.0f + expf(-z));
                                     a.out[(size_t)pt * a.out_ch + col] = z;
                                 }
@@ -751,14 +779,14 @@ static int launch_chain(bool bwd, MlpArgs& a, cudaStream_t stream) {
 }
 
 int rg_mlp_forward(int N, int multires, int out_ch, int out_act, const float* x, const void* packed, const float* bias,
-                   float* out, void* acts, void* emb, long long n_pad, rg_stream_t stream_) {
+                   float* out, void* acts, void* emb, void* relu_mask, long long n_pad, rg_stream_t stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     if (N < 0 || multires < 0 || multires > 10 || out_ch < 1 || out_ch > 128 || !x || !packed || !bias || !out) {
         set_error("rg_mlp_forward: bad argument");
         return -1;
     }
-    if ((acts || emb) && (n_pad < N || (n_pad & 127) || !acts || !emb)) {
-        set_error("rg_mlp_forward: training state needs both acts and emb, n_pad a multiple of 128 and >= N");
+    if ((acts || emb || relu_mask) && (n_pad < N || (n_pad & 127) || !acts || !emb || !relu_mask)) {
+        set_error("rg_mlp_forward: training state needs acts, emb and relu_mask, n_pad a multiple of 128 and >= N");
         return -1;
     }
     if (N == 0) return 0;
@@ -769,16 +797,17 @@ int rg_mlp_forward(int N, int multires, int out_ch, int out_act, const float* x,
     a.N = N; a.n_tiles = (N + kTileM - 1) / kTileM; a.multires = multires; a.out_ch = out_ch; a.out_act = out_act;
     a.x = x; a.w_packed = static_cast<const unsigned char*>(packed); a.bias = bias; a.out = out;
     a.acts = static_cast<__nv_bfloat16*>(acts); a.emb = static_cast<__nv_bfloat16*>(emb); a.n_pad = n_pad;
+    a.relu_mask = static_cast<uint32_t*>(relu_mask);
     LaunchScope ls("mlp_forward", stream);
     if (launch_chain(false, a, stream)) return -1;
     return check_launch("rg_mlp_forward", stream, false);
 }
 
 int rg_mlp_backward(int N, int out_ch, int out_act, int emb_cols, const float* g_out, const float* out_fwd, const void* packed,
-                    const void* acts, const void* emb, void* dz, long long n_pad, float* const* d_weights, const int* lds,
+                    const void* acts, const void* emb, const void* relu_mask, void* dz, long long n_pad, float* const* d_weights, const int* lds,
                     const int* emb_col0, const int* act_col0, float* d_bias, rg_stream_t stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-    if (N < 0 || out_ch < 1 || out_ch > 128 || !g_out || !packed || !acts || !emb || !dz || !d_weights || !lds || !emb_col0 ||
+    if (N < 0 || out_ch < 1 || out_ch > 128 || !g_out || !packed || !acts || !emb || !relu_mask || !dz || !d_weights || !lds || !emb_col0 ||
         !act_col0 || !d_bias || (out_act == 1 && !out_fwd) || n_pad < N || (n_pad & 127)) {
         set_error("rg_mlp_backward: bad argument");
         return -1;
@@ -795,6 +824,7 @@ int rg_mlp_backward(int N, int out_ch, int out_act, int emb_cols, const float* g
     a.w_packed = static_cast<const unsigned char*>(packed) + (size_t)fwd_chunks * kChunkBytes;
     a.acts = static_cast<__nv_bfloat16*>(const_cast<void*>(acts));
     a.n_pad = n_pad; a.g_out = g_out; a.out_fwd = out_fwd; a.dz = static_cast<__nv_bfloat16*>(dz);
+    a.relu_mask = static_cast<uint32_t*>(const_cast<void*>(relu_mask));
     {
         LaunchScope ls("mlp_backward_chain", stream);
         if (launch_chain(true, a, stream)) return -1;

@@ -95,24 +95,26 @@ class FusedSkipMLP:
         N = x.shape[0]
         out = torch.empty(N, self.out_ch, device=x.device)
         bias = self.biases(pose)
-        acts = emb = None
+        acts = emb = masks = None
         n_pad = 0
         if save:
             n_pad = (N + 127) // 128 * 128
             acts = torch.empty(8, 256, n_pad, dtype=torch.bfloat16, device=x.device)
             emb = torch.empty(64, n_pad, dtype=torch.bfloat16, device=x.device)
             emb[self.emb_cols:].zero_()  # the kernel writes the rows of the encoding only
+            masks = torch.empty(8, 8, n_pad, dtype=torch.int32, device=x.device)
         with torch.cuda.device(x.device):
             check(_lib.lib().rg_mlp_forward(N, self.multires, self.out_ch, self.out_act, ptr(x), self.packed.data_ptr(),
-                                            bias.data_ptr(), ptr(out), ptr(acts), ptr(emb), n_pad, stream_ptr()), "rg_mlp_forward")
+                                            bias.data_ptr(), ptr(out), ptr(acts), ptr(emb), ptr(masks), n_pad, stream_ptr()),
+                  "rg_mlp_forward")
         if save:
-            return out, (N, acts, emb, n_pad, pose.detach().reshape(-1).float() if pose is not None else None)
+            return out, (N, acts, emb, masks, n_pad, pose.detach().reshape(-1).float() if pose is not None else None)
         return out
 
     def backward(self, g_out: torch.Tensor, out: torch.Tensor, state):
         """dL/d out (N,out_ch) -> gradients of the module's parameters, in the order of ``parameters()``:
         [linear.0.weight, linear.0.bias, ..., head.weight, head.bias]."""
-        N, acts, emb, n_pad, pose = state
+        N, acts, emb, masks, n_pad, pose = state
         dev = g_out.device
         ws = self._weights()
         dws = [torch.zeros_like(w, dtype=torch.float32) for w in ws]
@@ -125,7 +127,7 @@ class FusedSkipMLP:
         g = f32c(g_out)
         with torch.cuda.device(dev):
             check(_lib.lib().rg_mlp_backward(N, self.out_ch, self.out_act, self.emb_cols, ptr(g), ptr(f32c(out)) if self.out_act else None,
-                                             self.packed.data_ptr(), ptr(acts), ptr(emb), ptr(dz), n_pad, ptrs, lds, emb0, act0,
+                                             self.packed.data_ptr(), ptr(acts), ptr(emb), ptr(masks), ptr(dz), n_pad, ptrs, lds, emb0, act0,
                                              db.data_ptr(), stream_ptr()), "rg_mlp_backward")
         if self.extra:  # the pose columns saw the same input for every point: their gradient is d_bias (x) pose
             lo, hi = self.emb_cols, self.emb_cols + self.extra
