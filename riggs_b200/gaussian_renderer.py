@@ -187,3 +187,61 @@ def render(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, d_xyz, d_rotation
                                                      rotations=rotations, cov3D_precomp=cov3D_precomp)
     return {"render": rendered_image, "viewspace_points": screenspace_points, "visibility_filter": radii > 0,
             "radii": radii, "depth": depth, "alpha": alpha, "bg_color": bg}
+
+
+def render_flow(pc, viewpoint_camera1, viewpoint_camera2, d_xyz1, d_xyz2, d_rotation1, d_scaling1, scaling_modifier=1.0,
+                compute_cov3D_python=False, scale_const=None, d_rot_as_res=True, **kwargs):
+    """Splat the per-Gaussian screen-space flow between two deformations (and the motion mask in the third channel) with
+    the Gaussians posed by the first one.  Same signature, arithmetic and result dict as the reference's ``render_flow``
+    (gaussian_renderer/__init__.py:154-269): the flow is ``project(xyz + d_xyz2, cam2) - project(xyz + d_xyz1, cam1)``
+    on detached positions, rasterised as ``colors_precomp`` over a zero background with SH degree 0."""
+    screenspace_points = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype, requires_grad=True, device="cuda") + 0
+    try:
+        screenspace_points.retain_grad()
+    except Exception:
+        pass
+    tanfovx = math.tan(viewpoint_camera1.FoVx * 0.5)
+    tanfovy = math.tan(viewpoint_camera1.FoVy * 0.5)
+
+    canonical = pc.get_xyz.clone().detach()  # the flow itself carries no gradient to the positions (:187)
+    xyz_t1 = canonical + d_xyz1
+    xyz_t2 = canonical + d_xyz2
+
+    def project(xyz, cam):
+        hom = torch.cat([xyz, torch.ones_like(xyz[..., :1])], dim=-1) @ cam.full_proj_transform
+        return hom[..., :3] / hom[..., -1:]
+
+    cam2 = viewpoint_camera2 if viewpoint_camera2 is not None else viewpoint_camera1
+    flow = project(xyz_t2, cam2) - project(xyz_t1, viewpoint_camera1)
+    flow[..., -1:] = pc.motion_mask  # third channel: the motion mask (:203)
+
+    raster_settings = GaussianRasterizationSettings(
+        image_height=int(viewpoint_camera1.image_height), image_width=int(viewpoint_camera1.image_width),
+        tanfovx=tanfovx, tanfovy=tanfovy, bg=torch.zeros_like(flow[0]), scale_modifier=scaling_modifier,
+        viewmatrix=viewpoint_camera1.world_view_transform, projmatrix=viewpoint_camera1.full_proj_transform,
+        sh_degree=0, campos=viewpoint_camera1.camera_center, prefiltered=False, debug=False)
+    rasterizer = GaussianRasterizer(raster_settings=raster_settings)
+
+    means3D = pc.get_xyz + d_xyz1
+    opacity = pc.get_opacity
+
+    def posed_rotation():
+        if d_rot_as_res:
+            return pc.get_rotation + d_rotation1
+        return pc.get_rotation if type(d_rotation1) is float else quaternion_multiply(d_rotation1, pc.get_rotation)
+
+    scales = rotations = cov3D_precomp = None
+    if scale_const is not None:
+        scales = torch.ones_like(pc.get_scaling) * scale_const
+        rotations = posed_rotation()
+    elif compute_cov3D_python:
+        cov3D_precomp = pc.get_covariance(scaling_modifier, d_rotation=None if type(d_rotation1) is float else d_rotation1)
+    else:
+        scales = pc.get_scaling + d_scaling1
+        rotations = posed_rotation()
+
+    rendered_image, radii, depth, alpha = rasterizer(means3D=means3D, means2D=screenspace_points, shs=None,
+                                                     colors_precomp=flow, opacities=opacity, scales=scales,
+                                                     rotations=rotations, cov3D_precomp=cov3D_precomp)
+    return {"render": rendered_image, "depth": depth, "alpha": alpha, "viewspace_points": screenspace_points,
+            "visibility_filter": radii > 0, "radii": radii}
