@@ -172,6 +172,17 @@ int rg_skin_backward(int N, int J, const float* xyz, const float* joints, const 
                      float* dnode_radius_raw, float* dglobal_trans, float* dmask, float* dmlp_weight,
                      float* doffsets, rg_stream_t stream);
 
+/* rg_skin_backward for either blend mode of rg_skin_forward.  blend_mode 1 (dual-quaternion blending,
+ * utils/dual_quaternion.py:135-180 differentiated: the reference would rely on torch autograd through QT2DQ / DQ2QT):
+ * the bone rotations enter through node_rot, which carries no gradient (skeleton_warp.py:144), so of dG only the
+ * translation entries 9..11 of every bone receive one; everything else as rg_skin_backward. */
+int rg_skin_backward_blend(int N, int J, const float* xyz, const float* joints, const int* parents,
+                           const float* node_radius_raw, const float* G, const float* node_rot,
+                           const float* global_trans, const float* motion_mask, const float* mlp_weight,
+                           const float* offsets, int blend_mode, const float* g_dxyz, const float* g_drot, float* dG,
+                           float* dnode_radius_raw, float* dglobal_trans, float* dmask, float* dmlp_weight,
+                           float* doffsets, rg_stream_t stream);
+
 /* Linear-blend skinning by the K nearest bones of every point: SkeletonWarp.cal_nn_weight_skeleton with K > 0
  * (skeleton_utils/skeleton_warp.py:46-49: torch.topk of the squared point-to-segment distances, smallest first,
  * nn_idx = bone + 1) followed by the LBS of deform_by_pose (:130-172).  Same arguments as rg_skin_forward without

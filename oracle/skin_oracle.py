@@ -110,8 +110,11 @@ def forward_kinematics(local_rot_mats: torch.Tensor, joints: torch.Tensor, paren
 
 
 def deform_by_pose(x, joints, parents, node_radius_raw, local_rotation, global_trans, motion_mask,
-                   mlp_weight=None, template_offsets=None, K=-1, nn_idx=None):
-    """LBS core.  Returns the dict of the reference's third boundary."""
+                   mlp_weight=None, template_offsets=None, K=-1, nn_idx=None, blend_mode="lbs"):
+    """LBS core.  Returns the dict of the reference's third boundary.
+    blend_mode "dq": the bone transforms (node_rot as detached quaternions, the translations of G) are blended as dual
+    quaternions (utils/dual_quaternion.py:135-180, DQBlending) instead of linearly; d_rotation is then the blended unit
+    quaternion times the mask.  K = -1 only."""
     x = x.detach()
     R_local = quat_to_mat(local_rotation)
     w, d2, idx = skin_weights(x, joints, parents, node_radius_raw, mlp_weight, K, nn_idx)
@@ -127,11 +130,20 @@ def deform_by_pose(x, joints, parents, node_radius_raw, local_rotation, global_t
         rot = node_rot[idx]
         nn_idx = idx
     Ax_avg = (Ax * w[..., None]).sum(1)
+    dq_rot = None
+    if blend_mode == "dq":
+        if idx is not None:
+            raise ValueError("dual-quaternion blending is defined for K = -1 (all bones)")
+        Rb, Tb = dq_blend(node_rot[1:], G_t[1:], w)
+        Ax_avg = torch.einsum("nab,nb->na", Rb, x) + Tb
+        dq_rot = dq_blend_quat(node_rot[1:], G_t[1:], w)
     Ax_avg = Ax_avg + global_trans
     if template_offsets is not None:
         Ax_avg = Ax_avg + template_offsets
     d_xyz = (Ax_avg - x) * motion_mask
     d_rot = (rot * w[..., None]).sum(1) * motion_mask
+    if dq_rot is not None:
+        d_rot = dq_rot * motion_mask
     return {"d_xyz": d_xyz, "d_rotation": d_rot,
             "d_scaling": torch.zeros(x.shape[0], 3, dtype=x.dtype, device=x.device),
             "d_nodes": posed + global_trans, "nn_weight": w, "nn_idx": nn_idx, "nn_dist2": d2,
@@ -178,6 +190,14 @@ def dq_blend(q, t, weights):
     dq = qt_to_dq(q, t)
     avg = (dq[None] * weights[..., None]).sum(-2)
     return dq_to_rt(avg)
+
+
+def dq_blend_quat(q, t, weights):
+    """The blended unit quaternion itself (real part of the normalised blend; DQ2QT's `real`, dual_quaternion.py:148-151)."""
+    dq = qt_to_dq(q, t)
+    avg = (dq[None] * weights[..., None]).sum(-2)
+    real = avg[..., :4]
+    return real / real.norm(dim=-1, keepdim=True).clamp(min=1e-8)
 
 
 # ---- render() activations --------------------------------------------------------------------

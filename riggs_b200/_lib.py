@@ -72,6 +72,7 @@ _SIGNATURES = {
     "rg_skinned_backward_part": (C.c_int, [_p, _p, _i, _i, _i] + [_p] * 20),
     "rg_skin_forward": (C.c_int, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _p]),
     "rg_skin_backward": (C.c_int, [_i, _i] + [_p] * 19),
+    "rg_skin_backward_blend": (C.c_int, [_i, _i] + [_p] * 10 + [_i] + [_p] * 9),
     "rg_l1_loss_scratch_bytes": (C.c_size_t, []),
     "rg_l1_loss": (C.c_int, [C.c_size_t, _p, _p, _p, _p, _p, C.c_size_t, _p]),
     "rg_allreduce_multimem": (C.c_int, [_p, C.c_size_t, _i, _i, _p]),

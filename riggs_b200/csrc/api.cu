@@ -315,21 +315,33 @@ int rg_skin_forward(int N, int J, const float* xyz, const float* joints, const i
     return check_launch("skin_forward", stream, false);
 }
 
-int rg_skin_backward(int N, int J, const float* xyz, const float* joints, const int* parents,
-                     const float* node_radius_raw, const float* G, const float* node_rot, const float* global_trans,
-                     const float* motion_mask, const float* mlp_weight, const float* offsets, const float* g_dxyz,
-                     const float* g_drot, float* dG, float* dnode_radius_raw, float* dglobal_trans, float* dmask,
-                     float* dmlp_weight, float* doffsets, rg_stream_t stream_) {
+int rg_skin_backward_blend(int N, int J, const float* xyz, const float* joints, const int* parents,
+                           const float* node_radius_raw, const float* G, const float* node_rot, const float* global_trans,
+                           const float* motion_mask, const float* mlp_weight, const float* offsets, int blend_mode,
+                           const float* g_dxyz, const float* g_drot, float* dG, float* dnode_radius_raw, float* dglobal_trans,
+                           float* dmask, float* dmlp_weight, float* doffsets, rg_stream_t stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     if (g_drot && !is_aligned16(g_drot)) { set_error("rg_skin_backward: g_drot must be 16-byte aligned"); return -1; }
+    if (blend_mode != 0 && blend_mode != 1) { set_error("rg_skin_backward: blend_mode must be 0 (linear) or 1 (dual quaternion)"); return -1; }
     SkinBwdArgs a;
     a.N = N; a.J = J; a.xyz = xyz; a.joints = joints; a.parents = parents; a.node_radius_raw = node_radius_raw;
     a.G = G; a.node_rot = node_rot; a.global_trans = global_trans; a.motion_mask = motion_mask;
     a.mlp_weight = mlp_weight; a.offsets = offsets; a.g_dxyz = g_dxyz; a.g_drot = g_drot; a.dG = dG;
+    a.blend_mode = blend_mode;
     a.dnode_radius_raw = dnode_radius_raw; a.dglobal_trans = dglobal_trans; a.dmask = dmask;
     a.dmlp_weight = dmlp_weight; a.doffsets = doffsets;
     if (launch_skin_backward(a, stream)) return -1;
     return check_launch("skin_backward", stream, false);
+}
+
+int rg_skin_backward(int N, int J, const float* xyz, const float* joints, const int* parents,
+                     const float* node_radius_raw, const float* G, const float* node_rot, const float* global_trans,
+                     const float* motion_mask, const float* mlp_weight, const float* offsets, const float* g_dxyz,
+                     const float* g_drot, float* dG, float* dnode_radius_raw, float* dglobal_trans, float* dmask,
+                     float* dmlp_weight, float* doffsets, rg_stream_t stream) {
+    return rg_skin_backward_blend(N, J, xyz, joints, parents, node_radius_raw, G, node_rot, global_trans, motion_mask,
+                                  mlp_weight, offsets, 0, g_dxyz, g_drot, dG, dnode_radius_raw, dglobal_trans, dmask,
+                                  dmlp_weight, doffsets, stream);
 }
 
 }  // extern "C"

@@ -9,6 +9,7 @@
 // 28 B written per Gaussian in the forward; the ~60 flops per (Gaussian, bone) pair stay in registers.
 #include "common.cuh"
 #include "kernels.cuh"
+#include "dq.cuh"
 #include "skin.cuh"
 #include "bones.cuh"
 
@@ -328,6 +329,18 @@ __global__ void __launch_bounds__(256) skin_backward_kernel(SkinBwdArgs a) {
                 const float4 h = reinterpret_cast<const float4*>(a.g_drot)[n];
                 h0 = h.x; h1 = h.y; h2 = h.z; h3 = h.w;
             }
+        }
+        if (a.blend_mode == 1) {  // dual-quaternion blend: its own pair of sweeps (dq.cuh)
+            float ox = 0.f, oy = 0.f, oz = 0.f;
+            if (a.offsets && live) { ox = a.offsets[3 * (size_t)n]; oy = a.offsets[3 * (size_t)n + 1]; oz = a.offsets[3 * (size_t)n + 2]; }
+            dq_skin_backward_point(s_b, K, lane, live, x, y, z, m, gx, gy, gz, h0, h1, h2, h3,
+                                   a.mlp_weight ? a.mlp_weight + (size_t)(live ? n : 0) * K : nullptr, g0, g1, g2, ox, oy, oz, s_acc,
+                                   (a.dmask && live) ? a.dmask + n : nullptr,
+                                   (a.dmlp_weight && live) ? a.dmlp_weight + (size_t)n * K : nullptr);
+            if (live && a.doffsets) {
+                a.doffsets[3 * (size_t)n] = m * gx; a.doffsets[3 * (size_t)n + 1] = m * gy; a.doffsets[3 * (size_t)n + 2] = m * gz;
+            }
+            continue;
         }
         // sweep 1
         float wsum = 0.f, sc = 0.f, ax = 0.f, ay = 0.f, az = 0.f, q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;

@@ -36,6 +36,7 @@ struct SkinBwdArgs {
     const float* offsets;
     const float* g_dxyz;
     const float* g_drot;  // optional
+    int blend_mode;       // 0: linear blend, 1: dual-quaternion blend (dq.cuh)
     float* dG;                // (J,12) accumulated
     float* dnode_radius_raw;  // (J) accumulated
     float* dglobal_trans;     // (3) accumulated, optional

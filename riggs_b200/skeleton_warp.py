@@ -89,8 +89,6 @@ class _SkinFunction(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g_dxyz, g_drot, _g_w):
-        if ctx.blend_mode != 0:
-            raise _lib.RiggsError("dual-quaternion blending is forward-only (the reference never trains with it)")
         (xyz, joints, parents_i32, node_radius_raw, G, node_rot, global_trans, motion_mask, mlp_weight,
          offsets) = ctx.saved_tensors
         N, J = xyz.shape[0], joints.shape[0]
@@ -105,11 +103,11 @@ class _SkinFunction(torch.autograd.Function):
         dmlp = torch.empty_like(mlp_weight) if (mlp_weight is not None and need[8]) else None
         doff = torch.empty_like(offsets) if (offsets is not None and need[9]) else None
         with torch.cuda.device(dev):
-            check(_lib.lib().rg_skin_backward(N, J, ptr(xyz), ptr(joints), ptr(parents_i32), ptr(node_radius_raw),
-                                              ptr(G), ptr(node_rot), ptr(global_trans), ptr(motion_mask),
-                                              ptr(mlp_weight), ptr(offsets), ptr(g_dxyz), ptr(g_drot), ptr(dG),
-                                              ptr(dradius), ptr(dtrans), ptr(dmask), ptr(dmlp), ptr(doff),
-                                              stream_ptr()), "skin_backward")
+            check(_lib.lib().rg_skin_backward_blend(N, J, ptr(xyz), ptr(joints), ptr(parents_i32), ptr(node_radius_raw),
+                                                    ptr(G), ptr(node_rot), ptr(global_trans), ptr(motion_mask),
+                                                    ptr(mlp_weight), ptr(offsets), int(ctx.blend_mode), ptr(g_dxyz),
+                                                    ptr(g_drot), ptr(dG), ptr(dradius), ptr(dtrans), ptr(dmask), ptr(dmlp),
+                                                    ptr(doff), stream_ptr()), "skin_backward")
         return (None, None, None, dradius, dG.view_as(G), None, dtrans.view_as(global_trans), dmask, dmlp, doff,
                 None, None)
 

@@ -106,6 +106,24 @@ def dq_case():
     print("wrote dq_blend")
 
 
+def dq_grad_case():
+    """Gradients of the reference's DQBlending by its own autograd: dL/dt (bone translations) and dL/dweights for seeded
+    cotangents on the blended rotation matrix and translation (pins the dual-quaternion backward of the kernels)."""
+    gen = torch.Generator().manual_seed(15)
+    K, N = 9, 33
+    q = torch.randn(K, 4, generator=gen).double()
+    t = torch.randn(K, 3, generator=gen).double().requires_grad_(True)
+    w = torch.softmax(torch.randn(N, K, generator=gen), -1).double().requires_grad_(True)
+    cR = torch.randn(N, 3, 3, generator=gen).double()
+    cT = torch.randn(N, 3, generator=gen).double()
+    R, T = refdq.DQBlending(q, t, w, rot_as_q=False)
+    ((R * cR).sum() + (T * cT).sum()).backward()
+    np.savez_compressed(os.path.join(HERE, "dq_blend_grad.npz"), q=q.numpy(), t=t.detach().numpy(), w=w.detach().numpy(),
+                        cR=cR.numpy(), cT=cT.numpy(), R=R.detach().numpy(), T=T.detach().numpy(), g_t=t.grad.numpy(),
+                        g_w=w.grad.numpy())
+    print("wrote dq_blend_grad")
+
+
 def sh_case():
     gen = torch.Generator().manual_seed(6)
     N = 64
@@ -120,6 +138,9 @@ def sh_case():
 
 if __name__ == "__main__":
     torch.manual_seed(0)
+    if "--dq-grad" in sys.argv:
+        dq_grad_case()
+        sys.exit(0)
     if "--topk" in sys.argv:  # only the K > 0 cases (added later; the files below are left untouched)
         # K > 0 with the weight MLP indexes the MLP output with bone numbers 1..J-1 (skeleton_warp.py:59) and fails
         # in the reference whenever the last bone is among the nearest: these cases run with the MLP off

@@ -246,3 +246,52 @@ def test_dual_quaternion_blend_vs_reference_golden():
     # blended unit quaternion: compare its rotation matrix (sign-free)
     Rq = so.quat_to_mat(d_rot.cpu().double())
     assert helpers.rel_err(Rq.numpy(), R.numpy()) <= 2e-5
+
+
+@pytest.mark.parametrize("over", [dict(), dict(soft_mask=True, with_mlp_weight=True, with_offsets=True)])
+def test_dual_quaternion_skinning_forward_backward_vs_float64_oracle(over):
+    """blend_mode = 1 (rg_skin_forward / rg_skin_backward_blend) against the float64 oracle, whose dual-quaternion blend
+    and its autograd gradients are pinned to the reference's DQBlending (tests/test_oracle.py).  Both sides start from the
+    SAME bone table (the FK kernel's G and node_rot): the reference's formula standardises the sign of every bone's dual
+    part by the sign of its real component, which is numerically zero for bones that barely move, so a bone table that
+    differs in the last bit can flip a sign and change the blend -- a property of the reference's (unused) formula, not of
+    either implementation."""
+    from riggs_b200 import skeleton_warp as sw
+    scene = synth.make_config("small", **over)
+    g = torch.Generator().manual_seed(21)
+    c_xyz = torch.randn(scene.N, 3, generator=g).double() / scene.N
+    c_rot = torch.randn(scene.N, 4, generator=g).double() / scene.N
+    joints = scene.joints.cuda()
+    par = scene.parents.to(torch.int32).cuda()
+    with torch.no_grad():
+        G0, node_rot, _ = sw.fk(scene.poses[0]["local_rotation"].cuda(), scene.poses[0]["global_trans"].cuda(), joints, par)
+
+    def leaves(dtype, dev):
+        mk = lambda t: None if t is None else t.to(dev, dtype).clone().requires_grad_(True)
+        return dict(nr=mk(scene.node_radius_raw), G=mk(G0.cpu()), g=mk(scene.poses[0]["global_trans"]),
+                    mask=mk(scene.motion_mask), mlp=mk(scene.mlp_weight), off=mk(scene.template_offsets))
+
+    L = leaves(torch.float64, "cpu")
+    x64 = scene.xyz.double()
+    w, _, _ = so.skin_weights(x64, scene.joints.double(), scene.parents, L["nr"], L["mlp"])
+    q64, t64 = node_rot.cpu().double()[1:], L["G"][1:, 9:12]
+    R, T = so.dq_blend(q64, t64, w)
+    y = torch.einsum("nab,nb->na", R, x64) + T + L["g"] + (L["off"] if L["off"] is not None else 0.0)
+    o_xyz = (y - x64) * L["mask"]
+    o_rot = so.dq_blend_quat(q64, t64, w) * L["mask"]
+    ((o_xyz * c_xyz).sum() + (o_rot * c_rot).sum()).backward()
+
+    C = leaves(torch.float32, "cuda")
+    d_xyz, d_rot, _ = sw.skin(scene.xyz.cuda(), joints, par, C["nr"], C["G"], node_rot, C["g"],
+                              C["mask"].reshape(-1), C["mlp"], C["off"], 1, False)
+    ((d_xyz * c_xyz.float().cuda()).sum() + (d_rot * c_rot.float().cuda()).sum()).backward()
+    torch.cuda.synchronize()
+    assert helpers.rel_err(d_xyz.detach().cpu().numpy(), o_xyz.detach().numpy()) <= 2e-5
+    assert helpers.rel_err(d_rot.detach().cpu().numpy(), o_rot.detach().numpy()) <= 2e-5
+    assert float(C["G"].grad[:, :9].abs().max()) == 0.0  # the rotation enters through the detached node_rot only
+    for k in ("nr", "G", "g", "mask", "mlp", "off"):
+        if L[k] is None:
+            continue
+        a, b = C[k].grad.cpu().numpy().reshape(-1), L[k].grad.numpy().reshape(-1)
+        assert helpers.rel_err(a, b, floor=1e-12) <= 1e-4, k
+        assert helpers.rel_l2(a, b) <= 1e-4, k

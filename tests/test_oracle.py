@@ -187,3 +187,16 @@ def test_node_warp_oracle_matches_reference_golden(name):
     for k, v in attrs.items():
         if v.grad is not None:
             close(v.grad.numpy(), g["g_node_" + k])
+
+
+def test_dq_oracle_gradients_vs_reference_autograd():
+    """skin_oracle.dq_blend differentiated by autograd against the gradients of the reference's own DQBlending
+    (tests/golden/dq_blend_grad.npz, made by make_skin_golden.py --dq-grad)."""
+    d = _load("dq_blend_grad")
+    t = d["t"].double().clone().requires_grad_(True)
+    w = d["w"].double().clone().requires_grad_(True)
+    R, T = so.dq_blend(d["q"].double(), t, w)
+    assert float((R - d["R"]).abs().max()) < 1e-12 and float((T - d["T"]).abs().max()) < 1e-12
+    ((R * d["cR"].double()).sum() + (T * d["cT"].double()).sum()).backward()
+    assert float((t.grad - d["g_t"]).abs().max()) < 1e-10
+    assert float((w.grad - d["g_w"]).abs().max()) < 1e-10
