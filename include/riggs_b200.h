@@ -265,6 +265,8 @@ typedef struct RgSkinnedScene {
     const float *local_rot;     /* (J,4) un-normalised quaternions of the pose */
     const float *global_trans;  /* (3) */
     const float *viewmatrix, *projmatrix, *campos, *background;
+    int blend_mode;             /* 0: linear blend skinning (skeleton_utils/skeleton_warp.py:149-150, what the reference runs);
+                                   1: the bone transforms blended as dual quaternions (utils/dual_quaternion.py:135-180) */
 } RgSkinnedScene;
 
 /* Caller-owned device scratch, reused across frames; nothing is allocated and the host never waits.

@@ -27,7 +27,8 @@ class RgSkinnedScene(C.Structure):
                 [(n, C.c_void_p) for n in ("xyz", "scaling_raw", "rotation_raw", "opacity_raw", "features_dc",
                                            "features_rest", "motion_mask", "mlp_weight", "offsets", "joints", "parents",
                                            "node_radius_raw", "local_rot", "global_trans", "viewmatrix", "projmatrix",
-                                           "campos", "background")])
+                                           "campos", "background")] +
+                [("blend_mode", C.c_int)])
 
 
 class RgAdamGroup(C.Structure):

@@ -39,12 +39,14 @@ int check_scene(const RgSkinnedScene* s, const RgWorkspace* w, const char* who) 
         return -1;
     }
     if (w->binning_bytes < 1024) { set_error(std::string(who) + ": workspace binning buffer too small"); return -1; }
+    if (s->blend_mode != 0 && s->blend_mode != 1) { set_error(std::string(who) + ": blend_mode must be 0 (linear) or 1 (dual quaternion)"); return -1; }
     return 0;
 }
 
 SkinFuseArgs fuse_args(const RgSkinnedScene* s, const GeomState& geom, const FkSlots& fk) {
     SkinFuseArgs f = {};
     f.J = s->J; f.M_rest = s->M_rest; f.isotropic = s->isotropic != 0; f.zero_d_rotation = s->zero_d_rotation != 0;
+    f.blend_mode = s->blend_mode;
     f.xyz = s->xyz; f.scaling_raw = s->scaling_raw; f.rotation_raw = s->rotation_raw; f.opacity_raw = s->opacity_raw;
     f.features_dc = s->features_dc; f.features_rest = s->features_rest; f.motion_mask = s->motion_mask;
     f.mlp_weight = s->mlp_weight; f.offsets = s->offsets; f.joints = s->joints; f.parents = s->parents;

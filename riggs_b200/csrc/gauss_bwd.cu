@@ -17,6 +17,7 @@
 #include "bones.cuh"
 #include "bulk_copy.cuh"
 #include "common.cuh"
+#include "dq.cuh"
 #include "kernels.cuh"
 #include "math.cuh"
 #include "sh.cuh"
@@ -61,7 +62,8 @@ __device__ __forceinline__ void cov3d_backward(const float3 scale, float mod, co
 #undef DM
 }
 
-template <bool FUSED>
+// DQ (fused entry only): the skinning backward of the dual-quaternion blend (dq.cuh) instead of the linear one.
+template <bool FUSED, bool DQ = false>
 __global__ void __launch_bounds__(256, 3) gauss_backward_kernel(GaussBwdArgs a, SkinFuseBwdArgs s) {
     const int idx = a.row_begin + blockIdx.x * blockDim.x + threadIdx.x;
     const int row_end = a.row_end > 0 ? a.row_end : a.P;
@@ -362,6 +364,15 @@ __global__ void __launch_bounds__(256, 3) gauss_backward_kernel(GaussBwdArgs a, 
             if (s.doffsets) { s.doffsets[3 * i] = 0.f; s.doffsets[3 * i + 1] = 0.f; s.doffsets[3 * i + 2] = 0.f; }
             if (s.dmlp_weight) for (int k = 0; k < K; k++) s.dmlp_weight[i * K + k] = 0.f;
         }
+    } else if (DQ) {
+        float ox = 0.f, oy = 0.f, oz = 0.f;
+        if (s.f.offsets && in_range) { ox = s.f.offsets[3 * i]; oy = s.f.offsets[3 * i + 1]; oz = s.f.offsets[3 * i + 2]; }
+        dq_skin_backward_point(s_b, K, lane, in_range, x, y, z, m, gx, gy, gz, h0, h1, h2, h3,
+                               s.f.mlp_weight ? s.f.mlp_weight + (in_range ? i : 0) * K : nullptr, s.f.global_trans[0],
+                               s.f.global_trans[1], s.f.global_trans[2], ox, oy, oz, s_acc,
+                               (s.dmask && in_range) ? s.dmask + i : nullptr,
+                               (s.dmlp_weight && in_range) ? s.dmlp_weight + i * K : nullptr);
+        if (in_range && s.doffsets) { s.doffsets[3 * i] = m * gx; s.doffsets[3 * i + 1] = m * gy; s.doffsets[3 * i + 2] = m * gz; }
     } else {
         // sweep 1: normaliser and sum_k w_k c_k
         float wsum = 0.f, scw = 0.f, ax = 0.f, ay = 0.f, az = 0.f, q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
@@ -458,7 +469,12 @@ int launch_gauss_skin_backward(const GaussBwdArgs& a, const SkinFuseBwdArgs& s, 
     if (ensure_dyn_smem(reinterpret_cast<const void*>(gauss_backward_kernel<true>), 160 * 1024)) return -1;
     const int rows = (a.row_end > 0 ? a.row_end : a.P) - a.row_begin;
     if (rows <= 0) return 0;
-    gauss_backward_kernel<true><<<(rows + 255) / 256, 256, smem, stream>>>(a, s);
+    if (s.f.blend_mode == 1) {
+        if (ensure_dyn_smem(reinterpret_cast<const void*>(gauss_backward_kernel<true, true>), 160 * 1024)) return -1;
+        gauss_backward_kernel<true, true><<<(rows + 255) / 256, 256, smem, stream>>>(a, s);
+    } else {
+        gauss_backward_kernel<true><<<(rows + 255) / 256, 256, smem, stream>>>(a, s);
+    }
     return 0;
 }
 

@@ -40,6 +40,7 @@ struct SkinFuseArgs {
     int J, M_rest;
     bool isotropic;        // _scaling has one column
     bool zero_d_rotation;  // the trainer zeroes d_rotation for isotropic Gaussians (train_rig.py:422-423)
+    int blend_mode;        // 0: linear blend skinning (what the reference runs), 1: dual-quaternion blending (dq.cuh)
     const float* xyz;
     const float* scaling_raw;
     const float* rotation_raw;

@@ -20,13 +20,15 @@
 #include "bulk_copy.cuh"
 #include "common.cuh"
 #include "cull.cuh"
+#include "dq.cuh"
 #include "kernels.cuh"
 #include "math.cuh"
 #include "sh.cuh"
 
 namespace rg {
 
-template <bool FUSED>
+// DQ (fused entry only): the bone transforms are blended as dual quaternions (dq.cuh) instead of linearly.
+template <bool FUSED, bool DQ = false>
 __global__ void __launch_bounds__(256, 4) preprocess_kernel(PreprocessArgs a, SkinFuseArgs s) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     __shared__ float s_mat[35];  // view[16], proj[16], campos[3]
@@ -75,6 +77,7 @@ __global__ void __launch_bounds__(256, 4) preprocess_kernel(PreprocessArgs a, Sk
         const float x = s.xyz[3 * i], y = s.xyz[3 * i + 1], z = s.xyz[3 * i + 2];
         const int K = s.J - 1;
         float wsum = 0.f, ax = 0.f, ay = 0.f, az = 0.f, q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
+        float Br[4] = {0, 0, 0, 0}, Bd[4] = {0, 0, 0, 0};
         for (int k = 0; k < K; k++) {
             const BoneSm& b = s_b[k];
             const float d2 = seg_dist2(b, x, y, z);
@@ -82,12 +85,26 @@ __global__ void __launch_bounds__(256, 4) preprocess_kernel(PreprocessArgs a, Sk
             if (s.mlp_weight) w *= s.mlp_weight[i * K + k];
             w += 1e-7f;
             wsum += w;
-            ax += w * (b.G[0] * x + b.G[1] * y + b.G[2] * z + b.G[9]);
-            ay += w * (b.G[3] * x + b.G[4] * y + b.G[5] * z + b.G[10]);
-            az += w * (b.G[6] * x + b.G[7] * y + b.G[8] * z + b.G[11]);
-            q0 += w * b.q[0]; q1 += w * b.q[1]; q2 += w * b.q[2]; q3 += w * b.q[3];
+            if (!DQ) {
+                ax += w * (b.G[0] * x + b.G[1] * y + b.G[2] * z + b.G[9]);
+                ay += w * (b.G[3] * x + b.G[4] * y + b.G[5] * z + b.G[10]);
+                az += w * (b.G[6] * x + b.G[7] * y + b.G[8] * z + b.G[11]);
+                q0 += w * b.q[0]; q1 += w * b.q[1]; q2 += w * b.q[2]; q3 += w * b.q[3];
+            } else {
+                const DqBone qb = dq_of_bone(b);
+#pragma unroll
+                for (int c = 0; c < 4; c++) { Br[c] += w * qb.r[c]; Bd[c] += w * qb.d[c]; }
+            }
         }
-        const float inv = 1.0f / wsum;
+        float inv = 1.0f / wsum;
+        if (DQ) {  // the blended rigid transform applied to x; its unit quaternion is the rotation output
+#pragma unroll
+            for (int c = 0; c < 4; c++) { Br[c] *= inv; Bd[c] *= inv; }
+            const DqBlend f = dq_finish(Br, Bd, x, y, z);
+            ax = f.y[0]; ay = f.y[1]; az = f.y[2];
+            q0 = f.r0[0]; q1 = f.r0[1]; q2 = f.r0[2]; q3 = f.r0[3];
+            inv = 1.0f;
+        }
         const float m = s.motion_mask ? s.motion_mask[i] : 1.0f;
         float ox = 0.f, oy = 0.f, oz = 0.f;
         if (s.offsets) { ox = s.offsets[3 * i]; oy = s.offsets[3 * i + 1]; oz = s.offsets[3 * i + 2]; }
@@ -216,7 +233,12 @@ int launch_skin_preprocess(const PreprocessArgs& a, const SkinFuseArgs& s, cudaS
     LaunchScope ls("skin_preprocess", stream);
     const size_t smem = align_up(bone_smem_bytes(s.J, false), 128) + (size_t)256 * s.M_rest * 3 * sizeof(float) + 16;
     if (ensure_dyn_smem(reinterpret_cast<const void*>(preprocess_kernel<true>), 96 * 1024)) return -1;
-    preprocess_kernel<true><<<(a.P + 255) / 256, 256, smem, stream>>>(a, s);
+    if (s.blend_mode == 1) {
+        if (ensure_dyn_smem(reinterpret_cast<const void*>(preprocess_kernel<true, true>), 96 * 1024)) return -1;
+        preprocess_kernel<true, true><<<(a.P + 255) / 256, 256, smem, stream>>>(a, s);
+    } else {
+        preprocess_kernel<true><<<(a.P + 255) / 256, 256, smem, stream>>>(a, s);
+    }
     return 0;
 }
 

@@ -111,8 +111,9 @@ class _Lease:
         self.release()
 
 
-def _scene_struct(P, J, sh_degree, M_rest, isotropic, zero_d_rot, W, H, tfx, tfy, scale_mod, t):
+def _scene_struct(P, J, sh_degree, M_rest, isotropic, zero_d_rot, W, H, tfx, tfy, scale_mod, t, blend_mode=0):
     s = _lib.RgSkinnedScene()
+    s.blend_mode = int(blend_mode)
     s.P, s.J, s.sh_degree, s.M_rest = P, J, sh_degree, M_rest
     s.isotropic, s.zero_d_rotation, s.width, s.height = int(isotropic), int(zero_d_rot), W, H
     s.tan_fovx, s.tan_fovy, s.scale_modifier = tfx, tfy, scale_mod
@@ -139,7 +140,7 @@ class _SkinnedRender(torch.autograd.Function):
         isotropic = scaling_raw.shape[-1] == 1
         M_rest = features_rest.shape[1]
         scene = _scene_struct(P, J, cfg["sh_degree"], M_rest, isotropic, cfg["zero_d_rotation"], W, H, cfg["tanfovx"],
-                              cfg["tanfovy"], cfg["scale_modifier"], t)
+                              cfg["tanfovy"], cfg["scale_modifier"], t, cfg.get("blend_mode", 0))
         color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
         depth = torch.empty((1, H, W), dtype=torch.float32, device=dev)
         alpha = torch.empty((1, H, W), dtype=torch.float32, device=dev)
@@ -324,7 +325,8 @@ def render_skinned(viewpoint_camera, pc, skeleton, pose: Dict[str, torch.Tensor]
                viewmatrix=f32c(viewpoint_camera.world_view_transform), projmatrix=f32c(viewpoint_camera.full_proj_transform),
                campos=f32c(viewpoint_camera.camera_center), bg=f32c(bg_color),
                zero_d_rotation=isotropic if zero_d_rotation is None else zero_d_rotation, debug_outputs=debug_outputs,
-               pool=pool, grad_out=grad_out, reduce=reduce, accumulate=accumulate)
+               pool=pool, grad_out=grad_out, reduce=reduce, accumulate=accumulate,
+               blend_mode=getattr(skeleton, "blend_mode", 0))
     mm = getattr(pc, "_motion_mask", None)
     mask = mm.reshape(-1) if mm is not None else None
     color, depth, alpha, radii, d_nodes = _SkinnedRender.apply(

@@ -567,3 +567,49 @@ def test_second_backward_raises_a_clear_error():
     loss.backward(retain_graph=True)
     with pytest.raises(_lib.RiggsError, match="already run"):
         loss.backward()
+
+
+@pytest.mark.parametrize("over", [dict(), dict(soft_mask=True, with_mlp_weight=True, with_offsets=True)])
+def test_fused_dual_quaternion_blending_matches_unfused(over):
+    """RgSkinnedScene.blend_mode = 1 (SkeletonWarp(blend_mode="dq")): the fused forward / backward kernels blend the bone
+    transforms as dual quaternions; checked against the unfused chain on the same FK output (FK kernel -> rg_skin_forward /
+    rg_skin_backward_blend, themselves pinned to the reference's DQBlending -> render())."""
+    from riggs_b200 import skeleton_warp as sw
+    from riggs_b200.fused import WorkspacePool, render_skinned
+    from riggs_b200.gaussian_renderer import GaussianParams, render
+    scene = synth.make_config("small", **over)
+    pc = GaussianParams.from_scene(scene)
+    warp = sw.SkeletonWarp(scene.joints, scene.parents, scene.node_radius_raw, use_skinning_weight_mlp=False,
+                           use_template_offsets=False, blend_mode="dq")
+    cam = scene.cameras[0].to("cuda")
+    bg = torch.tensor([0.1, 0.3, 0.2], device="cuda")
+    cots = [t.cuda() for t in synth.seeded_cotangents(cam.image_height, cam.image_width)]
+    params = [pc._xyz, pc._scaling, pc._rotation, pc._opacity, pc._features_dc, pc._features_rest, warp._node_radius]
+
+    def collect(pose, mlp, off):
+        g = [p.grad.clone() for p in params] + [pose["local_rotation"].grad.clone(), pose["global_trans"].grad.clone()]
+        g += [t.grad.clone() for t in (mlp, off) if t is not None]
+        for p in params:
+            p.grad = None
+        return g
+
+    pose, mlp, off = _leafs(scene)
+    out_f = render_skinned(cam, pc, warp, pose, _Pipe(), bg, mlp_weight=mlp, offsets=off, pool=WorkspacePool())
+    _loss(out_f, cots).backward()
+    g_f = collect(pose, mlp, off)
+
+    pose, mlp, off = _leafs(scene)
+    joints = warp.nodes[:, :3]
+    G, node_rot, _ = sw.fk(pose["local_rotation"], pose["global_trans"], joints, warp.parents_i32)
+    d_xyz, d_rot, _ = sw.skin(pc.get_xyz, joints, warp.parents_i32, warp._node_radius, G, node_rot, pose["global_trans"],
+                              pc._motion_mask.reshape(-1), mlp, off, 1, False)
+    out_u = render(cam, pc, _Pipe(), bg, d_xyz, d_rot, 0.0)
+    _loss(out_u, cots).backward()
+    g_u = collect(pose, mlp, off)
+    torch.cuda.synchronize()
+    assert torch.equal(out_f["radii"], out_u["radii"])
+    for k in ("render", "depth", "alpha"):
+        assert helpers.rel_err(out_f[k].detach().cpu().numpy(), out_u[k].detach().cpu().numpy()) <= 5e-5, k
+    for i, (a, b) in enumerate(zip(g_f, g_u)):
+        assert a.shape == b.shape
+        assert helpers.rel_err(a.cpu().numpy().reshape(-1), b.cpu().numpy().reshape(-1), floor=1e-9) <= E2E_GRAD_RTOL, i
