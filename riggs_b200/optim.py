@@ -44,8 +44,12 @@ class FusedAdam:
 
     @torch.no_grad()
     def step(self):
-        entries = []
+        # torch.optim.Adam keeps state['step'] per parameter and advances it only for parameters that have a gradient:
+        # entries are grouped by their own step count (one launch per distinct count -- one, unless some parameter
+        # missed gradients on earlier iterations)
+        buckets: Dict[int, list] = {}
         keep = []  # contiguous gradient copies must outlive the launch
+        dev = None
         for g in self.param_groups:
             for p in g["params"]:
                 if p.grad is None:
@@ -54,18 +58,23 @@ class FusedAdam:
                     raise _lib.RiggsError("FusedAdam needs contiguous fp32 CUDA parameters; riggs_b200 has no CPU path")
                 st = self.state.get(p)
                 if st is None:
-                    st = self.state[p] = {"exp_avg": torch.zeros_like(p), "exp_avg_sq": torch.zeros_like(p)}
+                    st = self.state[p] = {"step": 0, "exp_avg": torch.zeros_like(p), "exp_avg_sq": torch.zeros_like(p)}
+                st["step"] = int(st.get("step", 0)) + 1
                 grad = p.grad if p.grad.is_contiguous() else p.grad.contiguous()
                 keep.append(grad)
-                entries.append(_lib.RgAdamGroup(ptr(p), ptr(grad), ptr(st["exp_avg"]), ptr(st["exp_avg_sq"]), p.numel(),
-                                                float(g["lr"])))
-        if not entries:
+                dev = p.device
+                buckets.setdefault(st["step"], []).append(
+                    _lib.RgAdamGroup(ptr(p), ptr(grad), ptr(st["exp_avg"]), ptr(st["exp_avg_sq"]), p.numel(), float(g["lr"])))
+        if not buckets:
             return
         self._step += 1
-        arr = (_lib.RgAdamGroup * len(entries))(*entries)
-        with torch.cuda.device(entries and self.param_groups[0]["params"][0].device):
-            check(_lib.lib().rg_adam_step(len(entries), C.cast(arr, C.c_void_p), self._step, self.betas[0], self.betas[1],
-                                          self.eps, stream_ptr()), "rg_adam_step")
+        with torch.cuda.device(dev):
+            for step, entries in buckets.items():
+                for i in range(0, len(entries), 16):  # rg_adam_step takes up to 16 groups per launch
+                    part = entries[i:i + 16]
+                    arr = (_lib.RgAdamGroup * len(part))(*part)
+                    check(_lib.lib().rg_adam_step(len(part), C.cast(arr, C.c_void_p), step, self.betas[0], self.betas[1],
+                                                  self.eps, stream_ptr()), "rg_adam_step")
 
 
 @torch.no_grad()
@@ -144,7 +153,7 @@ def prune_points(optimizer: FusedAdam, mask: torch.Tensor, stats: Optional[Dict[
         newp = torch.nn.Parameter(out[i].requires_grad_(True))
         if st is not None:
             del optimizer.state[p]
-            optimizer.state[newp] = {"exp_avg": out[k], "exp_avg_sq": out[k + 1]}
+            optimizer.state[newp] = {"step": int(st.get("step", 0)), "exp_avg": out[k], "exp_avg_sq": out[k + 1]}
             k += 2
         g["params"][0] = newp
         new_params[g.get("name", str(i))] = newp
@@ -201,7 +210,7 @@ def regroup_rows(optimizer: FusedAdam, src_row: torch.Tensor, n_old_rows: int) -
         newp = torch.nn.Parameter(new[i].requires_grad_(True))
         if st is not None:
             del optimizer.state[p]
-            optimizer.state[newp] = {"exp_avg": m_dst[k], "exp_avg_sq": m_dst[k + 1]}
+            optimizer.state[newp] = {"step": int(st.get("step", 0)), "exp_avg": m_dst[k], "exp_avg_sq": m_dst[k + 1]}
             k += 2
         g["params"][0] = newp
         out[g.get("name", str(i))] = newp

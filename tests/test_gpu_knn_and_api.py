@@ -491,3 +491,28 @@ def test_render_flow_matches_reference_rasterizer_on_the_same_flow():
     d2g = d2.clone().requires_grad_(True)
     render_flow(pc, cam1, cam2, d1, d2g, 0.0, 0.0)["render"][:2].sum().backward()
     assert d2g.grad is not None and torch.isfinite(d2g.grad).all() and float(d2g.grad.abs().max()) > 0
+
+
+def test_fused_adam_keeps_a_step_count_per_parameter_like_torch():
+    """torch.optim.Adam advances state['step'] only for parameters that have a gradient: a parameter that misses gradients
+    on some iterations gets its own bias correction."""
+    from riggs_b200.optim import FusedAdam
+    g = torch.Generator().manual_seed(3)
+    a0, b0 = torch.randn(1000, 3, generator=g).cuda(), torch.randn(500, generator=g).cuda()
+    pa, pb = a0.clone().requires_grad_(True), b0.clone().requires_grad_(True)
+    qa, qb = a0.clone().requires_grad_(True), b0.clone().requires_grad_(True)
+    ours = FusedAdam([{"params": [pa], "lr": 1e-2, "name": "a"}, {"params": [pb], "lr": 3e-3, "name": "b"}], lr=0.0, eps=1e-15)
+    ref = torch.optim.Adam([{"params": [qa], "lr": 1e-2}, {"params": [qb], "lr": 3e-3}], lr=0.0, eps=1e-15)
+    for it in range(6):
+        ga, gb = torch.randn(1000, 3, generator=g).cuda(), torch.randn(500, generator=g).cuda()
+        pa.grad, qa.grad = ga.clone(), ga.clone()
+        if it % 3 != 1:  # b has no gradient on iterations 1 and 4
+            pb.grad, qb.grad = gb.clone(), gb.clone()
+        else:
+            pb.grad = qb.grad = None
+        ours.step()
+        ref.step()
+    torch.cuda.synchronize()
+    assert ours.state[pb]["step"] == 4 and ours.state[pa]["step"] == 6
+    assert helpers.rel_err(pa.detach().cpu().numpy(), qa.detach().cpu().numpy()) <= 1e-6
+    assert helpers.rel_err(pb.detach().cpu().numpy(), qb.detach().cpu().numpy()) <= 1e-6
