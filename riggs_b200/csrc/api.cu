@@ -51,6 +51,7 @@ GeomState GeomState::carve(char* base, size_t P, int W, int H, size_t* bytes) {
     g.status = c.take<uint32_t>(8);
     g.grad_acc = c.take<float>(10 * P);
     g.d_rot = c.take<float>(4 * P);
+    g.skin_wsum = c.take<float>(P);
     g.fk = c.take<float>(128 * (12 + 4 + 3 + 12 + 1) + 4);
     if (bytes) *bytes = align_up(c.off, 256) + 256;
     return g;

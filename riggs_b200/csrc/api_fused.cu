@@ -51,7 +51,7 @@ SkinFuseArgs fuse_args(const RgSkinnedScene* s, const GeomState& geom, const FkS
     f.features_dc = s->features_dc; f.features_rest = s->features_rest; f.motion_mask = s->motion_mask;
     f.mlp_weight = s->mlp_weight; f.offsets = s->offsets; f.joints = s->joints; f.parents = s->parents;
     f.node_radius_raw = s->node_radius_raw; f.G = fk.G; f.node_rot = fk.node_rot; f.global_trans = s->global_trans;
-    f.means3D_out = geom.means3D; f.d_rot_out = geom.d_rot;
+    f.means3D_out = geom.means3D; f.d_rot_out = geom.d_rot; f.wsum_out = geom.skin_wsum;
     return f;
 }
 }  // namespace
@@ -175,6 +175,7 @@ int rg_skinned_backward_part(const RgSkinnedScene* s, const RgWorkspace* w, int 
         SkinFuseBwdArgs sb = {};
         sb.f = fuse_args(s, geom, fk);
         sb.d_rot_saved = geom.d_rot;
+        sb.wsum_saved = geom.skin_wsum;
         sb.d_xyz = d_xyz; sb.d_scaling_raw = d_scaling_raw; sb.d_rotation_raw = d_rotation_raw; sb.d_opacity_raw = d_opacity_raw;
         sb.d_features_dc = d_features_dc; sb.d_features_rest = d_features_rest;
         sb.dG = fk.dG; sb.dnode_radius_raw = fk.dradius; sb.dglobal_trans = fk.dtrans;

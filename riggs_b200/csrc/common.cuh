@@ -73,6 +73,7 @@ struct GeomState {
     uint32_t* status;         // [0] num_rendered, [1] overflow flag
     float* grad_acc;          // 10P floats: per-Gaussian 2-D gradient accumulators of the backward blend
     float* d_rot;             // 4P blended bone quaternion * mask (fused entry, kept for the backward)
+    float* skin_wsum;         // P: sum of the un-normalised skinning weights (fused entry): spares the backward a sweep over the bones
     float* fk;                // bone tables of the fused entry: G 128x12 | node_rot 128x4 | posed 128x3 | dG 128x12 | dradius 128 | dtrans 4
     static GeomState carve(char* base, size_t P, int W, int H, size_t* bytes);
 };

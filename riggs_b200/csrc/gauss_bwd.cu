@@ -374,33 +374,25 @@ __global__ void __launch_bounds__(256, 3) gauss_backward_kernel(GaussBwdArgs a, 
                                (s.dmlp_weight && in_range) ? s.dmlp_weight + i * K : nullptr);
         if (in_range && s.doffsets) { s.doffsets[3 * i] = m * gx; s.doffsets[3 * i + 1] = m * gy; s.doffsets[3 * i + 2] = m * gz; }
     } else {
-        // sweep 1: normaliser and sum_k w_k c_k
-        float wsum = 0.f, scw = 0.f, ax = 0.f, ay = 0.f, az = 0.f, q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
-        for (int k = 0; k < K; k++) {
-            const BoneSm& b = s_b[k];
-            const float d2 = seg_dist2(b, x, y, z);
-            float w = expf(-d2 * b.inv_2r2);
-            if (s.f.mlp_weight && in_range) w *= s.f.mlp_weight[i * K + k];
-            w += 1e-7f;
-            const float yx = b.G[0] * x + b.G[1] * y + b.G[2] * z + b.G[9];
-            const float yy = b.G[3] * x + b.G[4] * y + b.G[5] * z + b.G[10];
-            const float yz = b.G[6] * x + b.G[7] * y + b.G[8] * z + b.G[11];
-            const float c = gx * yx + gy * yy + gz * yz + h0 * b.q[0] + h1 * b.q[1] + h2 * b.q[2] + h3 * b.q[3];
-            wsum += w;
-            scw += w * c;
-            ax += w * yx; ay += w * yy; az += w * yz;
-            q0 += w * b.q[0]; q1 += w * b.q[1]; q2 += w * b.q[2]; q3 += w * b.q[3];
-        }
-        const float inv = 1.0f / wsum;
-        const float cbar = scw * inv;
+        // No first sweep over the bones: the forward kept the normaliser, and m * sum_k w_k c_k follows from what it kept too --
+        //   m * sum_k w_k y_k = (p - x) - m (g + o - x)   (p = the skinned position),   m * sum_k w_k q_k = d_rot_saved.
+        float inv = 1.f, mcbar = 0.f;
         if (in_range) {
+            inv = 1.0f / s.wsum_saved[i];
             float ox = 0.f, oy = 0.f, oz = 0.f;
             if (s.f.offsets) { ox = s.f.offsets[3 * i]; oy = s.f.offsets[3 * i + 1]; oz = s.f.offsets[3 * i + 2]; }
-            if (s.dmask)
-                s.dmask[i] = gx * (ax * inv + s.f.global_trans[0] + ox - x) + gy * (ay * inv + s.f.global_trans[1] + oy - y) +
-                             gz * (az * inv + s.f.global_trans[2] + oz - z) + (h0 * q0 + h1 * q1 + h2 * q2 + h3 * q3) * inv;
+            const float sx = (a.means3D[3 * i] - x) - m * (s.f.global_trans[0] + ox - x);
+            const float sy = (a.means3D[3 * i + 1] - y) - m * (s.f.global_trans[1] + oy - y);
+            const float sz = (a.means3D[3 * i + 2] - z) - m * (s.f.global_trans[2] + oz - z);
+            mcbar = gx * sx + gy * sy + gz * sz;
+            if (!s.f.zero_d_rotation) {
+                const float4 dr = reinterpret_cast<const float4*>(s.d_rot_saved)[i];
+                mcbar += h0 * dr.x + h1 * dr.y + h2 * dr.z + h3 * dr.w;
+            }
             if (s.doffsets) { s.doffsets[3 * i] = m * gx; s.doffsets[3 * i + 1] = m * gy; s.doffsets[3 * i + 2] = m * gz; }
         }
+        const bool want_mask = s.dmask != nullptr;  // dL/dmask needs the un-masked blend (the kept one is lost where m = 0)
+        float ax = 0.f, ay = 0.f, az = 0.f, q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
         const float mgx = m * gx, mgy = m * gy, mgz = m * gz;
         {
             const float s0 = warp_sum(mgx), s1 = warp_sum(mgy), s2 = warp_sum(mgz);
@@ -419,7 +411,11 @@ __global__ void __launch_bounds__(256, 3) gauss_backward_kernel(GaussBwdArgs a, 
             const float yy = b.G[3] * x + b.G[4] * y + b.G[5] * z + b.G[10];
             const float yz = b.G[6] * x + b.G[7] * y + b.G[8] * z + b.G[11];
             const float c = gx * yx + gy * yy + gz * yz + h0 * b.q[0] + h1 * b.q[1] + h2 * b.q[2] + h3 * b.q[3];
-            const float dwhat = m * (c - cbar) * inv;
+            const float dwhat = (m * c - mcbar) * inv;
+            if (want_mask) {
+                ax += w * yx; ay += w * yy; az += w * yz;
+                q0 += w * b.q[0]; q1 += w * b.q[1]; q2 += w * b.q[2]; q3 += w * b.q[3];
+            }
             if (s.dmlp_weight && in_range) s.dmlp_weight[i * K + k] = dwhat * e;
             float v[16];
             v[0] = mgx * w * x; v[1] = mgx * w * y; v[2] = mgx * w * z;
@@ -430,6 +426,12 @@ __global__ void __launch_bounds__(256, 3) gauss_backward_kernel(GaussBwdArgs a, 
             v[13] = v[14] = v[15] = 0.f;
             const float r = transpose_reduce16(v, lane);
             if (writer) s_acc[k * 13 + my_id] += r;
+        }
+        if (want_mask && in_range) {
+            float ox = 0.f, oy = 0.f, oz = 0.f;
+            if (s.f.offsets) { ox = s.f.offsets[3 * i]; oy = s.f.offsets[3 * i + 1]; oz = s.f.offsets[3 * i + 2]; }
+            s.dmask[i] = gx * (ax + s.f.global_trans[0] + ox - x) + gy * (ay + s.f.global_trans[1] + oy - y) +
+                         gz * (az + s.f.global_trans[2] + oz - z) + h0 * q0 + h1 * q1 + h2 * q2 + h3 * q3;
         }
     }
     __syncthreads();

@@ -58,6 +58,7 @@ struct SkinFuseArgs {
     const float* global_trans;
     float* means3D_out;  // (N,3) kept for the backward
     float* d_rot_out;    // (N,4) blended bone quaternion * mask, kept for the backward
+    float* wsum_out;     // (N) sum of the un-normalised skinning weights, kept for the backward
     float* dbg_scales;   // optional test outputs: the activated tensors the reference rasterizer would be given
     float* dbg_rotations;
     float* dbg_opacities;
@@ -66,6 +67,7 @@ struct SkinFuseArgs {
 struct SkinFuseBwdArgs {
     SkinFuseArgs f;
     const float* d_rot_saved;  // (N,4) from the forward
+    const float* wsum_saved;   // (N) from the forward
     // gradients of the raw model tensors (fully written)
     float* d_xyz;
     float* d_scaling_raw;

@@ -97,6 +97,7 @@ __global__ void __launch_bounds__(256, 4) preprocess_kernel(PreprocessArgs a, Sk
             }
         }
         float inv = 1.0f / wsum;
+        s.wsum_out[i] = wsum;
         if (DQ) {  // the blended rigid transform applied to x; its unit quaternion is the rotation output
 #pragma unroll
             for (int c = 0; c < 4; c++) { Br[c] *= inv; Bd[c] *= inv; }
