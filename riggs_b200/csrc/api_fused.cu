@@ -95,9 +95,11 @@ int rg_skinned_forward(const RgSkinnedScene* s, const RgWorkspace* w, float* out
     SkinFuseArgs f = fuse_args(s, geom, fk);
     f.dbg_scales = dbg_scales; f.dbg_rotations = dbg_rotations; f.dbg_opacities = dbg_opacities;
     if (dbg_rotations && !al16(dbg_rotations)) { set_error("rg_skinned_forward: dbg_rotations must be 16-byte aligned"); return -1; }
+    pa.sort_hist = depth_sort_prepare(geom.sort_temp, P, stream);  // the preprocess kernel counts the sort's digits
     if (launch_skin_preprocess(pa, f, stream)) return -1;
 
-    if (launch_depth_sort(geom.sort_temp, geom.sort_temp_bytes, geom.depths, geom.sorted_keys, geom.ids, geom.sorted_ids, P, stream))
+    if (launch_depth_sort(geom.sort_temp, geom.sort_temp_bytes, geom.depths, geom.sorted_keys, geom.ids, geom.sorted_ids, P, stream,
+                          pa.sort_hist != nullptr))
         return -1;
     if (launch_tile_count(bp, P, grid_x, grid_y, geom.sorted_ids, geom.tiles_touched, geom.means2D, radii, geom.rects, geom.M, geom.Mg, stream))
         return -1;

@@ -33,6 +33,7 @@ struct PreprocessArgs {
     uint32_t* tiles_touched;
     uint8_t* clamped;
     uint32_t* ids;  // iota, value array of the depth sort
+    uint32_t* sort_hist;  // optional: the depth sort's four 8-bit digit histograms (4 x 256), counted here (fused entry)
 };
 
 // Extra inputs of the fused skin + activation + preprocess kernel: raw model tensors and one pose's bone table.
@@ -105,7 +106,8 @@ size_t depth_sort_temp_bytes_cub(size_t P);  // binning.cu
 int launch_depth_sort_cub(char* temp, size_t temp_bytes, const float* depths, uint32_t* keys_out, const uint32_t* ids_in,
                           uint32_t* ids_out, int P, cudaStream_t stream);
 int launch_depth_sort(char* temp, size_t temp_bytes, const float* depths, uint32_t* keys_out, const uint32_t* ids_in,
-                      uint32_t* ids_out, int P, cudaStream_t stream);
+                      uint32_t* ids_out, int P, cudaStream_t stream, bool hist_ready = false);
+uint32_t* depth_sort_prepare(char* temp, int P, cudaStream_t stream);  // see radix_sort.cu
 int launch_tile_count(const BinPlan& b, int P, int grid_x, int grid_y, const uint32_t* sorted_ids,
                       const uint32_t* tiles_touched, const float2* means2D, const int* radii, uint2* rects, uint16_t* M,
                       uint16_t* Mg, cudaStream_t stream);

@@ -37,6 +37,12 @@ __global__ void __launch_bounds__(256, 4) preprocess_kernel(PreprocessArgs a, Sk
     else if (threadIdx.x < 32) s_mat[threadIdx.x] = a.projmatrix[threadIdx.x - 16];
     else if (threadIdx.x < 35) s_mat[threadIdx.x] = a.cam_pos[threadIdx.x - 32];
     BoneSm* s_b = reinterpret_cast<BoneSm*>(s_raw);
+    // Fused variant: the depth sort's four 8-bit digit histograms are counted here, while the key is in a register
+    // (saves the sort its histogram launch and a read of the keys)
+    __shared__ uint32_t s_hist[FUSED ? 4 * 256 : 1];
+    const bool count_digits = FUSED && a.sort_hist != nullptr;
+    if (count_digits)
+        for (int k = threadIdx.x; k < 4 * 256; k += blockDim.x) s_hist[k] = 0;
     // Fused variant: this CTA's block of features_rest (256 rows of M_rest*12 B, contiguous in memory) is pulled into
     // shared memory by one bulk (TMA) copy that runs while the threads do the skinning loop below.
     __shared__ __align__(8) uint64_t s_bar;
@@ -64,7 +70,9 @@ __global__ void __launch_bounds__(256, 4) preprocess_kernel(PreprocessArgs a, Sk
     }
     // The thread that started the bulk copy is thread 0 and it is always a valid row (first < P).  Threads past P own
     // no row and never touch s_sh; the CTA stays alive until thread 0 has seen the copy land (end of the kernel).
-    if (idx >= a.P) return;
+    const bool has_row = idx < a.P;
+    if (!has_row && !count_digits) return;
+    if (has_row) {
     const float* view = s_mat;
     const float* proj = s_mat + 16;
     const size_t i = (size_t)idx;
@@ -205,6 +213,17 @@ __global__ void __launch_bounds__(256, 4) preprocess_kernel(PreprocessArgs a, Sk
     a.tiles_touched[idx] = my_tiles;
     if (my_tiles == 0) a.depths[idx] = __int_as_float(0x7f800000);  // culled: +inf sorts behind everything
     a.ids[idx] = idx;
+    if (count_digits) {
+        const uint32_t key = my_tiles == 0 ? 0x7f800000u : __float_as_uint(p_view.z);
+#pragma unroll
+        for (int d = 0; d < 4; d++) atomicAdd(&s_hist[d * 256 + ((key >> (8 * d)) & 255u)], 1u);
+    }
+    }  // has_row
+    if (count_digits) {
+        __syncthreads();
+        for (int k = threadIdx.x; k < 4 * 256; k += blockDim.x)
+            if (s_hist[k]) atomicAdd(&a.sort_hist[k], s_hist[k]);
+    }
     // A culled Gaussian leaves the loop above without reading the staged SH block, so it never waited for the bulk
     // copy.  The CTA must not retire while the copy engine may still write into its shared memory: the issuing thread
     // waits for the barrier's phase here (immediate when it already waited above).

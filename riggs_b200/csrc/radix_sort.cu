@@ -224,18 +224,31 @@ static bool use_cub_sort() {
     return v;
 }
 
+// Zeroes the sort's control words and returns the address of its four digit histograms, for a producer of the keys that
+// counts the digits itself while it has them in registers (the fused preprocess kernel): the sort then starts with its
+// first pass instead of a histogram launch.  Null when the library sort is selected (it counts for itself).
+uint32_t* depth_sort_prepare(char* temp, int P, cudaStream_t stream) {
+    if (P <= 0 || use_cub_sort() || P >= (1 << 30)) return nullptr;
+    const size_t tiles = ((size_t)P + kSortTile - 1) / kSortTile;
+    SortCtl c = sort_ctl(temp, tiles);
+    if (cudaMemsetAsync(temp, 0, c.words * 4, stream) != cudaSuccess) return nullptr;
+    return c.hist;
+}
+
 int launch_depth_sort(char* temp, size_t temp_bytes, const float* depths, uint32_t* keys_out, const uint32_t* ids_in,
-                      uint32_t* ids_out, int P, cudaStream_t stream) {
+                      uint32_t* ids_out, int P, cudaStream_t stream, bool hist_ready) {
     if (P <= 0) return 0;
     if (use_cub_sort() || P >= (1 << 30)) return launch_depth_sort_cub(temp, temp_bytes, depths, keys_out, ids_in, ids_out, P, stream);
-    LaunchScope ls("depth_sort", stream, 1 + kSortPasses);
+    LaunchScope ls("depth_sort", stream, (hist_ready ? 0 : 1) + kSortPasses);
     const size_t tiles = ((size_t)P + kSortTile - 1) / kSortTile;
     SortCtl c = sort_ctl(temp, tiles);
     uint32_t* tmp_keys = reinterpret_cast<uint32_t*>(temp + align_up(c.words * 4, 256));
     uint32_t* tmp_ids = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(tmp_keys) + align_up((size_t)P * 4, 256));
-    if (cudaMemsetAsync(temp, 0, c.words * 4, stream) != cudaSuccess) { set_error("depth sort: memset failed"); return -1; }
     const uint32_t* keys = reinterpret_cast<const uint32_t*>(depths);
-    sort_hist_kernel<<<std::min<int>((int)((P + 2047) / 2048), RG_NUM_SMS * 2), 256, 0, stream>>>(keys, P, c.hist);
+    if (!hist_ready) {
+        if (cudaMemsetAsync(temp, 0, c.words * 4, stream) != cudaSuccess) { set_error("depth sort: memset failed"); return -1; }
+        sort_hist_kernel<<<std::min<int>((int)((P + 2047) / 2048), RG_NUM_SMS * 2), 256, 0, stream>>>(keys, P, c.hist);
+    }
     // depths -> tmp -> out -> tmp -> out
     const uint32_t* kin = keys;
     const uint32_t* vin = nullptr;
