@@ -552,9 +552,9 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full, C0 on one B200 (profiles/)
-NCU_TRAFFIC = {"blend_backward": 17084416, "blend_forward": 14722304, "gauss_skin_backward": 122528256,
-               "skin_preprocess": 78285056}
+# dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full, C0 on one B200 (profiles/r2_r_full_raw.csv)
+NCU_TRAFFIC = {"blend_backward": 17107968, "blend_forward": 14824192, "gauss_skin_backward": 130815488,
+               "skin_preprocess": 79057408, "tile_scatter": 18270976, "tile_count": 6019840}
 
 
 def peer_copy_bandwidth(hp, dev, iters=10):

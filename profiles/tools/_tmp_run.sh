@@ -1,8 +1,6 @@
-python -m pytest tests/test_gpu_fused.py tests/test_gpu_fullsize.py tests/test_gpu_raster.py -m gpu -q -x 2>&1 | tail -4
-python bench.py --steps 40 --warmup 5 --no-cpu-baseline --no-ref-cuda > gpurun_out/r2n_bench.json 2> gpurun_out/r2n_bench.err; echo rc=$?
-python - <<PY
-import json
-d=json.loads(open("gpurun_out/r2n_bench.json").read().strip().splitlines()[-1])
-print(d["value"], d["ms_per_step"], d["e2e"]["value"], d["gpu_launches"])
-print({k:v["ms_per_launch"] for k,v in d["kernels"].items()})
-PY
+CMD="python bench.py --steps 2 --warmup 3 --no-graph --no-cpu-baseline --no-ref-cuda"
+$CMD > gpurun_out/r2r_plain.log 2>&1 && \
+ncu --metrics gpu__time_duration.sum --clock-control none -s 100 -c 300 --csv --log-file gpurun_out/r2r_launches.csv $CMD > gpurun_out/r2r_ncu1.log 2>&1
+echo "launch list rc=$?"
+ncu --set full --clock-control none --import-source on -k regex:"blend_backward|blend_forward|gauss_backward|preprocess_kernel|tile_scatter|tile_count|sort_pass" -s 14 -c 11 -o gpurun_out/r2r_full $CMD > gpurun_out/r2r_ncu2.log 2>&1
+echo "full rc=$?"; ls -la gpurun_out/r2r_*
