@@ -45,7 +45,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=WORKLOAD)
-    ap.add_argument("--mode", default="train", choices=["train", "sequence"],
+    ap.add_argument("--mode", default="train", choices=["train", "sequence", "split"],
                     help="train: fwd+bwd steps (default); sequence: forward-only novel-pose frame sequence (C5)")
     ap.add_argument("--views-per-step", type=int, default=0,
                     help="global views per optimiser step, sharded over the ranks and accumulated per rank "
@@ -163,6 +163,9 @@ def views_of_rank(rank, world, vps, n_views=N_VIEWS):
 
 
 def workload_string(name, scene, W, H, args, world):
+    if args.mode == "split":
+        return (f"{name}: {scene.N} Gaussians, {scene.J}-joint skeleton, {W}x{H}, ONE view per step rendered by all the GPUs "
+                f"together (tile rows interleaved), fwd+bwd and forward only")
     if args.mode == "sequence":
         return (f"{name}: {scene.N} Gaussians, {scene.J}-joint skeleton, {W}x{H}, {len(scene.poses)}-frame novel-pose sequence, "
                 f"forward only, frames sharded over the GPUs")
@@ -207,6 +210,8 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
     if args.mode == "sequence":
         return run_sequence(args, rank, world, dev)
+    if args.mode == "split":
+        return run_split(args, rank, world, dev)
 
     V = args.views_per_step
     if V > 0 and V % world:
@@ -739,6 +744,212 @@ def run_sequence(args, rank, world, dev):
     }
     if per_rank_ms is not None:
         line["per_rank_ms_per_frame"] = per_rank_ms
+    _emit(line)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_split(args, rank, world, dev):
+    """Latency of ONE view when all the GPUs work on it (dist.ViewSplit): the training step (fwd + L1 + bwd; every rank
+    ends with the full gradients, no gradient all-reduce) and the forward-only frame.  `value` = steps/s of the whole job
+    (one view per step, whatever N is: strong scaling)."""
+    import torch
+    import torch.distributed as dist
+    from riggs_b200 import _lib
+    from riggs_b200.hotpath import HotPath, PoseSequenceRenderer, RotatingSteps
+
+    scene = make_scene(args.workload, args.isotropic)
+    hp = HotPath(scene, device=dev, fused=True)
+    H, W = scene.cameras[0].image_height, scene.cameras[0].image_width
+    order = list(range(N_VIEWS))
+    g = torch.Generator().manual_seed(1000)
+    targets_host = [torch.rand(3, H, W, generator=g).pin_memory() for _ in range(N_VIEWS)]
+    cams = [scene.cameras[i].to(dev) for i in order]
+    targets = [t.to(dev) for t in targets_host]
+    poses_host = [{k: v.clone().pin_memory() for k, v in scene.poses[i].items()} for i in order]
+    poses = [{k: v.to(dev) for k, v in p.items()} for p in poses_host]
+    params = hp.parameters()
+
+    def eager(i, split):
+        old, hp.split = hp.split, split
+        try:
+            hp.zero_grad()
+            pose = {k: v.detach().clone().requires_grad_(True) for k, v in poses[i].items()}
+            out = hp.forward(cams[i], pose)
+            from riggs_b200.loss_utils import l1_loss_and_grad
+            loss, grad = l1_loss_and_grad(out["render"], targets[i])
+            out["render"].backward(grad)
+            torch.cuda.synchronize()
+            # nothing that carries a grad_fn leaves this function: an autograd graph kept alive breaks the later captures
+            res = {k: out[k].detach().clone() for k in ("render", "depth", "alpha", "radii")}
+            return res, [p.grad.clone() for p in params] + [pose["local_rotation"].grad.clone()], int(out["status"][0])
+        finally:
+            hp.split = old
+
+    # ---- the split view against the same view rendered by this rank alone, once, outside the timed regions ----
+    split = hp.enable_view_split(W, H)
+    checked = None
+    if split is not None:
+        hp.split = None
+        whole, g_whole, n_whole = eager(0, None)
+        _, g_whole2, _ = eager(0, None)
+        part, g_part, n_part = eager(0, split)
+        rel = lambda x, y: max(float((a - b).abs().max() / b.abs().max().clamp_min(1e-30)) for a, b in zip(x, y))
+        spread = rel(g_whole2, g_whole)  # the unsplit step against itself: float atomics land in another order every run
+        same = all(bool(torch.equal(part[k], whole[k])) for k in ("render", "depth", "alpha", "radii"))
+        err = rel(g_part, g_whole)
+        chk = g_part[0].clone()
+        dist.broadcast(chk, src=0)
+        identical = bool(torch.equal(chk, g_part[0]))  # replicated backward on bit-identical sums: same bits on every rank
+        cnt = torch.tensor([n_part], device=dev)
+        dist.all_reduce(cnt)
+        ok = same and err <= min(max(5e-5, 4.0 * spread), 1e-3) and int(cnt[0]) == n_whole
+        t_ok = torch.tensor([int(ok)], device=dev)
+        dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
+        checked = {"ok": bool(int(t_ok[0])), "image_bit_identical_to_unsplit": same, "max_grad_rel_err_vs_unsplit": err,
+                   "unsplit_run_to_run_rel_err": spread, "gradients_identical_on_all_ranks": identical, "instances_unsplit": n_whole, "instances_this_rank": n_part,
+                   "peer_memory": split.images.hdl is not None}
+        if not checked["ok"]:
+            raise SystemExit(f"rank {rank}: split view disagrees with the unsplit view: {checked}")
+        hp.split = split
+        del whole, part, g_whole, g_part, g_whole2
+    hp.zero_grad()
+
+    rot = RotatingSteps(hp, cams, poses, targets, views_per_step=1, warmup=2)
+    L = _lib.lib()
+    clocks = ClockSampler(dev.index or 0) if rank == 0 else None
+    for _ in range(max(args.warmup, 3) + 3):
+        rot.step()
+    torch.cuda.synchronize()
+    if clocks is not None:
+        t_wait = time.time()
+        while not clocks.rows and time.time() - t_wait < 5.0:
+            time.sleep(0.05)
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    t0 = time.time()
+    e0.record()
+    for _ in range(args.steps):
+        rot.step()
+    e1.record()
+    torch.cuda.synchronize()
+    t1 = time.time()
+    if world > 1:
+        dist.barrier()
+    ms = e0.elapsed_time(e1)
+    clk = clocks.stop(t0, t1) if clocks else None
+    overflowed = bool(rot.overflowed)
+
+    # per-kernel durations (eager pass)
+    L.rg_profile_reset()
+    L.rg_profile_enable(1)
+    for i in range(args.steps):
+        eager(i % N_VIEWS, hp.split)
+    torch.cuda.synchronize()
+    L.rg_profile_enable(0)
+    prof = _lib.profile_read()
+    L.rg_profile_reset()
+
+    # forward only: the same views as a frame sequence (graph replay, all ranks on every frame)
+    seq = PoseSequenceRenderer(hp, cams[0], scene.J, max_frames=N_VIEWS)
+    seq.load(torch.stack([p["local_rotation"] for p in poses]), torch.stack([p["global_trans"] for p in poses]))
+    n_fr = max(args.steps, N_VIEWS) // N_VIEWS * N_VIEWS
+    for _ in range(N_VIEWS):
+        seq.render_next()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s0.record()
+    for f in range(n_fr):
+        if f % N_VIEWS == 0:
+            seq.rewind()
+        seq.render_next()
+    s1.record()
+    torch.cuda.synchronize()
+    ms_fwd = s0.elapsed_time(s1) / n_fr
+
+    # end to end: pose and target from pinned host memory every step, the loss read back
+    from riggs_b200.hotpath import PipelinedSteps
+    pipe = PipelinedSteps(hp, cams[0], poses[0], targets[0], warmup=2, pool=rot.pool)
+    for i in range(2):
+        pipe.feed(None, poses_host[i], targets_host[i])
+        pipe.result(pipe.launch())
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    pipe.feed(None, poses_host[0], targets_host[0])
+    last = 0.0
+    for it in range(args.steps):
+        pipe.launch()
+        if it + 1 < args.steps:
+            pipe.feed(None, poses_host[(it + 1) % N_VIEWS], targets_host[(it + 1) % N_VIEWS])
+        if it > 0:
+            last = pipe.result(it - 1)
+    last = pipe.result(args.steps - 1)
+    f1.record()
+    torch.cuda.synchronize()
+    ms_e2e = f0.elapsed_time(f1)
+    per_rank = None
+    if world > 1:
+        mine = torch.tensor([ms / args.steps], device=dev)
+        allms = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allms, mine)
+        per_rank = [round(float(x), 4) for x in allms]
+        t = torch.tensor([ms, ms_e2e, ms_fwd], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, ms_e2e, ms_fwd = float(t[0]), float(t[1]), float(t[2])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    P = scene.N
+    peaks = load_peaks()
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    kern = {k: {"ms_per_launch": v[0] / max(v[1], 1), "launches": v[1], "ms_per_step": v[0] / args.steps} for k, v in prof.items()}
+    dom = max(kern, key=lambda k: kern[k]["ms_per_step"]) if kern else None
+    in_P = 236 - (8 if args.isotropic else 0)
+    R = checked["instances_unsplit"] if checked else int(rot.slots[0]._ws.status[0])
+    per, total_bytes, own_bytes = algorithmic_bytes(P, R, H * W, in_P=in_P)
+    roof = None
+    if dom:
+        # a rank's blend / binning kernels see 1/N of the instances and pixels; the per-Gaussian kernels all of P
+        shard = world if dom in ("blend_backward", "blend_forward", "tile_scatter") else 1
+        b = per.get(dom, 0) // shard
+        if dom.startswith("allreduce"):
+            b = (10 * P + 5 * H * W) * 4 // 2  # mean of the two sums' payloads per launch
+        ach = b / (kern[dom]["ms_per_launch"] * 1e-3) / 1e9
+        roof = {"kernel": dom, "bound": "hbm", "achieved": round(ach, 2), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4),
+                "traffic": None, "algorithmic_bytes_per_launch": b, "ms_per_launch": round(kern[dom]["ms_per_launch"], 4),
+                "peak_source": "measured" if "hbm_gbs" in peaks else "fallback"}
+    step_ms = ms / args.steps
+    line = {
+        "metric": METRIC, "value": round(args.steps / (ms / 1e3), 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": round(step_ms, 4), "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_string(args.workload, scene, W, H, args, world), "P": P, "R": R, "HW": H * W,
+                   "views": f"{N_VIEWS} resident views visited round-robin", "launch": "cuda graph replay",
+                   "l2": "no explicit flush: the view changes every step and a step reads the parameters and writes their gradients once",
+                   "parallelism": (f"one view over {world} GPUs: tile row y on GPU y % {world}; skin / project / depth sort and the "
+                                   f"per-Gaussian backward replicated; two in-graph sums per step (image rows {5 * H * W * 4 >> 10} KB, "
+                                   f"per-Gaussian screen-space accumulators {10 * P * 4 >> 10} KB); no gradient all-reduce")
+                   if world > 1 else "single GPU"},
+        "forward_only_ms_per_frame": round(ms_fwd, 4),
+        "e2e": {"value": round(args.steps / (ms_e2e / 1e3), 3), "unit": UNIT,
+                "h2d_bytes_per_step": int(targets_host[0].numel() * 4 + sum(v.numel() * 4 for v in poses_host[0].values())),
+                "d2h_bytes_per_step": 4, "last_loss": float(last)},
+        "gpu_launches": int(rot.launches_per_replay * args.steps), "clocks": clk, "roofline": roof,
+        "kernels": {k: {kk: round(vv, 4) if isinstance(vv, float) else vv for kk, vv in v.items()} for k, v in kern.items()},
+        "instance_buffer_overflowed": overflowed,
+    }
+    if checked is not None:
+        line["split_checked"] = checked
+    if per_rank is not None:
+        line["per_rank_ms_per_step"] = per_rank
     _emit(line)
     if world > 1:
         dist.destroy_process_group()

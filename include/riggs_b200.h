@@ -87,7 +87,9 @@ int rg_mark_visible(int P, const float* means3D, const float* viewmatrix, const 
  * out[2]=means2D f32x2[P]         out[3]=conic_opacity f32x4[P]      out[4]=splat records f32x16[P] (rgb at 8..10)
  * out[5]=tiles_touched u32[P]     out[6]=ids in depth order u32[P]   out[7]=means3D f32[3P] (fused entry only)
  * out[8]=point_list u32[R]        out[9]=n_contrib u32[H*W]          out[10]=ranges u32x2[tiles]
- * out[11]=status u32[2]: num_rendered, overflow flag */
+ * out[11]=status u32[2]: num_rendered, overflow flag
+ * out[12]=the backward's per-Gaussian screen-space accumulators f32[10P] (mean2D.xy, conic.xyw, opacity, colour.rgb,
+ *         depth), array-major: zeroed and filled by phase 1 of rg_skinned_backward_part, read by phase 2 */
 int rg_state_ptrs(int P, int64_t R, int width, int height, char* geom_buffer, char* binning_buffer,
                   char* image_buffer, void** out /* host, 12 entries */);
 
@@ -267,6 +269,12 @@ typedef struct RgSkinnedScene {
     const float *viewmatrix, *projmatrix, *campos, *background;
     int blend_mode;             /* 0: linear blend skinning (skeleton_utils/skeleton_warp.py:149-150, what the reference runs);
                                    1: the bone transforms blended as dual quaternions (utils/dual_quaternion.py:135-180) */
+    int split_index, split_count; /* one view rendered by split_count GPUs (last bullet; no counterpart
+                                   in the reference): with split_count > 1 this call bins and blends only the 16-pixel tile
+                                   rows y with y % split_count == split_index -- pixels of other rows are left untouched in
+                                   out_color / out_depth / out_alpha -- and phase 1 of the backward adds only those rows'
+                                   share to the per-Gaussian screen-space accumulators (out[12] of rg_state_ptrs), which the
+                                   caller sums over the GPUs before phases 2 and 4.  0 or 1: the whole image. */
 } RgSkinnedScene;
 
 /* Caller-owned device scratch, reused across frames; nothing is allocated and the host never waits.

@@ -28,7 +28,7 @@ class RgSkinnedScene(C.Structure):
                                            "features_rest", "motion_mask", "mlp_weight", "offsets", "joints", "parents",
                                            "node_radius_raw", "local_rot", "global_trans", "viewmatrix", "projmatrix",
                                            "campos", "background")] +
-                [("blend_mode", C.c_int)])
+                [("blend_mode", C.c_int), ("split_index", C.c_int), ("split_count", C.c_int)])
 
 
 class RgAdamGroup(C.Structure):

@@ -257,7 +257,7 @@ int rg_state_ptrs(int P, int64_t R, int width, int height, char* geom_buffer, ch
         out[8] = nullptr;
     }
     ImageState im = ImageState::carve(aligned_base(image_buffer), width, height, nullptr);
-    out[9] = im.n_contrib; out[10] = im.ranges; out[11] = g.status;
+    out[9] = im.n_contrib; out[10] = im.ranges; out[11] = g.status; out[12] = g.grad_acc;
     return 0;
 }
 

@@ -40,6 +40,10 @@ int check_scene(const RgSkinnedScene* s, const RgWorkspace* w, const char* who) 
     }
     if (w->binning_bytes < 1024) { set_error(std::string(who) + ": workspace binning buffer too small"); return -1; }
     if (s->blend_mode != 0 && s->blend_mode != 1) { set_error(std::string(who) + ": blend_mode must be 0 (linear) or 1 (dual quaternion)"); return -1; }
+    if (s->split_count < 0 || (s->split_count > 1 && (s->split_index < 0 || s->split_index >= s->split_count))) {
+        set_error(std::string(who) + ": split_index must lie in [0, split_count)");
+        return -1;
+    }
     return 0;
 }
 
@@ -101,15 +105,17 @@ int rg_skinned_forward(const RgSkinnedScene* s, const RgWorkspace* w, float* out
     if (launch_depth_sort(geom.sort_temp, geom.sort_temp_bytes, geom.depths, geom.sorted_keys, geom.ids, geom.sorted_ids, P, stream,
                           pa.sort_hist != nullptr))
         return -1;
-    if (launch_tile_count(bp, P, grid_x, grid_y, geom.sorted_ids, geom.tiles_touched, geom.means2D, radii, geom.rects, geom.M, geom.Mg, stream))
+    const int split_n = s->split_count > 1 ? s->split_count : 1, split_i = split_n > 1 ? s->split_index : 0;
+    if (launch_tile_count(bp, P, grid_x, grid_y, geom.sorted_ids, geom.tiles_touched, geom.means2D, radii, geom.rects, geom.M, geom.Mg, stream,
+                          split_i, split_n))
         return -1;
     // nobody reads num_rendered on the host here, so the prefix over the tiles rides along with the column scans
     launch_tile_offsets_a(bp, geom.Mg, geom.S, geom.tile_base, img.ranges, geom.tile_order, geom.status, cap, stream, false);
     launch_tile_scatter(bp, P, grid_x, grid_y, geom.sorted_ids, geom.rects, geom.M, geom.Mg, geom.S,
-                        geom.tile_base, geom.E, bin.point_list, cap, stream, true, img.ranges, geom.tile_order, geom.status);
+                        geom.tile_base, geom.E, bin.point_list, cap, stream, true, img.ranges, geom.tile_order, geom.status, split_n);
 
     BlendFwdArgs fa;
-    fa.W = W; fa.H = H; fa.grid_x = grid_x; fa.grid_y = grid_y;
+    fa.W = W; fa.H = H; fa.grid_x = grid_x; fa.grid_y = grid_y; fa.split_i = split_i; fa.split_n = split_n;
     cudaMemsetAsync(bin.surv_mask, 0, bin.surv_mask_bytes, stream);
     fa.ranges = img.ranges; fa.point_list = bin.point_list; fa.surv_mask = bin.surv_mask; fa.surv_stride = bin.surv_stride; fa.rec = geom.rec; fa.tile_order = geom.tile_order;
     fa.bg = s->background;
@@ -158,6 +164,7 @@ int rg_skinned_backward_part(const RgSkinnedScene* s, const RgWorkspace* w, int 
 
         BlendBwdArgs ba;
         ba.P = P; ba.W = W; ba.H = H; ba.grid_x = grid_x; ba.grid_y = grid_y;
+        ba.split_n = s->split_count > 1 ? s->split_count : 1; ba.split_i = ba.split_n > 1 ? s->split_index : 0;
         ba.ranges = img.ranges; ba.point_list = bin.point_list; ba.surv_mask = bin.surv_mask; ba.surv_stride = bin.surv_stride;
         ba.bg = s->background;
         ba.rec = geom.rec; ba.tile_order = geom.tile_order; ba.alphas = alphas;

@@ -55,7 +55,10 @@ int launch_depth_sort_cub(char* temp, size_t temp_bytes, const float* depths, ui
 // each tile of its rectangle (two 16-bit counters per shared-memory word, a chunk holds at most 65535 Gaussians so a
 // half never carries into its neighbour).  Rectangles of more than kWideRect tiles are left to the whole warp.
 constexpr uint32_t kWideRect = 48;
+// split_n > 1: only the tile rows y with y % split_n == split_i are binned (one view rendered by several GPUs, each
+// owning every split_n-th tile row); a rectangle then keeps its owned rows, split_n rows apart.
 __global__ void __launch_bounds__(256) tile_count_kernel(int P, int T, int NW, int L, int grid_x, int grid_y,
+                                                         int split_i, int split_n,
                                                          const uint32_t* __restrict__ sorted_ids,
                                                          const uint32_t* __restrict__ tiles_touched,
                                                          const float2* __restrict__ means2D, const int* __restrict__ radii,
@@ -78,11 +81,19 @@ __global__ void __launch_bounds__(256) tile_count_kernel(int P, int T, int NW, i
             const uint32_t id = sorted_ids[i];
             cnt = tiles_touched[id];
             if (cnt > 0) tile_rect(means2D[id], radii[id], rmin, rmax, grid_x, grid_y);
+            uint32_t rows = rmax.y - rmin.y;
+            if (split_n > 1 && cnt > 0) {  // first owned row at or below rmin.y, and how many owned rows the rectangle holds
+                const uint32_t y0 = rmin.y + ((uint32_t)(split_i + split_n) - rmin.y % (uint32_t)split_n) % (uint32_t)split_n;
+                rows = y0 < rmax.y ? (rmax.y - y0 + (uint32_t)split_n - 1) / (uint32_t)split_n : 0u;
+                rmin.y = y0;
+                cnt = rows * (rmax.x - rmin.x);
+                if (rows == 0) rmax.x = rmin.x;
+            }
             // kept for the scatter pass, which then reads one packed word pair per Gaussian in depth order
-            rects[i] = make_uint2(rmin.y * (uint32_t)grid_x + rmin.x, (rmax.x - rmin.x) | ((rmax.y - rmin.y) << 16));
+            rects[i] = make_uint2(rmin.y * (uint32_t)grid_x + rmin.x, (rmax.x - rmin.x) | (rows << 16));
         }
         if (cnt > 0 && cnt <= kWideRect) {
-            for (uint32_t y = rmin.y; y < rmax.y; y++) {
+            for (uint32_t y = rmin.y; y < rmax.y; y += (uint32_t)split_n) {
                 const uint32_t row = y * (uint32_t)grid_x;
                 for (uint32_t x = rmin.x; x < rmax.x; x++) {
                     const uint32_t t = row + x;
@@ -99,7 +110,7 @@ __global__ void __launch_bounds__(256) tile_count_kernel(int P, int T, int NW, i
             const float rw = __frcp_rn((float)w);  // s / w through a reciprocal, exact here (see tile_scatter_kernel)
             for (uint32_t s = lane; s < n; s += 32) {
                 const uint32_t q = __float2uint_rz(((float)s + 0.5f) * rw);
-                const uint32_t t = (y0 + q) * (uint32_t)grid_x + x0 + (s - q * w);
+                const uint32_t t = (y0 + q * (uint32_t)split_n) * (uint32_t)grid_x + x0 + (s - q * w);
                 atomicAdd(&h32[t >> 1], 1u << ((t & 1u) * 16u));
             }
         }
@@ -263,6 +274,7 @@ __global__ void __launch_bounds__(1024) col_scan_kernel(int T, int Tpad, int NW,
 // distinct, so its lanes read, use and bump the per-tile cursors without any ranking among themselves, and the
 // order between Gaussians is the order of the loop.  (The earlier walk of 32 instances of mixed Gaussians per step
 // needed a MATCH.ANY per step to rank equal tiles: 36 % of that kernel's stall samples.)
+// grid_x here is the distance between two rows of a rectangle: the grid's width, times split_n for a split view
 __global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int T, int NW, int L, int grid_x,
                                                            const uint32_t* __restrict__ sorted_ids,
                                                            const uint2* __restrict__ rects, const uint16_t* __restrict__ M,
@@ -372,7 +384,8 @@ BinPlan make_bin_plan(int P, int T) {
 
 int launch_tile_count(const BinPlan& b, int P, int grid_x, int grid_y, const uint32_t* sorted_ids,
                       const uint32_t* tiles_touched, const float2* means2D, const int* radii, uint2* rects, uint16_t* M,
-                      uint16_t* Mg, cudaStream_t stream) {
+                      uint16_t* Mg, cudaStream_t stream, int split_i, int split_n) {
+    if (split_n < 1) split_n = 1;
     if (b.wpc < 1 || (size_t)b.L * b.wpc > 65535 || b.T > 65535 || grid_x > 65535 || grid_y > 65535) {
         set_error("binning: image has too many tiles (or chunk too long) for the shared-memory tile counters");
         return -1;
@@ -382,7 +395,7 @@ int launch_tile_count(const BinPlan& b, int P, int grid_x, int grid_y, const uin
         ensure_dyn_smem(reinterpret_cast<const void*>(tile_scatter_kernel), 220 * 1024))
         return -1;
     LaunchScope ls("tile_count", stream);
-    tile_count_kernel<<<b.NG, b.wpc * 32, smem, stream>>>(P, b.T, b.NW, b.L, grid_x, grid_y, sorted_ids, tiles_touched, means2D,
+    tile_count_kernel<<<b.NG, b.wpc * 32, smem, stream>>>(P, b.T, b.NW, b.L, grid_x, grid_y, split_i, split_n, sorted_ids, tiles_touched, means2D,
                                                         radii, rects, M, Mg);
     return 0;
 }
@@ -401,12 +414,12 @@ int launch_tile_scatter(const BinPlan& b, int P, int grid_x, int grid_y, const u
                         const uint2* rects, const uint16_t* M, const uint16_t* Mg,
                         const uint32_t* S, uint32_t* tile_base, uint32_t* E, uint32_t* point_list,
                         uint32_t capacity, cudaStream_t stream, bool base_pending, uint2* ranges, uint32_t* tile_order,
-                        uint32_t* status) {
+                        uint32_t* status, int split_n) {
     LaunchScope ls("tile_scatter", stream, 2);
     dim3 g((b.T + 1023) / 1024, b.nseg + (base_pending ? 1 : 0));
     col_scan_kernel<<<g, 1024, 0, stream>>>(b.T, b.Tpad, b.NG, b.nseg, Mg, S, E, tile_base, ranges, tile_order, status, capacity);
     const size_t smem = (size_t)b.Tpad * 4 + (size_t)b.wpc * b.Tpad * 2;
-    tile_scatter_kernel<<<b.NG, b.wpc * 32, smem, stream>>>(P, b.T, b.NW, b.L, grid_x, sorted_ids, rects, M, E, tile_base,
+    tile_scatter_kernel<<<b.NG, b.wpc * 32, smem, stream>>>(P, b.T, b.NW, b.L, grid_x * (split_n > 1 ? split_n : 1), sorted_ids, rects, M, E, tile_base,
                                                           point_list, capacity);
     return 0;
 }

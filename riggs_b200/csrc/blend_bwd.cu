@@ -123,6 +123,7 @@ __global__ void __launch_bounds__(kBlendWarps * 32, RG_BWD_MINBLK) blend_backwar
     const int tile = (int)a.tile_order[blockIdx.x / kCtasPerTile];
     const int blk = (blockIdx.x % kCtasPerTile) * kBlendWarps + warp;  // 8x4 block of the tile: 2 across, 4 down
     const int tile_x = tile % a.grid_x, tile_y = tile / a.grid_x;
+    if (a.split_n > 1 && tile_y % a.split_n != a.split_i) return;  // another GPU's tile row: its n_contrib was never written here
     const int bx0 = (blk & 1) * kBlkW, by0 = (blk >> 1) * kBlkH;
     const uint2 pix = {(unsigned)(tile_x * RG_TILE + bx0 + (lane & 7)), (unsigned)(tile_y * RG_TILE + by0 + (lane >> 3))};
     const uint32_t pix_id = a.W * pix.y + pix.x;

@@ -110,7 +110,7 @@ int launch_depth_sort(char* temp, size_t temp_bytes, const float* depths, uint32
 uint32_t* depth_sort_prepare(char* temp, int P, cudaStream_t stream);  // see radix_sort.cu
 int launch_tile_count(const BinPlan& b, int P, int grid_x, int grid_y, const uint32_t* sorted_ids,
                       const uint32_t* tiles_touched, const float2* means2D, const int* radii, uint2* rects, uint16_t* M,
-                      uint16_t* Mg, cudaStream_t stream);
+                      uint16_t* Mg, cudaStream_t stream, int split_i = 0, int split_n = 1);  // split: see tile_count_kernel
 // segment sums + tile bases + ranges + tile launch order (longest lists first) + status[0] = num_rendered, status[1] = overflow flag
 int launch_tile_offsets_a(const BinPlan& b, const uint16_t* Mg, uint32_t* S, uint32_t* tile_base, uint2* ranges,
                           uint32_t* tile_order, uint32_t* status, uint32_t capacity, cudaStream_t stream, bool with_base = true);
@@ -118,12 +118,13 @@ int launch_tile_scatter(const BinPlan& b, int P, int grid_x, int grid_y, const u
                         const uint2* rects, const uint16_t* M, const uint16_t* Mg,
                         const uint32_t* S, uint32_t* tile_base, uint32_t* E, uint32_t* point_list,
                         uint32_t capacity, cudaStream_t stream, bool base_pending = false, uint2* ranges = nullptr,
-                        uint32_t* tile_order = nullptr, uint32_t* status = nullptr);
+                        uint32_t* tile_order = nullptr, uint32_t* status = nullptr, int split_n = 1);
 int launch_rebuild_keys(int T, const uint2* ranges, const uint32_t* point_list, const float* depths, uint64_t* keys,
                         cudaStream_t stream);
 
 struct BlendFwdArgs {
     int W, H, grid_x, grid_y;
+    int split_i = 0, split_n = 1;  // split_n > 1: tile rows with y % split_n != split_i belong to another GPU and are left untouched
     const uint2* ranges;
     const uint32_t* point_list;
     const float4* rec;  // packed splat records (cull.cuh)
@@ -141,6 +142,7 @@ int launch_blend_forward(const BlendFwdArgs& a, cudaStream_t stream);
 
 struct BlendBwdArgs {
     int P, W, H, grid_x, grid_y;
+    int split_i = 0, split_n = 1;
     const uint2* ranges;
     const uint32_t* point_list;
     const float* bg;

@@ -111,7 +111,7 @@ def mark_visible(means3D, viewmatrix, projmatrix):
 def state_ptrs(P, R, W, H, geomBuffer, binningBuffer, imageBuffer):
     """Test/debug helper: device addresses of the arrays inside the three opaque state buffers."""
     import ctypes as C
-    out = (C.c_void_p * 12)()
+    out = (C.c_void_p * 13)()
     _lib.lib().rg_state_ptrs(P, int(R), W, H, ptr(geomBuffer), ptr(binningBuffer), ptr(imageBuffer), out)
     return [int(v) if v else 0 for v in out]
 

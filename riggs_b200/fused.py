@@ -111,15 +111,25 @@ class _Lease:
         self.release()
 
 
-def _scene_struct(P, J, sh_degree, M_rest, isotropic, zero_d_rot, W, H, tfx, tfy, scale_mod, t, blend_mode=0):
+def _scene_struct(P, J, sh_degree, M_rest, isotropic, zero_d_rot, W, H, tfx, tfy, scale_mod, t, blend_mode=0, split=None):
     s = _lib.RgSkinnedScene()
     s.blend_mode = int(blend_mode)
+    if split is not None and split.count > 1:
+        s.split_index, s.split_count = split.index, split.count
     s.P, s.J, s.sh_degree, s.M_rest = P, J, sh_degree, M_rest
     s.isotropic, s.zero_d_rotation, s.width, s.height = int(isotropic), int(zero_d_rot), W, H
     s.tan_fovx, s.tan_fovy, s.scale_modifier = tfx, tfy, scale_mod
     for name, ten in t.items():
         setattr(s, name, ptr(ten))
     return s
+
+
+def _grad_acc_view(ws, P, W, H) -> torch.Tensor:
+    """The 10 P floats of per-Gaussian screen-space accumulators inside a workspace's geometry buffer (rg_state_ptrs)."""
+    out = (C.c_void_p * 13)()
+    _lib.lib().rg_state_ptrs(P, 0, W, H, ws.geom.data_ptr(), None, ws.image.data_ptr(), out)
+    off = int(out[12]) - ws.geom.data_ptr()
+    return ws.geom[off:off + 40 * P].view(torch.float32)
 
 
 class _SkinnedRender(torch.autograd.Function):
@@ -140,10 +150,19 @@ class _SkinnedRender(torch.autograd.Function):
         isotropic = scaling_raw.shape[-1] == 1
         M_rest = features_rest.shape[1]
         scene = _scene_struct(P, J, cfg["sh_degree"], M_rest, isotropic, cfg["zero_d_rotation"], W, H, cfg["tanfovx"],
-                              cfg["tanfovy"], cfg["scale_modifier"], t, cfg.get("blend_mode", 0))
-        color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
-        depth = torch.empty((1, H, W), dtype=torch.float32, device=dev)
-        alpha = torch.empty((1, H, W), dtype=torch.float32, device=dev)
+                              cfg["tanfovy"], cfg["scale_modifier"], t, cfg.get("blend_mode", 0), cfg.get("split"))
+        split = cfg.get("split")
+        if split is not None and split.count > 1:
+            # one view over several GPUs (dist.ViewSplit): this rank fills its tile rows of a zeroed image ...
+            if (split.P, split.width, split.height) != (P, W, H):
+                raise _lib.RiggsError("render_skinned: the ViewSplit was built for another (P, width, height)")
+            split.images.buf.zero_()
+            color, depth, alpha = split.image_views()
+        else:
+            split = None
+            color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+            depth = torch.empty((1, H, W), dtype=torch.float32, device=dev)
+            alpha = torch.empty((1, H, W), dtype=torch.float32, device=dev)
         radii = torch.empty((P,), dtype=torch.int32, device=dev)
         d_nodes = torch.empty((J, 3), dtype=torch.float32, device=dev)
         dbg = cfg.get("debug_outputs")
@@ -187,6 +206,12 @@ class _SkinnedRender(torch.autograd.Function):
                     continue
                 pool.note_capacity(ws, dev)
                 break
+        if split is not None:
+            # ... and the sum over the ranks' disjoint rows is the whole image, on every rank
+            with torch.cuda.device(dev):
+                split.sum_images()
+            color, depth, alpha = color.clone(), depth.clone(), alpha.clone()
+        ctx.split = split
         ctx.set_materialize_grads(False)  # outputs the loss does not use arrive as None, not as zero-filled images
         ctx.scene_tensors = t  # keeps the contiguous copies alive
         ctx.scene = scene
@@ -254,7 +279,16 @@ class _SkinnedRender(torch.autograd.Function):
                 ptr(d_mean2D), ptr(d_local_rot), ptr(d_trans), ptr(d_radius), ptr(d_mask), ptr(d_mlp), ptr(d_off))
         L = _lib.lib()
         with torch.cuda.device(dev):
-            if red is not None and red.can_overlap(P) and all(n in go for n in red.names):
+            if ctx.split is not None:
+                # blend backward over this rank's tile rows, sum of the per-Gaussian accumulators over the ranks, then the
+                # per-Gaussian and skeleton backward replicated: every rank ends with the full gradients
+                acc = 8 if ctx.accumulate else 0
+                check(L.rg_skinned_backward_part(C.byref(ctx.scene), C.byref(ctx.ws.c), 1, 0, 0, *args, stream_ptr()),
+                      "rg_skinned_backward_part")
+                ctx.split.sum_grad2d(_grad_acc_view(ctx.ws, P, W, H))
+                check(L.rg_skinned_backward_part(C.byref(ctx.scene), C.byref(ctx.ws.c), 6 | acc, 0, P, *args, stream_ptr()),
+                      "rg_skinned_backward_part")
+            elif red is not None and red.can_overlap(P) and all(n in go for n in red.names):
                 # Data parallel: the parameter gradients go straight into the ranks' peer-mapped flat buffer, and the
                 # rows of chunk c are summed over the ranks on a second stream while chunk c+1 is computed here.
                 acc = 8 if ctx.accumulate else 0
@@ -296,7 +330,7 @@ class _SkinnedRender(torch.autograd.Function):
 def render_skinned(viewpoint_camera, pc, skeleton, pose: Dict[str, torch.Tensor], pipe, bg_color: torch.Tensor,
                    scaling_modifier=1.0, mlp_weight=None, offsets=None, zero_d_rotation: Optional[bool] = None,
                    debug_outputs=None, pool: Optional[WorkspacePool] = None, grad_out=None, reduce=None,
-                   accumulate: bool = False):
+                   accumulate: bool = False, split=None):
     """Fused deform + render.  ``pc``: object with the GaussianModel raw tensors (_xyz, _scaling, _rotation, _opacity,
     _features_dc, _features_rest, motion_mask, active_sh_degree); ``skeleton``: riggs_b200 SkeletonWarp (joints,
     parents, _node_radius); ``pose``: {'local_rotation': (J,4), 'global_trans': (3,)}.
@@ -306,6 +340,8 @@ def render_skinned(viewpoint_camera, pc, skeleton, pose: Dict[str, torch.Tensor]
     ranks chunk by chunk while it is still computing later chunks (``FlatGrads.all_reduce`` then has nothing left to do).
     ``accumulate``: the backward ADDS the parameter gradients into ``grad_out`` instead of overwriting them -- the second
     and later views of a multi-view batch (rg_skinned_backward_part, phase bit 8).
+    ``split``: a ``dist.ViewSplit``: this ONE view is rendered by all the ranks together (each bins and blends every
+    count-th tile row; the image and the gradients come out complete and identical on every rank).
     Returns the dict of ``render()`` plus ``d_nodes`` and ``status``: a pinned host tensor {num_rendered, overflow}
     that is valid once the stream has been synchronised (``frame_overflowed``)."""
     xyz = pc._xyz
@@ -325,7 +361,7 @@ def render_skinned(viewpoint_camera, pc, skeleton, pose: Dict[str, torch.Tensor]
                viewmatrix=f32c(viewpoint_camera.world_view_transform), projmatrix=f32c(viewpoint_camera.full_proj_transform),
                campos=f32c(viewpoint_camera.camera_center), bg=f32c(bg_color),
                zero_d_rotation=isotropic if zero_d_rotation is None else zero_d_rotation, debug_outputs=debug_outputs,
-               pool=pool, grad_out=grad_out, reduce=reduce, accumulate=accumulate,
+               pool=pool, grad_out=grad_out, reduce=reduce, accumulate=accumulate, split=split,
                blend_mode=getattr(skeleton, "blend_mode", 0))
     mm = getattr(pc, "_motion_mask", None)
     mask = mm.reshape(-1) if mm is not None else None

@@ -57,6 +57,7 @@ class HotPath:
         self.isotropic = self.pc.use_isotropic_gs
         self.flat = None
         self.pool = None  # fused.WorkspacePool override (GraphedStep keeps a private one)
+        self.split = None  # dist.ViewSplit: every view is rendered by all the ranks together (enable_view_split)
 
     def measure_instances(self, cams, poses, pool) -> int:
         """Renders every (camera, pose) pair once without gradients and sizes `pool`'s instance buffers for the largest
@@ -115,6 +116,19 @@ class HotPath:
         self.flat = FlatGrads(self.named_parameters(), device=self.device)
         return self.flat
 
+    def enable_view_split(self, width: int, height: int, index=None, count=None):
+        """Latency mode: all the ranks render the SAME view, each binning and blending every count-th tile row
+        (dist.ViewSplit).  Images and gradients come out complete and identical on every rank, so there is no flat
+        buffer and no gradient all-reduce; the two sums that replace it (image rows, 10 floats per Gaussian) are part of
+        the forward / backward and of any graph captured around them."""
+        from .dist import ViewSplit
+        if not self.fused:
+            raise ValueError("the view split lives in the fused entry points: HotPath(fused=True)")
+        self.split = ViewSplit(self.pc._xyz.shape[0], width, height, self.device, index=index, count=count)
+        if self.split.count <= 1:
+            self.split = None
+        return self.split
+
     def reduce_grads(self):
         if self.flat is None:
             return
@@ -142,7 +156,7 @@ class HotPath:
             from .fused import render_skinned
             return render_skinned(cam, self.pc, self.warp, pose, self.pipe, self.bg, mlp_weight=mlp_weight,
                                   offsets=offsets, grad_out=self.flat.views if self.flat is not None else None,
-                                  pool=self.pool, accumulate=accumulate,
+                                  pool=self.pool, accumulate=accumulate, split=self.split,
                                   reduce=self.flat if (getattr(self.flat, "overlap", False) and last_view) else None)
         if accumulate:
             raise ValueError("multi-view accumulation needs HotPath(fused=True)")

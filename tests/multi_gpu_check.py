@@ -88,9 +88,71 @@ def main():
         if rank == 0:
             print(json.dumps({"mode": mode, "kernel": "rg_allreduce_ranges", "world": world, "chunks": len(chunks), "ok": bool(int(t[0]))}))
         del flat
+    ok_all = view_split_check(rank, world, dev) and ok_all
     dist.barrier()
     dist.destroy_process_group()
     sys.exit(0 if ok_all else 1)
+
+
+def view_split_check(rank, world, dev) -> bool:
+    """One view rendered by all the ranks together (dist.ViewSplit) against the same view rendered by this rank alone:
+    image, depth, alpha and radii bit-identical on every rank, every gradient within 5e-5 (max norm and L2)."""
+    from riggs_b200 import skeleton_warp as sw, synth
+    from riggs_b200.dist import ViewSplit
+    from riggs_b200.fused import WorkspacePool, render_skinned
+    from riggs_b200.gaussian_renderer import GaussianParams
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import helpers
+
+    class Pipe:
+        debug = False
+        convert_SHs_python = False
+        compute_cov3D_python = False
+
+    os.environ.pop("RG_ALLREDUCE", None)
+    ok_all = True
+    for name in ("small", "C2"):
+        scene = synth.make_config(name, **({"n_views": 1} if name == "C2" else {}))
+        pc = GaussianParams.from_scene(scene, device=dev)
+        warp = sw.SkeletonWarp(scene.joints, scene.parents, scene.node_radius_raw, use_skinning_weight_mlp=False,
+                               use_template_offsets=False, device=dev)
+        cam = scene.cameras[0].to(dev)
+        P, W, H = scene.N, cam.image_width, cam.image_height
+        bg = torch.tensor([0.1, 0.3, 0.2], device=dev)
+        cots = [t.to(dev) for t in synth.seeded_cotangents(H, W)]
+        params = [pc._xyz, pc._scaling, pc._rotation, pc._opacity, pc._features_dc, pc._features_rest, warp._node_radius]
+        pool = WorkspacePool()
+        split = ViewSplit(P, W, H, dev)
+
+        def run(sp):
+            pose = {k: v.to(dev).clone().requires_grad_(True) for k, v in scene.poses[0].items()}
+            out = render_skinned(cam, pc, warp, pose, Pipe(), bg, pool=pool, split=sp)
+            ((out["render"] * cots[0]).sum() + (out["depth"] * cots[1]).sum() + (out["alpha"] * cots[2]).sum()).backward()
+            g = [p.grad.clone() for p in params] + [pose["local_rotation"].grad.clone(), pose["global_trans"].grad.clone(),
+                                                    out["viewspace_points"].grad.clone()]
+            for p in params:
+                p.grad = None
+            torch.cuda.synchronize()
+            return out, g, int(out["status"][0])
+
+        whole, g_whole, n_whole = run(None)
+        for trial in range(2):
+            part, g_part, n_part = run(split)
+            same = all(bool(torch.equal(part[k], whole[k])) for k in ("render", "depth", "alpha", "radii"))
+            errs = [max(helpers.rel_err(a.cpu(), b.cpu()), helpers.rel_l2(a.cpu(), b.cpu())) for a, b in zip(g_part, g_whole)]
+            counts = torch.tensor([n_part], device=dev)
+            dist.all_reduce(counts)
+            ok = same and max(errs) < 5e-5 and int(counts[0]) == n_whole
+            t = torch.tensor([int(ok)], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+            ok_all = ok_all and bool(int(t[0]))
+            if rank == 0:
+                print(json.dumps({"check": "view_split", "config": name, "world": world, "trial": trial,
+                                  "peer_memory": split.images.hdl is not None, "image_bit_identical": same,
+                                  "max_grad_err": max(errs), "instances_whole": n_whole, "instances_sum_of_parts": int(counts[0]),
+                                  "instances_this_rank": n_part, "ok_all_ranks": bool(int(t[0]))}))
+        del split
+    return ok_all
 
 
 if __name__ == "__main__":

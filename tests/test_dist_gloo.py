@@ -68,6 +68,22 @@ def _worker(rank, world, port, out):
         ok = ok and torch.allclose(flat.flat, torch.full_like(flat.flat, float(sum(range(1, world + 1)))))
         m = all_reduce_max_(torch.tensor([float(rank), 5.0 - rank]))
         ok = ok and m.tolist() == [float(world - 1), 5.0]
+        # one view split over the ranks (dist.ViewSplit): rank r owns tile rows y % world == r; the ranks' disjoint image
+        # rows and their shares of the per-Gaussian accumulators are summed in place on every rank
+        from riggs_b200.dist import ViewSplit
+        sp = ViewSplit(P, 64, 48, "cpu")
+        ok = ok and (sp.index, sp.count, sp.emulated) == (rank, world, False)
+        color, depth, alpha = sp.image_views()
+        ok = ok and color.shape == (3, 48, 64) and depth.shape == (1, 48, 64) and alpha.data_ptr() == sp.images.buf[4 * 48 * 64:].data_ptr()
+        rows = (torch.arange(48) // 16) % world == rank
+        sp.images.buf.zero_()
+        color[:, rows] = 1.0 + rank
+        sp.sum_images()
+        want = (1.0 + (torch.arange(48) // 16) % world).float()[None, :, None].expand(3, 48, 64)
+        ok = ok and torch.equal(color, want)
+        acc = torch.full((10 * P,), float(rank + 1))
+        sp.sum_grad2d(acc)
+        ok = ok and torch.equal(acc, torch.full((10 * P,), float(sum(range(1, world + 1)))))
         out[rank] = bool(ok)
     finally:
         dist.destroy_process_group()

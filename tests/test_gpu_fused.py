@@ -613,3 +613,83 @@ def test_fused_dual_quaternion_blending_matches_unfused(over):
     for i, (a, b) in enumerate(zip(g_f, g_u)):
         assert a.shape == b.shape
         assert helpers.rel_err(a.cpu().numpy().reshape(-1), b.cpu().numpy().reshape(-1), floor=1e-9) <= E2E_GRAD_RTOL, i
+
+
+@pytest.mark.parametrize("name,over,count", [("small", dict(soft_mask=True, with_offsets=True), 2), ("small", dict(), 3),
+                                             ("ragged", dict(), 4), ("C2", dict(n_views=1), 8)])
+def test_view_split_emulated(name, over, count):
+    """One view split over `count` parts (dist.ViewSplit; every part bins and blends the tile rows y % count == index),
+    the parts run one after the other on this GPU.  Forward: each part touches only its rows and those rows are
+    BIT-identical to the unsplit frame's (same per-tile lists in the same order), so the parts' sum is the unsplit
+    image; the instance counts add up.  Backward: the sum of the parts' per-Gaussian screen-space accumulators goes
+    through the replicated per-Gaussian + skeleton backward and must give the unsplit gradients (float atomics in
+    another order and `count` partial sums: 5e-5 of the largest entry -- measured 1.8e-5 at C2 over 8 parts -- and 1e-5
+    in L2)."""
+    from riggs_b200.dist import ViewSplit
+    from riggs_b200.fused import WorkspacePool, render_skinned
+    scene, pc, warp, cam = _setup(name, over)
+    P, W, H = scene.N, cam.image_width, cam.image_height
+    bg = torch.tensor([0.1, 0.3, 0.2], device="cuda")
+    cots = [t.cuda() for t in synth.seeded_cotangents(H, W)]
+    params = [pc._xyz, pc._scaling, pc._rotation, pc._opacity, pc._features_dc, pc._features_rest, warp._node_radius]
+
+    def collect(pose, mlp, off, vsp):
+        g = [p.grad.clone() for p in params] + [pose["local_rotation"].grad.clone(), pose["global_trans"].grad.clone(), vsp.grad.clone()]
+        g += [t.grad.clone() for t in (mlp, off) if t is not None]
+        for p in params:
+            p.grad = None
+        return g
+
+    pose, mlp, off = _leafs(scene)
+    pool = WorkspacePool()
+    whole = render_skinned(cam, pc, warp, pose, _Pipe(), bg, mlp_weight=mlp, offsets=off, pool=pool)
+    _loss(whole, cots).backward()
+    g_whole = collect(pose, mlp, off, whole["viewspace_points"])
+    torch.cuda.synchronize()
+    n_whole = int(whole["status"][0])
+
+    splits = [ViewSplit(P, W, H, "cuda", index=k, count=count) for k in range(count)]
+    rows = (torch.arange(H, device="cuda") // 16) % count
+    recorded = {}
+
+    def run(pass_no):
+        pose, mlp, off = _leafs(scene)
+        outs, counts = [], []
+        for sp in splits:
+            if pass_no == 0:
+                sp.exchange = lambda s, acc: recorded.__setitem__(s.index, acc.clone())
+            else:
+                sp.exchange = lambda s, acc: acc.copy_(total)
+            outs.append(render_skinned(cam, pc, warp, pose, _Pipe(), bg, mlp_weight=mlp, offsets=off, pool=pool, split=sp))
+            torch.cuda.synchronize()
+            counts.append(int(outs[-1]["status"][0]))
+        return pose, mlp, off, outs, counts
+
+    pose, mlp, off, outs, counts = run(0)
+    assert sum(counts) == n_whole and max(counts) < n_whole
+    for k, o in enumerate(outs):
+        mine = rows == k
+        for key in ("render", "depth", "alpha"):
+            assert torch.equal(o[key][:, mine], whole[key][:, mine]), (key, k)
+            assert not o[key][:, ~mine].any(), (key, k)
+        assert torch.equal(o["radii"], whole["radii"])
+    # pass 0 records every part's accumulators (its parameter gradients are the part's share only) ...
+    for o in outs:
+        _loss(o, cots).backward()
+    for p in params:
+        p.grad = None
+    assert sorted(recorded) == list(range(count))
+    total = sum(recorded[k] for k in range(count))
+    # ... pass 1 hands every part the sum, as the all-reduce between the ranks does
+    pose, mlp, off, outs, _ = run(1)
+    for k, o in enumerate(outs):
+        _loss(o, cots).backward()
+        g = collect(pose, mlp, off, o["viewspace_points"])
+        pose["local_rotation"].grad = None
+        pose["global_trans"].grad = None
+        for t in (mlp, off):
+            if t is not None:
+                t.grad = None
+        for a, b in zip(g, g_whole):
+            a, b = a.cpu(), b.cpu()
+            assert helpers.rel_err(a, b) < 5e-5 and helpers.rel_l2(a, b) < 1e-5, (k, helpers.rel_err(a, b), helpers.rel_l2(a, b))
