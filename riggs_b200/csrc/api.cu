@@ -27,8 +27,7 @@ int check_launch(const char* what, cudaStream_t stream, bool debug) {
 GeomState GeomState::carve(char* base, size_t P, int W, int H, size_t* bytes) {
     Carver c(base);
     GeomState g;
-    const int T = ((W + RG_TILE - 1) / RG_TILE) * ((H + RG_TILE - 1) / RG_TILE);
-    const BinPlan bp = make_bin_plan((int)P, T);
+    const BinPlan bp = make_bin_plan((int)P, (W + RG_TILE - 1) / RG_TILE, (H + RG_TILE - 1) / RG_TILE);
     g.depths = c.take<float>(P);
     g.clamped = c.take<uint8_t>(P);
     g.means2D = c.take<float2>(P);
@@ -128,7 +127,7 @@ int rg_rasterize_forward(rg_alloc_fn geom_alloc, void* geom_ctx, rg_alloc_fn bin
     if (!gptr || !iptr) { set_error("rg_rasterize_forward: state buffer allocation failed"); return -1; }
     GeomState geom = GeomState::carve(aligned_base(gptr), P, width, height, nullptr);
     ImageState img = ImageState::carve(aligned_base(iptr), width, height, nullptr);
-    const BinPlan bp = make_bin_plan(P, grid_x * grid_y);
+    const BinPlan bp = make_bin_plan(P, grid_x, grid_y);
 
     PreprocessArgs pa;
     pa.P = P; pa.D = D; pa.M = M;

@@ -80,7 +80,7 @@ int rg_skinned_forward(const RgSkinnedScene* s, const RgWorkspace* w, float* out
     const uint32_t cap = rg_binning_capacity(w->binning_bytes);
     BinningState bin = BinningState::carve(abase(w->binning), cap, nullptr);
     FkSlots fk(geom.fk);
-    const BinPlan bp = make_bin_plan(P, grid_x * grid_y);
+    const BinPlan bp = make_bin_plan(P, grid_x, grid_y);
 
     if (launch_fk_forward(1, s->J, s->local_rot, s->global_trans, s->joints, s->parents, fk.G, fk.node_rot,
                           d_nodes ? d_nodes : fk.posed, stream))

@@ -23,6 +23,8 @@
 // same total order as the reference's stable sort on (tile, depth) over id-ordered emission.
 #include <cub/device/device_radix_sort.cuh>
 
+#include <algorithm>
+
 #include "common.cuh"
 #include "kernels.cuh"
 #include "math.cuh"
@@ -54,10 +56,21 @@ int launch_depth_sort_cub(char* temp, size_t temp_bytes, const float* depths, ui
 // Counting needs no order inside a chunk: every lane takes one Gaussian of the chunk and adds one to the counter of
 // each tile of its rectangle (two 16-bit counters per shared-memory word, a chunk holds at most 65535 Gaussians so a
 // half never carries into its neighbour).  Rectangles of more than kWideRect tiles are left to the whole warp.
-constexpr uint32_t kWideRect = 48;
+// blockIdx.y = band: the CTA counts only the tile rows [band * band_rows, (band + 1) * band_rows) and its counters
+// span those rows only (BinPlan).
 // split_n > 1: only the tile rows y with y % split_n == split_i are binned (one view rendered by several GPUs, each
 // owning every split_n-th tile row); a rectangle then keeps its owned rows, split_n rows apart.
-__global__ void __launch_bounds__(256) tile_count_kernel(int P, int T, int NW, int L, int grid_x, int grid_y,
+constexpr uint32_t kWideRect = 48;
+
+// Rows of [y0, y1) that belong to this part of a split view: first owned row and the number of owned rows.
+__device__ __forceinline__ void owned_rows(uint32_t y0, uint32_t y1, uint32_t split_i, uint32_t split_n, uint32_t& first,
+                                           uint32_t& rows) {
+    if (split_n <= 1) { first = y0; rows = y1 > y0 ? y1 - y0 : 0u; return; }
+    first = y0 + (split_i + split_n - y0 % split_n) % split_n;
+    rows = first < y1 ? (y1 - first + split_n - 1) / split_n : 0u;
+}
+
+__global__ void __launch_bounds__(256) tile_count_kernel(int P, int T, int NW, int L, int grid_x, int grid_y, int band_rows,
                                                          int split_i, int split_n,
                                                          const uint32_t* __restrict__ sorted_ids,
                                                          const uint32_t* __restrict__ tiles_touched,
@@ -68,49 +81,49 @@ __global__ void __launch_bounds__(256) tile_count_kernel(int P, int T, int NW, i
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpc = blockDim.x >> 5;
     const int gw = blockIdx.x * wpc + warp;
     const int Tpad = (T + 1) & ~1;
-    uint16_t* hist = reinterpret_cast<uint16_t*>(s_raw) + (size_t)warp * Tpad;
+    const uint32_t by0 = blockIdx.y * (uint32_t)band_rows, by1 = min((uint32_t)grid_y, by0 + (uint32_t)band_rows);
+    const uint32_t t_lo = by0 * (uint32_t)grid_x;              // even: band_rows is even
+    const int Tb = (int)((by1 - by0) * (uint32_t)grid_x), Tbpad = (Tb + 1) & ~1;
+    uint16_t* hist = reinterpret_cast<uint16_t*>(s_raw) + (size_t)warp * Tbpad;
     uint32_t* h32 = reinterpret_cast<uint32_t*>(hist);
-    for (int k = lane; k < Tpad / 2; k += 32) h32[k] = 0;
+    for (int k = lane; k < Tbpad / 2; k += 32) h32[k] = 0;
     __syncwarp();
     const int lo = min(P, gw * L), hi = gw < NW ? min(P, lo + L) : lo;  // warps past the last chunk count nothing
     for (int base = lo; base < hi; base += 32) {
         const int i = base + lane;
-        uint32_t cnt = 0;
-        uint2 rmin = make_uint2(0, 0), rmax = make_uint2(0, 0);
+        uint32_t cnt = 0, x0 = 0, w = 0, y0 = 0, rows = 0;
         if (i < hi) {
             const uint32_t id = sorted_ids[i];
-            cnt = tiles_touched[id];
-            if (cnt > 0) tile_rect(means2D[id], radii[id], rmin, rmax, grid_x, grid_y);
-            uint32_t rows = rmax.y - rmin.y;
-            if (split_n > 1 && cnt > 0) {  // first owned row at or below rmin.y, and how many owned rows the rectangle holds
-                const uint32_t y0 = rmin.y + ((uint32_t)(split_i + split_n) - rmin.y % (uint32_t)split_n) % (uint32_t)split_n;
-                rows = y0 < rmax.y ? (rmax.y - y0 + (uint32_t)split_n - 1) / (uint32_t)split_n : 0u;
-                rmin.y = y0;
-                cnt = rows * (rmax.x - rmin.x);
-                if (rows == 0) rmax.x = rmin.x;
+            uint2 rmin = make_uint2(0, 0), rmax = make_uint2(0, 0);
+            if (tiles_touched[id] > 0) tile_rect(means2D[id], radii[id], rmin, rmax, grid_x, grid_y);
+            x0 = rmin.x; w = rmax.x - rmin.x;
+            if (blockIdx.y == 0) {
+                // kept for the scatter pass, which then reads one packed word pair per Gaussian in depth order
+                uint32_t fy, fr;
+                owned_rows(rmin.y, rmax.y, (uint32_t)split_i, (uint32_t)split_n, fy, fr);
+                rects[i] = fr && w ? make_uint2(x0 | (fy << 16), w | (fr << 16)) : make_uint2(0, 0);
             }
-            // kept for the scatter pass, which then reads one packed word pair per Gaussian in depth order
-            rects[i] = make_uint2(rmin.y * (uint32_t)grid_x + rmin.x, (rmax.x - rmin.x) | (rows << 16));
+            owned_rows(max(rmin.y, by0), min(rmax.y, by1), (uint32_t)split_i, (uint32_t)split_n, y0, rows);
+            cnt = rows * w;
         }
+        const uint32_t step = (uint32_t)split_n * (uint32_t)grid_x;
         if (cnt > 0 && cnt <= kWideRect) {
-            for (uint32_t y = rmin.y; y < rmax.y; y += (uint32_t)split_n) {
-                const uint32_t row = y * (uint32_t)grid_x;
-                for (uint32_t x = rmin.x; x < rmax.x; x++) {
-                    const uint32_t t = row + x;
-                    atomicAdd(&h32[t >> 1], 1u << ((t & 1u) * 16u));
-                }
+            uint32_t row = y0 * (uint32_t)grid_x - t_lo + x0;
+            for (uint32_t r = 0; r < rows; r++, row += step) {
+                for (uint32_t t = row; t < row + w; t++) atomicAdd(&h32[t >> 1], 1u << ((t & 1u) * 16u));
             }
         }
         unsigned wide = __ballot_sync(0xffffffffu, cnt > kWideRect);
         while (wide) {
             const int o = __ffs(wide) - 1;
             wide &= wide - 1;
-            const uint32_t x0 = __shfl_sync(0xffffffffu, rmin.x, o), y0 = __shfl_sync(0xffffffffu, rmin.y, o);
-            const uint32_t w = __shfl_sync(0xffffffffu, rmax.x, o) - x0, n = __shfl_sync(0xffffffffu, cnt, o);
-            const float rw = __frcp_rn((float)w);  // s / w through a reciprocal, exact here (see tile_scatter_kernel)
+            const uint32_t bx0 = __shfl_sync(0xffffffffu, x0, o), yy0 = __shfl_sync(0xffffffffu, y0, o);
+            const uint32_t bw = __shfl_sync(0xffffffffu, w, o), n = __shfl_sync(0xffffffffu, cnt, o);
+            const float rw = __frcp_rn((float)bw);  // s / w through a reciprocal, exact here (see tile_scatter_kernel)
+            const uint32_t t0 = yy0 * (uint32_t)grid_x - t_lo + bx0;
             for (uint32_t s = lane; s < n; s += 32) {
                 const uint32_t q = __float2uint_rz(((float)s + 0.5f) * rw);
-                const uint32_t t = (y0 + q * (uint32_t)split_n) * (uint32_t)grid_x + x0 + (s - q * w);
+                const uint32_t t = t0 + q * step + (s - q * bw);
                 atomicAdd(&h32[t >> 1], 1u << ((t & 1u) * 16u));
             }
         }
@@ -121,19 +134,19 @@ __global__ void __launch_bounds__(256) tile_count_kernel(int P, int T, int NW, i
     __syncthreads();
     const uint16_t* all = reinterpret_cast<const uint16_t*>(s_raw);
     uint16_t* allw = reinterpret_cast<uint16_t*>(s_raw);
-    for (int t = threadIdx.x; t < Tpad; t += blockDim.x) {
+    for (int t = threadIdx.x; t < Tbpad; t += blockDim.x) {
         uint32_t run = 0;
         for (int w = 0; w < wpc; w++) {
-            const uint32_t c = all[(size_t)w * Tpad + t];
-            allw[(size_t)w * Tpad + t] = (uint16_t)run;
+            const uint32_t c = all[(size_t)w * Tbpad + t];
+            allw[(size_t)w * Tbpad + t] = (uint16_t)run;
             run += c;
         }
-        Mg[(size_t)blockIdx.x * Tpad + t] = (uint16_t)run;
+        Mg[(size_t)blockIdx.x * Tpad + t_lo + t] = (uint16_t)run;
     }
     __syncthreads();
     if (gw >= NW) return;
-    uint32_t* row = reinterpret_cast<uint32_t*>(M + (size_t)gw * Tpad);
-    for (int k = lane; k < Tpad / 2; k += 32) row[k] = h32[k];
+    uint32_t* row = reinterpret_cast<uint32_t*>(M + (size_t)gw * Tpad + t_lo);
+    for (int k = lane; k < Tbpad / 2; k += 32) row[k] = h32[k];
 }
 
 // ---- 3a. sums over segments of 32 group rows -----------------------------------------------------------
@@ -274,9 +287,9 @@ __global__ void __launch_bounds__(1024) col_scan_kernel(int T, int Tpad, int NW,
 // distinct, so its lanes read, use and bump the per-tile cursors without any ranking among themselves, and the
 // order between Gaussians is the order of the loop.  (The earlier walk of 32 instances of mixed Gaussians per step
 // needed a MATCH.ANY per step to rank equal tiles: 36 % of that kernel's stall samples.)
-// grid_x here is the distance between two rows of a rectangle: the grid's width, times split_n for a split view
-__global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int T, int NW, int L, int grid_x,
-                                                           const uint32_t* __restrict__ sorted_ids,
+// blockIdx.y = band, as in tile_count_kernel: the CTA hands out only the slots of its band's tiles.
+__global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int T, int NW, int L, int grid_x, int grid_y, int band_rows,
+                                                           int split_n, const uint32_t* __restrict__ sorted_ids,
                                                            const uint2* __restrict__ rects, const uint16_t* __restrict__ M,
                                                            const uint32_t* __restrict__ E,
                                                            const uint32_t* __restrict__ tile_base,
@@ -285,41 +298,56 @@ __global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int T, int NW,
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpc = blockDim.x >> 5;
     const int gw = blockIdx.x * wpc + warp;
     const int Tpad = (T + 1) & ~1;
+    const uint32_t by0 = blockIdx.y * (uint32_t)band_rows, by1 = min((uint32_t)grid_y, by0 + (uint32_t)band_rows);
+    const uint32_t t_lo = by0 * (uint32_t)grid_x;
+    const int Tb = (int)((by1 - by0) * (uint32_t)grid_x), Tbpad = (Tb + 1) & ~1;
     // slot of an instance = first slot of (group, tile) [32-bit, shared by the CTA's warps] + the warp's running
     // 16-bit cursor, which starts at the chunk's offset inside the group (tile_count's M rows)
     uint32_t* base = reinterpret_cast<uint32_t*>(s_raw);
-    uint16_t* cur = reinterpret_cast<uint16_t*>(base + Tpad) + (size_t)warp * Tpad;
-    const uint32_t* grow = E + (size_t)blockIdx.x * T;
-    for (int k = threadIdx.x; k < T; k += blockDim.x) base[k] = grow[k] + tile_base[k];
+    uint16_t* cur = reinterpret_cast<uint16_t*>(base + Tbpad) + (size_t)warp * Tbpad;
+    const uint32_t* grow = E + (size_t)blockIdx.x * T + t_lo;
+    for (int k = threadIdx.x; k < Tb; k += blockDim.x) base[k] = grow[k] + tile_base[t_lo + k];
     if (gw < NW) {
-        const uint32_t* row = reinterpret_cast<const uint32_t*>(M + (size_t)gw * Tpad);
+        const uint32_t* row = reinterpret_cast<const uint32_t*>(M + (size_t)gw * Tpad + t_lo);
         uint32_t* c32 = reinterpret_cast<uint32_t*>(cur);
-        for (int k = lane; k < Tpad / 2; k += 32) c32[k] = row[k];
+        for (int k = lane; k < Tbpad / 2; k += 32) c32[k] = row[k];
     }
     __syncthreads();
     if (gw >= NW) return;
     const int lo = min(P, gw * L), hi = min(P, lo + L);
     if (lo >= hi) return;
     const unsigned full = 0xffffffffu;
-    const uint32_t off_a = (uint32_t)(lane >> 3) * (uint32_t)grid_x + (uint32_t)(lane & 7);  // lane's tile in an 8 x 4 layout
-    const uint32_t off_b = (uint32_t)(lane >> 2) * (uint32_t)grid_x + (uint32_t)(lane & 3);  // ... in a 4 x 8 layout
+    const uint32_t pitch = (uint32_t)grid_x * (uint32_t)(split_n > 1 ? split_n : 1);  // distance between two rows of a rectangle
+    const uint32_t off_a = (uint32_t)(lane >> 3) * pitch + (uint32_t)(lane & 7);  // lane's tile in an 8 x 4 layout
+    const uint32_t off_b = (uint32_t)(lane >> 2) * pitch + (uint32_t)(lane & 3);  // ... in a 4 x 8 layout
+    const bool banded = gridDim.y > 1;
     // 32 Gaussians per block: one coalesced load of their rectangles and ids (the next block's is in flight while
     // this one is handed out), then lane j's values are broadcast in turn
     uint2 rc_next = lo + lane < hi ? rects[lo + lane] : make_uint2(0, 0);
     uint32_t id_next = lo + lane < hi ? sorted_ids[lo + lane] : 0u;
     for (int b0 = lo; b0 < hi; b0 += 32) {
-        const uint2 rc_mine = rc_next;
+        uint2 rc_mine = rc_next;
         const uint32_t id_mine = id_next;
         const int nx = b0 + 32 + lane;
         rc_next = nx < hi ? rects[nx] : make_uint2(0, 0);
         id_next = nx < hi ? sorted_ids[nx] : 0u;
-        unsigned live = __ballot_sync(full, rc_mine.y != 0);  // culled Gaussians have no tiles
+        if (banded && rc_mine.y != 0) {  // keep the rectangle's rows that lie in this band (rows are split_n apart)
+            const uint32_t sn = (uint32_t)(split_n > 1 ? split_n : 1);
+            uint32_t y0 = rc_mine.x >> 16, h = rc_mine.y >> 16;
+            const uint32_t skip = y0 < by0 ? (by0 - y0 + sn - 1) / sn : 0u;
+            y0 += skip * sn;
+            h = h > skip ? h - skip : 0u;
+            if (h) h = y0 < by1 ? min(h, (by1 - y0 + sn - 1) / sn) : 0u;
+            rc_mine = h ? make_uint2((rc_mine.x & 0xffffu) | (y0 << 16), (rc_mine.y & 0xffffu) | (h << 16)) : make_uint2(0, 0);
+        }
+        unsigned live = __ballot_sync(full, rc_mine.y != 0);  // culled Gaussians (and those outside the band) have no tiles
         while (live) {
             const int j = __ffs(live) - 1;
             live &= live - 1;
-            const uint32_t t0 = __shfl_sync(full, rc_mine.x, j), wh = __shfl_sync(full, rc_mine.y, j);
+            const uint32_t xy = __shfl_sync(full, rc_mine.x, j), wh = __shfl_sync(full, rc_mine.y, j);
             const uint32_t id = __shfl_sync(full, id_mine, j);
             const uint32_t w = wh & 0xffffu, h = wh >> 16;
+            const uint32_t t0 = (xy >> 16) * (uint32_t)grid_x + (xy & 0xffffu) - t_lo;  // band-local tile index
             if (w <= 8 && h <= 4) {  // the usual case: the rectangle fits the warp laid out 8 x 4 ...
                 if ((uint32_t)(lane & 7) < w && (uint32_t)(lane >> 3) < h) {
                     const uint32_t t = t0 + off_a;
@@ -343,7 +371,7 @@ __global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int T, int NW,
                 const float rw = __frcp_rn((float)w);
                 for (uint32_t s = lane; s < n; s += 32) {
                     const uint32_t q = __float2uint_rz(((float)s + 0.5f) * rw);
-                    const uint32_t t = t0 + q * (uint32_t)grid_x + (s - q * w);
+                    const uint32_t t = t0 + q * pitch + (s - q * w);
                     const uint32_t k = cur[t];
                     const uint32_t c = base[t] + k;
                     if (c < capacity) point_list[c] = id;
@@ -356,8 +384,9 @@ __global__ void __launch_bounds__(256) tile_scatter_kernel(int P, int T, int NW,
 }
 
 // ---- launch plumbing ----------------------------------------------------------------------------------
-BinPlan make_bin_plan(int P, int T) {
+BinPlan make_bin_plan(int P, int grid_x, int grid_y) {
     BinPlan b;
+    const int T = grid_x * grid_y;
     b.T = T;
     b.Tpad = (T + 1) & ~1;
     int L = 128;
@@ -371,10 +400,25 @@ BinPlan make_bin_plan(int P, int T) {
     if (NW < 1) NW = 1;
     b.L = L;
     b.NW = NW;
+    // Bands: the per-warp 16-bit counters / cursors of the two walking kernels cover one band of tile rows.  Up to
+    // 2560 tiles (an 800 x 800 image has 2500) one band is the whole image; a 1920 x 1080 grid (8160 tiles) is cut into
+    // four, which brings a CTA from 163 KB of shared memory (one CTA = 8 warps per SM) down to 43 KB.  Every band
+    // walks all the chunks and skips the Gaussians that do not reach its rows.  band_rows is even so that a band's
+    // first tile index is (the 16-bit rows are moved as 32-bit words).
+    const int kBandTiles = 2560;
+    int nb = (T + kBandTiles - 1) / kBandTiles;
+    if (nb < 1) nb = 1;
+    int band_rows = (grid_y + nb - 1) / nb;
+    band_rows = (band_rows + 1) & ~1;
+    if (band_rows < 2) band_rows = 2;
+    b.band_rows = band_rows;
+    b.nb = (grid_y + band_rows - 1) / band_rows;
+    if (b.nb < 1) b.nb = 1;
+    const int Tb = ((band_rows < grid_y ? band_rows : grid_y) * grid_x + 1) & ~1;
     // a group = the chunks of one CTA of the two walking kernels; its size is bounded by their shared memory
     // (scatter: 4 bytes per tile for the group + 2 per tile and warp)
     const size_t smem_budget = 200 * 1024;
-    int wpc = ((int)smem_budget - 4 * b.Tpad) / (2 * b.Tpad);
+    int wpc = ((int)smem_budget - 4 * Tb) / (2 * Tb);
     b.wpc = wpc > 8 ? 8 : wpc;
     if (b.wpc < 1) b.wpc = 0;
     b.NG = b.wpc ? (NW + b.wpc - 1) / b.wpc : 0;
@@ -390,13 +434,14 @@ int launch_tile_count(const BinPlan& b, int P, int grid_x, int grid_y, const uin
         set_error("binning: image has too many tiles (or chunk too long) for the shared-memory tile counters");
         return -1;
     }
-    const size_t smem = (size_t)b.wpc * b.Tpad * 2;
+    const size_t Tb = (size_t)((std::min(b.band_rows, grid_y) * grid_x + 1) & ~1);
+    const size_t smem = (size_t)b.wpc * Tb * 2;
     if (ensure_dyn_smem(reinterpret_cast<const void*>(tile_count_kernel), 220 * 1024) ||
         ensure_dyn_smem(reinterpret_cast<const void*>(tile_scatter_kernel), 220 * 1024))
         return -1;
     LaunchScope ls("tile_count", stream);
-    tile_count_kernel<<<b.NG, b.wpc * 32, smem, stream>>>(P, b.T, b.NW, b.L, grid_x, grid_y, split_i, split_n, sorted_ids, tiles_touched, means2D,
-                                                        radii, rects, M, Mg);
+    tile_count_kernel<<<dim3(b.NG, b.nb), b.wpc * 32, smem, stream>>>(P, b.T, b.NW, b.L, grid_x, grid_y, b.band_rows, split_i, split_n, sorted_ids,
+                                                                    tiles_touched, means2D, radii, rects, M, Mg);
     return 0;
 }
 
@@ -418,9 +463,10 @@ int launch_tile_scatter(const BinPlan& b, int P, int grid_x, int grid_y, const u
     LaunchScope ls("tile_scatter", stream, 2);
     dim3 g((b.T + 1023) / 1024, b.nseg + (base_pending ? 1 : 0));
     col_scan_kernel<<<g, 1024, 0, stream>>>(b.T, b.Tpad, b.NG, b.nseg, Mg, S, E, tile_base, ranges, tile_order, status, capacity);
-    const size_t smem = (size_t)b.Tpad * 4 + (size_t)b.wpc * b.Tpad * 2;
-    tile_scatter_kernel<<<b.NG, b.wpc * 32, smem, stream>>>(P, b.T, b.NW, b.L, grid_x * (split_n > 1 ? split_n : 1), sorted_ids, rects, M, E, tile_base,
-                                                          point_list, capacity);
+    const size_t Tb = (size_t)((std::min(b.band_rows, grid_y) * grid_x + 1) & ~1);
+    const size_t smem = Tb * 4 + (size_t)b.wpc * Tb * 2;
+    tile_scatter_kernel<<<dim3(b.NG, b.nb), b.wpc * 32, smem, stream>>>(P, b.T, b.NW, b.L, grid_x, grid_y, b.band_rows, split_n, sorted_ids, rects,
+                                                                      M, E, tile_base, point_list, capacity);
     return 0;
 }
 

@@ -61,7 +61,7 @@ struct GeomState {
     uint32_t* ids;            // P iota
     uint32_t* sorted_keys;    // P depth bits, ascending
     uint32_t* sorted_ids;     // P Gaussian ids in depth order (stable)
-    uint2* rects;             // P tile rectangles in depth order: {first tile, width | height << 16}, tile_count -> tile_scatter
+    uint2* rects;             // P tile rectangles in depth order: {x0 | y0 << 16, width | rows << 16}, tile_count -> tile_scatter
     char* sort_temp;
     size_t sort_temp_bytes;
     uint16_t* M;              // NW x Tpad per (chunk, tile): instances of the earlier chunks of the same group

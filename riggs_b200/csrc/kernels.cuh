@@ -99,8 +99,10 @@ struct BinPlan {
     int NW, L;        // chunks (one warp each) of L depth-ordered Gaussians
     int wpc, NG;      // chunks per group (= warps per CTA of the two walking kernels, shared-memory bound), groups
     int nseg;         // segments of 32 group rows
+    int nb, band_rows;  // the walking kernels cover the tile grid in nb bands of band_rows tile rows (grid.y = band): their
+                        // per-warp counters span one band, not the image, so a 1080p grid keeps 4-5 CTAs per SM instead of 1
 };
-BinPlan make_bin_plan(int P, int T);
+BinPlan make_bin_plan(int P, int grid_x, int grid_y);
 size_t depth_sort_temp_bytes(size_t P);      // radix_sort.cu (covers the library sort's need as well)
 size_t depth_sort_temp_bytes_cub(size_t P);  // binning.cu
 int launch_depth_sort_cub(char* temp, size_t temp_bytes, const float* depths, uint32_t* keys_out, const uint32_t* ids_in,
