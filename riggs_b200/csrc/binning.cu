@@ -24,6 +24,7 @@
 #include <cub/device/device_radix_sort.cuh>
 
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "kernels.cuh"
@@ -389,9 +390,12 @@ BinPlan make_bin_plan(int P, int grid_x, int grid_y) {
     const int T = grid_x * grid_y;
     b.T = T;
     b.Tpad = (T + 1) & ~1;
-    int L = 128;
+    static const int envL = [] { const char* e = std::getenv("RG_BIN_L"); return e ? atoi(e) : 0; }();
+    static const int envRows = [] { const char* e = std::getenv("RG_BIN_MAXROWS"); return e ? atoi(e) : 0; }();
+    static const int envBand = [] { const char* e = std::getenv("RG_BAND_TILES"); return e ? atoi(e) : 0; }();  // tuning aid
+    int L = envL > 0 ? envL : 128;
     int NW = (P + L - 1) / L;
-    const int kMaxRows = 4096;
+    const int kMaxRows = envRows > 0 ? envRows : 8192;
     if (NW > kMaxRows) {
         NW = kMaxRows;
         L = (P + NW - 1) / NW;
@@ -401,24 +405,31 @@ BinPlan make_bin_plan(int P, int grid_x, int grid_y) {
     b.L = L;
     b.NW = NW;
     // Bands: the per-warp 16-bit counters / cursors of the two walking kernels cover one band of tile rows.  Up to
-    // 2560 tiles (an 800 x 800 image has 2500) one band is the whole image; a 1920 x 1080 grid (8160 tiles) is cut into
-    // four, which brings a CTA from 163 KB of shared memory (one CTA = 8 warps per SM) down to 43 KB.  Every band
-    // walks all the chunks and skips the Gaussians that do not reach its rows.  band_rows is even so that a band's
-    // first tile index is (the 16-bit rows are moved as 32-bit words).
-    const int kBandTiles = 2560;
-    int nb = (T + kBandTiles - 1) / kBandTiles;
-    if (nb < 1) nb = 1;
-    int band_rows = (grid_y + nb - 1) / nb;
-    band_rows = (band_rows + 1) & ~1;
-    if (band_rows < 2) band_rows = 2;
-    b.band_rows = band_rows;
-    b.nb = (grid_y + band_rows - 1) / band_rows;
-    if (b.nb < 1) b.nb = 1;
-    const int Tb = ((band_rows < grid_y ? band_rows : grid_y) * grid_x + 1) & ~1;
+    // 4400 tiles (800 x 800: 2500, 1024 x 1024: 4096) one band is the whole image; a 1920 x 1080 grid (8160 tiles) is
+    // counted in two bands and scattered in four, which brings the scatter CTA from 163 KB of shared memory (one CTA =
+    // 8 warps per SM) down to 43 KB.  Every band walks all the chunks and skips the Gaussians that do not reach its rows
+    // (measured at C4, 1 M Gaussians: count 0.182 -> 0.111 ms with two bands, 0.142 with four; scatter 0.377 -> 0.296 ms
+    // with four; at 4096 tiles bands cost more than they give).  band_rows is even so that a band's first tile index is
+    // (the 16-bit rows are moved as 32-bit words).
+    auto bands = [&](int max_tiles, int& nb_out, int& rows_out) {
+        int nb = T <= 4400 ? 1 : (T + max_tiles - 1) / max_tiles;
+        if (envBand > 0) nb = (T + envBand - 1) / envBand;
+        if (nb < 1) nb = 1;
+        int rows = (grid_y + nb - 1) / nb;
+        rows = (rows + 1) & ~1;
+        if (rows < 2) rows = 2;
+        rows_out = rows;
+        nb_out = (grid_y + rows - 1) / rows;
+        if (nb_out < 1) nb_out = 1;
+    };
+    bands(4400, b.nb_count, b.band_rows_count);
+    bands(2560, b.nb, b.band_rows);
+    const int Tb = ((b.band_rows < grid_y ? b.band_rows : grid_y) * grid_x + 1) & ~1;
+    const int Tbc = ((b.band_rows_count < grid_y ? b.band_rows_count : grid_y) * grid_x + 1) & ~1;
     // a group = the chunks of one CTA of the two walking kernels; its size is bounded by their shared memory
-    // (scatter: 4 bytes per tile for the group + 2 per tile and warp)
+    // (scatter: 4 bytes per tile for the group + 2 per tile and warp; count: 2 per tile and warp)
     const size_t smem_budget = 200 * 1024;
-    int wpc = ((int)smem_budget - 4 * Tb) / (2 * Tb);
+    int wpc = std::min(((int)smem_budget - 4 * Tb) / (2 * Tb), (int)smem_budget / (2 * Tbc));
     b.wpc = wpc > 8 ? 8 : wpc;
     if (b.wpc < 1) b.wpc = 0;
     b.NG = b.wpc ? (NW + b.wpc - 1) / b.wpc : 0;
@@ -434,13 +445,13 @@ int launch_tile_count(const BinPlan& b, int P, int grid_x, int grid_y, const uin
         set_error("binning: image has too many tiles (or chunk too long) for the shared-memory tile counters");
         return -1;
     }
-    const size_t Tb = (size_t)((std::min(b.band_rows, grid_y) * grid_x + 1) & ~1);
+    const size_t Tb = (size_t)((std::min(b.band_rows_count, grid_y) * grid_x + 1) & ~1);
     const size_t smem = (size_t)b.wpc * Tb * 2;
     if (ensure_dyn_smem(reinterpret_cast<const void*>(tile_count_kernel), 220 * 1024) ||
         ensure_dyn_smem(reinterpret_cast<const void*>(tile_scatter_kernel), 220 * 1024))
         return -1;
     LaunchScope ls("tile_count", stream);
-    tile_count_kernel<<<dim3(b.NG, b.nb), b.wpc * 32, smem, stream>>>(P, b.T, b.NW, b.L, grid_x, grid_y, b.band_rows, split_i, split_n, sorted_ids,
+    tile_count_kernel<<<dim3(b.NG, b.nb_count), b.wpc * 32, smem, stream>>>(P, b.T, b.NW, b.L, grid_x, grid_y, b.band_rows_count, split_i, split_n, sorted_ids,
                                                                     tiles_touched, means2D, radii, rects, M, Mg);
     return 0;
 }

@@ -101,6 +101,7 @@ struct BinPlan {
     int nseg;         // segments of 32 group rows
     int nb, band_rows;  // the walking kernels cover the tile grid in nb bands of band_rows tile rows (grid.y = band): their
                         // per-warp counters span one band, not the image, so a 1080p grid keeps 4-5 CTAs per SM instead of 1
+    int nb_count, band_rows_count;  // ... tile_count's own band split (nb / band_rows are tile_scatter's)
 };
 BinPlan make_bin_plan(int P, int grid_x, int grid_y);
 size_t depth_sort_temp_bytes(size_t P);      // radix_sort.cu (covers the library sort's need as well)

@@ -3,7 +3,7 @@
 (:934-967, K nearest nodes + radial-basis weights) and the blending of ``forward`` (:1133-1236) -- with the same
 names, argument meaning and return dicts.  The node-motion network (``node_deform``: an 8x256 MLP, dense GEMMs)
 stays a torch module supplied by the caller; node initialisation (farthest-point sampling), densification, the
-ARAP regulariser and the animation branches (``node_trans_bias`` / ``animation_d_values``) are not part of the
+ARAP regulariser and the GUI's drag-editing branch (``node_trans_bias``) are not part of the
 hot path and are not mirrored.  No CPU path.
 """
 from __future__ import annotations
@@ -193,12 +193,23 @@ class ControlNodeWarp(nn.Module):
             self.nn_weight, self.nn_dist, self.nn_idxs = out["nn_weight"], out["nn_dist"], out["nn_idx"]
         return out["nn_weight"], out["nn_dist"], out["nn_idx"]
 
-    def forward(self, x, t, feature, motion_mask, iteration=0, is_training=True, node_attrs=None, **kwargs):
+    def forward(self, x, t, feature, motion_mask, iteration=0, is_training=True, node_attrs=None, node_trans_bias=None,
+                node_scaling_bias=None, animation_d_values=None, **kwargs):
+        """``animation_d_values``: per-key overrides of the node attributes (utils/time_utils.py:1142-1144: a motion
+        editor replaces the network's ``d_xyz`` / ``d_rotation`` / ... by its own values).  ``node_trans_bias`` -- the GUI's
+        drag editing (:1165-1204: per-node rotations by SVD over trajectories, geodesic re-weighting) -- belongs to
+        ``train_gui.py`` and is not part of this path."""
+        if node_trans_bias is not None:
+            raise NotImplementedError("ControlNodeWarp.forward(node_trans_bias=...) is the GUI's drag editing "
+                                      "(train_gui.py); not part of the hot path")
         if node_attrs is None:
             if t.dim() == 0:
                 t = self.expand_time(t)
             node_attrs = self.node_deform(t=t, **kwargs)
         attrs = dict(node_attrs)
+        if animation_d_values is not None:
+            for key in animation_d_values:
+                attrs[key] = animation_d_values[key]
         if not self.pred_opacity:
             attrs.pop("d_opacity", None)
         if not self.pred_color:
