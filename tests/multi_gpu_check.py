@@ -96,7 +96,7 @@ def main():
 
 def view_split_check(rank, world, dev) -> bool:
     """One view rendered by all the ranks together (dist.ViewSplit) against the same view rendered by this rank alone:
-    image, depth, alpha and radii bit-identical on every rank, every gradient within 5e-5 (max norm and L2)."""
+    image, depth, alpha and radii bit-identical on every rank, every gradient within four times the unsplit step's own run-to-run spread (at least 5e-5; max norm and L2)."""
     from riggs_b200 import skeleton_warp as sw, synth
     from riggs_b200.dist import ViewSplit
     from riggs_b200.fused import WorkspacePool, render_skinned
@@ -136,20 +136,23 @@ def view_split_check(rank, world, dev) -> bool:
             return out, g, int(out["status"][0])
 
         whole, g_whole, n_whole = run(None)
+        _, g_again, _ = run(None)  # the unsplit step against itself: float atomics land in another order every run
+        spread = max(max(helpers.rel_err(a.cpu(), b.cpu()), helpers.rel_l2(a.cpu(), b.cpu())) for a, b in zip(g_again, g_whole))
+        gate = min(max(5e-5, 4 * spread), 1e-3)
         for trial in range(2):
             part, g_part, n_part = run(split)
             same = all(bool(torch.equal(part[k], whole[k])) for k in ("render", "depth", "alpha", "radii"))
             errs = [max(helpers.rel_err(a.cpu(), b.cpu()), helpers.rel_l2(a.cpu(), b.cpu())) for a, b in zip(g_part, g_whole)]
             counts = torch.tensor([n_part], device=dev)
             dist.all_reduce(counts)
-            ok = same and max(errs) < 5e-5 and int(counts[0]) == n_whole
+            ok = same and max(errs) < gate and int(counts[0]) == n_whole
             t = torch.tensor([int(ok)], device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MIN)
             ok_all = ok_all and bool(int(t[0]))
             if rank == 0:
                 print(json.dumps({"check": "view_split", "config": name, "world": world, "trial": trial,
                                   "peer_memory": split.images.hdl is not None, "image_bit_identical": same,
-                                  "max_grad_err": max(errs), "instances_whole": n_whole, "instances_sum_of_parts": int(counts[0]),
+                                  "max_grad_err": max(errs), "unsplit_run_to_run": spread, "instances_whole": n_whole, "instances_sum_of_parts": int(counts[0]),
                                   "instances_this_rank": n_part, "ok_all_ranks": bool(int(t[0]))}))
         del split
     return ok_all
