@@ -39,8 +39,12 @@ constexpr int kTileM = 128;      // points per tile = TMEM lanes
 constexpr int kQuarter = 64;     // output columns per accumulator buffer = input columns per k-slab
 constexpr int kChunkBytes = kQuarter * kQuarter * 2;  // one weight chunk: 64 outputs x 64 inputs, bf16 = 8 KB
 constexpr int kStages = 20;      // ring depth: 160 KB of weights in flight / resident
-constexpr int kEpiWarps = 8;   // two per TMEM lane quarter, each takes half of a quarter's 64 columns
-constexpr int kMlpThreads = (kEpiWarps + 2) * 32;  // + MMA warp + producer warp
+constexpr int kEpiWarps = 8;   // one epilogue group: two warps per TMEM lane quarter, each takes half of a quarter's 64 columns
+constexpr int kEpiGroups = 2;  // group 0 takes the quarters that land in accumulator buffer 0, group 1 those in buffer 1:
+                               // a quarter's epilogue (TMEM load, bias / ReLU / pack, TMEM store, the training-state
+                               // stores) is a ~2000-cycle latency chain per warp, and with ONE group the four quarters of
+                               // a layer queued behind each other while the tensor core waited for the last one
+constexpr int kMlpThreads = (kEpiGroups * kEpiWarps + 2) * 32;  // + MMA warp + producer warp
 
 // TMEM columns (32-bit each, 128 lanes): two fp32 accumulator quarters, two bf16 activation buffers (256 values = 128
 // columns each), the embedded input (64 values = 32 columns)
@@ -102,6 +106,20 @@ __device__ __forceinline__ void mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_
         "}\n" ::"r"(d_tmem),
         "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
         : "memory");
+}
+// one lane of a converged warp (the warp stays converged around it: the issuing loop runs on all 32 lanes with
+// warp-uniform values, which the compiler keeps in uniform registers -- under `if (lane == 0)` it wrapped every
+// tcgen05 instruction in an election loop, ~90 instructions per weight chunk on the kernel's critical path)
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}\n"
+        : "=r"(pred));
+    return pred != 0;
 }
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile(
@@ -202,14 +220,15 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
     }
     if (!BWD)
         for (int i = threadIdx.x; i < (kLayers + 1) * kHid; i += blockDim.x) sm.bias[i] = a.bias[i];
-    if (warp == kEpiWarps) tmem_alloc(&sm.tmem_base, kTmemCols);
+    constexpr int kMmaWarp = kEpiGroups * kEpiWarps, kProducerWarp = kMmaWarp + 1;
+    if (warp == kMmaWarp) tmem_alloc(&sm.tmem_base, kTmemCols);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = sm.tmem_base;
     const int my_tiles = a.n_tiles > (int)blockIdx.x ? (a.n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
 
-    if (warp == kEpiWarps + 1) {
+    if (warp == kProducerWarp) {
         // ===================== producer: weight chunks, the same sequence for every tile =====================
         if (lane == 0) {
             uint32_t c = 0;
@@ -221,9 +240,9 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
                 }
             }
         }
-    } else if (warp == kEpiWarps) {
-        // ===================== MMA issuer =====================
-        if (lane == 0) {
+    } else if (warp == kMmaWarp) {
+        // ===================== MMA issuer: the whole warp runs the loop, one elected lane issues =====================
+        {
             uint32_t c = 0, g = 0;
             for (int t = 0; t < my_tiles; t++) {
                 mbar_wait(&sm.emb_ready, t & 1);
@@ -257,19 +276,24 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
                             mbar_wait(&sm.full[st], (c / kStages) & 1);
                             tc_fence_after();
                             const uint64_t bd = b_desc(smem_u32(ring + (size_t)st * kChunkBytes));
+                            if (elect_one()) {
 #pragma unroll
-                            for (int k = 0; k < 4; k++)  // the k-step of 16 columns starts 32 bytes (2 address units) further on
-                                mma_ts(d_col, a_col + (uint32_t)k * 8, bd + (uint64_t)(k * 2), idesc, (s | k) != 0);
-                            tc_commit(&sm.empty[st]);  // the chunk's slot is free once these MMAs have read it
+                                for (int k = 0; k < 4; k++)  // the k-step of 16 columns starts 32 bytes (2 address units) further on
+                                    mma_ts(d_col, a_col + (uint32_t)k * 8, bd + (uint64_t)(k * 2), idesc, (s | k) != 0);
+                                tc_commit(&sm.empty[st]);  // the chunk's slot is free once these MMAs have read it
+                            }
+                            __syncwarp();
                         }
-                        tc_commit(&sm.acc_full[ab]);
+                        if (elect_one()) tc_commit(&sm.acc_full[ab]);
+                        __syncwarp();
                     }
                 }
             }
         }
     } else {
         // ===================== epilogue warps: thread = point (TMEM lane) x half of a quarter's columns =====================
-        const int lq = warp & 3, ch = warp >> 2;
+        const int lq = warp & 3, ch = (warp >> 2) & 1;
+        const uint32_t group = (uint32_t)(warp >> 3);  // its quarters are those with (g & 1) == group
         const uint32_t lane_base = (uint32_t)(lq * 32) << 16;
         const int row = lq * 32 + lane;
         uint32_t g = 0;
@@ -278,7 +302,9 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
             const long long pt = ((long long)blockIdx.x + (long long)t * gridDim.x) * kTileM + row;
             const bool valid = pt < a.N;
             const bool in_buf = pt < a.n_pad;
-            if (!BWD) {
+            if (group != 0) {
+                // the tile's input region is written by group 0 alone
+            } else if (!BWD) {
                 // ---- positional encoding (utils/time_utils.py:208-256: x, then sin / cos per octave), bf16, into TMEM:
                 //      this thread packs features 32 ch .. 32 ch + 31
                 float e[64];
@@ -340,9 +366,11 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
                     if (in_buf) store_features(a.dz + ((size_t)kLayers * kHid + (size_t)sl * 64 + (size_t)ch * 32) * a.n_pad + pt, a.n_pad, pk);
                 }
             }
-            tmem_st_wait();
-            tc_fence_before();
-            mbar_arrive(&sm.emb_ready);
+            if (group == 0) {
+                tmem_st_wait();
+                tc_fence_before();
+                mbar_arrive(&sm.emb_ready);
+            }
 #pragma unroll 1
             for (int l = 0; l < a.n_steps; l++) {
                 const MlpLayerPlan p = a.plan[l];
@@ -351,6 +379,7 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
 #pragma unroll 1
                 for (int q = 0; q < p.n_quarters; q++, g++) {
                     const uint32_t ab = g & 1;
+                    if (ab != group) continue;
                     mbar_wait(&sm.acc_full[ab], (g >> 1) & 1);
                     tc_fence_after();
                     uint32_t v[32];
@@ -422,7 +451,7 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == kEpiWarps) tmem_dealloc(tmem, kTmemCols);
+    if (warp == kMmaWarp) tmem_dealloc(tmem, kTmemCols);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
