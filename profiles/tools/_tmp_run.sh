@@ -1,9 +1,10 @@
 #!/bin/bash
 cd /root/repo
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_gpu_mlp.py -x -q -m gpu > gpurun_out/mlp_tests.log 2>&1; echo "tests rc=$?"
+timeout 300 python -m pytest tests/test_gpu_mlp.py tests/test_gpu_fused.py -x -q -m gpu -k "mlp" > gpurun_out/mlp_tests.log 2>&1; echo "tests rc=$?"
 tail -n 3 gpurun_out/mlp_tests.log
-timeout 120 python profiles/tools/mlp_time.py 300000 5
+RG_LIB=/root/repo/riggs_b200/lib/libriggs_b200_prof.so timeout 120 python profiles/tools/mlp_prof.py > gpurun_out/mlp_prof.txt 2>&1
+sed -n 2,8p gpurun_out/mlp_prof.txt; tail -n 2 gpurun_out/mlp_prof.txt
 timeout 300 python bench.py --mlps on --steps 10 --no-cpu-baseline --no-ref-cuda > gpurun_out/mlp_on.json 2> gpurun_out/mlp_on.err
 python -c "
 import json,sys

@@ -25,18 +25,22 @@ __device__ __forceinline__ void bulk_load(void* smem_dst, const void* gmem_src, 
                  : "memory");
 }
 
-// Non-blocking probe and plain arrival, for warp-to-warp hand-offs inside a CTA (one lane arrives after a
+// Upper bound (ns) on how long the hardware may keep a waiting thread suspended inside one try_wait before it returns
+// false.  Without the hint the limit is short: the warps of the MLP chain kernel that wait for their next quarter polled
+// ~26 times per wait (16 M TRYWAIT instructions per launch) and took issue slots from the warps on the critical path.
+constexpr uint32_t kMbarSuspendHint = 0x989680;
+// Potentially-blocking probe and plain arrival, for warp-to-warp hand-offs inside a CTA (one lane arrives after a
 // __syncwarp; arrive has release, try_wait acquire semantics at CTA scope).
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
     uint32_t ok;
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n"
         "selp.u32 %0, 1, 0, p;\n"
         "}\n"
         : "=r"(ok)
-        : "r"(smem_u32(bar)), "r"(parity)
+        : "r"(smem_u32(bar)), "r"(parity), "r"(kMbarSuspendHint)
         : "memory");
     return ok != 0;
 }

@@ -32,23 +32,34 @@
 
 namespace rg {
 
+#ifndef RG_MLP_PROF
+#define RG_MLP_PROF 0  // 1: CTA 0 records cycle counts of its second tile (tuning builds only)
+#endif
+#if RG_MLP_PROF
+__device__ unsigned long long g_mlp_prof[4096];
+#define PROF_ON (blockIdx.x == 0 && t == 1)
+#endif
 constexpr int kHid = 256;        // hidden width of the reference's MLPs (W = 256)
 constexpr int kLayers = 8;       // D = 8 hidden layers, then the head
 constexpr int kSkipInto = 5;     // the embedded input is concatenated in front of layer 5's input (skips = [D // 2])
 constexpr int kTileM = 128;      // points per tile = TMEM lanes
 constexpr int kQuarter = 64;     // output columns per accumulator buffer = input columns per k-slab
 constexpr int kChunkBytes = kQuarter * kQuarter * 2;  // one weight chunk: 64 outputs x 64 inputs, bf16 = 8 KB
-constexpr int kStages = 20;      // ring depth: 160 KB of weights in flight / resident
+constexpr int kStages = 18;      // ring depth: 144 KB of weights in flight / resident
 constexpr int kEpiWarps = 8;   // one epilogue group: two warps per TMEM lane quarter, each takes half of a quarter's 64 columns
 constexpr int kEpiGroups = 2;  // group 0 takes the quarters that land in accumulator buffer 0, group 1 those in buffer 1:
                                // a quarter's epilogue (TMEM load, bias / ReLU / pack, TMEM store, the training-state
                                // stores) is a ~2000-cycle latency chain per warp, and with ONE group the four quarters of
                                // a layer queued behind each other while the tensor core waited for the last one
-constexpr int kMlpThreads = (kEpiGroups * kEpiWarps + 2) * 32;  // + MMA warp + producer warp
+constexpr int kMmaWarps = 2;   // issuing warp i feeds accumulator buffer i (the quarters with (g & 1) == i): issuing a weight
+                               // chunk's four tcgen05.mma (waits, descriptors, commit) is ~360 cycles of one warp's serial
+                               // instruction stream against 128 cycles of tensor-core work -- the kernel's bound with one issuer
+constexpr int kStageWarps = 4;  // warps of epilogue group 0 that also stage a tile's input region, one per TMEM lane quarter
+constexpr int kMlpThreads = (kEpiGroups * kEpiWarps + kMmaWarps + 1) * 32;  // + the weight producer warp
 
 // TMEM columns (32-bit each, 128 lanes): two fp32 accumulator quarters, two bf16 activation buffers (256 values = 128
 // columns each), the embedded input (64 values = 32 columns)
-constexpr uint32_t kColAcc = 0, kColAct = 128, kColEmb = 384, kTmemCols = 512;
+constexpr uint32_t kColAcc = 0, kColAct = 128, kColEmb = 384, kEmbCols = 64, kTmemCols = 512;  // two input regions of 64 columns
 
 struct MlpLayerPlan {
     int n_quarters;  // output quarters (4 for hidden layers; 1 or 2 for the head)
@@ -170,11 +181,18 @@ struct MlpSmem {
     uint64_t full[kStages], empty[kStages];
     uint64_t acc_full[2], acc_free[2];
     uint64_t act_ready[2][4];
-    uint64_t emb_ready;
+    uint64_t emb_ready[2];
     uint32_t tmem_base;
     alignas(16) float bias[(kLayers + 1) * kHid];  // read as float4
+    // head outputs of one warp's 32 points x 32 columns on their way to global memory (pitch 33: conflict-free both ways)
+    float out_stage[kEpiGroups * kEpiWarps][32 * 33];
 };
 
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&r)[8]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), "r"(r[0]), "r"(r[1]),
+                 "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+                 : "memory");
+}
 __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
     asm volatile(
         "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(
@@ -210,17 +228,19 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
     unsigned char* ring = reinterpret_cast<unsigned char*>(align_up_dev(reinterpret_cast<size_t>(s_dyn), 1024));
     MlpSmem& sm = *reinterpret_cast<MlpSmem*>(ring + (size_t)kStages * kChunkBytes);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    constexpr int kEpiThreads = kEpiWarps * 32;
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < kStages; i++) { mbar_init(&sm.full[i], 1); mbar_init(&sm.empty[i], 1); }
-        for (int i = 0; i < 2; i++) { mbar_init(&sm.acc_full[i], 1); mbar_init(&sm.acc_free[i], kEpiThreads); }
-        for (int i = 0; i < 8; i++) mbar_init(&sm.act_ready[i >> 2][i & 3], kEpiThreads);
-        mbar_init(&sm.emb_ready, kEpiThreads);
+        // epilogue -> tensor-core barriers count WARPS: every thread fences its TMEM accesses, the warp converges and one
+        // lane arrives (256 single-thread arrivals on one shared-memory word serialise: three such barriers per quarter
+        // were ~1500 cycles of the ~2300 a quarter took)
+        for (int i = 0; i < 2; i++) { mbar_init(&sm.acc_full[i], 1); mbar_init(&sm.acc_free[i], kEpiWarps); }
+        for (int i = 0; i < 8; i++) mbar_init(&sm.act_ready[i >> 2][i & 3], kEpiWarps);
+        for (int i = 0; i < 2; i++) mbar_init(&sm.emb_ready[i], kStageWarps);
     }
     if (!BWD)
         for (int i = threadIdx.x; i < (kLayers + 1) * kHid; i += blockDim.x) sm.bias[i] = a.bias[i];
-    constexpr int kMmaWarp = kEpiGroups * kEpiWarps, kProducerWarp = kMmaWarp + 1;
+    constexpr int kMmaWarp = kEpiGroups * kEpiWarps, kProducerWarp = kMmaWarp + kMmaWarps;
     if (warp == kMmaWarp) tmem_alloc(&sm.tmem_base, kTmemCols);
     tc_fence_before();
     __syncthreads();
@@ -240,41 +260,62 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
                 }
             }
         }
-    } else if (warp == kMmaWarp) {
-        // ===================== MMA issuer: the whole warp runs the loop, one elected lane issues =====================
+    } else if (warp >= kMmaWarp && warp < kProducerWarp) {
+        // ===================== MMA issuers: the whole warp runs the loop, one elected lane issues =====================
         {
+            const uint32_t iw = (uint32_t)(warp - kMmaWarp);
             uint32_t c = 0, g = 0;
             for (int t = 0; t < my_tiles; t++) {
-                mbar_wait(&sm.emb_ready, t & 1);
+                mbar_wait(&sm.emb_ready[t & 1], (t >> 1) & 1);  // the tile's input region: written while the tile before it ran
                 tc_fence_after();
 #pragma unroll 1
                 for (int l = 0; l < a.n_steps; l++) {
                     const MlpLayerPlan p = a.plan[l];
                     const uint32_t in_col = kColAct + (uint32_t)(l & 1) * 128;  // step l reads buffer l & 1 (l >= 1)
                     const int n_use = (l - 1) >> 1;  // how often this tile has written that buffer before (parity of the wait)
+                    bool slabs_seen = false;  // this warp has waited for the step's input slabs
 #pragma unroll 1
                     for (int q = 0; q < p.n_quarters; q++, g++) {
                         const uint32_t ab = g & 1;
+                        if (ab != iw) { c += (uint32_t)p.n_slabs; continue; }  // the other issuing warp's quarter
+#if RG_MLP_PROF
+                        long long pt0 = clock64(), w_act = 0, w_full = 0;
+#endif
                         mbar_wait(&sm.acc_free[ab], ((g >> 1) & 1) ^ 1);
                         tc_fence_after();
+#if RG_MLP_PROF
+                        long long pt1 = clock64();
+#endif
                         const int n = (q == p.n_quarters - 1) ? p.n_last : kQuarter;
                         const uint32_t idesc = instr_desc(n);
                         const uint32_t d_col = tmem + kColAcc + ab * kQuarter;
                         for (int s = 0; s < p.n_slabs; s++, c++) {
                             uint32_t a_col;
                             if (s < p.n_emb) {
-                                a_col = tmem + kColEmb + (uint32_t)s * 32;
+                                a_col = tmem + kColEmb + (uint32_t)(t & 1) * kEmbCols + (uint32_t)s * 32;
                             } else {
                                 const int sa = s - p.n_emb;  // activation slab = output quarter of the previous step
-                                if (q == 0) {  // later quarters of this step read slabs that quarter 0 has already waited for
+                                if (!slabs_seen) {  // this warp's later quarters of the step read slabs it has already waited for
+#if RG_MLP_PROF
+                                    long long x0 = clock64();
+#endif
                                     mbar_wait(&sm.act_ready[l & 1][sa], n_use & 1);
                                     tc_fence_after();
+#if RG_MLP_PROF
+                                    w_act += clock64() - x0;
+#endif
                                 }
                                 a_col = tmem + in_col + (uint32_t)sa * 32;
                             }
                             const uint32_t st = c % kStages;
+#if RG_MLP_PROF
+                            long long y0 = clock64();
+#endif
                             mbar_wait(&sm.full[st], (c / kStages) & 1);
                             tc_fence_after();
+#if RG_MLP_PROF
+                            w_full += clock64() - y0;
+#endif
                             const uint64_t bd = b_desc(smem_u32(ring + (size_t)st * kChunkBytes));
                             if (elect_one()) {
 #pragma unroll
@@ -286,6 +327,14 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
                         }
                         if (elect_one()) tc_commit(&sm.acc_full[ab]);
                         __syncwarp();
+                        slabs_seen = true;
+#if RG_MLP_PROF
+                        if (PROF_ON && lane == 0) {
+                            unsigned long long* o = g_mlp_prof + (size_t)(l * 4 + q) * 8;
+                            o[0] = (unsigned long long)pt0; o[1] = (unsigned long long)(pt1 - pt0); o[2] = (unsigned long long)w_act;
+                            o[3] = (unsigned long long)w_full; o[4] = (unsigned long long)(clock64() - pt0);
+                        }
+#endif
                     }
                 }
             }
@@ -298,51 +347,56 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
         const int row = lq * 32 + lane;
         uint32_t g = 0;
         const int n_emb = 3 + 6 * a.multires;
-        for (int t = 0; t < my_tiles; t++) {
+        // The input region of a tile (forward: the positional encoding; backward: dL/d head) is written one tile AHEAD, into
+        // the other of two TMEM regions, by four warps of group 0 (one per TMEM lane quarter) before they turn to the
+        // current tile's quarters: the tensor core never waits for it.
+        auto stage_input = [&](int t) {
             const long long pt = ((long long)blockIdx.x + (long long)t * gridDim.x) * kTileM + row;
             const bool valid = pt < a.N;
             const bool in_buf = pt < a.n_pad;
-            if (group != 0) {
-                // the tile's input region is written by group 0 alone
-            } else if (!BWD) {
+            const uint32_t emb_col = kColEmb + (uint32_t)(t & 1) * kEmbCols;
+            if (!BWD) {
                 // ---- positional encoding (utils/time_utils.py:208-256: x, then sin / cos per octave), bf16, into TMEM:
-                //      this thread packs features 32 ch .. 32 ch + 31
+                //      this thread packs its point's 64 features.  One sincosf per coordinate, the higher octaves by
+                //      angle doubling (sin 2t = 2 sin t cos t, cos 2t = 1 - 2 sin^2 t): the error doubles per octave, ~1e-4
+                //      at the tenth against the 4e-3 of the bf16 operand it becomes; thirty accurate sincosf per thread were
+                //      a ~10 000-cycle block in front of every tile
                 float e[64];
                 float xv[3] = {0.f, 0.f, 0.f};
                 if (valid) { xv[0] = a.x[3 * pt]; xv[1] = a.x[3 * pt + 1]; xv[2] = a.x[3 * pt + 2]; }
 #pragma unroll
                 for (int i = 0; i < 64; i++) e[i] = 0.f;
                 e[0] = xv[0]; e[1] = xv[1]; e[2] = xv[2];
-                float f = 1.0f;
+                float sv[3], cv[3];
+#pragma unroll
+                for (int d = 0; d < 3; d++) sincosf(xv[d], &sv[d], &cv[d]);
 #pragma unroll
                 for (int o = 0; o < 10; o++) {
                     if (o < a.multires) {
 #pragma unroll
                         for (int d = 0; d < 3; d++) {
-                            float sv, cv;
-                            sincosf(xv[d] * f, &sv, &cv);
-                            e[3 + 6 * o + d] = sv;
-                            e[6 + 6 * o + d] = cv;
+                            e[3 + 6 * o + d] = sv[d];
+                            e[6 + 6 * o + d] = cv[d];
+                            const float s2 = 2.f * sv[d] * cv[d], c2 = fmaf(-2.f * sv[d], sv[d], 1.f);
+                            sv[d] = s2; cv[d] = c2;
                         }
                     }
-                    f *= 2.0f;
                 }
-                uint32_t pk[16];
+                uint32_t pk[32];
 #pragma unroll
-                for (int i = 0; i < 16; i++) pk[i] = ch ? pack_bf16(e[32 + 2 * i], e[33 + 2 * i]) : pack_bf16(e[2 * i], e[2 * i + 1]);
-                tmem_st16(tmem + lane_base + kColEmb + (uint32_t)ch * 16, pk);
+                for (int i = 0; i < 32; i++) pk[i] = pack_bf16(e[2 * i], e[2 * i + 1]);
+                tmem_st32(tmem + lane_base + emb_col, pk);
                 if (a.emb && in_buf) {  // rows of points past N are written as zeros: the weight-gradient GEMM sums over them
 #pragma unroll
-                    for (int i = 0; i < 32; i++) {
-                        const int fi = ch * 32 + i;
-                        if (fi < n_emb) a.emb[(size_t)fi * a.n_pad + pt] = __float2bfloat16_rn(valid ? (ch ? e[32 + i] : e[i]) : 0.f);
-                    }
+                    for (int i = 0; i < 64; i++)
+                        if (i < n_emb) a.emb[(size_t)i * a.n_pad + pt] = __float2bfloat16_rn(valid ? e[i] : 0.f);
                 }
             } else {
                 // ---- dL/d(head pre-activation) of this point: the upstream gradient (times the sigmoid's derivative)
                 const int n_in = a.plan[0].n_emb;  // slabs of 64 head outputs
 #pragma unroll 1
-                for (int sl = 0; sl < n_in; sl++) {
+                for (int sc = 0; sc < 2 * n_in; sc++) {
+                    const int sl = sc >> 1, ch = sc & 1;
                     uint32_t pk[16];
 #pragma unroll
                     for (int i = 0; i < 16; i++) {
@@ -362,15 +416,41 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
                         }
                         pk[i] = pack_bf16(g2[0], g2[1]);
                     }
-                    tmem_st16(tmem + lane_base + kColEmb + (uint32_t)sl * 32 + (uint32_t)ch * 16, pk);
+                    tmem_st16(tmem + lane_base + emb_col + (uint32_t)sl * 32 + (uint32_t)ch * 16, pk);
                     if (in_buf) store_features(a.dz + ((size_t)kLayers * kHid + (size_t)sl * 64 + (size_t)ch * 32) * a.n_pad + pt, a.n_pad, pk);
                 }
             }
-            if (group == 0) {
-                tmem_st_wait();
-                tc_fence_before();
-                mbar_arrive(&sm.emb_ready);
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm.emb_ready[t & 1]);
+        };
+        const bool stages = group == 0 && ch == 0;
+        if (stages && my_tiles > 0) stage_input(0);
+        // deferred part of the head's epilogue (see there)
+        float* const stg = sm.out_stage[warp];
+        long long pend_pt0 = 0;
+        int pend_r = 0, pend_rows = 0, pend_cols = 0, pend_col0 = 0;
+        float pend_bias = 0.f;
+        auto head_piece = [&]() {
+            float z[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++) z[u] = stg[min(pend_r + u, 31) * 33 + lane] + pend_bias;
+            if (a.out_act == 1) {
+#pragma unroll
+                for (int u = 0; u < 8; u++) z[u] = __fdividef(1.0f, 1.0f + __expf(-z[u]));
             }
+#pragma unroll
+            for (int u = 0; u < 8; u++)
+                if (pend_r + u < pend_rows && lane < pend_cols)
+                    a.out[(size_t)(pend_pt0 + pend_r + u) * a.out_ch + pend_col0 + lane] = z[u];
+            pend_r += 8;
+        };
+        for (int t = 0; t < my_tiles; t++) {
+            const long long pt = ((long long)blockIdx.x + (long long)t * gridDim.x) * kTileM + row;
+            const bool valid = pt < a.N;
+            const bool in_buf = pt < a.n_pad;
+            if (stages && t + 1 < my_tiles) stage_input(t + 1);
 #pragma unroll 1
             for (int l = 0; l < a.n_steps; l++) {
                 const MlpLayerPlan p = a.plan[l];
@@ -380,15 +460,22 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
                 for (int q = 0; q < p.n_quarters; q++, g++) {
                     const uint32_t ab = g & 1;
                     if (ab != group) continue;
+#if RG_MLP_PROF
+                    long long e0 = clock64();
+#endif
                     mbar_wait(&sm.acc_full[ab], (g >> 1) & 1);
                     tc_fence_after();
+#if RG_MLP_PROF
+                    long long e1 = clock64();
+#endif
                     uint32_t v[32];
                     tmem_ld32(tmem + lane_base + kColAcc + ab * kQuarter + (uint32_t)ch * 32, v);
                     tmem_ld_wait();
                     // the accumulator is in registers: hand the buffer back before doing anything else (the tensor core is
                     // waiting for it two quarters ahead)
                     tc_fence_before();
-                    mbar_arrive(&sm.acc_free[ab]);
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&sm.acc_free[ab]);
                     const int col0 = q * kQuarter + ch * 32;  // first of this thread's 32 columns
                     if (BWD || l < kLayers) {
                         uint32_t pk[16];
@@ -426,28 +513,50 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
                         tmem_st16(tmem + lane_base + out_col + (uint32_t)q * 32 + (uint32_t)ch * 16, pk);
                         tmem_st_wait();
                         tc_fence_before();
-                        mbar_arrive(&sm.act_ready[(l + 1) & 1][q]);  // the next step may start on this k-slab
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&sm.act_ready[(l + 1) & 1][q]);  // the next step may start on this k-slab
+#if RG_MLP_PROF
+                        if (PROF_ON && (warp & 7) == 0 && lane == 0) {
+                            unsigned long long* o = g_mlp_prof + 1024 + (size_t)(l * 4 + q) * 8;
+                            o[0] = (unsigned long long)e0; o[1] = (unsigned long long)(e1 - e0); o[2] = (unsigned long long)(clock64() - e1);
+                        }
+#endif
                         __nv_bfloat16* store = BWD ? a.dz : a.acts;  // training state, feature-major
                         if (store && in_buf) {
                             store_features(store + ((size_t)slot * kHid + (size_t)col0) * a.n_pad + (size_t)pt, a.n_pad, pk);
                             if (!BWD) *mword = bits;
                         }
+                        if (!BWD && pend_r < pend_rows) head_piece();
                     } else {
-                        if (valid) {
+                        // The head's outputs leave through shared memory, transposed: a thread holds one point's columns; a
+                        // lane of head_piece() takes one COLUMN, so that a store instruction writes one point's columns side
+                        // by side.  Only the staging happens here: the loop over the points (exp, divide, store: ~6000 cycles
+                        // for one warp) is cut into pieces of eight points that run behind the warp's NEXT quarters, where it
+                        // has slack -- in one block it held up the first quarters of every following tile.
+                        while (pend_r < pend_rows) head_piece();  // (the previous tile's, if any is left)
+                        const int n_cols = min(32, a.out_ch - col0);  // this warp's columns of the head (<= 0: none)
+                        if (n_cols > 0) {
 #pragma unroll
-                            for (int i = 0; i < 32; i++) {
-                                const int col = col0 + i;
-                                if (col < a.out_ch) {
-                                    float z = __uint_as_float(v[i]) + bias[col];
-                                    if (a.out_act == 1) z = 1.0f / (1.0f + expf(-z));
-                                    a.out[(size_t)pt * a.out_ch + col] = z;
-                                }
-                            }
+                            for (int i = 0; i < 32; i++) stg[lane * 33 + i] = __uint_as_float(v[i]);
+                            __syncwarp();
+                            pend_pt0 = pt - lane;  // the warp's first point
+                            pend_rows = (int)min((long long)32, a.N - pend_pt0);
+                            pend_r = 0;
+                            pend_cols = n_cols;
+                            pend_col0 = col0;
+                            pend_bias = lane < n_cols ? bias[col0 + lane] : 0.f;
                         }
+#if RG_MLP_PROF
+                        if (PROF_ON && (warp & 7) == 0 && lane == 0) {
+                            unsigned long long* o = g_mlp_prof + 1024 + (size_t)(l * 4 + q) * 8;
+                            o[0] = (unsigned long long)e0; o[1] = (unsigned long long)(e1 - e0); o[2] = (unsigned long long)(clock64() - e1);
+                        }
+#endif
                     }
                 }
             }
         }
+        while (pend_r < pend_rows) head_piece();
     }
     tc_fence_before();
     __syncthreads();
@@ -806,6 +915,12 @@ static int launch_chain(bool bwd, MlpArgs& a, cudaStream_t stream) {
     else mlp_chain_kernel<false><<<grid, kMlpThreads, smem, stream>>>(a);
     return 0;
 }
+
+#if RG_MLP_PROF
+extern "C" int rg_debug_mlp_prof_read(unsigned long long* host, int n) {
+    return cudaMemcpyFromSymbol(host, g_mlp_prof, sizeof(unsigned long long) * (size_t)n) == cudaSuccess ? 0 : -1;
+}
+#endif
 
 int rg_mlp_forward(int N, int multires, int out_ch, int out_act, const float* x, const void* packed, const float* bias,
                    float* out, void* acts, void* emb, void* relu_mask, long long n_pad, rg_stream_t stream_) {
