@@ -1,12 +1,10 @@
 #!/bin/bash
 cd /root/repo
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_gpu_mlp.py tests/test_gpu_fused.py -x -q -m gpu -k "mlp" > gpurun_out/mlp_tests.log 2>&1; echo "tests rc=$?"
-tail -n 3 gpurun_out/mlp_tests.log
-RG_LIB=/root/repo/riggs_b200/lib/libriggs_b200_prof.so timeout 120 python profiles/tools/mlp_prof.py > gpurun_out/mlp_prof.txt 2>&1
-sed -n 2,8p gpurun_out/mlp_prof.txt; tail -n 2 gpurun_out/mlp_prof.txt
-timeout 300 python bench.py --mlps on --steps 10 --no-cpu-baseline --no-ref-cuda > gpurun_out/mlp_on.json 2> gpurun_out/mlp_on.err
+python -m pytest tests/test_gpu_fused.py tests/test_gpu_skin.py tests/test_gpu_knn_and_api.py -x -q -m gpu > gpurun_out/t.log 2>&1; echo "tests rc=$?"
+tail -n 3 gpurun_out/t.log
+python bench.py --steps 30 --no-cpu-baseline --no-ref-cuda > gpurun_out/c0.json 2> gpurun_out/c0.err
 python -c "
 import json,sys
-d=json.loads(open('gpurun_out/mlp_on.json').read().strip().splitlines()[-1]); print(d['ms_per_step'], d['value'], {k:round(v['ms_per_launch'],4) for k,v in d['kernels'].items() if k.startswith('mlp')})
+d=json.loads(open('gpurun_out/c0.json').read().strip().splitlines()[-1]); print(d['ms_per_step'], d['value'], d['e2e']['value'], d['gpu_launches'])
 "

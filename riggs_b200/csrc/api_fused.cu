@@ -10,12 +10,6 @@
 using namespace rg;
 
 namespace {
-// d_node_radius_raw leaves the workspace's accumulator either as a copy or, for the later views of a batch, as a sum
-__global__ void small_copy_or_add_kernel(float* __restrict__ dst, const float* __restrict__ src, int n, int add) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) dst[i] = add ? dst[i] + src[i] : src[i];
-}
-
 char* abase(char* p) { return reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(p), 256)); }
 bool al16(const void* p) { return (reinterpret_cast<size_t>(p) & 15) == 0; }
 
@@ -193,11 +187,10 @@ int rg_skinned_backward_part(const RgSkinnedScene* s, const RgWorkspace* w, int 
         if (launch_gauss_skin_backward(ga, sb, stream)) return -1;
     }
     if (phases & 4) {
+        // d_node_radius_raw leaves the workspace's accumulator inside the same launch: a copy or, for the later views of a batch, a sum
         if (launch_fk_backward(1, s->J, s->local_rot, s->joints, s->parents, fk.G, fk.dG, dL_dnodes, d_local_rot,
-                               d_global_trans, fk.dtrans, stream))
+                               d_global_trans, fk.dtrans, stream, d_node_radius_raw, fk.dradius, (phases & 8) != 0))
             return -1;
-        if (d_node_radius_raw)
-            small_copy_or_add_kernel<<<1, 128, 0, stream>>>(d_node_radius_raw, fk.dradius, s->J, (phases & 8) != 0);
     }
     return check_launch("rg_skinned_backward", stream, false);
 }

@@ -118,7 +118,9 @@ __global__ void __launch_bounds__(32) fk_backward_kernel(int F, int J, const flo
                                                          const float* __restrict__ joints, const int* __restrict__ parents,
                                                          const float* __restrict__ G, const float* __restrict__ dG_in,
                                                          const float* __restrict__ dposed, float* __restrict__ dlocal_rot,
-                                                         float* __restrict__ dgtrans, const float* __restrict__ dgtrans_add) {
+                                                         float* __restrict__ dgtrans, const float* __restrict__ dgtrans_add,
+                                                         float* __restrict__ radius_dst, const float* __restrict__ radius_src,
+                                                         int radius_add) {
     __shared__ float s_W[kMaxJoints * 12];   // running dL/dG_i; afterwards dL/dT_i (local rotation + translation)
     __shared__ float s_G[kMaxJoints * 12];
     __shared__ float s_R[kMaxJoints * 9];
@@ -127,6 +129,10 @@ __global__ void __launch_bounds__(32) fk_backward_kernel(int F, int J, const flo
     const int f = blockIdx.x, lane = threadIdx.x;
     const float* q = local_rot + (size_t)f * J * 4;
     float gt[3] = {0, 0, 0};
+    // rides along (fused entry): dL/d node_radius_raw leaves the workspace's accumulator as a copy or, for the later views of
+    // a batch, as a sum -- J floats that had a launch of their own
+    if (radius_dst && f == 0)
+        for (int k = lane; k < J; k += 32) radius_dst[k] = radius_add ? radius_dst[k] + radius_src[k] : radius_src[k];
     for (int k = lane; k < J * 12; k += 32) s_G[k] = G[(size_t)f * J * 12 + k];
     for (int i = lane; i < J; i += 32) {
         float* Wi = s_W + 12 * i;
@@ -433,12 +439,12 @@ int launch_fk_forward(int F, int J, const float* local_rot, const float* gtrans,
 
 int launch_fk_backward(int F, int J, const float* local_rot, const float* joints, const int* parents, const float* G,
                        const float* dG, const float* dposed, float* dlocal_rot, float* dgtrans, const float* dgtrans_add,
-                       cudaStream_t stream) {
+                       cudaStream_t stream, float* radius_dst, const float* radius_src, int radius_add) {
     if (F == 0 || J == 0) return 0;
     if (J > kMaxJoints) { set_error("forward kinematics: at most 128 joints"); return -1; }
     LaunchScope ls("fk_backward", stream);
     fk_backward_kernel<<<F, 32, 0, stream>>>(F, J, local_rot, joints, parents, G, dG, dposed, dlocal_rot, dgtrans,
-                                            dgtrans_add);
+                                            dgtrans_add, radius_dst, radius_src, radius_add);
     return 0;
 }
 

@@ -49,7 +49,7 @@ int launch_fk_forward(int F, int J, const float* local_rot, const float* gtrans,
                       const int* parents, float* G, float* node_rot, float* posed, cudaStream_t stream);
 int launch_fk_backward(int F, int J, const float* local_rot, const float* joints, const int* parents, const float* G,
                        const float* dG, const float* dposed, float* dlocal_rot, float* dgtrans, const float* dgtrans_add,
-                       cudaStream_t stream);
+                       cudaStream_t stream, float* radius_dst = nullptr, const float* radius_src = nullptr, int radius_add = 0);
 int launch_skin_forward(const SkinArgs& a, cudaStream_t stream);
 int launch_skin_backward(const SkinBwdArgs& a, cudaStream_t stream);
 

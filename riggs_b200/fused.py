@@ -327,6 +327,27 @@ class _SkinnedRender(torch.autograd.Function):
                 d_mask, d_mlp, d_off, d_mean2D, None)
 
 
+class _RenderResult(dict):
+    """The result dict of ``render()``; ``visibility_filter`` (= ``radii > 0``, one more pass over the P radii) is computed
+    when it is first asked for -- a training step that does not densify never asks."""
+
+    def __missing__(self, key):
+        if key == "visibility_filter":
+            v = self["radii"] > 0
+            self[key] = v
+            return v
+        raise KeyError(key)
+
+    def get(self, key, default=None):
+        try:
+            return self[key]
+        except KeyError:
+            return default
+
+    def __contains__(self, key):
+        return key == "visibility_filter" or dict.__contains__(self, key)
+
+
 def render_skinned(viewpoint_camera, pc, skeleton, pose: Dict[str, torch.Tensor], pipe, bg_color: torch.Tensor,
                    scaling_modifier=1.0, mlp_weight=None, offsets=None, zero_d_rotation: Optional[bool] = None,
                    debug_outputs=None, pool: Optional[WorkspacePool] = None, grad_out=None, reduce=None,
@@ -368,8 +389,8 @@ def render_skinned(viewpoint_camera, pc, skeleton, pose: Dict[str, torch.Tensor]
     color, depth, alpha, radii, d_nodes = _SkinnedRender.apply(
         xyz, pc._scaling, pc._rotation, pc._opacity, pc._features_dc, pc._features_rest, skeleton._node_radius,
         pose["local_rotation"], pose["global_trans"], mask, mlp_weight, offsets, screenspace_points, cfg)
-    return {"render": color, "viewspace_points": screenspace_points, "visibility_filter": radii > 0, "radii": radii,
-            "depth": depth, "alpha": alpha, "bg_color": bg_color, "d_nodes": d_nodes, "status": cfg.get("_status")}
+    return _RenderResult({"render": color, "viewspace_points": screenspace_points, "radii": radii, "depth": depth,
+                          "alpha": alpha, "bg_color": bg_color, "d_nodes": d_nodes, "status": cfg.get("_status")})
 
 
 def frame_overflowed(out) -> bool:

@@ -557,6 +557,20 @@ def test_pose_sequence_renderer_renders_every_frame_of_the_sequence():
     assert seq.launches_per_replay >= 8
 
 
+def test_result_dict_computes_the_visibility_filter_on_demand():
+    from riggs_b200.fused import WorkspacePool, render_skinned
+    scene, pc, warp, cam = _setup("tiny", dict(n_views=1))
+    pose, _, _ = _leafs(scene)
+    with torch.no_grad():
+        out = render_skinned(cam, pc, warp, pose, _Pipe(), torch.zeros(3, device="cuda"), pool=WorkspacePool())
+    assert "visibility_filter" in out and not dict.__contains__(out, "visibility_filter")
+    vis = out["visibility_filter"]
+    assert vis.dtype == torch.bool and torch.equal(vis, out["radii"] > 0) and int(vis.sum()) > 0
+    assert out.get("visibility_filter") is vis and out.get("no such key", 7) == 7
+    with pytest.raises(KeyError):
+        out["no such key"]
+
+
 def test_second_backward_raises_a_clear_error():
     from riggs_b200 import _lib
     from riggs_b200.fused import WorkspacePool, render_skinned
