@@ -45,7 +45,9 @@ constexpr int kSkipInto = 5;     // the embedded input is concatenated in front 
 constexpr int kTileM = 128;      // points per tile = TMEM lanes
 constexpr int kQuarter = 64;     // output columns per accumulator buffer = input columns per k-slab
 constexpr int kChunkBytes = kQuarter * kQuarter * 2;  // one weight chunk: 64 outputs x 64 inputs, bf16 = 8 KB
-constexpr int kStages = 18;      // ring depth: 144 KB of weights in flight / resident
+constexpr int kStageBytes = 2 * kChunkBytes;  // a ring stage holds TWO chunks (consecutive k-slabs of one quarter): one copy, one
+                                              // wait, one descriptor and one commit per eight tcgen05.mma instead of per four
+constexpr int kStages = 9;       // ring depth: 144 KB of weights in flight / resident
 constexpr int kEpiWarps = 8;   // one epilogue group: two warps per TMEM lane quarter, each takes half of a quarter's 64 columns
 constexpr int kEpiGroups = 2;  // group 0 takes the quarters that land in accumulator buffer 0, group 1 those in buffer 1:
                                // a quarter's epilogue (TMEM load, bias / ReLU / pack, TMEM store, the training-state
@@ -226,7 +228,7 @@ template <bool BWD>
 __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
     extern __shared__ __align__(1024) unsigned char s_dyn[];
     unsigned char* ring = reinterpret_cast<unsigned char*>(align_up_dev(reinterpret_cast<size_t>(s_dyn), 1024));
-    MlpSmem& sm = *reinterpret_cast<MlpSmem*>(ring + (size_t)kStages * kChunkBytes);
+    MlpSmem& sm = *reinterpret_cast<MlpSmem*>(ring + (size_t)kStages * kStageBytes);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
@@ -251,12 +253,21 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
     if (warp == kProducerWarp) {
         // ===================== producer: weight chunks, the same sequence for every tile =====================
         if (lane == 0) {
-            uint32_t c = 0;
+            uint32_t c = 0;  // ring stages handed out so far
             for (int t = 0; t < my_tiles; t++) {
-                for (int j = 0; j < a.total_chunks; j++, c++) {
-                    const uint32_t st = c % kStages;
-                    mbar_wait(&sm.empty[st], ((c / kStages) & 1) ^ 1);  // passes at once the first time round
-                    bulk_load(ring + (size_t)st * kChunkBytes, a.w_packed + (size_t)j * kChunkBytes, kChunkBytes, &sm.full[st]);
+                int j = 0;   // chunk index inside the packed image (consumption order)
+                for (int l = 0; l < a.n_steps; l++) {
+                    const int n_slabs = a.plan[l].n_slabs, n_q = a.plan[l].n_quarters;
+                    for (int q = 0; q < n_q; q++) {
+                        for (int s = 0; s < n_slabs; s += 2, c++) {
+                            const int n = min(2, n_slabs - s);  // the quarter's slabs s, s + 1 are adjacent chunks of the image
+                            const uint32_t st = c % kStages;
+                            mbar_wait(&sm.empty[st], ((c / kStages) & 1) ^ 1);  // passes at once the first time round
+                            bulk_load(ring + (size_t)st * kStageBytes, a.w_packed + (size_t)j * kChunkBytes, (uint32_t)(n * kChunkBytes),
+                                      &sm.full[st]);
+                            j += n;
+                        }
+                    }
                 }
             }
         }
@@ -277,7 +288,7 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
 #pragma unroll 1
                     for (int q = 0; q < p.n_quarters; q++, g++) {
                         const uint32_t ab = g & 1;
-                        if (ab != iw) { c += (uint32_t)p.n_slabs; continue; }  // the other issuing warp's quarter
+                        if (ab != iw) { c += (uint32_t)((p.n_slabs + 1) >> 1); continue; }  // the other issuing warp's quarter
 #if RG_MLP_PROF
                         long long pt0 = clock64(), w_act = 0, w_full = 0;
 #endif
@@ -289,23 +300,29 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
                         const int n = (q == p.n_quarters - 1) ? p.n_last : kQuarter;
                         const uint32_t idesc = instr_desc(n);
                         const uint32_t d_col = tmem + kColAcc + ab * kQuarter;
-                        for (int s = 0; s < p.n_slabs; s++, c++) {
-                            uint32_t a_col;
-                            if (s < p.n_emb) {
-                                a_col = tmem + kColEmb + (uint32_t)(t & 1) * kEmbCols + (uint32_t)s * 32;
-                            } else {
-                                const int sa = s - p.n_emb;  // activation slab = output quarter of the previous step
-                                if (!slabs_seen) {  // this warp's later quarters of the step read slabs it has already waited for
+                        for (int s0 = 0; s0 < p.n_slabs; s0 += 2, c++) {
+                            const int n_here = min(2, p.n_slabs - s0);  // slabs in this ring stage
+                            uint32_t a_cols[2] = {0u, 0u};
+#pragma unroll
+                            for (int h = 0; h < 2; h++) {
+                                const int s = s0 + h;
+                                if (h >= n_here) break;
+                                if (s < p.n_emb) {
+                                    a_cols[h] = tmem + kColEmb + (uint32_t)(t & 1) * kEmbCols + (uint32_t)s * 32;
+                                } else {
+                                    const int sa = s - p.n_emb;  // activation slab = output quarter of the previous step
+                                    if (!slabs_seen) {  // this warp's later quarters of the step read slabs it has already waited for
 #if RG_MLP_PROF
-                                    long long x0 = clock64();
+                                        long long x0 = clock64();
 #endif
-                                    mbar_wait(&sm.act_ready[l & 1][sa], n_use & 1);
-                                    tc_fence_after();
+                                        mbar_wait(&sm.act_ready[l & 1][sa], n_use & 1);
+                                        tc_fence_after();
 #if RG_MLP_PROF
-                                    w_act += clock64() - x0;
+                                        w_act += clock64() - x0;
 #endif
+                                    }
+                                    a_cols[h] = tmem + in_col + (uint32_t)sa * 32;
                                 }
-                                a_col = tmem + in_col + (uint32_t)sa * 32;
                             }
                             const uint32_t st = c % kStages;
 #if RG_MLP_PROF
@@ -316,12 +333,17 @@ __global__ void __launch_bounds__(kMlpThreads, 1) mlp_chain_kernel(MlpArgs a) {
 #if RG_MLP_PROF
                             w_full += clock64() - y0;
 #endif
-                            const uint64_t bd = b_desc(smem_u32(ring + (size_t)st * kChunkBytes));
+                            const uint64_t bd = b_desc(smem_u32(ring + (size_t)st * kStageBytes));
                             if (elect_one()) {
 #pragma unroll
                                 for (int k = 0; k < 4; k++)  // the k-step of 16 columns starts 32 bytes (2 address units) further on
-                                    mma_ts(d_col, a_col + (uint32_t)k * 8, bd + (uint64_t)(k * 2), idesc, (s | k) != 0);
-                                tc_commit(&sm.empty[st]);  // the chunk's slot is free once these MMAs have read it
+                                    mma_ts(d_col, a_cols[0] + (uint32_t)k * 8, bd + (uint64_t)(k * 2), idesc, (s0 | k) != 0);
+                                if (n_here == 2) {
+#pragma unroll
+                                    for (int k = 0; k < 4; k++)  // the second chunk of the stage: 8 KB = 512 address units further on
+                                        mma_ts(d_col, a_cols[1] + (uint32_t)k * 8, bd + (uint64_t)(kChunkBytes / 16 + k * 2), idesc, 1u);
+                                }
+                                tc_commit(&sm.empty[st]);  // the stage is free once these MMAs have read it
                             }
                             __syncwarp();
                         }
@@ -907,7 +929,7 @@ int rg_mlp_pack(int emb_cols, int out_ch, const float* const* weights, const int
 }
 
 static int launch_chain(bool bwd, MlpArgs& a, cudaStream_t stream) {
-    const size_t smem = (size_t)kStages * kChunkBytes + sizeof(MlpSmem) + 1024;
+    const size_t smem = (size_t)kStages * kStageBytes + sizeof(MlpSmem) + 1024;
     const void* fn = bwd ? reinterpret_cast<const void*>(mlp_chain_kernel<true>) : reinterpret_cast<const void*>(mlp_chain_kernel<false>);
     if (ensure_dyn_smem(fn, (int)smem)) return -1;
     const int grid = std::min(a.n_tiles, RG_NUM_SMS);
