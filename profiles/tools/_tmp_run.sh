@@ -1,5 +1,5 @@
 #!/bin/bash
 cd /root/repo
 mkdir -p gpurun_out
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/z_launches.csv python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-ref-cuda --no-graph > gpurun_out/ncu_bench.log 2>&1; echo "ncu rc=$?"
-wc -l gpurun_out/z_launches.csv
+timeout 300 python -m pytest tests/test_gpu_mlp.py -x -q -m gpu > gpurun_out/mlp_tests.log 2>&1; echo "tests rc=$?"
+tail -n 12 gpurun_out/mlp_tests.log

@@ -28,7 +28,7 @@ def _modules(J, seed=3):
     return wm, dn
 
 
-@pytest.mark.parametrize("N,J", [(128, 24), (1000, 24), (40_000, 60), (300, 7)])
+@pytest.mark.parametrize("N,J", [(128, 24), (1000, 24), (40_000, 60), (300, 7), (700, 100)])  # J = 100: a head of two quarters
 def test_fused_mlp_forward_matches_torch(N, J):
     from riggs_b200.mlp import FusedSkipMLP
     wm, dn = _modules(J)
@@ -101,7 +101,7 @@ def _emulated_forward(mod, x, pose=None):
     return torch.sigmoid(out) if hasattr(mod, "weight_predict") else out
 
 
-@pytest.mark.parametrize("N,J", [(1000, 24), (20_000, 24), (257, 7)])
+@pytest.mark.parametrize("N,J", [(1000, 24), (20_000, 24), (257, 7), (700, 100)])
 def test_fused_mlp_backward_matches_torch_autograd(N, J):
     """dL/d(parameters) of both MLPs through the tensor-core backward (chain + weight-gradient GEMMs) against torch
     autograd, for a seeded upstream gradient."""
