@@ -48,9 +48,8 @@ __global__ void __launch_bounds__(512) allreduce_multimem_kernel(float* __restri
 struct PeerPtrs {
     float* p[8];
 };
-template <int WORLD>
+template <int WORLD, int kUnroll = (WORLD <= 2 ? 4 : 2)>
 __global__ void __launch_bounds__(512) allreduce_p2p_kernel(PeerPtrs bufs, size_t w0, size_t w1) {
-    constexpr int kUnroll = WORLD <= 2 ? 4 : 2;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     size_t i = w0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     for (; i + (kUnroll - 1) * stride < w1; i += kUnroll * stride) {
@@ -193,7 +192,11 @@ extern "C" int rg_allreduce_p2p(float* const* peer_bufs, size_t n_floats, int ra
     if (w1 == w0) return 0;
     LaunchScope ls("allreduce_p2p", stream);
     const int nb = allreduce_blocks();
-    if (world == 2) allreduce_p2p_kernel<2><<<nb, 512, 0, stream>>>(pp, w0, w1);
+    static const int unroll = [] { const char* e = std::getenv("RG_AR_UNROLL"); return e ? std::atoi(e) : 0; }();  // tuning aid
+    if (world == 2 && unroll == 8) allreduce_p2p_kernel<2, 8><<<nb, 512, 0, stream>>>(pp, w0, w1);
+    else if (world == 2 && unroll == 2) allreduce_p2p_kernel<2, 2><<<nb, 512, 0, stream>>>(pp, w0, w1);
+    else if (world == 2) allreduce_p2p_kernel<2><<<nb, 512, 0, stream>>>(pp, w0, w1);
+    else if (world == 4 && unroll == 4) allreduce_p2p_kernel<4, 4><<<nb, 512, 0, stream>>>(pp, w0, w1);
     else if (world == 4) allreduce_p2p_kernel<4><<<nb, 512, 0, stream>>>(pp, w0, w1);
     else allreduce_p2p_kernel<8><<<nb, 512, 0, stream>>>(pp, w0, w1);
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
