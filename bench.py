@@ -134,8 +134,8 @@ def algorithmic_bytes(P, R, HW, in_P=236, out_P=248, passes=6, n_grad=0, world=1
     if world > 1:
         # bytes per NVLink direction and GPU: the switch-reduced kernel moves (N+1)/N of the buffer each way
         per["allreduce_multimem"] = int(n_grad * 4 * (world + 1) / world)
-        # bytes ONE link direction carries: the rank loads its slice from the N-1 peers (in) and stores the sum to them (out)
-        per["allreduce_p2p"] = int(n_grad * 4 * (world - 1) / world)
+        # the peer kernel: a GPU receives (N-1)/N of the buffer through its own loads and (N-1)/N through its peers' stores
+        per["allreduce_p2p"] = int(n_grad * 4 * 2 * (world - 1) / world)
     total = P * (2 * in_P + 336) + R * (148 + 24 * passes) + HW * 52
     own = sum(per[k] for k in ("skin_preprocess", "gauss_skin_backward", "depth_sort", "tile_count", "tile_scatter",
                                "blend_forward", "blend_backward")) + HW * 3 * 12
