@@ -1,8 +1,9 @@
 #!/bin/bash
 cd /root/repo
-N=2
-TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
-p=29720
-for cfg in "4 296" "8 296" "8 592" "4 592" "2 592" "8 1184"; do set -- $cfg; p=$((p+1))
-RG_AR_UNROLL=$1 RG_AR_BLOCKS=$2 timeout 120 $TR --master-port $p profiles/tools/ar_time.py 2>/dev/null | grep world
-done
+mkdir -p gpurun_out
+python -m pytest tests/test_gpu_knn_and_api.py -x -q -m gpu -k "l1 or loss" > gpurun_out/t.log 2>&1; echo "tests rc=$?"; tail -n 2 gpurun_out/t.log
+python bench.py --steps 30 --no-cpu-baseline --no-ref-cuda > gpurun_out/c0.json 2> gpurun_out/c0.err
+python -c "
+import json,sys
+d=json.loads(open('gpurun_out/c0.json').read().strip().splitlines()[-1]); print(d['ms_per_step'], d['value'], d['e2e']['value'], {k:round(v['ms_per_launch'],4) for k,v in d['kernels'].items() if k in ('l1_loss','fk_forward','fk_backward','tile_offsets')})
+"

@@ -22,7 +22,23 @@ __global__ void __launch_bounds__(kLossThreads) l1_loss_kernel(size_t n, const f
     const float4* b4 = reinterpret_cast<const float4*>(b);
     float4* g4 = reinterpret_cast<float4*>(grad);
     auto sgn = [&](float d) { return d > 0.f ? inv_n : (d < 0.f ? -inv_n : 0.f); };
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    // four independent 16-byte pairs in flight per thread: the grid is small on purpose (every CTA ends with an atomic on
+    // the same ticket word, and those serialise in L2), so a thread covers several words and must not wait for each in turn
+    constexpr int kU = 4;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + (kU - 1) * stride < n4; i += kU * stride) {
+        float4 x[kU], y[kU];
+#pragma unroll
+        for (int u = 0; u < kU; u++) { x[u] = a4[i + u * stride]; y[u] = b4[i + u * stride]; }
+#pragma unroll
+        for (int u = 0; u < kU; u++) {
+            const float4 d = {x[u].x - y[u].x, x[u].y - y[u].y, x[u].z - y[u].z, x[u].w - y[u].w};
+            acc += (fabsf(d.x) + fabsf(d.y)) + (fabsf(d.z) + fabsf(d.w));
+            g4[i + u * stride] = {sgn(d.x), sgn(d.y), sgn(d.z), sgn(d.w)};
+        }
+    }
+    for (; i < n4; i += stride) {
         const float4 x = a4[i], y = b4[i];
         const float4 d = {x.x - y.x, x.y - y.y, x.z - y.z, x.w - y.w};
         acc += (fabsf(d.x) + fabsf(d.y)) + (fabsf(d.z) + fabsf(d.w));
@@ -85,7 +101,7 @@ int rg_l1_loss(size_t n, const float* output, const float* gt, float* loss, floa
     float* partial = static_cast<float*>(scratch);
     unsigned int* ticket = reinterpret_cast<unsigned int*>(static_cast<char*>(scratch) + sizeof(float) * 1024);
     size_t want = ((n >> 2) + kLossThreads - 1) / kLossThreads;
-    const int blocks = (int)(want < 1 ? 1 : (want > 592 ? 592 : want));  // 148 SMs x 4 resident CTAs
+    const int blocks = (int)(want < 1 ? 1 : (want > 148 ? 148 : want));  // one CTA per SM: 148 ticket atomics, not 592
     LaunchScope ls("l1_loss", stream);
     l1_loss_kernel<<<blocks, kLossThreads, 0, stream>>>(n, output, gt, grad, loss, partial, ticket);
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
