@@ -631,7 +631,8 @@ def test_fused_dual_quaternion_blending_matches_unfused(over):
 
 @pytest.mark.parametrize("name,over,count", [("small", dict(soft_mask=True, with_offsets=True), 2), ("small", dict(), 3),
                                              ("ragged", dict(), 4), ("C2", dict(n_views=1), 8),
-                                             ("C4", dict(N=60_000, n_views=1), 3)])  # 1080p: the binning kernels run in bands
+                                             ("C4", dict(N=60_000, n_views=1), 3),  # 1080p: the binning kernels run in bands
+                                             ("C4", dict(N=20_000, n_views=1, scale_mu=0.15), 5)])  # ... wide rectangles, cut by bands and parts
 def test_view_split_emulated(name, over, count):
     """One view split over `count` parts (dist.ViewSplit; every part bins and blends the tile rows y % count == index),
     the parts run one after the other on this GPU.  Forward: each part touches only its rows and those rows are

@@ -46,6 +46,7 @@ def _run_ref(cin, cots=None):
 # worth of Gaussians (chunks longer than 128), and almost everything culled.
 BINNING_CASES = [
     ("C4", dict(N=60_000, n_views=1), (0.0, 0.0, 0.0)),
+    ("C4", dict(N=20_000, n_views=1, scale_mu=0.15), (0.0, 0.0, 0.0)),  # 1080p: rectangles far wider than a warp, cut by the bands
     ("small", dict(N=30_000, scale_mu=0.12, n_views=1), (0.0, 0.0, 0.0)),
     ("small", dict(N=600_000, n_views=1, scale_mu=0.004), (0.0, 0.0, 0.0)),
     ("tiny", dict(cam_radius=0.05, n_views=1), (0.0, 0.0, 0.0)),
