@@ -50,3 +50,33 @@ def test_no_cpu_fallback():
         _C.rasterize_gaussians(torch.zeros(3), torch.zeros(4, 3), e, torch.ones(4, 1), torch.ones(4, 3),
                                torch.ones(4, 4), 1.0, e, torch.eye(4), torch.eye(4), 0.5, 0.5, 16, 16,
                                torch.zeros(4, 16, 3), 3, torch.zeros(3), False, False)
+
+
+def test_scene_struct_layout_matches_the_header():
+    """RgSkinnedScene in riggs_b200/_lib.py mirrors the header field by field, in order (fields are only ever appended)."""
+    import re
+    text = open(os.path.join(ROOT, "include", "riggs_b200.h")).read()
+    body = text[text.index("typedef struct RgSkinnedScene {"):text.index("} RgSkinnedScene;")]
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    names = []
+    for decl in body.split(";"):
+        decl = decl.replace("typedef struct RgSkinnedScene {", "").strip()
+        if not decl:
+            continue
+        parts = [p.strip() for p in decl.split(",")]
+        names.append(re.split(r"[\s\*]+", parts[0])[-1])
+        names += [p.lstrip("* ").strip() for p in parts[1:]]
+    assert names == [n for n, _ in _lib.RgSkinnedScene._fields_]
+
+
+def test_render_result_computes_the_visibility_filter_on_demand():
+    import pytest
+    import torch
+    from riggs_b200.fused import _RenderResult
+    out = _RenderResult({"radii": torch.tensor([0, 3, 0, 7], dtype=torch.int32), "render": torch.zeros(3, 2, 2)})
+    assert "visibility_filter" in out and not dict.__contains__(out, "visibility_filter")
+    vis = out["visibility_filter"]
+    assert vis.tolist() == [False, True, False, True] and out.get("visibility_filter") is vis
+    assert out.get("missing", 5) == 5 and "missing" not in out
+    with pytest.raises(KeyError):
+        out["missing"]
