@@ -76,11 +76,25 @@ int rg_skinned_forward(const RgSkinnedScene* s, const RgWorkspace* w, float* out
     FkSlots fk(geom.fk);
     const BinPlan bp = make_bin_plan(P, grid_x, grid_y);
 
+    // The forward's three zero-fills run on a side stream (a parallel branch of a captured graph) instead of between
+    // the kernels of the chain: the sort's control words must be clean before the preprocess kernel counts digits into
+    // them, the tile totals before the column sums, the survivor bitmaps before the blend.
+    SideStream* side = side_stream();
+    PreprocessArgs pa = {};
+    if (side) {
+        cudaEventRecord(side->fork, stream);
+        cudaStreamWaitEvent(side->stream, side->fork, 0);
+        pa.sort_hist = depth_sort_prepare(geom.sort_temp, P, side->stream);
+        cudaEventRecord(side->join_a, side->stream);
+        cudaMemsetAsync(geom.tile_base, 0, sizeof(uint32_t) * bp.T, side->stream);
+        cudaMemsetAsync(bin.surv_mask, 0, bin.surv_mask_bytes, side->stream);
+        cudaEventRecord(side->join_b, side->stream);
+    }
+
     if (launch_fk_forward(1, s->J, s->local_rot, s->global_trans, s->joints, s->parents, fk.G, fk.node_rot,
                           d_nodes ? d_nodes : fk.posed, stream))
         return -1;
 
-    PreprocessArgs pa = {};
     pa.P = P; pa.D = s->sh_degree; pa.M = s->M_rest + 1;
     pa.scale_modifier = s->scale_modifier;
     pa.viewmatrix = s->viewmatrix; pa.projmatrix = s->projmatrix; pa.cam_pos = s->campos;
@@ -93,7 +107,8 @@ int rg_skinned_forward(const RgSkinnedScene* s, const RgWorkspace* w, float* out
     SkinFuseArgs f = fuse_args(s, geom, fk);
     f.dbg_scales = dbg_scales; f.dbg_rotations = dbg_rotations; f.dbg_opacities = dbg_opacities;
     if (dbg_rotations && !al16(dbg_rotations)) { set_error("rg_skinned_forward: dbg_rotations must be 16-byte aligned"); return -1; }
-    pa.sort_hist = depth_sort_prepare(geom.sort_temp, P, stream);  // the preprocess kernel counts the sort's digits
+    if (side) cudaStreamWaitEvent(stream, side->join_a, 0);
+    else pa.sort_hist = depth_sort_prepare(geom.sort_temp, P, stream);  // the preprocess kernel counts the sort's digits
     if (launch_skin_preprocess(pa, f, stream)) return -1;
 
     if (launch_depth_sort(geom.sort_temp, geom.sort_temp_bytes, geom.depths, geom.sorted_keys, geom.ids, geom.sorted_ids, P, stream,
@@ -104,13 +119,14 @@ int rg_skinned_forward(const RgSkinnedScene* s, const RgWorkspace* w, float* out
                           split_i, split_n))
         return -1;
     // nobody reads num_rendered on the host here, so the prefix over the tiles rides along with the column scans
-    launch_tile_offsets_a(bp, geom.Mg, geom.S, geom.tile_base, img.ranges, geom.tile_order, geom.status, cap, stream, false);
+    if (side) cudaStreamWaitEvent(stream, side->join_b, 0);
+    launch_tile_offsets_a(bp, geom.Mg, geom.S, geom.tile_base, img.ranges, geom.tile_order, geom.status, cap, stream, false, side != nullptr);
     launch_tile_scatter(bp, P, grid_x, grid_y, geom.sorted_ids, geom.rects, geom.M, geom.Mg, geom.S,
                         geom.tile_base, geom.E, bin.point_list, cap, stream, true, img.ranges, geom.tile_order, geom.status, split_n);
 
     BlendFwdArgs fa;
     fa.W = W; fa.H = H; fa.grid_x = grid_x; fa.grid_y = grid_y; fa.split_i = split_i; fa.split_n = split_n;
-    cudaMemsetAsync(bin.surv_mask, 0, bin.surv_mask_bytes, stream);
+    if (!side) cudaMemsetAsync(bin.surv_mask, 0, bin.surv_mask_bytes, stream);
     fa.ranges = img.ranges; fa.point_list = bin.point_list; fa.surv_mask = bin.surv_mask; fa.surv_stride = bin.surv_stride; fa.rec = geom.rec; fa.tile_order = geom.tile_order;
     fa.bg = s->background;
     fa.out_color = out_color; fa.out_depth = out_depth; fa.out_alpha = out_alpha; fa.n_contrib = img.n_contrib;

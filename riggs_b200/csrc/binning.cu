@@ -457,10 +457,11 @@ int launch_tile_count(const BinPlan& b, int P, int grid_x, int grid_y, const uin
 }
 
 int launch_tile_offsets_a(const BinPlan& b, const uint16_t* Mg, uint32_t* S, uint32_t* tile_base, uint2* ranges,
-                          uint32_t* tile_order, uint32_t* status, uint32_t capacity, cudaStream_t stream, bool with_base) {
+                          uint32_t* tile_order, uint32_t* status, uint32_t capacity, cudaStream_t stream, bool with_base,
+                          bool base_zeroed) {
     LaunchScope ls("tile_offsets", stream, with_base ? 2 : 1);
     dim3 g((b.T + 255) / 256, b.nseg);
-    cudaMemsetAsync(tile_base, 0, sizeof(uint32_t) * b.T, stream);
+    if (!base_zeroed) cudaMemsetAsync(tile_base, 0, sizeof(uint32_t) * b.T, stream);  // (the fused entry zeroes it on its side stream)
     seg_sum_kernel<<<g, 256, 0, stream>>>(b.T, b.Tpad, b.NG, Mg, S, tile_base);
     if (with_base) tile_base_kernel<<<1, 1024, 0, stream>>>(b.T, tile_base, ranges, tile_order, status, capacity);
     return 0;

@@ -32,6 +32,15 @@ private:
 // process that drives several GPUs gets it on each of them.  Returns 0, or -1 with the error text set.
 int ensure_dyn_smem(const void* func, int bytes);
 
+// A second stream (and three events) per (host thread, device) for work that need not sit in the launching stream's
+// chain: fork with cudaEventRecord(fork, main) + cudaStreamWaitEvent(side, fork), join with an event recorded on `side`.
+// Under stream capture the fork / join become parallel branches of the graph.  Null when the stream cannot be made.
+struct SideStream {
+    cudaStream_t stream;
+    cudaEvent_t fork, join_a, join_b;
+};
+SideStream* side_stream();
+
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 __device__ __forceinline__ size_t align_up_dev(size_t x, size_t a) { return (x + a - 1) / a * a; }
 

@@ -116,7 +116,8 @@ int launch_tile_count(const BinPlan& b, int P, int grid_x, int grid_y, const uin
                       uint16_t* Mg, cudaStream_t stream, int split_i = 0, int split_n = 1);  // split: see tile_count_kernel
 // segment sums + tile bases + ranges + tile launch order (longest lists first) + status[0] = num_rendered, status[1] = overflow flag
 int launch_tile_offsets_a(const BinPlan& b, const uint16_t* Mg, uint32_t* S, uint32_t* tile_base, uint2* ranges,
-                          uint32_t* tile_order, uint32_t* status, uint32_t capacity, cudaStream_t stream, bool with_base = true);
+                          uint32_t* tile_order, uint32_t* status, uint32_t capacity, cudaStream_t stream, bool with_base = true,
+                          bool base_zeroed = false);
 int launch_tile_scatter(const BinPlan& b, int P, int grid_x, int grid_y, const uint32_t* sorted_ids,
                         const uint2* rects, const uint16_t* M, const uint16_t* Mg,
                         const uint32_t* S, uint32_t* tile_base, uint32_t* E, uint32_t* point_list,

@@ -47,6 +47,21 @@ LaunchScope::~LaunchScope() {
     }
 }
 
+SideStream* side_stream() {
+    thread_local std::map<int, SideStream> streams;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
+    auto it = streams.find(dev);
+    if (it != streams.end()) return &it->second;
+    SideStream s = {};
+    if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    if (cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s.join_a, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s.join_b, cudaEventDisableTiming) != cudaSuccess)
+        return nullptr;
+    return &streams.emplace(dev, s).first->second;
+}
+
 int ensure_dyn_smem(const void* func, int bytes) {
     static std::mutex mu;
     static std::set<std::pair<const void*, int>> done;
