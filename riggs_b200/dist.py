@@ -271,6 +271,10 @@ class ViewSplit:
     accumulators (10 floats per Gaussian) are summed over the ranks, and the per-Gaussian + skeleton backward then runs
     replicated, so every rank ends with the full, identical parameter gradients: no further all-reduce.
 
+    Every forward and backward contains one collective, so the ranks must issue the same sequence of frames: size the
+    instance buffers on every rank before capturing graphs (``HotPath.measure_instances`` / ``fused.measure_instances``) --
+    a re-capture that an overflow triggers on one rank alone would leave the others waiting in a barrier.
+
     ``index`` / ``count`` default to the process group's rank / world size; explicit values without a process group give
     one part of an emulated split on a single GPU (tests sum the parts themselves through ``images`` / ``grad2d``)."""
 
